@@ -1,0 +1,490 @@
+// feelgpu_api.cu -- implementation of the C ABI declared in include/feelgpu.h.
+#include "feelgpu_internal.h"
+
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+static std::string g_create_error;
+
+#define CTX_CUDA(ctx, call) FEELGPU_CHECK_CUDA(ctx, call)
+#define ARG_FAIL(ctx, msg)             \
+    do {                               \
+        (ctx)->last_error = (msg);     \
+        return FEELGPU_ERR_ARG;        \
+    } while (0)
+
+extern "C" {
+
+int feelgpu_context_create(int device, feelgpu_context_t* out)
+{
+    if (!out) return FEELGPU_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t err = cudaGetDeviceCount(&ndev);
+    if (err != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no CUDA device: ") + (err != cudaSuccess ? cudaGetErrorString(err) : "device count is 0");
+        return FEELGPU_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) {
+        g_create_error = "device index out of range";
+        return FEELGPU_ERR_ARG;
+    }
+    feelgpu_context_t ctx = new (std::nothrow) feelgpu_context_s;
+    if (!ctx) return FEELGPU_ERR_ARG;
+    ctx->device = device;
+    if ((err = cudaSetDevice(device)) != cudaSuccess || (err = cudaStreamCreate(&ctx->stream)) != cudaSuccess ||
+        (err = cudaMalloc(&ctx->d_flag, sizeof(int))) != cudaSuccess) {
+        g_create_error = cudaGetErrorString(err);
+        delete ctx;
+        return FEELGPU_ERR_CUDA;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
+    for (int k = 0; k < 4; ++k) cudaEventCreate(&ctx->ev[k]);
+    *out = ctx;
+    return FEELGPU_OK;
+}
+
+int feelgpu_context_destroy(feelgpu_context_t ctx)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (auto& e : ctx->table_cache) cudaFree(e.dev);
+    for (int k = 0; k < 4; ++k)
+        if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+    if (ctx->d_flag) cudaFree(ctx->d_flag);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return FEELGPU_OK;
+}
+
+const char* feelgpu_last_error(feelgpu_context_t ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
+
+int feelgpu_sync(feelgpu_context_t ctx)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    CTX_CUDA(ctx, cudaDeviceSynchronize());
+    return FEELGPU_OK;
+}
+
+// ---- mesh ------------------------------------------------------------------------------------------------------
+static int upload_points(feelgpu_mesh_t m, const double* xyz, cudaStream_t s)
+{
+    feelgpu_context_t ctx = m->ctx;
+    for (int64_t p = 0; p < m->nPts; ++p) {
+        m->h_stage[4 * p + 0] = xyz[3 * p + 0];
+        m->h_stage[4 * p + 1] = xyz[3 * p + 1];
+        m->h_stage[4 * p + 2] = xyz[3 * p + 2];
+        m->h_stage[4 * p + 3] = 0.0;
+    }
+    CTX_CUDA(ctx, cudaMemcpyAsync(m->d_xyz, m->h_stage, sizeof(double) * 4 * m->nPts, cudaMemcpyHostToDevice, s));
+    return FEELGPU_OK;
+}
+
+int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz, int64_t nElt, const int32_t* conn,
+                        feelgpu_mesh_t* out)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!out || !xyz || !conn || nPts <= 0 || nElt < 0) ARG_FAIL(ctx, "mesh_create: bad argument");
+    if (nPts >= (int64_t)1 << 31) ARG_FAIL(ctx, "mesh_create: more than 2^31 points");
+    for (int64_t k = 0; k < 4 * nElt; ++k)
+        if (conn[k] < 0 || conn[k] >= nPts) ARG_FAIL(ctx, "mesh_create: connectivity entry outside [0,nPts)");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    feelgpu_mesh_t m = new feelgpu_mesh_s;
+    m->ctx = ctx;
+    m->nPts = nPts;
+    m->nElt = nElt;
+    cudaError_t err;
+    if ((err = cudaMalloc(&m->d_xyz, sizeof(double) * 4 * nPts)) != cudaSuccess ||
+        (err = cudaMalloc(&m->d_conn, sizeof(int4) * std::max<int64_t>(nElt, 1))) != cudaSuccess ||
+        (err = cudaMallocHost(&m->h_stage, sizeof(double) * 4 * nPts)) != cudaSuccess) {
+        ctx->last_error = std::string("mesh_create: ") + cudaGetErrorString(err);
+        feelgpu_mesh_destroy(m);
+        return FEELGPU_ERR_CUDA;
+    }
+    int rc = upload_points(m, xyz, ctx->stream);
+    if (rc) { feelgpu_mesh_destroy(m); return rc; }
+    err = cudaMemcpyAsync(m->d_conn, conn, sizeof(int32_t) * 4 * nElt, cudaMemcpyHostToDevice, ctx->stream);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(ctx->stream);
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("mesh_create: ") + cudaGetErrorString(err);
+        feelgpu_mesh_destroy(m);
+        return FEELGPU_ERR_CUDA;
+    }
+    *out = m;
+    return FEELGPU_OK;
+}
+
+int feelgpu_mesh_update_points(feelgpu_mesh_t m, const double* xyz, void* stream)
+{
+    if (!m) return FEELGPU_ERR_ARG;
+    if (!xyz) ARG_FAIL(m->ctx, "mesh_update_points: null xyz");
+    cudaStream_t s = stream ? (cudaStream_t)stream : m->ctx->stream;
+    // the pinned staging buffer is reused: wait for a previous upload on this stream to finish first
+    CTX_CUDA(m->ctx, cudaStreamSynchronize(s));
+    return upload_points(m, xyz, s);
+}
+
+int feelgpu_mesh_destroy(feelgpu_mesh_t m)
+{
+    if (!m) return FEELGPU_ERR_ARG;
+    if (m->d_xyz) cudaFree(m->d_xyz);
+    if (m->d_conn) cudaFree(m->d_conn);
+    if (m->h_stage) cudaFreeHost(m->h_stage);
+    delete m;
+    return FEELGPU_OK;
+}
+
+// ---- space -----------------------------------------------------------------------------------------------------
+int feelgpu_space_create(feelgpu_context_t ctx, feelgpu_mesh_t mesh, int order, int ncomp, const int32_t* l2g,
+                         int64_t nWithGhost, int64_t nOwned, const int64_t* p2c, feelgpu_space_t* out)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!mesh || !l2g || !out) ARG_FAIL(ctx, "space_create: bad argument");
+    if (order < 1 || order > 3) { ctx->last_error = "space_create: Lagrange order must be 1, 2 or 3"; return FEELGPU_ERR_UNSUPPORTED; }
+    if (ncomp != 1 && ncomp != 3) { ctx->last_error = "space_create: ncomp must be 1 or 3"; return FEELGPU_ERR_UNSUPPORTED; }
+    if (nOwned < 0 || nOwned > nWithGhost || nWithGhost >= (int64_t)1 << 31) ARG_FAIL(ctx, "space_create: bad dof counts");
+    const int n = (order + 1) * (order + 2) * (order + 3) / 6, nd = n * ncomp;
+    for (int64_t e = 0; e < mesh->nElt; ++e)
+        for (int i = 0; i < n; ++i) {
+            int32_t g0 = l2g[e * nd + i];
+            if (g0 < 0 || g0 + ncomp - 1 >= nWithGhost) ARG_FAIL(ctx, "space_create: dof id outside [0,nDofLocalWithGhost)");
+            // product spaces: local = n*c + i, global = base + c (feeldiscr/doftable.hpp:1289-1299)
+            for (int c = 1; c < ncomp; ++c)
+                if (l2g[e * nd + n * c + i] != g0 + c) {
+                    ctx->last_error = "space_create: vector dofs must be interleaved (global = ncomp*node + c)";
+                    return FEELGPU_ERR_UNSUPPORTED;
+                }
+        }
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    feelgpu_space_t sp = new feelgpu_space_s;
+    sp->ctx = ctx;
+    sp->mesh = mesh;
+    sp->order = order;
+    sp->ncomp = ncomp;
+    sp->n = n;
+    sp->nd = nd;
+    sp->nDofWithGhost = nWithGhost;
+    sp->nDofOwned = nOwned;
+    cudaError_t err = cudaMalloc(&sp->d_l2g, sizeof(int32_t) * std::max<int64_t>(mesh->nElt * nd, 1));
+    if (err == cudaSuccess) err = cudaMemcpy(sp->d_l2g, l2g, sizeof(int32_t) * mesh->nElt * nd, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess && p2c) {
+        err = cudaMalloc(&sp->d_p2c, sizeof(int64_t) * std::max<int64_t>(nWithGhost, 1));
+        if (err == cudaSuccess) err = cudaMemcpy(sp->d_p2c, p2c, sizeof(int64_t) * nWithGhost, cudaMemcpyHostToDevice);
+    }
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("space_create: ") + cudaGetErrorString(err);
+        feelgpu_space_destroy(sp);
+        return FEELGPU_ERR_CUDA;
+    }
+    *out = sp;
+    return FEELGPU_OK;
+}
+
+int feelgpu_space_destroy(feelgpu_space_t sp)
+{
+    if (!sp) return FEELGPU_ERR_ARG;
+    if (sp->d_l2g) cudaFree(sp->d_l2g);
+    if (sp->d_p2c) cudaFree(sp->d_p2c);
+    delete sp;
+    return FEELGPU_OK;
+}
+
+// ---- pattern ---------------------------------------------------------------------------------------------------
+int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_space_t trial, int64_t nRows,
+                           const int64_t* ia, const int64_t* ja, int flags, feelgpu_pattern_t* out)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!test || !trial || !ia || !ja || !out || nRows < 0) ARG_FAIL(ctx, "pattern_create: bad argument");
+    if (test->mesh != trial->mesh) ARG_FAIL(ctx, "pattern_create: test and trial spaces live on different meshes");
+    if (test->n != trial->n || test->ncomp != trial->ncomp) {
+        ctx->last_error = "pattern_create: test and trial spaces must have the same order and components";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    if (nRows > test->nDofWithGhost) ARG_FAIL(ctx, "pattern_create: more rows than local test dofs");
+    if (ia[0] != 0) ARG_FAIL(ctx, "pattern_create: ia[0] != 0");
+    for (int64_t r = 0; r < nRows; ++r)
+        if (ia[r + 1] < ia[r]) ARG_FAIL(ctx, "pattern_create: ia not monotone");
+    if (flags == 0) flags = FEELGPU_PATTERN_SLOTMAP | FEELGPU_PATTERN_ROWPLAN;
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    feelgpu_pattern_t pat = new feelgpu_pattern_s;
+    pat->ctx = ctx;
+    pat->test = test;
+    pat->trial = trial;
+    pat->nRows = nRows;
+    pat->nnz = ia[nRows];
+    const int n = test->n;
+    const int64_t nElt = test->mesh->nElt;
+    int64_t* d_ja = nullptr;
+    cudaError_t err = cudaMalloc(&pat->d_ia, sizeof(int64_t) * (nRows + 1));
+    if (err == cudaSuccess) err = cudaMemcpy(pat->d_ia, ia, sizeof(int64_t) * (nRows + 1), cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) err = cudaMalloc(&d_ja, sizeof(int64_t) * std::max<int64_t>(pat->nnz, 1));
+    if (err == cudaSuccess) err = cudaMemcpy(d_ja, ja, sizeof(int64_t) * pat->nnz, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess) err = cudaMalloc(&pat->d_pos, sizeof(uint16_t) * std::max<int64_t>(nElt * n * n, 1));
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("pattern_create: ") + cudaGetErrorString(err);
+        if (d_ja) cudaFree(d_ja);
+        feelgpu_pattern_destroy(pat);
+        return FEELGPU_ERR_CUDA;
+    }
+    int rc = feelgpu_launch_build_pos(pat, d_ja, ctx->stream);
+    cudaFree(d_ja); // the column array is only needed to build the maps
+    if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_ROWPLAN)) rc = feelgpu_rowplan_build(pat, ia, ja);
+    if (rc != FEELGPU_OK) {
+        feelgpu_pattern_destroy(pat);
+        return rc;
+    }
+    *out = pat;
+    return FEELGPU_OK;
+}
+
+int feelgpu_pattern_nnz(feelgpu_pattern_t pat, int64_t* nnz)
+{
+    if (!pat || !nnz) return FEELGPU_ERR_ARG;
+    *nnz = pat->nnz;
+    return FEELGPU_OK;
+}
+
+int feelgpu_pattern_destroy(feelgpu_pattern_t pat)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_rowplan_destroy(pat);
+    if (pat->d_ia) cudaFree(pat->d_ia);
+    if (pat->d_pos) cudaFree(pat->d_pos);
+    delete pat;
+    return FEELGPU_OK;
+}
+
+// ---- work calls ------------------------------------------------------------------------------------------------
+static int fill_params(feelgpu_context_t ctx, int kind, const feelgpu_coeff& c, const feelgpu_tables& t,
+                       feelgpu_space_t sp, bool form2, FormParams* hp)
+{
+    std::memset(hp, 0, sizeof(FormParams));
+    if (!t.w || !t.xi || !t.phi || t.nq < 1 || t.nq > FEELGPU_MAX_NQ) ARG_FAIL(ctx, "assemble: bad tables (nq must be in [1,64])");
+    if (t.n != sp->n) ARG_FAIL(ctx, "assemble: tables.n does not match the space");
+    if (form2 && kind != FEELGPU_FORM2_MASS && !t.dphi) ARG_FAIL(ctx, "assemble: tables.dphi is required");
+    hp->kind = kind;
+    hp->coeff_kind = c.kind;
+    hp->n = t.n;
+    hp->nq = t.nq;
+    hp->ncomp = sp->ncomp;
+    hp->cval[0] = c.value[0];
+    hp->cval[1] = c.value[1];
+    hp->cval[2] = c.value[2];
+    hp->lambda = c.lambda;
+    hp->mu = c.mu;
+    std::memcpy(hp->w, t.w, sizeof(double) * t.nq);
+    std::memcpy(hp->xi, t.xi, sizeof(double) * 3 * t.nq);
+    if (form2 && kind == FEELGPU_FORM2_ELASTICITY) {
+        if (sp->ncomp != 3) { ctx->last_error = "elasticity needs a 3-component space"; return FEELGPU_ERR_UNSUPPORTED; }
+        hp->coeff_kind = FEELGPU_COEFF_CONST;
+        return FEELGPU_OK;
+    }
+    switch (c.kind) {
+    case FEELGPU_COEFF_CONST: break;
+    case FEELGPU_COEFF_FIELD:
+        if (!c.field_space || !c.field_values || c.field_space->ncomp != 1 || c.field_space->mesh != sp->mesh)
+            ARG_FAIL(ctx, "assemble: FIELD coefficient needs a scalar space on the same mesh and device values");
+        if (t.nf != c.field_space->n || !t.phif) ARG_FAIL(ctx, "assemble: tables.phif/nf do not match the field space");
+        hp->nf = t.nf;
+        break;
+    case FEELGPU_COEFF_EXPR:
+        if (c.expr_len < 1 || c.expr_len > FEELGPU_EXPR_MAX_LEN || !c.expr_ops || !c.expr_consts)
+            ARG_FAIL(ctx, "assemble: bad EXPR program");
+        {
+            int sp_ = 0, maxsp = 0; // validate the postfix program's stack discipline
+            for (int k = 0; k < c.expr_len; ++k) {
+                int op = c.expr_ops[k];
+                if (op >= FEELGPU_OP_X && op <= FEELGPU_OP_CONST) sp_++;
+                else if ((op >= FEELGPU_OP_ADD && op <= FEELGPU_OP_DIV) || op == FEELGPU_OP_POW) sp_--;
+                else if (op < 0 || op > FEELGPU_OP_POW) ARG_FAIL(ctx, "assemble: unknown EXPR opcode");
+                if (sp_ < 1) ARG_FAIL(ctx, "assemble: EXPR stack underflow");
+                maxsp = std::max(maxsp, sp_);
+            }
+            if (sp_ != 1 || maxsp > 16) ARG_FAIL(ctx, "assemble: EXPR must leave one value and use <= 16 stack slots");
+        }
+        hp->expr_len = c.expr_len;
+        std::memcpy(hp->expr_ops, c.expr_ops, sizeof(int32_t) * c.expr_len);
+        std::memcpy(hp->expr_consts, c.expr_consts, sizeof(double) * c.expr_len);
+        break;
+    default: ARG_FAIL(ctx, "assemble: unknown coefficient kind");
+    }
+    if (sp->ncomp > 1 && c.kind != FEELGPU_COEFF_CONST) {
+        ctx->last_error = "assemble: vector spaces support constant coefficients only";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    return FEELGPU_OK;
+}
+
+int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc, int accumulate, double* a,
+                           void* stream)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = pat->ctx;
+    if (!desc || !a) ARG_FAIL(ctx, "form2_assemble: null argument");
+    if (desc->kind < FEELGPU_FORM2_MASS || desc->kind > FEELGPU_FORM2_ELASTICITY) {
+        ctx->last_error = "form2_assemble: unknown form kind";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    FormParams hp;
+    int rc = fill_params(ctx, desc->kind, desc->coeff, desc->tables, pat->test, true, &hp);
+    if (rc) return rc;
+    int algo = desc->algorithm;
+    if (algo == FEELGPU_ALGO_AUTO) algo = feelgpu_rowplan_supports(pat, desc) ? FEELGPU_ALGO_ROWPLAN : FEELGPU_ALGO_SCATTER;
+    if (algo == FEELGPU_ALGO_ROWPLAN && !feelgpu_rowplan_supports(pat, desc)) {
+        ctx->last_error = "form2_assemble: the owner-computes plan does not cover this form/pattern";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    if (ctx->timing) cudaEventRecord(ctx->ev[0], s);
+    if (algo == FEELGPU_ALGO_ROWPLAN) {
+        if (ctx->timing) cudaEventRecord(ctx->ev[1], s);
+        rc = feelgpu_launch_form2_rowplan(pat, hp, desc, accumulate, a, s);
+    } else {
+        if (!accumulate) CTX_CUDA(ctx, cudaMemsetAsync(a, 0, sizeof(double) * pat->nnz, s));
+        if (ctx->timing) cudaEventRecord(ctx->ev[1], s);
+        rc = feelgpu_launch_form2_scatter(pat, hp, desc, a, s);
+    }
+    if (ctx->timing) cudaEventRecord(ctx->ev[2], s);
+    return rc;
+}
+
+int feelgpu_form1_assemble(feelgpu_space_t sp, const feelgpu_form1_desc* desc, int accumulate, double* b, void* stream)
+{
+    if (!sp) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = sp->ctx;
+    if (!desc || !b) ARG_FAIL(ctx, "form1_assemble: null argument");
+    if (desc->kind != FEELGPU_FORM1_SOURCE) {
+        ctx->last_error = "form1_assemble: unknown form kind";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    FormParams hp;
+    int rc = fill_params(ctx, desc->kind, desc->coeff, desc->tables, sp, false, &hp);
+    if (rc) return rc;
+    if (!accumulate) CTX_CUDA(ctx, cudaMemsetAsync(b, 0, sizeof(double) * sp->nDofWithGhost, s));
+    return feelgpu_launch_form1(sp, hp, desc, b, s);
+}
+
+int feelgpu_form2_assemble_host(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc, int accumulate, double* a_host)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = pat->ctx;
+    if (!a_host) ARG_FAIL(ctx, "form2_assemble_host: null output");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    double* d = nullptr;
+    CTX_CUDA(ctx, cudaMalloc(&d, sizeof(double) * std::max<int64_t>(pat->nnz, 1)));
+    int rc = FEELGPU_OK;
+    cudaError_t err = cudaSuccess;
+    if (accumulate) err = cudaMemcpyAsync(d, a_host, sizeof(double) * pat->nnz, cudaMemcpyHostToDevice, ctx->stream);
+    if (err == cudaSuccess) rc = feelgpu_form2_assemble(pat, desc, accumulate, d, ctx->stream);
+    if (err == cudaSuccess && rc == FEELGPU_OK)
+        err = cudaMemcpyAsync(a_host, d, sizeof(double) * pat->nnz, cudaMemcpyDeviceToHost, ctx->stream);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("form2_assemble_host: ") + cudaGetErrorString(err);
+        return FEELGPU_ERR_CUDA;
+    }
+    return rc;
+}
+
+int feelgpu_form1_assemble_host(feelgpu_space_t sp, const feelgpu_form1_desc* desc, int accumulate, double* b_host)
+{
+    if (!sp) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = sp->ctx;
+    if (!b_host) ARG_FAIL(ctx, "form1_assemble_host: null output");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    double* d = nullptr;
+    CTX_CUDA(ctx, cudaMalloc(&d, sizeof(double) * std::max<int64_t>(sp->nDofWithGhost, 1)));
+    int rc = FEELGPU_OK;
+    cudaError_t err = cudaSuccess;
+    if (accumulate) err = cudaMemcpyAsync(d, b_host, sizeof(double) * sp->nDofWithGhost, cudaMemcpyHostToDevice, ctx->stream);
+    if (err == cudaSuccess) rc = feelgpu_form1_assemble(sp, desc, accumulate, d, ctx->stream);
+    if (err == cudaSuccess && rc == FEELGPU_OK)
+        err = cudaMemcpyAsync(b_host, d, sizeof(double) * sp->nDofWithGhost, cudaMemcpyDeviceToHost, ctx->stream);
+    if (err == cudaSuccess) err = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("form1_assemble_host: ") + cudaGetErrorString(err);
+        return FEELGPU_ERR_CUDA;
+    }
+    return rc;
+}
+
+// ---- memory helpers -----------------------------------------------------------------------------------------
+int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!dptr || bytes < 0) ARG_FAIL(ctx, "malloc: bad argument");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    CTX_CUDA(ctx, cudaMalloc(dptr, (size_t)std::max<int64_t>(bytes, 1)));
+    return FEELGPU_OK;
+}
+int feelgpu_free(feelgpu_context_t ctx, void* dptr)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    CTX_CUDA(ctx, cudaFree(dptr));
+    return FEELGPU_OK;
+}
+int feelgpu_memcpy_h2d(feelgpu_context_t ctx, void* dst, const void* src, int64_t bytes)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    CTX_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CTX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return FEELGPU_OK;
+}
+int feelgpu_memcpy_d2h(feelgpu_context_t ctx, void* dst, const void* src, int64_t bytes)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    CTX_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CTX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return FEELGPU_OK;
+}
+int feelgpu_host_alloc_pinned(feelgpu_context_t ctx, int64_t bytes, void** hptr)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!hptr || bytes < 0) ARG_FAIL(ctx, "host_alloc_pinned: bad argument");
+    CTX_CUDA(ctx, cudaMallocHost(hptr, (size_t)std::max<int64_t>(bytes, 1)));
+    return FEELGPU_OK;
+}
+int feelgpu_host_free_pinned(feelgpu_context_t ctx, void* hptr)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    CTX_CUDA(ctx, cudaFreeHost(hptr));
+    return FEELGPU_OK;
+}
+
+// ---- introspection -------------------------------------------------------------------------------------------
+int feelgpu_launch_count(feelgpu_context_t ctx, int64_t* count)
+{
+    if (!ctx || !count) return FEELGPU_ERR_ARG;
+    *count = ctx->launches;
+    return FEELGPU_OK;
+}
+int feelgpu_set_timing(feelgpu_context_t ctx, int enable)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    ctx->timing = enable != 0;
+    return FEELGPU_OK;
+}
+int feelgpu_last_timing(feelgpu_context_t ctx, double ms[3])
+{
+    if (!ctx || !ms) return FEELGPU_ERR_ARG;
+    if (!ctx->timing) ARG_FAIL(ctx, "last_timing: timing is disabled (feelgpu_set_timing)");
+    CTX_CUDA(ctx, cudaEventSynchronize(ctx->ev[2]));
+    float t01 = 0, t12 = 0;
+    CTX_CUDA(ctx, cudaEventElapsedTime(&t01, ctx->ev[0], ctx->ev[1]));
+    CTX_CUDA(ctx, cudaEventElapsedTime(&t12, ctx->ev[1], ctx->ev[2]));
+    ms[0] = t01;
+    ms[1] = t12;
+    ms[2] = 0;
+    return FEELGPU_OK;
+}
+
+} // extern "C"

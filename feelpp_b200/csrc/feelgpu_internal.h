@@ -1,0 +1,88 @@
+// feelgpu_internal.h -- device-side data layout shared by the C-ABI implementation and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/feelgpu.h"
+
+#define FEELGPU_MAX_NLOC 20   // P3 scalar local dofs
+#define FEELGPU_MAX_NQ 64
+
+struct feelgpu_context_s {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string last_error;
+    int64_t launches = 0;
+    bool timing = false;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    double last_ms[3] = {0, 0, 0};
+    int sm_count = 148;
+    int* d_flag = nullptr;       // device error flag (slot-map build)
+    struct TableEntry { std::vector<char> host; void* dev; };
+    std::vector<TableEntry> table_cache;   // parameter blocks + reference tables already on the device
+};
+
+struct feelgpu_mesh_s {
+    feelgpu_context_t ctx;
+    int64_t nPts = 0, nElt = 0;
+    double* d_xyz = nullptr;     // [nPts][4]: x,y,z,0 -- one 32-byte sector per vertex
+    int4* d_conn = nullptr;      // [nElt]
+    double* h_stage = nullptr;   // pinned staging for update_points
+};
+
+struct feelgpu_space_s {
+    feelgpu_context_t ctx;
+    feelgpu_mesh_t mesh;
+    int order = 1, ncomp = 1, n = 4, nd = 4;
+    int64_t nDofWithGhost = 0, nDofOwned = 0;
+    int32_t* d_l2g = nullptr;    // [nElt][nd]
+    int64_t* d_p2c = nullptr;    // process -> cluster ids, or null (identity)
+};
+
+struct RowPlan;  // kernels_rowplan.cu
+
+struct feelgpu_pattern_s {
+    feelgpu_context_t ctx;
+    feelgpu_space_t test, trial;
+    int64_t nRows = 0, nnz = 0;
+    int64_t* d_ia = nullptr;     // [nRows+1]
+    // element -> CSR position map, node level: pos[e][i][j] = position of column cluster(l2g_trial[e][j]) (component 0)
+    // inside row l2g_test[e][i] (component 0).  Full slot = ia[row + c1] + pos + c2 (components are interleaved:
+    // global = ncomp*node + c, feeldiscr/doftable.hpp:1289-1299).
+    uint16_t* d_pos = nullptr;   // [nElt][n][n]
+    RowPlan* plan = nullptr;
+};
+
+// parameter block copied to the device per assemble call
+struct FormParams {
+    int kind, coeff_kind, n, nq, nf, ncomp, expr_len, pad;
+    double cval[3];
+    double lambda, mu;
+    double w[FEELGPU_MAX_NQ];
+    double xi[FEELGPU_MAX_NQ * 3];
+    int32_t expr_ops[FEELGPU_EXPR_MAX_LEN];
+    double expr_consts[FEELGPU_EXPR_MAX_LEN];
+};
+
+#define FEELGPU_CHECK_CUDA(ctx, call)                                                                   \
+    do {                                                                                                \
+        cudaError_t err__ = (call);                                                                     \
+        if (err__ != cudaSuccess) {                                                                     \
+            (ctx)->last_error = std::string(#call) + ": " + cudaGetErrorString(err__);                  \
+            return FEELGPU_ERR_CUDA;                                                                    \
+        }                                                                                               \
+    } while (0)
+
+// ---- kernel launchers (kernels_scatter.cu) ----
+int feelgpu_launch_build_pos(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s);
+int feelgpu_launch_form2_scatter(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
+                                 double* a, cudaStream_t s);
+int feelgpu_launch_form1(feelgpu_space_t sp, const FormParams& hp, const feelgpu_form1_desc* desc, double* b,
+                         cudaStream_t s);
+// ---- kernels_rowplan.cu ----
+int feelgpu_rowplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, const int64_t* h_ja);
+void feelgpu_rowplan_destroy(feelgpu_pattern_t pat);
+int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
+                                 int accumulate, double* a, cudaStream_t s);
+bool feelgpu_rowplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);

@@ -1,0 +1,170 @@
+/* feelgpu.h -- C ABI of the B200 assembly engine.
+ *
+ * Drop-in boundary for the reference's element-range assembly path
+ *     form2(_test=Xh,_trial=Xh) [+]= integrate(_range=elements(mesh), _expr=...)
+ *     form1(_test=Xh)           [+]= integrate(_range=elements(mesh), _expr=...)
+ * (feelpp/feel/feelvf/form.hpp:92-147, integrate.hpp:64-98).  A Feel++-side adapter intercepts
+ * Integrator::assemble(form, MESH_ELEMENTS, same_mesh) (feelvf/integrator.hpp:975-1238) and calls these
+ * entry points instead of running the per-element update/integrate/assemble loop (integrator.hpp:1093-1207).
+ * See INTEGRATION.md for the adapter stub.
+ *
+ * Conventions: every function returns 0 on success or a FEELGPU_ERR_* code (no exceptions, no abort; the
+ * reference aborts through CHKERRABORT, feelalg/matrixpetsc.cpp:935); feelgpu_last_error() gives a message.
+ * Caller arrays passed to *_create are copied to the device during the call and may be freed afterwards.
+ * All work calls are asynchronous on the CUDA stream given (void* = cudaStream_t, NULL = the context's stream).
+ * There is no CPU fallback: without a CUDA device every call fails with FEELGPU_ERR_CUDA.
+ */
+#ifndef FEELGPU_H
+#define FEELGPU_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEELGPU_VERSION 100
+
+enum {
+    FEELGPU_OK = 0,
+    FEELGPU_ERR_ARG = 1,          /* bad argument                                                        */
+    FEELGPU_ERR_CUDA = 2,         /* CUDA runtime error (no device, launch failure, out of memory)       */
+    FEELGPU_ERR_NCCL = 3,         /* NCCL error                                                          */
+    FEELGPU_ERR_NOT_IN_PATTERN = 4, /* a (row,col) of an element is absent from the CSR graph: the analogue of
+                                     PETSc's MAT_NEW_NONZERO_ALLOCATION_ERR (feelalg/matrixpetsc.cpp:2688)  */
+    FEELGPU_ERR_UNSUPPORTED = 5   /* form / order / quadrature outside the supported set                 */
+};
+
+/* bilinear forms recognised on the path (feelvf/operators.hpp:134-153, operations.hpp:585-646, inner.hpp:374-420) */
+enum {
+    FEELGPU_FORM2_MASS = 0,       /* k * idt(u)*id(v)            / k*inner(idt(u),id(v)) on vector spaces         */
+    FEELGPU_FORM2_STIFFNESS = 1,  /* k * gradt(u)*trans(grad(v)) / k*inner(gradt(u),grad(v))                      */
+    FEELGPU_FORM2_ELASTICITY = 2  /* inner(lambda*trace(sym(gradt(u)))*Id + 2*mu*sym(gradt(u)), grad(v)), 3 comps */
+};
+/* linear forms (feelvf/linearformcontext.hpp:294-309) */
+enum {
+    FEELGPU_FORM1_SOURCE = 0      /* f*id(v) (scalar) / inner(f, id(v)) with a constant vector f (vector spaces)  */
+};
+/* coefficient kinds: cst(c), idv(k) for a Lagrange field, expr("...") (feelvf/detail/ginacexvf.hpp:750-848)     */
+enum { FEELGPU_COEFF_CONST = 0, FEELGPU_COEFF_FIELD = 1, FEELGPU_COEFF_EXPR = 2 };
+
+/* postfix program for closed-form coefficients, evaluated at xReal = G*N(xi_q) (feelpoly/geomap.hpp:1964-1969) */
+enum {
+    FEELGPU_OP_X = 0, FEELGPU_OP_Y = 1, FEELGPU_OP_Z = 2, FEELGPU_OP_CONST = 3,
+    FEELGPU_OP_ADD = 4, FEELGPU_OP_SUB = 5, FEELGPU_OP_MUL = 6, FEELGPU_OP_DIV = 7, FEELGPU_OP_NEG = 8,
+    FEELGPU_OP_SIN = 9, FEELGPU_OP_COS = 10, FEELGPU_OP_EXP = 11, FEELGPU_OP_LOG = 12, FEELGPU_OP_SQRT = 13,
+    FEELGPU_OP_POW = 14
+};
+#define FEELGPU_EXPR_MAX_LEN 64
+
+typedef struct feelgpu_context_s* feelgpu_context_t;
+typedef struct feelgpu_mesh_s* feelgpu_mesh_t;
+typedef struct feelgpu_space_s* feelgpu_space_t;
+typedef struct feelgpu_pattern_s* feelgpu_pattern_t;
+
+typedef struct {
+    int kind;                     /* FEELGPU_COEFF_*                                                            */
+    double value[3];              /* CONST: value[0]; form1 on vector spaces: the constant vector               */
+    feelgpu_space_t field_space;  /* FIELD: scalar Lagrange space of the field (same mesh)                      */
+    const double* field_values;   /* FIELD: DEVICE pointer, [nDofLocalWithGhost(field_space)]                    */
+    int expr_len;                 /* EXPR: program length (<= FEELGPU_EXPR_MAX_LEN)                             */
+    const int32_t* expr_ops;      /* EXPR: host pointer, opcodes                                                */
+    const double* expr_consts;    /* EXPR: host pointer, constant per op slot (read for FEELGPU_OP_CONST)       */
+    double lambda, mu;            /* ELASTICITY: Lame coefficients                                              */
+} feelgpu_coeff;
+
+/* reference tables the caller tabulated once on the host -- IMGeneral points/weights
+ * (feelpoly/pointsetquadrature.hpp:142-153) and PreCompute phi/grad (feelpoly/polynomialset.hpp:924-987) */
+typedef struct {
+    int nq;                       /* quadrature points                                                          */
+    const double* w;              /* [nq]                                                                       */
+    const double* xi;             /* [nq][3] reference points                                                   */
+    int n;                        /* scalar local dofs of the test=trial basis                                  */
+    const double* phi;            /* [n][nq]                                                                    */
+    const double* dphi;           /* [n][nq][3]                                                                 */
+    int nf;                       /* FIELD coefficient: local dofs of the field basis (0 otherwise)             */
+    const double* phif;           /* [nf][nq]                                                                   */
+} feelgpu_tables;
+
+typedef struct {
+    int kind;                     /* FEELGPU_FORM2_*                                                            */
+    feelgpu_coeff coeff;
+    feelgpu_tables tables;
+    int algorithm;                /* FEELGPU_ALGO_*                                                             */
+} feelgpu_form2_desc;
+
+typedef struct {
+    int kind;                     /* FEELGPU_FORM1_*                                                            */
+    feelgpu_coeff coeff;
+    feelgpu_tables tables;
+} feelgpu_form1_desc;
+
+/* assembly algorithms for form2 */
+enum {
+    FEELGPU_ALGO_AUTO = 0,        /* owner-computes plan when the pattern has one, else scatter                  */
+    FEELGPU_ALGO_SCATTER = 1,     /* element loop + red.global.add.f64 through the element->CSR-slot map         */
+    FEELGPU_ALGO_ROWPLAN = 2      /* owner-computes: every CSR value is produced by one thread and stored once  */
+};
+/* flags of feelgpu_pattern_create */
+enum { FEELGPU_PATTERN_SLOTMAP = 1, FEELGPU_PATTERN_ROWPLAN = 2 };
+
+/* ---- context ------------------------------------------------------------------------------------------------ */
+int feelgpu_context_create(int device, feelgpu_context_t* ctx);
+int feelgpu_context_destroy(feelgpu_context_t ctx);
+const char* feelgpu_last_error(feelgpu_context_t ctx);   /* ctx may be NULL: error of the failed context_create */
+int feelgpu_sync(feelgpu_context_t ctx);
+
+/* ---- mesh: element connectivity + vertex coordinates (replaces elt.point(i).id(), elt.G(): feelmesh/geond.hpp:626) */
+int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz /*[nPts][3]*/, int64_t nElt,
+                        const int32_t* conn /*[nElt][4]*/, feelgpu_mesh_t* mesh);
+int feelgpu_mesh_update_points(feelgpu_mesh_t mesh, const double* xyz /*host [nPts][3]*/, void* stream);
+int feelgpu_mesh_destroy(feelgpu_mesh_t mesh);
+
+/* ---- space: flattened DofTable (replaces DofTable::localToGlobalIndices, feeldiscr/doftable.hpp:732-750) ------ */
+int feelgpu_space_create(feelgpu_context_t ctx, feelgpu_mesh_t mesh, int order, int ncomp,
+                         const int32_t* l2g /*[nElt][ncomp*n] process-local dof ids, local index = n*c+i*/,
+                         int64_t nDofLocalWithGhost, int64_t nDofOwned,
+                         const int64_t* proc2cluster /*[nDofLocalWithGhost] or NULL = identity (datamap.hpp:467)*/,
+                         feelgpu_space_t* space);
+int feelgpu_space_destroy(feelgpu_space_t space);
+
+/* ---- pattern: the host-built CSR graph (GraphCSR::ia()/ja(), feelalg/graphcsr.hpp:287-295) ------------------- */
+/* Builds on the device the element->CSR-slot map (and, with FEELGPU_PATTERN_ROWPLAN, the owner-computes plan).   */
+/* Rows are process-local dof ids (owned first, then ghosts: doftable.hpp:1975-2030); columns are global-cluster. */
+int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_space_t trial, int64_t nRows,
+                           const int64_t* ia /*[nRows+1]*/, const int64_t* ja /*[nnz], ascending per row*/,
+                           int flags, feelgpu_pattern_t* pattern);
+int feelgpu_pattern_nnz(feelgpu_pattern_t pattern, int64_t* nnz);
+int feelgpu_pattern_destroy(feelgpu_pattern_t pattern);
+
+/* ---- work calls (replace the loop integrator.hpp:1093-1207 + MatSetValues/VecSetValues ADD_VALUES) ----------- */
+/* accumulate = 0: operator=  (zero, then assemble: bilinearform.hpp:1368-1371); 1: operator+=                   */
+int feelgpu_form2_assemble(feelgpu_pattern_t pattern, const feelgpu_form2_desc* desc, int accumulate,
+                           double* a_values /*DEVICE [nnz], slot order == ja order*/, void* stream);
+int feelgpu_form1_assemble(feelgpu_space_t space, const feelgpu_form1_desc* desc, int accumulate,
+                           double* b /*DEVICE [nDofLocalWithGhost]*/, void* stream);
+/* end-to-end variants with HOST output buffers (what the adapter calls when the PETSc Mat/Vec lives on the host):
+ * assemble on the device, copy the values to a_host / b_host, synchronise.                                       */
+int feelgpu_form2_assemble_host(feelgpu_pattern_t pattern, const feelgpu_form2_desc* desc, int accumulate,
+                                double* a_host /*[nnz]*/);
+int feelgpu_form1_assemble_host(feelgpu_space_t space, const feelgpu_form1_desc* desc, int accumulate,
+                                double* b_host);
+
+/* ---- device memory helpers for callers without a CUDA runtime of their own ---------------------------------- */
+int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr);
+int feelgpu_free(feelgpu_context_t ctx, void* dptr);
+int feelgpu_memcpy_h2d(feelgpu_context_t ctx, void* dst, const void* src, int64_t bytes);
+int feelgpu_memcpy_d2h(feelgpu_context_t ctx, void* dst, const void* src, int64_t bytes);
+int feelgpu_host_alloc_pinned(feelgpu_context_t ctx, int64_t bytes, void** hptr);
+int feelgpu_host_free_pinned(feelgpu_context_t ctx, void* hptr);
+
+/* ---- introspection / measurement ----------------------------------------------------------------------------- */
+/* number of kernel launches issued by this context since creation (bench.py's gpu_launches)                      */
+int feelgpu_launch_count(feelgpu_context_t ctx, int64_t* count);
+/* device milliseconds of the last feelgpu_form2_assemble on its stream (CUDA events), per kernel class:
+ * ms[0] zero-fill, ms[1] main assembly kernel, ms[2] other                                                       */
+int feelgpu_last_timing(feelgpu_context_t ctx, double ms[3]);
+int feelgpu_set_timing(feelgpu_context_t ctx, int enable);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
