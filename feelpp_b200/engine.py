@@ -1,0 +1,249 @@
+"""Engine-side objects: context, device mirrors of mesh/space/pattern, and the form2/form1 objects.
+
+Everything here goes through the C ABI of include/feelgpu.h (libfeelgpu.so).  No computation happens in Python.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi as capi
+from . import hostmirror as hm
+from . import vf
+from ._capi import Coeff, Form1Desc, Form2Desc, Tables, c_dblp, c_i32p, c_i64p, check, ptr
+
+ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN = 0, 1, 2
+PATTERN_SLOTMAP, PATTERN_ROWPLAN = 1, 2
+
+
+class Engine:
+    """one context per GPU (feelgpu_context_create)."""
+
+    def __init__(self, device=0):
+        self.lib = capi.gpu()
+        self.ctx = C.c_void_p()
+        check(self.lib.feelgpu_context_create(device, C.byref(self.ctx)), None)
+        self._meshes, self._spaces = {}, {}
+
+    def close(self):
+        if self.ctx:
+            self.lib.feelgpu_context_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def sync(self):
+        check(self.lib.feelgpu_sync(self.ctx), self.ctx)
+
+    def launch_count(self):
+        n = C.c_int64()
+        check(self.lib.feelgpu_launch_count(self.ctx, C.byref(n)), self.ctx)
+        return n.value
+
+    # ---- device mirrors (cached per host object) ----
+    def mesh(self, mesh):
+        key = builtins_id(mesh)
+        if key not in self._meshes:
+            h = C.c_void_p()
+            check(self.lib.feelgpu_mesh_create(self.ctx, mesh.numPoints(), ptr(mesh.xyz, c_dblp), mesh.numElements(),
+                                               ptr(mesh.conn, c_i32p), C.byref(h)), self.ctx)
+            self._meshes[key] = (h, mesh)
+        return self._meshes[key][0]
+
+    def space(self, Xh):
+        key = builtins_id(Xh)
+        if key not in self._spaces:
+            h = C.c_void_p()
+            check(self.lib.feelgpu_space_create(self.ctx, self.mesh(Xh.mesh), Xh.order, Xh.ncomp,
+                                                ptr(Xh.l2g, c_i32p), Xh.nDof(), Xh.nDof(), None, C.byref(h)), self.ctx)
+            self._spaces[key] = (h, Xh)
+        return self._spaces[key][0]
+
+    # ---- raw device memory ----
+    def malloc(self, nbytes):
+        p = C.c_void_p()
+        check(self.lib.feelgpu_malloc(self.ctx, nbytes, C.byref(p)), self.ctx)
+        return p
+
+    def free(self, p):
+        check(self.lib.feelgpu_free(self.ctx, p), self.ctx)
+
+    def to_device(self, arr):
+        arr = np.ascontiguousarray(arr)
+        p = self.malloc(arr.nbytes)
+        check(self.lib.feelgpu_memcpy_h2d(self.ctx, p, arr.ctypes.data_as(C.c_void_p), arr.nbytes), self.ctx)
+        return p
+
+    def to_host(self, p, shape, dtype=np.float64):
+        out = np.empty(shape, dtype=dtype)
+        check(self.lib.feelgpu_memcpy_d2h(self.ctx, out.ctypes.data_as(C.c_void_p), p, out.nbytes), self.ctx)
+        return out
+
+
+def builtins_id(o):
+    import builtins
+    return builtins.id(o)
+
+
+class _Keep:
+    """keeps numpy buffers referenced by a ctypes descriptor alive"""
+
+    def __init__(self):
+        self.refs = []
+
+    def arr(self, a, typ):
+        a = np.ascontiguousarray(a)
+        self.refs.append(a)
+        return a.ctypes.data_as(typ)
+
+
+def _fill_tables(keep, order, quad_order, field_order=None):
+    xi, w = hm.im(quad_order)
+    phi, dphi = hm.tabulate(order, xi)
+    t = Tables()
+    t.nq, t.n = len(w), phi.shape[0]
+    t.w, t.xi = keep.arr(w, c_dblp), keep.arr(xi, c_dblp)
+    t.phi, t.dphi = keep.arr(phi, c_dblp), keep.arr(dphi, c_dblp)
+    t.nf, t.phif = 0, None
+    if field_order is not None:
+        phif, _ = hm.tabulate(field_order, xi)
+        t.nf, t.phif = phif.shape[0], keep.arr(phif, c_dblp)
+    return t
+
+
+def _fill_coeff(eng, keep, cl, c):
+    co = cl.coeff
+    c.kind = co.kind()
+    c.value[0] = co.scale
+    c.value[1] = c.value[2] = 0.0
+    if co.vector is not None:
+        for k in range(3):
+            c.value[k] = co.scale * co.vector[k]
+    c.lambda_, c.mu = cl.lam, cl.mu
+    if co.field is not None:
+        fe = co.field
+        c.field_space = eng.space(fe.space)
+        dv = eng.to_device(np.asarray(fe.values, dtype=np.float64) * co.scale)
+        keep.refs.append(("dev", dv))
+        c.field_values = dv
+    if co.prog is not None:
+        ops, consts = co.prog.ops, co.prog.consts
+        if co.scale != 1.0:  # fold the constant factor into the program: prog * scale
+            ops = np.concatenate([ops, np.array([3, 6], dtype=np.int32)])
+            consts = np.concatenate([consts, np.array([co.scale, 0.0])])
+        c.expr_len = len(ops)
+        c.expr_ops = keep.arr(ops.astype(np.int32), c_i32p)
+        c.expr_consts = keep.arr(consts.astype(np.float64), c_dblp)
+
+
+class BilinearForm:
+    """form2(_test=Xh,_trial=Xh): owns the CSR graph (host) and the device value array."""
+
+    def __init__(self, test, trial, engine, pattern_flags=0, algorithm=ALGO_AUTO):
+        if test is not trial:
+            raise NotImplementedError("test and trial spaces must be the same space on this path")
+        self.Xh, self.eng, self.algorithm = test, engine, algorithm
+        self.ia, self.ja = test.graph()
+        self.pat = C.c_void_p()
+        sp = engine.space(test)
+        check(engine.lib.feelgpu_pattern_create(engine.ctx, sp, sp, test.nDof(), ptr(self.ia, c_i64p),
+                                                ptr(self.ja, c_i64p), pattern_flags, C.byref(self.pat)), engine.ctx)
+        self.nnz = int(self.ia[-1])
+        self.d_values = engine.malloc(8 * max(self.nnz, 1))
+        self._zeroed = False
+        self.assign(None)
+
+    def _desc(self, integ, keep):
+        cl = vf.classify_form2(integ.expr, self.Xh.order)
+        qo = integ.quad if integ.quad is not None else cl.quad_order
+        d = Form2Desc()
+        d.kind = cl.kind
+        d.algorithm = self.algorithm
+        fo = cl.coeff.field.space.order if cl.coeff.field is not None else None
+        d.tables = _fill_tables(keep, self.Xh.order, qo, fo)
+        _fill_coeff(self.eng, keep, cl, d.coeff)
+        return d
+
+    def assign(self, integ):
+        """a = integrate(...): zero, then assemble (feelvf/bilinearform.hpp:1368-1371)."""
+        if integ is None:
+            z = np.zeros(max(self.nnz, 1))
+            check(self.eng.lib.feelgpu_memcpy_h2d(self.eng.ctx, self.d_values, z.ctypes.data_as(C.c_void_p), z.nbytes),
+                  self.eng.ctx)
+            return self
+        return self._assemble(integ, 0)
+
+    def __iadd__(self, integ):
+        """a += integrate(...) (feelvf/bilinearform.hpp:1458-1468)."""
+        return self._assemble(integ, 1)
+
+    def _assemble(self, integ, accumulate):
+        keep = _Keep()
+        d = self._desc(integ, keep)
+        check(self.eng.lib.feelgpu_form2_assemble(self.pat, C.byref(d), accumulate, self.d_values, None), self.eng.ctx)
+        self.eng.sync()
+        for r in keep.refs:
+            if isinstance(r, tuple):
+                self.eng.free(r[1])
+        return self
+
+    def assemble_host(self, integ, accumulate=0, out=None):
+        """end-to-end variant: values land in a host array (feelgpu_form2_assemble_host)."""
+        keep = _Keep()
+        d = self._desc(integ, keep)
+        if out is None:
+            out = np.zeros(max(self.nnz, 1))
+        check(self.eng.lib.feelgpu_form2_assemble_host(self.pat, C.byref(d), accumulate, ptr(out, c_dblp)), self.eng.ctx)
+        return out[:self.nnz]
+
+    def values(self):
+        return self.eng.to_host(self.d_values, max(self.nnz, 1))[:self.nnz]
+
+    def scipy(self):
+        import scipy.sparse as sps
+        return sps.csr_matrix((self.values(), self.ja, self.ia), shape=(self.Xh.nDof(), self.Xh.nDof()))
+
+
+class LinearForm:
+    """form1(_test=Xh)."""
+
+    def __init__(self, test, engine):
+        self.Xh, self.eng = test, engine
+        self.sp = engine.space(test)
+        self.d_values = engine.to_device(np.zeros(max(test.nDof(), 1)))
+
+    def _desc(self, integ, keep):
+        cl = vf.classify_form1(integ.expr, self.Xh.order)
+        qo = integ.quad if integ.quad is not None else cl.quad_order
+        d = Form1Desc()
+        d.kind = cl.kind
+        fo = cl.coeff.field.space.order if cl.coeff.field is not None else None
+        d.tables = _fill_tables(keep, self.Xh.order, qo, fo)
+        _fill_coeff(self.eng, keep, cl, d.coeff)
+        return d
+
+    def _assemble(self, integ, accumulate):
+        keep = _Keep()
+        d = self._desc(integ, keep)
+        check(self.eng.lib.feelgpu_form1_assemble(self.sp, C.byref(d), accumulate, self.d_values, None), self.eng.ctx)
+        self.eng.sync()
+        for r in keep.refs:
+            if isinstance(r, tuple):
+                self.eng.free(r[1])
+        return self
+
+    def assign(self, integ):
+        return self._assemble(integ, 0)
+
+    def __iadd__(self, integ):
+        return self._assemble(integ, 1)
+
+    def values(self):
+        return self.eng.to_host(self.d_values, max(self.Xh.nDof(), 1))[:self.Xh.nDof()]
+
+
+def form2(_test, _trial, engine, pattern_flags=0, algorithm=ALGO_AUTO):
+    """form2(_test=Xh,_trial=Xh) (feelvf/form.hpp:130-147): pattern COUPLED, matrix zeroed."""
+    return BilinearForm(_test, _trial, engine, pattern_flags, algorithm)
+
+
+def form1(_test, engine):
+    """form1(_test=Xh) (feelvf/form.hpp:92-106)."""
+    return LinearForm(_test, engine)

@@ -1,0 +1,124 @@
+// capi.cpp -- plain-C entry points of the host-side mirror, for the Python test/bench harness (ctypes).
+// These expose the pieces a Feel++ build already owns (mesh, DofTable, graph, reference tables); the engine itself
+// is reached through include/feelgpu.h only.
+#include <cstring>
+#include <exception>
+#include <stdexcept>
+#include <string>
+
+#include "doftable.hpp"
+#include "ginac.hpp"
+#include "lagrange.hpp"
+#include "mesh.hpp"
+#include "stencil.hpp"
+
+using namespace feelpp_b200;
+
+static thread_local std::string g_err;
+#define GUARD(body)                              \
+    try { body; return 0; }                      \
+    catch (std::exception const& e) { g_err = e.what(); return 1; }
+
+extern "C" {
+
+const char* feelhost_last_error() { return g_err.c_str(); }
+
+// ---- mesh ----
+int feelhost_unit_cube_sizes(int m, int64_t* nPts, int64_t* nElt)
+{
+    *nPts = (int64_t)(m + 1) * (m + 1) * (m + 1);
+    *nElt = (int64_t)m * m * m * 6;
+    return 0;
+}
+int feelhost_unit_cube(int m, double jitter, int shuffle, double* xyz, int32_t* conn)
+{
+    GUARD({
+        auto mesh = unitCube(m, jitter, shuffle != 0);
+        std::memcpy(xyz, mesh->xyz.data(), sizeof(double) * mesh->xyz.size());
+        std::memcpy(conn, mesh->conn.data(), sizeof(int32_t) * mesh->conn.size());
+    })
+}
+
+// ---- DofTable ----
+int feelhost_doftable(int64_t nPts, const double* xyz, int64_t nElt, const int32_t* conn, int order, int ncomp,
+                      int32_t* l2g, int64_t* nDof)
+{
+    GUARD({
+        Mesh mesh;
+        mesh.xyz.assign(xyz, xyz + 3 * nPts);
+        mesh.conn.assign(conn, conn + 4 * nElt);
+        DofTable dof;
+        dof.build(mesh, order, ncomp);
+        std::memcpy(l2g, dof.l2g.data(), sizeof(int32_t) * dof.l2g.size());
+        *nDof = dof.nDof;
+    })
+}
+
+// ---- graph: two calls (sizes, then fill) so that the caller owns the arrays ----
+struct feelhost_graph_s { GraphCSR g; };
+int feelhost_graph_build(int64_t nElt, int order, int ncomp, const int32_t* l2g, int64_t nDof, int nthreads,
+                         feelhost_graph_s** out, int64_t* nnz)
+{
+    GUARD({
+        DofTable dof;
+        dof.order = order;
+        dof.ncomp = ncomp;
+        dof.n = nLocalDofTet(order);
+        dof.nd = dof.n * ncomp;
+        dof.nDof = nDof;
+        dof.l2g.assign(l2g, l2g + nElt * dof.nd);
+        auto* h = new feelhost_graph_s;
+        computeGraph(dof, nElt, h->g, nthreads);
+        *out = h;
+        *nnz = h->g.nnz();
+    })
+}
+int feelhost_graph_get(feelhost_graph_s* h, int64_t* ia, int64_t* ja)
+{
+    std::memcpy(ia, h->g.ia.data(), sizeof(int64_t) * h->g.ia.size());
+    std::memcpy(ja, h->g.ja.data(), sizeof(int64_t) * h->g.ja.size());
+    return 0;
+}
+int feelhost_graph_free(feelhost_graph_s* h) { delete h; return 0; }
+
+// ---- reference tables ----
+int feelhost_quadrature(int order, int* nq, double* xi, double* w)
+{
+    GUARD({
+        Quadrature q = im(order);
+        *nq = q.nq;
+        if (xi) std::memcpy(xi, q.xi.data(), sizeof(double) * 3 * q.nq);
+        if (w) std::memcpy(w, q.w.data(), sizeof(double) * q.nq);
+    })
+}
+int feelhost_nlocaldof(int order) { return nLocalDofTet(order); }
+int feelhost_lagrange_points(int order, double* pts)
+{
+    GUARD({
+        auto p = lagrangePoints(order);
+        std::memcpy(pts, p.data(), sizeof(double) * p.size());
+    })
+}
+int feelhost_tabulate(int order, int nq, const double* xi, double* phi, double* dphi)
+{
+    GUARD({
+        BasisTables T = tabulate(order, nq, xi);
+        std::memcpy(phi, T.phi.data(), sizeof(double) * T.phi.size());
+        std::memcpy(dphi, T.dphi.data(), sizeof(double) * T.dphi.size());
+    })
+}
+
+// ---- expr("...") ----
+int feelhost_parse_expr(const char* s, int cap, int32_t* ops, double* consts, int* len, int* polyDegree)
+{
+    GUARD({
+        GinacProgram g = parseExpr(s);
+        if ((int)g.ops.size() > cap) throw std::length_error("parse_expr: program longer than the caller's buffer");
+        *len = (int)g.ops.size();
+        *polyDegree = g.polyDegree;
+        std::memcpy(ops, g.ops.data(), sizeof(int32_t) * g.ops.size());
+        std::memcpy(consts, g.consts.data(), sizeof(double) * g.consts.size());
+    })
+}
+
+} // extern "C"

@@ -1,0 +1,159 @@
+"""Host-side objects of the harness: mesh, function space (DofTable), graph, reference tables, expr("...").
+
+They wrap libfeelhost.so (C++), and hold what a Feel++ build already owns when it reaches
+Integrator::assemble (feelvf/integrator.hpp:975): Mesh (feeldiscr/mesh.hpp:162), Pch<k>/Pchv<k> spaces
+(feeldiscr/pch.hpp:85-90, pchv.hpp:43-48), the CSR graph (feelalg/graphcsr.hpp:287-295).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi as capi
+from ._capi import c_dblp, c_i32p, c_i64p, hcheck, ptr
+
+
+class Mesh:
+    def __init__(self, xyz, conn):
+        self.xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+        self.conn = np.ascontiguousarray(conn, dtype=np.int32).reshape(-1, 4)
+
+    def numPoints(self):
+        return self.xyz.shape[0]
+
+    def numElements(self):
+        return self.conn.shape[0]
+
+    numGlobalElements = numElements
+
+
+def unitCube(m, jitter=0.0, shuffle=False):
+    """Synthetic unit-cube tet mesh, m^3 cells x 6 tets (stands in for gmsh's unitCube(), feelfilters/unitcube.cpp:38-52)."""
+    h = capi.host()
+    npts, nelt = C.c_int64(), C.c_int64()
+    h.feelhost_unit_cube_sizes(m, C.byref(npts), C.byref(nelt))
+    xyz = np.empty((npts.value, 3), dtype=np.float64)
+    conn = np.empty((nelt.value, 4), dtype=np.int32)
+    hcheck(h.feelhost_unit_cube(m, float(jitter), int(bool(shuffle)), ptr(xyz, c_dblp), ptr(conn, c_i32p)))
+    return Mesh(xyz, conn)
+
+
+class ElementRange:
+    def __init__(self, mesh):
+        self.mesh = mesh
+
+
+def elements(mesh):
+    """elements(mesh) (feelmesh/filters.hpp:201)."""
+    return ElementRange(mesh)
+
+
+def nLocalDof(order):
+    return (order + 1) * (order + 2) * (order + 3) // 6
+
+
+class FunctionSpace:
+    """Continuous Lagrange Pk space on a tet mesh; holds the flattened DofTable."""
+
+    def __init__(self, mesh, order, ncomp=1):
+        h = capi.host()
+        self.mesh, self.order, self.ncomp = mesh, order, ncomp
+        self.n = nLocalDof(order)
+        self.nd = self.n * ncomp
+        self.l2g = np.empty((mesh.numElements(), self.nd), dtype=np.int32)
+        nd = C.c_int64()
+        hcheck(h.feelhost_doftable(mesh.numPoints(), ptr(mesh.xyz, c_dblp), mesh.numElements(),
+                                   ptr(mesh.conn, c_i32p), order, ncomp, ptr(self.l2g, c_i32p), C.byref(nd)))
+        self._ndof = nd.value
+        self._graph = None
+        self._dofpts = None
+
+    def nDof(self):
+        return self._ndof
+
+    nLocalDofWithGhost = nDof
+    nLocalDofWithoutGhost = nDof
+
+    def graph(self, nthreads=0):
+        """CSR graph of (this, this): (ia, ja) int64, ascending columns (Stencil::computeGraph + GraphCSR::close)."""
+        if self._graph is None:
+            h = capi.host()
+            hd, nnz = C.c_void_p(), C.c_int64()
+            hcheck(h.feelhost_graph_build(self.mesh.numElements(), self.order, self.ncomp, ptr(self.l2g, c_i32p),
+                                          self._ndof, nthreads, C.byref(hd), C.byref(nnz)))
+            ia = np.empty(self._ndof + 1, dtype=np.int64)
+            ja = np.empty(nnz.value, dtype=np.int64)
+            h.feelhost_graph_get(hd, ptr(ia, c_i64p), ptr(ja, c_i64p))
+            h.feelhost_graph_free(hd)
+            self._graph = (ia, ja)
+        return self._graph
+
+    def dofPoints(self):
+        """physical coordinates of the scalar nodes, [nDof/ncomp][3] (for interpolation in tests)."""
+        if self._dofpts is None:
+            ref = lagrangePoints(self.order)
+            lam = np.stack([-(1 + ref.sum(1)) / 2, (1 + ref[:, 0]) / 2, (1 + ref[:, 1]) / 2, (1 + ref[:, 2]) / 2], 1)
+            P = self.mesh.xyz[self.mesh.conn]               # [nElt][4][3]
+            X = np.einsum("nk,ekc->enc", lam, P)             # [nElt][n][3]
+            pts = np.zeros((self._ndof // self.ncomp, 3))
+            pts[self.l2g[:, :self.n] // self.ncomp] = X
+            self._dofpts = pts
+        return self._dofpts
+
+    def interpolate(self, f):
+        """nodal interpolant of a scalar callable f(x,y,z) -> array (scalar spaces)."""
+        assert self.ncomp == 1
+        p = self.dofPoints()
+        return np.asarray(f(p[:, 0], p[:, 1], p[:, 2]), dtype=np.float64)
+
+
+def Pch(mesh, order):
+    """Pch<order>(mesh) (feeldiscr/pch.hpp:85-90)."""
+    return FunctionSpace(mesh, order, 1)
+
+
+def Pchv(mesh, order):
+    """Pchv<order>(mesh) (feeldiscr/pchv.hpp:43-48)."""
+    return FunctionSpace(mesh, order, 3)
+
+
+def im(order):
+    """im(3,order,simplex): (xi[nq][3], w[nq]) (feelpoly/imsimplex.cpp:8375-8396)."""
+    h = capi.host()
+    nq = C.c_int()
+    hcheck(h.feelhost_quadrature(order, C.byref(nq), None, None))
+    xi = np.empty((nq.value, 3))
+    w = np.empty(nq.value)
+    hcheck(h.feelhost_quadrature(order, C.byref(nq), ptr(xi, c_dblp), ptr(w, c_dblp)))
+    return xi, w
+
+
+def lagrangePoints(order):
+    h = capi.host()
+    pts = np.empty((nLocalDof(order), 3))
+    hcheck(h.feelhost_lagrange_points(order, ptr(pts, c_dblp)))
+    return pts
+
+
+def tabulate(order, xi):
+    """PreCompute tables: phi[n][nq], dphi[n][nq][3] (feelpoly/polynomialset.hpp:1052-1083)."""
+    h = capi.host()
+    xi = np.ascontiguousarray(xi, dtype=np.float64).reshape(-1, 3)
+    n, nq = nLocalDof(order), xi.shape[0]
+    phi = np.empty((n, nq))
+    dphi = np.empty((n, nq, 3))
+    hcheck(h.feelhost_tabulate(order, nq, ptr(xi, c_dblp), ptr(phi, c_dblp), ptr(dphi, c_dblp)))
+    return phi, dphi
+
+
+class GinacProgram:
+    def __init__(self, source):
+        h = capi.host()
+        self.source = source
+        ops = np.zeros(64, dtype=np.int32)
+        consts = np.zeros(64)
+        ln, deg = C.c_int(), C.c_int()
+        hcheck(h.feelhost_parse_expr(source.encode(), 64, ptr(ops, c_i32p), ptr(consts, c_dblp), C.byref(ln),
+                                     C.byref(deg)))
+        self.ops = ops[:ln.value].copy()
+        self.consts = consts[:ln.value].copy()
+        self.polyDegree = deg.value

@@ -511,6 +511,9 @@ int oracle_form2(int kind, int order, int ncomp, int quad_order, int64_t nPts, c
 {
     (void)nPts;
     (void)nElt;
+    // ORACLE_ABS_FLAG: accumulate |a^e_ij| instead (the cancellation scale used by the parity tolerance)
+    const bool absmode = (kind & ORACLE_ABS_FLAG) != 0;
+    kind &= ~ORACLE_ABS_FLAG;
     Tables T = make_tables(order, quad_order);
     Tables Tf;
     if (coeff && coeff->kind == ORACLE_COEFF_FIELD) Tf = make_tables(coeff->field_order, quad_order);
@@ -528,7 +531,7 @@ int oracle_form2(int kind, int order, int ncomp, int quad_order, int64_t nPts, c
             for (int j = 0; j < nd; ++j) {
                 int64_t s = find_slot(ia, ja, idx[i], idx[j]);
                 if (s < 0) return 1; // new nonzero outside the preallocated pattern (matrixpetsc.cpp:2688)
-                a[s] += W.Ae[i * nd + j];
+                a[s] += absmode ? std::fabs(W.Ae[i * nd + j]) : W.Ae[i * nd + j];
             }
     }
     return 0;

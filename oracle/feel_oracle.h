@@ -21,6 +21,7 @@ extern "C" {
 /* form kinds (same numeric values as include/feelgpu.h, restated here so that the oracle has no product include) */
 enum { ORACLE_FORM2_MASS = 0, ORACLE_FORM2_STIFFNESS = 1, ORACLE_FORM2_ELASTICITY = 2 };
 enum { ORACLE_FORM1_SOURCE = 0 };
+#define ORACLE_ABS_FLAG 0x100  /* oracle_form2: accumulate |a^e_ij| (cancellation scale for tolerances) */
 enum { ORACLE_COEFF_CONST = 0, ORACLE_COEFF_FIELD = 1, ORACLE_COEFF_EXPR = 2 };
 
 typedef struct {

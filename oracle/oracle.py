@@ -1,0 +1,174 @@
+"""ctypes wrapper of the CPU oracle (oracle/_build/libfeel_oracle.so).  TEST INFRASTRUCTURE ONLY:
+imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs; never by feelpp_b200/."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libfeel_oracle.so")
+c_i32p, c_i64p, c_dblp = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_double)
+
+MASS, STIFFNESS, ELASTICITY = 0, 1, 2
+ABS_FLAG = 0x100
+COEFF_CONST, COEFF_FIELD, COEFF_EXPR = 0, 1, 2
+
+
+class OCoeff(C.Structure):
+    _fields_ = [("kind", C.c_int), ("value", C.c_double * 3), ("field_order", C.c_int), ("field_l2g", c_i32p),
+                ("field_values", c_dblp), ("expr_len", C.c_int), ("expr_ops", c_i32p), ("expr_consts", c_dblp),
+                ("lambda_", C.c_double), ("mu", C.c_double)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            subprocess.check_call(["make", "-C", _HERE], stdout=subprocess.DEVNULL)
+        L = C.CDLL(_SO)
+        L.oracle_quadrature.argtypes = [C.c_int, c_dblp]
+        L.oracle_lagrange_points.argtypes = [C.c_int, c_dblp]
+        L.oracle_tabulate.argtypes = [C.c_int, C.c_int, c_dblp, c_dblp, c_dblp]
+        L.oracle_doftable.argtypes = [C.c_int64, C.c_int64, c_i32p, C.c_int, C.c_int, c_i32p]
+        L.oracle_doftable.restype = C.c_int64
+        L.oracle_graph.argtypes = [C.c_int64, C.c_int, c_i32p, C.c_int64, c_i64p, C.POINTER(c_i64p)]
+        L.oracle_graph.restype = C.c_int64
+        L.oracle_free.argtypes = [C.c_void_p]
+        f2 = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, c_dblp, C.c_int64, c_i32p, c_i32p, c_i64p, c_i64p,
+              C.POINTER(OCoeff)]
+        L.oracle_form2.argtypes = f2 + [C.c_int64, C.c_int64, c_dblp]
+        L.oracle_form2_threads.argtypes = f2 + [C.c_int, C.c_int64, C.c_int64, c_dblp]
+        L.oracle_form2_threads.restype = C.c_double
+        L.oracle_form1.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, c_dblp, C.c_int64, c_i32p, c_i32p,
+                                   C.POINTER(OCoeff), C.c_int64, C.c_int64, c_dblp]
+        L.oracle_local_matrix.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, c_dblp, C.POINTER(OCoeff), c_dblp]
+        _lib = L
+    return _lib
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t)
+
+
+def nloc(order):
+    return (order + 1) * (order + 2) * (order + 3) // 6
+
+
+def quadrature(order):
+    n = lib().oracle_quadrature(order, None)
+    q = np.empty(4 * n)
+    lib().oracle_quadrature(order, _p(q, c_dblp))
+    q = q.reshape(n, 4)
+    return q[:, :3].copy(), q[:, 3].copy()
+
+
+def lagrange_points(order):
+    p = np.empty((nloc(order), 3))
+    lib().oracle_lagrange_points(order, _p(p, c_dblp))
+    return p
+
+
+def tabulate(order, xi):
+    xi = np.ascontiguousarray(xi, dtype=np.float64).reshape(-1, 3)
+    n, Q = nloc(order), xi.shape[0]
+    phi, dphi = np.empty((n, Q)), np.empty((n, Q, 3))
+    lib().oracle_tabulate(order, Q, _p(xi, c_dblp), _p(phi, c_dblp), _p(dphi, c_dblp))
+    return phi, dphi
+
+
+def quad_order_form2(kind, order, coeff_deg=0):
+    return lib().oracle_quad_order_form2(kind, order, coeff_deg)
+
+
+def quad_order_form1(order, coeff_deg=0):
+    return lib().oracle_quad_order_form1(order, coeff_deg)
+
+
+def doftable(npts, conn, order, ncomp=1):
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    l2g = np.empty((conn.shape[0], nloc(order) * ncomp), dtype=np.int32)
+    nd = lib().oracle_doftable(npts, conn.shape[0], _p(conn, c_i32p), order, ncomp, _p(l2g, c_i32p))
+    return l2g, int(nd)
+
+
+def graph(l2g, ndof):
+    l2g = np.ascontiguousarray(l2g, dtype=np.int32)
+    ia = np.empty(ndof + 1, dtype=np.int64)
+    jap = c_i64p()
+    nnz = lib().oracle_graph(l2g.shape[0], l2g.shape[1], _p(l2g, c_i32p), ndof, _p(ia, c_i64p), C.byref(jap))
+    ja = np.ctypeslib.as_array(jap, shape=(max(nnz, 1),))[:nnz].copy()
+    lib().oracle_free(jap)
+    return ia, ja
+
+
+class Coeff:
+    """keeps the numpy buffers of an oracle_coeff alive"""
+
+    def __init__(self, kind=COEFF_CONST, value=1.0, vector=None, field_order=0, field_l2g=None, field_values=None,
+                 ops=None, consts=None, lam=0.0, mu=0.0):
+        self.c = OCoeff()
+        self.c.kind = kind
+        self.c.value[0] = value
+        if vector is not None:
+            for k in range(3):
+                self.c.value[k] = vector[k]
+        self.c.lambda_, self.c.mu = lam, mu
+        self._keep = []
+        if field_l2g is not None:
+            a = np.ascontiguousarray(field_l2g, dtype=np.int32)
+            b = np.ascontiguousarray(field_values, dtype=np.float64)
+            self._keep += [a, b]
+            self.c.field_order, self.c.field_l2g, self.c.field_values = field_order, _p(a, c_i32p), _p(b, c_dblp)
+        if ops is not None:
+            a = np.ascontiguousarray(ops, dtype=np.int32)
+            b = np.ascontiguousarray(consts, dtype=np.float64)
+            self._keep += [a, b]
+            self.c.expr_len, self.c.expr_ops, self.c.expr_consts = len(a), _p(a, c_i32p), _p(b, c_dblp)
+
+
+def form2(kind, order, ncomp, quad_order, xyz, conn, l2g, ia, ja, coeff=None, a=None, elt_range=None, threads=0):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    l2g = np.ascontiguousarray(l2g, dtype=np.int32)
+    ia = np.ascontiguousarray(ia, dtype=np.int64)
+    ja = np.ascontiguousarray(ja, dtype=np.int64)
+    if a is None:
+        a = np.zeros(int(ia[-1]))
+    coeff = coeff or Coeff()
+    eb, ee = elt_range if elt_range is not None else (0, conn.shape[0])
+    args = [kind, order, ncomp, quad_order, xyz.shape[0], _p(xyz, c_dblp), conn.shape[0], _p(conn, c_i32p),
+            _p(l2g, c_i32p), _p(ia, c_i64p), _p(ja, c_i64p), C.byref(coeff.c)]
+    if threads > 0:
+        secs = lib().oracle_form2_threads(*args, threads, eb, ee, _p(a, c_dblp))
+        if secs < 0:
+            raise RuntimeError("oracle: entry outside the pattern")
+        return a, secs
+    rc = lib().oracle_form2(*args, eb, ee, _p(a, c_dblp))
+    if rc:
+        raise RuntimeError("oracle: entry outside the pattern")
+    return a
+
+
+def form1(order, ncomp, quad_order, xyz, conn, l2g, ndof, coeff=None, b=None):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    l2g = np.ascontiguousarray(l2g, dtype=np.int32)
+    if b is None:
+        b = np.zeros(ndof)
+    coeff = coeff or Coeff()
+    lib().oracle_form1(0, order, ncomp, quad_order, xyz.shape[0], _p(xyz, c_dblp), conn.shape[0], _p(conn, c_i32p),
+                       _p(l2g, c_i32p), C.byref(coeff.c), 0, conn.shape[0], _p(b, c_dblp))
+    return b
+
+
+def local_matrix(kind, order, ncomp, quad_order, G, coeff=None):
+    G = np.ascontiguousarray(G, dtype=np.float64).reshape(4, 3)
+    nd = nloc(order) * ncomp
+    Ae = np.empty((nd, nd))
+    coeff = coeff or Coeff()
+    lib().oracle_local_matrix(kind, order, ncomp, quad_order, _p(G, c_dblp), C.byref(coeff.c), _p(Ae, c_dblp))
+    return Ae
