@@ -1,0 +1,190 @@
+"""GPU parity: the CUDA engine (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Tolerance (BASELINE.json north_star): |a - a_ref| <= 1e-12 * |a_ref| per nonzero, plus a cancellation floor of
+1e-14 * S_ij where S_ij = sum_e |a^e_ij| (entries that cancel to ~0 on structured meshes have no meaningful relative
+error; fp64 sums over <= ~30 elements are reordered).  Pattern (ia/ja) parity is bit-exact and checked on the CPU in
+tests/test_host_vs_oracle.py.
+"""
+import numpy as np
+import pytest
+
+import feelpp_b200 as fpp
+from feelpp_b200 import (cst, elements, expr, grad, gradt, id, idt, idv, inner, integrate, sym, trace, trans, vec, Id)
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+RTOL, FLOOR = 1e-12, 1e-14
+ALGOS = [fpp.ALGO_SCATTER, fpp.ALGO_ROWPLAN]
+
+
+import contextlib
+
+
+@contextlib.contextmanager
+def guard(algo):
+    """a form the owner-computes plan does not cover yet is reported as a skip for ALGO_ROWPLAN only"""
+    try:
+        yield
+    except fpp.FeelGpuError as e:
+        if algo == fpp.ALGO_ROWPLAN and e.code == 5:
+            pytest.skip("row plan does not cover this form: " + str(e))
+        raise
+
+
+def check_values(a, ref, scale, what):
+    err = np.abs(a - ref)
+    tol = RTOL * np.abs(ref) + FLOOR * scale
+    bad = err > tol
+    assert not bad.any(), "%s: %d/%d nonzeros out of tolerance, worst err %.3e (ref %.3e, scale %.3e)" % (
+        what, bad.sum(), len(ref), err[bad].max(), np.abs(ref[bad]).max(), scale[bad].max())
+
+
+def oracle_form2(kind, Xh, quad, coeff=None):
+    m = Xh.mesh
+    ia, ja = Xh.graph()
+    ref = orc.form2(kind, Xh.order, Xh.ncomp, quad, m.xyz, m.conn, Xh.l2g, ia, ja, coeff)
+    scale = orc.form2(kind | orc.ABS_FLAG, Xh.order, Xh.ncomp, quad, m.xyz, m.conn, Xh.l2g, ia, ja, coeff)
+    return ref, scale
+
+
+@pytest.fixture(scope="module")
+def meshes():
+    return {"reg": fpp.unitCube(4), "jit": fpp.unitCube(5, 0.15, True)}
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("order", [1, 2, 3])
+@pytest.mark.parametrize("mk", ["reg", "jit"])
+def test_stiffness_and_mass(engine, meshes, order, mk, algo):
+    mesh = meshes[mk]
+    Xh = fpp.Pch(mesh, order)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, algorithm=algo)
+    with guard(algo):
+        a.assign(integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v))))
+    ref, scale = oracle_form2(orc.STIFFNESS, Xh, orc.quad_order_form2(orc.STIFFNESS, order))
+    check_values(a.values(), ref, scale, "stiffness P%d" % order)
+    # a = mass ; a += stiffness  (operator= then operator+=)
+    with guard(algo):
+        a.assign(integrate(_range=elements(mesh), _expr=idt(u) * id(v)))
+    refm, scalem = oracle_form2(orc.MASS, Xh, orc.quad_order_form2(orc.MASS, order))
+    check_values(a.values(), refm, scalem, "mass P%d" % order)
+    with guard(algo):
+        a += integrate(_range=elements(mesh), _expr=inner(gradt(u), grad(v)))
+    check_values(a.values(), refm + ref, scalem + scale, "mass+stiffness P%d" % order)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_weighted_stiffness_expr(engine, meshes, order, algo):
+    mesh = meshes["jit"]
+    Xh = fpp.Pch(mesh, order)
+    u = v = fpp.Element(Xh)
+    k = expr("1+x*y+z^2")
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, algorithm=algo)
+    with guard(algo):
+        a.assign(integrate(_range=elements(mesh), _expr=k * inner(gradt(u), grad(v))))
+    q = orc.quad_order_form2(orc.STIFFNESS, order, 2)
+    co = orc.Coeff(kind=orc.COEFF_EXPR, ops=k.prog.ops, consts=k.prog.consts)
+    ref, scale = oracle_form2(orc.STIFFNESS, Xh, q, co)
+    check_values(a.values(), ref, scale, "k(x)*stiffness P%d" % order)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_weighted_stiffness_field_p3(engine, meshes, algo):
+    mesh = meshes["jit"]
+    Xh, Kh = fpp.Pch(mesh, 3), fpp.Pch(mesh, 1)
+    kv = Kh.interpolate(lambda x, y, z: 1 + 0.5 * np.sin(2 * np.pi * x))
+    k = fpp.Element(Kh, kv)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, algorithm=algo)
+    with guard(algo):
+        a.assign(integrate(_range=elements(mesh), _expr=idv(k) * inner(gradt(u), grad(v))))
+    q = orc.quad_order_form2(orc.STIFFNESS, 3, 1)
+    assert q == 5
+    co = orc.Coeff(kind=orc.COEFF_FIELD, field_order=1, field_l2g=Kh.l2g, field_values=kv)
+    ref, scale = oracle_form2(orc.STIFFNESS, Xh, q, co)
+    check_values(a.values(), ref, scale, "idv(k)*stiffness P3")
+    with guard(algo):
+        a.assign(integrate(_range=elements(mesh), _expr=idv(k) * idt(u) * id(v)))
+    qm = orc.quad_order_form2(orc.MASS, 3, 1)
+    ref, scale = oracle_form2(orc.MASS, Xh, qm, co)
+    check_values(a.values(), ref, scale, "idv(k)*mass P3")
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("order", [1, 2])
+def test_elasticity(engine, meshes, order, algo):
+    mesh = meshes["jit"]
+    Xh = fpp.Pchv(mesh, order)
+    u = v = fpp.Element(Xh)
+    E, nu = 1e8, 0.25   # benchmarks/ATTIC/perf/assembly.cpp:86-89
+    lam, mu = E * nu / ((1 + nu) * (1 - 2 * nu)), E / (2 * (1 + nu))
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, algorithm=algo)
+    with guard(algo):
+        a.assign(integrate(_range=elements(mesh),
+                           _expr=inner(lam * trace(sym(gradt(u))) * Id() + 2 * mu * sym(gradt(u)), grad(v))))
+    ref, scale = oracle_form2(orc.ELASTICITY, Xh, orc.quad_order_form2(orc.ELASTICITY, order),
+                              orc.Coeff(lam=lam, mu=mu))
+    check_values(a.values(), ref, scale, "elasticity P%dv" % order)
+    # vector mass, block diagonal inside the COUPLED pattern
+    with guard(algo):
+        a.assign(integrate(_range=elements(mesh), _expr=inner(idt(u), id(v))))
+    ref, scale = oracle_form2(orc.MASS, Xh, orc.quad_order_form2(orc.MASS, order))
+    check_values(a.values(), ref, scale, "vector mass P%dv" % order)
+
+
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_form1(engine, meshes, order):
+    mesh = meshes["jit"]
+    Xh = fpp.Pch(mesh, order)
+    v = fpp.Element(Xh)
+    l = fpp.form1(_test=Xh, engine=engine)
+    l.assign(integrate(_range=elements(mesh), _expr=cst(1.0) * id(v)))
+    ref = orc.form1(order, 1, orc.quad_order_form1(order, 0), mesh.xyz, mesh.conn, Xh.l2g, Xh.nDof())
+    np.testing.assert_allclose(l.values(), ref, rtol=1e-12, atol=1e-16)
+    assert abs(l.values().sum() - 1.0) < 1e-12
+    f = expr("sin(pi*x)*cos(pi*y)*z")
+    l += integrate(_range=elements(mesh), _expr=f * id(v))
+    co = orc.Coeff(kind=orc.COEFF_EXPR, ops=f.prog.ops, consts=f.prog.consts)
+    ref2 = orc.form1(order, 1, orc.quad_order_form1(order, -1), mesh.xyz, mesh.conn, Xh.l2g, Xh.nDof(), co)
+    np.testing.assert_allclose(l.values(), ref + ref2, rtol=1e-12, atol=1e-15)
+
+
+def test_form1_vector(engine, meshes):
+    mesh = meshes["jit"]
+    Xh = fpp.Pchv(mesh, 2)
+    v = fpp.Element(Xh)
+    l = fpp.form1(_test=Xh, engine=engine)
+    l.assign(integrate(_range=elements(mesh), _expr=inner(vec(0, -1e3, 0), id(v))))
+    co = orc.Coeff(vector=[0, -1e3, 0])
+    ref = orc.form1(2, 3, orc.quad_order_form1(2, 0), mesh.xyz, mesh.conn, Xh.l2g, Xh.nDof(), co)
+    np.testing.assert_allclose(l.values(), ref, rtol=1e-12, atol=1e-13)
+
+
+def test_host_output_variant(engine, meshes):
+    mesh = meshes["jit"]
+    Xh = fpp.Pch(mesh, 2)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine)
+    vals = a.assemble_host(integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v))))
+    ref, scale = oracle_form2(orc.STIFFNESS, Xh, 2)
+    check_values(vals, ref, scale, "assemble_host")
+
+
+def test_errors(engine, meshes):
+    mesh = meshes["reg"]
+    Xh = fpp.Pch(mesh, 1)
+    ia, ja = Xh.graph()
+    # drop one column from the graph: the engine must refuse it (PETSc's new-nonzero error, matrixpetsc.cpp:2688)
+    ja2 = ja.copy()
+    ja2[ia[5]] = ja2[ia[5] + 1]
+    import ctypes as C
+    from feelpp_b200._capi import c_i64p, ptr
+    pat = C.c_void_p()
+    sp = engine.space(Xh)
+    rc = engine.lib.feelgpu_pattern_create(engine.ctx, sp, sp, Xh.nDof(), ptr(ia, c_i64p), ptr(ja2, c_i64p), 1,
+                                           C.byref(pat))
+    assert rc == 4
+    assert b"not in the CSR graph" in engine.lib.feelgpu_last_error(engine.ctx)

@@ -1,0 +1,141 @@
+"""Pins the oracle with the analytic identities the reference's own tests use (no golden matrices exist upstream):
+testsuite/feelvf/test_forms.cpp:135-139 (a(1,1) == measure), testsuite/feeldiscr/test_wire_basket.cpp:141-142
+(mass energy), testsuite/feelvf/test_laplaciant.cpp:108-126 (energy of an interpolant), testsuite/feelpoly/
+testlagrange.hpp:100-137 (phi_i(x_j) = delta_ij within 3000 eps), testsuite/feelintegration/
+test_auto_order_integrate.cpp:169-211 (quadrature-order rule), and the extracted imsimplex.cpp literals."""
+import json
+import os
+
+import numpy as np
+import pytest
+import scipy.sparse as sps
+
+import feelpp_b200 as fpp
+from oracle import oracle as orc
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_quadrature_tables_match_reference_literals():
+    js = json.load(open(os.path.join(GOLD, "tet_quadrature.json")))
+    for order, rule in js.items():
+        xi, w = orc.quadrature(int(order))
+        q = np.array(rule["q"]).reshape(-1, 4)
+        assert len(w) == rule["npts"]
+        assert np.array_equal(xi, q[:, :3]) and np.array_equal(w, q[:, 3])
+        hxi, hw = fpp.im(int(order))          # the product's copy of the same tables
+        assert np.array_equal(hxi, xi) and np.array_equal(hw, w)
+    # point counts of SURVEY.md section 8: orders 1,2,4,5,6 -> 1,4,11,14,24
+    assert [js[str(o)]["npts"] for o in (1, 2, 4, 5, 6)] == [1, 4, 11, 14, 24]
+
+
+@pytest.mark.parametrize("order", range(1, 10))
+def test_quadrature_exactness(order):
+    """integrates monomials of total degree <= order exactly on the reference tet (test_quad_order.cpp:132-385)"""
+    from math import factorial
+    xi, w = orc.quadrature(order)
+    lam = np.stack([(1 + xi[:, 0]) / 2, (1 + xi[:, 1]) / 2, (1 + xi[:, 2]) / 2], 1)
+    for a in range(order + 1):
+        for b in range(order + 1 - a):
+            for c in range(order + 1 - a - b):
+                exact = 8 * factorial(a) * factorial(b) * factorial(c) / factorial(a + b + c + 3)
+                got = np.sum(w * lam[:, 0] ** a * lam[:, 1] ** b * lam[:, 2] ** c)
+                assert abs(got - exact) < 2e-13, (order, a, b, c)
+
+
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_lagrange_kronecker_and_partition_of_unity(order):
+    pts = orc.lagrange_points(order)
+    phi, dphi = orc.tabulate(order, pts)
+    assert np.abs(phi - np.eye(len(pts))).max() < 3000 * np.finfo(float).eps
+    xi, _ = orc.quadrature(6)
+    phi, dphi = orc.tabulate(order, xi)
+    assert np.abs(phi.sum(0) - 1).max() < 1e-14 and np.abs(dphi.sum(0)).max() < 1e-13
+    # derivative consistency: central finite differences
+    h = 1e-6
+    for c in range(3):
+        e = np.zeros(3); e[c] = h
+        fd = (orc.tabulate(order, xi + e)[0] - orc.tabulate(order, xi - e)[0]) / (2 * h)
+        assert np.abs(fd - dphi[:, :, c]).max() < 1e-8
+
+
+def test_p3_edge_nodes_are_gauss_lobatto():
+    pts = orc.lagrange_points(3)
+    # edge 2 = (v0,v1) runs along xi_0 from -1 to 1: interior nodes at -+1/sqrt(5) (warpblend.hpp:96-121)
+    assert np.allclose(pts[8], [-1 / np.sqrt(5), -1, -1]) and np.allclose(pts[9], [1 / np.sqrt(5), -1, -1])
+    assert np.allclose(pts[16], [1 / 3 - 2 / 3 + 0, 1 / 3 - 2 / 3, 1 / 3 - 2 / 3])  # face 0 centroid (v1,v2,v3)
+
+
+def test_quadrature_order_rule():
+    # (kind, order, coeff degree) -> order ; SURVEY.md section 8 table
+    assert orc.quad_order_form2(orc.STIFFNESS, 1) == 1
+    assert orc.quad_order_form2(orc.STIFFNESS, 2) == 2
+    assert orc.quad_order_form2(orc.MASS, 2) == 4
+    assert orc.quad_order_form2(orc.STIFFNESS, 3) == 4
+    assert orc.quad_order_form2(orc.STIFFNESS, 3, 1) == 5
+    assert orc.quad_order_form2(orc.STIFFNESS, 3, 2) == 6
+    assert orc.quad_order_form2(orc.STIFFNESS, 3, -1) == 6
+    assert orc.quad_order_form2(orc.ELASTICITY, 2) == 2
+    assert orc.quad_order_form1(2, 0) == 2 and orc.quad_order_form1(2, -1) == 4
+    # the harness' DSEL picks the same orders
+    mesh = fpp.unitCube(1)
+    for k in (1, 2, 3):
+        Xh = fpp.Pch(mesh, k)
+        u = v = fpp.Element(Xh)
+        assert fpp.classify_form2(fpp.gradt(u) * fpp.trans(fpp.grad(v)), k).quad_order == orc.quad_order_form2(orc.STIFFNESS, k)
+        assert fpp.classify_form2(fpp.idt(u) * fpp.id(v), k).quad_order == orc.quad_order_form2(orc.MASS, k)
+        e = fpp.expr("1+x*y+z^2") * fpp.inner(fpp.gradt(u), fpp.grad(v))
+        assert fpp.classify_form2(e, k).quad_order == orc.quad_order_form2(orc.STIFFNESS, k, 2)
+        e = fpp.expr("sin(pi*x)*cos(pi*y)*z") * fpp.id(v)
+        assert fpp.classify_form1(e, k).quad_order == orc.quad_order_form1(k, -1)
+
+
+@pytest.fixture(scope="module")
+def mesh():
+    return fpp.unitCube(3, 0.15, True)
+
+
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_mass_and_stiffness_identities(mesh, order):
+    Xh = fpp.Pch(mesh, order)
+    ia, ja = Xh.graph()
+    M = orc.form2(orc.MASS, order, 1, orc.quad_order_form2(orc.MASS, order), mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+    K = orc.form2(orc.STIFFNESS, order, 1, orc.quad_order_form2(orc.STIFFNESS, order), mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+    M, K = sps.csr_matrix((M, ja, ia)), sps.csr_matrix((K, ja, ia))
+    one = np.ones(Xh.nDof())
+    assert abs(one @ M @ one - 1.0) < 1e-10                 # a(1,1) == measure (test_forms.cpp:135-139)
+    assert np.abs(K @ one).max() < 1e-12 * np.abs(K).max()    # constants are in the kernel
+    assert abs(K - K.T).max() == 0 or abs(K - K.T).max() < 1e-15 * np.abs(K).max()
+    f = {1: lambda x, y, z: x + 2 * y - z, 2: lambda x, y, z: x * x + 2 * y * z, 3: lambda x, y, z: x ** 3 + 2 * y * z}[order]
+    exact = {1: 6.0, 2: 4.0, 3: 9 / 5 + 8 / 3}[order]
+    u = Xh.interpolate(f)
+    assert abs(u @ K @ u - exact) < 1e-9                      # energy of an exactly represented polynomial
+
+
+def test_elasticity_rigid_body_modes(mesh):
+    Xh = fpp.Pchv(mesh, 2)
+    ia, ja = Xh.graph()
+    lam = mu = 4e7
+    E = orc.form2(orc.ELASTICITY, 2, 3, 2, mesh.xyz, mesh.conn, Xh.l2g, ia, ja, orc.Coeff(lam=lam, mu=mu))
+    Es = sps.csr_matrix((E, ja, ia))
+    p = Xh.dofPoints()
+    rot = np.zeros(Xh.nDof()); rot[0::3] = -p[:, 1]; rot[1::3] = p[:, 0]
+    assert np.abs(Es @ rot).max() < 1e-12 * np.abs(E).max()
+    stretch = np.zeros(Xh.nDof()); stretch[0::3] = p[:, 0]
+    assert abs(stretch @ Es @ stretch - (lam + 2 * mu)) < 1e-9 * (lam + 2 * mu)
+
+
+def test_local_matrix_p1_closed_form():
+    """P1 stiffness of the reference tet scaled to unit edge: A_ij = V grad(l_i).grad(l_j)"""
+    G = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1.0]])
+    A = orc.local_matrix(orc.STIFFNESS, 1, 1, 1, G)
+    g = np.array([[-1, -1, -1], [1, 0, 0], [0, 1, 0], [0, 0, 1.0]])
+    assert np.abs(A - (g @ g.T) / 6).max() < 1e-15
+
+
+def test_threaded_baseline_matches_serial(mesh):
+    Xh = fpp.Pch(mesh, 2)
+    ia, ja = Xh.graph()
+    ref = orc.form2(orc.STIFFNESS, 2, 1, 2, mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+    par, secs = orc.form2(orc.STIFFNESS, 2, 1, 2, mesh.xyz, mesh.conn, Xh.l2g, ia, ja, threads=3)
+    assert secs >= 0 and np.abs(par - ref).max() < 1e-13 * np.abs(ref).max()
