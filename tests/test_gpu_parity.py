@@ -1,8 +1,8 @@
 """GPU parity: the CUDA engine (through the C ABI) against the CPU oracle on the same seeded inputs.
 
-Tolerance (BASELINE.json north_star): |a - a_ref| <= 1e-12 * |a_ref| per nonzero, plus a cancellation floor of
-1e-14 * S_ij where S_ij = sum_e |a^e_ij| (entries that cancel to ~0 on structured meshes have no meaningful relative
-error; fp64 sums over <= ~30 elements are reordered).  Pattern (ia/ja) parity is bit-exact and checked on the CPU in
+Tolerance (BASELINE.json north_star): |a - a_ref| <= 1e-12 * |a_ref| per nonzero, plus the absolute floor
+1e-14 * sqrt(S_ii S_jj), S = sum_e |a^e| (oracle/parity.py: entries that vanish in exact arithmetic carry only rounding
+noise; fp64 sums over <= ~30 elements are reordered).  Pattern (ia/ja) parity is bit-exact and checked on the CPU in
 tests/test_host_vs_oracle.py.
 """
 import numpy as np
@@ -11,10 +11,10 @@ import pytest
 import feelpp_b200 as fpp
 from feelpp_b200 import (cst, elements, expr, grad, gradt, id, idt, idv, inner, integrate, sym, trace, trans, vec, Id)
 from oracle import oracle as orc
+from oracle import parity
 
 pytestmark = pytest.mark.gpu
 
-RTOL, FLOOR = 1e-12, 1e-14
 ALGOS = [fpp.ALGO_SCATTER, fpp.ALGO_ROWPLAN]
 
 
@@ -33,11 +33,8 @@ def guard(algo):
 
 
 def check_values(a, ref, scale, what):
-    err = np.abs(a - ref)
-    tol = RTOL * np.abs(ref) + FLOOR * scale
-    bad = err > tol
-    assert not bad.any(), "%s: %d/%d nonzeros out of tolerance, worst err %.3e (ref %.3e, scale %.3e)" % (
-        what, bad.sum(), len(ref), err[bad].max(), np.abs(ref[bad]).max(), scale[bad].max())
+    ref, ia, ja = ref
+    parity.check(a, ref, scale, ia, ja, what)
 
 
 def oracle_form2(kind, Xh, quad, coeff=None):
@@ -45,7 +42,7 @@ def oracle_form2(kind, Xh, quad, coeff=None):
     ia, ja = Xh.graph()
     ref = orc.form2(kind, Xh.order, Xh.ncomp, quad, m.xyz, m.conn, Xh.l2g, ia, ja, coeff)
     scale = orc.form2(kind | orc.ABS_FLAG, Xh.order, Xh.ncomp, quad, m.xyz, m.conn, Xh.l2g, ia, ja, coeff)
-    return ref, scale
+    return (ref, ia, ja), scale
 
 
 @pytest.fixture(scope="module")
@@ -72,7 +69,7 @@ def test_stiffness_and_mass(engine, meshes, order, mk, algo):
     check_values(a.values(), refm, scalem, "mass P%d" % order)
     with guard(algo):
         a += integrate(_range=elements(mesh), _expr=inner(gradt(u), grad(v)))
-    check_values(a.values(), refm + ref, scalem + scale, "mass+stiffness P%d" % order)
+    check_values(a.values(), (refm[0] + ref[0], ref[1], ref[2]), scalem + scale, "mass+stiffness P%d" % order)
 
 
 @pytest.mark.parametrize("algo", ALGOS)
