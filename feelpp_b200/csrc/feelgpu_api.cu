@@ -105,6 +105,8 @@ int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz, 
         feelgpu_mesh_destroy(m);
         return FEELGPU_ERR_CUDA;
     }
+    m->h_xyz.assign(xyz, xyz + 3 * nPts);
+    m->h_conn.assign(conn, conn + 4 * nElt);
     int rc = upload_points(m, xyz, ctx->stream);
     if (rc) { feelgpu_mesh_destroy(m); return rc; }
     err = cudaMemcpyAsync(m->d_conn, conn, sizeof(int32_t) * 4 * nElt, cudaMemcpyHostToDevice, ctx->stream);
@@ -169,6 +171,7 @@ int feelgpu_space_create(feelgpu_context_t ctx, feelgpu_mesh_t mesh, int order, 
     sp->nd = nd;
     sp->nDofWithGhost = nWithGhost;
     sp->nDofOwned = nOwned;
+    sp->h_l2g.assign(l2g, l2g + mesh->nElt * nd);
     cudaError_t err = cudaMalloc(&sp->d_l2g, sizeof(int32_t) * std::max<int64_t>(mesh->nElt * nd, 1));
     if (err == cudaSuccess) err = cudaMemcpy(sp->d_l2g, l2g, sizeof(int32_t) * mesh->nElt * nd, cudaMemcpyHostToDevice);
     if (err == cudaSuccess && p2c) {

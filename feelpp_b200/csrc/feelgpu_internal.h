@@ -29,6 +29,8 @@ struct feelgpu_mesh_s {
     double* d_xyz = nullptr;     // [nPts][4]: x,y,z,0 -- one 32-byte sector per vertex
     int4* d_conn = nullptr;      // [nElt]
     double* h_stage = nullptr;   // pinned staging for update_points
+    std::vector<double> h_xyz;   // host copies: the plan builder orders rows along a space-filling curve
+    std::vector<int32_t> h_conn;
 };
 
 struct feelgpu_space_s {
@@ -38,6 +40,7 @@ struct feelgpu_space_s {
     int64_t nDofWithGhost = 0, nDofOwned = 0;
     int32_t* d_l2g = nullptr;    // [nElt][nd]
     int64_t* d_p2c = nullptr;    // process -> cluster ids, or null (identity)
+    std::vector<int32_t> h_l2g;  // host copy for the plan builder
 };
 
 struct RowPlan;  // kernels_rowplan.cu
@@ -52,6 +55,7 @@ struct feelgpu_pattern_s {
     // global = ncomp*node + c, feeldiscr/doftable.hpp:1289-1299).
     uint16_t* d_pos = nullptr;   // [nElt][n][n]
     RowPlan* plan = nullptr;
+    std::string plan_note;       // why no owner-computes plan exists (if none)
 };
 
 // parameter block copied to the device per assemble call
