@@ -20,28 +20,81 @@ struct RowTables {
     int pad;
 };
 
-__device__ __forceinline__ int pair_idx(int x, int y) { return x + y - 1 + (min(x, y) >= 1 ? 1 : 0); }
+// one unit's row of the re-labelled local matrix -> stage[entry][lane]; returns the canonical (diagonal) entry.
+// sT: the canonical rows of the reference matrices in shared memory, [kind][j][6]; every lane reads the same 16 bytes
+// (broadcast, one wavefront).  They cannot live in the constant bank: ptxas hoists the uniform loads out of the bundle
+// loop and 120 doubles do not fit the uniform register file.
+template <int ORDER, int FORM, int KIND>
+__device__ __forceinline__ double unit_row(const double* __restrict__ sT, const double* __restrict__ sS, uint32_t u,
+                                           double* st)
+{
+    constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
+    constexpr int CANON = KIND == 0 ? 0 : (KIND == 1 ? 4 + 2 * (ORDER - 1) : 4 + 6 * (ORDER - 1) + 3);
+    const int vis = u & 0x3FF;
+    double dv = 0.0;
+    if (FORM == 0) {
+        const double cj = sS[vis];
+        const double2* t2 = reinterpret_cast<const double2*>(sT + KIND * 20);
+#pragma unroll
+        for (int j = 0; j < N; j += 2) {
+            const double2 t = t2[j / 2];
+            const double v0 = cj * t.x, v1 = cj * t.y;
+            st[j * 32] = v0;
+            if (j == CANON) dv = v0;
+            if (j + 1 < N) {
+                st[(j + 1) * 32] = v1;
+                if (j + 1 == CANON) dv = v1;
+            }
+        }
+    } else {
+        const double s01 = sS[((u >> 10) & 7) * ROWPLAN_VMAX + vis];
+        const double s02 = sS[((u >> 13) & 7) * ROWPLAN_VMAX + vis];
+        const double s03 = sS[((u >> 16) & 7) * ROWPLAN_VMAX + vis];
+        const double s12 = sS[((u >> 19) & 7) * ROWPLAN_VMAX + vis];
+        const double s13 = sS[((u >> 22) & 7) * ROWPLAN_VMAX + vis];
+        const double s23 = sS[((u >> 25) & 7) * ROWPLAN_VMAX + vis];
+        // rows of the barycentric Gram matrix sum to zero: S_kk = -sum_{l != k} S_kl
+        const double s11 = -(s01 + s12 + s13), s22 = -(s02 + s12 + s23), s33 = -(s03 + s13 + s23);
+        const double2* t2 = reinterpret_cast<const double2*>(sT + KIND * 120);
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            const double2 ta = t2[j * 3 + 0], tb = t2[j * 3 + 1], tc = t2[j * 3 + 2];
+            double v = s11 * ta.x;
+            v = fma(s22, ta.y, v);
+            v = fma(s33, tb.x, v);
+            v = fma(s12, tb.y, v);
+            v = fma(s13, tc.x, v);
+            v = fma(s23, tc.y, v);
+            st[j * 32] = v;
+            if (j == CANON) dv = v;
+        }
+    }
+    return dv;
+}
 
 template <int ORDER, int FORM>   // FORM 0: mass, 1: stiffness
-__global__ void __launch_bounds__(ROWPLAN_WARPS * 32)
-k_rowplan(const RowPlanCta* __restrict__ ctas, const RowPlanBundle* __restrict__ bundles,
-          const int32_t* __restrict__ visits, const uint32_t* __restrict__ units, const uint16_t* __restrict__ srcs,
-          const uint16_t* __restrict__ omap, const int32_t* __restrict__ rows, const double* __restrict__ xyz,
-          const int4* __restrict__ conn, const int64_t* __restrict__ ia, double* __restrict__ a, int accumulate,
-          int ncomp, int maxchunks, int maxrounds, double cval, const __grid_constant__ RowTables tab)
+__global__ void __launch_bounds__(ROWPLAN_WARPS * 32, 3)
+k_rowplan(const RowPlanCta* __restrict__ ctas, const uint4* __restrict__ hdrs, const int32_t* __restrict__ visits,
+          const uint4* __restrict__ blob, const double* __restrict__ xyz, const int4* __restrict__ conn,
+          double* __restrict__ a, int accumulate, int ncomp, int maxchunks, int maxrounds, double cval,
+          const __grid_constant__ RowTables tab)
 {
     constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
     constexpr int NS = FORM == 1 ? 6 : 1;
     extern __shared__ double sm[];
-    double* sS = sm;                                    // [NS][ROWPLAN_VMAX]
+    double* sT = sm;                                    // [3][20][6] (stiffness) / [3][20] (mass)
+    double* sS = sm + 360;                              // [NS][ROWPLAN_VMAX]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int stageSize = maxchunks * N * 32 + 2;       // + zero cell (kept even)
-    const int outSize = maxrounds * 32 + 32;            // task results + 32 diagonal slots
-    double* stage = sm + NS * ROWPLAN_VMAX + warp * (stageSize + outSize);
+    const int stageSize = ROWPLAN_ZOFF + maxchunks * N * 32;   // zero cell (+pad), then the tile
+    const int outSize = maxrounds * 32 + 2;                    // task results + the warp-reduced diagonal
+    double* stage = sS + NS * ROWPLAN_VMAX + warp * (stageSize + outSize);
+    for (int k = threadIdx.x; k < 360; k += blockDim.x)
+        sT[k] = FORM == 0 ? (k < 60 ? tab.T[k / 20][k % 20][0] : 0.0) : tab.T[k / 120][(k / 6) % 20][k % 6];
     double* out = stage + stageSize;
-    const int ZERO = maxchunks * N * 32;
     const int DIAG = maxrounds * 32;
     const RowPlanCta cta = ctas[blockIdx.x];
+    uint32_t b = warp;
+    uint4 hq = __ldg(&hdrs[cta.bundle_off + b]);        // header array is padded: always in bounds
 
     // ---- phase A: geometry of every element touched by this CTA's rows, once ----
     for (int v = threadIdx.x; v < (int)cta.nvisit; v += blockDim.x) {
@@ -98,138 +151,103 @@ k_rowplan(const RowPlanCta* __restrict__ ctas, const RowPlanBundle* __restrict__
             sS[5 * ROWPLAN_VMAX + v] = cj * (h[2][0] * h[3][0] + h[2][1] * h[3][1] + h[2][2] * h[3][2]);
         }
     }
-    if (lane == 0) stage[ZERO] = 0.0;
+    if (lane == 0) stage[0] = 0.0;
     __syncthreads();
 
-    for (uint32_t b = warp; b < cta.nbundle; b += ROWPLAN_WARPS) {
-        const RowPlanBundle bd = bundles[cta.bundle_off + b];
-        const int kind = bd.kind;
-        const int canon = tab.canon[kind];
-        out[DIAG + lane] = 0.0;
-        __syncwarp();
+    while (b < cta.nbundle) {
+        const uint4 hnext = __ldg(&hdrs[cta.bundle_off + b + ROWPLAN_WARPS]);
+        const int niter4 = hq.y & 0xFFFF, nout = hq.y >> 16;
+        const int nrows = hq.z & 0xFF, nchunks = (hq.z >> 8) & 0xFF, kind = (hq.z >> 16) & 0xFF, flags = hq.z >> 24;
+        const uint4* B = blob + hq.x;
+        // ---- all loads of the bundle are issued up front ----
+        const uint32_t u0 = __ldg(reinterpret_cast<const uint32_t*>(B) + lane);
+        const uint4 ri = __ldg(B + nchunks * 8 + min(lane, nrows - 1));
+        const uint2* sp = reinterpret_cast<const uint2*>(B + nchunks * 8 + nrows) + (size_t)lane * niter4;
+        const uint16_t* om = reinterpret_cast<const uint16_t*>(B + nchunks * 8 + nrows + niter4 * 16);
+        uint2 cur = niter4 ? __ldg(sp) : make_uint2(0u, 0u);
+        uint32_t om0 = lane < nout ? __ldg(om + lane) : ROWPLAN_OMAP_ZERO;
+        uint32_t om1 = lane + 32 < nout ? __ldg(om + lane + 32) : ROWPLAN_OMAP_ZERO;
+        uint32_t om2 = lane + 64 < nout ? __ldg(om + lane + 64) : ROWPLAN_OMAP_ZERO;
+        uint32_t om3 = lane + 96 < nout ? __ldg(om + lane + 96) : ROWPLAN_OMAP_ZERO;
+
         // ---- phase 1: lane = unit; its row of the (re-labelled) local matrix goes to stage[entry][lane] ----
-        for (int ch = 0; ch < bd.nchunks; ++ch) {
-            const uint32_t u = __ldg(&units[(size_t)(bd.unit_off + ch) * 32 + lane]);
-            const bool active = u != ROWPLAN_UNIT_NONE;
-            const int slot = (int)(u >> 24);
-            double dval = 0.0;
-            if (active) {
-                const int vis = u & 0xFFFF;
-                double* st = stage + (size_t)ch * N * 32 + lane;
-                if (FORM == 0) {
-                    const double cj = sS[vis];
-#pragma unroll
-                    for (int j = 0; j < N; ++j) {
-                        const double v = cj * tab.T[kind][j][0];
-                        st[j * 32] = v;
-                        if (j == canon) dval = v;
-                    }
-                } else {
-                    const int p0 = (u >> 16) & 3, p1 = (u >> 18) & 3, p2 = (u >> 20) & 3, p3 = (u >> 22) & 3;
-                    const double s01 = sS[pair_idx(p0, p1) * ROWPLAN_VMAX + vis];
-                    const double s02 = sS[pair_idx(p0, p2) * ROWPLAN_VMAX + vis];
-                    const double s03 = sS[pair_idx(p0, p3) * ROWPLAN_VMAX + vis];
-                    const double s12 = sS[pair_idx(p1, p2) * ROWPLAN_VMAX + vis];
-                    const double s13 = sS[pair_idx(p1, p3) * ROWPLAN_VMAX + vis];
-                    const double s23 = sS[pair_idx(p2, p3) * ROWPLAN_VMAX + vis];
-                    // rows of the Gram matrix sum to zero: S_kk = -sum_{l != k} S_kl
-                    const double s11 = -(s01 + s12 + s13), s22 = -(s02 + s12 + s23), s33 = -(s03 + s13 + s23);
-#pragma unroll
-                    for (int j = 0; j < N; ++j) {
-                        const double* t = tab.T[kind][j];
-                        double v = s11 * t[0];
-                        v = fma(s22, t[1], v);
-                        v = fma(s33, t[2], v);
-                        v = fma(s12, t[3], v);
-                        v = fma(s13, t[4], v);
-                        v = fma(s23, t[5], v);
-                        st[j * 32] = v;
-                        if (j == canon) dval = v;
-                    }
-                }
-            }
-            // diagonal: segmented sum over the lanes of each row (contiguous lanes share a slot)
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const double v = __shfl_down_sync(0xffffffffu, dval, off);
-                const int s2 = __shfl_down_sync(0xffffffffu, slot, off);
-                if (lane + off < 32 && s2 == slot) dval += v;
-            }
-            const int sprev = __shfl_up_sync(0xffffffffu, slot, 1);
-            if (active && (lane == 0 || sprev != slot)) out[DIAG + slot] += dval;
-            __syncwarp();
+        double dsum = 0.0;
+        for (int ch = 0; ch < nchunks; ++ch) {
+            const uint32_t u = ch == 0 ? u0 : __ldg(reinterpret_cast<const uint32_t*>(B) + ch * 32 + lane);
+            // every lane computes (inactive lanes read visit 0 and write a tile column nobody references): the code
+            // stays warp-convergent, so the reference tables are read through the uniform datapath (LDCU + DFMA UR)
+            double* st = stage + ROWPLAN_ZOFF + ch * N * 32 + lane;
+            double dv;
+            if (ORDER == 1 || kind == 0) dv = unit_row<ORDER, FORM, 0>(sT, sS, u, st);
+            else if (ORDER == 2 || kind == 1) dv = unit_row<ORDER, FORM, (ORDER >= 2 ? 1 : 0)>(sT, sS, u, st);
+            else dv = unit_row<ORDER, FORM, (ORDER >= 3 ? 2 : 0)>(sT, sS, u, st);
+            if (!(u & ROWPLAN_UNIT_ACTIVE)) dv = 0.0;
+            dsum += dv;
         }
+        if (flags & ROWPLAN_FLAG_WARPDIAG) {
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) dsum += __shfl_xor_sync(0xffffffffu, dsum, off);
+            if (lane == 0) out[DIAG] = dsum;
+        }
+        __syncwarp();
         // ---- phase 2: lane = a balanced list of output nonzeros, summed from the staging tile in plan order ----
         {
-            const uint16_t* sp = srcs + (size_t)bd.src_off * 32 + lane;
             double acc = 0.0;
-            int t = 0;
-            uint32_t e = bd.niter ? __ldg(sp) : 0;
-            for (int it = 0; it < bd.niter; ++it) {
-                const uint32_t en = (it + 1 < bd.niter) ? __ldg(sp + (size_t)(it + 1) * 32) : 0;
-                int sl = e & ROWPLAN_SRC_MASK;
-                sl = sl == ROWPLAN_SRC_MASK ? ZERO : sl;
-                acc += stage[sl];
-                if (e & ROWPLAN_SRC_END) {
-                    out[t * 32 + lane] = acc;
-                    acc = 0.0;
-                    ++t;
+            double* op = out + lane;
+            for (int it = 0; it < niter4; ++it) {
+                const uint2 nxt = (it + 1 < niter4) ? __ldg(sp + it + 1) : make_uint2(0u, 0u);
+                const uint32_t e[4] = {cur.x & 0xFFFFu, cur.x >> 16, cur.y & 0xFFFFu, cur.y >> 16};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    acc += stage[e[k] & 0x7FFFu];
+                    if (e[k] & ROWPLAN_SRC_END) {
+                        *op = acc;
+                        op += 32;
+                        acc = 0.0;
+                    }
                 }
-                e = en;
+                cur = nxt;
             }
         }
         __syncwarp();
         // ---- phase 3: coalesced store of the rows' value segments ----
-        {
-            int64_t mybase = 0;
-            int mylen = 0;
-            int32_t myrow = 0;
-            if (lane < bd.nrows) {
-                myrow = __ldg(&rows[bd.row_off + lane]);
-                mybase = __ldg(&ia[(int64_t)myrow * ncomp]);
-                mylen = (int)((__ldg(&ia[(int64_t)myrow * ncomp + 1]) - mybase) / ncomp);
-            }
-            int off = 0;
-            for (int k = 0; k < bd.nrows; ++k) {
-                const int64_t base = __shfl_sync(0xffffffffu, mybase, k);
-                const int len = __shfl_sync(0xffffffffu, mylen, k);
-                const int32_t row = __shfl_sync(0xffffffffu, myrow, k);
-                const uint16_t* om = omap + (size_t)bd.omap_off + off;
+        for (int ob = 0, r = 0; ob < nout; ob += 32, ++r) {
+            const int o = ob + lane;
+            uint32_t m = r == 0 ? om0 : r == 1 ? om1 : r == 2 ? om2 : r == 3 ? om3
+                                                       : (o < nout ? (uint32_t)__ldg(om + o) : ROWPLAN_OMAP_ZERO);
+            const int k = m >> 11;
+            const uint32_t blo = __shfl_sync(0xffffffffu, ri.x, k), bhi = __shfl_sync(0xffffffffu, ri.y, k);
+            const int len = (int)__shfl_sync(0xffffffffu, ri.z, k), roff = (int)__shfl_sync(0xffffffffu, ri.w, k);
+            if (o < nout) {
+                const uint32_t slot = m & 0x3FFu;
+                const double v = (m & ROWPLAN_OMAP_DIAG) ? out[DIAG] : (slot == ROWPLAN_OMAP_ZERO ? 0.0 : out[slot]);
+                const int64_t base = (int64_t)(((uint64_t)bhi << 32) | blo);
+                const int p = o - roff;
                 if (ncomp == 1) {
-                    for (int p = lane; p < len; p += 32) {
-                        const uint32_t m = __ldg(om + p);
-                        const double v = m == 0xFFFFu ? 0.0 : out[(m & 0x8000u) ? DIAG + (m & 0x7FFFu) : m];
-                        if (accumulate) a[base + p] += v;
-                        else a[base + p] = v;
-                    }
+                    if (accumulate) a[base + p] += v;
+                    else a[base + p] = v;
                 } else {
-                    // product space, block = v * Id: row c1 holds v at column 3p + c1 (zeros elsewhere)
-                    for (int c1 = 0; c1 < ncomp; ++c1) {
-                        const int64_t b1 = c1 == 0 ? base : __ldg(&ia[(int64_t)row * ncomp + c1]);
-                        for (int q = lane; q < len * ncomp; q += 32) {
-                            const int p = q / ncomp, c2 = q - p * ncomp;
-                            double v = 0.0;
-                            if (c2 == c1) {
-                                const uint32_t m = __ldg(om + p);
-                                v = m == 0xFFFFu ? 0.0 : out[(m & 0x8000u) ? DIAG + (m & 0x7FFFu) : m];
-                            }
-                            if (!accumulate) a[b1 + q] = v;
-                            else if (c2 == c1) a[b1 + q] += v;
+                    // product space, block = v * Id: component row c1 starts at base + c1*len*ncomp
+                    for (int c1 = 0; c1 < ncomp; ++c1)
+                        for (int c2 = 0; c2 < ncomp; ++c2) {
+                            double* dst = a + base + (int64_t)c1 * len * ncomp + (int64_t)p * ncomp + c2;
+                            if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
+                            else if (!accumulate) *dst = 0.0;
                         }
-                    }
                 }
-                off += len;
             }
         }
         __syncwarp();
+        hq = hnext;
+        b += ROWPLAN_WARPS;
     }
 }
 
 size_t rowplan_smem_bytes(const RowPlan* p, int form)
 {
     const int NS = form == 1 ? 6 : 1;
-    const size_t stageSize = (size_t)p->maxchunks * p->n * 32 + 2, outSize = (size_t)p->maxrounds * 32 + 32;
-    return sizeof(double) * (NS * ROWPLAN_VMAX + ROWPLAN_WARPS * (stageSize + outSize));
+    const size_t stageSize = ROWPLAN_ZOFF + (size_t)p->maxchunks * p->n * 32, outSize = (size_t)p->maxrounds * 32 + 2;
+    return sizeof(double) * (360 + NS * ROWPLAN_VMAX + ROWPLAN_WARPS * (stageSize + outSize));
 }
 
 template <typename T>
@@ -270,13 +288,11 @@ int feelgpu_rowplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, const int6
     p->ncontrib = hp.ncontrib;
     p->nsrc_padded = hp.nsrc_padded;
     p->nvisits = hp.nvisits;
+    p->nbundle = (int64_t)hp.hdrs.size() - ROWPLAN_WARPS;
     cudaError_t err = upload(&p->d_ctas, hp.ctas, p->bytes);
-    if (err == cudaSuccess) err = upload(&p->d_bundles, hp.bundles, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_hdrs, hp.hdrs, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_visits, hp.visits, p->bytes);
-    if (err == cudaSuccess) err = upload(&p->d_units, hp.units, p->bytes);
-    if (err == cudaSuccess) err = upload(&p->d_srcs, hp.srcs, p->bytes);
-    if (err == cudaSuccess) err = upload(&p->d_omap, hp.omap, p->bytes);
-    if (err == cudaSuccess) err = upload(&p->d_rows, hp.rows, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_blob, hp.blob, p->bytes);
     pat->plan = p;
     if (err != cudaSuccess) {
         ctx->last_error = std::string("rowplan upload: ") + cudaGetErrorString(err);
@@ -295,12 +311,9 @@ void feelgpu_rowplan_destroy(feelgpu_pattern_t pat)
     RowPlan* p = pat->plan;
     if (!p) return;
     cudaFree(p->d_ctas);
-    cudaFree(p->d_bundles);
+    cudaFree(p->d_hdrs);
     cudaFree(p->d_visits);
-    cudaFree(p->d_units);
-    cudaFree(p->d_srcs);
-    cudaFree(p->d_omap);
-    cudaFree(p->d_rows);
+    cudaFree(p->d_blob);
     delete p;
     pat->plan = nullptr;
 }
@@ -359,8 +372,8 @@ int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, co
 #define RLAUNCH(O, F)                                                                                               \
     do {                                                                                                            \
         FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rowplan<O, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-        k_rowplan<O, F><<<grid, threads, sh, s>>>(p->d_ctas, p->d_bundles, p->d_visits, p->d_units, p->d_srcs,       \
-                                                  p->d_omap, p->d_rows, m->d_xyz, m->d_conn, pat->d_ia, a,          \
+        k_rowplan<O, F><<<grid, threads, sh, s>>>(p->d_ctas, reinterpret_cast<const uint4*>(p->d_hdrs), p->d_visits, \
+                                                  reinterpret_cast<const uint4*>(p->d_blob), m->d_xyz, m->d_conn, a, \
                                                   accumulate, p->ncomp, p->maxchunks, p->maxrounds, hp.cval[0], tab); \
     } while (0)
     switch (p->order * 2 + form) {

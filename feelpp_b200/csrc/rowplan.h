@@ -23,43 +23,49 @@
 #include <string>
 #include <vector>
 
-struct RowPlanBundle {           // 32 bytes
-    uint32_t unit_off;           // units:  u32 [unit_off + chunk][32]
-    uint32_t src_off;            // sources: u16 [src_off + iter][32]
-    uint32_t omap_off;           // out map: u16 [omap_off + o], o over the concatenated outputs of the bundle's rows
-    uint32_t row_off;            // rows:   i32 [row_off + k]
-    uint16_t niter;              // phase-2 iterations
-    uint16_t nout;               // outputs (node-level nonzeros) of the bundle
-    uint8_t nrows, nchunks, kind, nrounds;
-    uint32_t pad[2];
+// ---- device layout (v2) ------------------------------------------------------------------------------------------
+// Every bundle is one contiguous, 16-byte aligned blob so that all its loads can be issued at once:
+//   [units   : nchunks x 8 quads ]  u32 [chunk][lane]
+//   [rowinfo : nrows quads       ]  {int64 base (CSR offset of the row's first value), int32 len (node level), int32 pad}
+//   [sources : niter4 x 16 quads ]  u16, LANE-major: lane l owns entries [l*4*niter4, (l+1)*4*niter4), read 4 at a time
+//   [outmap  : ceil(nout/8) quads]  u16 per output nonzero of the concatenated rows
+// and a 16-byte header in a separate array (the next bundle's header is prefetched while the current one runs).
+struct RowPlanHeader {           // 16 bytes
+    uint32_t q0;                 // blob offset in quads (16 B)
+    uint16_t niter4;             // phase-2 iterations / 4
+    uint16_t nout;               // output nonzeros (node level)
+    uint8_t nrows, nchunks, kind, flags;
+    uint32_t pad;
 };
+#define ROWPLAN_FLAG_WARPDIAG 1  // single row: its diagonal is a full-warp reduction of the canonical entry
 
 struct RowPlanCta {              // 16 bytes
     uint32_t visit_off, nvisit;  // visit element ids: i32 [visit_off + v]
     uint32_t bundle_off, nbundle;
 };
 
-// unit word: visit (16 bits) | perm (8 bits: 4 x 2-bit vertex labels) | row slot in the bundle (8 bits)
-#define ROWPLAN_UNIT_NONE 0xFFFFFFFFu
-// source entry: staging slot (bits 0..13) | end-of-output flag (bit 15)
+// unit word: bits 0-9 visit | bits 10-27 six 3-bit indices of S01,S02,S03,S12,S13,S23 in the visit record | bit 30 active
+#define ROWPLAN_UNIT_ACTIVE 0x40000000u
+// source entry: staging slot + ROWPLAN_ZOFF (0 = the zero cell) | end-of-output flag (bit 15)
 #define ROWPLAN_SRC_END 0x8000u
-#define ROWPLAN_SRC_MASK 0x3FFFu
+#define ROWPLAN_ZOFF 32
+// outmap entry: bits 0-9 result slot (task*32+lane; 1023 = structural zero) | bit 10 warp-diagonal | bits 11-15 row slot
+#define ROWPLAN_OMAP_ZERO 1023u
+#define ROWPLAN_OMAP_DIAG 0x400u
 
-#define ROWPLAN_VMAX 640         // visits per CTA
+#define ROWPLAN_VMAX 640         // visits per CTA (< 1024)
 #define ROWPLAN_WARPS 8          // warps per CTA
 #define ROWPLAN_MAXCHUNKS 4      // a row may have up to 128 elements around its node
-#define ROWPLAN_MAXROUNDS 24     // outputs per lane per bundle
+#define ROWPLAN_MAXROUNDS 23     // results per lane per bundle (23*32+31 < 1023)
+#define ROWPLAN_BIGROW 12        // rows with more units are alone in their bundle (warp-reduced diagonal)
 
 struct RowPlanHost {
     int order = 0, n = 0, ncomp = 1;
     int maxchunks = 1, maxrounds = 1;
     std::vector<RowPlanCta> ctas;
-    std::vector<RowPlanBundle> bundles;
+    std::vector<RowPlanHeader> hdrs;
     std::vector<int32_t> visits;
-    std::vector<uint32_t> units;
-    std::vector<uint16_t> srcs;
-    std::vector<uint16_t> omap;
-    std::vector<int32_t> rows;
+    std::vector<uint32_t> blob;  // 4 words per quad
     // statistics
     int64_t nunits = 0, ncontrib = 0, nsrc_padded = 0, nvisits = 0;
     std::string error;
@@ -67,14 +73,11 @@ struct RowPlanHost {
 
 struct RowPlan {                 // device mirror
     int order = 0, n = 0, ncomp = 1, maxchunks = 1, maxrounds = 1;
-    int64_t ncta = 0;
+    int64_t ncta = 0, nbundle = 0;
     RowPlanCta* d_ctas = nullptr;
-    RowPlanBundle* d_bundles = nullptr;
+    RowPlanHeader* d_hdrs = nullptr;
     int32_t* d_visits = nullptr;
-    uint32_t* d_units = nullptr;
-    uint16_t* d_srcs = nullptr;
-    uint16_t* d_omap = nullptr;
-    int32_t* d_rows = nullptr;
+    uint32_t* d_blob = nullptr;
     int64_t bytes = 0;
     int64_t nunits = 0, ncontrib = 0, nsrc_padded = 0, nvisits = 0;
 };

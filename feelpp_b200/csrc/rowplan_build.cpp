@@ -178,17 +178,17 @@ namespace {
 struct CtaSeg { int64_t nb, ne; uint32_t visit_off, nvisit; };
 
 struct Local {                      // per-thread output, concatenated at the end
-    std::vector<RowPlanBundle> bundles;
-    std::vector<uint32_t> units;
-    std::vector<uint16_t> srcs, omap;
-    std::vector<int32_t> rows;
+    std::vector<RowPlanHeader> hdrs;
+    std::vector<uint32_t> blob;     // 4 words per quad
     std::vector<std::pair<uint32_t, uint32_t>> cta_bundles;   // (first bundle, count) per CTA handled
     int maxchunks = 1, maxrounds = 1;
-    int64_t nunits = 0, ncontrib = 0;
+    int64_t nunits = 0, ncontrib = 0, nsrc = 0;
     std::string error;
 };
 
-// builds one bundle from nodes nodes[s..t) (same kind); returns false if a capacity limit is hit
+inline int pair_idx(int x, int y) { return x + y - 1 + (std::min(x, y) >= 1 ? 1 : 0); }
+
+// builds one bundle from nodes[0..cnt) (same kind); returns false if a capacity limit is hit
 bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int32_t* nodes, int cnt, Local& L,
                  std::vector<std::vector<uint16_t>>& srcOfOut, std::vector<int>& taskOrder, bool& hardFail)
 {
@@ -200,20 +200,21 @@ bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int3
         totalUnits += B.nptr[nd + 1] - B.nptr[nd];
         nout += (int)((B.ia[nd * B.ncomp + 1] - B.ia[nd * B.ncomp]) / B.ncomp);
     }
-    int nchunks = (int)std::max<int64_t>(1, (totalUnits + 31) / 32);
+    const int nchunks = (int)std::max<int64_t>(1, (totalUnits + 31) / 32);
     if (cnt > 1 && totalUnits > 32) return false;
-    if (cnt > 32) return false;
+    if (cnt > 31) return false;
     if (nchunks > ROWPLAN_MAXCHUNKS || nout > 32 * ROWPLAN_MAXROUNDS) {
         if (cnt == 1) hardFail = true;
         return false;
     }
     const int kind = B.kind[nodes[0]];
-    // lanes: rows in order, units in ascending element order
-    std::vector<uint32_t> unitw((size_t)nchunks * 32, ROWPLAN_UNIT_NONE);
+    const bool warpDiag = (cnt == 1 && totalUnits > ROWPLAN_BIGROW);
+    std::vector<uint32_t> unitw((size_t)nchunks * 32, 0u);
     if ((int)srcOfOut.size() < nout) srcOfOut.resize(nout);
     for (int o = 0; o < nout; ++o) srcOfOut[o].clear();
-    std::vector<int> diagOut(cnt, -1);
+    int diagOut = -1;
     int lane = 0, outoff = 0;
+    std::vector<int> rowOff(cnt + 1, 0);
     for (int k = 0; k < cnt; ++k) {
         const int64_t nd = nodes[k];
         const int len = (int)((B.ia[nd * B.ncomp + 1] - B.ia[nd * B.ncomp]) / B.ncomp);
@@ -221,19 +222,22 @@ bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int3
             const int64_t e = B.uelt[q];
             const int i = B.uloc[q];
             const RowPlanRot& R = B.rot[i];
-            const uint32_t perm = R.perm[0] | (R.perm[1] << 2) | (R.perm[2] << 4) | (R.perm[3] << 6);
-            unitw[lane] = (uint32_t)uvis[q] | (perm << 16) | ((uint32_t)k << 24);
+            const int p0 = R.perm[0], p1 = R.perm[1], p2 = R.perm[2], p3 = R.perm[3];
+            const uint32_t pairs = pair_idx(p0, p1) | (pair_idx(p0, p2) << 3) | (pair_idx(p0, p3) << 6) |
+                                   (pair_idx(p1, p2) << 9) | (pair_idx(p1, p3) << 12) | (pair_idx(p2, p3) << 15);
+            unitw[lane] = (uint32_t)uvis[q] | (pairs << 10) | ROWPLAN_UNIT_ACTIVE;
             const uint16_t* pe = B.pos + (e * n + i) * n;     // positions of the element's columns in this row
             const int chunk = lane >> 5, ln = lane & 31;
             for (int jr = 0; jr < n; ++jr) {
                 const int jo = R.rmap[jr];
                 const int p = pe[jo];
                 if (p >= len) { L.error = "row plan: position outside the row"; hardFail = true; return false; }
-                if (jo == i) { diagOut[k] = outoff + p; continue; }   // diagonal: warp-reduced in phase 1
-                srcOfOut[outoff + p].push_back((uint16_t)((chunk * n + jr) * 32 + ln));
+                if (jo == i && warpDiag) { diagOut = outoff + p; continue; }   // diagonal: warp-reduced in phase 1
+                srcOfOut[outoff + p].push_back((uint16_t)(ROWPLAN_ZOFF + (chunk * n + jr) * 32 + ln));
             }
         }
         outoff += len;
+        rowOff[k + 1] = outoff;
     }
     // LPT dealing of the outputs over the 32 lanes
     taskOrder.clear();
@@ -258,43 +262,60 @@ bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int3
         if (cnt == 1) hardFail = true;
         return false;
     }
-    // emit
-    RowPlanBundle bd;
-    std::memset(&bd, 0, sizeof(bd));
-    bd.unit_off = (uint32_t)(L.units.size() / 32);
-    bd.src_off = (uint32_t)(L.srcs.size() / 32);
-    bd.omap_off = (uint32_t)L.omap.size();
-    bd.row_off = (uint32_t)L.rows.size();
-    bd.niter = (uint16_t)niter;
-    bd.nout = (uint16_t)nout;
-    bd.nrows = (uint8_t)cnt;
-    bd.nchunks = (uint8_t)nchunks;
-    bd.kind = (uint8_t)kind;
-    bd.nrounds = (uint8_t)nrounds;
-    L.units.insert(L.units.end(), unitw.begin(), unitw.end());
-    const uint16_t nullSlot = 0x3FFF;   // the kernel maps it to its zero cell
-    size_t sbase = L.srcs.size();
-    L.srcs.resize(sbase + (size_t)niter * 32, nullSlot);
-    size_t obase = L.omap.size();
-    L.omap.resize(obase + nout, 0xFFFF);   // 0xFFFF: structural zero (no source): stored as 0
+    const int niter4 = (niter + 3) / 4;
+    // ---- emit the blob ----
+    RowPlanHeader h;
+    std::memset(&h, 0, sizeof(h));
+    h.q0 = (uint32_t)(L.blob.size() / 4);
+    h.niter4 = (uint16_t)niter4;
+    h.nout = (uint16_t)nout;
+    h.nrows = (uint8_t)cnt;
+    h.nchunks = (uint8_t)nchunks;
+    h.kind = (uint8_t)kind;
+    h.flags = warpDiag ? ROWPLAN_FLAG_WARPDIAG : 0;
+    const size_t qUnits = (size_t)nchunks * 8, qRows = (size_t)cnt, qSrc = (size_t)niter4 * 16, qOmap = (size_t)(nout + 7) / 8;
+    const size_t base = L.blob.size();
+    L.blob.resize(base + 4 * (qUnits + qRows + qSrc + qOmap), 0u);
+    uint32_t* w = L.blob.data() + base;
+    std::memcpy(w, unitw.data(), sizeof(uint32_t) * unitw.size());
+    w += 4 * qUnits;
+    for (int k = 0; k < cnt; ++k) {
+        const int64_t nd = nodes[k];
+        const int64_t b0 = B.ia[nd * B.ncomp];
+        const int32_t len = (int32_t)((B.ia[nd * B.ncomp + 1] - b0) / B.ncomp);
+        std::memcpy(w + 4 * k, &b0, 8);
+        std::memcpy(w + 4 * k + 2, &len, 4);
+        w[4 * k + 3] = (uint32_t)rowOff[k];
+    }
+    w += 4 * qRows;
+    uint16_t* sp = reinterpret_cast<uint16_t*>(w);            // lane-major, 4*niter4 entries per lane, null = 0
+    std::vector<uint16_t> om(qOmap * 8, (uint16_t)ROWPLAN_OMAP_ZERO);
+    {
+        // row slot of every output
+        int k = 0;
+        for (int o = 0; o < nout; ++o) {
+            while (o >= rowOff[k + 1]) ++k;
+            om[o] = (uint16_t)(ROWPLAN_OMAP_ZERO | (k << 11));
+        }
+    }
     for (int l = 0; l < 32; ++l) {
         int it = 0;
         for (size_t t = 0; t < laneTasks[l].size(); ++t) {
             const int o = laneTasks[l][t];
             const auto& sv = srcOfOut[o];
-            for (size_t s = 0; s < sv.size(); ++s, ++it)
-                L.srcs[sbase + (size_t)it * 32 + l] = (uint16_t)(sv[s] | (s + 1 == sv.size() ? ROWPLAN_SRC_END : 0));
-            L.omap[obase + o] = (uint16_t)(t * 32 + l);
+            for (size_t s2 = 0; s2 < sv.size(); ++s2, ++it)
+                sp[(size_t)l * 4 * niter4 + it] = (uint16_t)(sv[s2] | (s2 + 1 == sv.size() ? ROWPLAN_SRC_END : 0));
+            om[o] = (uint16_t)((om[o] & 0xF800u) | (uint16_t)(t * 32 + l));
         }
     }
-    for (int k = 0; k < cnt; ++k) {
-        if (diagOut[k] >= 0) L.omap[obase + diagOut[k]] = (uint16_t)(0x8000 | k);   // diagonal slot k
-        L.rows.push_back(nodes[k]);
-    }
-    L.bundles.push_back(bd);
+    if (diagOut >= 0) om[diagOut] = (uint16_t)((om[diagOut] & 0xF800u) | ROWPLAN_OMAP_DIAG);
+    w += 4 * qSrc;
+    std::memcpy(w, om.data(), sizeof(uint16_t) * om.size());
+    L.hdrs.push_back(h);
     L.maxchunks = std::max(L.maxchunks, nchunks);
     L.maxrounds = std::max(L.maxrounds, nrounds);
     L.nunits += totalUnits;
+    L.nsrc += (int64_t)niter4 * 4 * 32;
     for (int o = 0; o < nout; ++o) L.ncontrib += (int64_t)srcOfOut[o].size();
     return true;
 }
@@ -367,10 +388,8 @@ bool rowplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, 
             segs.push_back(sg);
         }
     }
-    stamp.clear();
-    stamp.shrink_to_fit();
-    vidx.clear();
-    vidx.shrink_to_fit();
+    stamp = std::vector<int32_t>();
+    vidx = std::vector<int32_t>();
 
     // ---- bundles, in parallel over CTAs ----
     const int64_t nCta = (int64_t)segs.size();
@@ -384,17 +403,21 @@ bool rowplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, 
             const CtaSeg& sg = segs[c];
             for (int kd = 0; kd < 3; ++kd) byKind[kd].clear();
             for (int64_t k = sg.nb; k < sg.ne; ++k) byKind[B.kind[B.order_[k]]].push_back(B.order_[k]);
-            const uint32_t first = (uint32_t)L.bundles.size();
+            const uint32_t first = (uint32_t)L.hdrs.size();
             for (int kd = 0; kd < 3; ++kd) {
                 const std::vector<int32_t>& nodes = byKind[kd];
                 size_t s = 0;
                 while (s < nodes.size()) {
-                    // greedy: the longest run of rows whose units fit one warp
+                    // greedy: the longest run of small rows whose units fit one warp; a big row goes alone
                     size_t t2 = s;
                     int64_t units = 0;
-                    while (t2 < nodes.size() && t2 - s < 32) {
+                    while (t2 < nodes.size() && t2 - s < 31) {
                         const int64_t u = B.nptr[nodes[t2] + 1] - B.nptr[nodes[t2]];
-                        if (t2 > s && units + u > 32) break;
+                        if (u > ROWPLAN_BIGROW) {
+                            if (t2 == s) ++t2;
+                            break;
+                        }
+                        if (units + u > 32) break;
                         units += u;
                         ++t2;
                     }
@@ -409,7 +432,7 @@ bool rowplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, 
                     s = t2;
                 }
             }
-            L.cta_bundles.emplace_back(first, (uint32_t)L.bundles.size() - first);
+            L.cta_bundles.emplace_back(first, (uint32_t)L.hdrs.size() - first);
         }
     };
     {
@@ -425,34 +448,24 @@ bool rowplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, 
     plan.order = order;
     plan.n = B.n;
     plan.ncomp = ncomp;
-    size_t nb = 0, nu = 0, ns = 0, no = 0, nr = 0;
-    for (auto& L : locals) { nb += L.bundles.size(); nu += L.units.size(); ns += L.srcs.size(); no += L.omap.size(); nr += L.rows.size(); }
-    if (nu / 32 > 0xFFFFFFFFull || ns / 32 > 0xFFFFFFFFull || no > 0xFFFFFFFFull) { plan.error = "row plan: offsets exceed 32 bits"; return false; }
-    plan.bundles.reserve(nb);
-    plan.units.reserve(nu);
-    plan.srcs.reserve(ns);
-    plan.omap.reserve(no);
-    plan.rows.reserve(nr);
+    size_t nb = 0, nq = 0;
+    for (auto& L : locals) { nb += L.hdrs.size(); nq += L.blob.size() / 4; }
+    if (nq + 64 > 0xFFFFFFFFull) { plan.error = "row plan: blob offsets exceed 32 bits"; return false; }
+    plan.hdrs.reserve(nb);
+    plan.blob.reserve(nq * 4 + 256);
     plan.ctas.resize(nCta);
     int64_t c = 0;
     for (auto& L : locals) {
-        const uint32_t bb = (uint32_t)plan.bundles.size(), ub = (uint32_t)(plan.units.size() / 32),
-                       sb = (uint32_t)(plan.srcs.size() / 32), ob = (uint32_t)plan.omap.size(), rb = (uint32_t)plan.rows.size();
-        for (auto bd : L.bundles) {
-            bd.unit_off += ub;
-            bd.src_off += sb;
-            bd.omap_off += ob;
-            bd.row_off += rb;
-            plan.bundles.push_back(bd);
+        const uint32_t hb = (uint32_t)plan.hdrs.size(), qb = (uint32_t)(plan.blob.size() / 4);
+        for (auto h : L.hdrs) {
+            h.q0 += qb;
+            plan.hdrs.push_back(h);
         }
-        plan.units.insert(plan.units.end(), L.units.begin(), L.units.end());
-        plan.srcs.insert(plan.srcs.end(), L.srcs.begin(), L.srcs.end());
-        plan.omap.insert(plan.omap.end(), L.omap.begin(), L.omap.end());
-        plan.rows.insert(plan.rows.end(), L.rows.begin(), L.rows.end());
+        plan.blob.insert(plan.blob.end(), L.blob.begin(), L.blob.end());
         for (auto& cb : L.cta_bundles) {
             plan.ctas[c].visit_off = segs[c].visit_off;
             plan.ctas[c].nvisit = segs[c].nvisit;
-            plan.ctas[c].bundle_off = bb + cb.first;
+            plan.ctas[c].bundle_off = hb + cb.first;
             plan.ctas[c].nbundle = cb.second;
             ++c;
         }
@@ -460,9 +473,13 @@ bool rowplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, 
         plan.maxrounds = std::max(plan.maxrounds, L.maxrounds);
         plan.nunits += L.nunits;
         plan.ncontrib += L.ncontrib;
+        plan.nsrc_padded += L.nsrc;
         L = Local();
     }
-    plan.nsrc_padded = (int64_t)plan.srcs.size();
+    plan.blob.resize(plan.blob.size() + 256, 0u);   // the kernel may read a few quads past the last blob
+    RowPlanHeader tail;
+    std::memset(&tail, 0, sizeof(tail));
+    for (int k = 0; k < ROWPLAN_WARPS; ++k) plan.hdrs.push_back(tail);   // header prefetch of "the next bundle"
     plan.nvisits = (int64_t)plan.visits.size();
     return true;
 }
