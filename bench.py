@@ -173,6 +173,7 @@ def gpu_arm(args):
     t0 = time.time()
     a = fpp.form2(_test=Xh, _trial=Xh, engine=eng, algorithm=algo)
     info["pattern_create_s"] = round(time.time() - t0, 2)
+    info["plan"] = a.plan_stats()
     u = v = fpp.Element(Xh)
     integ = integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v)))
     keep = E._Keep()

@@ -57,6 +57,7 @@ GPU_SYMBOLS = {
                                C.POINTER(C.c_void_p)],
     "feelgpu_pattern_nnz": [C.c_void_p, c_i64p],
     "feelgpu_pattern_destroy": [C.c_void_p],
+    "feelgpu_pattern_plan_stats": [C.c_void_p, c_i64p],
     "feelgpu_form2_assemble": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form1_assemble": [C.c_void_p, C.POINTER(Form1Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form2_assemble_host": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, c_dblp],

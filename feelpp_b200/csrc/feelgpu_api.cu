@@ -1,5 +1,6 @@
 // feelgpu_api.cu -- implementation of the C ABI declared in include/feelgpu.h.
 #include "feelgpu_internal.h"
+#include "rowplan.h"
 
 #include <algorithm>
 #include <cstring>
@@ -248,6 +249,25 @@ int feelgpu_pattern_nnz(feelgpu_pattern_t pat, int64_t* nnz)
 {
     if (!pat || !nnz) return FEELGPU_ERR_ARG;
     *nnz = pat->nnz;
+    return FEELGPU_OK;
+}
+
+int feelgpu_pattern_plan_stats(feelgpu_pattern_t pat, int64_t stats[10])
+{
+    if (!pat || !stats) return FEELGPU_ERR_ARG;
+    for (int k = 0; k < 10; ++k) stats[k] = 0;
+    const RowPlan* p = pat->plan;
+    if (!p) return FEELGPU_OK;
+    stats[0] = 1;
+    stats[1] = p->ncta;
+    stats[2] = p->nbundle;
+    stats[3] = p->nunits;
+    stats[4] = p->ncontrib;
+    stats[5] = p->nsrc_padded;
+    stats[6] = p->nvisits;
+    stats[7] = p->bytes;
+    stats[8] = p->maxchunks;
+    stats[9] = p->maxrounds;
     return FEELGPU_OK;
 }
 

@@ -20,13 +20,15 @@ struct RowTables {
     int pad;
 };
 
+// Canonical rows of the reference matrices.  They are read with a RUNTIME kind index (LDC through the constant cache,
+// all lanes the same address): with a compile-time index ptxas hoists the loads out of the bundle loop, 120 doubles do
+// not fit the uniform register file and spill; reading them from shared memory costs 30 LSU wavefronts per bundle on a
+// kernel that is LSU-bound.
+__constant__ RowTables c_rowtab;
+
 // one unit's row of the re-labelled local matrix -> stage[entry][lane]; returns the canonical (diagonal) entry.
-// sT: the canonical rows of the reference matrices in shared memory, [kind][j][6]; every lane reads the same 16 bytes
-// (broadcast, one wavefront).  They cannot live in the constant bank: ptxas hoists the uniform loads out of the bundle
-// loop and 120 doubles do not fit the uniform register file.
 template <int ORDER, int FORM, int KIND>
-__device__ __forceinline__ double unit_row(const double* __restrict__ sT, const double* __restrict__ sS, uint32_t u,
-                                           double* st)
+__device__ __forceinline__ double unit_row(int kind, const double* __restrict__ sS, uint32_t u, double* st)
 {
     constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
     constexpr int CANON = KIND == 0 ? 0 : (KIND == 1 ? 4 + 2 * (ORDER - 1) : 4 + 6 * (ORDER - 1) + 3);
@@ -34,17 +36,11 @@ __device__ __forceinline__ double unit_row(const double* __restrict__ sT, const 
     double dv = 0.0;
     if (FORM == 0) {
         const double cj = sS[vis];
-        const double2* t2 = reinterpret_cast<const double2*>(sT + KIND * 20);
 #pragma unroll
-        for (int j = 0; j < N; j += 2) {
-            const double2 t = t2[j / 2];
-            const double v0 = cj * t.x, v1 = cj * t.y;
-            st[j * 32] = v0;
-            if (j == CANON) dv = v0;
-            if (j + 1 < N) {
-                st[(j + 1) * 32] = v1;
-                if (j + 1 == CANON) dv = v1;
-            }
+        for (int j = 0; j < N; ++j) {
+            const double v = cj * c_rowtab.T[kind][j][0];
+            st[j * 32] = v;
+            if (j == CANON) dv = v;
         }
     } else {
         const double s01 = sS[((u >> 10) & 7) * ROWPLAN_VMAX + vis];
@@ -55,16 +51,15 @@ __device__ __forceinline__ double unit_row(const double* __restrict__ sT, const 
         const double s23 = sS[((u >> 25) & 7) * ROWPLAN_VMAX + vis];
         // rows of the barycentric Gram matrix sum to zero: S_kk = -sum_{l != k} S_kl
         const double s11 = -(s01 + s12 + s13), s22 = -(s02 + s12 + s23), s33 = -(s03 + s13 + s23);
-        const double2* t2 = reinterpret_cast<const double2*>(sT + KIND * 120);
-#pragma unroll
+        // partially unrolled on purpose: a rolled loop keeps the table loads next to their uses (no hoisting, no spills)
+#pragma unroll 2
         for (int j = 0; j < N; ++j) {
-            const double2 ta = t2[j * 3 + 0], tb = t2[j * 3 + 1], tc = t2[j * 3 + 2];
-            double v = s11 * ta.x;
-            v = fma(s22, ta.y, v);
-            v = fma(s33, tb.x, v);
-            v = fma(s12, tb.y, v);
-            v = fma(s13, tc.x, v);
-            v = fma(s23, tc.y, v);
+            double v = s11 * c_rowtab.T[kind][j][0];
+            v = fma(s22, c_rowtab.T[kind][j][1], v);
+            v = fma(s33, c_rowtab.T[kind][j][2], v);
+            v = fma(s12, c_rowtab.T[kind][j][3], v);
+            v = fma(s13, c_rowtab.T[kind][j][4], v);
+            v = fma(s23, c_rowtab.T[kind][j][5], v);
             st[j * 32] = v;
             if (j == CANON) dv = v;
         }
@@ -76,20 +71,16 @@ template <int ORDER, int FORM>   // FORM 0: mass, 1: stiffness
 __global__ void __launch_bounds__(ROWPLAN_WARPS * 32, 3)
 k_rowplan(const RowPlanCta* __restrict__ ctas, const uint4* __restrict__ hdrs, const int32_t* __restrict__ visits,
           const uint4* __restrict__ blob, const double* __restrict__ xyz, const int4* __restrict__ conn,
-          double* __restrict__ a, int accumulate, int ncomp, int maxchunks, int maxrounds, double cval,
-          const __grid_constant__ RowTables tab)
+          double* __restrict__ a, int accumulate, int ncomp, int maxchunks, int maxrounds, double cval)
 {
     constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
     constexpr int NS = FORM == 1 ? 6 : 1;
     extern __shared__ double sm[];
-    double* sT = sm;                                    // [3][20][6] (stiffness) / [3][20] (mass)
-    double* sS = sm + 360;                              // [NS][ROWPLAN_VMAX]
+    double* sS = sm;                                    // [NS][ROWPLAN_VMAX]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int stageSize = ROWPLAN_ZOFF + maxchunks * N * 32;   // zero cell (+pad), then the tile
     const int outSize = maxrounds * 32 + 2;                    // task results + the warp-reduced diagonal
     double* stage = sS + NS * ROWPLAN_VMAX + warp * (stageSize + outSize);
-    for (int k = threadIdx.x; k < 360; k += blockDim.x)
-        sT[k] = FORM == 0 ? (k < 60 ? tab.T[k / 20][k % 20][0] : 0.0) : tab.T[k / 120][(k / 6) % 20][k % 6];
     double* out = stage + stageSize;
     const int DIAG = maxrounds * 32;
     const RowPlanCta cta = ctas[blockIdx.x];
@@ -178,9 +169,9 @@ k_rowplan(const RowPlanCta* __restrict__ ctas, const uint4* __restrict__ hdrs, c
             // stays warp-convergent, so the reference tables are read through the uniform datapath (LDCU + DFMA UR)
             double* st = stage + ROWPLAN_ZOFF + ch * N * 32 + lane;
             double dv;
-            if (ORDER == 1 || kind == 0) dv = unit_row<ORDER, FORM, 0>(sT, sS, u, st);
-            else if (ORDER == 2 || kind == 1) dv = unit_row<ORDER, FORM, (ORDER >= 2 ? 1 : 0)>(sT, sS, u, st);
-            else dv = unit_row<ORDER, FORM, (ORDER >= 3 ? 2 : 0)>(sT, sS, u, st);
+            if (ORDER == 1 || kind == 0) dv = unit_row<ORDER, FORM, 0>(kind, sS, u, st);
+            else if (ORDER == 2 || kind == 1) dv = unit_row<ORDER, FORM, (ORDER >= 2 ? 1 : 0)>(kind, sS, u, st);
+            else dv = unit_row<ORDER, FORM, (ORDER >= 3 ? 2 : 0)>(kind, sS, u, st);
             if (!(u & ROWPLAN_UNIT_ACTIVE)) dv = 0.0;
             dsum += dv;
         }
@@ -247,7 +238,7 @@ size_t rowplan_smem_bytes(const RowPlan* p, int form)
 {
     const int NS = form == 1 ? 6 : 1;
     const size_t stageSize = ROWPLAN_ZOFF + (size_t)p->maxchunks * p->n * 32, outSize = (size_t)p->maxrounds * 32 + 2;
-    return sizeof(double) * (360 + NS * ROWPLAN_VMAX + ROWPLAN_WARPS * (stageSize + outSize));
+    return sizeof(double) * (NS * ROWPLAN_VMAX + ROWPLAN_WARPS * (stageSize + outSize));
 }
 
 template <typename T>
@@ -366,6 +357,8 @@ int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, co
             }
         }
     }
+    // stream-ordered upload of the tables (one context drives one stream at a time, see feelgpu.h)
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rowtab, &tab, sizeof(RowTables), 0, cudaMemcpyHostToDevice, s));
     const size_t sh = rowplan_smem_bytes(p, form);
     const int grid = (int)p->ncta, threads = ROWPLAN_WARPS * 32;
     if (grid == 0) return FEELGPU_OK;
@@ -374,7 +367,7 @@ int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, co
         FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rowplan<O, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
         k_rowplan<O, F><<<grid, threads, sh, s>>>(p->d_ctas, reinterpret_cast<const uint4*>(p->d_hdrs), p->d_visits, \
                                                   reinterpret_cast<const uint4*>(p->d_blob), m->d_xyz, m->d_conn, a, \
-                                                  accumulate, p->ncomp, p->maxchunks, p->maxrounds, hp.cval[0], tab); \
+                                                  accumulate, p->ncomp, p->maxchunks, p->maxrounds, hp.cval[0]); \
     } while (0)
     switch (p->order * 2 + form) {
     case 2: RLAUNCH(1, 0); break;

@@ -248,10 +248,22 @@ bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int3
     int load[32], ntask[32];
     std::vector<int> laneTasks[32];
     for (int l = 0; l < 32; ++l) { load[l] = 0; ntask[l] = 0; }
+    // phase 3 reads result slot (task*32 + owner lane) of 16 consecutive outputs per half-warp: owners of an aligned
+    // group of 16 outputs should sit in distinct shared-memory banks (owner lane mod 16)
+    std::vector<uint16_t> groupMask((nout + 15) / 16, 0);
     for (int o : taskOrder) {
-        int best = 0;
-        for (int l = 1; l < 32; ++l)
-            if (load[l] < load[best]) best = l;
+        int minload = load[0];
+        for (int l = 1; l < 32; ++l) minload = std::min(minload, load[l]);
+        const uint16_t gm = groupMask[o >> 4];
+        int best = -1, bestFree = -1;
+        for (int l = 0; l < 32; ++l) {
+            if (load[l] > minload + 1) continue;
+            const bool freeBank = !((gm >> (l & 15)) & 1);
+            if (freeBank && (bestFree < 0 || load[l] < load[bestFree])) bestFree = l;
+            if (best < 0 || load[l] < load[best]) best = l;
+        }
+        if (bestFree >= 0) best = bestFree;
+        groupMask[o >> 4] |= (uint16_t)(1u << (best & 15));
         load[best] += (int)srcOfOut[o].size();
         laneTasks[best].push_back(o);
         ntask[best]++;
@@ -298,15 +310,42 @@ bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int3
             om[o] = (uint16_t)(ROWPLAN_OMAP_ZERO | (k << 11));
         }
     }
-    for (int l = 0; l < 32; ++l) {
-        int it = 0;
-        for (size_t t = 0; t < laneTasks[l].size(); ++t) {
-            const int o = laneTasks[l][t];
-            const auto& sv = srcOfOut[o];
-            for (size_t s2 = 0; s2 < sv.size(); ++s2, ++it)
-                sp[(size_t)l * 4 * niter4 + it] = (uint16_t)(sv[s2] | (s2 + 1 == sv.size() ? ROWPLAN_SRC_END : 0));
-            om[o] = (uint16_t)((om[o] & 0xF800u) | (uint16_t)(t * 32 + l));
+    // Phase 2 reads one source per lane and iteration; the bank of a source is its unit lane mod 16 and a half-warp is
+    // served in one pass only if its 16 lanes hit distinct banks.  The order of the sources inside an output is free
+    // (it only fixes the summation order), so pick, iteration by iteration, a source whose bank is still unused.
+    {
+        int curTask[32], remaining[32];
+        std::vector<uint16_t> pool[32];
+        for (int l = 0; l < 32; ++l) {
+            curTask[l] = 0;
+            remaining[l] = 0;
+            for (size_t t = 0; t < laneTasks[l].size(); ++t) om[laneTasks[l][t]] = (uint16_t)((om[laneTasks[l][t]] & 0xF800u) | (uint16_t)(t * 32 + l));
+            if (!laneTasks[l].empty()) { pool[l] = srcOfOut[laneTasks[l][0]]; remaining[l] = (int)pool[l].size(); }
         }
+        for (int it = 0; it < niter; ++it)
+            for (int half = 0; half < 2; ++half) {
+                uint32_t used = 0;
+                for (int l = half * 16; l < half * 16 + 16; ++l) {
+                    if (curTask[l] >= (int)laneTasks[l].size()) continue;   // stream exhausted: stays null (zero cell)
+                    int pick = 0;
+                    for (int k = 0; k < remaining[l]; ++k)
+                        if (!((used >> (pool[l][k] & 15)) & 1)) { pick = k; break; }
+                    const uint16_t sv = pool[l][pick];
+                    used |= 1u << (sv & 15);
+                    pool[l][pick] = pool[l][remaining[l] - 1];
+                    --remaining[l];
+                    uint16_t ent = sv;
+                    if (remaining[l] == 0) {
+                        ent |= ROWPLAN_SRC_END;
+                        ++curTask[l];
+                        if (curTask[l] < (int)laneTasks[l].size()) {
+                            pool[l] = srcOfOut[laneTasks[l][curTask[l]]];
+                            remaining[l] = (int)pool[l].size();
+                        }
+                    }
+                    sp[(size_t)l * 4 * niter4 + it] = ent;
+                }
+            }
     }
     if (diagOut >= 0) om[diagOut] = (uint16_t)((om[diagOut] & 0xF800u) | ROWPLAN_OMAP_DIAG);
     w += 4 * qSrc;

@@ -196,6 +196,13 @@ class BilinearForm:
     def values(self):
         return self.eng.to_host(self.d_values, max(self.nnz, 1))[:self.nnz]
 
+    def plan_stats(self):
+        st = np.zeros(10, dtype=np.int64)
+        check(self.eng.lib.feelgpu_pattern_plan_stats(self.pat, ptr(st, c_i64p)), self.eng.ctx)
+        keys = ["has_plan", "ctas", "bundles", "units", "contributions", "sources_padded", "visits", "bytes",
+                "max_chunks", "max_rounds"]
+        return dict(zip(keys, (int(x) for x in st)))
+
     def scipy(self):
         import scipy.sparse as sps
         return sps.csr_matrix((self.values(), self.ja, self.ia), shape=(self.Xh.nDof(), self.Xh.nDof()))

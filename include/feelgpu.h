@@ -163,6 +163,10 @@ int feelgpu_launch_count(feelgpu_context_t ctx, int64_t* count);
  * ms[0] zero-fill, ms[1] main assembly kernel, ms[2] other                                                       */
 int feelgpu_last_timing(feelgpu_context_t ctx, double ms[3]);
 int feelgpu_set_timing(feelgpu_context_t ctx, int enable);
+/* statistics of the owner-computes plan of a pattern: stats[0] = 1 if a plan exists, [1] CTAs, [2] bundles, [3] units
+ * (row, element) pairs, [4] contributions summed in phase 2, [5] source entries incl. padding, [6] element visits
+ * (geometry evaluations), [7] plan bytes on the device, [8] max chunks, [9] max rounds                                */
+int feelgpu_pattern_plan_stats(feelgpu_pattern_t pattern, int64_t stats[10]);
 
 #ifdef __cplusplus
 }
