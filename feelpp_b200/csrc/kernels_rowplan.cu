@@ -28,19 +28,16 @@ __constant__ RowTables c_rowtab;
 
 // one unit's row of the re-labelled local matrix -> stage[entry][lane]; returns the canonical (diagonal) entry.
 template <int ORDER, int FORM, int KIND>
-__device__ __forceinline__ double unit_row(int kind, const double* __restrict__ sS, uint32_t u, double* st)
+__device__ __forceinline__ void unit_row(int kind, const double* __restrict__ sS, uint32_t u, double* st)
 {
     constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
-    constexpr int CANON = KIND == 0 ? 0 : (KIND == 1 ? 4 + 2 * (ORDER - 1) : 4 + 6 * (ORDER - 1) + 3);
     const int vis = u & 0x3FF;
-    double dv = 0.0;
     if (FORM == 0) {
         const double cj = sS[vis];
 #pragma unroll
         for (int j = 0; j < N; ++j) {
             const double v = cj * c_rowtab.T[kind][j][0];
             st[j * 32] = v;
-            if (j == CANON) dv = v;
         }
     } else {
         const double s01 = sS[((u >> 10) & 7) * ROWPLAN_VMAX + vis];
@@ -61,17 +58,15 @@ __device__ __forceinline__ double unit_row(int kind, const double* __restrict__ 
             v = fma(s13, c_rowtab.T[kind][j][4], v);
             v = fma(s23, c_rowtab.T[kind][j][5], v);
             st[j * 32] = v;
-            if (j == CANON) dv = v;
         }
     }
-    return dv;
 }
 
-template <int ORDER, int FORM>   // FORM 0: mass, 1: stiffness
+template <int ORDER, int FORM, int NCOMP>   // FORM 0: mass, 1: stiffness; NCOMP components (block = value * Id)
 __global__ void __launch_bounds__(ROWPLAN_WARPS * 32, 3)
 k_rowplan(const RowPlanCta* __restrict__ ctas, const uint4* __restrict__ hdrs, const int32_t* __restrict__ visits,
           const uint4* __restrict__ blob, const double* __restrict__ xyz, const int4* __restrict__ conn,
-          double* __restrict__ a, int accumulate, int ncomp, int maxchunks, int maxrounds, double cval)
+          double* __restrict__ a, int accumulate, int maxchunks, int maxrounds, double cval)
 {
     constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
     constexpr int NS = FORM == 1 ? 6 : 1;
@@ -79,13 +74,13 @@ k_rowplan(const RowPlanCta* __restrict__ ctas, const uint4* __restrict__ hdrs, c
     double* sS = sm;                                    // [NS][ROWPLAN_VMAX]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int stageSize = ROWPLAN_ZOFF + maxchunks * N * 32;   // zero cell (+pad), then the tile
-    const int outSize = maxrounds * 32 + 2;                    // task results + the warp-reduced diagonal
+    const int outSize = 32 + maxrounds * 32 + 64;              // {zero, diagonal}, task results, row table
     double* stage = sS + NS * ROWPLAN_VMAX + warp * (stageSize + outSize);
     double* out = stage + stageSize;
-    const int DIAG = maxrounds * 32;
     const RowPlanCta cta = ctas[blockIdx.x];
     uint32_t b = warp;
     uint4 hq = __ldg(&hdrs[cta.bundle_off + b]);        // header array is padded: always in bounds
+    uint4 hnext = __ldg(&hdrs[cta.bundle_off + b + ROWPLAN_WARPS]);
 
     // ---- phase A: geometry of every element touched by this CTA's rows, once ----
     for (int v = threadIdx.x; v < (int)cta.nvisit; v += blockDim.x) {
@@ -145,91 +140,97 @@ k_rowplan(const RowPlanCta* __restrict__ ctas, const uint4* __restrict__ hdrs, c
     if (lane == 0) stage[0] = 0.0;
     __syncthreads();
 
+    uint4* rowsm = reinterpret_cast<uint4*>(out + 32 + maxrounds * 32);   // the bundle's row table {base, len, offset}
+    const uint32_t stg = (uint32_t)__cvta_generic_to_shared(stage);
+    const uint32_t outs = (uint32_t)__cvta_generic_to_shared(out);
+    if (lane == 0) out[0] = 0.0;
+
     while (b < cta.nbundle) {
-        const uint4 hnext = __ldg(&hdrs[cta.bundle_off + b + ROWPLAN_WARPS]);
+        // software pipeline: the header two bundles ahead is requested now
+        const uint4 hnext2 = __ldg(&hdrs[min(cta.bundle_off + b + 2 * ROWPLAN_WARPS, cta.bundle_off + cta.nbundle)]);
         const int niter4 = hq.y & 0xFFFF, nout = hq.y >> 16;
         const int nrows = hq.z & 0xFF, nchunks = (hq.z >> 8) & 0xFF, kind = (hq.z >> 16) & 0xFF, flags = hq.z >> 24;
         const uint4* B = blob + hq.x;
         // ---- all loads of the bundle are issued up front ----
         const uint32_t u0 = __ldg(reinterpret_cast<const uint32_t*>(B) + lane);
-        const uint4 ri = __ldg(B + nchunks * 8 + min(lane, nrows - 1));
         const uint2* sp = reinterpret_cast<const uint2*>(B + nchunks * 8 + nrows) + (size_t)lane * niter4;
         const uint16_t* om = reinterpret_cast<const uint16_t*>(B + nchunks * 8 + nrows + niter4 * 16);
         uint2 cur = niter4 ? __ldg(sp) : make_uint2(0u, 0u);
-        uint32_t om0 = lane < nout ? __ldg(om + lane) : ROWPLAN_OMAP_ZERO;
-        uint32_t om1 = lane + 32 < nout ? __ldg(om + lane + 32) : ROWPLAN_OMAP_ZERO;
-        uint32_t om2 = lane + 64 < nout ? __ldg(om + lane + 64) : ROWPLAN_OMAP_ZERO;
-        uint32_t om3 = lane + 96 < nout ? __ldg(om + lane + 96) : ROWPLAN_OMAP_ZERO;
+        uint32_t omr[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) omr[r] = (lane + 32 * r < nout) ? (uint32_t)__ldg(om + lane + 32 * r) : 0u;
+        if (lane < nrows) rowsm[lane] = __ldg(B + nchunks * 8 + lane);
 
         // ---- phase 1: lane = unit; its row of the (re-labelled) local matrix goes to stage[entry][lane] ----
-        double dsum = 0.0;
+        // every lane computes (inactive lanes read visit 0 and write a tile column nobody references)
         for (int ch = 0; ch < nchunks; ++ch) {
             const uint32_t u = ch == 0 ? u0 : __ldg(reinterpret_cast<const uint32_t*>(B) + ch * 32 + lane);
-            // every lane computes (inactive lanes read visit 0 and write a tile column nobody references): the code
-            // stays warp-convergent, so the reference tables are read through the uniform datapath (LDCU + DFMA UR)
             double* st = stage + ROWPLAN_ZOFF + ch * N * 32 + lane;
-            double dv;
-            if (ORDER == 1 || kind == 0) dv = unit_row<ORDER, FORM, 0>(kind, sS, u, st);
-            else if (ORDER == 2 || kind == 1) dv = unit_row<ORDER, FORM, (ORDER >= 2 ? 1 : 0)>(kind, sS, u, st);
-            else dv = unit_row<ORDER, FORM, (ORDER >= 3 ? 2 : 0)>(kind, sS, u, st);
-            if (!(u & ROWPLAN_UNIT_ACTIVE)) dv = 0.0;
-            dsum += dv;
-        }
-        if (flags & ROWPLAN_FLAG_WARPDIAG) {
+            if (ORDER == 1 || kind == 0) unit_row<ORDER, FORM, 0>(kind, sS, u, st);
+            else if (ORDER == 2 || kind == 1) unit_row<ORDER, FORM, (ORDER >= 2 ? 1 : 0)>(kind, sS, u, st);
+            else unit_row<ORDER, FORM, (ORDER >= 3 ? 2 : 0)>(kind, sS, u, st);
+            if (flags & ROWPLAN_FLAG_WARPDIAG) {
+                // single row: its diagonal is the warp sum of the canonical entries of all units
+                const int canon = kind == 0 ? 0 : (kind == 1 ? 4 + 2 * (ORDER - 1) : 4 + 6 * (ORDER - 1) + 3);
+                double dv = (u & ROWPLAN_UNIT_ACTIVE) ? st[canon * 32] : 0.0;
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) dsum += __shfl_xor_sync(0xffffffffu, dsum, off);
-            if (lane == 0) out[DIAG] = dsum;
+                for (int off = 16; off > 0; off >>= 1) dv += __shfl_xor_sync(0xffffffffu, dv, off);
+                if (lane == 0) out[1] = ch == 0 ? dv : out[1] + dv;
+            }
         }
         __syncwarp();
         // ---- phase 2: lane = a balanced list of output nonzeros, summed from the staging tile in plan order ----
         {
             double acc = 0.0;
-            double* op = out + lane;
+            uint32_t op = outs + (32 + lane) * 8;
             for (int it = 0; it < niter4; ++it) {
                 const uint2 nxt = (it + 1 < niter4) ? __ldg(sp + it + 1) : make_uint2(0u, 0u);
                 const uint32_t e[4] = {cur.x & 0xFFFFu, cur.x >> 16, cur.y & 0xFFFFu, cur.y >> 16};
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    acc += stage[e[k] & 0x7FFFu];
-                    if (e[k] & ROWPLAN_SRC_END) {
-                        *op = acc;
-                        op += 32;
-                        acc = 0.0;
-                    }
+                    double v;
+                    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(stg + ((e[k] & 0x7FFFu) << 3)));
+                    acc += v;
+                    // predicated (branch-free) end-of-output: store the sum, advance the result slot, restart
+                    const uint32_t end = e[k] >> 15;
+                    asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p st.shared.f64 [%1], %2; }" ::"r"(end), "r"(op), "d"(acc)
+                                 : "memory");
+                    op += end << 8;
+                    acc = end ? 0.0 : acc;
                 }
                 cur = nxt;
             }
         }
         __syncwarp();
         // ---- phase 3: coalesced store of the rows' value segments ----
-        for (int ob = 0, r = 0; ob < nout; ob += 32, ++r) {
-            const int o = ob + lane;
-            uint32_t m = r == 0 ? om0 : r == 1 ? om1 : r == 2 ? om2 : r == 3 ? om3
-                                                       : (o < nout ? (uint32_t)__ldg(om + o) : ROWPLAN_OMAP_ZERO);
-            const int k = m >> 11;
-            const uint32_t blo = __shfl_sync(0xffffffffu, ri.x, k), bhi = __shfl_sync(0xffffffffu, ri.y, k);
-            const int len = (int)__shfl_sync(0xffffffffu, ri.z, k), roff = (int)__shfl_sync(0xffffffffu, ri.w, k);
-            if (o < nout) {
-                const uint32_t slot = m & 0x3FFu;
-                const double v = (m & ROWPLAN_OMAP_DIAG) ? out[DIAG] : (slot == ROWPLAN_OMAP_ZERO ? 0.0 : out[slot]);
-                const int64_t base = (int64_t)(((uint64_t)bhi << 32) | blo);
-                const int p = o - roff;
-                if (ncomp == 1) {
-                    if (accumulate) a[base + p] += v;
-                    else a[base + p] = v;
-                } else {
-                    // product space, block = v * Id: component row c1 starts at base + c1*len*ncomp
-                    for (int c1 = 0; c1 < ncomp; ++c1)
-                        for (int c2 = 0; c2 < ncomp; ++c2) {
-                            double* dst = a + base + (int64_t)c1 * len * ncomp + (int64_t)p * ncomp + c2;
-                            if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
-                            else if (!accumulate) *dst = 0.0;
-                        }
-                }
+        auto emit = [&](int o, uint32_t m) {
+            const uint4 r = rowsm[m >> 11];
+            const double v = out[m & 0x3FFu];
+            const int64_t base = (int64_t)(((uint64_t)r.y << 32) | r.x);
+            const int p = o - (int)r.w;
+            if (NCOMP == 1) {
+                if (accumulate) a[base + p] += v;
+                else a[base + p] = v;
+            } else {
+                // product space, block = v * Id: component row c1 starts at base + c1*len*NCOMP
+                const int len = (int)r.z;
+#pragma unroll
+                for (int c1 = 0; c1 < NCOMP; ++c1)
+#pragma unroll
+                    for (int c2 = 0; c2 < NCOMP; ++c2) {
+                        double* dst = a + base + (int64_t)c1 * len * NCOMP + (int64_t)p * NCOMP + c2;
+                        if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
+                        else if (!accumulate) *dst = 0.0;
+                    }
             }
-        }
+        };
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+            if (lane + 32 * r < nout) emit(lane + 32 * r, omr[r]);
+        for (int o = lane + 128; o < nout; o += 32) emit(o, (uint32_t)__ldg(om + o));
         __syncwarp();
         hq = hnext;
+        hnext = hnext2;
         b += ROWPLAN_WARPS;
     }
 }
@@ -237,7 +238,7 @@ k_rowplan(const RowPlanCta* __restrict__ ctas, const uint4* __restrict__ hdrs, c
 size_t rowplan_smem_bytes(const RowPlan* p, int form)
 {
     const int NS = form == 1 ? 6 : 1;
-    const size_t stageSize = ROWPLAN_ZOFF + (size_t)p->maxchunks * p->n * 32, outSize = (size_t)p->maxrounds * 32 + 2;
+    const size_t stageSize = ROWPLAN_ZOFF + (size_t)p->maxchunks * p->n * 32, outSize = 32 + (size_t)p->maxrounds * 32 + 64;
     return sizeof(double) * (NS * ROWPLAN_VMAX + ROWPLAN_WARPS * (stageSize + outSize));
 }
 
@@ -362,12 +363,17 @@ int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, co
     const size_t sh = rowplan_smem_bytes(p, form);
     const int grid = (int)p->ncta, threads = ROWPLAN_WARPS * 32;
     if (grid == 0) return FEELGPU_OK;
-#define RLAUNCH(O, F)                                                                                               \
+#define RLAUNCH1(O, F, C)                                                                                          \
     do {                                                                                                            \
-        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rowplan<O, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-        k_rowplan<O, F><<<grid, threads, sh, s>>>(p->d_ctas, reinterpret_cast<const uint4*>(p->d_hdrs), p->d_visits, \
-                                                  reinterpret_cast<const uint4*>(p->d_blob), m->d_xyz, m->d_conn, a, \
-                                                  accumulate, p->ncomp, p->maxchunks, p->maxrounds, hp.cval[0]); \
+        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rowplan<O, F, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+        k_rowplan<O, F, C><<<grid, threads, sh, s>>>(p->d_ctas, reinterpret_cast<const uint4*>(p->d_hdrs), p->d_visits, \
+                                                     reinterpret_cast<const uint4*>(p->d_blob), m->d_xyz, m->d_conn, a, \
+                                                     accumulate, p->maxchunks, p->maxrounds, hp.cval[0]);          \
+    } while (0)
+#define RLAUNCH(O, F)                         \
+    do {                                      \
+        if (p->ncomp == 1) RLAUNCH1(O, F, 1); \
+        else RLAUNCH1(O, F, 3);               \
     } while (0)
     switch (p->order * 2 + form) {
     case 2: RLAUNCH(1, 0); break;
@@ -379,6 +385,7 @@ int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, co
     default: ctx->last_error = "rowplan: unsupported order"; return FEELGPU_ERR_UNSUPPORTED;
     }
 #undef RLAUNCH
+#undef RLAUNCH1
     ctx->launches++;
     FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
     return FEELGPU_OK;

@@ -49,14 +49,15 @@ struct RowPlanCta {              // 16 bytes
 // source entry: staging slot + ROWPLAN_ZOFF (0 = the zero cell) | end-of-output flag (bit 15)
 #define ROWPLAN_SRC_END 0x8000u
 #define ROWPLAN_ZOFF 32
-// outmap entry: bits 0-9 result slot (task*32+lane; 1023 = structural zero) | bit 10 warp-diagonal | bits 11-15 row slot
-#define ROWPLAN_OMAP_ZERO 1023u
-#define ROWPLAN_OMAP_DIAG 0x400u
+// outmap entry: bits 0-9 index into the warp's result buffer (0 = zero cell: structural zero, 1 = warp-reduced diagonal,
+// 32 + task*32 + lane = task result) | bits 11-15 row slot
+#define ROWPLAN_OMAP_ZERO 0u
+#define ROWPLAN_OMAP_DIAG 1u
 
 #define ROWPLAN_VMAX 640         // visits per CTA (< 1024)
 #define ROWPLAN_WARPS 8          // warps per CTA
 #define ROWPLAN_MAXCHUNKS 4      // a row may have up to 128 elements around its node
-#define ROWPLAN_MAXROUNDS 23     // results per lane per bundle (23*32+31 < 1023)
+#define ROWPLAN_MAXROUNDS 23     // results per lane per bundle (32 + 23*32 + 31 < 1024)
 #define ROWPLAN_BIGROW 12        // rows with more units are alone in their bundle (warp-reduced diagonal)
 
 struct RowPlanHost {

@@ -319,7 +319,7 @@ bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int3
         for (int l = 0; l < 32; ++l) {
             curTask[l] = 0;
             remaining[l] = 0;
-            for (size_t t = 0; t < laneTasks[l].size(); ++t) om[laneTasks[l][t]] = (uint16_t)((om[laneTasks[l][t]] & 0xF800u) | (uint16_t)(t * 32 + l));
+            for (size_t t = 0; t < laneTasks[l].size(); ++t) om[laneTasks[l][t]] = (uint16_t)((om[laneTasks[l][t]] & 0xF800u) | (uint16_t)(32 + t * 32 + l));
             if (!laneTasks[l].empty()) { pool[l] = srcOfOut[laneTasks[l][0]]; remaining[l] = (int)pool[l].size(); }
         }
         for (int it = 0; it < niter; ++it)
@@ -347,7 +347,7 @@ bool make_bundle(const Builder& B, const std::vector<uint16_t>& uvis, const int3
                 }
             }
     }
-    if (diagOut >= 0) om[diagOut] = (uint16_t)((om[diagOut] & 0xF800u) | ROWPLAN_OMAP_DIAG);
+    if (diagOut >= 0) om[diagOut] = (uint16_t)((om[diagOut] & 0xF800u) | ROWPLAN_OMAP_DIAG);   // result slot 1
     w += 4 * qSrc;
     std::memcpy(w, om.data(), sizeof(uint16_t) * om.size());
     L.hdrs.push_back(h);
