@@ -68,6 +68,7 @@ GPU_SYMBOLS = {
     "feelgpu_memcpy_d2h": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64],
     "feelgpu_host_alloc_pinned": [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)],
     "feelgpu_host_free_pinned": [C.c_void_p, C.c_void_p],
+    "feelgpu_scatter_add": [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "feelgpu_launch_count": [C.c_void_p, c_i64p],
     "feelgpu_last_timing": [C.c_void_p, c_dblp],
     "feelgpu_set_timing": [C.c_void_p, C.c_int],
@@ -125,6 +126,8 @@ def host():
         lib.feelhost_tabulate.argtypes = [C.c_int, C.c_int, c_dblp, c_dblp, c_dblp]
         lib.feelhost_parse_expr.argtypes = [C.c_char_p, C.c_int, c_i32p, c_dblp, C.POINTER(C.c_int),
                                             C.POINTER(C.c_int)]
+        lib.feelhost_csr_select_remap_sort.argtypes = [C.c_int64, C.c_int64, c_i64p, c_i64p, c_i64p, c_i64p, c_i64p,
+                                                       c_i64p, c_i64p, c_i64p]
         _host = lib
     return _host
 

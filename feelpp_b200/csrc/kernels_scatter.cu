@@ -304,7 +304,32 @@ k_form1(const FormParams* __restrict__ P, DevTables T, int64_t nElt, const doubl
     }
 }
 
+__global__ void k_scatter_add(int64_t n, const int64_t* __restrict__ slots, const double* __restrict__ vals,
+                              double* __restrict__ a)
+{
+    // every slot appears at most once per neighbour message, but messages of different neighbours may overlap
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x)
+        atomicAdd(&a[slots[k]], vals[k]);
+}
+
 } // namespace
+
+extern "C" int feelgpu_scatter_add(feelgpu_context_t ctx, int64_t n, const int64_t* slots, const double* vals, double* a,
+                                   void* stream)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (n < 0 || (n > 0 && (!slots || !vals || !a))) {
+        ctx->last_error = "scatter_add: bad argument";
+        return FEELGPU_ERR_ARG;
+    }
+    if (n == 0) return FEELGPU_OK;
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+    k_scatter_add<<<grid, 256, 0, s>>>(n, slots, vals, a);
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    return FEELGPU_OK;
+}
 
 int feelgpu_launch_build_pos(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s)
 {

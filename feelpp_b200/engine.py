@@ -51,8 +51,11 @@ class Engine:
         key = builtins_id(Xh)
         if key not in self._spaces:
             h = C.c_void_p()
+            p2c = getattr(Xh, "p2c", None)     # distributed spaces: process -> global-cluster ids, owned dofs first
+            nown = getattr(Xh, "nDofOwned", Xh.nDof())
             check(self.lib.feelgpu_space_create(self.ctx, self.mesh(Xh.mesh), Xh.order, Xh.ncomp,
-                                                ptr(Xh.l2g, c_i32p), Xh.nDof(), Xh.nDof(), None, C.byref(h)), self.ctx)
+                                                ptr(Xh.l2g, c_i32p), Xh.nDof(), nown,
+                                                ptr(p2c, c_i64p) if p2c is not None else None, C.byref(h)), self.ctx)
             self._spaces[key] = (h, Xh)
         return self._spaces[key][0]
 
@@ -146,9 +149,12 @@ class BilinearForm:
         check(engine.lib.feelgpu_pattern_create(engine.ctx, sp, sp, test.nDof(), ptr(self.ia, c_i64p),
                                                 ptr(self.ja, c_i64p), pattern_flags, C.byref(self.pat)), engine.ctx)
         self.nnz = int(self.ia[-1])
-        self.d_values = engine.malloc(8 * max(self.nnz, 1))
+        self.d_values = self._alloc_values()
         self._zeroed = False
         self.assign(None)
+
+    def _alloc_values(self):
+        return self.eng.malloc(8 * max(self.nnz, 1))
 
     def _desc(self, integ, keep):
         cl = vf.classify_form2(integ.expr, self.Xh.order)

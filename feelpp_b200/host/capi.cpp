@@ -122,3 +122,39 @@ int feelhost_parse_expr(const char* s, int cap, int32_t* ops, double* consts, in
 }
 
 } // extern "C"
+
+// ---- distributed setup helper: build the local CSR rows of one rank -------------------------------------------
+// Row k of the result is row rid[k] of graph A (k < nFromA: owned rows, complete pattern) or of graph B (ghost rows,
+// pattern of the local elements only); columns are mapped through colmap (process-local -> global-cluster ids,
+// feelalg/datamap.hpp:467) and sorted ascending as GraphCSR::close does (feelalg/graphcsr.cpp:994-1019).
+#include <algorithm>
+#include <thread>
+#include <vector>
+extern "C" int feelhost_csr_select_remap_sort(int64_t nNew, int64_t nFromA, const int64_t* rid, const int64_t* iaA,
+                                               const int64_t* jaA, const int64_t* iaB, const int64_t* jaB,
+                                               const int64_t* colmap, int64_t* iaOut, int64_t* jaOut /*may be NULL: count only*/)
+{
+    iaOut[0] = 0;
+    for (int64_t k = 0; k < nNew; ++k) {
+        const int64_t* ia = k < nFromA ? iaA : iaB;
+        iaOut[k + 1] = iaOut[k] + (ia[rid[k] + 1] - ia[rid[k]]);
+    }
+    if (!jaOut) return 0;
+    int nth = (int)std::max(1u, std::thread::hardware_concurrency());
+    nth = std::min(nth, 32);
+    auto work = [&](int t) {
+        for (int64_t k = nNew * t / nth; k < nNew * (t + 1) / nth; ++k) {
+            const int64_t* ia = k < nFromA ? iaA : iaB;
+            const int64_t* ja = k < nFromA ? jaA : jaB;
+            int64_t* out = jaOut + iaOut[k];
+            const int64_t b = ia[rid[k]], e = ia[rid[k] + 1];
+            for (int64_t q = b; q < e; ++q) out[q - b] = colmap[ja[q]];
+            std::sort(out, out + (e - b));
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nth; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto& x : th) x.join();
+    return 0;
+}

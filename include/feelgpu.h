@@ -148,6 +148,14 @@ int feelgpu_form2_assemble_host(feelgpu_pattern_t pattern, const feelgpu_form2_d
 int feelgpu_form1_assemble_host(feelgpu_space_t space, const feelgpu_form1_desc* desc, int accumulate,
                                 double* b_host);
 
+/* ---- close(): owner-side accumulation of ghost-row contributions -------------------------------------------------
+ * The reference ships stashed off-rank rows inside MatAssemblyBegin/End (feelalg/matrixpetsc.cpp:750-752).  Here the
+ * values of a rank's ghost rows are the tail of its value array (rows nDofOwned..nDofLocalWithGhost-1), sent as they
+ * are (values only, NCCL send/recv on the caller's communicator); the owner adds what it received with
+ *     a[slots[k]] += vals[k],  k < n        (slots: DEVICE int64, built once from the graph exchange)              */
+int feelgpu_scatter_add(feelgpu_context_t ctx, int64_t n, const int64_t* slots, const double* vals, double* a,
+                        void* stream);
+
 /* ---- device memory helpers for callers without a CUDA runtime of their own ---------------------------------- */
 int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr);
 int feelgpu_free(feelgpu_context_t ctx, void* dptr);
