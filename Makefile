@@ -8,7 +8,7 @@ LIB := feelpp_b200/lib
 
 all: $(LIB)/libfeelgpu.so $(LIB)/libfeelhost.so oracle
 
-$(LIB)/%.o: $(CSRC)/%.cu $(CSRC)/feelgpu_internal.h $(CSRC)/rowplan.h include/feelgpu.h
+$(LIB)/%.o: $(CSRC)/%.cu $(CSRC)/feelgpu_internal.h $(CSRC)/rowplan.h $(CSRC)/eplan.h include/feelgpu.h
 	@mkdir -p $(LIB)
 	$(NVCC) $(NVCCFLAGS) -c $< -o $@ 2> $(LIB)/$*.ptxas.log || (cat $(LIB)/$*.ptxas.log; false)
 
@@ -16,7 +16,11 @@ $(LIB)/rowplan_build.o: $(CSRC)/rowplan_build.cpp $(CSRC)/rowplan.h
 	@mkdir -p $(LIB)
 	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread -c $< -o $@
 
-$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o
+$(LIB)/eplan_build.o: $(CSRC)/eplan_build.cpp $(CSRC)/eplan.h
+	@mkdir -p $(LIB)
+	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread -c $< -o $@
+
+$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart
 
 HOSTSRC := $(wildcard feelpp_b200/host/*.cpp)

@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--m", type=int, default=110, help="cells per edge of the unit cube (110 -> 7 986 000 tets)")
     ap.add_argument("--order", type=int, default=2)
-    ap.add_argument("--algo", default="auto", choices=["auto", "scatter", "rowplan"])
+    ap.add_argument("--algo", default="auto", choices=["auto", "scatter", "rowplan", "eplan"])
     ap.add_argument("--shuffle", action="store_true", help="Fisher-Yates shuffled element order")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -166,13 +166,14 @@ def gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    algo = {"auto": fpp.ALGO_AUTO, "scatter": fpp.ALGO_SCATTER, "rowplan": fpp.ALGO_ROWPLAN}[args.algo]
+    algo = {"auto": fpp.ALGO_AUTO, "scatter": fpp.ALGO_SCATTER, "rowplan": fpp.ALGO_ROWPLAN, "eplan": fpp.ALGO_EPLAN}[args.algo]
     eng = fpp.Engine(local)
     if world == 1:
         mesh, Xh, ia, ja, info = workload(args)
         nElt, nnz = mesh.numElements(), int(ia[-1])
         t0 = time.time()
-        a = fpp.form2(_test=Xh, _trial=Xh, engine=eng, algorithm=algo)
+        a = fpp.form2(_test=Xh, _trial=Xh, engine=eng, algorithm=algo,
+                      pattern_flags={"rowplan": 3, "scatter": 1}.get(args.algo, 0))
         info["pattern_create_s"] = round(time.time() - t0, 2)
         nElt_total, nnz_total, gmesh = nElt, nnz, mesh
     else:

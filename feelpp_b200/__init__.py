@@ -7,5 +7,6 @@ from .hostmirror import (Mesh, unitCube, elements, FunctionSpace, Pch, Pchv, im,
                          nLocalDof, GinacProgram)
 from .vf import (Element, cst, vec, idv, expr, id, idt, grad, gradt, trans, sym, trace, Id, inner, integrate,
                  classify_form1, classify_form2)
-from .engine import (Engine, form1, form2, ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, PATTERN_SLOTMAP, PATTERN_ROWPLAN)
+from .engine import (Engine, form1, form2, ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN,
+                     PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN)
 from ._capi import FeelGpuError

@@ -44,6 +44,7 @@ struct feelgpu_space_s {
 };
 
 struct RowPlan;  // kernels_rowplan.cu
+struct EPlan;    // kernels_eplan.cu
 
 struct feelgpu_pattern_s {
     feelgpu_context_t ctx;
@@ -56,6 +57,8 @@ struct feelgpu_pattern_s {
     uint16_t* d_pos = nullptr;   // [nElt][n][n]
     RowPlan* plan = nullptr;
     std::string plan_note;       // why no owner-computes plan exists (if none)
+    EPlan* eplan = nullptr;
+    std::string eplan_note;
 };
 
 // parameter block copied to the device per assemble call
@@ -90,3 +93,10 @@ void feelgpu_rowplan_destroy(feelgpu_pattern_t pat);
 int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
                                  int accumulate, double* a, cudaStream_t s);
 bool feelgpu_rowplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
+// ---- kernels_eplan.cu ----
+int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia);
+void feelgpu_eplan_destroy(feelgpu_pattern_t pat);
+int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
+                               int accumulate, double* a, cudaStream_t s);
+bool feelgpu_eplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
+int feelgpu_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10]);

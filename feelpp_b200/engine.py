@@ -11,8 +11,8 @@ from . import hostmirror as hm
 from . import vf
 from ._capi import Coeff, Form1Desc, Form2Desc, Tables, c_dblp, c_i32p, c_i64p, check, ptr
 
-ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN = 0, 1, 2
-PATTERN_SLOTMAP, PATTERN_ROWPLAN = 1, 2
+ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN = 0, 1, 2, 3
+PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN = 1, 2, 4
 
 
 class Engine:
@@ -207,7 +207,12 @@ class BilinearForm:
         check(self.eng.lib.feelgpu_pattern_plan_stats(self.pat, ptr(st, c_i64p)), self.eng.ctx)
         keys = ["has_plan", "ctas", "bundles", "units", "contributions", "sources_padded", "visits", "bytes",
                 "max_chunks", "max_rounds"]
-        return dict(zip(keys, (int(x) for x in st)))
+        out = dict(zip(keys, (int(x) for x in st)))
+        check(self.eng.lib.feelgpu_pattern_eplan_stats(self.pat, ptr(st, c_i64p)), self.eng.ctx)
+        ekeys = ["has_plan", "ctas", "tasks", "iterations", "iterations_padded", "visits", "outputs", "bytes",
+                 "lds_wavefronts", "lds_wavefronts_ideal"]
+        out["eplan"] = dict(zip(ekeys, (int(x) for x in st)))
+        return out
 
     def scipy(self):
         import scipy.sparse as sps

@@ -99,12 +99,13 @@ typedef struct {
 
 /* assembly algorithms for form2 */
 enum {
-    FEELGPU_ALGO_AUTO = 0,        /* owner-computes plan when the pattern has one, else scatter                  */
+    FEELGPU_ALGO_AUTO = 0,        /* entity plan, else row plan, when the pattern has one and the form is covered; else scatter */
     FEELGPU_ALGO_SCATTER = 1,     /* element loop + red.global.add.f64 through the element->CSR-slot map         */
-    FEELGPU_ALGO_ROWPLAN = 2      /* owner-computes: every CSR value is produced by one thread and stored once  */
+    FEELGPU_ALGO_ROWPLAN = 2,     /* owner-computes by (row, element) units: warp tile + planned gather          */
+    FEELGPU_ALGO_EPLAN = 3        /* owner-computes by (row, simplex) tasks: register accumulation over star(sigma) */
 };
-/* flags of feelgpu_pattern_create */
-enum { FEELGPU_PATTERN_SLOTMAP = 1, FEELGPU_PATTERN_ROWPLAN = 2 };
+/* flags of feelgpu_pattern_create (0 = SLOTMAP + the best plan available for the space: EPLAN for P1/P2, ROWPLAN for P3) */
+enum { FEELGPU_PATTERN_SLOTMAP = 1, FEELGPU_PATTERN_ROWPLAN = 2, FEELGPU_PATTERN_EPLAN = 4 };
 
 /* ---- context ------------------------------------------------------------------------------------------------ */
 int feelgpu_context_create(int device, feelgpu_context_t* ctx);
@@ -175,6 +176,27 @@ int feelgpu_set_timing(feelgpu_context_t ctx, int enable);
  * (row, element) pairs, [4] contributions summed in phase 2, [5] source entries incl. padding, [6] element visits
  * (geometry evaluations), [7] plan bytes on the device, [8] max chunks, [9] max rounds                                */
 int feelgpu_pattern_plan_stats(feelgpu_pattern_t pattern, int64_t stats[10]);
+/* statistics of the entity plan: stats[0] = 1 if it exists, [1] CTAs, [2] tasks, [3] task iterations (= loads of a unit
+ * word), [4] iterations incl. padding, [5] element visits, [6] output values, [7] plan bytes on the device,
+ * [8] modelled shared-memory wavefronts of the S loads, [9] the same without bank conflicts                          */
+int feelgpu_pattern_eplan_stats(feelgpu_pattern_t pattern, int64_t stats[10]);
+
+
+/* ---- host-side view of the entity plan (no device needed): what feelgpu_pattern_create builds for P1/P2 spaces ------
+ * Used by the CPU tests to interpret the plan on the host and by tools that want to inspect it.
+ * pos = element -> CSR position map [nElt][n][n] (position of column l2g[e][j] inside row l2g[e][i], component 0).
+ * sizes: [0] CTAs, [1] vertex ids, [2] visit words, [3] chunks, [4] blob words (u32), [5] rows, [6] out-buffer slots,
+ *        [7] visit slots per CTA                                                                                       */
+int feelgpu_eplan_host_build(int order, int ncomp, int64_t nElt, const int32_t* l2g, int64_t nPts, const double* xyz,
+                             const int32_t* conn, int64_t nRows, const int64_t* ia, const uint16_t* pos,
+                             void** plan, int64_t sizes[8]);
+int feelgpu_eplan_host_copy(void* plan, void* ctas /*32 B each*/, int32_t* verts, uint32_t* visits,
+                            void* chunks /*8 B each*/, uint32_t* blob, void* rows /*16 B each*/, double stats[8]);
+const char* feelgpu_eplan_host_error(void* plan);
+int feelgpu_eplan_host_free(void* plan);
+/* coefficients the kernel applies to the per-task sums, from the caller's reference tables:
+ * coef[type][out][load] (6 x 3 x 5), mass[type][out] (6 x 3); form: 0 mass, 1 stiffness                              */
+int feelgpu_eplan_host_coefficients(int order, const feelgpu_tables* tables, int form, double* coef, double* mass);
 
 #ifdef __cplusplus
 }

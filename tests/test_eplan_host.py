@@ -1,0 +1,160 @@
+"""The entity-task plan (feelpp_b200/csrc/eplan_build.cpp) interpreted on the host, without a GPU.
+
+The plan is built through the C ABI's host view (feelgpu_eplan_host_*), then executed here exactly as the kernel does
+(phase A: S per visit; phase B: per-task sums over the unit words, coefficients, stores into the CTA's row block; phase C:
+row block -> CSR values) and compared with the CPU oracle.  This pins the plan builder and the coefficient projection;
+the GPU parity tests then only have to show that the kernel is a faithful interpreter.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import feelpp_b200 as fpp
+from feelpp_b200 import _capi as capi
+from feelpp_b200._capi import Tables, c_dblp, c_i32p, c_i64p, ptr
+from feelpp_b200 import hostmirror as hm
+from oracle import oracle as orc
+from oracle import parity
+
+NLD = {1: [1, 1], 2: [1, 2, 2, 3, 5, 4]}
+NOUT = {1: [1, 1], 2: [1, 2, 1, 3, 3, 1]}
+CTA = np.dtype([("vert_off", "<u4"), ("visit_off", "<u4"), ("chunk_off", "<u4"), ("row_off", "<u4"), ("nverts", "<u2"),
+                ("nvisit", "<u2"), ("nchunk", "<u2"), ("nrows", "<u2"), ("nout", "<u2"), ("blob_nq", "<u2"),
+                ("blob_q0", "<u4")])
+CHUNK = np.dtype([("q0", "<u4"), ("type", "u1"), ("niter", "u1"), ("pad", "<u2")])
+ROW = np.dtype([("base", "<i8"), ("off", "<u4"), ("len", "<u4")])
+
+
+def position_map(l2g, ia, ja, ncomp):
+    """pos[e][i][j]: position of column l2g[e][j] in row l2g[e][i] (component 0), as k_build_pos computes it"""
+    n = l2g.shape[1] // ncomp
+    N = int(ia.shape[0])
+    rows = np.repeat(np.arange(N - 1), np.diff(ia))
+    keys = rows * N + ja
+    r = l2g[:, :n, None].astype(np.int64)
+    c = l2g[:, None, :n].astype(np.int64)
+    idx = np.searchsorted(keys, r * N + c)
+    assert (keys[idx] == r * N + c).all()
+    return (idx - ia[r]).astype(np.uint16)
+
+
+def build_plan(mesh, Xh, ia, ja):
+    lib = capi.gpu()
+    pos = np.ascontiguousarray(position_map(Xh.l2g, ia, ja, Xh.ncomp))
+    h = C.c_void_p()
+    sizes = np.zeros(8, dtype=np.int64)
+    rc = lib.feelgpu_eplan_host_build(Xh.order, Xh.ncomp, mesh.numElements(), ptr(Xh.l2g, c_i32p), mesh.numPoints(),
+                                      ptr(mesh.xyz, c_dblp), ptr(mesh.conn, c_i32p), Xh.nDof(), ptr(ia, c_i64p),
+                                      pos.ctypes.data_as(C.c_void_p), C.byref(h), ptr(sizes, c_i64p))
+    assert rc == 0, lib.feelgpu_eplan_host_error(h)
+    P = {"ctas": np.zeros(sizes[0], dtype=CTA), "verts": np.zeros(sizes[1], dtype=np.int32),
+         "visits": np.zeros(sizes[2], dtype=np.uint32), "chunks": np.zeros(sizes[3], dtype=CHUNK),
+         "blob": np.zeros(sizes[4], dtype=np.uint32), "rows": np.zeros(sizes[5], dtype=ROW), "omax": int(sizes[6]),
+         "vs": int(sizes[7])}
+    stats = np.zeros(8)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    lib.feelgpu_eplan_host_copy(h, vp(P["ctas"]), ptr(P["verts"], c_i32p), vp(P["visits"]), vp(P["chunks"]),
+                                vp(P["blob"]), vp(P["rows"]), ptr(stats, c_dblp))
+    lib.feelgpu_eplan_host_free(h)
+    P["stats"] = dict(zip(["tasks", "iters", "iters_padded", "visits", "outputs", "wavefronts", "wavefronts_ideal"], stats))
+    return P
+
+
+def coefficients(order, quad, form):
+    xi, w = hm.im(quad)
+    phi, dphi = hm.tabulate(order, xi)
+    t = Tables()
+    keep = [np.ascontiguousarray(x) for x in (w, xi, phi, dphi)]
+    t.nq, t.n = len(w), phi.shape[0]
+    t.w, t.xi, t.phi, t.dphi = (ptr(k, c_dblp) for k in keep)
+    coef, mass = np.zeros((6, 3, 5)), np.zeros((6, 3))
+    rc = capi.gpu().feelgpu_eplan_host_coefficients(order, C.byref(t), form, ptr(coef, c_dblp), ptr(mass, c_dblp))
+    assert rc == 0
+    return coef, mass
+
+
+def visit_records(xyz):
+    """S (10 per visit: diagonals, then (0,1),(0,2),(0,3),(1,2),(1,3),(2,3)) and J, as phase A1 of the kernel"""
+    K = 0.5 * (xyz[:, 1:4, :] - xyz[:, 0:1, :]).transpose(0, 2, 1)    # K[r][b] = (x_{b+1}-x_0)_r / 2
+    det = np.linalg.det(K)
+    Binv = np.linalg.inv(K)                                          # rows b: grad xi_b
+    h = np.zeros((xyz.shape[0], 4, 3))
+    h[:, 1:4, :] = 0.5 * Binv
+    h[:, 0, :] = -h[:, 1:4, :].sum(axis=1)
+    J = np.abs(det)
+    G = np.einsum("vkc,vlc->vkl", h, h) * J[:, None, None]
+    pairs = [(0, 0), (1, 1), (2, 2), (3, 3), (0, 1), (0, 2), (0, 3), (1, 2), (1, 3), (2, 3)]
+    return np.stack([G[:, k, l] for k, l in pairs], axis=1), J
+
+
+def interpret(P, mesh, order, nnz, form, coef, mass):
+    a = np.full(nnz, np.nan)
+    vs = P["vs"]
+    written = np.zeros(nnz, dtype=np.int32)
+    for ct in P["ctas"]:
+        verts = P["verts"][ct["vert_off"]:ct["vert_off"] + ct["nverts"]]
+        vw = P["visits"][ct["visit_off"]:ct["visit_off"] + ct["nvisit"]]
+        lv = np.stack([(vw >> (8 * k)) & 255 for k in range(4)], axis=1)
+        assert lv.max(initial=0) < ct["nverts"]
+        S, J = visit_records(mesh.xyz[verts[lv]])
+        rec = np.zeros((vs, 10))
+        rec[:ct["nvisit"]] = S if form == 1 else J[:, None]
+        out = np.zeros(P["omax"])
+        hit = np.zeros(P["omax"], dtype=np.int32)
+        for ch in P["chunks"][ct["chunk_off"]:ct["chunk_off"] + ct["nchunk"]]:
+            ty, niter = int(ch["type"]), int(ch["niter"])
+            nld, nout = (NLD[order][ty] if form == 1 else 1), NOUT[order][ty]
+            w0 = int(ch["q0"]) * 4
+            words = P["blob"][w0:w0 + niter * 32].reshape(niter, 32)
+            opos = P["blob"][w0 + niter * 32:w0 + niter * 32 + nout * 16].view(np.uint16).reshape(nout, 32)
+            slot = words & 0x3FF
+            sums = np.zeros((nld, 32))
+            for t in range(niter):           # plan order
+                for k in range(nld):
+                    idx = (words[t] >> (10 + 4 * k)) & 15 if form == 1 else 0
+                    sums[k] += rec[slot[t], idx]
+            for o in range(nout):
+                v = mass[ty][o] * sums[0] if form == 0 else sum(coef[ty][o][k] * sums[k] for k in range(nld))
+                live = opos[o] != 0
+                out[opos[o][live]] = v[live]
+                np.add.at(hit, opos[o][live], 1)
+        assert hit[1:ct["nout"]].min(initial=1) == 1 and hit[1:ct["nout"]].max(initial=1) == 1, "every slot exactly once"
+        for rw in P["rows"][ct["row_off"]:ct["row_off"] + ct["nrows"]]:
+            b, o, ln = int(rw["base"]), int(rw["off"]), int(rw["len"])
+            a[b:b + ln] = out[o:o + ln]
+            written[b:b + ln] += 1
+    assert (written == 1).all(), "every CSR value is written exactly once"
+    return a
+
+
+@pytest.mark.parametrize("order", [1, 2])
+@pytest.mark.parametrize("mk", ["reg", "jit"])
+def test_plan_interpreted_on_host_matches_oracle(order, mk):
+    mesh = fpp.unitCube(4) if mk == "reg" else fpp.unitCube(5, 0.15, True)
+    Xh = fpp.Pch(mesh, order)
+    ia, ja = Xh.graph()
+    P = build_plan(mesh, Xh, ia, ja)
+    nnz = int(ia[-1])
+    for form, kind in ((1, orc.STIFFNESS), (0, orc.MASS)):
+        quad = orc.quad_order_form2(kind, order)
+        coef, mass = coefficients(order, quad, form)
+        a = interpret(P, mesh, order, nnz, form, coef, mass)
+        ref = orc.form2(kind, order, 1, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+        scale = orc.form2(kind | orc.ABS_FLAG, order, 1, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+        parity.check(a, ref, scale, ia, ja, "eplan host P%d form %d" % (order, form))
+    st = P["stats"]
+    assert st["outputs"] == nnz
+    assert st["wavefronts"] >= st["wavefronts_ideal"] > 0
+
+
+def test_plan_limits_split_ctas():
+    """a mesh larger than one CTA's limits is split; every row belongs to exactly one CTA"""
+    mesh = fpp.unitCube(8, 0.1, False)
+    Xh = fpp.Pch(mesh, 2)
+    ia, ja = Xh.graph()
+    P = build_plan(mesh, Xh, ia, ja)
+    assert len(P["ctas"]) > 1
+    assert int(P["ctas"]["nrows"].sum()) == Xh.nDof()
+    assert (P["ctas"]["nvisit"] < P["vs"]).all() and (P["ctas"]["nverts"] <= 256).all()
+    assert (P["ctas"]["nout"] <= P["omax"]).all()

@@ -15,7 +15,8 @@ from oracle import parity
 
 pytestmark = pytest.mark.gpu
 
-ALGOS = [fpp.ALGO_SCATTER, fpp.ALGO_ROWPLAN]
+PFLAGS = {fpp.ALGO_SCATTER: 1, fpp.ALGO_ROWPLAN: 3, fpp.ALGO_EPLAN: 5}
+ALGOS = [fpp.ALGO_SCATTER, fpp.ALGO_ROWPLAN, fpp.ALGO_EPLAN]
 
 
 import contextlib
@@ -27,8 +28,8 @@ def guard(algo):
     try:
         yield
     except fpp.FeelGpuError as e:
-        if algo == fpp.ALGO_ROWPLAN and e.code == 5:
-            pytest.skip("row plan does not cover this form: " + str(e))
+        if algo in (fpp.ALGO_ROWPLAN, fpp.ALGO_EPLAN) and e.code == 5:
+            pytest.skip("the plan does not cover this form: " + str(e))
         raise
 
 
@@ -57,7 +58,7 @@ def test_stiffness_and_mass(engine, meshes, order, mk, algo):
     mesh = meshes[mk]
     Xh = fpp.Pch(mesh, order)
     u = v = fpp.Element(Xh)
-    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, algorithm=algo)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, algorithm=algo, pattern_flags=PFLAGS[algo])
     with guard(algo):
         a.assign(integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v))))
     ref, scale = oracle_form2(orc.STIFFNESS, Xh, orc.quad_order_form2(orc.STIFFNESS, order))
