@@ -26,6 +26,7 @@
 #define EPLAN_VS 512             // visit slots per CTA (the last one is the all-zero record)
 #define EPLAN_VERTS 256          // unique vertices per CTA (u8 local vertex ids)
 #define EPLAN_WARPS 16
+#define EPLAN_ROWS 384            // rows per CTA: the row table reuses the 6 KB vertex cache after phase A
 #define EPLAN_OMAX 7936          // 62 KB row block per CTA: two CTAs per SM next to the 40 KB geometry cache
 #define EPLAN_MAXTYPES 6
 #define EPLAN_MAXLD 5
@@ -61,11 +62,12 @@ struct EPlanCta {                // 32 bytes
     uint32_t row_off;            // row table
     uint16_t nverts, nvisit;
     uint16_t nchunk, nrows;
-    uint16_t nout;               // out-buffer slots used (incl. slot 0 = trash)
+    uint16_t nout;               // out-buffer slots used (incl. slot 0 = trash); bit 15: zero the row block first
     uint16_t blob_nq;            // length of this CTA's chunk data in quads (16 B), for the L2 prefetch
     uint32_t blob_q0;            // its first quad
 };
 static_assert(sizeof(EPlanCta) == 32, "EPlanCta is read as two uint4");
+static_assert(EPLAN_ROWS * 16 <= 3 * EPLAN_VERTS * 8 && EPLAN_ROWS <= EPLAN_WARPS * 32, "row table reuses the vertex cache");
 struct EPlanChunk {              // 8 bytes
     uint32_t q0;                 // offset of the chunk data in quads (16 B): words u32 [niter][32], then outpos u16 [nout][32]
     uint8_t type, niter;

@@ -72,7 +72,7 @@ struct Local {                      // per-thread output, concatenated at the en
     std::vector<EPlanChunk> chunks;
     std::vector<uint32_t> blob;
     std::vector<EPlanRow> rows;
-    struct PerCta { uint32_t chunk0, nchunk, row0, nrows, q0, nq; };
+    struct PerCta { uint32_t chunk0, nchunk, row0, nrows, q0, nq, needzero; };
     std::vector<PerCta> per;
     int64_t ntasks = 0, niters = 0, niters_padded = 0;
     double wf = 0, wf_ideal = 0;
@@ -259,7 +259,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     B.ia = ia;
     B.pos = pos;
     if (nRows % ncomp) { plan.error = "entity plan: rows not a multiple of ncomp"; return false; }
-    if (omax < 512 || omax > 65535) { plan.error = "entity plan: bad out-buffer size"; return false; }
+    if (omax < 512 || omax > 32767) { plan.error = "entity plan: bad out-buffer size"; return false; }
     for (int64_t e = 0; e < nElt; ++e) {
         for (int i = 0; i < B.n; ++i)
             if (l2g[e * nd + i] >= nRows) { plan.error = "entity plan: a test dof has no CSR row"; return false; }
@@ -305,7 +305,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 addp = (uint32_t)newpts.size();
                 const uint32_t len = (uint32_t)B.row_len(node);
                 if (rows > 0 && (nv + addv > EPLAN_VS - 1 || np + addp > EPLAN_VERTS || nout + len > (uint32_t)omax ||
-                                 rows >= 65535))
+                                 rows >= EPLAN_ROWS))
                     break;
                 if (addv > EPLAN_VS - 1 || addp > EPLAN_VERTS || 1 + len > (uint32_t)omax) {
                     plan.error = "entity plan: a single row exceeds the CTA limits (elements around a node / row length)";
@@ -352,9 +352,14 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         std::vector<uint32_t> iterw;          // iteration words of the CTA's tasks
         std::vector<uint32_t> cw;             // one chunk's words
         std::vector<uint8_t> bankcnt;
+        uint8_t outcnt[EPLAN_MAXOUT * 16];
+        std::vector<uint8_t> covered;
+        std::vector<uint32_t> usage, sorted, perm, vtmp;
+        std::vector<uint32_t> cell[256];      // tasks with <= 2 elements by (bank pair of element 0, of element 1)
+        int cnt2[32];
         std::vector<uint32_t> pool, lanes;    // remaining tasks of a type; tasks of every chunk lane
         struct ChunkTmp { uint8_t type, niter; uint32_t first, count; int cost; };
-        std::vector<ChunkTmp> ctmp;
+        std::vector<ChunkTmp> ctmp, dealt;
         for (int64_t c = nCta * t / nthreads; c < nCta * (t + 1) / nthreads; ++c) {
             const CtaSeg& sg = segs[c];
             for (int ty = 0; ty < S.ntypes; ++ty) tasks[ty].clear();
@@ -408,6 +413,28 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 rowoff += len;
             }
             pc.nrows = (uint32_t)L.rows.size() - pc.row0;
+            // ---- renumber the visit slots: every half-warp wants 16 distinct bank pairs (slot mod 16) per iteration, which
+            // needs the load-weighted use of the 16 residues to be level: deal the slots, most used first, in snake order
+            {
+                const uint32_t nv = sg.nvisit;
+                usage.assign(nv, 0);
+                for (int ty = 0; ty < S.ntypes; ++ty)
+                    for (const Task& tk : tasks[ty])
+                        for (int it = 0; it < tk.niter; ++it) usage[iterw[tk.first + it] & 0x3FF] += (uint32_t)S.type[ty].nld;
+                sorted.resize(nv);
+                for (uint32_t v = 0; v < nv; ++v) sorted[v] = v;
+                std::stable_sort(sorted.begin(), sorted.end(), [&](uint32_t x, uint32_t y) { return usage[x] > usage[y]; });
+                perm.resize(nv);
+                const uint32_t full = nv / 16 * 16;
+                for (uint32_t i2 = 0; i2 < nv; ++i2) {
+                    const uint32_t g = i2 / 16, j = i2 % 16;
+                    perm[sorted[i2]] = (i2 < full && (g & 1)) ? g * 16 + 15 - j : i2;
+                }
+                for (uint32_t& w : iterw) w = (w & ~0x3FFu) | perm[w & 0x3FF];
+                uint32_t* vw = plan.visits.data() + sg.visit_off;      // this CTA's segment: no other thread touches it
+                vtmp.assign(vw, vw + nv);
+                for (uint32_t v = 0; v < nv; ++v) vw[perm[v]] = vtmp[v];
+            }
             // ---- chunks: 32 tasks of one type, longest first ----
             // All S loads of one iteration hit the bank pair (visit slot mod 16); a half-warp is served in one pass only
             // if its 16 lanes hit distinct bank pairs.  Which tasks share a half-warp and the order in which a task walks
@@ -418,26 +445,34 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             for (int ty = 0; ty < S.ntypes; ++ty) {
                 std::vector<Task>& tv = tasks[ty];
                 std::stable_sort(tv.begin(), tv.end(), [](const Task& a, const Task& b) { return a.niter > b.niter; });
-                pool.resize(tv.size());
-                for (size_t k = 0; k < tv.size(); ++k) pool[k] = (uint32_t)k;
+                const int nto = S.type[ty].nout;
+                L.ntasks += (int64_t)tv.size();
+                size_t nlong = 0;
+                while (nlong < tv.size() && tv[nlong].niter > 2) ++nlong;
+                // ---- tasks with 3 or more elements: window search ----
+                pool.resize(nlong);
+                for (size_t k = 0; k < nlong; ++k) pool[k] = (uint32_t)k;
                 size_t head = 0;
                 while (head < pool.size()) {
                     ChunkTmp ch;
                     ch.type = (uint8_t)ty;
-                    {   // the window below displaces tasks by up to 136 places: bring the longest of them to the front
+                    {   // the window below displaces tasks by up to 40 places: bring the longest of them to the front
                         size_t mx = head;
-                        for (size_t c = head + 1; c < std::min(pool.size(), head + 160); ++c)
+                        for (size_t c = head + 1; c < std::min(pool.size(), head + 128); ++c)
                             if (tv[pool[c]].niter > tv[pool[mx]].niter) mx = c;
                         std::swap(pool[head], pool[mx]);
                     }
                     ch.niter = (uint8_t)tv[pool[head]].niter;
                     ch.first = (uint32_t)lanes.size();
                     ch.count = 0;
-                    ch.cost = ch.niter * (S.type[ty].nld + 2) + 4 * S.type[ty].nout + 8;
+                    ch.cost = ch.niter * (S.type[ty].nld + 2) + 4 * nto + 8;
                     for (int l = 0; l < 32 && head < pool.size(); ++l) {
-                        if ((l & 15) == 0) bankcnt.assign((size_t)ch.niter * 16, 0);
+                        if ((l & 15) == 0) {
+                            bankcnt.assign((size_t)ch.niter * 16, 0);
+                            for (int z = 0; z < EPLAN_MAXOUT * 16; ++z) outcnt[z] = 0;
+                        }
                         const int hl = l & 15;
-                        size_t K = l == 0 ? 1 : (ch.niter <= 2 ? 16 + 8 * hl : 8 + 2 * hl);
+                        size_t K = l == 0 ? 1 : 8 + 4 * hl;
                         K = std::min(K, pool.size() - head);
                         size_t best = head;
                         int bestcost = 1 << 30;
@@ -447,25 +482,19 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             if (nt > ch.niter) continue;
                             const uint32_t* src = &iterw[tk.first];
                             int cost = 0;
-                            if (nt == 1) {
-                                cost = bankcnt[src[0] & 15];
-                            } else if (nt == 2) {
-                                const int r0 = src[0] & 15, r1 = src[1] & 15;
-                                cost = std::min(bankcnt[r0] + bankcnt[16 + r1], bankcnt[r1] + bankcnt[16 + r0]);
-                            } else {
-                                uint8_t res[256];
-                                for (int j = 0; j < nt; ++j) res[j] = (uint8_t)(src[j] & 15);
-                                for (int it = 0; it < nt; ++it) {
-                                    int bj = it;
-                                    uint8_t bc = 255;
-                                    for (int j = it; j < nt; ++j) {
-                                        const uint8_t c2 = bankcnt[(size_t)it * 16 + res[j]];
-                                        if (c2 < bc) { bc = c2; bj = j; if (!c2) break; }
-                                    }
-                                    std::swap(res[it], res[bj]);
-                                    cost += bc;
+                            uint8_t res[256];
+                            for (int j = 0; j < nt; ++j) res[j] = (uint8_t)(src[j] & 15);
+                            for (int it = 0; it < nt; ++it) {
+                                int bj = it;
+                                uint8_t bc = 255;
+                                for (int j = it; j < nt; ++j) {
+                                    const uint8_t c2 = bankcnt[(size_t)it * 16 + res[j]];
+                                    if (c2 < bc) { bc = c2; bj = j; if (!c2) break; }
                                 }
+                                std::swap(res[it], res[bj]);
+                                cost += bc * S.type[ty].nld;
                             }
+                            for (int o = 0; o < nto; ++o) cost += outcnt[o * 16 + (tk.out[o] & 15)];   // stores into the row block
                             if (cost < bestcost) { bestcost = cost; best = c; if (!cost) break; }
                         }
                         std::swap(pool[head], pool[best]);
@@ -483,15 +512,92 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             std::swap(src[it], src[bj]);
                             bankcnt[(size_t)it * 16 + (src[it] & 15)]++;
                         }
+                        for (int o = 0; o < nto; ++o) outcnt[o * 16 + (tk.out[o] & 15)]++;
                         lanes.push_back(pool[head]);
                         ++head;
                         ++ch.count;
                     }
                     ctmp.push_back(ch);
                 }
-                L.ntasks += (int64_t)tv.size();
+                // ---- tasks with two elements, then with one: buckets by bank pair.  A lane takes a task whose bank pairs
+                // are still free in both iterations of its half-warp (the order of the two elements is chosen to fit).
+                for (int nt = 2; nt >= 1; --nt) {
+                    for (auto& cvec : cell) cvec.clear();
+                    size_t remaining = 0;
+                    for (size_t k = nlong; k < tv.size(); ++k) {
+                        if (tv[k].niter != nt) continue;
+                        const uint32_t* src = &iterw[tv[k].first];
+                        const int r0 = src[0] & 15, r1 = nt == 2 ? (int)(src[1] & 15) : r0;
+                        cell[std::min(r0, r1) * 16 + std::max(r0, r1)].push_back((uint32_t)k);
+                        ++remaining;
+                    }
+                    while (remaining) {
+                        ChunkTmp ch;
+                        ch.type = (uint8_t)ty;
+                        ch.niter = (uint8_t)nt;
+                        ch.first = (uint32_t)lanes.size();
+                        ch.count = 0;
+                        ch.cost = nt * (S.type[ty].nld + 2) + 4 * nto + 8;
+                        for (int l = 0; l < 32 && remaining; ++l) {
+                            if ((l & 15) == 0) {
+                                for (int z = 0; z < 32; ++z) cnt2[z] = 0;
+                                for (int z = 0; z < EPLAN_MAXOUT * 16; ++z) outcnt[z] = 0;
+                            }
+                            // best cell: fewest S-load conflicts, then the fullest (keeps the buckets level)
+                            int bc = -1, ba = 0, bb = 0, bcost = 1 << 30;
+                            size_t bsize = 0;
+                            for (int a2 = 0; a2 < 16; ++a2)            // a2: bank pair of iteration 0, b2: of iteration 1
+                                for (int b2 = (nt == 2 ? 0 : a2); b2 < (nt == 2 ? 16 : a2 + 1); ++b2) {
+                                    const int ci = std::min(a2, b2) * 16 + std::max(a2, b2);
+                                    const size_t sz = cell[ci].size();
+                                    if (!sz) continue;
+                                    const int cost = cnt2[a2] + (nt == 2 ? cnt2[16 + b2] : 0);
+                                    if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bc = ci; ba = a2; bb = b2; }
+                                }
+                            // inside the cell: the task whose stores into the row block collide the least
+                            std::vector<uint32_t>& cv = cell[bc];
+                            size_t bk = 0;
+                            int bo = 1 << 30;
+                            for (size_t k = 0; k < cv.size() && k < 12; ++k) {
+                                int oc = 0;
+                                for (int o = 0; o < nto; ++o) oc += outcnt[o * 16 + (tv[cv[k]].out[o] & 15)];
+                                if (oc < bo) { bo = oc; bk = k; if (!oc) break; }
+                            }
+                            const uint32_t ti = cv[bk];
+                            cv[bk] = cv.back();
+                            cv.pop_back();
+                            --remaining;
+                            const Task& tk = tv[ti];
+                            uint32_t* src = &iterw[tk.first];
+                            if (nt == 2 && (int)(src[0] & 15) != ba) std::swap(src[0], src[1]);
+                            cnt2[ba]++;
+                            if (nt == 2) cnt2[16 + bb]++;
+                            for (int o = 0; o < nto; ++o) outcnt[o * 16 + (tk.out[o] & 15)]++;
+                            lanes.push_back(ti);
+                            ++ch.count;
+                        }
+                        ctmp.push_back(ch);
+                    }
+                }
             }
             std::stable_sort(ctmp.begin(), ctmp.end(), [](const ChunkTmp& a, const ChunkTmp& b) { return a.cost > b.cost; });
+            {   // warp w runs the chunks w, w + W, ...: deal the sorted chunks in snake order so that the warps' loads even out
+                const size_t W = EPLAN_WARPS, full = ctmp.size() / W * W;
+                dealt = ctmp;
+                for (size_t s2 = 0; s2 < full; ++s2) {
+                    const size_t round = s2 / W, j = s2 % W;
+                    dealt[round * W + ((round & 1) ? W - 1 - j : j)] = ctmp[s2];
+                }
+                ctmp.swap(dealt);
+            }
+            // does every slot of the row block receive a value?  (always, unless the graph holds entries no element produces)
+            covered.assign(sg.nout, 0);
+            for (int ty = 0; ty < S.ntypes; ++ty)
+                for (const Task& tk : tasks[ty])
+                    for (int o = 0; o < S.type[ty].nout; ++o) covered[tk.out[o]] = 1;
+            pc.needzero = 0;
+            for (uint32_t z = 1; z < sg.nout; ++z)
+                if (!covered[z]) pc.needzero = 1;
             pc.chunk0 = (uint32_t)L.chunks.size();
             pc.q0 = (uint32_t)(L.blob.size() / 4);
             for (const ChunkTmp& ch : ctmp) {
@@ -565,7 +671,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             ct.nvisit = sg.nvisit;
             ct.nchunk = (uint16_t)pc.nchunk;
             ct.nrows = (uint16_t)pc.nrows;
-            ct.nout = (uint16_t)sg.nout;
+            ct.nout = (uint16_t)(sg.nout | (pc.needzero ? 0x8000u : 0u));
             ct.blob_q0 = qb + pc.q0;
             ct.blob_nq = (uint16_t)pc.nq;
             plan.nouts += sg.nout - 1;

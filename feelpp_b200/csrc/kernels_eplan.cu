@@ -95,7 +95,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     const uint4 c0 = __ldg(cq), c1 = __ldg(cq + 1);
     const uint32_t vert_off = c0.x, visit_off = c0.y, chunk_off = c0.z, row_off = c0.w;
     const int nverts = c1.x & 0xFFFF, nvisit = c1.x >> 16, nchunk = c1.y & 0xFFFF, nrows = c1.y >> 16;
-    const uint32_t nout = c1.z & 0xFFFF, blob_nq = c1.z >> 16, blob_q0 = c1.w;
+    const uint32_t nout = c1.z & 0x7FFF, needzero = c1.z & 0x8000, blob_nq = c1.z >> 16, blob_q0 = c1.w;
 
     // ---- L2 prefetch of this CTA's chunk data (streamed once from HBM; phase B then reads it at L2 latency) ----
     {
@@ -111,8 +111,10 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     // are in flight while phase A runs
     uint2 hdr = make_uint2(0u, 0u);
     if (warp + EPLAN_WARPS * lane < nchunk) hdr = __ldg(&chunks[chunk_off + warp + EPLAN_WARPS * lane]);
-    uint4 rw = make_uint4(0u, 0u, 0u, 0u);
-    if (warp * 32 + lane < nrows) rw = __ldg(&rows[row_off + warp * 32 + lane]);
+    uint4 rw = make_uint4(0u, 0u, 0u, 0u);     // row tid of the CTA's row table (EPLAN_ROWS <= blockDim.x)
+    if (tid < nrows) rw = __ldg(&rows[row_off + tid]);
+    uint32_t vw0 = 0;                          // visit word of this thread's first visit
+    if (tid < nvisit) vw0 = __ldg(&visits[visit_off + tid]);
 
     // ---- phase A0: coordinates of the CTA's unique vertices ----
     for (int i = tid; i < nverts; i += blockDim.x) {
@@ -123,12 +125,13 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
         sX[EPLAN_VERTS + i] = p0.y;
         sX[2 * EPLAN_VERTS + i] = p1.x;
     }
-    for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
+    if (needzero)   // only when the graph holds entries that no element produces
+        for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
     if (tid < NSREC) sS[tid * vs + vs - 1] = 0.0;             // the all-zero visit record (padding of the chunks)
     __syncthreads();
     // ---- phase A1: geometry of every element touched by this CTA's rows, once ----
     for (int v = tid; v < nvisit; v += blockDim.x) {
-        const uint32_t w = __ldg(&visits[visit_off + v]);
+        const uint32_t w = v == tid ? vw0 : __ldg(&visits[visit_off + v]);
         double x[4][3];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -179,6 +182,10 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
         }
     }
     __syncthreads();
+
+    // the vertex cache is dead now: it becomes the CTA's row table (read in phase C, after the next barrier)
+    uint4* sR = reinterpret_cast<uint4*>(sX);
+    if (tid < nrows) sR[tid] = rw;
 
     // ---- phase B: task chunks, lane = task; the next chunk's first words and positions are fetched one chunk ahead ----
     {
@@ -233,38 +240,33 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     __syncthreads();
 
     // ---- phase C: the CTA's row block goes to the CSR value array, every value once ----
-    for (int r0 = warp * 32; r0 < nrows; r0 += EPLAN_WARPS * 32) {
-        if (r0 != warp * 32) {
-            rw = make_uint4(0u, 0u, 0u, 0u);
-            if (r0 + lane < nrows) rw = __ldg(&rows[row_off + r0 + lane]);
-        }
-        const int cnt = min(32, nrows - r0);
-        for (int j = 0; j < cnt; ++j) {
-            const uint32_t blo = __shfl_sync(0xffffffffu, rw.x, j), bhi = __shfl_sync(0xffffffffu, rw.y, j);
-            const uint32_t off = __shfl_sync(0xffffffffu, rw.z, j);
-            const int len = (int)__shfl_sync(0xffffffffu, rw.w, j);
-            const int64_t base = (int64_t)(((uint64_t)bhi << 32) | blo);
-            const double* src = sO + off;
-            if (NCOMP == 1) {
-                double* dst = a + base;
-                if (accumulate) {
-                    for (int i = lane; i < len; i += 32) dst[i] += src[i];
-                } else {
-                    for (int i = lane; i < len; i += 32) dst[i] = src[i];
-                }
+    for (int r = warp; r < nrows; r += EPLAN_WARPS) {
+        const uint4 q = sR[r];
+        const int64_t base = (int64_t)(((uint64_t)q.y << 32) | q.x);
+        const double* src = sO + q.z;
+        const int len = (int)q.w;
+        if (NCOMP == 1) {
+            double* dst = a + base;
+            if (accumulate) {
+#pragma unroll 1
+                for (int i = lane; i < len; i += 32) dst[i] += src[i];
             } else {
-                // product space, block = v * Id: component row c1 starts at base + c1*len*NCOMP
-                for (int i = lane; i < len; i += 32) {
-                    const double v = src[i];
+#pragma unroll 1
+                for (int i = lane; i < len; i += 32) dst[i] = src[i];
+            }
+        } else {
+            // product space, block = v * Id: component row c1 starts at base + c1*len*NCOMP
+#pragma unroll 1
+            for (int i = lane; i < len; i += 32) {
+                const double v = src[i];
 #pragma unroll
-                    for (int c1 = 0; c1 < NCOMP; ++c1)
+                for (int c1 = 0; c1 < NCOMP; ++c1)
 #pragma unroll
-                        for (int c2 = 0; c2 < NCOMP; ++c2) {
-                            double* dst = a + base + (int64_t)c1 * len * NCOMP + (int64_t)i * NCOMP + c2;
-                            if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
-                            else if (!accumulate) *dst = 0.0;
-                        }
-                }
+                    for (int c2 = 0; c2 < NCOMP; ++c2) {
+                        double* dst = a + base + (int64_t)c1 * len * NCOMP + (int64_t)i * NCOMP + c2;
+                        if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
+                        else if (!accumulate) *dst = 0.0;
+                    }
             }
         }
     }

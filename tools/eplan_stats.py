@@ -26,7 +26,7 @@ print("S-load wavefronts per element: %.2f  ideal %.2f  conflict factor %.2f" % 
     st["wavefronts"] / ne, st["wavefronts_ideal"] / ne, st["wavefronts"] / st["wavefronts_ideal"]))
 c = P["ctas"]
 print("per CTA: rows %.0f  visits %.0f  verts %.0f  out %.0f  chunks %.0f" % (
-    c["nrows"].mean(), c["nvisit"].mean(), c["nverts"].mean(), c["nout"].mean(), c["nchunk"].mean()))
+    c["nrows"].mean(), c["nvisit"].mean(), c["nverts"].mean(), (c["nout"] & 0x7FFF).mean(), c["nchunk"].mean()))
 ty = P["chunks"]["type"]
 for t in range(6):
     sel = ty == t
