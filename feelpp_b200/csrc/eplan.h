@@ -28,6 +28,7 @@
 #define EPLAN_WARPS 16
 #define EPLAN_ROWS 384            // rows per CTA: the row table reuses the 6 KB vertex cache after phase A
 #define EPLAN_OMAX 7936          // 62 KB row block per CTA: two CTAs per SM next to the 40 KB geometry cache
+#define EPLAN_AHEAD 296           // CTAs between a CTA and the one that follows it on the same SM slot (2 per SM x 148)
 #define EPLAN_MAXTYPES 6
 #define EPLAN_MAXLD 5
 #define EPLAN_MAXOUT 3

@@ -2,6 +2,7 @@
 #include "eplan.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -29,6 +30,30 @@ const EPlanSpec SPEC_P2 = {2, 10, 6,
                             {2, 2, 3, {{0, 0}, {0, 1}, {1, 1}}, 3, {0, 1, 6}, 6},
                             {2, 3, 5, {{0, 0}, {0, 1}, {0, 2}, {1, 1}, {1, 2}}, 3, {2, 5, 4}, 6},
                             {2, 4, 4, {{0, 2}, {0, 3}, {1, 2}, {1, 3}}, 1, {9}, 6}}};
+
+// position of the grid point (x,y,z), 10 bits each, along the 3-D Hilbert curve (Skilling's transpose algorithm): consecutive
+// curve positions are face-adjacent cells, so a run of rows is a compact patch (a Morton run can jump across the domain)
+inline uint32_t hilbert3(uint32_t x, uint32_t y, uint32_t z)
+{
+    uint32_t X[3] = {x & 0x3FF, y & 0x3FF, z & 0x3FF};
+    const uint32_t M = 1u << 9;
+    for (uint32_t Q = M; Q > 1; Q >>= 1) {       // inverse undo
+        const uint32_t P = Q - 1;
+        for (int i = 0; i < 3; ++i) {
+            if (X[i] & Q) X[0] ^= P;
+            else { const uint32_t t = (X[0] ^ X[i]) & P; X[0] ^= t; X[i] ^= t; }
+        }
+    }
+    for (int i = 1; i < 3; ++i) X[i] ^= X[i - 1];   // Gray encode
+    uint32_t t = 0;
+    for (uint32_t Q = M; Q > 1; Q >>= 1)
+        if (X[2] & Q) t ^= Q - 1;
+    for (int i = 0; i < 3; ++i) X[i] ^= t;
+    uint32_t h = 0;                                  // interleave, X[0] most significant
+    for (int b = 9; b >= 0; --b)
+        for (int i = 0; i < 3; ++i) h = (h << 1) | ((X[i] >> b) & 1);
+    return h;
+}
 
 inline uint32_t spread3(uint32_t x)
 {
@@ -93,6 +118,7 @@ struct Builder {
     std::vector<uint8_t> uloc;
     std::vector<uint16_t> uvis;     // visit slot of every unit inside its CTA
     std::vector<int32_t> order_;    // nodes along the curve
+    bool use_hilbert = true;
 
     inline int64_t node_of(int64_t e, int i) const { return l2g[e * nd + i] / ncomp; }
     inline int row_len(int64_t node) const { return (int)((ia[node * ncomp + 1] - ia[node * ncomp]) / ncomp); }
@@ -138,7 +164,11 @@ struct Builder {
             for (int a = 0; a < nv; ++a)
                 for (int c = 0; c < 3; ++c) p[c] += xyz[3 * (int64_t)conn[4 * e + v[a]] + c];
             uint32_t m = 0;
-            for (int c = 0; c < 3; ++c) m |= spread3((uint32_t)((p[c] / nv - lo[c]) * sc[c])) << c;
+            if (use_hilbert)
+                m = hilbert3((uint32_t)((p[0] / nv - lo[0]) * sc[0]), (uint32_t)((p[1] / nv - lo[1]) * sc[1]),
+                             (uint32_t)((p[2] / nv - lo[2]) * sc[2]));
+            else
+                for (int c = 0; c < 3; ++c) m |= spread3((uint32_t)((p[c] / nv - lo[c]) * sc[c])) << c;
             key[k] = ((uint64_t)m << 32) | (uint32_t)k;
         }
         std::sort(key.begin(), key.end());
@@ -268,6 +298,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 if (conn[4 * e + a] == conn[4 * e + b]) { plan.error = "entity plan: degenerate element"; return false; }
     }
     B.node_units();
+    if (const char* cv = std::getenv("FEELGPU_EPLAN_CURVE")) B.use_hilbert = std::strcmp(cv, "morton") != 0;
     B.curve_order();
     if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
     nthreads = std::min(nthreads, 64);
@@ -355,7 +386,9 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         uint8_t outcnt[EPLAN_MAXOUT * 16];
         std::vector<uint8_t> covered;
         std::vector<uint32_t> usage, sorted, perm, vtmp;
+        std::vector<int32_t> cnodes;
         std::vector<uint32_t> cell[256];      // tasks with <= 2 elements by (bank pair of element 0, of element 1)
+        std::vector<uint32_t> cell1[16];
         int cnt2[32];
         std::vector<uint32_t> pool, lanes;    // remaining tasks of a type; tasks of every chunk lane
         struct ChunkTmp { uint8_t type, niter; uint32_t first, count; int cost; };
@@ -367,14 +400,22 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             Local::PerCta pc;
             pc.row0 = (uint32_t)L.rows.size();
             uint32_t rowoff = 1;
-            for (int64_t k = sg.nb; k < sg.ne; ++k) {
-                const int64_t node = B.order_[k];
+            // rows in CSR order: neighbours in memory are neighbours in the row block, and runs of them are written as one
+            // segment (scalar spaces; pieces of <= 256 values so that the warps share long runs)
+            cnodes.assign(B.order_.begin() + sg.nb, B.order_.begin() + sg.ne);
+            std::sort(cnodes.begin(), cnodes.end(), [&](int32_t x, int32_t y) { return B.ia[(int64_t)x * B.ncomp] < B.ia[(int64_t)y * B.ncomp]; });
+            for (size_t k = 0; k < cnodes.size(); ++k) {
+                const int64_t node = cnodes[k];
                 const uint32_t len = (uint32_t)B.row_len(node);
                 EPlanRow row;
                 row.base = B.ia[node * B.ncomp];
                 row.off = rowoff;
                 row.len = len;
-                L.rows.push_back(row);
+                if (B.ncomp == 1 && L.rows.size() > pc.row0 && L.rows.back().base + (int64_t)L.rows.back().len == row.base &&
+                    L.rows.back().len + len <= 256)
+                    L.rows.back().len += len;
+                else
+                    L.rows.push_back(row);
                 ent.clear();
                 for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) B.unit_entries(q, ent);
                 std::sort(ent.begin(), ent.end());
@@ -521,41 +562,59 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 }
                 // ---- tasks with two elements, then with one: buckets by bank pair.  A lane takes a task whose bank pairs
                 // are still free in both iterations of its half-warp (the order of the two elements is chosen to fit).
-                for (int nt = 2; nt >= 1; --nt) {
+                {
                     for (auto& cvec : cell) cvec.clear();
-                    size_t remaining = 0;
+                    for (auto& cvec : cell1) cvec.clear();
+                    size_t rem2 = 0, rem1 = 0;
                     for (size_t k = nlong; k < tv.size(); ++k) {
-                        if (tv[k].niter != nt) continue;
                         const uint32_t* src = &iterw[tv[k].first];
-                        const int r0 = src[0] & 15, r1 = nt == 2 ? (int)(src[1] & 15) : r0;
-                        cell[std::min(r0, r1) * 16 + std::max(r0, r1)].push_back((uint32_t)k);
-                        ++remaining;
+                        const int r0 = src[0] & 15;
+                        if (tv[k].niter == 2) {
+                            const int r1 = src[1] & 15;
+                            cell[std::min(r0, r1) * 16 + std::max(r0, r1)].push_back((uint32_t)k);
+                            ++rem2;
+                        } else {
+                            cell1[r0].push_back((uint32_t)k);
+                            ++rem1;
+                        }
                     }
-                    while (remaining) {
+                    while (rem2 + rem1) {
+                        const int cn = rem2 ? 2 : 1;                 // a chunk of two-element tasks is topped up with one-element tasks
                         ChunkTmp ch;
                         ch.type = (uint8_t)ty;
-                        ch.niter = (uint8_t)nt;
+                        ch.niter = (uint8_t)cn;
                         ch.first = (uint32_t)lanes.size();
                         ch.count = 0;
-                        ch.cost = nt * (S.type[ty].nld + 2) + 4 * nto + 8;
-                        for (int l = 0; l < 32 && remaining; ++l) {
+                        ch.cost = cn * (S.type[ty].nld + 2) + 4 * nto + 8;
+                        for (int l = 0; l < 32 && rem2 + rem1; ++l) {
                             if ((l & 15) == 0) {
                                 for (int z = 0; z < 32; ++z) cnt2[z] = 0;
                                 for (int z = 0; z < EPLAN_MAXOUT * 16; ++z) outcnt[z] = 0;
                             }
+                            const int nt = rem2 ? 2 : 1;
                             // best cell: fewest S-load conflicts, then the fullest (keeps the buckets level)
-                            int bc = -1, ba = 0, bb = 0, bcost = 1 << 30;
+                            int ba = 0, bb = 0, bcost = 1 << 30;
                             size_t bsize = 0;
-                            for (int a2 = 0; a2 < 16; ++a2)            // a2: bank pair of iteration 0, b2: of iteration 1
-                                for (int b2 = (nt == 2 ? 0 : a2); b2 < (nt == 2 ? 16 : a2 + 1); ++b2) {
-                                    const int ci = std::min(a2, b2) * 16 + std::max(a2, b2);
-                                    const size_t sz = cell[ci].size();
+                            std::vector<uint32_t>* bcv = nullptr;
+                            if (nt == 2) {
+                                for (int a2 = 0; a2 < 16; ++a2)      // a2: bank pair of iteration 0, b2: of iteration 1
+                                    for (int b2 = 0; b2 < 16; ++b2) {
+                                        std::vector<uint32_t>& cv2 = cell[std::min(a2, b2) * 16 + std::max(a2, b2)];
+                                        const size_t sz = cv2.size();
+                                        if (!sz) continue;
+                                        const int cost = cnt2[a2] + cnt2[16 + b2];
+                                        if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bcv = &cv2; ba = a2; bb = b2; }
+                                    }
+                            } else {
+                                for (int a2 = 0; a2 < 16; ++a2) {
+                                    const size_t sz = cell1[a2].size();
                                     if (!sz) continue;
-                                    const int cost = cnt2[a2] + (nt == 2 ? cnt2[16 + b2] : 0);
-                                    if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bc = ci; ba = a2; bb = b2; }
+                                    const int cost = cnt2[a2];
+                                    if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bcv = &cell1[a2]; ba = a2; }
                                 }
+                            }
                             // inside the cell: the task whose stores into the row block collide the least
-                            std::vector<uint32_t>& cv = cell[bc];
+                            std::vector<uint32_t>& cv = *bcv;
                             size_t bk = 0;
                             int bo = 1 << 30;
                             for (size_t k = 0; k < cv.size() && k < 12; ++k) {
@@ -566,7 +625,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             const uint32_t ti = cv[bk];
                             cv[bk] = cv.back();
                             cv.pop_back();
-                            --remaining;
+                            if (nt == 2) --rem2; else --rem1;
                             const Task& tk = tv[ti];
                             uint32_t* src = &iterw[tk.first];
                             if (nt == 2 && (int)(src[0] & 15) != ba) std::swap(src[0], src[1]);

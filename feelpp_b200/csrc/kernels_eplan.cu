@@ -97,15 +97,31 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     const int nverts = c1.x & 0xFFFF, nvisit = c1.x >> 16, nchunk = c1.y & 0xFFFF, nrows = c1.y >> 16;
     const uint32_t nout = c1.z & 0x7FFF, needzero = c1.z & 0x8000, blob_nq = c1.z >> 16, blob_q0 = c1.w;
 
-    // ---- L2 prefetch of this CTA's chunk data (streamed once from HBM; phase B then reads it at L2 latency) ----
+    // ---- L2 prefetch: the plan is streamed once from HBM.  One warp pulls the data of the CTA that will follow this one on
+    // the SM (blockIdx.x + EPLAN_AHEAD) into L2, so that its prologue and its phase B run at L2 latency; the first CTAs of
+    // the grid prefetch their own chunk data.
     {
-        const uint32_t pieces = (blob_nq + 255) >> 8;                // 4 KB pieces
-        for (uint32_t p = tid; p < pieces; p += blockDim.x) {
-            const uint32_t q = p << 8;
-            const uint32_t bytes = min(256u, blob_nq - q) << 4;
-            const void* ptr = reinterpret_cast<const uint4*>(blob) + blob_q0 + q;
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
+        auto prefetch_range = [&](const void* p0, uint32_t nbytes, int l0) {
+            const uintptr_t lo = reinterpret_cast<uintptr_t>(p0) & ~(uintptr_t)15;
+            const uintptr_t hi = (reinterpret_cast<uintptr_t>(p0) + nbytes + 15) & ~(uintptr_t)15;
+            for (uintptr_t q = lo + (uintptr_t)l0 * 4096; q < hi; q += 32 * 4096) {
+                const uint32_t bytes = (uint32_t)min((uintptr_t)4096, hi - q);
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(q), "r"(bytes) : "memory");
+            }
+        };
+        if (warp == EPLAN_WARPS - 1) {
+            const uint32_t nb = blockIdx.x + EPLAN_AHEAD;
+            if (nb < gridDim.x) {
+                const uint4* nq = reinterpret_cast<const uint4*>(ctas + nb);
+                const uint4 n0 = __ldg(nq), n1 = __ldg(nq + 1);
+                prefetch_range(verts + n0.x, (n1.x & 0xFFFF) * 4u, lane);
+                prefetch_range(visits + n0.y, (n1.x >> 16) * 4u, lane);
+                prefetch_range(chunks + n0.z, (n1.y & 0xFFFF) * 8u, lane);
+                prefetch_range(rows + n0.w, (n1.y >> 16) * 16u, lane);
+                prefetch_range(reinterpret_cast<const uint4*>(blob) + n1.w, (n1.z >> 16) * 16u, lane);
+            }
         }
+        if (blockIdx.x < EPLAN_AHEAD && warp == 0) prefetch_range(reinterpret_cast<const uint4*>(blob) + blob_q0, blob_nq * 16u, lane);
     }
     // headers of this warp's chunks (warp, warp + W, ...: lane k holds the k-th) and its first batch of rows: the loads
     // are in flight while phase A runs
