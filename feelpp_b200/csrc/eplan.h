@@ -41,6 +41,7 @@ struct EPlanType {
     int nout;
     int outdof[EPLAN_MAXOUT];    // re-labelled local dof of every output column
     int rowdof;                  // re-labelled local dof of the row
+    int phaseA;                  // 1: single-element tasks whose outputs are stored by phase A (sigma = the whole tet)
 };
 struct EPlanSpec {
     int order, n, ntypes;
@@ -58,7 +59,8 @@ inline int eplan_sidx(int k, int l)
 
 struct EPlanCta {                // 32 bytes
     uint32_t vert_off;           // unique vertex ids: i32 [vert_off + i]
-    uint32_t visit_off;          // visit words: u32 [visit_off + v] = 4 x u8 local vertex index
+    uint32_t visit_off;          // visit words (P1: 1 per visit, P2: 4): 4 x u8 local vertex index [, 6 x u16 row-block slots of the
+                                 // outputs (edge le, opposite edge), le = original local edge of the row]
     uint32_t chunk_off;          // chunk headers
     uint32_t row_off;            // row table
     uint16_t nverts, nvisit;

@@ -29,7 +29,7 @@ const EPlanSpec SPEC_P2 = {2, 10, 6,
                             {1, 3, 2, {{0, 1}, {0, 2}}, 1, {4}, 0},
                             {2, 2, 3, {{0, 0}, {0, 1}, {1, 1}}, 3, {0, 1, 6}, 6},
                             {2, 3, 5, {{0, 0}, {0, 1}, {0, 2}, {1, 1}, {1, 2}}, 3, {2, 5, 4}, 6},
-                            {2, 4, 4, {{0, 2}, {0, 3}, {1, 2}, {1, 3}}, 1, {9}, 6}}};
+                            {2, 4, 4, {{0, 2}, {0, 3}, {1, 2}, {1, 3}}, 1, {9}, 6, 1}}};
 
 // position of the grid point (x,y,z), 10 bits each, along the 3-D Hilbert curve (Skilling's transpose algorithm): consecutive
 // curve positions are face-adjacent cells, so a run of rows is a compact patch (a Morton run can jump across the domain)
@@ -84,6 +84,7 @@ struct Task {
     uint16_t niter;
     uint32_t first;                 // into the per-CTA iteration word array
     uint16_t out[EPLAN_MAXOUT];
+    uint8_t aux;                    // tasks done in phase A: original local edge of the row dof
 };
 
 struct CtaSeg {
@@ -308,6 +309,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     B.uvis.resize(B.uelt.size());
     plan.verts.clear();
     plan.visits.clear();
+    const int vstride = order == 2 ? 4 : 1;   // words per visit: vertex bytes [+ 6 u16 row-block slots of the tet-type outputs]
     {
         std::vector<int32_t> estamp(nElt, -1), eslot(nElt, 0), pstamp(nPts, -1), pslot(nPts, 0), newpts;
         int64_t k = 0;
@@ -358,6 +360,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             w |= (uint32_t)pslot[pt] << (8 * a);
                         }
                         plan.visits.push_back(w);
+                        for (int z = 1; z < vstride; ++z) plan.visits.push_back(0u);   // filled per CTA below
                     }
                     B.uvis[q] = (uint16_t)eslot[e];
                 }
@@ -429,6 +432,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                     tk.niter = (uint16_t)(g1 - g0);
                     tk.first = (uint32_t)iterw.size();
                     for (int o = 0; o < EPLAN_MAXOUT; ++o) tk.out[o] = 0;
+                    tk.aux = (uint8_t)(B.uloc[ent[g0].q] >= 4 ? B.uloc[ent[g0].q] - 4 : 0);
                     if (g1 - g0 > 255) { L.error = "entity plan: more than 255 elements around an entity"; return; }
                     for (size_t g = g0; g < g1; ++g) {
                         const Entry& en = ent[g];
@@ -461,7 +465,8 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 usage.assign(nv, 0);
                 for (int ty = 0; ty < S.ntypes; ++ty)
                     for (const Task& tk : tasks[ty])
-                        for (int it = 0; it < tk.niter; ++it) usage[iterw[tk.first + it] & 0x3FF] += (uint32_t)S.type[ty].nld;
+                        for (int it = 0; it < tk.niter; ++it)
+                            usage[iterw[tk.first + it] & 0x3FF] += (uint32_t)(S.type[ty].phaseA ? 0 : S.type[ty].nld);
                 sorted.resize(nv);
                 for (uint32_t v = 0; v < nv; ++v) sorted[v] = v;
                 std::stable_sort(sorted.begin(), sorted.end(), [&](uint32_t x, uint32_t y) { return usage[x] > usage[y]; });
@@ -473,8 +478,18 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 }
                 for (uint32_t& w : iterw) w = (w & ~0x3FFu) | perm[w & 0x3FF];
                 uint32_t* vw = plan.visits.data() + sg.visit_off;      // this CTA's segment: no other thread touches it
-                vtmp.assign(vw, vw + nv);
-                for (uint32_t v = 0; v < nv; ++v) vw[perm[v]] = vtmp[v];
+                vtmp.assign(vw, vw + (size_t)nv * vstride);
+                for (uint32_t v = 0; v < nv; ++v)
+                    for (int z = 0; z < vstride; ++z) vw[(size_t)perm[v] * vstride + z] = vtmp[(size_t)v * vstride + z];
+                // outputs whose simplex is the whole tet have one contribution: the thread that computes the element's S in
+                // phase A stores them straight into the row block (slot per original local edge of the row; 0 = not ours)
+                for (int ty = 0; ty < S.ntypes; ++ty) {
+                    if (!S.type[ty].phaseA) continue;
+                    for (const Task& tk : tasks[ty]) {
+                        const uint32_t slot = iterw[tk.first] & 0x3FF;
+                        vw[(size_t)slot * vstride + 1 + tk.aux / 2] |= (uint32_t)tk.out[0] << (16 * (tk.aux & 1));
+                    }
+                }
             }
             // ---- chunks: 32 tasks of one type, longest first ----
             // All S loads of one iteration hit the bank pair (visit slot mod 16); a half-warp is served in one pass only
@@ -485,9 +500,10 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             lanes.clear();
             for (int ty = 0; ty < S.ntypes; ++ty) {
                 std::vector<Task>& tv = tasks[ty];
+                L.ntasks += (int64_t)tv.size();
+                if (S.type[ty].phaseA) continue;
                 std::stable_sort(tv.begin(), tv.end(), [](const Task& a, const Task& b) { return a.niter > b.niter; });
                 const int nto = S.type[ty].nout;
-                L.ntasks += (int64_t)tv.size();
                 size_t nlong = 0;
                 while (nlong < tv.size() && tv[nlong].niter > 2) ++nlong;
                 // ---- tasks with 3 or more elements: window search ----
@@ -744,6 +760,6 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         L = Local();
     }
     plan.blob.resize(plan.blob.size() + 64, 0u);
-    plan.nvisits = (int64_t)plan.visits.size();
+    plan.nvisits = (int64_t)plan.visits.size() / vstride;
     return true;
 }

@@ -129,8 +129,11 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     if (warp + EPLAN_WARPS * lane < nchunk) hdr = __ldg(&chunks[chunk_off + warp + EPLAN_WARPS * lane]);
     uint4 rw = make_uint4(0u, 0u, 0u, 0u);     // row tid of the CTA's row table (EPLAN_ROWS <= blockDim.x)
     if (tid < nrows) rw = __ldg(&rows[row_off + tid]);
-    uint32_t vw0 = 0;                          // visit word of this thread's first visit
-    if (tid < nvisit) vw0 = __ldg(&visits[visit_off + tid]);
+    uint4 vw0 = make_uint4(0u, 0u, 0u, 0u);    // visit record of this thread's first visit
+    if (tid < nvisit) {
+        if (ORDER == 2) vw0 = __ldg(reinterpret_cast<const uint4*>(visits + visit_off) + tid);
+        else vw0.x = __ldg(&visits[visit_off + tid]);
+    }
 
     // ---- phase A0: coordinates of the CTA's unique vertices ----
     for (int i = tid; i < nverts; i += blockDim.x) {
@@ -147,7 +150,12 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     __syncthreads();
     // ---- phase A1: geometry of every element touched by this CTA's rows, once ----
     for (int v = tid; v < nvisit; v += blockDim.x) {
-        const uint32_t w = v == tid ? vw0 : __ldg(&visits[visit_off + v]);
+        uint4 vq = vw0;
+        if (v != tid) {
+            if (ORDER == 2) vq = __ldg(reinterpret_cast<const uint4*>(visits + visit_off) + v);
+            else vq.x = __ldg(&visits[visit_off + v]);
+        }
+        const uint32_t w = vq.x;
         double x[4][3];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -171,6 +179,11 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
         const double cj = cval * fabs(det);
         if (FORM == 0) {
             sS[v] = cj;
+            if (ORDER == 2) {   // (edge, opposite edge) entries: one element each, stored here (0 = not a row of this CTA)
+                const double m = c_ecoef.mass[5][0] * cj;
+                sO[vq.y & 0xFFFF] = m; sO[vq.y >> 16] = m; sO[vq.z & 0xFFFF] = m;
+                sO[vq.z >> 16] = m;    sO[vq.w & 0xFFFF] = m; sO[vq.w >> 16] = m;
+            }
         } else {
             const double id = 1.0 / det;
             // B = K^{-T} (geomap.hpp:1985-1991): B[r][b] = d xi_b / d x_r ; grad lambda_{b+1} = B[:,b]/2
@@ -189,12 +202,29 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
             // S_kl = c J grad(l_k).grad(l_l): diagonals 0..3, then (0,1),(0,2),(0,3),(1,2),(1,3),(2,3)
 #pragma unroll
             for (int k = 0; k < 4; ++k) sS[k * vs + v] = cj * (h[k][0] * h[k][0] + h[k][1] * h[k][1] + h[k][2] * h[k][2]);
-            sS[4 * vs + v] = cj * (h[0][0] * h[1][0] + h[0][1] * h[1][1] + h[0][2] * h[1][2]);
-            sS[5 * vs + v] = cj * (h[0][0] * h[2][0] + h[0][1] * h[2][1] + h[0][2] * h[2][2]);
-            sS[6 * vs + v] = cj * (h[0][0] * h[3][0] + h[0][1] * h[3][1] + h[0][2] * h[3][2]);
-            sS[7 * vs + v] = cj * (h[1][0] * h[2][0] + h[1][1] * h[2][1] + h[1][2] * h[2][2]);
-            sS[8 * vs + v] = cj * (h[1][0] * h[3][0] + h[1][1] * h[3][1] + h[1][2] * h[3][2]);
-            sS[9 * vs + v] = cj * (h[2][0] * h[3][0] + h[2][1] * h[3][1] + h[2][2] * h[3][2]);
+            const double s01 = cj * (h[0][0] * h[1][0] + h[0][1] * h[1][1] + h[0][2] * h[1][2]);
+            const double s02 = cj * (h[0][0] * h[2][0] + h[0][1] * h[2][1] + h[0][2] * h[2][2]);
+            const double s03 = cj * (h[0][0] * h[3][0] + h[0][1] * h[3][1] + h[0][2] * h[3][2]);
+            const double s12 = cj * (h[1][0] * h[2][0] + h[1][1] * h[2][1] + h[1][2] * h[2][2]);
+            const double s13 = cj * (h[1][0] * h[3][0] + h[1][1] * h[3][1] + h[1][2] * h[3][2]);
+            const double s23 = cj * (h[2][0] * h[3][0] + h[2][1] * h[3][1] + h[2][2] * h[3][2]);
+            sS[4 * vs + v] = s01;
+            sS[5 * vs + v] = s02;
+            sS[6 * vs + v] = s03;
+            sS[7 * vs + v] = s12;
+            sS[8 * vs + v] = s13;
+            sS[9 * vs + v] = s23;
+            if (ORDER == 2) {
+                // (edge, opposite edge) entries have sigma = the whole tet, i.e. this element alone: value =
+                // x (S_ac + S_ad + S_bc + S_bd) for edges (a,b) | (c,d); local edges e0=(1,2)|e3=(0,3), e1=(2,0)|e4=(1,3),
+                // e2=(0,1)|e5=(2,3) (feelmesh/simplexordering.hpp:283-291).  Slot per row edge; 0 = not a row of this CTA.
+                const double x5 = c_ecoef.coef[5][0][0];
+                const double t0 = x5 * ((s01 + s13) + (s02 + s23));
+                const double t1 = x5 * ((s12 + s23) + (s01 + s03));
+                const double t2 = x5 * ((s02 + s03) + (s12 + s13));
+                sO[vq.y & 0xFFFF] = t0; sO[vq.y >> 16] = t1; sO[vq.z & 0xFFFF] = t2;
+                sO[vq.z >> 16] = t0;    sO[vq.w & 0xFFFF] = t1; sO[vq.w >> 16] = t2;
+            }
         }
     }
     __syncthreads();
@@ -243,8 +273,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
                 case 1: run_chunk<ORDER, FORM, 1>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
                 case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
                 case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                case 4: if (ORDER >= 2) run_chunk<ORDER, FORM, 4>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                default: if (ORDER >= 2) run_chunk<ORDER, FORM, 5>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
                 }
                 w = nw;
                 w1 = nw1;
@@ -475,6 +504,12 @@ static bool eplan_coefficients(const EPlanSpec& S, const feelgpu_tables& t, int 
                 return false;
             }
             for (int k = 0; k < T.nld; ++k) out->coef[ty][o][k] = x[k];
+            if (T.phaseA)   // phase A applies one coefficient to the sum of the loaded entries
+                for (int k = 1; k < T.nld; ++k)
+                    if (std::fabs(x[k] - x[0]) > 1e-11 * std::fabs(x[0])) {
+                        *why = "entity plan: the (edge, opposite edge) entry is not symmetric in the loaded S entries";
+                        return false;
+                    }
         }
     }
     return true;

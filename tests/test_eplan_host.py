@@ -94,7 +94,9 @@ def interpret(P, mesh, order, nnz, form, coef, mass):
     written = np.zeros(nnz, dtype=np.int32)
     for ct in P["ctas"]:
         verts = P["verts"][ct["vert_off"]:ct["vert_off"] + ct["nverts"]]
-        vw = P["visits"][ct["visit_off"]:ct["visit_off"] + ct["nvisit"]]
+        vst = 4 if order == 2 else 1            # words per visit
+        vrec = P["visits"][ct["visit_off"]:ct["visit_off"] + vst * int(ct["nvisit"])].reshape(-1, vst)
+        vw = vrec[:, 0]
         lv = np.stack([(vw >> (8 * k)) & 255 for k in range(4)], axis=1)
         assert lv.max(initial=0) < ct["nverts"]
         S, J = visit_records(mesh.xyz[verts[lv]])
@@ -103,6 +105,19 @@ def interpret(P, mesh, order, nnz, form, coef, mass):
         nout, needzero = int(ct["nout"]) & 0x7FFF, int(ct["nout"]) >> 15
         out = np.zeros(P["omax"]) if needzero else np.full(P["omax"], np.nan)   # the kernel skips the zero fill
         hit = np.zeros(P["omax"], dtype=np.int32)
+        if order == 2 and ct["nvisit"]:
+            # phase A: (edge, opposite edge) entries, one element each; slot per original local edge of the row, 0 = trash
+            if form == 1:
+                s01, s02, s03, s12, s13, s23 = (S[:, k] for k in range(4, 10))
+                x5 = coef[5][0][0]
+                t = [x5 * ((s01 + s13) + (s02 + s23)), x5 * ((s12 + s23) + (s01 + s03)), x5 * ((s02 + s03) + (s12 + s13))]
+            else:
+                t = [mass[5][0] * J] * 3
+            for le in range(6):
+                pos = (vrec[:, 1 + le // 2] >> (16 * (le & 1))) & 0xFFFF
+                live = pos != 0
+                out[pos[live]] = t[le % 3][live]
+                np.add.at(hit, pos[live], 1)
         for ch in P["chunks"][ct["chunk_off"]:ct["chunk_off"] + ct["nchunk"]]:
             ty, niter = int(ch["type"]), int(ch["niter"])
             nld, no = (NLD[order][ty] if form == 1 else 1), NOUT[order][ty]
@@ -157,5 +172,6 @@ def test_plan_limits_split_ctas():
     P = build_plan(mesh, Xh, ia, ja)
     assert len(P["ctas"]) > 1
     assert int(P["rows"]["len"].sum()) == int(ia[-1]) and int(P["ctas"]["nrows"].sum()) <= Xh.nDof()
+    assert (P["chunks"]["type"] != 5).all()
     assert (P["ctas"]["nvisit"] < P["vs"]).all() and (P["ctas"]["nverts"] <= 256).all()
     assert ((P["ctas"]["nout"] & 0x7FFF) <= P["omax"]).all() and (P["ctas"]["nrows"] <= 384).all()
