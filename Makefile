@@ -2,7 +2,8 @@
 NVCC ?= /usr/local/cuda/bin/nvcc
 CXX ?= g++
 ARCH := -gencode arch=compute_100a,code=sm_100a
-NVCCFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xptxas -v
+EPLAN_DEFS ?=
+NVCCFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xptxas -v $(EPLAN_DEFS)
 CSRC := feelpp_b200/csrc
 LIB := feelpp_b200/lib
 
@@ -18,7 +19,7 @@ $(LIB)/rowplan_build.o: $(CSRC)/rowplan_build.cpp $(CSRC)/rowplan.h
 
 $(LIB)/eplan_build.o: $(CSRC)/eplan_build.cpp $(CSRC)/eplan.h
 	@mkdir -p $(LIB)
-	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread -c $< -o $@
+	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread $(EPLAN_DEFS) -c $< -o $@
 
 $(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart

@@ -23,12 +23,25 @@
 #include <string>
 #include <vector>
 
+#ifndef EPLAN_VS
 #define EPLAN_VS 512             // visit slots per CTA (the last one is the all-zero record)
+#endif
 #define EPLAN_VERTS 256          // unique vertices per CTA (u8 local vertex ids)
+#ifndef EPLAN_WARPS
 #define EPLAN_WARPS 16
+#endif
+#ifndef EPLAN_MINB
+#define EPLAN_MINB 2               // CTAs per SM the kernel is compiled for
+#endif
 #define EPLAN_ROWS 384            // rows per CTA: the row table reuses the 6 KB vertex cache after phase A
+#ifndef EPLAN_OMAX
 #define EPLAN_OMAX 7936          // 62 KB row block per CTA: two CTAs per SM next to the 40 KB geometry cache
-#define EPLAN_AHEAD 296           // CTAs between a CTA and the one that follows it on the same SM slot (2 per SM x 148)
+#endif
+#define EPLAN_AHEAD (EPLAN_MINB * 148)   // CTAs between a CTA and the one that follows it on the same SM slot
+#define EPLAN_HDRS 256            // chunk headers kept in shared memory (the rest, if any, is read from global memory)
+#ifndef EPLAN_NSUB
+#define EPLAN_NSUB 1               // short chunks run under one header: measured slower on B200 (coarser hand-out, deeper word stream); kept at 1
+#endif
 #define EPLAN_MAXTYPES 6
 #define EPLAN_MAXLD 5
 #define EPLAN_MAXOUT 3
@@ -72,9 +85,9 @@ struct EPlanCta {                // 32 bytes
 static_assert(sizeof(EPlanCta) == 32, "EPlanCta is read as two uint4");
 static_assert(EPLAN_ROWS * 16 <= 3 * EPLAN_VERTS * 8 && EPLAN_ROWS <= EPLAN_WARPS * 32, "row table reuses the vertex cache");
 struct EPlanChunk {              // 8 bytes
-    uint32_t q0;                 // offset of the chunk data in quads (16 B): words u32 [niter][32], then outpos u16 [nout][32]
+    uint32_t q0;                 // offset of the chunk data in quads (16 B): words u32 [nsub*niter][32], then slots u16 [nsub*nout][32]
     uint8_t type, niter;
-    uint16_t pad;
+    uint16_t pad;                // nsub: sub-chunks (32 tasks each) run back to back
 };
 struct EPlanRow {                // 16 bytes
     int64_t base;                // CSR offset of the row's first value (dof level, component 0 row)

@@ -395,7 +395,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         int cnt2[32];
         std::vector<uint32_t> pool, lanes;    // remaining tasks of a type; tasks of every chunk lane
         struct ChunkTmp { uint8_t type, niter; uint32_t first, count; int cost; };
-        std::vector<ChunkTmp> ctmp, dealt;
+        std::vector<ChunkTmp> ctmp;
         for (int64_t c = nCta * t / nthreads; c < nCta * (t + 1) / nthreads; ++c) {
             const CtaSeg& sg = segs[c];
             for (int ty = 0; ty < S.ntypes; ++ty) tasks[ty].clear();
@@ -522,7 +522,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                     ch.niter = (uint8_t)tv[pool[head]].niter;
                     ch.first = (uint32_t)lanes.size();
                     ch.count = 0;
-                    ch.cost = ch.niter * (S.type[ty].nld + 2) + 4 * nto + 8;
+                    ch.cost = 45 + ch.niter * (5 * S.type[ty].nld + 8) + nto * (S.type[ty].nld + 3);
                     for (int l = 0; l < 32 && head < pool.size(); ++l) {
                         if ((l & 15) == 0) {
                             bankcnt.assign((size_t)ch.niter * 16, 0);
@@ -601,7 +601,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                         ch.niter = (uint8_t)cn;
                         ch.first = (uint32_t)lanes.size();
                         ch.count = 0;
-                        ch.cost = cn * (S.type[ty].nld + 2) + 4 * nto + 8;
+                        ch.cost = 45 + cn * (5 * S.type[ty].nld + 8) + nto * (S.type[ty].nld + 3);
                         for (int l = 0; l < 32 && rem2 + rem1; ++l) {
                             if ((l & 15) == 0) {
                                 for (int z = 0; z < 32; ++z) cnt2[z] = 0;
@@ -656,15 +656,6 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 }
             }
             std::stable_sort(ctmp.begin(), ctmp.end(), [](const ChunkTmp& a, const ChunkTmp& b) { return a.cost > b.cost; });
-            {   // warp w runs the chunks w, w + W, ...: deal the sorted chunks in snake order so that the warps' loads even out
-                const size_t W = EPLAN_WARPS, full = ctmp.size() / W * W;
-                dealt = ctmp;
-                for (size_t s2 = 0; s2 < full; ++s2) {
-                    const size_t round = s2 / W, j = s2 % W;
-                    dealt[round * W + ((round & 1) ? W - 1 - j : j)] = ctmp[s2];
-                }
-                ctmp.swap(dealt);
-            }
             // does every slot of the row block receive a value?  (always, unless the graph holds entries no element produces)
             covered.assign(sg.nout, 0);
             for (int ty = 0; ty < S.ntypes; ++ty)
@@ -675,29 +666,43 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 if (!covered[z]) pc.needzero = 1;
             pc.chunk0 = (uint32_t)L.chunks.size();
             pc.q0 = (uint32_t)(L.blob.size() / 4);
-            for (const ChunkTmp& ch : ctmp) {
+            // Short chunks (<= 2 iterations) cost more in per-chunk overhead than in work: up to EPLAN_NSUB of them (same
+            // type and length) are run back to back under one header.  Data of a chunk: words u32 [nsub*niter][32], then
+            // row-block slots u16 [nsub*nout][32].
+            for (size_t c0 = 0; c0 < ctmp.size();) {
+                const ChunkTmp& ch = ctmp[c0];
                 const EPlanType& T = S.type[ch.type];
                 const std::vector<Task>& tv = tasks[ch.type];
-                cw.assign((size_t)ch.niter * 32, (uint32_t)(EPLAN_VS - 1));   // padding: the all-zero visit record
-                for (uint32_t l = 0; l < ch.count; ++l) {
-                    const Task& tk = tv[lanes[ch.first + l]];
-                    for (int it = 0; it < tk.niter; ++it) cw[(size_t)it * 32 + l] = iterw[tk.first + it];
-                    L.niters += tk.niter;
-                }
-                L.niters_padded += (int64_t)ch.niter * 32;
-                model_chunk(T, cw, ch.niter, L.wf, L.wf_ideal);
+                size_t nsub = 1;
+                if (ch.niter <= 2)
+                    while (nsub < EPLAN_NSUB && c0 + nsub < ctmp.size() && ctmp[c0 + nsub].type == ch.type && ctmp[c0 + nsub].niter == ch.niter) ++nsub;
                 EPlanChunk hc;
                 hc.q0 = (uint32_t)(L.blob.size() / 4);
                 hc.type = ch.type;
                 hc.niter = ch.niter;
-                hc.pad = 0;
+                hc.pad = (uint16_t)nsub;
                 L.chunks.push_back(hc);
-                L.blob.insert(L.blob.end(), cw.begin(), cw.end());
-                const size_t ob = L.blob.size();
-                L.blob.resize(ob + (size_t)T.nout * 16, 0u);              // u16 [nout][32], 0 = trash cell
-                uint16_t* op = reinterpret_cast<uint16_t*>(L.blob.data() + ob);
-                for (uint32_t l = 0; l < ch.count; ++l)
-                    for (int o = 0; o < T.nout; ++o) op[o * 32 + l] = tv[lanes[ch.first + l]].out[o];
+                for (size_t j = 0; j < nsub; ++j) {
+                    const ChunkTmp& cj = ctmp[c0 + j];
+                    cw.assign((size_t)cj.niter * 32, (uint32_t)(EPLAN_VS - 1));   // padding: the all-zero visit record
+                    for (uint32_t l = 0; l < cj.count; ++l) {
+                        const Task& tk = tv[lanes[cj.first + l]];
+                        for (int it = 0; it < tk.niter; ++it) cw[(size_t)it * 32 + l] = iterw[tk.first + it];
+                        L.niters += tk.niter;
+                    }
+                    L.niters_padded += (int64_t)cj.niter * 32;
+                    model_chunk(T, cw, cj.niter, L.wf, L.wf_ideal);
+                    L.blob.insert(L.blob.end(), cw.begin(), cw.end());
+                }
+                for (size_t j = 0; j < nsub; ++j) {
+                    const ChunkTmp& cj = ctmp[c0 + j];
+                    const size_t ob = L.blob.size();
+                    L.blob.resize(ob + (size_t)T.nout * 16, 0u);              // u16 [nout][32], 0 = trash cell
+                    uint16_t* op = reinterpret_cast<uint16_t*>(L.blob.data() + ob);
+                    for (uint32_t l = 0; l < cj.count; ++l)
+                        for (int o = 0; o < T.nout; ++o) op[o * 32 + l] = tv[lanes[cj.first + l]].out[o];
+                }
+                c0 += nsub;
             }
             pc.nchunk = (uint32_t)L.chunks.size() - pc.chunk0;
             pc.nq = (uint32_t)(L.blob.size() / 4) - pc.q0;

@@ -287,6 +287,7 @@ int feelgpu_pattern_destroy(feelgpu_pattern_t pat)
     feelgpu_eplan_destroy(pat);
     if (pat->d_ia) cudaFree(pat->d_ia);
     if (pat->d_pos) cudaFree(pat->d_pos);
+    if (pat->d_stage) cudaFree(pat->d_stage);
     delete pat;
     return FEELGPU_OK;
 }
@@ -416,8 +417,9 @@ int feelgpu_form2_assemble_host(feelgpu_pattern_t pat, const feelgpu_form2_desc*
     feelgpu_context_t ctx = pat->ctx;
     if (!a_host) ARG_FAIL(ctx, "form2_assemble_host: null output");
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));
-    double* d = nullptr;
-    CTX_CUDA(ctx, cudaMalloc(&d, sizeof(double) * std::max<int64_t>(pat->nnz, 1)));
+    // the device staging array lives with the pattern: allocating 8*nnz bytes per call costs more than the assembly
+    if (!pat->d_stage) CTX_CUDA(ctx, cudaMalloc(&pat->d_stage, sizeof(double) * std::max<int64_t>(pat->nnz, 1)));
+    double* d = pat->d_stage;
     int rc = FEELGPU_OK;
     cudaError_t err = cudaSuccess;
     if (accumulate) err = cudaMemcpyAsync(d, a_host, sizeof(double) * pat->nnz, cudaMemcpyHostToDevice, ctx->stream);
@@ -425,7 +427,6 @@ int feelgpu_form2_assemble_host(feelgpu_pattern_t pat, const feelgpu_form2_desc*
     if (err == cudaSuccess && rc == FEELGPU_OK)
         err = cudaMemcpyAsync(a_host, d, sizeof(double) * pat->nnz, cudaMemcpyDeviceToHost, ctx->stream);
     if (err == cudaSuccess) err = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d);
     if (err != cudaSuccess) {
         ctx->last_error = std::string("form2_assemble_host: ") + cudaGetErrorString(err);
         return FEELGPU_ERR_CUDA;

@@ -55,6 +55,7 @@ struct feelgpu_pattern_s {
     // inside row l2g_test[e][i] (component 0).  Full slot = ia[row + c1] + pos + c2 (components are interleaved:
     // global = ncomp*node + c, feeldiscr/doftable.hpp:1289-1299).
     uint16_t* d_pos = nullptr;   // [nElt][n][n]
+    double* d_stage = nullptr;   // [nnz] device staging of feelgpu_form2_assemble_host, allocated on first use
     RowPlan* plan = nullptr;
     std::string plan_note;       // why no owner-computes plan exists (if none)
     EPlan* eplan = nullptr;

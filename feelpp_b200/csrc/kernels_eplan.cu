@@ -80,7 +80,7 @@ __device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int n
 }
 
 template <int ORDER, int FORM, int NCOMP>   // FORM 0: mass, 1: stiffness; NCOMP components (block = value * Id)
-__global__ void __launch_bounds__(EPLAN_WARPS * 32, 2)
+__global__ void __launch_bounds__(EPLAN_WARPS * 32, EPLAN_MINB)
 k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, const uint32_t* __restrict__ visits,
         const uint2* __restrict__ chunks, const uint32_t* __restrict__ blob, const uint4* __restrict__ rows,
         const double* __restrict__ xyz, double* __restrict__ a, int accumulate, int vs, int omax, double cval)
@@ -90,6 +90,8 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     double* sS = sm;                          // [NSREC][vs]
     double* sX = sS + NSREC * vs;             // [3][EPLAN_VERTS]
     double* sO = sX + 3 * EPLAN_VERTS;        // [omax]: the CTA's row block; slot 0 = trash
+    uint2* sH = reinterpret_cast<uint2*>(sO + omax);   // [EPLAN_HDRS] chunk headers, then the chunk counter
+    int* sCnt = reinterpret_cast<int*>(sH + EPLAN_HDRS);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint4* cq = reinterpret_cast<const uint4*>(ctas + blockIdx.x);
     const uint4 c0 = __ldg(cq), c1 = __ldg(cq + 1);
@@ -125,8 +127,8 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     }
     // headers of this warp's chunks (warp, warp + W, ...: lane k holds the k-th) and its first batch of rows: the loads
     // are in flight while phase A runs
-    uint2 hdr = make_uint2(0u, 0u);
-    if (warp + EPLAN_WARPS * lane < nchunk) hdr = __ldg(&chunks[chunk_off + warp + EPLAN_WARPS * lane]);
+    if (tid < nchunk && tid < EPLAN_HDRS) sH[tid] = __ldg(&chunks[chunk_off + tid]);
+    if (tid == 0) *sCnt = EPLAN_WARPS;         // chunks 0..W-1 are the warps' first ones, the rest is handed out on demand
     uint4 rw = make_uint4(0u, 0u, 0u, 0u);     // row tid of the CTA's row table (EPLAN_ROWS <= blockDim.x)
     if (tid < nrows) rw = __ldg(&rows[row_off + tid]);
     uint4 vw0 = make_uint4(0u, 0u, 0u, 0u);    // visit record of this thread's first visit
@@ -233,19 +235,17 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     uint4* sR = reinterpret_cast<uint4*>(sX);
     if (tid < nrows) sR[tid] = rw;
 
-    // ---- phase B: task chunks, lane = task; the next chunk's first words and positions are fetched one chunk ahead ----
+    // ---- phase B: task chunks, lane = task.  Chunks are sorted by cost and handed out on demand (shared counter); the next
+    // chunk's header, first words and positions are fetched while the current one runs.
     {
         const uint32_t sSa = (uint32_t)__cvta_generic_to_shared(sS), sOa = (uint32_t)__cvta_generic_to_shared(sO);
-        const uint32_t vsb = (uint32_t)vs * 8u;
-        for (int cb = 0; cb < nchunk; cb += 32 * EPLAN_WARPS) {
-            if (cb) {
-                hdr = make_uint2(0u, 0u);
-                if (cb + warp + EPLAN_WARPS * lane < nchunk) hdr = __ldg(&chunks[chunk_off + cb + warp + EPLAN_WARPS * lane]);
-            }
-            const int mine = min(32, (nchunk - cb - warp + EPLAN_WARPS - 1) / EPLAN_WARPS);   // chunks of this warp in the batch
-            if (mine <= 0) break;
-            uint32_t q0 = __shfl_sync(0xffffffffu, hdr.x, 0), meta = __shfl_sync(0xffffffffu, hdr.y, 0);
-            const uint32_t* wp = blob + (size_t)q0 * 4 + lane;
+        const uint32_t vsb = (uint32_t)vs * 8u, sCa = (uint32_t)__cvta_generic_to_shared(sCnt);
+        auto header = [&](int c) { return c < EPLAN_HDRS ? sH[c] : __ldg(&chunks[chunk_off + c]); };
+        int c = warp;
+        if (c < nchunk) {
+            uint2 ch = header(c);
+            const uint32_t* wp = blob + (size_t)ch.x * 4 + lane;
+            uint32_t meta = ch.y;
             uint32_t w = __ldg(wp), w1 = __ldg(wp + 32);
             uint32_t pos[EPLAN_MAXOUT];
             {
@@ -253,14 +253,17 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
 #pragma unroll
                 for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = __ldg(op + o * 32);
             }
-            for (int k = 0; k < mine; ++k) {
+            while (true) {
                 const int type = meta & 0xFF, niter = (meta >> 8) & 0xFF;
                 const uint32_t* wpc = wp;
-                // the next chunk of this warp (the last one re-reads itself: harmless)
-                const int kn = min(k + 1, mine - 1);
-                q0 = __shfl_sync(0xffffffffu, hdr.x, kn);
-                meta = __shfl_sync(0xffffffffu, hdr.y, kn);
-                wp = blob + (size_t)q0 * 4 + lane;
+                int cn;   // next chunk: one shared-memory atomic by lane 0 (written out: the compiler's warp-aggregated form costs 20 instructions)
+                asm volatile("{ .reg .pred p; setp.eq.u32 p, %1, 0; mov.u32 %0, 0; @p atom.shared.inc.u32 %0, [%2], 0x7fffffff; }"
+                             : "=r"(cn) : "r"(lane), "r"(sCa) : "memory");
+                cn = __shfl_sync(0xffffffffu, cn, 0);
+                const bool more = cn < nchunk;
+                ch = header(more ? cn : c);                  // past the end: re-read the current chunk (harmless)
+                wp = blob + (size_t)ch.x * 4 + lane;
+                meta = ch.y;
                 const uint32_t nw = __ldg(wp), nw1 = __ldg(wp + 32);
                 uint32_t npos[EPLAN_MAXOUT];
                 {
@@ -275,6 +278,8 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
                 case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
                 default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
                 }
+                if (!more) break;
+                c = cn;
                 w = nw;
                 w1 = nw1;
 #pragma unroll
@@ -320,7 +325,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
 size_t eplan_smem_bytes(const EPlan* p, int form)
 {
     const int nsrec = form == 1 ? 10 : 1;
-    return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax);
+    return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax) + EPLAN_HDRS * sizeof(uint2) + 16;
 }
 
 template <typename T>

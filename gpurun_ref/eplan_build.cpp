@@ -1,0 +1,765 @@
+// eplan_build.cpp -- host-side construction of the entity-task plan (see eplan.h).
+#include "eplan.h"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+
+namespace {
+
+// local entity numbering of the reference tetrahedron (feelmesh/simplexordering.hpp:283-291)
+const int E2P[6][2] = {{1, 2}, {2, 0}, {0, 1}, {0, 3}, {1, 3}, {2, 3}};
+
+inline int edge_of(int a, int b)
+{
+    for (int e = 0; e < 6; ++e)
+        if ((E2P[e][0] == a && E2P[e][1] == b) || (E2P[e][0] == b && E2P[e][1] == a)) return e;
+    return -1;
+}
+
+const EPlanSpec SPEC_P1 = {1, 4, 2,
+                           {{1, 1, 1, {{0, 0}}, 1, {0}, 0},
+                            {1, 2, 1, {{0, 1}}, 1, {1}, 0}}};
+// P2 local dofs: vertices 0-3, edge dofs 4+e; re-labelled edges used below: (0,1) -> e2 -> dof 6, (1,2) -> e0 -> dof 4,
+// (2,0) -> e1 -> dof 5, (2,3) -> e5 -> dof 9
+const EPlanSpec SPEC_P2 = {2, 10, 6,
+                           {{1, 1, 1, {{0, 0}}, 1, {0}, 0},
+                            {1, 2, 2, {{0, 0}, {0, 1}}, 2, {1, 6}, 0},
+                            {1, 3, 2, {{0, 1}, {0, 2}}, 1, {4}, 0},
+                            {2, 2, 3, {{0, 0}, {0, 1}, {1, 1}}, 3, {0, 1, 6}, 6},
+                            {2, 3, 5, {{0, 0}, {0, 1}, {0, 2}, {1, 1}, {1, 2}}, 3, {2, 5, 4}, 6},
+                            {2, 4, 4, {{0, 2}, {0, 3}, {1, 2}, {1, 3}}, 1, {9}, 6, 1}}};
+
+// position of the grid point (x,y,z), 10 bits each, along the 3-D Hilbert curve (Skilling's transpose algorithm): consecutive
+// curve positions are face-adjacent cells, so a run of rows is a compact patch (a Morton run can jump across the domain)
+inline uint32_t hilbert3(uint32_t x, uint32_t y, uint32_t z)
+{
+    uint32_t X[3] = {x & 0x3FF, y & 0x3FF, z & 0x3FF};
+    const uint32_t M = 1u << 9;
+    for (uint32_t Q = M; Q > 1; Q >>= 1) {       // inverse undo
+        const uint32_t P = Q - 1;
+        for (int i = 0; i < 3; ++i) {
+            if (X[i] & Q) X[0] ^= P;
+            else { const uint32_t t = (X[0] ^ X[i]) & P; X[0] ^= t; X[i] ^= t; }
+        }
+    }
+    for (int i = 1; i < 3; ++i) X[i] ^= X[i - 1];   // Gray encode
+    uint32_t t = 0;
+    for (uint32_t Q = M; Q > 1; Q >>= 1)
+        if (X[2] & Q) t ^= Q - 1;
+    for (int i = 0; i < 3; ++i) X[i] ^= t;
+    uint32_t h = 0;                                  // interleave, X[0] most significant
+    for (int b = 9; b >= 0; --b)
+        for (int i = 0; i < 3; ++i) h = (h << 1) | ((X[i] >> b) & 1);
+    return h;
+}
+
+inline uint32_t spread3(uint32_t x)
+{
+    x &= 0x3FF;
+    x = (x | (x << 16)) & 0x30000FF;
+    x = (x | (x << 8)) & 0x300F00F;
+    x = (x | (x << 4)) & 0x30C30C3;
+    x = (x | (x << 2)) & 0x9249249;
+    return x;
+}
+
+struct Entry {                      // one (task, element) incidence of a row
+    uint32_t type;
+    int32_t k1, k2;                 // global vertex ids completing sigma (ascending), -1 if unused
+    int64_t q;                      // unit index (element, local dof)
+    uint8_t p[4];                   // re-labelling: new local vertex k = original local vertex p[k]
+    bool operator<(const Entry& o) const
+    {
+        if (type != o.type) return type < o.type;
+        if (k1 != o.k1) return k1 < o.k1;
+        if (k2 != o.k2) return k2 < o.k2;
+        return q < o.q;
+    }
+};
+
+struct Task {
+    uint8_t type;
+    uint16_t niter;
+    uint32_t first;                 // into the per-CTA iteration word array
+    uint16_t out[EPLAN_MAXOUT];
+    uint8_t aux;                    // tasks done in phase A: original local edge of the row dof
+};
+
+struct CtaSeg {
+    int64_t nb, ne;                 // node range along the curve
+    uint32_t vert_off, visit_off;
+    uint16_t nverts, nvisit;
+    uint32_t nout;
+};
+
+struct Local {                      // per-thread output, concatenated at the end
+    std::vector<EPlanChunk> chunks;
+    std::vector<uint32_t> blob;
+    std::vector<EPlanRow> rows;
+    struct PerCta { uint32_t chunk0, nchunk, row0, nrows, q0, nq, needzero; };
+    std::vector<PerCta> per;
+    int64_t ntasks = 0, niters = 0, niters_padded = 0;
+    double wf = 0, wf_ideal = 0;
+    std::string error;
+};
+
+struct Builder {
+    const EPlanSpec* spec;
+    int order, ncomp, n, nd;
+    int64_t nElt, nNode;
+    const int32_t* l2g;
+    const double* xyz;
+    const int32_t* conn;
+    const int64_t* ia;
+    const uint16_t* pos;
+    std::vector<int64_t> nptr;      // node -> units
+    std::vector<int32_t> uelt;
+    std::vector<uint8_t> uloc;
+    std::vector<uint16_t> uvis;     // visit slot of every unit inside its CTA
+    std::vector<int32_t> order_;    // nodes along the curve
+    bool use_hilbert = true;
+
+    inline int64_t node_of(int64_t e, int i) const { return l2g[e * nd + i] / ncomp; }
+    inline int row_len(int64_t node) const { return (int)((ia[node * ncomp + 1] - ia[node * ncomp]) / ncomp); }
+
+    void node_units()
+    {
+        nptr.assign(nNode + 1, 0);
+        for (int64_t e = 0; e < nElt; ++e)
+            for (int i = 0; i < n; ++i) nptr[node_of(e, i) + 1]++;
+        for (int64_t k = 0; k < nNode; ++k) nptr[k + 1] += nptr[k];
+        uelt.resize(nptr[nNode]);
+        uloc.resize(nptr[nNode]);
+        std::vector<int64_t> cur(nptr.begin(), nptr.end() - 1);
+        for (int64_t e = 0; e < nElt; ++e)          // ascending e: every task sums its elements in mesh order
+            for (int i = 0; i < n; ++i) {
+                int64_t q = cur[node_of(e, i)]++;
+                uelt[q] = (int32_t)e;
+                uloc[q] = (uint8_t)i;
+            }
+    }
+
+    void curve_order()
+    {
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (int64_t e = 0; e < nElt; ++e)
+            for (int a = 0; a < 4; ++a)
+                for (int c = 0; c < 3; ++c) {
+                    double x = xyz[3 * (int64_t)conn[4 * e + a] + c];
+                    lo[c] = std::min(lo[c], x);
+                    hi[c] = std::max(hi[c], x);
+                }
+        double sc[3];
+        for (int c = 0; c < 3; ++c) sc[c] = hi[c] > lo[c] ? 1023.999 / (hi[c] - lo[c]) : 0.0;
+        std::vector<uint64_t> key(nNode);
+        for (int64_t k = 0; k < nNode; ++k) {
+            if (nptr[k] == nptr[k + 1]) { key[k] = ((uint64_t)0x3FFFFFFF << 32) | (uint32_t)k; continue; }
+            const int64_t e = uelt[nptr[k]];
+            const int i = uloc[nptr[k]];
+            int v[2], nv = 1;
+            if (i < 4) v[0] = i;
+            else { v[0] = E2P[i - 4][0]; v[1] = E2P[i - 4][1]; nv = 2; }
+            double p[3] = {0, 0, 0};
+            for (int a = 0; a < nv; ++a)
+                for (int c = 0; c < 3; ++c) p[c] += xyz[3 * (int64_t)conn[4 * e + v[a]] + c];
+            uint32_t m = 0;
+            if (use_hilbert)
+                m = hilbert3((uint32_t)((p[0] / nv - lo[0]) * sc[0]), (uint32_t)((p[1] / nv - lo[1]) * sc[1]),
+                             (uint32_t)((p[2] / nv - lo[2]) * sc[2]));
+            else
+                for (int c = 0; c < 3; ++c) m |= spread3((uint32_t)((p[c] / nv - lo[c]) * sc[c])) << c;
+            key[k] = ((uint64_t)m << 32) | (uint32_t)k;
+        }
+        std::sort(key.begin(), key.end());
+        order_.resize(nNode);
+        for (int64_t k = 0; k < nNode; ++k) order_[k] = (int32_t)(key[k] & 0xFFFFFFFFu);
+    }
+
+    // entries of one unit (row node, element e, local dof i)
+    void unit_entries(int64_t q, std::vector<Entry>& out) const
+    {
+        const int64_t e = uelt[q];
+        const int i = uloc[q];
+        const int32_t* c = conn + 4 * e;
+        Entry en;
+        en.q = q;
+        if (i < 4) {
+            int o[3], no = 0;
+            for (int v = 0; v < 4; ++v)
+                if (v != i) o[no++] = v;
+            std::sort(o, o + 3, [&](int a, int b) { return c[a] < c[b]; });
+            en.type = 0; en.k1 = en.k2 = -1;
+            en.p[0] = (uint8_t)i; en.p[1] = (uint8_t)o[0]; en.p[2] = (uint8_t)o[1]; en.p[3] = (uint8_t)o[2];
+            out.push_back(en);
+            for (int b = 0; b < 3; ++b) {                       // (1,2): sigma = {v, o[b]}
+                en.type = 1; en.k1 = c[o[b]]; en.k2 = -1;
+                en.p[1] = (uint8_t)o[b];
+                int r = 2;
+                for (int x = 0; x < 3; ++x)
+                    if (x != b) en.p[r++] = (uint8_t)o[x];
+                out.push_back(en);
+            }
+            if (spec->ntypes > 2)
+                for (int d = 0; d < 3; ++d) {                   // (1,3): sigma = {v} U (o minus o[d])
+                    int b0 = d == 0 ? 1 : 0, b1 = d == 2 ? 1 : 2;
+                    en.type = 2; en.k1 = c[o[b0]]; en.k2 = c[o[b1]];
+                    en.p[1] = (uint8_t)o[b0]; en.p[2] = (uint8_t)o[b1]; en.p[3] = (uint8_t)o[d];
+                    out.push_back(en);
+                }
+        } else {
+            int r0 = E2P[i - 4][0], r1 = E2P[i - 4][1];
+            if (c[r0] > c[r1]) std::swap(r0, r1);
+            int o[2], no = 0;
+            for (int v = 0; v < 4; ++v)
+                if (v != r0 && v != r1) o[no++] = v;
+            if (c[o[0]] > c[o[1]]) std::swap(o[0], o[1]);
+            en.p[0] = (uint8_t)r0; en.p[1] = (uint8_t)r1;
+            en.type = 3; en.k1 = en.k2 = -1; en.p[2] = (uint8_t)o[0]; en.p[3] = (uint8_t)o[1];
+            out.push_back(en);
+            en.type = 4; en.k1 = c[o[0]];
+            out.push_back(en);
+            en.k1 = c[o[1]]; en.p[2] = (uint8_t)o[1]; en.p[3] = (uint8_t)o[0];
+            out.push_back(en);
+            en.type = 5; en.k1 = c[o[0]]; en.k2 = c[o[1]]; en.p[2] = (uint8_t)o[0]; en.p[3] = (uint8_t)o[1];
+            out.push_back(en);
+        }
+    }
+
+    // original local dof of the re-labelled local dof d under the re-labelling p
+    inline int orig_dof(int d, const uint8_t* p) const
+    {
+        if (d < 4) return p[d];
+        const int e = d - 4;
+        return 4 + edge_of(p[E2P[e][0]], p[E2P[e][1]]);
+    }
+};
+
+// modelled shared-memory wavefronts of one chunk's S loads: per iteration, per load, per half-warp the conflict degree
+// is the largest number of distinct addresses that fall into one 8-byte bank pair (bank pair = visit slot mod 16)
+void model_chunk(const EPlanType& T, const std::vector<uint32_t>& words, int niter, double& wf, double& ideal)
+{
+    for (int t = 0; t < niter; ++t)
+        for (int k = 0; k < T.nld; ++k)
+            for (int half = 0; half < 2; ++half) {
+                uint32_t seen[16][16];
+                int cnt[16];
+                for (int b = 0; b < 16; ++b) cnt[b] = 0;
+                for (int l = half * 16; l < half * 16 + 16; ++l) {
+                    const uint32_t w = words[(size_t)t * 32 + l];
+                    const uint32_t slot = w & 0x3FF, idx = (w >> (10 + 4 * k)) & 15;
+                    const uint32_t addr = idx * EPLAN_VS + slot, b = slot & 15;
+                    bool dup = false;
+                    for (int s = 0; s < cnt[b]; ++s)
+                        if (seen[b][s] == addr) dup = true;
+                    if (!dup) seen[b][cnt[b]++] = addr;
+                }
+                int deg = 1;
+                for (int b = 0; b < 16; ++b) deg = std::max(deg, cnt[b]);
+                wf += deg;
+                ideal += 1;
+            }
+}
+
+} // namespace
+
+const EPlanSpec* eplan_spec(int order)
+{
+    if (order == 1) return &SPEC_P1;
+    if (order == 2) return &SPEC_P2;
+    return nullptr;
+}
+
+bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_t* l2g, int nd, int64_t nPts,
+                      const double* xyz, const int32_t* conn, int64_t nRows, const int64_t* ia, const uint16_t* pos,
+                      int nthreads, EPlanHost& plan)
+{
+    Builder B;
+    B.spec = eplan_spec(order);
+    if (!B.spec) { plan.error = "entity plan: order not covered"; return false; }
+    B.order = order;
+    B.ncomp = ncomp;
+    B.n = B.spec->n;
+    B.nd = nd;
+    B.nElt = nElt;
+    B.nNode = nRows / ncomp;
+    B.l2g = l2g;
+    B.xyz = xyz;
+    B.conn = conn;
+    B.ia = ia;
+    B.pos = pos;
+    if (nRows % ncomp) { plan.error = "entity plan: rows not a multiple of ncomp"; return false; }
+    if (omax < 512 || omax > 32767) { plan.error = "entity plan: bad out-buffer size"; return false; }
+    for (int64_t e = 0; e < nElt; ++e) {
+        for (int i = 0; i < B.n; ++i)
+            if (l2g[e * nd + i] >= nRows) { plan.error = "entity plan: a test dof has no CSR row"; return false; }
+        for (int a = 0; a < 4; ++a)
+            for (int b = a + 1; b < 4; ++b)
+                if (conn[4 * e + a] == conn[4 * e + b]) { plan.error = "entity plan: degenerate element"; return false; }
+    }
+    B.node_units();
+    if (const char* cv = std::getenv("FEELGPU_EPLAN_CURVE")) B.use_hilbert = std::strcmp(cv, "morton") != 0;
+    B.curve_order();
+    if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
+    nthreads = std::min(nthreads, 64);
+
+    // ---- CTA packing along the curve: consecutive rows while visits, unique vertices and outputs fit ----
+    std::vector<CtaSeg> segs;
+    B.uvis.resize(B.uelt.size());
+    plan.verts.clear();
+    plan.visits.clear();
+    const int vstride = order == 2 ? 4 : 1;   // words per visit: vertex bytes [+ 6 u16 row-block slots of the tet-type outputs]
+    {
+        std::vector<int32_t> estamp(nElt, -1), eslot(nElt, 0), pstamp(nPts, -1), pslot(nPts, 0), newpts;
+        int64_t k = 0;
+        while (k < B.nNode) {
+            CtaSeg sg;
+            sg.nb = k;
+            sg.vert_off = (uint32_t)plan.verts.size();
+            sg.visit_off = (uint32_t)plan.visits.size();
+            const int32_t id = (int32_t)segs.size();
+            uint32_t nv = 0, np = 0, nout = 1;      // slot 0 of the out buffer is the trash cell
+            int64_t rows = 0;
+            for (; k < B.nNode; ++k) {
+                const int64_t node = B.order_[k];
+                uint32_t addv = 0, addp = 0;
+                newpts.clear();
+                for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) {
+                    const int32_t e = B.uelt[q];
+                    if (estamp[e] != id) {
+                        ++addv;
+                        for (int a = 0; a < 4; ++a) {
+                            const int32_t pt = conn[4 * e + a];
+                            if (pstamp[pt] != id && std::find(newpts.begin(), newpts.end(), pt) == newpts.end()) newpts.push_back(pt);
+                        }
+                    }
+                }
+                addp = (uint32_t)newpts.size();
+                const uint32_t len = (uint32_t)B.row_len(node);
+                if (rows > 0 && (nv + addv > EPLAN_VS - 1 || np + addp > EPLAN_VERTS || nout + len > (uint32_t)omax ||
+                                 rows >= EPLAN_ROWS))
+                    break;
+                if (addv > EPLAN_VS - 1 || addp > EPLAN_VERTS || 1 + len > (uint32_t)omax) {
+                    plan.error = "entity plan: a single row exceeds the CTA limits (elements around a node / row length)";
+                    return false;
+                }
+                for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) {
+                    const int32_t e = B.uelt[q];
+                    if (estamp[e] != id) {
+                        estamp[e] = id;
+                        eslot[e] = (int32_t)nv++;
+                        uint32_t w = 0;
+                        for (int a = 0; a < 4; ++a) {
+                            const int32_t pt = conn[4 * e + a];
+                            if (pstamp[pt] != id) {
+                                pstamp[pt] = id;
+                                pslot[pt] = (int32_t)np++;
+                                plan.verts.push_back(pt);
+                            }
+                            w |= (uint32_t)pslot[pt] << (8 * a);
+                        }
+                        plan.visits.push_back(w);
+                        for (int z = 1; z < vstride; ++z) plan.visits.push_back(0u);   // filled per CTA below
+                    }
+                    B.uvis[q] = (uint16_t)eslot[e];
+                }
+                nout += len;
+                ++rows;
+            }
+            sg.ne = k;
+            sg.nverts = (uint16_t)np;
+            sg.nvisit = (uint16_t)nv;
+            sg.nout = nout;
+            segs.push_back(sg);
+        }
+    }
+
+    // ---- tasks and chunks, in parallel over CTAs ----
+    const int64_t nCta = (int64_t)segs.size();
+    const EPlanSpec& S = *B.spec;
+    std::vector<Local> locals(nthreads);
+    auto work = [&](int t) {
+        Local& L = locals[t];
+        std::vector<Entry> ent;
+        std::vector<Task> tasks[EPLAN_MAXTYPES];
+        std::vector<uint32_t> iterw;          // iteration words of the CTA's tasks
+        std::vector<uint32_t> cw;             // one chunk's words
+        std::vector<uint8_t> bankcnt;
+        uint8_t outcnt[EPLAN_MAXOUT * 16];
+        std::vector<uint8_t> covered;
+        std::vector<uint32_t> usage, sorted, perm, vtmp;
+        std::vector<int32_t> cnodes;
+        std::vector<uint32_t> cell[256];      // tasks with <= 2 elements by (bank pair of element 0, of element 1)
+        std::vector<uint32_t> cell1[16];
+        int cnt2[32];
+        std::vector<uint32_t> pool, lanes;    // remaining tasks of a type; tasks of every chunk lane
+        struct ChunkTmp { uint8_t type, niter; uint32_t first, count; int cost; };
+        std::vector<ChunkTmp> ctmp, dealt;
+        for (int64_t c = nCta * t / nthreads; c < nCta * (t + 1) / nthreads; ++c) {
+            const CtaSeg& sg = segs[c];
+            for (int ty = 0; ty < S.ntypes; ++ty) tasks[ty].clear();
+            iterw.clear();
+            Local::PerCta pc;
+            pc.row0 = (uint32_t)L.rows.size();
+            uint32_t rowoff = 1;
+            // rows in CSR order: neighbours in memory are neighbours in the row block, and runs of them are written as one
+            // segment (scalar spaces; pieces of <= 256 values so that the warps share long runs)
+            cnodes.assign(B.order_.begin() + sg.nb, B.order_.begin() + sg.ne);
+            std::sort(cnodes.begin(), cnodes.end(), [&](int32_t x, int32_t y) { return B.ia[(int64_t)x * B.ncomp] < B.ia[(int64_t)y * B.ncomp]; });
+            for (size_t k = 0; k < cnodes.size(); ++k) {
+                const int64_t node = cnodes[k];
+                const uint32_t len = (uint32_t)B.row_len(node);
+                EPlanRow row;
+                row.base = B.ia[node * B.ncomp];
+                row.off = rowoff;
+                row.len = len;
+                if (B.ncomp == 1 && L.rows.size() > pc.row0 && L.rows.back().base + (int64_t)L.rows.back().len == row.base &&
+                    L.rows.back().len + len <= 256)
+                    L.rows.back().len += len;
+                else
+                    L.rows.push_back(row);
+                ent.clear();
+                for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) B.unit_entries(q, ent);
+                std::sort(ent.begin(), ent.end());
+                size_t g0 = 0;
+                while (g0 < ent.size()) {
+                    size_t g1 = g0 + 1;
+                    while (g1 < ent.size() && ent[g1].type == ent[g0].type && ent[g1].k1 == ent[g0].k1 && ent[g1].k2 == ent[g0].k2) ++g1;
+                    const EPlanType& T = S.type[ent[g0].type];
+                    Task tk;
+                    tk.type = (uint8_t)ent[g0].type;
+                    tk.niter = (uint16_t)(g1 - g0);
+                    tk.first = (uint32_t)iterw.size();
+                    for (int o = 0; o < EPLAN_MAXOUT; ++o) tk.out[o] = 0;
+                    tk.aux = (uint8_t)(B.uloc[ent[g0].q] >= 4 ? B.uloc[ent[g0].q] - 4 : 0);
+                    if (g1 - g0 > 255) { L.error = "entity plan: more than 255 elements around an entity"; return; }
+                    for (size_t g = g0; g < g1; ++g) {
+                        const Entry& en = ent[g];
+                        const int64_t e = B.uelt[en.q];
+                        const int i = B.uloc[en.q];
+                        uint32_t w = B.uvis[en.q];
+                        for (int kk = 0; kk < T.nld; ++kk)
+                            w |= (uint32_t)eplan_sidx(en.p[T.ld[kk][0]], en.p[T.ld[kk][1]]) << (10 + 4 * kk);
+                        iterw.push_back(w);
+                        if (B.orig_dof(T.rowdof, en.p) != i) { L.error = "entity plan: re-labelling does not map the row dof"; return; }
+                        for (int o = 0; o < T.nout; ++o) {
+                            const int j = B.orig_dof(T.outdof[o], en.p);
+                            const uint32_t p = B.pos[(e * B.n + i) * B.n + j] / (uint32_t)B.ncomp;
+                            if (p >= len) { L.error = "entity plan: position outside the row"; return; }
+                            const uint16_t slot = (uint16_t)(rowoff + p);
+                            if (g == g0) tk.out[o] = slot;
+                            else if (tk.out[o] != slot) { L.error = "entity plan: elements of one task disagree on an output column"; return; }
+                        }
+                    }
+                    tasks[tk.type].push_back(tk);
+                    g0 = g1;
+                }
+                rowoff += len;
+            }
+            pc.nrows = (uint32_t)L.rows.size() - pc.row0;
+            // ---- renumber the visit slots: every half-warp wants 16 distinct bank pairs (slot mod 16) per iteration, which
+            // needs the load-weighted use of the 16 residues to be level: deal the slots, most used first, in snake order
+            {
+                const uint32_t nv = sg.nvisit;
+                usage.assign(nv, 0);
+                for (int ty = 0; ty < S.ntypes; ++ty)
+                    for (const Task& tk : tasks[ty])
+                        for (int it = 0; it < tk.niter; ++it)
+                            usage[iterw[tk.first + it] & 0x3FF] += (uint32_t)(S.type[ty].phaseA ? 0 : S.type[ty].nld);
+                sorted.resize(nv);
+                for (uint32_t v = 0; v < nv; ++v) sorted[v] = v;
+                std::stable_sort(sorted.begin(), sorted.end(), [&](uint32_t x, uint32_t y) { return usage[x] > usage[y]; });
+                perm.resize(nv);
+                const uint32_t full = nv / 16 * 16;
+                for (uint32_t i2 = 0; i2 < nv; ++i2) {
+                    const uint32_t g = i2 / 16, j = i2 % 16;
+                    perm[sorted[i2]] = (i2 < full && (g & 1)) ? g * 16 + 15 - j : i2;
+                }
+                for (uint32_t& w : iterw) w = (w & ~0x3FFu) | perm[w & 0x3FF];
+                uint32_t* vw = plan.visits.data() + sg.visit_off;      // this CTA's segment: no other thread touches it
+                vtmp.assign(vw, vw + (size_t)nv * vstride);
+                for (uint32_t v = 0; v < nv; ++v)
+                    for (int z = 0; z < vstride; ++z) vw[(size_t)perm[v] * vstride + z] = vtmp[(size_t)v * vstride + z];
+                // outputs whose simplex is the whole tet have one contribution: the thread that computes the element's S in
+                // phase A stores them straight into the row block (slot per original local edge of the row; 0 = not ours)
+                for (int ty = 0; ty < S.ntypes; ++ty) {
+                    if (!S.type[ty].phaseA) continue;
+                    for (const Task& tk : tasks[ty]) {
+                        const uint32_t slot = iterw[tk.first] & 0x3FF;
+                        vw[(size_t)slot * vstride + 1 + tk.aux / 2] |= (uint32_t)tk.out[0] << (16 * (tk.aux & 1));
+                    }
+                }
+            }
+            // ---- chunks: 32 tasks of one type, longest first ----
+            // All S loads of one iteration hit the bank pair (visit slot mod 16); a half-warp is served in one pass only
+            // if its 16 lanes hit distinct bank pairs.  Which tasks share a half-warp and the order in which a task walks
+            // its elements are both free (the latter only fixes the summation order): lanes are filled one by one with the
+            // candidate (from a window of the remaining tasks) whose greedy element order adds the fewest bank conflicts.
+            ctmp.clear();
+            lanes.clear();
+            for (int ty = 0; ty < S.ntypes; ++ty) {
+                std::vector<Task>& tv = tasks[ty];
+                L.ntasks += (int64_t)tv.size();
+                if (S.type[ty].phaseA) continue;
+                std::stable_sort(tv.begin(), tv.end(), [](const Task& a, const Task& b) { return a.niter > b.niter; });
+                const int nto = S.type[ty].nout;
+                size_t nlong = 0;
+                while (nlong < tv.size() && tv[nlong].niter > 2) ++nlong;
+                // ---- tasks with 3 or more elements: window search ----
+                pool.resize(nlong);
+                for (size_t k = 0; k < nlong; ++k) pool[k] = (uint32_t)k;
+                size_t head = 0;
+                while (head < pool.size()) {
+                    ChunkTmp ch;
+                    ch.type = (uint8_t)ty;
+                    {   // the window below displaces tasks by up to 40 places: bring the longest of them to the front
+                        size_t mx = head;
+                        for (size_t c = head + 1; c < std::min(pool.size(), head + 128); ++c)
+                            if (tv[pool[c]].niter > tv[pool[mx]].niter) mx = c;
+                        std::swap(pool[head], pool[mx]);
+                    }
+                    ch.niter = (uint8_t)tv[pool[head]].niter;
+                    ch.first = (uint32_t)lanes.size();
+                    ch.count = 0;
+                    ch.cost = ch.niter * (S.type[ty].nld + 2) + 4 * nto + 8;
+                    for (int l = 0; l < 32 && head < pool.size(); ++l) {
+                        if ((l & 15) == 0) {
+                            bankcnt.assign((size_t)ch.niter * 16, 0);
+                            for (int z = 0; z < EPLAN_MAXOUT * 16; ++z) outcnt[z] = 0;
+                        }
+                        const int hl = l & 15;
+                        size_t K = l == 0 ? 1 : 8 + 4 * hl;
+                        K = std::min(K, pool.size() - head);
+                        size_t best = head;
+                        int bestcost = 1 << 30;
+                        for (size_t c = head; c < head + K; ++c) {
+                            const Task& tk = tv[pool[c]];
+                            const int nt = tk.niter;
+                            if (nt > ch.niter) continue;
+                            const uint32_t* src = &iterw[tk.first];
+                            int cost = 0;
+                            uint8_t res[256];
+                            for (int j = 0; j < nt; ++j) res[j] = (uint8_t)(src[j] & 15);
+                            for (int it = 0; it < nt; ++it) {
+                                int bj = it;
+                                uint8_t bc = 255;
+                                for (int j = it; j < nt; ++j) {
+                                    const uint8_t c2 = bankcnt[(size_t)it * 16 + res[j]];
+                                    if (c2 < bc) { bc = c2; bj = j; if (!c2) break; }
+                                }
+                                std::swap(res[it], res[bj]);
+                                cost += bc * S.type[ty].nld;
+                            }
+                            for (int o = 0; o < nto; ++o) cost += outcnt[o * 16 + (tk.out[o] & 15)];   // stores into the row block
+                            if (cost < bestcost) { bestcost = cost; best = c; if (!cost) break; }
+                        }
+                        std::swap(pool[head], pool[best]);
+                        // commit: greedy element order of the chosen task
+                        const Task& tk = tv[pool[head]];
+                        const int nt = tk.niter;
+                        uint32_t* src = &iterw[tk.first];
+                        for (int it = 0; it < nt; ++it) {
+                            int bj = it;
+                            uint8_t bc = 255;
+                            for (int j = it; j < nt; ++j) {
+                                const uint8_t c2 = bankcnt[(size_t)it * 16 + (src[j] & 15)];
+                                if (c2 < bc) { bc = c2; bj = j; if (!c2) break; }
+                            }
+                            std::swap(src[it], src[bj]);
+                            bankcnt[(size_t)it * 16 + (src[it] & 15)]++;
+                        }
+                        for (int o = 0; o < nto; ++o) outcnt[o * 16 + (tk.out[o] & 15)]++;
+                        lanes.push_back(pool[head]);
+                        ++head;
+                        ++ch.count;
+                    }
+                    ctmp.push_back(ch);
+                }
+                // ---- tasks with two elements, then with one: buckets by bank pair.  A lane takes a task whose bank pairs
+                // are still free in both iterations of its half-warp (the order of the two elements is chosen to fit).
+                {
+                    for (auto& cvec : cell) cvec.clear();
+                    for (auto& cvec : cell1) cvec.clear();
+                    size_t rem2 = 0, rem1 = 0;
+                    for (size_t k = nlong; k < tv.size(); ++k) {
+                        const uint32_t* src = &iterw[tv[k].first];
+                        const int r0 = src[0] & 15;
+                        if (tv[k].niter == 2) {
+                            const int r1 = src[1] & 15;
+                            cell[std::min(r0, r1) * 16 + std::max(r0, r1)].push_back((uint32_t)k);
+                            ++rem2;
+                        } else {
+                            cell1[r0].push_back((uint32_t)k);
+                            ++rem1;
+                        }
+                    }
+                    while (rem2 + rem1) {
+                        const int cn = rem2 ? 2 : 1;                 // a chunk of two-element tasks is topped up with one-element tasks
+                        ChunkTmp ch;
+                        ch.type = (uint8_t)ty;
+                        ch.niter = (uint8_t)cn;
+                        ch.first = (uint32_t)lanes.size();
+                        ch.count = 0;
+                        ch.cost = cn * (S.type[ty].nld + 2) + 4 * nto + 8;
+                        for (int l = 0; l < 32 && rem2 + rem1; ++l) {
+                            if ((l & 15) == 0) {
+                                for (int z = 0; z < 32; ++z) cnt2[z] = 0;
+                                for (int z = 0; z < EPLAN_MAXOUT * 16; ++z) outcnt[z] = 0;
+                            }
+                            const int nt = rem2 ? 2 : 1;
+                            // best cell: fewest S-load conflicts, then the fullest (keeps the buckets level)
+                            int ba = 0, bb = 0, bcost = 1 << 30;
+                            size_t bsize = 0;
+                            std::vector<uint32_t>* bcv = nullptr;
+                            if (nt == 2) {
+                                for (int a2 = 0; a2 < 16; ++a2)      // a2: bank pair of iteration 0, b2: of iteration 1
+                                    for (int b2 = 0; b2 < 16; ++b2) {
+                                        std::vector<uint32_t>& cv2 = cell[std::min(a2, b2) * 16 + std::max(a2, b2)];
+                                        const size_t sz = cv2.size();
+                                        if (!sz) continue;
+                                        const int cost = cnt2[a2] + cnt2[16 + b2];
+                                        if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bcv = &cv2; ba = a2; bb = b2; }
+                                    }
+                            } else {
+                                for (int a2 = 0; a2 < 16; ++a2) {
+                                    const size_t sz = cell1[a2].size();
+                                    if (!sz) continue;
+                                    const int cost = cnt2[a2];
+                                    if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bcv = &cell1[a2]; ba = a2; }
+                                }
+                            }
+                            // inside the cell: the task whose stores into the row block collide the least
+                            std::vector<uint32_t>& cv = *bcv;
+                            size_t bk = 0;
+                            int bo = 1 << 30;
+                            for (size_t k = 0; k < cv.size() && k < 12; ++k) {
+                                int oc = 0;
+                                for (int o = 0; o < nto; ++o) oc += outcnt[o * 16 + (tv[cv[k]].out[o] & 15)];
+                                if (oc < bo) { bo = oc; bk = k; if (!oc) break; }
+                            }
+                            const uint32_t ti = cv[bk];
+                            cv[bk] = cv.back();
+                            cv.pop_back();
+                            if (nt == 2) --rem2; else --rem1;
+                            const Task& tk = tv[ti];
+                            uint32_t* src = &iterw[tk.first];
+                            if (nt == 2 && (int)(src[0] & 15) != ba) std::swap(src[0], src[1]);
+                            cnt2[ba]++;
+                            if (nt == 2) cnt2[16 + bb]++;
+                            for (int o = 0; o < nto; ++o) outcnt[o * 16 + (tk.out[o] & 15)]++;
+                            lanes.push_back(ti);
+                            ++ch.count;
+                        }
+                        ctmp.push_back(ch);
+                    }
+                }
+            }
+            std::stable_sort(ctmp.begin(), ctmp.end(), [](const ChunkTmp& a, const ChunkTmp& b) { return a.cost > b.cost; });
+            {   // warp w runs the chunks w, w + W, ...: deal the sorted chunks in snake order so that the warps' loads even out
+                const size_t W = EPLAN_WARPS, full = ctmp.size() / W * W;
+                dealt = ctmp;
+                for (size_t s2 = 0; s2 < full; ++s2) {
+                    const size_t round = s2 / W, j = s2 % W;
+                    dealt[round * W + ((round & 1) ? W - 1 - j : j)] = ctmp[s2];
+                }
+                ctmp.swap(dealt);
+            }
+            // does every slot of the row block receive a value?  (always, unless the graph holds entries no element produces)
+            covered.assign(sg.nout, 0);
+            for (int ty = 0; ty < S.ntypes; ++ty)
+                for (const Task& tk : tasks[ty])
+                    for (int o = 0; o < S.type[ty].nout; ++o) covered[tk.out[o]] = 1;
+            pc.needzero = 0;
+            for (uint32_t z = 1; z < sg.nout; ++z)
+                if (!covered[z]) pc.needzero = 1;
+            pc.chunk0 = (uint32_t)L.chunks.size();
+            pc.q0 = (uint32_t)(L.blob.size() / 4);
+            for (const ChunkTmp& ch : ctmp) {
+                const EPlanType& T = S.type[ch.type];
+                const std::vector<Task>& tv = tasks[ch.type];
+                cw.assign((size_t)ch.niter * 32, (uint32_t)(EPLAN_VS - 1));   // padding: the all-zero visit record
+                for (uint32_t l = 0; l < ch.count; ++l) {
+                    const Task& tk = tv[lanes[ch.first + l]];
+                    for (int it = 0; it < tk.niter; ++it) cw[(size_t)it * 32 + l] = iterw[tk.first + it];
+                    L.niters += tk.niter;
+                }
+                L.niters_padded += (int64_t)ch.niter * 32;
+                model_chunk(T, cw, ch.niter, L.wf, L.wf_ideal);
+                EPlanChunk hc;
+                hc.q0 = (uint32_t)(L.blob.size() / 4);
+                hc.type = ch.type;
+                hc.niter = ch.niter;
+                hc.pad = 0;
+                L.chunks.push_back(hc);
+                L.blob.insert(L.blob.end(), cw.begin(), cw.end());
+                const size_t ob = L.blob.size();
+                L.blob.resize(ob + (size_t)T.nout * 16, 0u);              // u16 [nout][32], 0 = trash cell
+                uint16_t* op = reinterpret_cast<uint16_t*>(L.blob.data() + ob);
+                for (uint32_t l = 0; l < ch.count; ++l)
+                    for (int o = 0; o < T.nout; ++o) op[o * 32 + l] = tv[lanes[ch.first + l]].out[o];
+            }
+            pc.nchunk = (uint32_t)L.chunks.size() - pc.chunk0;
+            pc.nq = (uint32_t)(L.blob.size() / 4) - pc.q0;
+            if (pc.nchunk > 65535 || pc.nq > 65535) { L.error = "entity plan: too many chunks in one CTA"; return; }
+            L.per.push_back(pc);
+        }
+    };
+    {
+        std::vector<std::thread> th;
+        for (int t = 1; t < nthreads; ++t) th.emplace_back(work, t);
+        work(0);
+        for (auto& x : th) x.join();
+    }
+    for (auto& L : locals)
+        if (!L.error.empty()) { plan.error = L.error; return false; }
+
+    // ---- concatenate ----
+    plan.order = order;
+    plan.n = B.n;
+    plan.ncomp = ncomp;
+    plan.omax = omax;
+    size_t nq = 0, nch = 0, nrw = 0;
+    for (auto& L : locals) { nq += L.blob.size() / 4; nch += L.chunks.size(); nrw += L.rows.size(); }
+    if (nq + 64 > 0xFFFFFFFFull) { plan.error = "entity plan: blob offsets exceed 32 bits"; return false; }
+    plan.ctas.resize(nCta);
+    plan.chunks.reserve(nch);
+    plan.rows.reserve(nrw);
+    plan.blob.reserve(nq * 4 + 64);
+    int64_t c = 0;
+    for (auto& L : locals) {
+        const uint32_t cb = (uint32_t)plan.chunks.size(), rb = (uint32_t)plan.rows.size(), qb = (uint32_t)(plan.blob.size() / 4);
+        for (auto h : L.chunks) {
+            h.q0 += qb;
+            plan.chunks.push_back(h);
+        }
+        plan.rows.insert(plan.rows.end(), L.rows.begin(), L.rows.end());
+        plan.blob.insert(plan.blob.end(), L.blob.begin(), L.blob.end());
+        for (auto& pc : L.per) {
+            EPlanCta& ct = plan.ctas[c];
+            const CtaSeg& sg = segs[c];
+            ct.vert_off = sg.vert_off;
+            ct.visit_off = sg.visit_off;
+            ct.chunk_off = cb + pc.chunk0;
+            ct.row_off = rb + pc.row0;
+            ct.nverts = sg.nverts;
+            ct.nvisit = sg.nvisit;
+            ct.nchunk = (uint16_t)pc.nchunk;
+            ct.nrows = (uint16_t)pc.nrows;
+            ct.nout = (uint16_t)(sg.nout | (pc.needzero ? 0x8000u : 0u));
+            ct.blob_q0 = qb + pc.q0;
+            ct.blob_nq = (uint16_t)pc.nq;
+            plan.nouts += sg.nout - 1;
+            ++c;
+        }
+        plan.ntasks += L.ntasks;
+        plan.niters += L.niters;
+        plan.niters_padded += L.niters_padded;
+        plan.lds_wavefronts += L.wf;
+        plan.lds_ideal += L.wf_ideal;
+        L = Local();
+    }
+    plan.blob.resize(plan.blob.size() + 64, 0u);
+    plan.nvisits = (int64_t)plan.visits.size() / vstride;
+    return true;
+}

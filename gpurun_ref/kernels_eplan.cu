@@ -1,0 +1,644 @@
+// kernels_eplan.cu -- entity-task assembly kernel (see eplan.h for the design) and the plan's device mirror.
+//
+// Replaces, for constant-coefficient mass and stiffness forms on P1/P2 tetrahedra, the reference's per-element
+// update/integrate/assemble + MatSetValues(ADD_VALUES) (feelvf/integrator.hpp:1093-1207,
+// feelalg/matrixpetsc.cpp:917-936): every CSR value is accumulated in the registers of one thread over star(sigma)
+// and stored once, in a summation order fixed by the plan.
+#include <string>
+#include "feelgpu_internal.h"
+#include "eplan.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace {
+
+// out_o = sum_k coef[type][o][k] * (sum over the task's elements of the k-th loaded S entry)   (stiffness)
+// out_o = mass[type][o] * (sum over the task's elements of c J)                                  (mass)
+struct ECoef {
+    double coef[EPLAN_MAXTYPES][EPLAN_MAXOUT][EPLAN_MAXLD];
+    double mass[EPLAN_MAXTYPES][EPLAN_MAXOUT];
+};
+__constant__ ECoef c_ecoef;
+
+__host__ __device__ constexpr int e_nld(int order, int type)
+{
+    return order == 1 ? 1 : (type == 0 ? 1 : type == 1 ? 2 : type == 2 ? 2 : type == 3 ? 3 : type == 4 ? 5 : 4);
+}
+__host__ __device__ constexpr int e_nout(int order, int type)
+{
+    return order == 1 ? 1 : (type == 0 ? 1 : type == 1 ? 2 : type == 2 ? 1 : type == 3 ? 3 : type == 4 ? 3 : 1);
+}
+
+__device__ __forceinline__ double lds64(uint32_t addr)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts64(uint32_t addr, double v)
+{
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+
+// one chunk: lane = task.  wp points at this lane's first unit word; words are [niter][32] (the first two and the
+// out-buffer positions were fetched while the previous chunk ran).
+template <int ORDER, int FORM, int TYPE>
+__device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int niter, uint32_t w, uint32_t w1,
+                                          const uint32_t (&pos)[EPLAN_MAXOUT], uint32_t sS, uint32_t vsb, uint32_t sO)
+{
+    constexpr int NLD = FORM == 1 ? e_nld(ORDER, TYPE) : 1;
+    constexpr int NOUT = e_nout(ORDER, TYPE);
+    double sum[NLD];
+#pragma unroll
+    for (int k = 0; k < NLD; ++k) sum[k] = 0.0;
+    for (int t = 0; t < niter; ++t) {
+        const uint32_t w2 = (t + 2 < niter) ? __ldg(wp + (t + 2) * 32) : 0u;
+        const uint32_t va = sS + ((w & 0x3FFu) << 3);
+        if (FORM == 0) {
+            sum[0] += lds64(va);
+        } else {
+#pragma unroll
+            for (int k = 0; k < NLD; ++k) sum[k] += lds64(va + ((w >> (10 + 4 * k)) & 15u) * vsb);
+        }
+        w = w1;
+        w1 = w2;
+    }
+#pragma unroll
+    for (int o = 0; o < NOUT; ++o) {
+        double v;
+        if (FORM == 0) {
+            v = c_ecoef.mass[TYPE][o] * sum[0];
+        } else {
+            v = c_ecoef.coef[TYPE][o][0] * sum[0];
+#pragma unroll
+            for (int k = 1; k < NLD; ++k) v = fma(c_ecoef.coef[TYPE][o][k], sum[k], v);
+        }
+        sts64(sO + (pos[o] << 3), v);
+    }
+}
+
+template <int ORDER, int FORM, int NCOMP>   // FORM 0: mass, 1: stiffness; NCOMP components (block = value * Id)
+__global__ void __launch_bounds__(EPLAN_WARPS * 32, 2)
+k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, const uint32_t* __restrict__ visits,
+        const uint2* __restrict__ chunks, const uint32_t* __restrict__ blob, const uint4* __restrict__ rows,
+        const double* __restrict__ xyz, double* __restrict__ a, int accumulate, int vs, int omax, double cval)
+{
+    constexpr int NSREC = FORM == 1 ? 10 : 1;
+    extern __shared__ double sm[];
+    double* sS = sm;                          // [NSREC][vs]
+    double* sX = sS + NSREC * vs;             // [3][EPLAN_VERTS]
+    double* sO = sX + 3 * EPLAN_VERTS;        // [omax]: the CTA's row block; slot 0 = trash
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint4* cq = reinterpret_cast<const uint4*>(ctas + blockIdx.x);
+    const uint4 c0 = __ldg(cq), c1 = __ldg(cq + 1);
+    const uint32_t vert_off = c0.x, visit_off = c0.y, chunk_off = c0.z, row_off = c0.w;
+    const int nverts = c1.x & 0xFFFF, nvisit = c1.x >> 16, nchunk = c1.y & 0xFFFF, nrows = c1.y >> 16;
+    const uint32_t nout = c1.z & 0x7FFF, needzero = c1.z & 0x8000, blob_nq = c1.z >> 16, blob_q0 = c1.w;
+
+    // ---- L2 prefetch: the plan is streamed once from HBM.  One warp pulls the data of the CTA that will follow this one on
+    // the SM (blockIdx.x + EPLAN_AHEAD) into L2, so that its prologue and its phase B run at L2 latency; the first CTAs of
+    // the grid prefetch their own chunk data.
+    {
+        auto prefetch_range = [&](const void* p0, uint32_t nbytes, int l0) {
+            const uintptr_t lo = reinterpret_cast<uintptr_t>(p0) & ~(uintptr_t)15;
+            const uintptr_t hi = (reinterpret_cast<uintptr_t>(p0) + nbytes + 15) & ~(uintptr_t)15;
+            for (uintptr_t q = lo + (uintptr_t)l0 * 4096; q < hi; q += 32 * 4096) {
+                const uint32_t bytes = (uint32_t)min((uintptr_t)4096, hi - q);
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(q), "r"(bytes) : "memory");
+            }
+        };
+        if (warp == EPLAN_WARPS - 1) {
+            const uint32_t nb = blockIdx.x + EPLAN_AHEAD;
+            if (nb < gridDim.x) {
+                const uint4* nq = reinterpret_cast<const uint4*>(ctas + nb);
+                const uint4 n0 = __ldg(nq), n1 = __ldg(nq + 1);
+                prefetch_range(verts + n0.x, (n1.x & 0xFFFF) * 4u, lane);
+                prefetch_range(visits + n0.y, (n1.x >> 16) * 4u, lane);
+                prefetch_range(chunks + n0.z, (n1.y & 0xFFFF) * 8u, lane);
+                prefetch_range(rows + n0.w, (n1.y >> 16) * 16u, lane);
+                prefetch_range(reinterpret_cast<const uint4*>(blob) + n1.w, (n1.z >> 16) * 16u, lane);
+            }
+        }
+        if (blockIdx.x < EPLAN_AHEAD && warp == 0) prefetch_range(reinterpret_cast<const uint4*>(blob) + blob_q0, blob_nq * 16u, lane);
+    }
+    // headers of this warp's chunks (warp, warp + W, ...: lane k holds the k-th) and its first batch of rows: the loads
+    // are in flight while phase A runs
+    uint2 hdr = make_uint2(0u, 0u);
+    if (warp + EPLAN_WARPS * lane < nchunk) hdr = __ldg(&chunks[chunk_off + warp + EPLAN_WARPS * lane]);
+    uint4 rw = make_uint4(0u, 0u, 0u, 0u);     // row tid of the CTA's row table (EPLAN_ROWS <= blockDim.x)
+    if (tid < nrows) rw = __ldg(&rows[row_off + tid]);
+    uint4 vw0 = make_uint4(0u, 0u, 0u, 0u);    // visit record of this thread's first visit
+    if (tid < nvisit) {
+        if (ORDER == 2) vw0 = __ldg(reinterpret_cast<const uint4*>(visits + visit_off) + tid);
+        else vw0.x = __ldg(&visits[visit_off + tid]);
+    }
+
+    // ---- phase A0: coordinates of the CTA's unique vertices ----
+    for (int i = tid; i < nverts; i += blockDim.x) {
+        const int32_t id = __ldg(&verts[vert_off + i]);
+        const double2* q = reinterpret_cast<const double2*>(xyz + 4 * (int64_t)id);
+        const double2 p0 = __ldg(q), p1 = __ldg(q + 1);
+        sX[i] = p0.x;
+        sX[EPLAN_VERTS + i] = p0.y;
+        sX[2 * EPLAN_VERTS + i] = p1.x;
+    }
+    if (needzero)   // only when the graph holds entries that no element produces
+        for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
+    if (tid < NSREC) sS[tid * vs + vs - 1] = 0.0;             // the all-zero visit record (padding of the chunks)
+    __syncthreads();
+    // ---- phase A1: geometry of every element touched by this CTA's rows, once ----
+    for (int v = tid; v < nvisit; v += blockDim.x) {
+        uint4 vq = vw0;
+        if (v != tid) {
+            if (ORDER == 2) vq = __ldg(reinterpret_cast<const uint4*>(visits + visit_off) + v);
+            else vq.x = __ldg(&visits[visit_off + v]);
+        }
+        const uint32_t w = vq.x;
+        double x[4][3];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int lv = (w >> (8 * k)) & 255;
+            x[k][0] = sX[lv];
+            x[k][1] = sX[EPLAN_VERTS + lv];
+            x[k][2] = sX[2 * EPLAN_VERTS + lv];
+        }
+        // K = G grad(N) (edge vectors / 2), det, J = |det| (feelpoly/geomap.hpp:2320-2355, 1971-1976)
+        double K[3][3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            K[r][0] = 0.5 * (x[1][r] - x[0][r]);
+            K[r][1] = 0.5 * (x[2][r] - x[0][r]);
+            K[r][2] = 0.5 * (x[3][r] - x[0][r]);
+        }
+        const double c00 = K[1][1] * K[2][2] - K[1][2] * K[2][1];
+        const double c01 = K[1][2] * K[2][0] - K[1][0] * K[2][2];
+        const double c02 = K[1][0] * K[2][1] - K[1][1] * K[2][0];
+        const double det = K[0][0] * c00 + K[0][1] * c01 + K[0][2] * c02;
+        const double cj = cval * fabs(det);
+        if (FORM == 0) {
+            sS[v] = cj;
+            if (ORDER == 2) {   // (edge, opposite edge) entries: one element each, stored here (0 = not a row of this CTA)
+                const double m = c_ecoef.mass[5][0] * cj;
+                sO[vq.y & 0xFFFF] = m; sO[vq.y >> 16] = m; sO[vq.z & 0xFFFF] = m;
+                sO[vq.z >> 16] = m;    sO[vq.w & 0xFFFF] = m; sO[vq.w >> 16] = m;
+            }
+        } else {
+            const double id = 1.0 / det;
+            // B = K^{-T} (geomap.hpp:1985-1991): B[r][b] = d xi_b / d x_r ; grad lambda_{b+1} = B[:,b]/2
+            double h[4][3];
+            h[1][0] = 0.5 * c00 * id;
+            h[2][0] = 0.5 * c01 * id;
+            h[3][0] = 0.5 * c02 * id;
+            h[1][1] = 0.5 * (K[0][2] * K[2][1] - K[0][1] * K[2][2]) * id;
+            h[2][1] = 0.5 * (K[0][0] * K[2][2] - K[0][2] * K[2][0]) * id;
+            h[3][1] = 0.5 * (K[0][1] * K[2][0] - K[0][0] * K[2][1]) * id;
+            h[1][2] = 0.5 * (K[0][1] * K[1][2] - K[0][2] * K[1][1]) * id;
+            h[2][2] = 0.5 * (K[0][2] * K[1][0] - K[0][0] * K[1][2]) * id;
+            h[3][2] = 0.5 * (K[0][0] * K[1][1] - K[0][1] * K[1][0]) * id;
+#pragma unroll
+            for (int r = 0; r < 3; ++r) h[0][r] = -(h[1][r] + h[2][r] + h[3][r]);
+            // S_kl = c J grad(l_k).grad(l_l): diagonals 0..3, then (0,1),(0,2),(0,3),(1,2),(1,3),(2,3)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) sS[k * vs + v] = cj * (h[k][0] * h[k][0] + h[k][1] * h[k][1] + h[k][2] * h[k][2]);
+            const double s01 = cj * (h[0][0] * h[1][0] + h[0][1] * h[1][1] + h[0][2] * h[1][2]);
+            const double s02 = cj * (h[0][0] * h[2][0] + h[0][1] * h[2][1] + h[0][2] * h[2][2]);
+            const double s03 = cj * (h[0][0] * h[3][0] + h[0][1] * h[3][1] + h[0][2] * h[3][2]);
+            const double s12 = cj * (h[1][0] * h[2][0] + h[1][1] * h[2][1] + h[1][2] * h[2][2]);
+            const double s13 = cj * (h[1][0] * h[3][0] + h[1][1] * h[3][1] + h[1][2] * h[3][2]);
+            const double s23 = cj * (h[2][0] * h[3][0] + h[2][1] * h[3][1] + h[2][2] * h[3][2]);
+            sS[4 * vs + v] = s01;
+            sS[5 * vs + v] = s02;
+            sS[6 * vs + v] = s03;
+            sS[7 * vs + v] = s12;
+            sS[8 * vs + v] = s13;
+            sS[9 * vs + v] = s23;
+            if (ORDER == 2) {
+                // (edge, opposite edge) entries have sigma = the whole tet, i.e. this element alone: value =
+                // x (S_ac + S_ad + S_bc + S_bd) for edges (a,b) | (c,d); local edges e0=(1,2)|e3=(0,3), e1=(2,0)|e4=(1,3),
+                // e2=(0,1)|e5=(2,3) (feelmesh/simplexordering.hpp:283-291).  Slot per row edge; 0 = not a row of this CTA.
+                const double x5 = c_ecoef.coef[5][0][0];
+                const double t0 = x5 * ((s01 + s13) + (s02 + s23));
+                const double t1 = x5 * ((s12 + s23) + (s01 + s03));
+                const double t2 = x5 * ((s02 + s03) + (s12 + s13));
+                sO[vq.y & 0xFFFF] = t0; sO[vq.y >> 16] = t1; sO[vq.z & 0xFFFF] = t2;
+                sO[vq.z >> 16] = t0;    sO[vq.w & 0xFFFF] = t1; sO[vq.w >> 16] = t2;
+            }
+        }
+    }
+    __syncthreads();
+
+    // the vertex cache is dead now: it becomes the CTA's row table (read in phase C, after the next barrier)
+    uint4* sR = reinterpret_cast<uint4*>(sX);
+    if (tid < nrows) sR[tid] = rw;
+
+    // ---- phase B: task chunks, lane = task; the next chunk's first words and positions are fetched one chunk ahead ----
+    {
+        const uint32_t sSa = (uint32_t)__cvta_generic_to_shared(sS), sOa = (uint32_t)__cvta_generic_to_shared(sO);
+        const uint32_t vsb = (uint32_t)vs * 8u;
+        for (int cb = 0; cb < nchunk; cb += 32 * EPLAN_WARPS) {
+            if (cb) {
+                hdr = make_uint2(0u, 0u);
+                if (cb + warp + EPLAN_WARPS * lane < nchunk) hdr = __ldg(&chunks[chunk_off + cb + warp + EPLAN_WARPS * lane]);
+            }
+            const int mine = min(32, (nchunk - cb - warp + EPLAN_WARPS - 1) / EPLAN_WARPS);   // chunks of this warp in the batch
+            if (mine <= 0) break;
+            uint32_t q0 = __shfl_sync(0xffffffffu, hdr.x, 0), meta = __shfl_sync(0xffffffffu, hdr.y, 0);
+            const uint32_t* wp = blob + (size_t)q0 * 4 + lane;
+            uint32_t w = __ldg(wp), w1 = __ldg(wp + 32);
+            uint32_t pos[EPLAN_MAXOUT];
+            {
+                const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((meta >> 8) & 0xFF) * 32) + lane;
+#pragma unroll
+                for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = __ldg(op + o * 32);
+            }
+            for (int k = 0; k < mine; ++k) {
+                const int type = meta & 0xFF, niter = (meta >> 8) & 0xFF;
+                const uint32_t* wpc = wp;
+                // the next chunk of this warp (the last one re-reads itself: harmless)
+                const int kn = min(k + 1, mine - 1);
+                q0 = __shfl_sync(0xffffffffu, hdr.x, kn);
+                meta = __shfl_sync(0xffffffffu, hdr.y, kn);
+                wp = blob + (size_t)q0 * 4 + lane;
+                const uint32_t nw = __ldg(wp), nw1 = __ldg(wp + 32);
+                uint32_t npos[EPLAN_MAXOUT];
+                {
+                    const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((meta >> 8) & 0xFF) * 32) + lane;
+#pragma unroll
+                    for (int o = 0; o < EPLAN_MAXOUT; ++o) npos[o] = __ldg(op + o * 32);
+                }
+                switch (type) {
+                case 0: run_chunk<ORDER, FORM, 0>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                case 1: run_chunk<ORDER, FORM, 1>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
+                }
+                w = nw;
+                w1 = nw1;
+#pragma unroll
+                for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = npos[o];
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- phase C: the CTA's row block goes to the CSR value array, every value once ----
+    for (int r = warp; r < nrows; r += EPLAN_WARPS) {
+        const uint4 q = sR[r];
+        const int64_t base = (int64_t)(((uint64_t)q.y << 32) | q.x);
+        const double* src = sO + q.z;
+        const int len = (int)q.w;
+        if (NCOMP == 1) {
+            double* dst = a + base;
+            if (accumulate) {
+#pragma unroll 1
+                for (int i = lane; i < len; i += 32) dst[i] += src[i];
+            } else {
+#pragma unroll 1
+                for (int i = lane; i < len; i += 32) dst[i] = src[i];
+            }
+        } else {
+            // product space, block = v * Id: component row c1 starts at base + c1*len*NCOMP
+#pragma unroll 1
+            for (int i = lane; i < len; i += 32) {
+                const double v = src[i];
+#pragma unroll
+                for (int c1 = 0; c1 < NCOMP; ++c1)
+#pragma unroll
+                    for (int c2 = 0; c2 < NCOMP; ++c2) {
+                        double* dst = a + base + (int64_t)c1 * len * NCOMP + (int64_t)i * NCOMP + c2;
+                        if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
+                        else if (!accumulate) *dst = 0.0;
+                    }
+            }
+        }
+    }
+}
+
+size_t eplan_smem_bytes(const EPlan* p, int form)
+{
+    const int nsrec = form == 1 ? 10 : 1;
+    return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax);
+}
+
+template <typename T>
+cudaError_t upload(T** d, const std::vector<T>& h, int64_t& bytes)
+{
+    cudaError_t err = cudaMalloc(d, std::max<size_t>(h.size(), 1) * sizeof(T));
+    if (err != cudaSuccess) return err;
+    bytes += (int64_t)(h.size() * sizeof(T));
+    return cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+// least squares x of U x = t (U: 6 x m, column-major in u[k][6]); returns the relative residual
+double lsq6(int m, const double u[][6], const double* t, double* x)
+{
+    double A[EPLAN_MAXLD][EPLAN_MAXLD + 1];
+    for (int r = 0; r < m; ++r) {
+        for (int c = 0; c < m; ++c) {
+            double s = 0;
+            for (int k = 0; k < 6; ++k) s += u[r][k] * u[c][k];
+            A[r][c] = s;
+        }
+        double s = 0;
+        for (int k = 0; k < 6; ++k) s += u[r][k] * t[k];
+        A[r][m] = s;
+    }
+    for (int c = 0; c < m; ++c) {
+        int piv = c;
+        for (int r = c + 1; r < m; ++r)
+            if (std::fabs(A[r][c]) > std::fabs(A[piv][c])) piv = r;
+        if (std::fabs(A[piv][c]) < 1e-300) return 1.0;
+        for (int k = 0; k <= m; ++k) std::swap(A[c][k], A[piv][k]);
+        for (int r = 0; r < m; ++r) {
+            if (r == c) continue;
+            const double f = A[r][c] / A[c][c];
+            for (int k = c; k <= m; ++k) A[r][k] -= f * A[c][k];
+        }
+    }
+    for (int c = 0; c < m; ++c) x[c] = A[c][m] / A[c][c];
+    double res = 0, nt = 0;
+    for (int k = 0; k < 6; ++k) {
+        double s = -t[k];
+        for (int c = 0; c < m; ++c) s += u[c][k] * x[c];
+        res += s * s;
+        nt += t[k] * t[k];
+    }
+    return nt > 0 ? std::sqrt(res / nt) : std::sqrt(res);
+}
+
+// S_kl in the basis {S11,S22,S33,S12,S13,S23} (rows of the barycentric Gram matrix sum to zero)
+void s_in_b0(int k, int l, double* v)
+{
+    for (int i = 0; i < 6; ++i) v[i] = 0;
+    if (k > l) std::swap(k, l);
+    auto off = [](int a, int b) { return a == 1 ? (b == 2 ? 3 : 4) : 5; };   // (1,2)->3 (1,3)->4 (2,3)->5
+    if (k >= 1) {
+        if (k == l) v[k - 1] = 1;
+        else v[off(k, l)] = 1;
+        return;
+    }
+    if (l >= 1) {   // S_0l = -(S_1l + S_2l + S_3l)
+        for (int a = 1; a <= 3; ++a) {
+            if (a == l) v[a - 1] -= 1;
+            else v[off(std::min(a, l), std::max(a, l))] -= 1;
+        }
+        return;
+    }
+    v[0] = v[1] = v[2] = 1;   // S_00 = sum of all S_ab, a,b >= 1
+    v[3] = v[4] = v[5] = 2;
+}
+
+} // namespace
+
+int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    feelgpu_space_t sp = pat->test;
+    feelgpu_mesh_t m = sp->mesh;
+    if (pat->test != pat->trial) return FEELGPU_OK;   // the plan needs test == trial
+    if (!eplan_spec(sp->order)) { pat->eplan_note = "entity plan: order not covered"; return FEELGPU_OK; }
+    const int n = sp->n;
+    std::vector<uint16_t> pos((size_t)m->nElt * n * n);
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpy(pos.data(), pat->d_pos, pos.size() * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+    EPlanHost hp;
+    if (!eplan_build_host(sp->order, sp->ncomp, EPLAN_OMAX, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(),
+                          m->h_conn.data(), pat->nRows, h_ia, pos.data(), 0, hp)) {
+        pat->eplan_note = hp.error;   // not an error: another path stays available
+        return FEELGPU_OK;
+    }
+    EPlan* p = new EPlan;
+    p->order = hp.order;
+    p->n = hp.n;
+    p->ncomp = hp.ncomp;
+    p->omax = hp.omax;
+    p->ncta = (int64_t)hp.ctas.size();
+    p->ntasks = hp.ntasks;
+    p->niters = hp.niters;
+    p->niters_padded = hp.niters_padded;
+    p->nvisits = hp.nvisits;
+    p->nouts = hp.nouts;
+    p->lds_wavefronts = hp.lds_wavefronts;
+    p->lds_ideal = hp.lds_ideal;
+    cudaError_t err = upload(&p->d_ctas, hp.ctas, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_verts, hp.verts, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_visits, hp.visits, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_chunks, hp.chunks, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_blob, hp.blob, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_rows, hp.rows, p->bytes);
+    pat->eplan = p;
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("entity plan upload: ") + cudaGetErrorString(err);
+        feelgpu_eplan_destroy(pat);
+        return FEELGPU_ERR_CUDA;
+    }
+    return FEELGPU_OK;
+}
+
+int feelgpu_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
+{
+    for (int k = 0; k < 10; ++k) stats[k] = 0;
+    const EPlan* p = pat->eplan;
+    if (!p) return FEELGPU_OK;
+    stats[0] = 1;
+    stats[1] = p->ncta;
+    stats[2] = p->ntasks;
+    stats[3] = p->niters;
+    stats[4] = p->niters_padded;
+    stats[5] = p->nvisits;
+    stats[6] = p->nouts;
+    stats[7] = p->bytes;
+    stats[8] = (int64_t)p->lds_wavefronts;
+    stats[9] = (int64_t)p->lds_ideal;
+    return FEELGPU_OK;
+}
+
+void feelgpu_eplan_destroy(feelgpu_pattern_t pat)
+{
+    EPlan* p = pat->eplan;
+    if (!p) return;
+    cudaFree(p->d_ctas);
+    cudaFree(p->d_verts);
+    cudaFree(p->d_visits);
+    cudaFree(p->d_chunks);
+    cudaFree(p->d_blob);
+    cudaFree(p->d_rows);
+    delete p;
+    pat->eplan = nullptr;
+}
+
+// coefficients of every (type, output) from the caller's reference tables; false if the basis does not have the
+// entity-local structure the plan assumes (the residual of the projection onto the loaded S entries is not zero)
+static bool eplan_coefficients(const EPlanSpec& S, const feelgpu_tables& t, int form, ECoef* out, std::string* why)
+{
+    std::memset(out, 0, sizeof(ECoef));
+    const int nq = t.nq;
+    for (int ty = 0; ty < S.ntypes; ++ty) {
+        const EPlanType& T = S.type[ty];
+        const int i0 = T.rowdof;
+        for (int o = 0; o < T.nout; ++o) {
+            const int j = T.outdof[o];
+            if (form == 0) {
+                double mm = 0;
+                for (int q = 0; q < nq; ++q) mm += t.w[q] * (t.phi[i0 * nq + q] * t.phi[j * nq + q]);
+                out->mass[ty][o] = mm;
+                continue;
+            }
+            double M[3][3];
+            for (int b = 0; b < 3; ++b)
+                for (int d = 0; d < 3; ++d) {
+                    double v = 0;
+                    for (int q = 0; q < nq; ++q) v += t.w[q] * (t.dphi[(i0 * nq + q) * 3 + b] * t.dphi[(j * nq + q) * 3 + d]);
+                    M[b][d] = v;
+                }
+            // A = sum_bd G'_bd M_bd with G'_bd = 4 S_{b+1,d+1}  (grad xi_b = 2 grad lambda_{b+1})
+            const double tv[6] = {4 * M[0][0], 4 * M[1][1], 4 * M[2][2], 4 * (M[0][1] + M[1][0]), 4 * (M[0][2] + M[2][0]),
+                                  4 * (M[1][2] + M[2][1])};
+            double u[EPLAN_MAXLD][6], x[EPLAN_MAXLD];
+            for (int k = 0; k < T.nld; ++k) s_in_b0(T.ld[k][0], T.ld[k][1], u[k]);
+            const double res = lsq6(T.nld, u, tv, x);
+            if (!(res < 1e-11)) {
+                *why = "entity plan: the reference tables are not those of an entity-local Lagrange basis";
+                return false;
+            }
+            for (int k = 0; k < T.nld; ++k) out->coef[ty][o][k] = x[k];
+            if (T.phaseA)   // phase A applies one coefficient to the sum of the loaded entries
+                for (int k = 1; k < T.nld; ++k)
+                    if (std::fabs(x[k] - x[0]) > 1e-11 * std::fabs(x[0])) {
+                        *why = "entity plan: the (edge, opposite edge) entry is not symmetric in the loaded S entries";
+                        return false;
+                    }
+        }
+    }
+    return true;
+}
+
+bool feelgpu_eplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc)
+{
+    if (!pat->eplan) return false;
+    if (desc->kind != FEELGPU_FORM2_MASS && desc->kind != FEELGPU_FORM2_STIFFNESS) return false;
+    if (desc->coeff.kind != FEELGPU_COEFF_CONST) return false;
+    const EPlanSpec* S = eplan_spec(pat->eplan->order);
+    if (!S || desc->tables.n != S->n) return false;
+    if (desc->kind == FEELGPU_FORM2_STIFFNESS && !desc->tables.dphi) return false;
+    ECoef tmp;
+    std::string why;
+    return eplan_coefficients(*S, desc->tables, desc->kind == FEELGPU_FORM2_STIFFNESS ? 1 : 0, &tmp, &why);
+}
+
+int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
+                               int accumulate, double* a, cudaStream_t s)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    EPlan* p = pat->eplan;
+    feelgpu_mesh_t m = pat->test->mesh;
+    const int form = desc->kind == FEELGPU_FORM2_STIFFNESS ? 1 : 0;
+    ECoef tab;
+    std::string why;
+    if (!eplan_coefficients(*eplan_spec(p->order), desc->tables, form, &tab, &why)) {
+        ctx->last_error = why;
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    // stream-ordered upload of the coefficients (one context drives one stream at a time, see feelgpu.h)
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_ecoef, &tab, sizeof(ECoef), 0, cudaMemcpyHostToDevice, s));
+    const size_t sh = eplan_smem_bytes(p, form);
+    const int grid = (int)p->ncta, threads = EPLAN_WARPS * 32;
+    if (grid == 0) return FEELGPU_OK;
+#define ELAUNCH1(O, F, C)                                                                                          \
+    do {                                                                                                            \
+        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_eplan<O, F, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+        k_eplan<O, F, C><<<grid, threads, sh, s>>>(p->d_ctas, p->d_verts, p->d_visits,                              \
+                                                   reinterpret_cast<const uint2*>(p->d_chunks), p->d_blob,          \
+                                                   reinterpret_cast<const uint4*>(p->d_rows), m->d_xyz, a, accumulate, \
+                                                   EPLAN_VS, p->omax, hp.cval[0]);                                  \
+    } while (0)
+#define ELAUNCH(O, F)                         \
+    do {                                      \
+        if (p->ncomp == 1) ELAUNCH1(O, F, 1); \
+        else ELAUNCH1(O, F, 3);               \
+    } while (0)
+    switch (p->order * 2 + form) {
+    case 2: ELAUNCH(1, 0); break;
+    case 3: ELAUNCH(1, 1); break;
+    case 4: ELAUNCH(2, 0); break;
+    case 5: ELAUNCH(2, 1); break;
+    default: ctx->last_error = "entity plan: unsupported order"; return FEELGPU_ERR_UNSUPPORTED;
+    }
+#undef ELAUNCH
+#undef ELAUNCH1
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    return FEELGPU_OK;
+}
+
+// ---- host-side view of the plan (include/feelgpu.h) ----------------------------------------------------------------
+extern "C" {
+
+int feelgpu_eplan_host_build(int order, int ncomp, int64_t nElt, const int32_t* l2g, int64_t nPts, const double* xyz,
+                             const int32_t* conn, int64_t nRows, const int64_t* ia, const uint16_t* pos, void** plan,
+                             int64_t sizes[8])
+{
+    if (!l2g || !xyz || !conn || !ia || !pos || !plan || !sizes) return FEELGPU_ERR_ARG;
+    const EPlanSpec* S = eplan_spec(order);
+    if (!S) return FEELGPU_ERR_UNSUPPORTED;
+    EPlanHost* hp = new EPlanHost;
+    *plan = hp;
+    const bool ok = eplan_build_host(order, ncomp, EPLAN_OMAX, nElt, l2g, S->n * ncomp, nPts, xyz, conn, nRows, ia, pos, 0, *hp);
+    sizes[0] = (int64_t)hp->ctas.size();
+    sizes[1] = (int64_t)hp->verts.size();
+    sizes[2] = (int64_t)hp->visits.size();
+    sizes[3] = (int64_t)hp->chunks.size();
+    sizes[4] = (int64_t)hp->blob.size();
+    sizes[5] = (int64_t)hp->rows.size();
+    sizes[6] = hp->omax;
+    sizes[7] = EPLAN_VS;
+    return ok ? FEELGPU_OK : FEELGPU_ERR_UNSUPPORTED;
+}
+
+int feelgpu_eplan_host_copy(void* plan, void* ctas, int32_t* verts, uint32_t* visits, void* chunks, uint32_t* blob,
+                            void* rows, double stats[8])
+{
+    if (!plan) return FEELGPU_ERR_ARG;
+    const EPlanHost* hp = static_cast<const EPlanHost*>(plan);
+    if (ctas) std::memcpy(ctas, hp->ctas.data(), hp->ctas.size() * sizeof(EPlanCta));
+    if (verts) std::memcpy(verts, hp->verts.data(), hp->verts.size() * sizeof(int32_t));
+    if (visits) std::memcpy(visits, hp->visits.data(), hp->visits.size() * sizeof(uint32_t));
+    if (chunks) std::memcpy(chunks, hp->chunks.data(), hp->chunks.size() * sizeof(EPlanChunk));
+    if (blob) std::memcpy(blob, hp->blob.data(), hp->blob.size() * sizeof(uint32_t));
+    if (rows) std::memcpy(rows, hp->rows.data(), hp->rows.size() * sizeof(EPlanRow));
+    if (stats) {
+        stats[0] = (double)hp->ntasks;
+        stats[1] = (double)hp->niters;
+        stats[2] = (double)hp->niters_padded;
+        stats[3] = (double)hp->nvisits;
+        stats[4] = (double)hp->nouts;
+        stats[5] = hp->lds_wavefronts;
+        stats[6] = hp->lds_ideal;
+        stats[7] = 0;
+    }
+    return FEELGPU_OK;
+}
+
+const char* feelgpu_eplan_host_error(void* plan) { return plan ? static_cast<const EPlanHost*>(plan)->error.c_str() : ""; }
+
+int feelgpu_eplan_host_free(void* plan)
+{
+    delete static_cast<EPlanHost*>(plan);
+    return FEELGPU_OK;
+}
+
+int feelgpu_eplan_host_coefficients(int order, const feelgpu_tables* tables, int form, double* coef, double* mass)
+{
+    const EPlanSpec* S = eplan_spec(order);
+    if (!S || !tables || !coef || !mass || tables->n != S->n) return FEELGPU_ERR_ARG;
+    ECoef tab;
+    std::string why;
+    if (!eplan_coefficients(*S, *tables, form, &tab, &why)) return FEELGPU_ERR_UNSUPPORTED;
+    std::memcpy(coef, tab.coef, sizeof(tab.coef));
+    std::memcpy(mass, tab.mass, sizeof(tab.mass));
+    return FEELGPU_OK;
+}
+
+} // extern "C"

@@ -119,22 +119,25 @@ def interpret(P, mesh, order, nnz, form, coef, mass):
                 out[pos[live]] = t[le % 3][live]
                 np.add.at(hit, pos[live], 1)
         for ch in P["chunks"][ct["chunk_off"]:ct["chunk_off"] + ct["nchunk"]]:
-            ty, niter = int(ch["type"]), int(ch["niter"])
+            ty, niter, nsub = int(ch["type"]), int(ch["niter"]), int(ch["pad"])
             nld, no = (NLD[order][ty] if form == 1 else 1), NOUT[order][ty]
             w0 = int(ch["q0"]) * 4
-            words = P["blob"][w0:w0 + niter * 32].reshape(niter, 32)
-            opos = P["blob"][w0 + niter * 32:w0 + niter * 32 + no * 16].view(np.uint16).reshape(no, 32)
-            slot = words & 0x3FF
-            sums = np.zeros((nld, 32))
-            for t in range(niter):           # plan order
-                for k in range(nld):
-                    idx = (words[t] >> (10 + 4 * k)) & 15 if form == 1 else 0
-                    sums[k] += rec[slot[t], idx]
-            for o in range(no):
-                v = mass[ty][o] * sums[0] if form == 0 else sum(coef[ty][o][k] * sums[k] for k in range(nld))
-                live = opos[o] != 0
-                out[opos[o][live]] = v[live]
-                np.add.at(hit, opos[o][live], 1)
+            allw = P["blob"][w0:w0 + nsub * niter * 32].reshape(nsub, niter, 32)
+            p0 = w0 + nsub * niter * 32
+            allp = P["blob"][p0:p0 + nsub * no * 16].view(np.uint16).reshape(nsub, no, 32)
+            for j in range(nsub):
+                words, opos = allw[j], allp[j]
+                slot = words & 0x3FF
+                sums = np.zeros((nld, 32))
+                for t in range(niter):           # plan order
+                    for k in range(nld):
+                        idx = (words[t] >> (10 + 4 * k)) & 15 if form == 1 else 0
+                        sums[k] += rec[slot[t], idx]
+                for o in range(no):
+                    v = mass[ty][o] * sums[0] if form == 0 else sum(coef[ty][o][k] * sums[k] for k in range(nld))
+                    live = opos[o] != 0
+                    out[opos[o][live]] = v[live]
+                    np.add.at(hit, opos[o][live], 1)
         assert hit[1:nout].max(initial=1) == 1 and (needzero or hit[1:nout].min(initial=1) == 1), "every slot once"
         for rw in P["rows"][ct["row_off"]:ct["row_off"] + ct["nrows"]]:
             b, o, ln = int(rw["base"]), int(rw["off"]), int(rw["len"])
