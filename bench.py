@@ -253,9 +253,12 @@ def gpu_arm(args):
 
     # ---- end to end: host buffers, H2D of the coordinates + D2H of the CSR values inside the timed region ----
     e2e = None
-    if not args.no_e2e and world == 1:
+    if not args.no_e2e:
+        # host buffers in, host buffers out: per step H2D of the (local) vertex coordinates from host memory, assembly
+        # [+ NCCL ghost-row exchange], D2H of the (owned) CSR values into pinned host memory
+        nown = nnz if world == 1 else lp.nnz_owned()
         hp = C.c_void_p()
-        check(lib.feelgpu_host_alloc_pinned(eng.ctx, 8 * nnz, C.byref(hp)), eng.ctx)
+        check(lib.feelgpu_host_alloc_pinned(eng.ctx, 8 * max(nown, 1), C.byref(hp)), eng.ctx)
         hostvals = C.cast(hp, c_dblp)
         mh = eng.mesh(mesh)
         ksteps = max(2, min(args.steps, 5))
@@ -263,17 +266,24 @@ def gpu_arm(args):
             if it == 1:
                 barrier()
                 te0 = time.perf_counter()
-            check(lib.feelgpu_mesh_update_points(mh, ptr(mesh.xyz, c_dblp), None), eng.ctx)
-            check(lib.feelgpu_form2_assemble_host(a.pat, C.byref(desc), 0, hostvals), eng.ctx)
+            check(lib.feelgpu_mesh_update_points(mh, ptr(mesh.xyz, c_dblp), sptr), eng.ctx)
+            if world == 1:
+                check(lib.feelgpu_form2_assemble_host(a.pat, C.byref(desc), 0, hostvals), eng.ctx)
+            else:
+                step()
+                torch.cuda.synchronize()
+                check(lib.feelgpu_memcpy_d2h(eng.ctx, hp, a.d_values, 8 * nown), eng.ctx)
         barrier()
         te = (time.perf_counter() - te0) / ksteps
         tt = torch.tensor([te], device="cuda", dtype=torch.float64)
+        tb = torch.tensor([mesh.xyz.nbytes * 4 // 3, 8 * nown], device="cuda", dtype=torch.int64)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tb)
         te = float(tt.item())
-        e2e = {"value": world * nElt / te, "unit": UNIT, "h2d_bytes_per_step": int(mesh.xyz.nbytes * 4 // 3),
-               "d2h_bytes_per_step": 8 * nnz, "ms_per_step": 1e3 * te, "steps": ksteps,
-               "timer": "host perf_counter around synchronous feelgpu_form2_assemble_host calls"}
+        e2e = {"value": nElt_total / te, "unit": UNIT, "h2d_bytes_per_step": int(tb[0].item()),
+               "d2h_bytes_per_step": int(tb[1].item()), "ms_per_step": 1e3 * te, "steps": ksteps,
+               "timer": "host perf_counter around synchronous host-buffer calls, max over ranks"}
         lib.feelgpu_host_free_pinned(eng.ctx, hp)
 
     if rank == 0:
@@ -289,8 +299,15 @@ def gpu_arm(args):
         kms = sorted(k[1] for k in kern_ms)[len(kern_ms) // 2]
         zms = sorted(k[0] for k in kern_ms)[len(kern_ms) // 2]
         achieved = Be * nElt / (kms * 1e-3) / 1e9
+        traffic = None     # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same config only)
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_eplan_traffic.json")))
+            if world == 1 and args.m == 110 and args.order == 2 and args.algo in ("auto", "eplan") and not args.shuffle:
+                traffic = tr["dram_bytes_per_launch"]
+        except Exception:
+            pass
         roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel_ms": kms, "zero_fill_ms": zms, "algorithmic_bytes_per_element": Be,
+                "traffic": traffic, "kernel_ms": kms, "zero_fill_ms": zms, "algorithmic_bytes_per_element": Be,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                 "step_frac_vs_peak": Be * nElt_total / world / (ms / args.steps * 1e-3) / 1e9 / peak}
         cpu = None
