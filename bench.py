@@ -266,7 +266,7 @@ def gpu_arm(args):
             if it == 1:
                 barrier()
                 te0 = time.perf_counter()
-            check(lib.feelgpu_mesh_update_points(mh, ptr(mesh.xyz, c_dblp), sptr), eng.ctx)
+            check(lib.feelgpu_mesh_update_points(mh, ptr(mesh.xyz, c_dblp), None if world == 1 else sptr), eng.ctx)
             if world == 1:
                 check(lib.feelgpu_form2_assemble_host(a.pat, C.byref(desc), 0, hostvals), eng.ctx)
             else:
