@@ -369,6 +369,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             }
             sg.ne = k;
             sg.nverts = (uint16_t)np;
+            plan.verts.resize((size_t)sg.vert_off + EPLAN_VERTS, 0);   // fixed stride: the kernel loads ids before it has the CTA header
             sg.nvisit = (uint16_t)nv;
             sg.nout = nout;
             segs.push_back(sg);

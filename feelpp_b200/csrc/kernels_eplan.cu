@@ -94,6 +94,9 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
     int* sCnt = reinterpret_cast<int*>(sH + EPLAN_HDRS);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint4* cq = reinterpret_cast<const uint4*>(ctas + blockIdx.x);
+    // vertex lists have a fixed stride, so the id of "my" vertex is requested together with the CTA header
+    int32_t myvert = 0;
+    if (tid < EPLAN_VERTS) myvert = __ldg(&verts[(size_t)blockIdx.x * EPLAN_VERTS + tid]);
     const uint4 c0 = __ldg(cq), c1 = __ldg(cq + 1);
     const uint32_t vert_off = c0.x, visit_off = c0.y, chunk_off = c0.z, row_off = c0.w;
     const int nverts = c1.x & 0xFFFF, nvisit = c1.x >> 16, nchunk = c1.y & 0xFFFF, nrows = c1.y >> 16;
@@ -139,7 +142,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, co
 
     // ---- phase A0: coordinates of the CTA's unique vertices ----
     for (int i = tid; i < nverts; i += blockDim.x) {
-        const int32_t id = __ldg(&verts[vert_off + i]);
+        const int32_t id = i == tid ? myvert : __ldg(&verts[vert_off + i]);
         const double2* q = reinterpret_cast<const double2*>(xyz + 4 * (int64_t)id);
         const double2 p0 = __ldg(q), p1 = __ldg(q + 1);
         sX[i] = p0.x;
