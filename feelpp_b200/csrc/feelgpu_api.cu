@@ -235,7 +235,24 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
         return FEELGPU_ERR_CUDA;
     }
     int rc = feelgpu_launch_build_pos(pat, d_ja, ctx->stream);
-    cudaFree(d_ja); // the column array is only needed to build the maps
+    cudaFree(d_ja); // the 64-bit column array is only needed to build the maps
+    {   // 32-bit copy of the columns for feelgpu_form2_zero_rows
+        bool fits = true;
+        std::vector<int32_t> ja32((size_t)pat->nnz);
+        for (int64_t k = 0; k < pat->nnz; ++k) {
+            if (ja[k] < 0 || ja[k] >= ((int64_t)1 << 31)) { fits = false; break; }
+            ja32[k] = (int32_t)ja[k];
+        }
+        if (fits && rc == FEELGPU_OK) {
+            err = cudaMalloc(&pat->d_ja32, sizeof(int32_t) * std::max<int64_t>(pat->nnz, 1));
+            if (err == cudaSuccess) err = cudaMemcpy(pat->d_ja32, ja32.data(), sizeof(int32_t) * pat->nnz, cudaMemcpyHostToDevice);
+            if (err != cudaSuccess) {
+                ctx->last_error = std::string("pattern_create: ") + cudaGetErrorString(err);
+                feelgpu_pattern_destroy(pat);
+                return FEELGPU_ERR_CUDA;
+            }
+        }
+    }
     if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_EPLAN)) rc = feelgpu_eplan_build(pat, ia);
     // the row plan is also the fallback of a mesh the entity plan could not take
     if (rc == FEELGPU_OK && ((flags & FEELGPU_PATTERN_ROWPLAN) || ((flags & FEELGPU_PATTERN_EPLAN) && !pat->eplan)))
@@ -288,6 +305,7 @@ int feelgpu_pattern_destroy(feelgpu_pattern_t pat)
     if (pat->d_ia) cudaFree(pat->d_ia);
     if (pat->d_pos) cudaFree(pat->d_pos);
     if (pat->d_stage) cudaFree(pat->d_stage);
+    if (pat->d_ja32) cudaFree(pat->d_ja32);
     delete pat;
     return FEELGPU_OK;
 }
@@ -455,6 +473,21 @@ int feelgpu_form1_assemble_host(feelgpu_space_t sp, const feelgpu_form1_desc* de
         return FEELGPU_ERR_CUDA;
     }
     return rc;
+}
+
+int feelgpu_form2_zero_rows(feelgpu_pattern_t pat, int64_t n, const int32_t* rows, const double* values, int strategy,
+                            double value_on_diagonal, double* a_values, double* b, void* stream)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = pat->ctx;
+    if (n < 0 || n > pat->nRows || (n && (!rows || !values)) || !a_values) ARG_FAIL(ctx, "zero_rows: bad argument");
+    if (!(strategy & (FEELGPU_ON_ELIMINATION | FEELGPU_ON_SYMMETRIC))) {
+        ctx->last_error = "zero_rows: the strategy must contain ELIMINATION or SYMMETRIC (penalisation stays on the host)";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    return feelgpu_launch_zero_rows(pat, (int)n, rows, values, strategy, value_on_diagonal, a_values, b, s);
 }
 
 // ---- memory helpers -----------------------------------------------------------------------------------------

@@ -51,6 +51,7 @@ struct feelgpu_pattern_s {
     feelgpu_space_t test, trial;
     int64_t nRows = 0, nnz = 0;
     int64_t* d_ia = nullptr;     // [nRows+1]
+    int32_t* d_ja32 = nullptr;   // [nnz] column ids (kept for the Dirichlet elimination); null if an id needs more than 31 bits
     // element -> CSR position map, node level: pos[e][i][j] = position of column cluster(l2g_trial[e][j]) (component 0)
     // inside row l2g_test[e][i] (component 0).  Full slot = ia[row + c1] + pos + c2 (components are interleaved:
     // global = ncomp*node + c, feeldiscr/doftable.hpp:1289-1299).
@@ -88,6 +89,9 @@ int feelgpu_launch_form2_scatter(feelgpu_pattern_t pat, const FormParams& hp, co
                                  double* a, cudaStream_t s);
 int feelgpu_launch_form1(feelgpu_space_t sp, const FormParams& hp, const feelgpu_form1_desc* desc, double* b,
                          cudaStream_t s);
+// ---- kernels_on.cu ----
+int feelgpu_launch_zero_rows(feelgpu_pattern_t pat, int n, const int32_t* h_rows, const double* h_x, int strategy,
+                             double value_on_diagonal, double* a, double* b, cudaStream_t s);
 // ---- kernels_rowplan.cu ----
 int feelgpu_rowplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, const int64_t* h_ja);
 void feelgpu_rowplan_destroy(feelgpu_pattern_t pat);

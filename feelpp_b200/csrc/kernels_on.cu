@@ -1,0 +1,114 @@
+// kernels_on.cu -- Dirichlet elimination on the assembled CSR: form2 += on(_range=boundaryfaces(mesh), _rhs=l, _element=u,
+// _expr=g).  The reference collects the boundary dofs and their values on the host (feelvf/on.hpp:395-449) and calls
+// MatrixPetsc::zeroRows (feelalg/matrixpetsc.cpp:1762-1860), i.e. PETSc's MatZeroRows / MatZeroRowsColumns with the
+// value vector x and the right-hand side b:
+//     ELIMINATION            rows r: a_r* = 0, a_rr = d,  b_r = d x_r
+//     SYMMETRIC              additionally columns: b_i -= a_ir x_r, a_ir = 0 for every other row i
+//     KEEP_DIAGONAL          d = the old a_rr instead of value_on_diagonal (matrixpetsc.cpp:1817-1829)
+// Here the matrix stays on the device: one warp per eliminated row.  The column pass uses the structural symmetry of the
+// COUPLED pattern of one space: the transpose of entry (r,c) is found by a binary search in row c.
+#include <string>
+#include "feelgpu_internal.h"
+
+#include <algorithm>
+
+namespace {
+
+__global__ void k_on_mark(int n, const int32_t* __restrict__ rows, int32_t* __restrict__ mark)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) mark[rows[k]] = k + 1;
+}
+
+// SYMMETRIC: for every eliminated row r and every entry (r,c) of it: the transpose (c,r) is zeroed and, when c itself is
+// not eliminated, b_c -= a_cr x_r
+__global__ void k_on_columns(int n, const int32_t* __restrict__ rows, const double* __restrict__ x,
+                             const int32_t* __restrict__ mark, const int64_t* __restrict__ ia,
+                             const int32_t* __restrict__ ja, double* __restrict__ a, double* __restrict__ b)
+{
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= n) return;
+    const int32_t r = rows[w];
+    const double xr = x[w];
+    for (int64_t p = ia[r] + lane; p < ia[r + 1]; p += 32) {
+        const int32_t c = ja[p];
+        if (c == r) continue;
+        int64_t lo = ia[c], hi = ia[c + 1];
+        const int64_t end = hi;
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (ja[mid] < r) lo = mid + 1;
+            else hi = mid;
+        }
+        if (lo < end && ja[lo] == r) {
+            if (b && !mark[c]) atomicAdd(&b[c], -a[lo] * xr);
+            a[lo] = 0.0;
+        }
+    }
+}
+
+__global__ void k_on_rows(int n, const int32_t* __restrict__ rows, const double* __restrict__ x,
+                          const int64_t* __restrict__ ia, const int32_t* __restrict__ ja, const int64_t* __restrict__ p2c,
+                          double* __restrict__ a, double* __restrict__ b, int keep_diagonal, double value_on_diagonal)
+{
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= n) return;
+    const int32_t r = rows[w];
+    const int32_t dcol = p2c ? (int32_t)p2c[r] : r;   // columns are global-cluster ids (feelalg/datamap.hpp:467)
+    double d = value_on_diagonal;
+    for (int64_t p = ia[r] + lane; p < ia[r + 1]; p += 32) {
+        if (ja[p] == dcol) {
+            if (keep_diagonal) d = a[p];
+            else a[p] = d;
+            if (b) b[r] = x[w] * d;      // exactly one lane holds the diagonal (GraphCSR always inserts it, graphcsr.cpp:633-659)
+        } else
+            a[p] = 0.0;
+    }
+}
+
+} // namespace
+
+int feelgpu_launch_zero_rows(feelgpu_pattern_t pat, int n, const int32_t* h_rows, const double* h_x, int strategy,
+                             double value_on_diagonal, double* a, double* b, cudaStream_t s)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    if (n == 0) return FEELGPU_OK;
+    const bool symmetric = (strategy & FEELGPU_ON_SYMMETRIC) != 0;
+    if (symmetric && (pat->test->d_p2c || pat->test != pat->trial)) {
+        ctx->last_error = "zero_rows: the symmetric elimination needs one space with identity process->cluster numbering";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    if (!pat->d_ja32) {
+        ctx->last_error = "zero_rows: the pattern holds column ids beyond 32 bits";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    for (int k = 0; k < n; ++k)
+        if (h_rows[k] < 0 || h_rows[k] >= pat->nRows) {
+            ctx->last_error = "zero_rows: row id outside [0,nRows)";
+            return FEELGPU_ERR_ARG;
+        }
+    int32_t* d_rows = nullptr;
+    double* d_x = nullptr;
+    FEELGPU_CHECK_CUDA(ctx, cudaMallocAsync(&d_rows, sizeof(int32_t) * n, s));
+    FEELGPU_CHECK_CUDA(ctx, cudaMallocAsync(&d_x, sizeof(double) * n, s));
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(d_rows, h_rows, sizeof(int32_t) * n, cudaMemcpyHostToDevice, s));
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(d_x, h_x, sizeof(double) * n, cudaMemcpyHostToDevice, s));
+    const int threads = 256, wblocks = (int)(((int64_t)n * 32 + threads - 1) / threads);
+    if (symmetric) {
+        int32_t* d_mark = nullptr;
+        FEELGPU_CHECK_CUDA(ctx, cudaMallocAsync(&d_mark, sizeof(int32_t) * std::max<int64_t>(pat->nRows, 1), s));
+        FEELGPU_CHECK_CUDA(ctx, cudaMemsetAsync(d_mark, 0, sizeof(int32_t) * pat->nRows, s));
+        k_on_mark<<<(n + threads - 1) / threads, threads, 0, s>>>(n, d_rows, d_mark);
+        k_on_columns<<<wblocks, threads, 0, s>>>(n, d_rows, d_x, d_mark, pat->d_ia, pat->d_ja32, a, b);
+        ctx->launches += 2;
+        FEELGPU_CHECK_CUDA(ctx, cudaFreeAsync(d_mark, s));
+    }
+    k_on_rows<<<wblocks, threads, 0, s>>>(n, d_rows, d_x, pat->d_ia, pat->d_ja32, pat->test->d_p2c, a, b,
+                                          (strategy & FEELGPU_ON_KEEP_DIAGONAL) ? 1 : 0, value_on_diagonal);
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    FEELGPU_CHECK_CUDA(ctx, cudaFreeAsync(d_rows, s));
+    FEELGPU_CHECK_CUDA(ctx, cudaFreeAsync(d_x, s));
+    // the host arrays were read by asynchronous copies from pageable memory: those are staged before the call returns
+    return FEELGPU_OK;
+}

@@ -177,8 +177,18 @@ class BilinearForm:
         return self._assemble(integ, 0)
 
     def __iadd__(self, integ):
-        """a += integrate(...) (feelvf/bilinearform.hpp:1458-1468)."""
+        """a += integrate(...) (feelvf/bilinearform.hpp:1458-1468); a += on(...) (feelvf/on.hpp:1126-1190)."""
+        if isinstance(integ, vf.On):
+            return self._on(integ)
         return self._assemble(integ, 1)
+
+    def _on(self, o):
+        dofs, vals = o.dofs_and_values()
+        b = o.rhs.d_values if o.rhs is not None else None
+        check(self.eng.lib.feelgpu_form2_zero_rows(self.pat, len(dofs), ptr(dofs, c_i32p), ptr(vals, c_dblp), o.strategy,
+                                                   o.value_on_diagonal, self.d_values, b, None), self.eng.ctx)
+        self.eng.sync()
+        return self
 
     def _assemble(self, integ, accumulate):
         keep = _Keep()

@@ -37,6 +37,17 @@ def unitCube(m, jitter=0.0, shuffle=False):
     return Mesh(xyz, conn)
 
 
+class BoundaryFaceRange:
+    """boundaryfaces(mesh) (feelmesh/filters.hpp): used by on()"""
+
+    def __init__(self, mesh):
+        self.mesh = mesh
+
+
+def boundaryfaces(mesh):
+    return BoundaryFaceRange(mesh)
+
+
 class ElementRange:
     def __init__(self, mesh):
         self.mesh = mesh
@@ -105,6 +116,31 @@ class FunctionSpace:
         p = self.dofPoints()
         return np.asarray(f(p[:, 0], p[:, 1], p[:, 2]), dtype=np.float64)
 
+    def boundaryDofs(self):
+        """scalar node ids carried by the boundary faces (faces of exactly one element): what
+        on(_range=boundaryfaces(mesh), ...) visits through the face dof table (feelvf/on.hpp:395-449)."""
+        conn = self.mesh.conn.astype(np.int64)
+        npts = self.mesh.numPoints()
+        F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])        # feelmesh/simplexordering.hpp:341-347
+        E2P = np.array([[1, 2], [2, 0], [0, 1], [0, 3], [1, 3], [2, 3]])    # :283-291
+        fv = np.sort(conn[:, F2P], axis=2)                                    # [nElt][4][3]
+        key = (fv[..., 0] * npts + fv[..., 1]) * npts + fv[..., 2]
+        _, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
+        onb = (cnt[inv] == 1).reshape(key.shape)                             # [nElt][4] boundary faces
+        nodes = self.l2g[:, :self.n] // self.ncomp
+        out = []
+        npe = self.order - 1
+        for f in range(4):
+            sel = onb[:, f]
+            loc = list(F2P[f])
+            for e, (a, b) in enumerate(E2P):
+                if a in F2P[f] and b in F2P[f]:
+                    loc += [4 + e * npe + l for l in range(npe)]
+            if self.order >= 3:
+                loc.append(4 + 6 * npe + f)
+            out.append(nodes[sel][:, loc].ravel())
+        return np.unique(np.concatenate(out)).astype(np.int32)
+
 
 def Pch(mesh, order):
     """Pch<order>(mesh) (feeldiscr/pch.hpp:85-90)."""
@@ -157,3 +193,22 @@ class GinacProgram:
         self.ops = ops[:ln.value].copy()
         self.consts = consts[:ln.value].copy()
         self.polyDegree = deg.value
+
+    def evaluate(self, p):
+        """the postfix program at the points p[:,3] (host side: Dirichlet values of on())"""
+        p = np.asarray(p, dtype=np.float64)
+        st = []
+        un = {8: np.negative, 9: np.sin, 10: np.cos, 11: np.exp, 12: np.log, 13: np.sqrt}
+        bi = {4: np.add, 5: np.subtract, 6: np.multiply, 7: np.divide, 14: np.power}
+        for op, c in zip(self.ops, self.consts):
+            if op <= 2:
+                st.append(p[:, op].copy())
+            elif op == 3:
+                st.append(np.full(p.shape[0], c))
+            elif op in un:
+                st.append(un[op](st.pop()))
+            else:
+                b = st.pop()
+                a = st.pop()
+                st.append(bi[op](a, b))
+        return st[0]

@@ -10,6 +10,8 @@ expression), operators.hpp:134-153 (id/idt/grad/gradt and their polynomial order
 raises NotImplementedError -- on the Feel++ side the adapter would fall through to the reference loop; the engine
 itself has no CPU path.
 """
+import numpy as np
+
 from . import hostmirror as hm
 
 FORM2_MASS, FORM2_STIFFNESS, FORM2_ELASTICITY = 0, 1, 2
@@ -250,3 +252,47 @@ def integrate(_range, _expr, _quad=None):
     if not isinstance(_range, hm.ElementRange):
         raise NotImplementedError("only elements(mesh) ranges are accelerated")
     return Integrator(_range, _expr, _quad)
+
+
+ON_ELIMINATION, ON_SYMMETRIC, ON_KEEP_DIAGONAL = 1, 2, 4
+_ON_TYPES = {"elimination": ON_ELIMINATION, "elimination_keep_diagonal": ON_ELIMINATION | ON_KEEP_DIAGONAL,
+             "elimination_symmetric": ON_SYMMETRIC, "elimination_symmetric_keep_diagonal": ON_SYMMETRIC | ON_KEEP_DIAGONAL}
+
+
+class On:
+    """on(_range=boundaryfaces(mesh), _rhs=l, _element=u, _expr=g, _type="elimination", _value_on_diagonal=1.0)
+    (feelvf/on.hpp:1126-1190): the Dirichlet dofs and their values are collected on the host by nodal interpolation of
+    g (on.hpp:395-449: fe->interpolate(expr)); the elimination itself runs on the device CSR (feelgpu_form2_zero_rows)."""
+
+    def __init__(self, _range, _rhs, _element, _expr, _type="elimination", _value_on_diagonal=1.0):
+        if not isinstance(_range, hm.BoundaryFaceRange):
+            raise NotImplementedError("on(): only boundaryfaces(mesh) ranges")
+        if _type not in _ON_TYPES:
+            raise NotImplementedError("on(): type %r stays on the host path (penalisation)" % _type)
+        self.range, self.rhs, self.element, self.expr = _range, _rhs, _element, _expr
+        self.strategy, self.value_on_diagonal = _ON_TYPES[_type], float(_value_on_diagonal)
+
+    def dofs_and_values(self):
+        Xh = self.element.space
+        nodes = Xh.boundaryDofs()
+        p = Xh.dofPoints()[nodes]
+        g = self.expr
+        if callable(g):
+            val = np.asarray(g(p[:, 0], p[:, 1], p[:, 2]), dtype=np.float64)
+        elif isinstance(g, Cst):
+            val = np.full(len(nodes), float(g.v))
+        elif isinstance(g, Ginac):
+            val = g.prog.evaluate(p)
+        else:
+            val = np.full(len(nodes), float(g))
+        if Xh.ncomp == 1:
+            return nodes.astype(np.int32), np.broadcast_to(val, (len(nodes),)).astype(np.float64).copy()
+        val = np.asarray(val, dtype=np.float64)
+        if val.ndim == 1:
+            val = np.repeat(val[:, None], Xh.ncomp, axis=1)
+        dofs = (nodes[:, None] * Xh.ncomp + np.arange(Xh.ncomp)[None, :]).ravel()
+        return dofs.astype(np.int32), val.ravel().copy()
+
+
+def on(_range, _rhs, _element, _expr, _type="elimination", _value_on_diagonal=1.0):
+    return On(_range, _rhs, _element, _expr, _type, _value_on_diagonal)

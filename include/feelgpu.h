@@ -149,6 +149,18 @@ int feelgpu_form2_assemble_host(feelgpu_pattern_t pattern, const feelgpu_form2_d
 int feelgpu_form1_assemble_host(feelgpu_space_t space, const feelgpu_form1_desc* desc, int accumulate,
                                 double* b_host);
 
+/* ---- on(): Dirichlet elimination on the assembled matrix and right-hand side -----------------------------------------
+ * form2 += on(_range=boundaryfaces(mesh), _rhs=l, _element=u, _expr=g) collects the boundary dofs and their values on the
+ * host (feelvf/on.hpp:395-449) and calls MatrixPetsc::zeroRows (feelalg/matrixpetsc.cpp:1762-1860), i.e. PETSc's
+ * MatZeroRows / MatZeroRowsColumns.  rows: process-local dof ids (host), values: the Dirichlet value of every row (host);
+ * a_values and b are DEVICE arrays (b may be NULL).  Strategies (feelvf/on.hpp:1159-1175):
+ *   ELIMINATION      rows zeroed, a_rr = d, b_r = d*x_r                      (unsymmetric, the reference's default)
+ *   SYMMETRIC        also the columns: b_i -= a_ir*x_r, a_ir = 0             (one space, identity cluster numbering)
+ *   KEEP_DIAGONAL    d = the assembled a_rr instead of value_on_diagonal                                          */
+enum { FEELGPU_ON_ELIMINATION = 1, FEELGPU_ON_SYMMETRIC = 2, FEELGPU_ON_KEEP_DIAGONAL = 4 };
+int feelgpu_form2_zero_rows(feelgpu_pattern_t pattern, int64_t n, const int32_t* rows, const double* values, int strategy,
+                            double value_on_diagonal, double* a_values, double* b, void* stream);
+
 /* ---- close(): owner-side accumulation of ghost-row contributions -------------------------------------------------
  * The reference ships stashed off-rank rows inside MatAssemblyBegin/End (feelalg/matrixpetsc.cpp:750-752).  Here the
  * values of a rank's ghost rows are the tail of its value array (rows nDofOwned..nDofLocalWithGhost-1), sent as they

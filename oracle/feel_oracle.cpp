@@ -643,3 +643,41 @@ double oracle_form2_threads(int kind, int order, int ncomp, int quad_order, int6
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// on(): Dirichlet elimination.  feelvf/on.hpp:395-449 collects (dof, value) pairs and calls MatrixPetsc::zeroRows
+// (feelalg/matrixpetsc.cpp:1762-1860), which is PETSc's MatZeroRows(A, rows, diag, x, b) -- rows zeroed, diag on the
+// diagonal, b_r = diag*x_r -- or, with ContextOn::SYMMETRIC, MatZeroRowsColumns -- additionally b_i -= a_ir*x_r and
+// a_ir = 0 for the other rows.  ContextOn::KEEP_DIAGONAL restores the assembled diagonal afterwards
+// (MatDiagonalSet(diag, INSERT_VALUES)) and sets b_r = x_r * a_rr (matrixpetsc.cpp:1817-1829).
+// strategy bits: 1 elimination, 2 symmetric, 4 keep diagonal.  Sequential restatement, test infrastructure only.
+// ---------------------------------------------------------------------------------------------------------------
+extern "C" int oracle_zero_rows(int64_t nRows, const int64_t* ia, const int64_t* ja, int64_t n, const int32_t* rows,
+                                const double* x, int strategy, double value_on_diagonal, double* a, double* b)
+{
+    std::vector<int64_t> mark((size_t)nRows, -1);
+    for (int64_t k = 0; k < n; ++k) {
+        if (rows[k] < 0 || rows[k] >= nRows) return 1;
+        mark[rows[k]] = k;
+    }
+    std::vector<double> olddiag((size_t)n, 0.0);
+    for (int64_t k = 0; k < n; ++k)
+        for (int64_t p = ia[rows[k]]; p < ia[rows[k] + 1]; ++p)
+            if (ja[p] == rows[k]) olddiag[k] = a[p];
+    if (strategy & 2)
+        for (int64_t i = 0; i < nRows; ++i) {          // columns first: every other row loses its coupling to the rows
+            for (int64_t p = ia[i]; p < ia[i + 1]; ++p) {
+                const int64_t k = mark[ja[p]];
+                if (k < 0 || ja[p] == i) continue;
+                if (mark[i] < 0 && b) b[i] -= a[p] * x[k];
+                a[p] = 0.0;
+            }
+        }
+    for (int64_t k = 0; k < n; ++k) {
+        const int64_t r = rows[k];
+        const double d = (strategy & 4) ? olddiag[k] : value_on_diagonal;
+        for (int64_t p = ia[r]; p < ia[r + 1]; ++p) a[p] = (ja[p] == r) ? d : 0.0;
+        if (b) b[r] = x[k] * d;
+    }
+    return 0;
+}

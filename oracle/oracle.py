@@ -172,3 +172,22 @@ def local_matrix(kind, order, ncomp, quad_order, G, coeff=None):
     coeff = coeff or Coeff()
     lib().oracle_local_matrix(kind, order, ncomp, quad_order, _p(G, c_dblp), C.byref(coeff.c), _p(Ae, c_dblp))
     return Ae
+
+
+ON_ELIMINATION, ON_SYMMETRIC, ON_KEEP_DIAGONAL = 1, 2, 4
+
+
+def zero_rows(ia, ja, a, b, rows, x, strategy=ON_ELIMINATION, value_on_diagonal=1.0):
+    """MatrixPetsc::zeroRows on a copy of (a, b); returns the eliminated (a, b)."""
+    ia = np.ascontiguousarray(ia, dtype=np.int64)
+    ja = np.ascontiguousarray(ja, dtype=np.int64)
+    a, b = np.array(a, dtype=np.float64), np.array(b, dtype=np.float64)
+    rows = np.ascontiguousarray(rows, dtype=np.int32)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    lib().oracle_zero_rows.argtypes = [C.c_int64, c_i64p, c_i64p, C.c_int64, c_i32p, c_dblp, C.c_int, C.c_double, c_dblp,
+                                       c_dblp]
+    rc = lib().oracle_zero_rows(len(ia) - 1, _p(ia, c_i64p), _p(ja, c_i64p), len(rows), _p(rows, c_i32p), _p(x, c_dblp),
+                                strategy, value_on_diagonal, _p(a, c_dblp), _p(b, c_dblp))
+    if rc:
+        raise RuntimeError("oracle: row outside the matrix")
+    return a, b
