@@ -37,8 +37,7 @@
 #ifndef EPLAN_OMAX
 #define EPLAN_OMAX 7936          // 62 KB row block per CTA: two CTAs per SM next to the 40 KB geometry cache
 #endif
-#define EPLAN_AHEAD (EPLAN_MINB * 148)   // CTAs between a CTA and the one that follows it on the same SM slot
-#define EPLAN_HDRS 256            // chunk headers kept in shared memory (the rest, if any, is read from global memory)
+#define EPLAN_HDRS 128            // chunk headers kept in shared memory (the rest, if any, is read from global memory)
 #ifndef EPLAN_NSUB
 #define EPLAN_NSUB 1               // short chunks run under one header: measured slower on B200 (coarser hand-out, deeper word stream); kept at 1
 #endif
@@ -119,6 +118,7 @@ struct EPlan {                   // device mirror
     EPlanChunk* d_chunks = nullptr;
     uint32_t* d_blob = nullptr;
     EPlanRow* d_rows = nullptr;
+    int* d_sched = nullptr;      // [2] patch counter and exit counter of the persistent kernel (zero between launches)
     int64_t bytes = 0;
     int64_t ntasks = 0, niters = 0, niters_padded = 0, nvisits = 0, nouts = 0;
     double lds_wavefronts = 0, lds_ideal = 0;

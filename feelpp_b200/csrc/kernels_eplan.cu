@@ -37,6 +37,13 @@ __device__ __forceinline__ double lds64(uint32_t addr)
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
     return v;
 }
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* dst_shared, const void* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_shared)), "l"(src),
+                 "n"(BYTES) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ void sts64(uint32_t addr, double v)
 {
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
@@ -81,254 +88,292 @@ __device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int n
 
 template <int ORDER, int FORM, int NCOMP>   // FORM 0: mass, 1: stiffness; NCOMP components (block = value * Id)
 __global__ void __launch_bounds__(EPLAN_WARPS * 32, EPLAN_MINB)
-k_eplan(const EPlanCta* __restrict__ ctas, const int32_t* __restrict__ verts, const uint32_t* __restrict__ visits,
+k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, const int32_t* __restrict__ verts, const uint32_t* __restrict__ visits,
         const uint2* __restrict__ chunks, const uint32_t* __restrict__ blob, const uint4* __restrict__ rows,
         const double* __restrict__ xyz, double* __restrict__ a, int accumulate, int vs, int omax, double cval)
 {
+    static_assert(EPLAN_WARPS * 32 >= EPLAN_VS - 1 && EPLAN_WARPS * 32 >= EPLAN_ROWS && EPLAN_WARPS * 32 >= EPLAN_VERTS &&
+                      EPLAN_WARPS * 32 >= EPLAN_HDRS, "one thread per visit / row / vertex / cached chunk header");
     constexpr int NSREC = FORM == 1 ? 10 : 1;
     extern __shared__ double sm[];
     double* sS = sm;                          // [NSREC][vs]
     double* sX = sS + NSREC * vs;             // [3][EPLAN_VERTS]
-    double* sO = sX + 3 * EPLAN_VERTS;        // [omax]: the CTA's row block; slot 0 = trash
+    double* sO = sX + 3 * EPLAN_VERTS;        // [omax]: the patch's row block; slot 0 = trash
     uint2* sH = reinterpret_cast<uint2*>(sO + omax);   // [EPLAN_HDRS] chunk headers, then the chunk counter
     int* sCnt = reinterpret_cast<int*>(sH + EPLAN_HDRS);
+    uint4* sN = reinterpret_cast<uint4*>(sCnt + 4);    // [2][2] headers of the current and of the next patch (by parity)
+    int32_t* sVid = reinterpret_cast<int32_t*>(sN + 4);   // [EPLAN_VERTS] vertex ids of the next patch
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint4* cq = reinterpret_cast<const uint4*>(ctas + blockIdx.x);
-    // vertex lists have a fixed stride, so the id of "my" vertex is requested together with the CTA header
-    int32_t myvert = 0;
-    if (tid < EPLAN_VERTS) myvert = __ldg(&verts[(size_t)blockIdx.x * EPLAN_VERTS + tid]);
-    const uint4 c0 = __ldg(cq), c1 = __ldg(cq + 1);
-    const uint32_t vert_off = c0.x, visit_off = c0.y, chunk_off = c0.z, row_off = c0.w;
-    const int nverts = c1.x & 0xFFFF, nvisit = c1.x >> 16, nchunk = c1.y & 0xFFFF, nrows = c1.y >> 16;
-    const uint32_t nout = c1.z & 0x7FFF, needzero = c1.z & 0x8000, blob_nq = c1.z >> 16, blob_q0 = c1.w;
 
-    // ---- L2 prefetch: the plan is streamed once from HBM.  One warp pulls the data of the CTA that will follow this one on
-    // the SM (blockIdx.x + EPLAN_AHEAD) into L2, so that its prologue and its phase B run at L2 latency; the first CTAs of
-    // the grid prefetch their own chunk data.
+    // The CTA is persistent: after patch blockIdx.x it takes patches from a global counter (sched[0]).  Everything a patch's
+    // prologue reads from global memory (vertex coordinates and visit record: one of each per thread; row table and chunk
+    // headers: asynchronous copies to shared memory) is requested while the previous patch's phase C drains, so no patch
+    // but the first pays for the chain header -> vertex id -> coordinates.
+    double px = 0.0, py = 0.0, pz = 0.0;
+    uint4 vq = make_uint4(0u, 0u, 0u, 0u);
+    auto fetch = [&](const uint4& h0, const uint4& h1, int32_t id) {
+        if (tid < (int)(h1.x & 0xFFFF)) {
+            const double2* q = reinterpret_cast<const double2*>(xyz + 4 * (int64_t)id);
+            const double2 p0 = __ldg(q), p1 = __ldg(q + 1);
+            px = p0.x; py = p0.y; pz = p1.x;
+        }
+        if (tid < (int)(h1.x >> 16)) {
+            if (ORDER == 2) vq = __ldg(reinterpret_cast<const uint4*>(visits + h0.y) + tid);
+            else vq.x = __ldg(&visits[h0.y + tid]);
+        }
+        // chunk headers go straight to shared memory (phase B of the previous patch is over)
+        if (tid < (int)(h1.y & 0xFFFF) && tid < EPLAN_HDRS) cp_async<8>(&sH[tid], &chunks[h0.z + tid]);
+    };
+    auto prefetch_range = [&](const void* p0, uint32_t nbytes, int l0) {
+        const uintptr_t lo = reinterpret_cast<uintptr_t>(p0) & ~(uintptr_t)15;
+        const uintptr_t hi = (reinterpret_cast<uintptr_t>(p0) + nbytes + 15) & ~(uintptr_t)15;
+        for (uintptr_t q = lo + (uintptr_t)l0 * 4096; q < hi; q += 32 * 4096) {
+            const uint32_t bytes = (uint32_t)min((uintptr_t)4096, hi - q);
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(q), "r"(bytes) : "memory");
+        }
+    };
     {
-        auto prefetch_range = [&](const void* p0, uint32_t nbytes, int l0) {
-            const uintptr_t lo = reinterpret_cast<uintptr_t>(p0) & ~(uintptr_t)15;
-            const uintptr_t hi = (reinterpret_cast<uintptr_t>(p0) + nbytes + 15) & ~(uintptr_t)15;
-            for (uintptr_t q = lo + (uintptr_t)l0 * 4096; q < hi; q += 32 * 4096) {
-                const uint32_t bytes = (uint32_t)min((uintptr_t)4096, hi - q);
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(q), "r"(bytes) : "memory");
-            }
-        };
+        // vertex lists have a fixed stride, so the id of "my" vertex is requested together with the patch header
+        int32_t vid = 0;
+        if (tid < EPLAN_VERTS) vid = __ldg(&verts[(size_t)blockIdx.x * EPLAN_VERTS + tid]);
+        const uint4* cq = reinterpret_cast<const uint4*>(ctas + blockIdx.x);
+        const uint4 c0 = __ldg(cq), c1 = __ldg(cq + 1);
+        if (warp == 0) prefetch_range(reinterpret_cast<const uint4*>(blob) + c1.w, (c1.z >> 16) * 16u, lane);
+        fetch(c0, c1, vid);
+        if (tid == 0) { sN[0] = c0; sN[1] = c1; }
+    }
+    if (tid < NSREC) sS[tid * vs + vs - 1] = 0.0;             // the all-zero visit record (padding of the chunks)
+    __syncthreads();
+
+    for (int par = 0;; par ^= 1) {
+        const uint32_t chunk_off = sN[2 * par].z;
+        const uint4 c1 = sN[2 * par + 1];
+        const int nverts = c1.x & 0xFFFF, nvisit = c1.x >> 16, nchunk = c1.y & 0xFFFF, nrows = c1.y >> 16;
+        const uint32_t nout = c1.z & 0x7FFF, needzero = c1.z & 0x8000;
+        // ---- phase A0: the prologue data waiting in registers goes to shared memory ----
+        if (tid < nverts) {
+            sX[tid] = px;
+            sX[EPLAN_VERTS + tid] = py;
+            sX[2 * EPLAN_VERTS + tid] = pz;
+        }
+        cp_async_wait();                       // the chunk headers
+        if (tid == 0) *sCnt = EPLAN_WARPS;     // chunks 0..W-1 are the warps' first ones, the rest is handed out on demand
+        if (needzero)   // only when the graph holds entries that no element produces
+            for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
+        __syncthreads();
+        // ---- next patch: the last warp (it owns no visit: EPLAN_VS <= 32 (EPLAN_WARPS - 1)) takes the next patch id from the
+        // global counter, pulls that patch's data into L2 (the plan is streamed once from HBM) and leaves its header and
+        // vertex ids in shared memory.  Nobody waits for this chain: it is needed after phase B.
         if (warp == EPLAN_WARPS - 1) {
-            const uint32_t nb = blockIdx.x + EPLAN_AHEAD;
-            if (nb < gridDim.x) {
-                const uint4* nq = reinterpret_cast<const uint4*>(ctas + nb);
-                const uint4 n0 = __ldg(nq), n1 = __ldg(nq + 1);
-                prefetch_range(verts + n0.x, (n1.x & 0xFFFF) * 4u, lane);
-                prefetch_range(visits + n0.y, (n1.x >> 16) * 4u, lane);
+            int pn = 0;
+            if (lane == 0) pn = (int)gridDim.x + atomicAdd(sched, 1);
+            pn = __shfl_sync(0xffffffffu, pn, 0);
+            if (pn < ncta) {
+                const uint4* nq = reinterpret_cast<const uint4*>(ctas + pn);
+                uint4 n0 = __ldg(nq);
+                const uint4 n1 = __ldg(nq + 1);
+                int32_t ids[EPLAN_VERTS / 32];
+#pragma unroll
+                for (int k = 0; k < EPLAN_VERTS / 32; ++k) ids[k] = __ldg(&verts[(size_t)pn * EPLAN_VERTS + 32 * k + lane]);
+                prefetch_range(visits + n0.y, (n1.x >> 16) * (ORDER == 2 ? 16u : 4u), lane);
                 prefetch_range(chunks + n0.z, (n1.y & 0xFFFF) * 8u, lane);
                 prefetch_range(rows + n0.w, (n1.y >> 16) * 16u, lane);
                 prefetch_range(reinterpret_cast<const uint4*>(blob) + n1.w, (n1.z >> 16) * 16u, lane);
+#pragma unroll
+                for (int k = 0; k < EPLAN_VERTS / 32; ++k) {
+                    sVid[32 * k + lane] = ids[k];
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(xyz + 4 * (int64_t)ids[k]));
+                }
+                n0.x = (uint32_t)pn;           // (the vertex offset is implied by the fixed stride)
+                if (lane == 0) { sN[2 * (par ^ 1)] = n0; sN[2 * (par ^ 1) + 1] = n1; }
+            } else if (lane == 0)
+                sN[2 * (par ^ 1)].x = (uint32_t)pn;
+        }
+        // ---- phase A1: geometry of every element touched by this patch's rows, once (thread = visit) ----
+        if (tid < nvisit) {
+            const int v = tid;
+            const uint32_t w = vq.x;
+            double x[4][3];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int lv = (w >> (8 * k)) & 255;
+                x[k][0] = sX[lv];
+                x[k][1] = sX[EPLAN_VERTS + lv];
+                x[k][2] = sX[2 * EPLAN_VERTS + lv];
+            }
+            // K = G grad(N) (edge vectors / 2), det, J = |det| (feelpoly/geomap.hpp:2320-2355, 1971-1976)
+            double K[3][3];
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                K[r][0] = 0.5 * (x[1][r] - x[0][r]);
+                K[r][1] = 0.5 * (x[2][r] - x[0][r]);
+                K[r][2] = 0.5 * (x[3][r] - x[0][r]);
+            }
+            const double c00 = K[1][1] * K[2][2] - K[1][2] * K[2][1];
+            const double c01 = K[1][2] * K[2][0] - K[1][0] * K[2][2];
+            const double c02 = K[1][0] * K[2][1] - K[1][1] * K[2][0];
+            const double det = K[0][0] * c00 + K[0][1] * c01 + K[0][2] * c02;
+            const double cj = cval * fabs(det);
+            if (FORM == 0) {
+                sS[v] = cj;
+                if (ORDER == 2) {   // (edge, opposite edge) entries: one element each, stored here (0 = not a row of this CTA)
+                    const double m = c_ecoef.mass[5][0] * cj;
+                    sO[vq.y & 0xFFFF] = m; sO[vq.y >> 16] = m; sO[vq.z & 0xFFFF] = m;
+                    sO[vq.z >> 16] = m;    sO[vq.w & 0xFFFF] = m; sO[vq.w >> 16] = m;
+                }
+            } else {
+                const double id = 1.0 / det;
+                // B = K^{-T} (geomap.hpp:1985-1991): B[r][b] = d xi_b / d x_r ; grad lambda_{b+1} = B[:,b]/2
+                double h[4][3];
+                h[1][0] = 0.5 * c00 * id;
+                h[2][0] = 0.5 * c01 * id;
+                h[3][0] = 0.5 * c02 * id;
+                h[1][1] = 0.5 * (K[0][2] * K[2][1] - K[0][1] * K[2][2]) * id;
+                h[2][1] = 0.5 * (K[0][0] * K[2][2] - K[0][2] * K[2][0]) * id;
+                h[3][1] = 0.5 * (K[0][1] * K[2][0] - K[0][0] * K[2][1]) * id;
+                h[1][2] = 0.5 * (K[0][1] * K[1][2] - K[0][2] * K[1][1]) * id;
+                h[2][2] = 0.5 * (K[0][2] * K[1][0] - K[0][0] * K[1][2]) * id;
+                h[3][2] = 0.5 * (K[0][0] * K[1][1] - K[0][1] * K[1][0]) * id;
+#pragma unroll
+                for (int r = 0; r < 3; ++r) h[0][r] = -(h[1][r] + h[2][r] + h[3][r]);
+                // S_kl = c J grad(l_k).grad(l_l): diagonals 0..3, then (0,1),(0,2),(0,3),(1,2),(1,3),(2,3)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) sS[k * vs + v] = cj * (h[k][0] * h[k][0] + h[k][1] * h[k][1] + h[k][2] * h[k][2]);
+                const double s01 = cj * (h[0][0] * h[1][0] + h[0][1] * h[1][1] + h[0][2] * h[1][2]);
+                const double s02 = cj * (h[0][0] * h[2][0] + h[0][1] * h[2][1] + h[0][2] * h[2][2]);
+                const double s03 = cj * (h[0][0] * h[3][0] + h[0][1] * h[3][1] + h[0][2] * h[3][2]);
+                const double s12 = cj * (h[1][0] * h[2][0] + h[1][1] * h[2][1] + h[1][2] * h[2][2]);
+                const double s13 = cj * (h[1][0] * h[3][0] + h[1][1] * h[3][1] + h[1][2] * h[3][2]);
+                const double s23 = cj * (h[2][0] * h[3][0] + h[2][1] * h[3][1] + h[2][2] * h[3][2]);
+                sS[4 * vs + v] = s01;
+                sS[5 * vs + v] = s02;
+                sS[6 * vs + v] = s03;
+                sS[7 * vs + v] = s12;
+                sS[8 * vs + v] = s13;
+                sS[9 * vs + v] = s23;
+                if (ORDER == 2) {
+                    // (edge, opposite edge) entries have sigma = the whole tet, i.e. this element alone: value =
+                    // x (S_ac + S_ad + S_bc + S_bd) for edges (a,b) | (c,d); local edges e0=(1,2)|e3=(0,3), e1=(2,0)|e4=(1,3),
+                    // e2=(0,1)|e5=(2,3) (feelmesh/simplexordering.hpp:283-291).  Slot per row edge; 0 = not a row of this CTA.
+                    const double x5 = c_ecoef.coef[5][0][0];
+                    const double t0 = x5 * ((s01 + s13) + (s02 + s23));
+                    const double t1 = x5 * ((s12 + s23) + (s01 + s03));
+                    const double t2 = x5 * ((s02 + s03) + (s12 + s13));
+                    sO[vq.y & 0xFFFF] = t0; sO[vq.y >> 16] = t1; sO[vq.z & 0xFFFF] = t2;
+                    sO[vq.z >> 16] = t0;    sO[vq.w & 0xFFFF] = t1; sO[vq.w >> 16] = t2;
+                }
             }
         }
-        if (blockIdx.x < EPLAN_AHEAD && warp == 0) prefetch_range(reinterpret_cast<const uint4*>(blob) + blob_q0, blob_nq * 16u, lane);
-    }
-    // headers of this warp's chunks (warp, warp + W, ...: lane k holds the k-th) and its first batch of rows: the loads
-    // are in flight while phase A runs
-    if (tid < nchunk && tid < EPLAN_HDRS) sH[tid] = __ldg(&chunks[chunk_off + tid]);
-    if (tid == 0) *sCnt = EPLAN_WARPS;         // chunks 0..W-1 are the warps' first ones, the rest is handed out on demand
-    uint4 rw = make_uint4(0u, 0u, 0u, 0u);     // row tid of the CTA's row table (EPLAN_ROWS <= blockDim.x)
-    if (tid < nrows) rw = __ldg(&rows[row_off + tid]);
-    uint4 vw0 = make_uint4(0u, 0u, 0u, 0u);    // visit record of this thread's first visit
-    if (tid < nvisit) {
-        if (ORDER == 2) vw0 = __ldg(reinterpret_cast<const uint4*>(visits + visit_off) + tid);
-        else vw0.x = __ldg(&visits[visit_off + tid]);
-    }
+        __syncthreads();
 
-    // ---- phase A0: coordinates of the CTA's unique vertices ----
-    for (int i = tid; i < nverts; i += blockDim.x) {
-        const int32_t id = i == tid ? myvert : __ldg(&verts[vert_off + i]);
-        const double2* q = reinterpret_cast<const double2*>(xyz + 4 * (int64_t)id);
-        const double2 p0 = __ldg(q), p1 = __ldg(q + 1);
-        sX[i] = p0.x;
-        sX[EPLAN_VERTS + i] = p0.y;
-        sX[2 * EPLAN_VERTS + i] = p1.x;
-    }
-    if (needzero)   // only when the graph holds entries that no element produces
-        for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
-    if (tid < NSREC) sS[tid * vs + vs - 1] = 0.0;             // the all-zero visit record (padding of the chunks)
-    __syncthreads();
-    // ---- phase A1: geometry of every element touched by this CTA's rows, once ----
-    for (int v = tid; v < nvisit; v += blockDim.x) {
-        uint4 vq = vw0;
-        if (v != tid) {
-            if (ORDER == 2) vq = __ldg(reinterpret_cast<const uint4*>(visits + visit_off) + v);
-            else vq.x = __ldg(&visits[visit_off + v]);
-        }
-        const uint32_t w = vq.x;
-        double x[4][3];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int lv = (w >> (8 * k)) & 255;
-            x[k][0] = sX[lv];
-            x[k][1] = sX[EPLAN_VERTS + lv];
-            x[k][2] = sX[2 * EPLAN_VERTS + lv];
-        }
-        // K = G grad(N) (edge vectors / 2), det, J = |det| (feelpoly/geomap.hpp:2320-2355, 1971-1976)
-        double K[3][3];
-#pragma unroll
-        for (int r = 0; r < 3; ++r) {
-            K[r][0] = 0.5 * (x[1][r] - x[0][r]);
-            K[r][1] = 0.5 * (x[2][r] - x[0][r]);
-            K[r][2] = 0.5 * (x[3][r] - x[0][r]);
-        }
-        const double c00 = K[1][1] * K[2][2] - K[1][2] * K[2][1];
-        const double c01 = K[1][2] * K[2][0] - K[1][0] * K[2][2];
-        const double c02 = K[1][0] * K[2][1] - K[1][1] * K[2][0];
-        const double det = K[0][0] * c00 + K[0][1] * c01 + K[0][2] * c02;
-        const double cj = cval * fabs(det);
-        if (FORM == 0) {
-            sS[v] = cj;
-            if (ORDER == 2) {   // (edge, opposite edge) entries: one element each, stored here (0 = not a row of this CTA)
-                const double m = c_ecoef.mass[5][0] * cj;
-                sO[vq.y & 0xFFFF] = m; sO[vq.y >> 16] = m; sO[vq.z & 0xFFFF] = m;
-                sO[vq.z >> 16] = m;    sO[vq.w & 0xFFFF] = m; sO[vq.w >> 16] = m;
-            }
-        } else {
-            const double id = 1.0 / det;
-            // B = K^{-T} (geomap.hpp:1985-1991): B[r][b] = d xi_b / d x_r ; grad lambda_{b+1} = B[:,b]/2
-            double h[4][3];
-            h[1][0] = 0.5 * c00 * id;
-            h[2][0] = 0.5 * c01 * id;
-            h[3][0] = 0.5 * c02 * id;
-            h[1][1] = 0.5 * (K[0][2] * K[2][1] - K[0][1] * K[2][2]) * id;
-            h[2][1] = 0.5 * (K[0][0] * K[2][2] - K[0][2] * K[2][0]) * id;
-            h[3][1] = 0.5 * (K[0][1] * K[2][0] - K[0][0] * K[2][1]) * id;
-            h[1][2] = 0.5 * (K[0][1] * K[1][2] - K[0][2] * K[1][1]) * id;
-            h[2][2] = 0.5 * (K[0][2] * K[1][0] - K[0][0] * K[1][2]) * id;
-            h[3][2] = 0.5 * (K[0][0] * K[1][1] - K[0][1] * K[1][0]) * id;
-#pragma unroll
-            for (int r = 0; r < 3; ++r) h[0][r] = -(h[1][r] + h[2][r] + h[3][r]);
-            // S_kl = c J grad(l_k).grad(l_l): diagonals 0..3, then (0,1),(0,2),(0,3),(1,2),(1,3),(2,3)
-#pragma unroll
-            for (int k = 0; k < 4; ++k) sS[k * vs + v] = cj * (h[k][0] * h[k][0] + h[k][1] * h[k][1] + h[k][2] * h[k][2]);
-            const double s01 = cj * (h[0][0] * h[1][0] + h[0][1] * h[1][1] + h[0][2] * h[1][2]);
-            const double s02 = cj * (h[0][0] * h[2][0] + h[0][1] * h[2][1] + h[0][2] * h[2][2]);
-            const double s03 = cj * (h[0][0] * h[3][0] + h[0][1] * h[3][1] + h[0][2] * h[3][2]);
-            const double s12 = cj * (h[1][0] * h[2][0] + h[1][1] * h[2][1] + h[1][2] * h[2][2]);
-            const double s13 = cj * (h[1][0] * h[3][0] + h[1][1] * h[3][1] + h[1][2] * h[3][2]);
-            const double s23 = cj * (h[2][0] * h[3][0] + h[2][1] * h[3][1] + h[2][2] * h[3][2]);
-            sS[4 * vs + v] = s01;
-            sS[5 * vs + v] = s02;
-            sS[6 * vs + v] = s03;
-            sS[7 * vs + v] = s12;
-            sS[8 * vs + v] = s13;
-            sS[9 * vs + v] = s23;
-            if (ORDER == 2) {
-                // (edge, opposite edge) entries have sigma = the whole tet, i.e. this element alone: value =
-                // x (S_ac + S_ad + S_bc + S_bd) for edges (a,b) | (c,d); local edges e0=(1,2)|e3=(0,3), e1=(2,0)|e4=(1,3),
-                // e2=(0,1)|e5=(2,3) (feelmesh/simplexordering.hpp:283-291).  Slot per row edge; 0 = not a row of this CTA.
-                const double x5 = c_ecoef.coef[5][0][0];
-                const double t0 = x5 * ((s01 + s13) + (s02 + s23));
-                const double t1 = x5 * ((s12 + s23) + (s01 + s03));
-                const double t2 = x5 * ((s02 + s03) + (s12 + s13));
-                sO[vq.y & 0xFFFF] = t0; sO[vq.y >> 16] = t1; sO[vq.z & 0xFFFF] = t2;
-                sO[vq.z >> 16] = t0;    sO[vq.w & 0xFFFF] = t1; sO[vq.w >> 16] = t2;
-            }
-        }
-    }
-    __syncthreads();
+        // the vertex cache is dead now: it becomes the patch's row table (read in phase C, after the next barrier)
+        uint4* sR = reinterpret_cast<uint4*>(sX);
+        if (tid < nrows) cp_async<16>(&sR[tid], &rows[sN[2 * par].w + tid]);
 
-    // the vertex cache is dead now: it becomes the CTA's row table (read in phase C, after the next barrier)
-    uint4* sR = reinterpret_cast<uint4*>(sX);
-    if (tid < nrows) sR[tid] = rw;
-
-    // ---- phase B: task chunks, lane = task.  Chunks are sorted by cost and handed out on demand (shared counter); the next
-    // chunk's header, first words and positions are fetched while the current one runs.
-    {
-        const uint32_t sSa = (uint32_t)__cvta_generic_to_shared(sS), sOa = (uint32_t)__cvta_generic_to_shared(sO);
-        const uint32_t vsb = (uint32_t)vs * 8u, sCa = (uint32_t)__cvta_generic_to_shared(sCnt);
-        auto header = [&](int c) { return c < EPLAN_HDRS ? sH[c] : __ldg(&chunks[chunk_off + c]); };
-        int c = warp;
-        if (c < nchunk) {
-            uint2 ch = header(c);
-            const uint32_t* wp = blob + (size_t)ch.x * 4 + lane;
-            uint32_t meta = ch.y;
-            uint32_t w = __ldg(wp), w1 = __ldg(wp + 32);
-            uint32_t pos[EPLAN_MAXOUT];
-            {
-                const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((meta >> 8) & 0xFF) * 32) + lane;
-#pragma unroll
-                for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = __ldg(op + o * 32);
-            }
-            while (true) {
-                const int type = meta & 0xFF, niter = (meta >> 8) & 0xFF;
-                const uint32_t* wpc = wp;
-                int cn;   // next chunk: one shared-memory atomic by lane 0 (written out: the compiler's warp-aggregated form costs 20 instructions)
-                asm volatile("{ .reg .pred p; setp.eq.u32 p, %1, 0; mov.u32 %0, 0; @p atom.shared.inc.u32 %0, [%2], 0x7fffffff; }"
-                             : "=r"(cn) : "r"(lane), "r"(sCa) : "memory");
-                cn = __shfl_sync(0xffffffffu, cn, 0);
-                const bool more = cn < nchunk;
-                ch = header(more ? cn : c);                  // past the end: re-read the current chunk (harmless)
-                wp = blob + (size_t)ch.x * 4 + lane;
-                meta = ch.y;
-                const uint32_t nw = __ldg(wp), nw1 = __ldg(wp + 32);
-                uint32_t npos[EPLAN_MAXOUT];
+        // ---- phase B: task chunks, lane = task.  Chunks are sorted by cost and handed out on demand (shared counter); the next
+        // chunk's header, first words and positions are fetched while the current one runs.
+        {
+            const uint32_t sSa = (uint32_t)__cvta_generic_to_shared(sS), sOa = (uint32_t)__cvta_generic_to_shared(sO);
+            const uint32_t vsb = (uint32_t)vs * 8u, sCa = (uint32_t)__cvta_generic_to_shared(sCnt);
+            auto header = [&](int c) { return c < EPLAN_HDRS ? sH[c] : __ldg(&chunks[chunk_off + c]); };
+            int c = warp;
+            if (c < nchunk) {
+                uint2 ch = header(c);
+                const uint32_t* wp = blob + (size_t)ch.x * 4 + lane;
+                uint32_t meta = ch.y;
+                uint32_t w = __ldg(wp), w1 = __ldg(wp + 32);
+                uint32_t pos[EPLAN_MAXOUT];
                 {
                     const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((meta >> 8) & 0xFF) * 32) + lane;
 #pragma unroll
-                    for (int o = 0; o < EPLAN_MAXOUT; ++o) npos[o] = __ldg(op + o * 32);
+                    for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = __ldg(op + o * 32);
                 }
-                switch (type) {
-                case 0: run_chunk<ORDER, FORM, 0>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                case 1: run_chunk<ORDER, FORM, 1>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
-                }
-                if (!more) break;
-                c = cn;
-                w = nw;
-                w1 = nw1;
+                while (true) {
+                    const int type = meta & 0xFF, niter = (meta >> 8) & 0xFF;
+                    const uint32_t* wpc = wp;
+                    int cn;   // next chunk: one shared-memory atomic by lane 0 (written out: the compiler's warp-aggregated form costs 20 instructions)
+                    asm volatile("{ .reg .pred p; setp.eq.u32 p, %1, 0; mov.u32 %0, 0; @p atom.shared.inc.u32 %0, [%2], 0x7fffffff; }"
+                                 : "=r"(cn) : "r"(lane), "r"(sCa) : "memory");
+                    cn = __shfl_sync(0xffffffffu, cn, 0);
+                    const bool more = cn < nchunk;
+                    ch = header(more ? cn : c);                  // past the end: re-read the current chunk (harmless)
+                    wp = blob + (size_t)ch.x * 4 + lane;
+                    meta = ch.y;
+                    const uint32_t nw = __ldg(wp), nw1 = __ldg(wp + 32);
+                    uint32_t npos[EPLAN_MAXOUT];
+                    {
+                        const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((meta >> 8) & 0xFF) * 32) + lane;
 #pragma unroll
-                for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = npos[o];
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- phase C: the CTA's row block goes to the CSR value array, every value once ----
-    for (int r = warp; r < nrows; r += EPLAN_WARPS) {
-        const uint4 q = sR[r];
-        const int64_t base = (int64_t)(((uint64_t)q.y << 32) | q.x);
-        const double* src = sO + q.z;
-        const int len = (int)q.w;
-        if (NCOMP == 1) {
-            double* dst = a + base;
-            if (accumulate) {
-#pragma unroll 1
-                for (int i = lane; i < len; i += 32) dst[i] += src[i];
-            } else {
-#pragma unroll 1
-                for (int i = lane; i < len; i += 32) dst[i] = src[i];
-            }
-        } else {
-            // product space, block = v * Id: component row c1 starts at base + c1*len*NCOMP
-#pragma unroll 1
-            for (int i = lane; i < len; i += 32) {
-                const double v = src[i];
-#pragma unroll
-                for (int c1 = 0; c1 < NCOMP; ++c1)
-#pragma unroll
-                    for (int c2 = 0; c2 < NCOMP; ++c2) {
-                        double* dst = a + base + (int64_t)c1 * len * NCOMP + (int64_t)i * NCOMP + c2;
-                        if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
-                        else if (!accumulate) *dst = 0.0;
+                        for (int o = 0; o < EPLAN_MAXOUT; ++o) npos[o] = __ldg(op + o * 32);
                     }
+                    switch (type) {
+                    case 0: run_chunk<ORDER, FORM, 0>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    case 1: run_chunk<ORDER, FORM, 1>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
+                    }
+                    if (!more) break;
+                    c = cn;
+                    w = nw;
+                    w1 = nw1;
+#pragma unroll
+                    for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = npos[o];
+                }
             }
         }
+        cp_async_wait();   // the row table
+        __syncthreads();
+
+        // the next patch's prologue loads fly while phase C runs
+        const bool has_next = (int)sN[2 * (par ^ 1)].x < ncta;
+        if (has_next) fetch(sN[2 * (par ^ 1)], sN[2 * (par ^ 1) + 1], tid < EPLAN_VERTS ? sVid[tid] : 0);
+
+        // ---- phase C: the CTA's row block goes to the CSR value array, every value once ----
+        for (int r = warp; r < nrows; r += EPLAN_WARPS) {
+            const uint4 q = sR[r];
+            const int64_t base = (int64_t)(((uint64_t)q.y << 32) | q.x);
+            const double* src = sO + q.z;
+            const int len = (int)q.w;
+            if (NCOMP == 1) {
+                double* dst = a + base;
+                if (accumulate) {
+#pragma unroll 1
+                    for (int i = lane; i < len; i += 32) dst[i] += src[i];
+                } else {
+#pragma unroll 1
+                    for (int i = lane; i < len; i += 32) dst[i] = src[i];
+                }
+            } else {
+                // product space, block = v * Id: component row c1 starts at base + c1*len*NCOMP
+#pragma unroll 1
+                for (int i = lane; i < len; i += 32) {
+                    const double v = src[i];
+#pragma unroll
+                    for (int c1 = 0; c1 < NCOMP; ++c1)
+#pragma unroll
+                        for (int c2 = 0; c2 < NCOMP; ++c2) {
+                            double* dst = a + base + (int64_t)c1 * len * NCOMP + (int64_t)i * NCOMP + c2;
+                            if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
+                            else if (!accumulate) *dst = 0.0;
+                        }
+                }
+            }
+        }
+        if (!has_next) break;
+        __syncthreads();   // phase C has read the row table and the row block
+    }
+    // the last CTA to leave rearms the counters for the next launch
+    if (tid == 0 && atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {
+        sched[0] = 0;
+        sched[1] = 0;
     }
 }
 
 size_t eplan_smem_bytes(const EPlan* p, int form)
 {
     const int nsrec = form == 1 ? 10 : 1;
-    return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax) + EPLAN_HDRS * sizeof(uint2) + 16;
+    return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax) + EPLAN_HDRS * sizeof(uint2) + 16 + 4 * sizeof(uint4) + EPLAN_VERTS * sizeof(int32_t);
 }
 
 template <typename T>
@@ -436,6 +481,8 @@ int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     if (err == cudaSuccess) err = upload(&p->d_chunks, hp.chunks, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_blob, hp.blob, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_rows, hp.rows, p->bytes);
+    if (err == cudaSuccess) err = cudaMalloc(&p->d_sched, 2 * sizeof(int));
+    if (err == cudaSuccess) err = cudaMemset(p->d_sched, 0, 2 * sizeof(int));
     pat->eplan = p;
     if (err != cudaSuccess) {
         ctx->last_error = std::string("entity plan upload: ") + cudaGetErrorString(err);
@@ -473,6 +520,7 @@ void feelgpu_eplan_destroy(feelgpu_pattern_t pat)
     cudaFree(p->d_chunks);
     cudaFree(p->d_blob);
     cudaFree(p->d_rows);
+    cudaFree(p->d_sched);
     delete p;
     pat->eplan = nullptr;
 }
@@ -552,12 +600,13 @@ int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     // stream-ordered upload of the coefficients (one context drives one stream at a time, see feelgpu.h)
     FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_ecoef, &tab, sizeof(ECoef), 0, cudaMemcpyHostToDevice, s));
     const size_t sh = eplan_smem_bytes(p, form);
-    const int grid = (int)p->ncta, threads = EPLAN_WARPS * 32;
+    // persistent CTAs: EPLAN_MINB per SM, each runs every gridDim.x-th patch
+    const int grid = (int)std::min<int64_t>(p->ncta, (int64_t)ctx->sm_count * EPLAN_MINB), threads = EPLAN_WARPS * 32;
     if (grid == 0) return FEELGPU_OK;
 #define ELAUNCH1(O, F, C)                                                                                          \
     do {                                                                                                            \
         FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_eplan<O, F, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-        k_eplan<O, F, C><<<grid, threads, sh, s>>>(p->d_ctas, p->d_verts, p->d_visits,                              \
+        k_eplan<O, F, C><<<grid, threads, sh, s>>>(p->d_ctas, (int)p->ncta, p->d_sched, p->d_verts, p->d_visits,                              \
                                                    reinterpret_cast<const uint2*>(p->d_chunks), p->d_blob,          \
                                                    reinterpret_cast<const uint4*>(p->d_rows), m->d_xyz, a, accumulate, \
                                                    EPLAN_VS, p->omax, hp.cval[0]);                                  \
