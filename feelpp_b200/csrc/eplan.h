@@ -106,6 +106,7 @@ struct EPlanHost {
     int64_t ntasks = 0, niters = 0, niters_padded = 0, nvisits = 0, nouts = 0;
     double lds_wavefronts = 0;   // modelled shared-memory wavefronts of the S loads (stiffness) over the whole plan
     double lds_ideal = 0;        // the same without bank conflicts
+    double a1_passes = 0, a1_passes_before = 0;   // modelled passes of one coordinate read of phase A1 (per half-warp and corner), after / before the vertex slots were levelled
     std::string error;
 };
 

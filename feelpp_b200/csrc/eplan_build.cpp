@@ -101,7 +101,7 @@ struct Local {                      // per-thread output, concatenated at the en
     struct PerCta { uint32_t chunk0, nchunk, row0, nrows, q0, nq, needzero; };
     std::vector<PerCta> per;
     int64_t ntasks = 0, niters = 0, niters_padded = 0;
-    double wf = 0, wf_ideal = 0;
+    double wf = 0, wf_ideal = 0, a1 = 0, a1_before = 0;
     std::string error;
 };
 
@@ -262,6 +262,113 @@ void model_chunk(const EPlanType& T, const std::vector<uint32_t>& words, int nit
             }
 }
 
+// Phase A1 reads the coordinates of corner k of 16 consecutive visits at a time (one half-warp, thread = visit slot); the
+// read is served in as many passes as the fullest bank pair (vertex slot mod 16) holds distinct vertices.  The slot of a
+// vertex is free: deal the vertices to the 16 bank pairs (16 slots each), most used first, each to the pair that raises the
+// fewest group maxima, then let every vertex reconsider once.  Returns the modelled passes; rewrites verts[] and the
+// corner bytes of the visit words; nverts becomes the highest slot in use + 1.
+double level_vertex_banks(uint32_t nv, uint32_t np, uint32_t* vw, int vstride, int32_t* verts, uint16_t& nverts,
+                          double& before)
+{
+    const uint32_t ngrp = (nv + 15) / 16 * 4;
+    std::vector<uint32_t> gptr(np + 1, 0), gl;
+    std::vector<uint8_t> cnt((size_t)ngrp * 16, 0), gmax(ngrp, 0);
+    auto group_of = [&](uint32_t v, int k) { return (v / 16) * 4 + (uint32_t)k; };
+    // distinct (vertex, group) pairs
+    std::vector<uint32_t> pairs;
+    pairs.reserve((size_t)nv * 4);
+    for (uint32_t v = 0; v < nv; ++v)
+        for (int k = 0; k < 4; ++k) pairs.push_back((((vw[(size_t)v * vstride] >> (8 * k)) & 255u) << 16) | group_of(v, k));
+    std::sort(pairs.begin(), pairs.end());
+    pairs.erase(std::unique(pairs.begin(), pairs.end()), pairs.end());
+    for (uint32_t pr : pairs) gptr[(pr >> 16) + 1]++;
+    for (uint32_t u = 0; u < np; ++u) gptr[u + 1] += gptr[u];
+    gl.resize(pairs.size());
+    for (size_t i = 0; i < pairs.size(); ++i) gl[i] = pairs[i] & 0xFFFF;   // sorted by vertex: already in CSR order
+    auto passes = [&]() {
+        double t = 0;
+        for (uint32_t g = 0; g < ngrp; ++g) t += std::max<int>(1, gmax[g]);
+        return t;
+    };
+    // the numbering found by the packing pass
+    for (uint32_t u = 0; u < np; ++u)
+        for (uint32_t q = gptr[u]; q < gptr[u + 1]; ++q) {
+            uint8_t& c = cnt[(size_t)gl[q] * 16 + (u & 15)];
+            gmax[gl[q]] = std::max<uint8_t>(gmax[gl[q]], ++c);
+        }
+    before = passes();
+    if (np <= 16) return before;
+    std::fill(cnt.begin(), cnt.end(), 0);
+    std::fill(gmax.begin(), gmax.end(), 0);
+    std::vector<uint32_t> order(np);
+    for (uint32_t u = 0; u < np; ++u) order[u] = u;
+    std::stable_sort(order.begin(), order.end(),
+                     [&](uint32_t x, uint32_t y) { return gptr[x + 1] - gptr[x] > gptr[y + 1] - gptr[y]; });
+    std::vector<int> bank(np, -1);
+    int load[16] = {0};
+    auto best_bank = [&](uint32_t u) {
+        int bb = -1;
+        long bcost = 0;
+        for (int b = 0; b < 16; ++b) {
+            if (load[b] >= EPLAN_VERTS / 16) continue;
+            long raise = 0, crowd = 0;
+            for (uint32_t q = gptr[u]; q < gptr[u + 1]; ++q) {
+                const uint8_t c = cnt[(size_t)gl[q] * 16 + b];
+                raise += c + 1 > gmax[gl[q]];
+                crowd += c;
+            }
+            const long cost = (raise << 20) + (crowd << 8) + load[b];
+            if (bb < 0 || cost < bcost) { bb = b; bcost = cost; }
+        }
+        return bb;
+    };
+    auto put = [&](uint32_t u, int b) {
+        bank[u] = b;
+        ++load[b];
+        for (uint32_t q = gptr[u]; q < gptr[u + 1]; ++q) {
+            uint8_t& c = cnt[(size_t)gl[q] * 16 + b];
+            gmax[gl[q]] = std::max<uint8_t>(gmax[gl[q]], ++c);
+        }
+    };
+    auto take = [&](uint32_t u) {
+        const int b = bank[u];
+        --load[b];
+        for (uint32_t q = gptr[u]; q < gptr[u + 1]; ++q) {
+            const uint32_t g = gl[q];
+            --cnt[(size_t)g * 16 + b];
+            uint8_t m = 0;
+            for (int x = 0; x < 16; ++x) m = std::max(m, cnt[(size_t)g * 16 + x]);
+            gmax[g] = m;
+        }
+    };
+    for (uint32_t u : order) put(u, best_bank(u));
+    for (int pass = 0; pass < 2; ++pass)
+        for (uint32_t u : order) {
+            take(u);
+            put(u, best_bank(u));
+        }
+    // slots: the j-th vertex of bank pair b sits at b + 16 j
+    int fill[16] = {0};
+    std::vector<uint8_t> slot(np);
+    std::vector<int32_t> old(verts, verts + np);
+    uint32_t hi = 0;
+    std::fill(verts, verts + EPLAN_VERTS, 0);
+    for (uint32_t u = 0; u < np; ++u) {
+        const uint32_t sl = (uint32_t)bank[u] + 16u * (uint32_t)fill[bank[u]]++;
+        slot[u] = (uint8_t)sl;
+        verts[sl] = old[u];
+        hi = std::max(hi, sl + 1);
+    }
+    nverts = (uint16_t)hi;
+    for (uint32_t v = 0; v < nv; ++v) {
+        uint32_t& w = vw[(size_t)v * vstride];
+        uint32_t r = 0;
+        for (int k = 0; k < 4; ++k) r |= (uint32_t)slot[(w >> (8 * k)) & 255u] << (8 * k);
+        w = r;
+    }
+    return passes();
+}
+
 } // namespace
 
 const EPlanSpec* eplan_spec(int order)
@@ -398,7 +505,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         struct ChunkTmp { uint8_t type, niter; uint32_t first, count; int cost; };
         std::vector<ChunkTmp> ctmp;
         for (int64_t c = nCta * t / nthreads; c < nCta * (t + 1) / nthreads; ++c) {
-            const CtaSeg& sg = segs[c];
+            CtaSeg& sg = segs[c];
             for (int ty = 0; ty < S.ntypes; ++ty) tasks[ty].clear();
             iterw.clear();
             Local::PerCta pc;
@@ -491,6 +598,12 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                         vw[(size_t)slot * vstride + 1 + tk.aux / 2] |= (uint32_t)tk.out[0] << (16 * (tk.aux & 1));
                     }
                 }
+            }
+            if (!getenv("FEELGPU_EPLAN_NO_VERTEX_BANKS")) {
+                double before = 0;
+                L.a1 += level_vertex_banks(sg.nvisit, sg.nverts, plan.visits.data() + sg.visit_off, vstride,
+                                           plan.verts.data() + sg.vert_off, sg.nverts, before);
+                L.a1_before += before;
             }
             // ---- chunks: 32 tasks of one type, longest first ----
             // All S loads of one iteration hit the bank pair (visit slot mod 16); a half-warp is served in one pass only
@@ -763,6 +876,8 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         plan.niters_padded += L.niters_padded;
         plan.lds_wavefronts += L.wf;
         plan.lds_ideal += L.wf_ideal;
+        plan.a1_passes += L.a1;
+        plan.a1_passes_before += L.a1_before;
         L = Local();
     }
     plan.blob.resize(plan.blob.size() + 64, 0u);

@@ -673,7 +673,7 @@ int feelgpu_eplan_host_copy(void* plan, void* ctas, int32_t* verts, uint32_t* vi
         stats[4] = (double)hp->nouts;
         stats[5] = hp->lds_wavefronts;
         stats[6] = hp->lds_ideal;
-        stats[7] = 0;
+        stats[7] = hp->a1_passes_before > 0 ? hp->a1_passes / hp->a1_passes_before : 0;
     }
     return FEELGPU_OK;
 }

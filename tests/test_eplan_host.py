@@ -57,7 +57,7 @@ def build_plan(mesh, Xh, ia, ja):
     lib.feelgpu_eplan_host_copy(h, vp(P["ctas"]), ptr(P["verts"], c_i32p), vp(P["visits"]), vp(P["chunks"]),
                                 vp(P["blob"]), vp(P["rows"]), ptr(stats, c_dblp))
     lib.feelgpu_eplan_host_free(h)
-    P["stats"] = dict(zip(["tasks", "iters", "iters_padded", "visits", "outputs", "wavefronts", "wavefronts_ideal"], stats))
+    P["stats"] = dict(zip(["tasks", "iters", "iters_padded", "visits", "outputs", "wavefronts", "wavefronts_ideal", "a1_ratio"], stats))
     return P
 
 

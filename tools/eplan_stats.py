@@ -32,3 +32,4 @@ for t in range(6):
     sel = ty == t
     if sel.any():
         print("  type %d: chunks %d  mean niter %.1f" % (t, sel.sum(), P["chunks"]["niter"][sel].mean()))
+print("phase A1 coordinate reads: modelled passes after / before levelling the vertex slots: %.3f" % st.get("a1_ratio", 0))
