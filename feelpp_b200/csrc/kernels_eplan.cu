@@ -161,34 +161,6 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         if (needzero)   // only when the graph holds entries that no element produces
             for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
         __syncthreads();
-        // ---- next patch: the last warp (it owns no visit: EPLAN_VS <= 32 (EPLAN_WARPS - 1)) takes the next patch id from the
-        // global counter, pulls that patch's data into L2 (the plan is streamed once from HBM) and leaves its header and
-        // vertex ids in shared memory.  Nobody waits for this chain: it is needed after phase B.
-        if (warp == EPLAN_WARPS - 1) {
-            int pn = 0;
-            if (lane == 0) pn = (int)gridDim.x + atomicAdd(sched, 1);
-            pn = __shfl_sync(0xffffffffu, pn, 0);
-            if (pn < ncta) {
-                const uint4* nq = reinterpret_cast<const uint4*>(ctas + pn);
-                uint4 n0 = __ldg(nq);
-                const uint4 n1 = __ldg(nq + 1);
-                int32_t ids[EPLAN_VERTS / 32];
-#pragma unroll
-                for (int k = 0; k < EPLAN_VERTS / 32; ++k) ids[k] = __ldg(&verts[(size_t)pn * EPLAN_VERTS + 32 * k + lane]);
-                prefetch_range(visits + n0.y, (n1.x >> 16) * (ORDER == 2 ? 16u : 4u), lane);
-                prefetch_range(chunks + n0.z, (n1.y & 0xFFFF) * 8u, lane);
-                prefetch_range(rows + n0.w, (n1.y >> 16) * 16u, lane);
-                prefetch_range(reinterpret_cast<const uint4*>(blob) + n1.w, (n1.z >> 16) * 16u, lane);
-#pragma unroll
-                for (int k = 0; k < EPLAN_VERTS / 32; ++k) {
-                    sVid[32 * k + lane] = ids[k];
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(xyz + 4 * (int64_t)ids[k]));
-                }
-                n0.x = (uint32_t)pn;           // (the vertex offset is implied by the fixed stride)
-                if (lane == 0) { sN[2 * (par ^ 1)] = n0; sN[2 * (par ^ 1) + 1] = n1; }
-            } else if (lane == 0)
-                sN[2 * (par ^ 1)].x = (uint32_t)pn;
-        }
         // ---- phase A1: geometry of every element touched by this patch's rows, once (thread = visit) ----
         if (tid < nvisit) {
             const int v = tid;
@@ -270,6 +242,34 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         uint4* sR = reinterpret_cast<uint4*>(sX);
         if (tid < nrows) cp_async<16>(&sR[tid], &rows[sN[2 * par].w + tid]);
 
+        // ---- next patch: before it joins phase B the last warp takes the next patch id from the global counter, pulls that
+        // patch's data into L2 (the plan is streamed once from HBM) and leaves its header and vertex ids in shared memory.
+        // Nobody waits for this chain of three loads: chunks are handed out on demand and the result is needed after phase B.
+        if (warp == EPLAN_WARPS - 1) {
+            int pn = 0;
+            if (lane == 0) pn = (int)gridDim.x + atomicAdd(sched, 1);
+            pn = __shfl_sync(0xffffffffu, pn, 0);
+            if (pn < ncta) {
+                const uint4* nq = reinterpret_cast<const uint4*>(ctas + pn);
+                uint4 n0 = __ldg(nq);
+                const uint4 n1 = __ldg(nq + 1);
+                int32_t ids[EPLAN_VERTS / 32];
+#pragma unroll
+                for (int k = 0; k < EPLAN_VERTS / 32; ++k) ids[k] = __ldg(&verts[(size_t)pn * EPLAN_VERTS + 32 * k + lane]);
+                prefetch_range(visits + n0.y, (n1.x >> 16) * (ORDER == 2 ? 16u : 4u), lane);
+                prefetch_range(chunks + n0.z, (n1.y & 0xFFFF) * 8u, lane);
+                prefetch_range(rows + n0.w, (n1.y >> 16) * 16u, lane);
+                prefetch_range(reinterpret_cast<const uint4*>(blob) + n1.w, (n1.z >> 16) * 16u, lane);
+#pragma unroll
+                for (int k = 0; k < EPLAN_VERTS / 32; ++k) {
+                    sVid[32 * k + lane] = ids[k];
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(xyz + 4 * (int64_t)ids[k]));
+                }
+                n0.x = (uint32_t)pn;           // (the vertex offset is implied by the fixed stride)
+                if (lane == 0) { sN[2 * (par ^ 1)] = n0; sN[2 * (par ^ 1) + 1] = n1; }
+            } else if (lane == 0)
+                sN[2 * (par ^ 1)].x = (uint32_t)pn;
+        }
         // ---- phase B: task chunks, lane = task.  Chunks are sorted by cost and handed out on demand (shared counter); the next
         // chunk's header, first words and positions are fetched while the current one runs.
         {

@@ -1,4 +1,4 @@
 source tools/variants.sh true
-timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -2
 run new
+run new16 -DEPLAN_WARPS=16
 runref old
