@@ -12,6 +12,8 @@
  * reference aborts through CHKERRABORT, feelalg/matrixpetsc.cpp:935); feelgpu_last_error() gives a message.
  * Caller arrays passed to *_create are copied to the device during the call and may be freed afterwards.
  * All work calls are asynchronous on the CUDA stream given (void* = cudaStream_t, NULL = the context's stream).
+ * Assemblies through one pattern must be ordered with respect to each other (one stream, or events): the pattern owns
+ * the coefficient table and the patch counter of its assembly kernel.
  * There is no CPU fallback: without a CUDA device every call fails with FEELGPU_ERR_CUDA.
  */
 #ifndef FEELGPU_H
