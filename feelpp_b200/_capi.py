@@ -77,6 +77,11 @@ GPU_SYMBOLS = {
     "feelgpu_host_alloc_pinned": [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)],
     "feelgpu_host_free_pinned": [C.c_void_p, C.c_void_p],
     "feelgpu_scatter_add": [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "feelgpu_ipc_export": [C.c_void_p, C.c_void_p, C.c_char_p],
+    "feelgpu_ipc_open": [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)],
+    "feelgpu_ipc_close": [C.c_void_p, C.c_void_p],
+    "feelgpu_pattern_set_remote": [C.c_void_p, C.c_int, c_i64p, c_i64p, C.POINTER(C.c_void_p)],
+    "feelgpu_form2_uses_remote": [C.c_void_p, C.c_void_p, C.POINTER(C.c_int)],
     "feelgpu_launch_count": [C.c_void_p, c_i64p],
     "feelgpu_last_timing": [C.c_void_p, c_dblp],
     "feelgpu_set_timing": [C.c_void_p, C.c_int],

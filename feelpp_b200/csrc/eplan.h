@@ -38,6 +38,7 @@
 #define EPLAN_OMAX 7936          // 62 KB row block per CTA: two CTAs per SM next to the 40 KB geometry cache
 #endif
 #define EPLAN_HDRS 128            // chunk headers kept in shared memory (the rest, if any, is read from global memory)
+#define EPLAN_MAXREMOTE 8          // peers a rank's ghost rows can belong to
 #ifndef EPLAN_NSUB
 #define EPLAN_NSUB 1               // short chunks run under one header: measured slower on B200 (coarser hand-out, deeper word stream); kept at 1
 #endif
@@ -104,6 +105,7 @@ struct EPlanHost {
     std::vector<EPlanRow> rows;
     // statistics
     int64_t ntasks = 0, niters = 0, niters_padded = 0, nvisits = 0, nouts = 0;
+    int64_t nomerge_from = INT64_MAX;   // input: rows whose values start at or after this slot stay one segment each (ghost rows: their segments may be redirected to different owners)
     double lds_wavefronts = 0;   // modelled shared-memory wavefronts of the S loads (stiffness) over the whole plan
     double lds_ideal = 0;        // the same without bank conflicts
     double a1_passes = 0, a1_passes_before = 0;   // modelled passes of one coordinate read of phase A1 (per half-warp and corner), after / before the vertex slots were levelled
@@ -119,6 +121,11 @@ struct EPlan {                   // device mirror
     EPlanChunk* d_chunks = nullptr;
     uint32_t* d_blob = nullptr;
     EPlanRow* d_rows = nullptr;
+    // ghost rows written straight into their owners' memory (feelgpu_pattern_set_remote)
+    int nremote = 0;
+    bool remote_fresh = true;    // no assembly has written the current landing buffers yet: the first one stores, later ones may add
+    int64_t remote_lo[EPLAN_MAXREMOTE], remote_hi[EPLAN_MAXREMOTE];
+    double* remote_ptr[EPLAN_MAXREMOTE];
     int* d_sched = nullptr;      // [2] patch counter and exit counter of the persistent kernel (zero between launches)
     int64_t bytes = 0;
     int64_t ntasks = 0, niters = 0, niters_padded = 0, nvisits = 0, nouts = 0;

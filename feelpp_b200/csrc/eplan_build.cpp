@@ -151,8 +151,10 @@ struct Builder {
                     lo[c] = std::min(lo[c], x);
                     hi[c] = std::max(hi[c], x);
                 }
-        double sc[3];
-        for (int c = 0; c < 3; ++c) sc[c] = hi[c] > lo[c] ? 1023.999 / (hi[c] - lo[c]) : 0.0;
+        // one scale for the three axes: the curve's cells stay cubes on a partition whose bounding box is not one
+        double sc[3], ext = 0.0;
+        for (int c = 0; c < 3; ++c) ext = std::max(ext, hi[c] - lo[c]);
+        for (int c = 0; c < 3; ++c) sc[c] = ext > 0.0 ? 1023.999 / ext : 0.0;
         std::vector<uint64_t> key(nNode);
         for (int64_t k = 0; k < nNode; ++k) {
             if (nptr[k] == nptr[k + 1]) { key[k] = ((uint64_t)0x3FFFFFFF << 32) | (uint32_t)k; continue; }
@@ -523,7 +525,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 row.off = rowoff;
                 row.len = len;
                 if (B.ncomp == 1 && L.rows.size() > pc.row0 && L.rows.back().base + (int64_t)L.rows.back().len == row.base &&
-                    L.rows.back().len + len <= 256)
+                    L.rows.back().len + len <= 256 && row.base < plan.nomerge_from)
                     L.rows.back().len += len;
                 else
                     L.rows.push_back(row);

@@ -1,6 +1,7 @@
 // feelgpu_api.cu -- implementation of the C ABI declared in include/feelgpu.h.
 #include "feelgpu_internal.h"
 #include "rowplan.h"
+#include "eplan.h"
 
 #include <algorithm>
 #include <cstring>
@@ -220,6 +221,7 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     pat->trial = trial;
     pat->nRows = nRows;
     pat->nnz = ia[nRows];
+    pat->h_ia_owned_end = ia[std::min<int64_t>(test->nDofOwned, nRows)];
     const int n = test->n;
     const int64_t nElt = test->mesh->nElt;
     int64_t* d_ja = nullptr;
@@ -411,6 +413,16 @@ int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc
     return rc;
 }
 
+int feelgpu_form2_uses_remote(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc, int* yes)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    if (!desc || !yes) ARG_FAIL(pat->ctx, "form2_uses_remote: null argument");
+    const bool eplan = (desc->algorithm == FEELGPU_ALGO_AUTO || desc->algorithm == FEELGPU_ALGO_EPLAN) &&
+                       feelgpu_eplan_supports(pat, desc);
+    *yes = eplan && pat->eplan ? 1 : 0;   // (also on a rank without ghost rows: the answer must agree across ranks)
+    return FEELGPU_OK;
+}
+
 int feelgpu_form1_assemble(feelgpu_space_t sp, const feelgpu_form1_desc* desc, int accumulate, double* b, void* stream)
 {
     if (!sp) return FEELGPU_ERR_ARG;
@@ -491,6 +503,58 @@ int feelgpu_form2_zero_rows(feelgpu_pattern_t pat, int64_t n, const int32_t* row
 }
 
 // ---- memory helpers -----------------------------------------------------------------------------------------
+int feelgpu_ipc_export(feelgpu_context_t ctx, void* device_ptr, unsigned char handle[64])
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!device_ptr || !handle) ARG_FAIL(ctx, "ipc_export: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    cudaIpcMemHandle_t h;
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    CTX_CUDA(ctx, cudaIpcGetMemHandle(&h, device_ptr));
+    std::memcpy(handle, &h, sizeof(h));
+    return FEELGPU_OK;
+}
+int feelgpu_ipc_open(feelgpu_context_t ctx, const unsigned char handle[64], void** device_ptr)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!device_ptr || !handle) ARG_FAIL(ctx, "ipc_open: bad argument");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    CTX_CUDA(ctx, cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return FEELGPU_OK;
+}
+int feelgpu_ipc_close(feelgpu_context_t ctx, void* device_ptr)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    CTX_CUDA(ctx, cudaIpcCloseMemHandle(device_ptr));
+    return FEELGPU_OK;
+}
+
+int feelgpu_pattern_set_remote(feelgpu_pattern_t pat, int n, const int64_t* lo, const int64_t* hi, void* const* target)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = pat->ctx;
+    if (n < 0 || n > EPLAN_MAXREMOTE || (n > 0 && (!lo || !hi || !target))) ARG_FAIL(ctx, "set_remote: bad argument");
+    if (n > 0 && !pat->eplan) {
+        ctx->last_error = "set_remote: the pattern has no entity plan (only that kernel writes to peer memory)";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    const int64_t tail = pat->test->nDofOwned < pat->nRows ? pat->h_ia_owned_end : pat->nnz;
+    for (int k = 0; k < n; ++k)
+        if (lo[k] < tail || hi[k] > pat->nnz || lo[k] > hi[k] || (k > 0 && lo[k] < hi[k - 1]) || !target[k])
+            ARG_FAIL(ctx, "set_remote: ranges must be ascending, disjoint and inside the ghost-row tail");
+    if (!pat->eplan) return FEELGPU_OK;
+    pat->eplan->nremote = n;
+    pat->eplan->remote_fresh = true;
+    for (int k = 0; k < n; ++k) {
+        pat->eplan->remote_lo[k] = lo[k];
+        pat->eplan->remote_hi[k] = hi[k];
+        pat->eplan->remote_ptr[k] = static_cast<double*>(target[k]);
+    }
+    return FEELGPU_OK;
+}
+
 int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr)
 {
     if (!ctx) return FEELGPU_ERR_ARG;

@@ -50,6 +50,7 @@ struct feelgpu_pattern_s {
     feelgpu_context_t ctx;
     feelgpu_space_t test, trial;
     int64_t nRows = 0, nnz = 0;
+    int64_t h_ia_owned_end = 0;  // ia[nDofOwned]: first value slot of the ghost-row tail
     int64_t* d_ia = nullptr;     // [nRows+1]
     int32_t* d_ja32 = nullptr;   // [nnz] column ids (kept for the Dirichlet elimination); null if an id needs more than 31 bits
     // element -> CSR position map, node level: pos[e][i][j] = position of column cluster(l2g_trial[e][j]) (component 0)

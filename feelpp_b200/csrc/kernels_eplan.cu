@@ -16,6 +16,13 @@ namespace {
 
 // out_o = sum_k coef[type][o][k] * (sum over the task's elements of the k-th loaded S entry)   (stiffness)
 // out_o = mass[type][o] * (sum over the task's elements of c J)                                  (mass)
+// value slots [lo, hi) of the CSR array live in another GPU's memory (ghost rows land directly in their owner's buffer)
+struct ERemote {
+    int n, accumulate;
+    int64_t lo[EPLAN_MAXREMOTE], hi[EPLAN_MAXREMOTE];
+    double* ptr[EPLAN_MAXREMOTE];
+};
+
 struct ECoef {
     double coef[EPLAN_MAXTYPES][EPLAN_MAXOUT][EPLAN_MAXLD];
     double mass[EPLAN_MAXTYPES][EPLAN_MAXOUT];
@@ -90,7 +97,8 @@ template <int ORDER, int FORM, int NCOMP>   // FORM 0: mass, 1: stiffness; NCOMP
 __global__ void __launch_bounds__(EPLAN_WARPS * 32, EPLAN_MINB)
 k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, const int32_t* __restrict__ verts, const uint32_t* __restrict__ visits,
         const uint2* __restrict__ chunks, const uint32_t* __restrict__ blob, const uint4* __restrict__ rows,
-        const double* __restrict__ xyz, double* __restrict__ a, int accumulate, int vs, int omax, double cval)
+        const double* __restrict__ xyz, double* __restrict__ a, int accumulate, int vs, int omax, double cval,
+        const ERemote rem)
 {
     static_assert(EPLAN_WARPS * 32 >= EPLAN_VS - 1 && EPLAN_WARPS * 32 >= EPLAN_ROWS && EPLAN_WARPS * 32 >= EPLAN_VERTS &&
                       EPLAN_WARPS * 32 >= EPLAN_HDRS, "one thread per visit / row / vertex / cached chunk header");
@@ -103,19 +111,20 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
     int* sCnt = reinterpret_cast<int*>(sH + EPLAN_HDRS);
     uint4* sN = reinterpret_cast<uint4*>(sCnt + 4);    // [2][2] headers of the current and of the next patch (by parity)
     int32_t* sVid = reinterpret_cast<int32_t*>(sN + 4);   // [EPLAN_VERTS] vertex ids of the next patch
+    double* sZ = reinterpret_cast<double*>(sVid + EPLAN_VERTS);   // [EPLAN_VERTS] z coordinates of the next patch (staging)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     // The CTA is persistent: after patch blockIdx.x it takes patches from a global counter (sched[0]).  Everything a patch's
     // prologue reads from global memory (vertex coordinates and visit record: one of each per thread; row table and chunk
     // headers: asynchronous copies to shared memory) is requested while the previous patch's phase C drains, so no patch
     // but the first pays for the chain header -> vertex id -> coordinates.
-    double px = 0.0, py = 0.0, pz = 0.0;
+    double px = 0.0, py = 0.0;
     uint4 vq = make_uint4(0u, 0u, 0u, 0u);
     auto fetch = [&](const uint4& h0, const uint4& h1, int32_t id) {
         if (tid < (int)(h1.x & 0xFFFF)) {
-            const double2* q = reinterpret_cast<const double2*>(xyz + 4 * (int64_t)id);
-            const double2 p0 = __ldg(q), p1 = __ldg(q + 1);
-            px = p0.x; py = p0.y; pz = p1.x;
+            const double2 p0 = __ldg(reinterpret_cast<const double2*>(xyz + 4 * (int64_t)id));
+            px = p0.x; py = p0.y;
+            cp_async<8>(&sZ[tid], xyz + 4 * (int64_t)id + 2);   // (registers are short while phase C runs)
         }
         if (tid < (int)(h1.x >> 16)) {
             if (ORDER == 2) vq = __ldg(reinterpret_cast<const uint4*>(visits + h0.y) + tid);
@@ -151,12 +160,12 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         const int nverts = c1.x & 0xFFFF, nvisit = c1.x >> 16, nchunk = c1.y & 0xFFFF, nrows = c1.y >> 16;
         const uint32_t nout = c1.z & 0x7FFF, needzero = c1.z & 0x8000;
         // ---- phase A0: the prologue data waiting in registers goes to shared memory ----
+        cp_async_wait();                       // the chunk headers and z
         if (tid < nverts) {
             sX[tid] = px;
             sX[EPLAN_VERTS + tid] = py;
-            sX[2 * EPLAN_VERTS + tid] = pz;
+            sX[2 * EPLAN_VERTS + tid] = sZ[tid];
         }
-        cp_async_wait();                       // the chunk headers
         if (tid == 0) *sCnt = EPLAN_WARPS;     // chunks 0..W-1 are the warps' first ones, the rest is handed out on demand
         if (needzero)   // only when the graph holds entries that no element produces
             for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
@@ -335,9 +344,20 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
             const int64_t base = (int64_t)(((uint64_t)q.y << 32) | q.x);
             const double* src = sO + q.z;
             const int len = (int)q.w;
+            // a ghost row goes over NVLink into the buffer its owner exported (ranges are ordered: the first is the lowest)
+            double* rowp = a + base;
+            int acc = accumulate;
+            if (rem.n > 0 && base >= rem.lo[0]) {
+#pragma unroll 1
+                for (int k = 0; k < rem.n; ++k)
+                    if (base >= rem.lo[k] && base < rem.hi[k]) {
+                        rowp = rem.ptr[k] + (base - rem.lo[k]);
+                        acc = rem.accumulate;
+                    }
+            }
             if (NCOMP == 1) {
-                double* dst = a + base;
-                if (accumulate) {
+                double* dst = rowp;
+                if (acc) {
 #pragma unroll 1
                     for (int i = lane; i < len; i += 32) dst[i] += src[i];
                 } else {
@@ -353,9 +373,9 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
                     for (int c1 = 0; c1 < NCOMP; ++c1)
 #pragma unroll
                         for (int c2 = 0; c2 < NCOMP; ++c2) {
-                            double* dst = a + base + (int64_t)c1 * len * NCOMP + (int64_t)i * NCOMP + c2;
-                            if (c1 == c2) { if (accumulate) *dst += v; else *dst = v; }
-                            else if (!accumulate) *dst = 0.0;
+                            double* dst = rowp + (int64_t)c1 * len * NCOMP + (int64_t)i * NCOMP + c2;
+                            if (c1 == c2) { if (acc) *dst += v; else *dst = v; }
+                            else if (!acc) *dst = 0.0;
                         }
                 }
             }
@@ -373,7 +393,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
 size_t eplan_smem_bytes(const EPlan* p, int form)
 {
     const int nsrec = form == 1 ? 10 : 1;
-    return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax) + EPLAN_HDRS * sizeof(uint2) + 16 + 4 * sizeof(uint4) + EPLAN_VERTS * sizeof(int32_t);
+    return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax) + EPLAN_HDRS * sizeof(uint2) + 16 + 4 * sizeof(uint4) + EPLAN_VERTS * (sizeof(int32_t) + sizeof(double));
 }
 
 template <typename T>
@@ -457,6 +477,7 @@ int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     std::vector<uint16_t> pos((size_t)m->nElt * n * n);
     FEELGPU_CHECK_CUDA(ctx, cudaMemcpy(pos.data(), pat->d_pos, pos.size() * sizeof(uint16_t), cudaMemcpyDeviceToHost));
     EPlanHost hp;
+    if (sp->nDofOwned < pat->nRows) hp.nomerge_from = h_ia[sp->nDofOwned];
     if (!eplan_build_host(sp->order, sp->ncomp, EPLAN_OMAX, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(),
                           m->h_conn.data(), pat->nRows, h_ia, pos.data(), 0, hp)) {
         pat->eplan_note = hp.error;   // not an error: another path stays available
@@ -599,6 +620,15 @@ int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     }
     // stream-ordered upload of the coefficients (one context drives one stream at a time, see feelgpu.h)
     FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_ecoef, &tab, sizeof(ECoef), 0, cudaMemcpyHostToDevice, s));
+    ERemote rem;
+    rem.n = p->nremote;
+    rem.accumulate = accumulate && !p->remote_fresh;   // a landing buffer starts every epoch empty, whatever it holds
+    p->remote_fresh = false;
+    for (int k = 0; k < EPLAN_MAXREMOTE; ++k) {
+        rem.lo[k] = k < p->nremote ? p->remote_lo[k] : 0;
+        rem.hi[k] = k < p->nremote ? p->remote_hi[k] : 0;
+        rem.ptr[k] = k < p->nremote ? p->remote_ptr[k] : nullptr;
+    }
     const size_t sh = eplan_smem_bytes(p, form);
     // persistent CTAs: EPLAN_MINB per SM, each runs every gridDim.x-th patch
     const int grid = (int)std::min<int64_t>(p->ncta, (int64_t)ctx->sm_count * EPLAN_MINB), threads = EPLAN_WARPS * 32;
@@ -609,7 +639,7 @@ int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, cons
         k_eplan<O, F, C><<<grid, threads, sh, s>>>(p->d_ctas, (int)p->ncta, p->d_sched, p->d_verts, p->d_visits,                              \
                                                    reinterpret_cast<const uint2*>(p->d_chunks), p->d_blob,          \
                                                    reinterpret_cast<const uint4*>(p->d_rows), m->d_xyz, a, accumulate, \
-                                                   EPLAN_VS, p->omax, hp.cval[0]);                                  \
+                                                   EPLAN_VS, p->omax, hp.cval[0], rem);                                  \
     } while (0)
 #define ELAUNCH(O, F)                         \
     do {                                      \

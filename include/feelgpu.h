@@ -171,6 +171,27 @@ int feelgpu_form2_zero_rows(feelgpu_pattern_t pattern, int64_t n, const int32_t*
 int feelgpu_scatter_add(feelgpu_context_t ctx, int64_t n, const int64_t* slots, const double* vals, double* a,
                         void* stream);
 
+/* ---- ghost rows over peer memory (one node, NVLink / NVSwitch) ------------------------------------------------------
+ * Instead of stashing off-rank rows and shipping them in MatAssemblyBegin (feelalg/matrixpetsc.cpp:726-760, stash
+ * exchange :750-752), the assembly kernel can store a rank's ghost rows straight into a landing buffer in the owner's
+ * memory while it runs: the owner allocates one buffer per neighbour (feelgpu_malloc), exports it
+ * (feelgpu_ipc_export, a 64-byte cudaIpcMemHandle_t that the caller ships by any means), the neighbour opens it
+ * (feelgpu_ipc_open) and registers it for the slot range of the rows that neighbour owns:
+ *     value slots [lo[k], hi[k]) of this pattern are written to target[k][slot - lo[k]] instead of a_values[slot]
+ * (ranges ascending, disjoint, inside the ghost-row tail; n = 0 restores local stores; at most 8 ranges).  A landing
+ * buffer counts as empty after every set_remote call: the first assembly after it stores into the buffer, later
+ * accumulating assemblies add to it.  Forms that the entity plan does not cover keep writing the local tail:
+ * feelgpu_form2_uses_remote tells the caller which of the two happens for a description (same answer on every rank).
+ * After a device-wide barrier across the ranks (any NCCL collective on the stream), the owner adds the landing
+ * buffers with feelgpu_scatter_add; callers alternate between two sets of buffers so that one barrier per close
+ * is enough (feelpp_b200/distributed.py).                                                                          */
+int feelgpu_ipc_export(feelgpu_context_t ctx, void* device_ptr /* from feelgpu_malloc */, unsigned char handle[64]);
+int feelgpu_ipc_open(feelgpu_context_t ctx, const unsigned char handle[64], void** device_ptr);
+int feelgpu_ipc_close(feelgpu_context_t ctx, void* device_ptr);
+int feelgpu_pattern_set_remote(feelgpu_pattern_t pattern, int n, const int64_t* lo, const int64_t* hi,
+                               void* const* target);
+int feelgpu_form2_uses_remote(feelgpu_pattern_t pattern, const feelgpu_form2_desc* desc, int* yes);
+
 /* ---- device memory helpers for callers without a CUDA runtime of their own ---------------------------------- */
 int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr);
 int feelgpu_free(feelgpu_context_t ctx, void* dptr);

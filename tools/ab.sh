@@ -1,4 +1,5 @@
 source tools/variants.sh true
-run new
-run new16 -DEPLAN_WARPS=16
+run c2
+run c1 -DEPLAN_CUNROLL=1
+run c4 -DEPLAN_CUNROLL=4
 runref old
