@@ -77,6 +77,10 @@ GPU_SYMBOLS = {
     "feelgpu_host_alloc_pinned": [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)],
     "feelgpu_host_free_pinned": [C.c_void_p, C.c_void_p],
     "feelgpu_scatter_add": [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "feelgpu_faces_create": [C.c_void_p, C.c_int64, c_i32p, c_i32p, C.POINTER(C.c_void_p)],
+    "feelgpu_faces_destroy": [C.c_void_p],
+    "feelgpu_form1_assemble_faces": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p],
+    "feelgpu_form2_assemble_faces": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_ipc_export": [C.c_void_p, C.c_void_p, C.c_char_p],
     "feelgpu_ipc_open": [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)],
     "feelgpu_ipc_close": [C.c_void_p, C.c_void_p],
@@ -136,6 +140,7 @@ def host():
         lib.feelhost_graph_get.argtypes = [C.c_void_p, c_i64p, c_i64p]
         lib.feelhost_graph_free.argtypes = [C.c_void_p]
         lib.feelhost_quadrature.argtypes = [C.c_int, C.POINTER(C.c_int), c_dblp, c_dblp]
+        lib.feelhost_face_quadrature.argtypes = [C.c_int, C.POINTER(C.c_int), c_dblp, c_dblp]
         lib.feelhost_nlocaldof.argtypes = [C.c_int]
         lib.feelhost_lagrange_points.argtypes = [C.c_int, c_dblp]
         lib.feelhost_tabulate.argtypes = [C.c_int, C.c_int, c_dblp, c_dblp, c_dblp]

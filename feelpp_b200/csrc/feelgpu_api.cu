@@ -503,6 +503,95 @@ int feelgpu_form2_zero_rows(feelgpu_pattern_t pat, int64_t n, const int32_t* row
 }
 
 // ---- memory helpers -----------------------------------------------------------------------------------------
+int feelgpu_faces_create(feelgpu_mesh_t mesh, int64_t nFaces, const int32_t* element, const int32_t* local_face,
+                         feelgpu_faces_t* out)
+{
+    if (!mesh) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = mesh->ctx;
+    if (!out || nFaces < 0 || (nFaces > 0 && (!element || !local_face))) ARG_FAIL(ctx, "faces_create: bad argument");
+    for (int64_t k = 0; k < nFaces; ++k)
+        if (element[k] < 0 || element[k] >= mesh->nElt || local_face[k] < 0 || local_face[k] > 3)
+            ARG_FAIL(ctx, "faces_create: (element, local face) out of range");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    feelgpu_faces_t fc = new feelgpu_faces_s;
+    fc->mesh = mesh;
+    fc->n = nFaces;
+    const size_t bytes = sizeof(int32_t) * (size_t)std::max<int64_t>(nFaces, 1);
+    CTX_CUDA(ctx, cudaMalloc(&fc->d_elt, bytes));
+    CTX_CUDA(ctx, cudaMalloc(&fc->d_lface, bytes));
+    if (nFaces > 0) {
+        CTX_CUDA(ctx, cudaMemcpy(fc->d_elt, element, sizeof(int32_t) * nFaces, cudaMemcpyHostToDevice));
+        CTX_CUDA(ctx, cudaMemcpy(fc->d_lface, local_face, sizeof(int32_t) * nFaces, cudaMemcpyHostToDevice));
+    }
+    *out = fc;
+    return FEELGPU_OK;
+}
+
+int feelgpu_faces_destroy(feelgpu_faces_t fc)
+{
+    if (!fc) return FEELGPU_ERR_ARG;
+    cudaFree(fc->d_elt);
+    cudaFree(fc->d_lface);
+    delete fc;
+    return FEELGPU_OK;
+}
+
+static int check_face_tables(feelgpu_context_t ctx, const feelgpu_coeff& c, const feelgpu_tables& t)
+{
+    if (t.nq % 4 != 0) ARG_FAIL(ctx, "assemble_faces: tables.nq must be 4 x (points per face)");
+    if (c.kind == FEELGPU_COEFF_FIELD) {
+        ctx->last_error = "assemble_faces: FIELD coefficients are not covered on faces";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    return FEELGPU_OK;
+}
+
+int feelgpu_form1_assemble_faces(feelgpu_space_t sp, feelgpu_faces_t fc, const feelgpu_form1_desc* desc, int accumulate,
+                                 double* b, void* stream)
+{
+    if (!sp) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = sp->ctx;
+    if (!fc || !desc || !b) ARG_FAIL(ctx, "form1_assemble_faces: null argument");
+    if (fc->mesh != sp->mesh) ARG_FAIL(ctx, "form1_assemble_faces: the faces belong to another mesh");
+    if (desc->kind != FEELGPU_FORM1_SOURCE) {
+        ctx->last_error = "form1_assemble_faces: unknown form kind";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    FormParams hp;
+    int rc = fill_params(ctx, desc->kind, desc->coeff, desc->tables, sp, false, &hp);
+    if (rc) return rc;
+    if ((rc = check_face_tables(ctx, desc->coeff, desc->tables))) return rc;
+    if (!accumulate) CTX_CUDA(ctx, cudaMemsetAsync(b, 0, sizeof(double) * sp->nDofWithGhost, s));
+    return fc->n ? feelgpu_launch_form1_faces(sp, fc, hp, desc, b, s) : FEELGPU_OK;
+}
+
+int feelgpu_form2_assemble_faces(feelgpu_pattern_t pat, feelgpu_faces_t fc, const feelgpu_form2_desc* desc, int accumulate,
+                                 double* a, void* stream)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = pat->ctx;
+    if (!fc || !desc || !a) ARG_FAIL(ctx, "form2_assemble_faces: null argument");
+    if (fc->mesh != pat->test->mesh) ARG_FAIL(ctx, "form2_assemble_faces: the faces belong to another mesh");
+    if (desc->kind != FEELGPU_FORM2_MASS) {
+        ctx->last_error = "form2_assemble_faces: only k*idt(u)*id(v) is covered on faces";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    if (!pat->d_pos) {
+        ctx->last_error = "form2_assemble_faces: the pattern was created without the element->slot map";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    FormParams hp;
+    int rc = fill_params(ctx, desc->kind, desc->coeff, desc->tables, pat->test, true, &hp);
+    if (rc) return rc;
+    if ((rc = check_face_tables(ctx, desc->coeff, desc->tables))) return rc;
+    if (!accumulate) CTX_CUDA(ctx, cudaMemsetAsync(a, 0, sizeof(double) * pat->nnz, s));
+    return fc->n ? feelgpu_launch_form2_faces(pat, fc, hp, desc, a, s) : FEELGPU_OK;
+}
+
 int feelgpu_ipc_export(feelgpu_context_t ctx, void* device_ptr, unsigned char handle[64])
 {
     if (!ctx) return FEELGPU_ERR_ARG;

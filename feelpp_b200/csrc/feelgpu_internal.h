@@ -65,6 +65,13 @@ struct feelgpu_pattern_s {
 };
 
 // parameter block copied to the device per assemble call
+struct feelgpu_faces_s {
+    feelgpu_mesh_t mesh = nullptr;
+    int64_t n = 0;
+    int32_t* d_elt = nullptr;    // [n] element of the face
+    int32_t* d_lface = nullptr;  // [n] local face id 0..3
+};
+
 struct FormParams {
     int kind, coeff_kind, n, nq, nf, ncomp, expr_len, pad;
     double cval[3];
@@ -90,6 +97,10 @@ int feelgpu_launch_form2_scatter(feelgpu_pattern_t pat, const FormParams& hp, co
                                  double* a, cudaStream_t s);
 int feelgpu_launch_form1(feelgpu_space_t sp, const FormParams& hp, const feelgpu_form1_desc* desc, double* b,
                          cudaStream_t s);
+int feelgpu_launch_form1_faces(feelgpu_space_t sp, feelgpu_faces_t fc, const FormParams& hp, const feelgpu_form1_desc* desc,
+                               double* b, cudaStream_t s);
+int feelgpu_launch_form2_faces(feelgpu_pattern_t pat, feelgpu_faces_t fc, const FormParams& hp,
+                               const feelgpu_form2_desc* desc, double* a, cudaStream_t s);
 // ---- kernels_on.cu ----
 int feelgpu_launch_zero_rows(feelgpu_pattern_t pat, int n, const int32_t* h_rows, const double* h_x, int strategy,
                              double value_on_diagonal, double* a, double* b, cudaStream_t s);

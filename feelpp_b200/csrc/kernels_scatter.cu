@@ -304,6 +304,91 @@ k_form1(const FormParams* __restrict__ P, DevTables T, int64_t nElt, const doubl
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// boundary faces (feelvf/integrator.hpp:3242-3704): the points q of block f = local face of the tables lie on that face of
+// the reference tet; prod[q] = w[q] * J * |B n_f| (feelpoly/pointsetquadrature.hpp:481-490), n_f the reference normal:
+// (1,1,1)/sqrt(3) for face 0, -e_{f-1} otherwise (feelmesh/refsimplex.hpp:1045-1083)
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double face_measure(const Geo& g, int f)
+{
+    double N[3];
+    if (f == 0) {
+        const double r = sqrt(1.0 / 3.0);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) N[a] = g.B[a][0] * r + g.B[a][1] * r + g.B[a][2] * r;
+    } else {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) N[a] = -(f == 1 ? g.B[a][0] : f == 2 ? g.B[a][1] : g.B[a][2]);
+    }
+    return g.J * sqrt(N[0] * N[0] + N[1] * N[1] + N[2] * N[2]);
+}
+
+// one thread per (face, local dof): b[l2g] += sum_q prod[q] g(x_q) phi_i(q)
+__global__ void __launch_bounds__(256)
+k_form1_faces(const FormParams* __restrict__ P, DevTables T, int64_t nFaces, const int32_t* __restrict__ felt,
+              const int32_t* __restrict__ flocal, const double* __restrict__ xyz, const int4* __restrict__ conn,
+              const int32_t* __restrict__ l2g, int nd, double* __restrict__ b)
+{
+    extern __shared__ double smem[];
+    const int n = P->n, nq = P->nq, nqf = nq / 4, ncomp = P->ncomp;
+    double* s_phi = smem;
+    for (int k = threadIdx.x; k < n * nq; k += blockDim.x) s_phi[k] = T.phi[k];
+    __syncthreads();
+    const int64_t total = nFaces * n;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k = t / n;
+        const int i = (int)(t - k * n);
+        const int64_t e = felt[k];
+        const int f = flocal[k];
+        Geo g;
+        geo_update(xyz, __ldg(&conn[e]), g);
+        const double mf = face_measure(g, f);
+        if (ncomp == 1) {
+            double s = 0;
+            for (int q = f * nqf; q < (f + 1) * nqf; ++q)
+                s += (P->w[q] * mf) * (coeff_at(P, nullptr, g, e, q, nullptr, nullptr) * s_phi[i * nq + q]);
+            atomicAdd(&b[l2g[e * nd + i]], s);
+        } else {
+            for (int c = 0; c < ncomp; ++c) {
+                double s = 0;
+                for (int q = f * nqf; q < (f + 1) * nqf; ++q) s += (P->w[q] * mf) * (P->cval[c] * s_phi[i * nq + q]);
+                atomicAdd(&b[l2g[e * nd + n * c + i]], s);
+            }
+        }
+    }
+}
+
+// one thread per (face, i, j): a[row_i, col_j] += sum_q prod[q] k(x_q) phi_j(q) phi_i(q)
+__global__ void __launch_bounds__(256)
+k_form2_faces_mass(const FormParams* __restrict__ P, DevTables T, int64_t nFaces, const int32_t* __restrict__ felt,
+                   const int32_t* __restrict__ flocal, const double* __restrict__ xyz, const int4* __restrict__ conn,
+                   const int32_t* __restrict__ l2g, int nd, const int64_t* __restrict__ ia,
+                   const uint16_t* __restrict__ pos, double* __restrict__ a)
+{
+    extern __shared__ double smem[];
+    const int n = P->n, nq = P->nq, nqf = nq / 4, ncomp = P->ncomp;
+    double* s_phi = smem;
+    for (int k = threadIdx.x; k < n * nq; k += blockDim.x) s_phi[k] = T.phi[k];
+    __syncthreads();
+    const int64_t total = nFaces * n * n;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k = t / (n * n);
+        const int idx = (int)(t - k * n * n);
+        const int i = idx / n, j = idx - i * n;
+        const int64_t e = felt[k];
+        const int f = flocal[k];
+        Geo g;
+        geo_update(xyz, __ldg(&conn[e]), g);
+        const double mf = face_measure(g, f);
+        double s = 0;
+        for (int q = f * nqf; q < (f + 1) * nqf; ++q)
+            s += (P->w[q] * mf) * (coeff_at(P, nullptr, g, e, q, nullptr, nullptr) * (s_phi[j * nq + q] * s_phi[i * nq + q]));
+        const int64_t row = l2g[e * nd + i];
+        const int64_t p0 = pos[e * (int64_t)(n * n) + idx];
+        for (int c = 0; c < ncomp; ++c) atomicAdd(&a[ia[row + c] + p0 + c], s);
+    }
+}
+
 __global__ void k_scatter_add(int64_t n, const int64_t* __restrict__ slots, const double* __restrict__ vals,
                               double* __restrict__ a)
 {
@@ -478,6 +563,47 @@ int feelgpu_launch_form2_scatter(feelgpu_pattern_t pat, const FormParams& hp, co
         return FEELGPU_ERR_UNSUPPORTED;
     }
 #undef LAUNCH
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    return FEELGPU_OK;
+}
+
+int feelgpu_launch_form1_faces(feelgpu_space_t sp, feelgpu_faces_t fc, const FormParams& hp, const feelgpu_form1_desc* desc,
+                               double* b, cudaStream_t s)
+{
+    feelgpu_context_t ctx = sp->ctx;
+    const FormParams* dP;
+    DevTables T;
+    int rc = upload_tables(ctx, hp, desc->tables, s, &dP, &T);
+    if (rc) return rc;
+    feelgpu_mesh_t m = sp->mesh;
+    const size_t sh = sizeof(double) * (hp.n * hp.nq);
+    const int64_t total = fc->n * hp.n;
+    int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 16);
+    k_form1_faces<<<std::max(grid, 1), 256, sh, s>>>(dP, T, fc->n, fc->d_elt, fc->d_lface, m->d_xyz, m->d_conn, sp->d_l2g,
+                                                     sp->nd, b);
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    return FEELGPU_OK;
+}
+
+int feelgpu_launch_form2_faces(feelgpu_pattern_t pat, feelgpu_faces_t fc, const FormParams& hp,
+                               const feelgpu_form2_desc* desc, double* a, cudaStream_t s)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    const FormParams* dP;
+    DevTables T;
+    int rc = upload_tables(ctx, hp, desc->tables, s, &dP, &T);
+    if (rc) return rc;
+    feelgpu_space_t sp = pat->test;
+    feelgpu_mesh_t m = sp->mesh;
+    const size_t sh = sizeof(double) * (hp.n * hp.nq);
+    const int64_t total = fc->n * hp.n * hp.n;
+    int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 16);
+    if (sh > 48 * 1024)
+        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_form2_faces_mass, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+    k_form2_faces_mass<<<std::max(grid, 1), 256, sh, s>>>(dP, T, fc->n, fc->d_elt, fc->d_lface, m->d_xyz, m->d_conn,
+                                                          sp->d_l2g, sp->nd, pat->d_ia, pat->d_pos, a);
     ctx->launches++;
     FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
     return FEELGPU_OK;

@@ -22,7 +22,7 @@ class Engine:
         self.lib = capi.gpu()
         self.ctx = C.c_void_p()
         check(self.lib.feelgpu_context_create(device, C.byref(self.ctx)), None)
-        self._meshes, self._spaces = {}, {}
+        self._meshes, self._spaces, self._faces = {}, {}, {}
 
     def close(self):
         if self.ctx:
@@ -58,6 +58,17 @@ class Engine:
                                                 ptr(p2c, c_i64p) if p2c is not None else None, C.byref(h)), self.ctx)
             self._spaces[key] = (h, Xh)
         return self._spaces[key][0]
+
+    def faces(self, rng):
+        """device list of the (element, local face) pairs of a face range (feelgpu_faces_create)"""
+        key = builtins_id(rng)
+        if key not in self._faces:
+            h = C.c_void_p()
+            e, f = rng.faces()
+            check(self.lib.feelgpu_faces_create(self.mesh(rng.mesh), len(e), ptr(e, c_i32p), ptr(f, c_i32p), C.byref(h)),
+                  self.ctx)
+            self._faces[key] = (h, rng)
+        return self._faces[key][0]
 
     # ---- raw device memory ----
     def malloc(self, nbytes):
@@ -97,8 +108,8 @@ class _Keep:
         return a.ctypes.data_as(typ)
 
 
-def _fill_tables(keep, order, quad_order, field_order=None):
-    xi, w = hm.im(quad_order)
+def _fill_tables(keep, order, quad_order, field_order=None, faces=False):
+    xi, w = hm.im_faces(quad_order) if faces else hm.im(quad_order)
     phi, dphi = hm.tabulate(order, xi)
     t = Tables()
     t.nq, t.n = len(w), phi.shape[0]
@@ -163,7 +174,7 @@ class BilinearForm:
         d.kind = cl.kind
         d.algorithm = self.algorithm
         fo = cl.coeff.field.space.order if cl.coeff.field is not None else None
-        d.tables = _fill_tables(keep, self.Xh.order, qo, fo)
+        d.tables = _fill_tables(keep, self.Xh.order, qo, fo, isinstance(integ.range, hm.BoundaryFaceRange))
         _fill_coeff(self.eng, keep, cl, d.coeff)
         return d
 
@@ -193,7 +204,11 @@ class BilinearForm:
     def _assemble(self, integ, accumulate):
         keep = _Keep()
         d = self._desc(integ, keep)
-        check(self.eng.lib.feelgpu_form2_assemble(self.pat, C.byref(d), accumulate, self.d_values, None), self.eng.ctx)
+        if isinstance(integ.range, hm.BoundaryFaceRange):
+            check(self.eng.lib.feelgpu_form2_assemble_faces(self.pat, self.eng.faces(integ.range), C.byref(d), accumulate,
+                                                            self.d_values, None), self.eng.ctx)
+        else:
+            check(self.eng.lib.feelgpu_form2_assemble(self.pat, C.byref(d), accumulate, self.d_values, None), self.eng.ctx)
         self.eng.sync()
         for r in keep.refs:
             if isinstance(r, tuple):
@@ -243,14 +258,18 @@ class LinearForm:
         d = Form1Desc()
         d.kind = cl.kind
         fo = cl.coeff.field.space.order if cl.coeff.field is not None else None
-        d.tables = _fill_tables(keep, self.Xh.order, qo, fo)
+        d.tables = _fill_tables(keep, self.Xh.order, qo, fo, isinstance(integ.range, hm.BoundaryFaceRange))
         _fill_coeff(self.eng, keep, cl, d.coeff)
         return d
 
     def _assemble(self, integ, accumulate):
         keep = _Keep()
         d = self._desc(integ, keep)
-        check(self.eng.lib.feelgpu_form1_assemble(self.sp, C.byref(d), accumulate, self.d_values, None), self.eng.ctx)
+        if isinstance(integ.range, hm.BoundaryFaceRange):
+            check(self.eng.lib.feelgpu_form1_assemble_faces(self.sp, self.eng.faces(integ.range), C.byref(d), accumulate,
+                                                            self.d_values, None), self.eng.ctx)
+        else:
+            check(self.eng.lib.feelgpu_form1_assemble(self.sp, C.byref(d), accumulate, self.d_values, None), self.eng.ctx)
         self.eng.sync()
         for r in keep.refs:
             if isinstance(r, tuple):

@@ -91,6 +91,15 @@ int feelhost_quadrature(int order, int* nq, double* xi, double* w)
         if (w) std::memcpy(w, q.w.data(), sizeof(double) * q.nq);
     })
 }
+int feelhost_face_quadrature(int order, int* nq, double* xi, double* w)
+{
+    GUARD({
+        Quadrature q = imFaces(order);
+        *nq = q.nq;
+        if (xi) std::memcpy(xi, q.xi.data(), sizeof(double) * 3 * q.nq);
+        if (w) std::memcpy(w, q.w.data(), sizeof(double) * q.nq);
+    })
+}
 int feelhost_nlocaldof(int order) { return nLocalDofTet(order); }
 int feelhost_lagrange_points(int order, double* pts)
 {

@@ -29,6 +29,38 @@ Quadrature im(int order)
 
 static const double kRefVertex[4][3] = {{-1, -1, -1}, {1, -1, -1}, {-1, 1, -1}, {-1, -1, 1}};
 
+// Face rules: IMTriangle<order> carried onto face f of the reference tet by the face's boundary map (vertices in f2p
+// order, feelmesh/simplexordering.hpp:341-347), weights times the map's area factor (feelpoly/pointsetquadrature.hpp:
+// 696-760, identity permutation).  Result: 4 blocks of nq points, block f = local face f.
+Quadrature imFaces(int order)
+{
+    if (order < 0 || order > FEELGPU_TET_QUAD_MAX_ORDER) throw std::out_of_range("imFaces: quadrature order not tabulated");
+    static const int f2p[4][3] = {{1, 2, 3}, {0, 2, 3}, {0, 1, 3}, {0, 1, 2}};
+    Quadrature q;
+    q.order = order;
+    const int nqf = feelgpu_tri_quad_npts[order];
+    const double* t = feelgpu_tri_quad_rule[order];
+    q.nq = 4 * nqf;
+    q.xi.resize(3 * q.nq);
+    q.w.resize(q.nq);
+    for (int f = 0; f < 4; ++f) {
+        const double *a = kRefVertex[f2p[f][0]], *b = kRefVertex[f2p[f][1]], *c = kRefVertex[f2p[f][2]];
+        double u[3], v[3];
+        for (int d = 0; d < 3; ++d) { u[d] = 0.5 * (b[d] - a[d]); v[d] = 0.5 * (c[d] - a[d]); }
+        const double uu = u[0] * u[0] + u[1] * u[1] + u[2] * u[2], uv = u[0] * v[0] + u[1] * v[1] + u[2] * v[2],
+                     vv = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+        const double area = std::sqrt(uu * vv - uv * uv);
+        for (int k = 0; k < nqf; ++k) {
+            const double s = t[3 * k], r = t[3 * k + 1];
+            const double l0 = -0.5 * (s + r), l1 = 0.5 * (1.0 + s), l2 = 0.5 * (1.0 + r);
+            const int p = f * nqf + k;
+            for (int d = 0; d < 3; ++d) q.xi[3 * p + d] = a[d] * l0 + b[d] * l1 + c[d] * l2;
+            q.w[p] = t[3 * k + 2] * area;
+        }
+    }
+    return q;
+}
+
 std::vector<double> lagrangePoints(int order)
 {
     if (order < 1 || order > 3) throw std::invalid_argument("lagrangePoints: order must be 1, 2 or 3");

@@ -18,6 +18,8 @@ struct Quadrature {
 };
 // im(3, order, simplex) (feelpoly/imsimplex.cpp:8375-8396); throws std::out_of_range beyond the tabulated orders
 Quadrature im(int order);
+// the triangle rule of that order on the 4 faces of the reference tet: 4 blocks of nq/4 points (pointsetquadrature.hpp:696-760)
+Quadrature imFaces(int order);
 
 struct BasisTables {
     int n = 0, nq = 0;

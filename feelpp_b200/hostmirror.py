@@ -38,10 +38,24 @@ def unitCube(m, jitter=0.0, shuffle=False):
 
 
 class BoundaryFaceRange:
-    """boundaryfaces(mesh) (feelmesh/filters.hpp): used by on()"""
+    """boundaryfaces(mesh) (feelmesh/filters.hpp): used by on() and by face integrals.  faces() lists the faces that belong
+    to one element only as (element, local face) pairs in element order (face.element(0).id(), face.pos_first())."""
 
     def __init__(self, mesh):
         self.mesh = mesh
+        self._faces = None
+
+    def faces(self):
+        if self._faces is None:
+            conn = self.mesh.conn.astype(np.int64)
+            npts = self.mesh.numPoints()
+            F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])    # feelmesh/simplexordering.hpp:341-347
+            fv = np.sort(conn[:, F2P], axis=2)
+            key = (fv[..., 0] * npts + fv[..., 1]) * npts + fv[..., 2]
+            _, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
+            e, f = np.nonzero((cnt[inv] == 1).reshape(key.shape))
+            self._faces = (np.ascontiguousarray(e, dtype=np.int32), np.ascontiguousarray(f, dtype=np.int32))
+        return self._faces
 
 
 def boundaryfaces(mesh):
@@ -160,6 +174,18 @@ def im(order):
     xi = np.empty((nq.value, 3))
     w = np.empty(nq.value)
     hcheck(h.feelhost_quadrature(order, C.byref(nq), ptr(xi, c_dblp), ptr(w, c_dblp)))
+    return xi, w
+
+
+def im_faces(order):
+    """the triangle rule of that order carried onto the 4 faces of the reference tet: (xi[4*Qf][3], w[4*Qf]), block f =
+    local face f, weights times the reference-face area factor (feelpoly/pointsetquadrature.hpp:696-760)."""
+    h = capi.host()
+    nq = C.c_int()
+    hcheck(h.feelhost_face_quadrature(order, C.byref(nq), None, None))
+    xi = np.empty((nq.value, 3))
+    w = np.empty(nq.value)
+    hcheck(h.feelhost_face_quadrature(order, C.byref(nq), ptr(xi, c_dblp), ptr(w, c_dblp)))
     return xi, w
 
 

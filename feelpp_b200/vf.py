@@ -248,9 +248,9 @@ class Integrator:
 
 
 def integrate(_range, _expr, _quad=None):
-    """integrate(_range=elements(mesh), _expr=..., [_quad=order]) (feelvf/integrate.hpp:64-98)."""
-    if not isinstance(_range, hm.ElementRange):
-        raise NotImplementedError("only elements(mesh) ranges are accelerated")
+    """integrate(_range=elements(mesh) | boundaryfaces(mesh), _expr=..., [_quad=order]) (feelvf/integrate.hpp:64-98)."""
+    if not isinstance(_range, (hm.ElementRange, hm.BoundaryFaceRange)):
+        raise NotImplementedError("only elements(mesh) and boundaryfaces(mesh) ranges are accelerated")
     return Integrator(_range, _expr, _quad)
 
 

@@ -61,6 +61,7 @@ typedef struct feelgpu_context_s* feelgpu_context_t;
 typedef struct feelgpu_mesh_s* feelgpu_mesh_t;
 typedef struct feelgpu_space_s* feelgpu_space_t;
 typedef struct feelgpu_pattern_s* feelgpu_pattern_t;
+typedef struct feelgpu_faces_s* feelgpu_faces_t;
 
 typedef struct {
     int kind;                     /* FEELGPU_COEFF_*                                                            */
@@ -162,6 +163,23 @@ int feelgpu_form1_assemble_host(feelgpu_space_t space, const feelgpu_form1_desc*
 enum { FEELGPU_ON_ELIMINATION = 1, FEELGPU_ON_SYMMETRIC = 2, FEELGPU_ON_KEEP_DIAGONAL = 4 };
 int feelgpu_form2_zero_rows(feelgpu_pattern_t pattern, int64_t n, const int32_t* rows, const double* values, int strategy,
                             double value_on_diagonal, double* a_values, double* b, void* stream);
+
+/* ---- boundary-face integrals: integrate(_range=boundaryfaces(mesh) | markedfaces(mesh, ...), _expr=...) ------------
+ * Replaces Integrator::assemble(..., mpl::int_<MESH_FACES>, ...) for faces with one adjacent element
+ * (feelvf/integrator.hpp:3242-3704): Neumann terms g*id(v) / inner(g, id(v)) and Robin terms k*idt(u)*id(v).
+ * A range is a list of (element id, local face 0..3) pairs: face.element(0).id(), face.pos_first().
+ * Tables: the caller maps the triangle rule onto the 4 faces of the reference tet as the reference does
+ * (feelpoly/pointsetquadrature.hpp:696-760): tables.nq = 4*Qf, block f = local face f; w already holds the reference-face
+ * area factor; xi are points of the reference tet; phi = basis at those points; dphi unused.  Per face the kernel uses
+ *     prod[q] = w[q] * J * |B n_f|          (pointsetquadrature.hpp:481-490, feelpoly/geomap.hpp:2021-2034)
+ * Coefficients: CONST and EXPR.  accumulate = 0 zeroes the whole target first ('=' on a form).                        */
+int feelgpu_faces_create(feelgpu_mesh_t mesh, int64_t nFaces, const int32_t* element, const int32_t* local_face,
+                         feelgpu_faces_t* faces);
+int feelgpu_faces_destroy(feelgpu_faces_t faces);
+int feelgpu_form1_assemble_faces(feelgpu_space_t space, feelgpu_faces_t faces, const feelgpu_form1_desc* desc,
+                                 int accumulate, double* b /*DEVICE*/, void* stream);
+int feelgpu_form2_assemble_faces(feelgpu_pattern_t pattern, feelgpu_faces_t faces, const feelgpu_form2_desc* desc /*MASS*/,
+                                 int accumulate, double* a_values /*DEVICE*/, void* stream);
 
 /* ---- close(): owner-side accumulation of ghost-row contributions -------------------------------------------------
  * The reference ships stashed off-rank rows inside MatAssemblyBegin/End (feelalg/matrixpetsc.cpp:750-752).  Here the

@@ -573,6 +573,157 @@ int oracle_form1(int kind, int order, int ncomp, int quad_order, int64_t nPts, c
     return 0;
 }
 
+} // extern "C"
+
+namespace {
+
+// ---- boundary-face integrals (feelvf/integrator.hpp:3242-3704) -----------------------------------------------------
+// Face quadrature: the triangle rule IMTriangle<k> on the reference triangle (-1,-1),(1,-1),(-1,1) is mapped onto face f of
+// the reference tet through its boundary map, vertices in f2p order (feelmesh/simplexordering.hpp:341-347), and the weights
+// are multiplied by that map's Jacobian sqrt(det(K^T K)) (feelpoly/pointsetquadrature.hpp:696-760).  Identity permutation:
+// for a boundary face the permutation only reorders the points of these symmetric rules.  In an element the weights become
+//   prod[q] = w_f[q] * J * |B n_f|    (pointsetquadrature.hpp:481-490; n_f the reference normal, feelmesh/refsimplex.hpp:1045-1083,
+//   |B n_f| from geomap.hpp:2021-2034)
+struct FaceTables {
+    int n, Qf;
+    std::vector<double> w, xi, phi;   // [4][Qf], [4][Qf][3], [n][4*Qf]
+};
+
+void ref_normal(int f, double* nrm)
+{
+    if (f == 0) nrm[0] = nrm[1] = nrm[2] = std::sqrt(1.0 / 3.0);
+    else {
+        nrm[0] = nrm[1] = nrm[2] = 0.0;
+        nrm[f - 1] = -1.0;
+    }
+}
+
+FaceTables make_face_tables(int order, int quad_order)
+{
+    FaceTables T;
+    T.n = nloc(order);
+    T.Qf = feelgpu_tri_quad_npts[quad_order];
+    const double* q = feelgpu_tri_quad_rule[quad_order];
+    const int Q = 4 * T.Qf;
+    T.w.resize(Q);
+    T.xi.resize(3 * Q);
+    T.phi.resize(T.n * Q);
+    std::vector<double> p(T.n), dp(T.n * 3);
+    for (int f = 0; f < 4; ++f) {
+        const double* a = REFV[F2P[f][0]];
+        const double* b = REFV[F2P[f][1]];
+        const double* c = REFV[F2P[f][2]];
+        // boundary map of the face: x = a N0 + b N1 + c N2, K = [ (b-a)/2 | (c-a)/2 ], J = sqrt(det(K^T K))
+        double k0[3], k1[3];
+        for (int d = 0; d < 3; ++d) { k0[d] = 0.5 * (b[d] - a[d]); k1[d] = 0.5 * (c[d] - a[d]); }
+        const double g00 = k0[0] * k0[0] + k0[1] * k0[1] + k0[2] * k0[2];
+        const double g01 = k0[0] * k1[0] + k0[1] * k1[1] + k0[2] * k1[2];
+        const double g11 = k1[0] * k1[0] + k1[1] * k1[1] + k1[2] * k1[2];
+        const double Jf = std::sqrt(g00 * g11 - g01 * g01);
+        for (int k = 0; k < T.Qf; ++k) {
+            const double s = q[3 * k], t = q[3 * k + 1];
+            const double N0 = -0.5 * (s + t), N1 = 0.5 * (1.0 + s), N2 = 0.5 * (1.0 + t);
+            const int qq = f * T.Qf + k;
+            for (int d = 0; d < 3; ++d) T.xi[3 * qq + d] = a[d] * N0 + b[d] * N1 + c[d] * N2;
+            T.w[qq] = q[3 * k + 2] * Jf;
+            basis(order).eval(&T.xi[3 * qq], p.data(), dp.data());
+            for (int i = 0; i < T.n; ++i) T.phi[i * Q + qq] = p[i];
+        }
+    }
+    return T;
+}
+
+double face_measure_factor(const Geo& g, int f)
+{
+    double nrm[3], N[3];
+    ref_normal(f, nrm);
+    for (int a = 0; a < 3; ++a) N[a] = g.B[a][0] * nrm[0] + g.B[a][1] * nrm[1] + g.B[a][2] * nrm[2];
+    return g.J * std::sqrt(N[0] * N[0] + N[1] * N[1] + N[2] * N[2]);
+}
+
+inline double face_coeff_at(const oracle_coeff* c, const Geo& g, const FaceTables& T, int q)
+{
+    if (!c || c->kind == ORACLE_COEFF_CONST) return c ? c->value[0] : 1.0;
+    double x[3];
+    geo_xreal(g, &T.xi[3 * q], x);
+    return eval_expr(c, x[0], x[1], x[2]);
+}
+
+} // namespace
+
+extern "C" {
+
+int oracle_face_quadrature(int quad_order, double* xi, double* w)
+{
+    if (quad_order < 0 || quad_order > FEELGPU_TET_QUAD_MAX_ORDER) return -1;
+    FaceTables T = make_face_tables(1, quad_order);
+    if (xi) std::memcpy(xi, T.xi.data(), sizeof(double) * T.xi.size());
+    if (w) std::memcpy(w, T.w.data(), sizeof(double) * T.w.size());
+    return T.Qf;
+}
+
+// form1 on boundary faces: b_i += sum_q prod[q] g(x_q) phi_i(x_q); faces = (element, local face) pairs
+int oracle_form1_faces(int order, int ncomp, int quad_order, const double* xyz, const int32_t* conn, const int32_t* l2g,
+                       int64_t nFaces, const int32_t* felt, const int32_t* flocal, const oracle_coeff* coeff, double* b)
+{
+    if (coeff && coeff->kind == ORACLE_COEFF_FIELD) return -1;
+    FaceTables T = make_face_tables(order, quad_order);
+    const int n = T.n, nd = n * ncomp, Qf = T.Qf, Q = 4 * Qf;
+    for (int64_t k = 0; k < nFaces; ++k) {
+        const int64_t e = felt[k];
+        const int f = flocal[k];
+        const int32_t* v = conn + 4 * e;
+        const double* Gp[4] = {xyz + 3 * (int64_t)v[0], xyz + 3 * (int64_t)v[1], xyz + 3 * (int64_t)v[2],
+                               xyz + 3 * (int64_t)v[3]};
+        Geo g;
+        geo_update(Gp, g);
+        const double mf = face_measure_factor(g, f);
+        for (int c = 0; c < ncomp; ++c)
+            for (int i = 0; i < n; ++i) {
+                double s = 0;
+                for (int q = f * Qf; q < (f + 1) * Qf; ++q) {
+                    const double fq = ncomp == 1 ? face_coeff_at(coeff, g, T, q) : (coeff ? coeff->value[c] : 1.0);
+                    s += (T.w[q] * mf) * (fq * T.phi[i * Q + q]);
+                }
+                b[l2g[e * nd + n * c + i]] += s;
+            }
+    }
+    return 0;
+}
+
+// form2 on boundary faces, k idt(u) id(v) (Robin term): a(row_i, col_j) += sum_q prod[q] k(x_q) phi_j phi_i, all i, j
+int oracle_form2_faces(int order, int ncomp, int quad_order, const double* xyz, const int32_t* conn, const int32_t* l2g,
+                       int64_t nFaces, const int32_t* felt, const int32_t* flocal, const oracle_coeff* coeff,
+                       const int64_t* ia, const int64_t* ja, double* a)
+{
+    if (coeff && coeff->kind == ORACLE_COEFF_FIELD) return -1;
+    FaceTables T = make_face_tables(order, quad_order);
+    const int n = T.n, nd = n * ncomp, Qf = T.Qf, Q = 4 * Qf;
+    for (int64_t k = 0; k < nFaces; ++k) {
+        const int64_t e = felt[k];
+        const int f = flocal[k];
+        const int32_t* v = conn + 4 * e;
+        const double* Gp[4] = {xyz + 3 * (int64_t)v[0], xyz + 3 * (int64_t)v[1], xyz + 3 * (int64_t)v[2],
+                               xyz + 3 * (int64_t)v[3]};
+        Geo g;
+        geo_update(Gp, g);
+        const double mf = face_measure_factor(g, f);
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < n; ++j) {
+                double s = 0;
+                for (int q = f * Qf; q < (f + 1) * Qf; ++q)
+                    s += (T.w[q] * mf) * (face_coeff_at(coeff, g, T, q) * (T.phi[j * Q + q] * T.phi[i * Q + q]));
+                for (int c = 0; c < ncomp; ++c) {
+                    const int64_t row = l2g[e * nd + n * c + i], col = l2g[e * nd + n * c + j];
+                    const int64_t* lo = std::lower_bound(ja + ia[row], ja + ia[row + 1], col);
+                    if (lo == ja + ia[row + 1] || *lo != col) return -2;
+                    a[lo - ja] += s;
+                }
+            }
+    }
+    return 0;
+}
+
 // CPU baseline with P worker threads: contiguous element blocks ("partitions"); a row is owned by the lowest block
 // touching it (feeldiscr/doftablempi.hpp:138-200); contributions to rows owned by another block go to a private
 // stash and are added by the owner after the loop -- the shape of MatSetValuesLocal + MatAssemblyBegin/End

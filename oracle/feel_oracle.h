@@ -68,6 +68,16 @@ int oracle_zero_rows(int64_t nRows, const int64_t* ia, const int64_t* ja, int64_
                      int strategy, double value_on_diagonal, double* a, double* b);
 int oracle_local_matrix(int kind, int order, int ncomp, int quad_order, const double* G /*[4][3]*/,
                         const oracle_coeff* coeff, double* Ae);
+/* boundary-face integrals (feelvf/integrator.hpp:3242-3704): faces = (element, local face 0..3) pairs; face rule =
+ * IMTriangle<quad_order> mapped onto the faces of the reference tet (pointsetquadrature.hpp:696-760).
+ * oracle_face_quadrature returns the points per face and fills xi[4][Qf][3], w[4][Qf] (weights include the
+ * reference-face Jacobian). */
+int oracle_face_quadrature(int quad_order, double* xi, double* w);
+int oracle_form1_faces(int order, int ncomp, int quad_order, const double* xyz, const int32_t* conn, const int32_t* l2g,
+                       int64_t nFaces, const int32_t* felt, const int32_t* flocal, const oracle_coeff* coeff, double* b);
+int oracle_form2_faces(int order, int ncomp, int quad_order, const double* xyz, const int32_t* conn, const int32_t* l2g,
+                       int64_t nFaces, const int32_t* felt, const int32_t* flocal, const oracle_coeff* coeff,
+                       const int64_t* ia, const int64_t* ja, double* a);
 /* multi-threaded CPU baseline: P threads each on a contiguous element block with a private value array
  * merged at the end (shape of the reference's `mpirun -np P` run); returns seconds of the element loop */
 double oracle_form2_threads(int kind, int order, int ncomp, int quad_order,

@@ -46,6 +46,10 @@ def lib():
         L.oracle_form1.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, c_dblp, C.c_int64, c_i32p, c_i32p,
                                    C.POINTER(OCoeff), C.c_int64, C.c_int64, c_dblp]
         L.oracle_local_matrix.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, c_dblp, C.POINTER(OCoeff), c_dblp]
+        L.oracle_face_quadrature.argtypes = [C.c_int, c_dblp, c_dblp]
+        ff = [C.c_int, C.c_int, C.c_int, c_dblp, c_i32p, c_i32p, C.c_int64, c_i32p, c_i32p, C.POINTER(OCoeff)]
+        L.oracle_form1_faces.argtypes = ff + [c_dblp]
+        L.oracle_form2_faces.argtypes = ff + [c_i64p, c_i64p, c_dblp]
         _lib = L
     return _lib
 
@@ -163,6 +167,59 @@ def form1(order, ncomp, quad_order, xyz, conn, l2g, ndof, coeff=None, b=None):
     lib().oracle_form1(0, order, ncomp, quad_order, xyz.shape[0], _p(xyz, c_dblp), conn.shape[0], _p(conn, c_i32p),
                        _p(l2g, c_i32p), C.byref(coeff.c), 0, conn.shape[0], _p(b, c_dblp))
     return b
+
+
+def face_quadrature(quad_order):
+    """(xi[4][Qf][3], w[4][Qf]): IMTriangle<quad_order> mapped onto the four faces of the reference tet"""
+    qf = lib().oracle_face_quadrature(quad_order, None, None)
+    assert qf > 0
+    xi, w = np.empty((4, qf, 3)), np.empty((4, qf))
+    lib().oracle_face_quadrature(quad_order, _p(xi, c_dblp), _p(w, c_dblp))
+    return xi, w
+
+
+def boundary_faces(conn, npts):
+    """(element, local face) of every face that belongs to one element only, in element order"""
+    conn = np.asarray(conn, dtype=np.int64)
+    F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])   # feelmesh/simplexordering.hpp:341-347
+    fv = np.sort(conn[:, F2P], axis=2)
+    key = (fv[..., 0] * npts + fv[..., 1]) * npts + fv[..., 2]
+    _, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
+    e, f = np.nonzero((cnt[inv] == 1).reshape(key.shape))
+    return e.astype(np.int32), f.astype(np.int32)
+
+
+def form1_faces(order, ncomp, quad_order, xyz, conn, l2g, ndof, felt, flocal, coeff=None, b=None):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    l2g = np.ascontiguousarray(l2g, dtype=np.int32)
+    felt = np.ascontiguousarray(felt, dtype=np.int32)
+    flocal = np.ascontiguousarray(flocal, dtype=np.int32)
+    if b is None:
+        b = np.zeros(ndof)
+    coeff = coeff or Coeff()
+    rc = lib().oracle_form1_faces(order, ncomp, quad_order, _p(xyz, c_dblp), _p(conn, c_i32p), _p(l2g, c_i32p), len(felt),
+                                  _p(felt, c_i32p), _p(flocal, c_i32p), C.byref(coeff.c), _p(b, c_dblp))
+    assert rc == 0, rc
+    return b
+
+
+def form2_faces(order, ncomp, quad_order, xyz, conn, l2g, ia, ja, felt, flocal, coeff=None, a=None):
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    l2g = np.ascontiguousarray(l2g, dtype=np.int32)
+    felt = np.ascontiguousarray(felt, dtype=np.int32)
+    flocal = np.ascontiguousarray(flocal, dtype=np.int32)
+    ia = np.ascontiguousarray(ia, dtype=np.int64)
+    ja = np.ascontiguousarray(ja, dtype=np.int64)
+    if a is None:
+        a = np.zeros(int(ia[-1]))
+    coeff = coeff or Coeff()
+    rc = lib().oracle_form2_faces(order, ncomp, quad_order, _p(xyz, c_dblp), _p(conn, c_i32p), _p(l2g, c_i32p), len(felt),
+                                  _p(felt, c_i32p), _p(flocal, c_i32p), C.byref(coeff.c), _p(ia, c_i64p), _p(ja, c_i64p),
+                                  _p(a, c_dblp))
+    assert rc == 0, rc
+    return a
 
 
 def local_matrix(kind, order, ncomp, quad_order, G, coeff=None):
