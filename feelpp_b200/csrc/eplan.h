@@ -38,6 +38,7 @@
 #define EPLAN_OMAX 7936          // 62 KB row block per CTA: two CTAs per SM next to the 40 KB geometry cache
 #endif
 #define EPLAN_HDRS 128            // chunk headers kept in shared memory (the rest, if any, is read from global memory)
+#define EPLAN_PADRES 16            // row-block slots the packing pass holds back for phase pads (see eplan_build.cpp)
 #define EPLAN_MAXREMOTE 8          // peers a rank's ghost rows can belong to
 #ifndef EPLAN_NSUB
 #define EPLAN_NSUB 1               // short chunks run under one header: measured slower on B200 (coarser hand-out, deeper word stream); kept at 1

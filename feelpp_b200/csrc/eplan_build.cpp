@@ -91,7 +91,7 @@ struct CtaSeg {
     int64_t nb, ne;                 // node range along the curve
     uint32_t vert_off, visit_off;
     uint16_t nverts, nvisit;
-    uint32_t nout;
+    uint32_t nout, npad = 0;
 };
 
 struct Local {                      // per-thread output, concatenated at the end
@@ -446,7 +446,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 }
                 addp = (uint32_t)newpts.size();
                 const uint32_t len = (uint32_t)B.row_len(node);
-                if (rows > 0 && (nv + addv > EPLAN_VS - 1 || np + addp > EPLAN_VERTS || nout + len > (uint32_t)omax ||
+                if (rows > 0 && (nv + addv > EPLAN_VS - 1 || np + addp > EPLAN_VERTS || nout + len > (uint32_t)omax - (B.ncomp == 1 ? EPLAN_PADRES : 0) ||
                                  rows >= EPLAN_ROWS))
                     break;
                 if (addv > EPLAN_VS - 1 || addp > EPLAN_VERTS || 1 + len > (uint32_t)omax) {
@@ -506,29 +506,76 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         std::vector<uint32_t> pool, lanes;    // remaining tasks of a type; tasks of every chunk lane
         struct ChunkTmp { uint8_t type, niter; uint32_t first, count; int cost; };
         std::vector<ChunkTmp> ctmp;
+        std::vector<uint32_t> noff, segoff, pads;
         for (int64_t c = nCta * t / nthreads; c < nCta * (t + 1) / nthreads; ++c) {
             CtaSeg& sg = segs[c];
             for (int ty = 0; ty < S.ntypes; ++ty) tasks[ty].clear();
             iterw.clear();
             Local::PerCta pc;
             pc.row0 = (uint32_t)L.rows.size();
-            uint32_t rowoff = 1;
-            // rows in CSR order: neighbours in memory are neighbours in the row block, and runs of them are written as one
-            // segment (scalar spaces; pieces of <= 256 values so that the warps share long runs)
+            // rows in CSR order: runs that are contiguous in memory are written as one segment (scalar spaces; pieces of
+            // <= 256 values).  Phase C moves a segment with one bulk copy (TMA) when the segment starts at the same 16-byte
+            // phase in the row block as in the CSR array, i.e. when slot and base have the same parity; the order of the
+            // segments inside the row block is free, so they are dealt greedily to keep the parities equal (a segment of odd
+            // length flips the phase); the few that cannot be matched are copied by the warps.
             cnodes.assign(B.order_.begin() + sg.nb, B.order_.begin() + sg.ne);
             std::sort(cnodes.begin(), cnodes.end(), [&](int32_t x, int32_t y) { return B.ia[(int64_t)x * B.ncomp] < B.ia[(int64_t)y * B.ncomp]; });
+            noff.assign(cnodes.size(), 0);
+            {
+                struct SegTmp { int64_t base; uint32_t len, k0, k1; };
+                std::vector<SegTmp> st;
+                for (size_t k = 0; k < cnodes.size(); ++k) {
+                    const int64_t node = cnodes[k];
+                    const uint32_t len = (uint32_t)B.row_len(node);
+                    const int64_t base = B.ia[node * B.ncomp];
+                    if (B.ncomp == 1 && !st.empty() && st.back().base + (int64_t)st.back().len == base &&
+                        st.back().len + len <= 256 && base < plan.nomerge_from) {
+                        st.back().len += len;
+                        st.back().k1 = (uint32_t)k + 1;
+                    } else
+                        st.push_back(SegTmp{base, len, (uint32_t)k, (uint32_t)k + 1});
+                }
+                // a walk on the two phases: a segment of even length stays, one of odd length crosses over; when the phase has
+                // nothing left a one-slot pad crosses (EPLAN_PADRES slots are held back for that by the packing pass)
+                std::vector<uint32_t> queue[2][2];      // [base parity][length parity]
+                for (size_t i = 0; i < st.size(); ++i) queue[st[i].base & 1][st[i].len & 1].push_back((uint32_t)i);
+                size_t qh[2][2] = {{0, 0}, {0, 0}};
+                auto left = [&](int b, int l) { return queue[b][l].size() - qh[b][l]; };
+                uint32_t off = 1;      // slot 0 of the row block is the trash cell
+                segoff.assign(st.size(), 0);
+                pads.clear();
+                for (size_t placed = 0; placed < st.size(); ++placed) {
+                    int p = (int)(off & 1), b, l;
+                    if (left(p, 0)) { b = p; l = 0; }
+                    else if (left(p, 1)) { b = p; l = 1; }
+                    else if (B.ncomp == 1 && sg.nout + (uint32_t)pads.size() + 1 <= (uint32_t)omax) {
+                        pads.push_back(off++);           // (the values still to place fit behind the pad)
+                        --placed;
+                        continue;
+                    } else { b = p ^ 1; l = left(b, 1) ? 1 : 0; }
+                    const uint32_t i = queue[b][l][qh[b][l]++];
+                    segoff[i] = off;
+                    off += st[i].len;
+                }
+                sg.nout = off;
+                sg.npad = (uint32_t)pads.size();
+                for (size_t i = 0; i < st.size(); ++i) {
+                    EPlanRow row;
+                    row.base = st[i].base;
+                    row.off = segoff[i];
+                    row.len = st[i].len;
+                    L.rows.push_back(row);
+                    uint32_t o = segoff[i];
+                    for (uint32_t k = st[i].k0; k < st[i].k1; ++k) {
+                        noff[k] = o;
+                        o += (uint32_t)B.row_len(cnodes[k]);
+                    }
+                }
+            }
             for (size_t k = 0; k < cnodes.size(); ++k) {
                 const int64_t node = cnodes[k];
                 const uint32_t len = (uint32_t)B.row_len(node);
-                EPlanRow row;
-                row.base = B.ia[node * B.ncomp];
-                row.off = rowoff;
-                row.len = len;
-                if (B.ncomp == 1 && L.rows.size() > pc.row0 && L.rows.back().base + (int64_t)L.rows.back().len == row.base &&
-                    L.rows.back().len + len <= 256 && row.base < plan.nomerge_from)
-                    L.rows.back().len += len;
-                else
-                    L.rows.push_back(row);
+                const uint32_t rowoff = noff[k];
                 ent.clear();
                 for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) B.unit_entries(q, ent);
                 std::sort(ent.begin(), ent.end());
@@ -565,7 +612,6 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                     tasks[tk.type].push_back(tk);
                     g0 = g1;
                 }
-                rowoff += len;
             }
             pc.nrows = (uint32_t)L.rows.size() - pc.row0;
             // ---- renumber the visit slots: every half-warp wants 16 distinct bank pairs (slot mod 16) per iteration, which
@@ -777,6 +823,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             for (int ty = 0; ty < S.ntypes; ++ty)
                 for (const Task& tk : tasks[ty])
                     for (int o = 0; o < S.type[ty].nout; ++o) covered[tk.out[o]] = 1;
+            for (uint32_t z : pads) covered[z] = 1;
             pc.needzero = 0;
             for (uint32_t z = 1; z < sg.nout; ++z)
                 if (!covered[z]) pc.needzero = 1;
@@ -870,7 +917,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             ct.nout = (uint16_t)(sg.nout | (pc.needzero ? 0x8000u : 0u));
             ct.blob_q0 = qb + pc.q0;
             ct.blob_nq = (uint16_t)pc.nq;
-            plan.nouts += sg.nout - 1;
+            plan.nouts += sg.nout - 1 - sg.npad;
             ++c;
         }
         plan.ntasks += L.ntasks;

@@ -161,6 +161,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         const uint32_t nout = c1.z & 0x7FFF, needzero = c1.z & 0x8000;
         // ---- phase A0: the prologue data waiting in registers goes to shared memory ----
         cp_async_wait();                       // the chunk headers and z
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the copy engine has read the previous row block
         if (tid < nverts) {
             sX[tid] = px;
             sX[EPLAN_VERTS + tid] = py;
@@ -331,6 +332,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
                 }
             }
         }
+        if (NCOMP == 1) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // phase C reads the row block through the copy engine
         cp_async_wait();   // the row table
         __syncthreads();
 
@@ -338,33 +340,69 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         const bool has_next = (int)sN[2 * (par ^ 1)].x < ncta;
         if (has_next) fetch(sN[2 * (par ^ 1)], sN[2 * (par ^ 1) + 1], tid < EPLAN_VERTS ? sVid[tid] : 0);
 
-        // ---- phase C: the CTA's row block goes to the CSR value array, every value once ----
-        for (int r = warp; r < nrows; r += EPLAN_WARPS) {
-            const uint4 q = sR[r];
-            const int64_t base = (int64_t)(((uint64_t)q.y << 32) | q.x);
-            const double* src = sO + q.z;
-            const int len = (int)q.w;
-            // a ghost row goes over NVLink into the buffer its owner exported (ranges are ordered: the first is the lowest)
-            double* rowp = a + base;
-            int acc = accumulate;
+        // ---- phase C: the patch's row block goes to the CSR value array, every value once ----
+        // a ghost row goes over NVLink into the buffer its owner exported (ranges are ordered: the first is the lowest)
+        auto resolve = [&](int64_t base, int& acc) {
+            double* p = a + base;
+            acc = accumulate;
             if (rem.n > 0 && base >= rem.lo[0]) {
 #pragma unroll 1
                 for (int k = 0; k < rem.n; ++k)
                     if (base >= rem.lo[k] && base < rem.hi[k]) {
-                        rowp = rem.ptr[k] + (base - rem.lo[k]);
+                        p = rem.ptr[k] + (base - rem.lo[k]);
                         acc = rem.accumulate;
                     }
             }
-            if (NCOMP == 1) {
-                double* dst = rowp;
-                if (acc) {
-#pragma unroll 1
-                    for (int i = lane; i < len; i += 32) dst[i] += src[i];
-                } else {
-#pragma unroll 1
-                    for (int i = lane; i < len; i += 32) dst[i] = src[i];
-                }
-            } else {
+            return p;
+        };
+        if (NCOMP == 1) {
+            // Scalar spaces: thread = row segment.  A segment that starts on the same 16-byte phase in the row block as in
+            // the CSR array (the host plan arranges it for all but a few) is one bulk copy shared -> global (TMA; a bulk
+            // reduction for '+='), plus at most one value by hand at either end; the copy engine reads the row block while
+            // the CTA goes on.  The rest is copied by the warp.
+            double* dst = nullptr;
+            uint32_t soff = 0, len = 0;
+            int acc = 0;
+            bool byhand = false;
+            if (tid < nrows) {
+                const uint4 q = sR[tid];
+                dst = resolve((int64_t)(((uint64_t)q.y << 32) | q.x), acc);
+                soff = q.z;
+                len = q.w;
+                const uint32_t dphase = (uint32_t)(reinterpret_cast<uintptr_t>(dst) >> 3) & 1u;
+                if (dphase == (soff & 1u)) {
+                    const uint32_t head = dphase, nmid = (len - head) & ~1u;     // len >= 1
+                    if (head) { if (acc) dst[0] += sO[soff]; else dst[0] = sO[soff]; }
+                    if (nmid) {
+                        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(sO + soff + head);
+                        if (acc)
+                            asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f64 [%0], [%1], %2;"
+                                         ::"l"(dst + head), "r"(sa), "r"(nmid * 8u) : "memory");
+                        else
+                            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                                         ::"l"(dst + head), "r"(sa), "r"(nmid * 8u) : "memory");
+                    }
+                    if ((len - head) & 1u) { if (acc) dst[len - 1] += sO[soff + len - 1]; else dst[len - 1] = sO[soff + len - 1]; }
+                } else
+                    byhand = true;
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            unsigned todo = __ballot_sync(0xffffffffu, byhand);
+            while (todo) {
+                const int l = __ffs(todo) - 1;
+                todo &= todo - 1;
+                double* d = reinterpret_cast<double*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dst), l));
+                const uint32_t so = __shfl_sync(0xffffffffu, soff, l), n = __shfl_sync(0xffffffffu, len, l);
+                const int ac = __shfl_sync(0xffffffffu, acc, l);
+                for (uint32_t i = lane; i < n; i += 32) { if (ac) d[i] += sO[so + i]; else d[i] = sO[so + i]; }
+            }
+        } else {
+            for (int r = warp; r < nrows; r += EPLAN_WARPS) {
+                const uint4 q = sR[r];
+                const double* src = sO + q.z;
+                const int len = (int)q.w;
+                int acc;
+                double* rowp = resolve((int64_t)(((uint64_t)q.y << 32) | q.x), acc);
                 // product space, block = v * Id: component row c1 starts at base + c1*len*NCOMP
 #pragma unroll 1
                 for (int i = lane; i < len; i += 32) {
@@ -383,6 +421,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         if (!has_next) break;
         __syncthreads();   // phase C has read the row table and the row block
     }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     // the last CTA to leave rearms the counters for the next launch
     if (tid == 0 && atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {
         sched[0] = 0;

@@ -138,7 +138,14 @@ def interpret(P, mesh, order, nnz, form, coef, mass):
                     live = opos[o] != 0
                     out[opos[o][live]] = v[live]
                     np.add.at(hit, opos[o][live], 1)
-        assert hit[1:nout].max(initial=1) == 1 and (needzero or hit[1:nout].min(initial=1) == 1), "every slot once"
+        # slots of the row block: row segments (each written exactly once unless the block is zero-filled first) and the
+        # one-slot pads that keep a segment on the 16-byte phase of its CSR position (never written, never copied)
+        inrow = np.zeros(P["omax"], dtype=bool)
+        for rw in P["rows"][ct["row_off"]:ct["row_off"] + ct["nrows"]]:
+            assert not inrow[int(rw["off"]):int(rw["off"]) + int(rw["len"])].any(), "row segments overlap"
+            inrow[int(rw["off"]):int(rw["off"]) + int(rw["len"])] = True
+        assert not inrow[0] and not inrow[nout:].any() and hit[~inrow][1:].max(initial=0) == 0
+        assert hit[inrow].max(initial=1) == 1 and (needzero or hit[inrow].min(initial=1) == 1), "every slot once"
         for rw in P["rows"][ct["row_off"]:ct["row_off"] + ct["nrows"]]:
             b, o, ln = int(rw["base"]), int(rw["off"]), int(rw["len"])
             a[b:b + ln] = out[o:o + ln]

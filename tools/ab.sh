@@ -1,5 +1,4 @@
 source tools/variants.sh true
-run c2
-run c1 -DEPLAN_CUNROLL=1
-run c4 -DEPLAN_CUNROLL=4
+timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -2
+run new
 runref old

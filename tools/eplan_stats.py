@@ -33,3 +33,7 @@ for t in range(6):
     if sel.any():
         print("  type %d: chunks %d  mean niter %.1f" % (t, sel.sum(), P["chunks"]["niter"][sel].mean()))
 print("phase A1 coordinate reads: modelled passes after / before levelling the vertex slots: %.3f" % st.get("a1_ratio", 0))
+r = P["rows"]
+mis = ((r["base"] ^ r["off"].astype(np.int64)) & 1) == 1
+print("row segments: %d (%.1f per CTA, mean length %.1f); parity mismatch (copied by warps, not by TMA): %d = %.2f %% of the values" % (
+    len(r), len(r) / len(P["ctas"]), r["len"].mean(), mis.sum(), 100.0 * r["len"][mis].sum() / r["len"].sum()))
