@@ -503,6 +503,15 @@ int feelgpu_form2_zero_rows(feelgpu_pattern_t pat, int64_t n, const int32_t* row
 }
 
 // ---- memory helpers -----------------------------------------------------------------------------------------
+int feelgpu_matvec(feelgpu_pattern_t pat, const double* a_values, const double* x, double* y, void* stream)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = pat->ctx;
+    if (!a_values || !x || !y) ARG_FAIL(ctx, "matvec: null argument");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    return feelgpu_launch_matvec(pat, a_values, x, y, stream ? (cudaStream_t)stream : ctx->stream);
+}
+
 int feelgpu_faces_create(feelgpu_mesh_t mesh, int64_t nFaces, const int32_t* element, const int32_t* local_face,
                          feelgpu_faces_t* out)
 {

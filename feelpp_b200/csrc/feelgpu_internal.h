@@ -102,6 +102,7 @@ int feelgpu_launch_form1_faces(feelgpu_space_t sp, feelgpu_faces_t fc, const For
 int feelgpu_launch_form2_faces(feelgpu_pattern_t pat, feelgpu_faces_t fc, const FormParams& hp,
                                const feelgpu_form2_desc* desc, double* a, cudaStream_t s);
 // ---- kernels_on.cu ----
+int feelgpu_launch_matvec(feelgpu_pattern_t pat, const double* a, const double* x, double* y, cudaStream_t s);
 int feelgpu_launch_zero_rows(feelgpu_pattern_t pat, int n, const int32_t* h_rows, const double* h_x, int strategy,
                              double value_on_diagonal, double* a, double* b, cudaStream_t s);
 // ---- kernels_rowplan.cu ----

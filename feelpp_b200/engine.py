@@ -227,6 +227,20 @@ class BilinearForm:
     def values(self):
         return self.eng.to_host(self.d_values, max(self.nnz, 1))[:self.nnz]
 
+    def multVector(self, x):
+        """y = A x on the device (MatrixPetsc::multVector, feelalg/matrixpetsc.cpp:998-1062); x, y host arrays here"""
+        dx = self.eng.to_device(np.ascontiguousarray(x, dtype=np.float64))
+        dy = self.eng.malloc(8 * max(self.Xh.nDof(), 1))
+        check(self.eng.lib.feelgpu_matvec(self.pat, self.d_values, dx, dy, None), self.eng.ctx)
+        y = self.eng.to_host(dy, max(self.Xh.nDof(), 1))[:self.Xh.nDof()]
+        self.eng.free(dx)
+        self.eng.free(dy)
+        return y
+
+    def energy(self, v, u):
+        """v^T A u (MatrixPetsc::energy, feelalg/matrixpetsc.cpp:2132-2170)"""
+        return float(np.dot(v, self.multVector(u)))
+
     def plan_stats(self):
         st = np.zeros(10, dtype=np.int64)
         check(self.eng.lib.feelgpu_pattern_plan_stats(self.pat, ptr(st, c_i64p)), self.eng.ctx)

@@ -164,6 +164,11 @@ enum { FEELGPU_ON_ELIMINATION = 1, FEELGPU_ON_SYMMETRIC = 2, FEELGPU_ON_KEEP_DIA
 int feelgpu_form2_zero_rows(feelgpu_pattern_t pattern, int64_t n, const int32_t* rows, const double* values, int strategy,
                             double value_on_diagonal, double* a_values, double* b, void* stream);
 
+/* ---- device hand-off: y = A x on the assembled CSR (MatrixPetsc::multVector -> MatMult, feelalg/matrixpetsc.cpp:998-1062;
+ * with it MatrixPetsc::energy :2132-2170 is a dot product).  Sequential matrices (one space, identity cluster numbering);
+ * x [nDof], y [nRows] DEVICE.  The matrix never leaves the GPU between assembly, on() and the products of a Krylov loop. */
+int feelgpu_matvec(feelgpu_pattern_t pattern, const double* a_values, const double* x, double* y, void* stream);
+
 /* ---- boundary-face integrals: integrate(_range=boundaryfaces(mesh) | markedfaces(mesh, ...), _expr=...) ------------
  * Replaces Integrator::assemble(..., mpl::int_<MESH_FACES>, ...) for faces with one adjacent element
  * (feelvf/integrator.hpp:3242-3704): Neumann terms g*id(v) / inner(g, id(v)) and Robin terms k*idt(u)*id(v).

@@ -171,6 +171,32 @@ def test_host_output_variant(engine, meshes):
     check_values(vals, ref, scale, "assemble_host")
 
 
+@pytest.mark.parametrize("order,ncomp", [(1, 1), (2, 1), (2, 3)])
+def test_matvec_and_energy(engine, meshes, order, ncomp):
+    """device hand-off: y = A x on the assembled CSR (MatMult, feelalg/matrixpetsc.cpp:998-1062) against scipy on the
+    oracle's matrix; K 1 = 0 and u^T K u = |grad u|^2 for a linear u (reference tests test_laplaciant.cpp:108-126)"""
+    import scipy.sparse as sps
+    mesh = meshes["jit"]
+    Xh = fpp.FunctionSpace(mesh, order, ncomp)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine)
+    a.assign(integrate(_range=elements(mesh), _expr=inner(gradt(u), grad(v)) if ncomp > 1 else gradt(u) * trans(grad(v))))
+    ia, ja = Xh.graph()
+    ref = orc.form2(orc.STIFFNESS, order, ncomp, orc.quad_order_form2(orc.STIFFNESS, order), mesh.xyz, mesh.conn, Xh.l2g,
+                    ia, ja)
+    K = sps.csr_matrix((ref, ja, ia), shape=(Xh.nDof(), Xh.nDof()))
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal(Xh.nDof())
+    y, yr = a.multVector(x), K @ x
+    assert np.abs(y - yr).max() <= 1e-12 * np.abs(yr).max()
+    ones = np.ones(Xh.nDof())
+    assert np.abs(a.multVector(ones)).max() <= 1e-11 * np.abs(ref).max()
+    if ncomp == 1:
+        X = Xh.dofPoints()
+        f = 2.0 * X[:, 0] - X[:, 1] + 0.5 * X[:, 2]
+        assert abs(a.energy(f, f) - (4.0 + 1.0 + 0.25)) < 1e-11
+
+
 def test_errors(engine, meshes):
     mesh = meshes["reg"]
     Xh = fpp.Pch(mesh, 1)
