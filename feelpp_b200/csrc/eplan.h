@@ -38,6 +38,8 @@
 #define EPLAN_OMAX 7936          // 62 KB row block per CTA: two CTAs per SM next to the 40 KB geometry cache
 #endif
 #define EPLAN_HDRS 128            // chunk headers kept in shared memory (the rest, if any, is read from global memory)
+#define EPLAN_IDX_SHIFT 12          // unit word: bits 0-8 visit slot, 4-bit S indices from bit 12 (index k at 12 + 4k): with the S
+                                   // array on a 64 KB boundary of shared memory, (w >> 4k) & 0xF000 | base is the address of load k
 #define EPLAN_PADRES 16            // row-block slots the packing pass holds back for phase pads (see eplan_build.cpp)
 #define EPLAN_MAXREMOTE 8          // peers a rank's ghost rows can belong to
 #ifndef EPLAN_NSUB

@@ -250,7 +250,7 @@ void model_chunk(const EPlanType& T, const std::vector<uint32_t>& words, int nit
                 for (int b = 0; b < 16; ++b) cnt[b] = 0;
                 for (int l = half * 16; l < half * 16 + 16; ++l) {
                     const uint32_t w = words[(size_t)t * 32 + l];
-                    const uint32_t slot = w & 0x3FF, idx = (w >> (10 + 4 * k)) & 15;
+                    const uint32_t slot = w & 0x3FF, idx = (w >> (EPLAN_IDX_SHIFT + 4 * k)) & 15;
                     const uint32_t addr = idx * EPLAN_VS + slot, b = slot & 15;
                     bool dup = false;
                     for (int s = 0; s < cnt[b]; ++s)
@@ -597,7 +597,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                         const int i = B.uloc[en.q];
                         uint32_t w = B.uvis[en.q];
                         for (int kk = 0; kk < T.nld; ++kk)
-                            w |= (uint32_t)eplan_sidx(en.p[T.ld[kk][0]], en.p[T.ld[kk][1]]) << (10 + 4 * kk);
+                            w |= (uint32_t)eplan_sidx(en.p[T.ld[kk][0]], en.p[T.ld[kk][1]]) << (EPLAN_IDX_SHIFT + 4 * kk);
                         iterw.push_back(w);
                         if (B.orig_dof(T.rowdof, en.p) != i) { L.error = "entity plan: re-labelling does not map the row dof"; return; }
                         for (int o = 0; o < T.nout; ++o) {

@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace {
@@ -51,6 +52,13 @@ __device__ __forceinline__ void cp_async(void* dst_shared, const void* src)
                  "n"(BYTES) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+// the same at shared address 0x10000 + off (the S array of the aligned layout; the constant rides in the instruction)
+__device__ __forceinline__ double lds64_s(uint32_t off)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1+65536];" : "=d"(v) : "r"(off));
+    return v;
+}
 __device__ __forceinline__ void sts64(uint32_t addr, double v)
 {
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
@@ -58,7 +66,7 @@ __device__ __forceinline__ void sts64(uint32_t addr, double v)
 
 // one chunk: lane = task.  wp points at this lane's first unit word; words are [niter][32] (the first two and the
 // out-buffer positions were fetched while the previous chunk ran).
-template <int ORDER, int FORM, int TYPE>
+template <int ORDER, int FORM, int TYPE, bool AL>
 __device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int niter, uint32_t w, uint32_t w1,
                                           const uint32_t (&pos)[EPLAN_MAXOUT], uint32_t sS, uint32_t vsb, uint32_t sO)
 {
@@ -69,12 +77,19 @@ __device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int n
     for (int k = 0; k < NLD; ++k) sum[k] = 0.0;
     for (int t = 0; t < niter; ++t) {
         const uint32_t w2 = (t + 2 < niter) ? __ldg(wp + (t + 2) * 32) : 0u;
-        const uint32_t va = sS + ((w & 0x3FFu) << 3);
-        if (FORM == 0) {
-            sum[0] += lds64(va);
-        } else {
+        if (AL) {
+            // S starts on a 64 KB boundary of shared memory and holds 4 KB per index: the address is a bit-field composition
+            const uint32_t va = (w & 0x1FFu) << 3;   // (sS == 0x10000: checked by the caller)
 #pragma unroll
-            for (int k = 0; k < NLD; ++k) sum[k] += lds64(va + ((w >> (10 + 4 * k)) & 15u) * vsb);
+            for (int k = 0; k < NLD; ++k) sum[k] += lds64_s((((k == 0 || FORM == 0) ? w : (w >> (4 * k))) & (FORM == 0 ? 0u : 0xF000u)) | va);
+        } else {
+            const uint32_t va = sS + ((w & 0x1FFu) << 3);
+            if (FORM == 0) {
+                sum[0] += lds64(va);
+            } else {
+#pragma unroll
+                for (int k = 0; k < NLD; ++k) sum[k] += lds64(va + ((w >> (EPLAN_IDX_SHIFT + 4 * k)) & 15u) * vsb);
+            }
         }
         w = w1;
         w1 = w2;
@@ -93,7 +108,8 @@ __device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int n
     }
 }
 
-template <int ORDER, int FORM, int NCOMP>   // FORM 0: mass, 1: stiffness; NCOMP components (block = value * Id)
+template <int ORDER, int FORM, int NCOMP, bool AL>   // FORM 0: mass, 1: stiffness; NCOMP components (block = value * Id);
+                                                    // AL: the S array sits on a 64 KB boundary of shared memory
 __global__ void __launch_bounds__(EPLAN_WARPS * 32, EPLAN_MINB)
 k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, const int32_t* __restrict__ verts, const uint32_t* __restrict__ visits,
         const uint2* __restrict__ chunks, const uint32_t* __restrict__ blob, const uint4* __restrict__ rows,
@@ -104,11 +120,11 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
                       EPLAN_WARPS * 32 >= EPLAN_HDRS, "one thread per visit / row / vertex / cached chunk header");
     constexpr int NSREC = FORM == 1 ? 10 : 1;
     extern __shared__ double sm[];
-    double* sS = sm;                          // [NSREC][vs]
+    double* sO = sm;                          // [omax]: the patch's row block; slot 0 = trash
+    uint2* sH = reinterpret_cast<uint2*>(sO + omax);   // [EPLAN_HDRS] chunk headers
+    double* sS = reinterpret_cast<double*>(sH + EPLAN_HDRS);   // [NSREC][vs] (row block + headers = 63 KB: see AL)
     double* sX = sS + NSREC * vs;             // [3][EPLAN_VERTS]
-    double* sO = sX + 3 * EPLAN_VERTS;        // [omax]: the patch's row block; slot 0 = trash
-    uint2* sH = reinterpret_cast<uint2*>(sO + omax);   // [EPLAN_HDRS] chunk headers, then the chunk counter
-    int* sCnt = reinterpret_cast<int*>(sH + EPLAN_HDRS);
+    int* sCnt = reinterpret_cast<int*>(sX + 3 * EPLAN_VERTS);   // the chunk counter
     uint4* sN = reinterpret_cast<uint4*>(sCnt + 4);    // [2][2] headers of the current and of the next patch (by parity)
     int32_t* sVid = reinterpret_cast<int32_t*>(sN + 4);   // [EPLAN_VERTS] vertex ids of the next patch
     double* sZ = reinterpret_cast<double*>(sVid + EPLAN_VERTS);   // [EPLAN_VERTS] z coordinates of the next patch (staging)
@@ -284,6 +300,7 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         // chunk's header, first words and positions are fetched while the current one runs.
         {
             const uint32_t sSa = (uint32_t)__cvta_generic_to_shared(sS), sOa = (uint32_t)__cvta_generic_to_shared(sO);
+            if (AL && sSa != 0x10000u) __trap();   // the host checked the layout
             const uint32_t vsb = (uint32_t)vs * 8u, sCa = (uint32_t)__cvta_generic_to_shared(sCnt);
             auto header = [&](int c) { return c < EPLAN_HDRS ? sH[c] : __ldg(&chunks[chunk_off + c]); };
             int c = warp;
@@ -317,11 +334,11 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
                         for (int o = 0; o < EPLAN_MAXOUT; ++o) npos[o] = __ldg(op + o * 32);
                     }
                     switch (type) {
-                    case 0: run_chunk<ORDER, FORM, 0>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    case 1: run_chunk<ORDER, FORM, 1>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
+                    case 0: run_chunk<ORDER, FORM, 0, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    case 1: run_chunk<ORDER, FORM, 1, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
+                    default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
                     }
                     if (!more) break;
                     c = cn;
@@ -427,6 +444,35 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         sched[0] = 0;
         sched[1] = 0;
     }
+}
+
+// shared-window address at which a kernel's dynamic shared memory starts (the same for every kernel without static
+// shared memory): decides whether the S array of k_eplan falls on a 64 KB boundary
+__global__ void k_smem_base(uint32_t* out)
+{
+    extern __shared__ double sm[];
+    *out = (uint32_t)__cvta_generic_to_shared(sm);
+}
+
+int smem_base(feelgpu_context_t ctx, cudaStream_t s)
+{
+    static int cached[64];
+    static bool have[64];
+    const int d = ctx->device & 63;
+    if (!have[d]) {
+        uint32_t* dv = nullptr;
+        uint32_t hv = 0xFFFFFFFFu;
+        if (cudaMalloc(&dv, sizeof(uint32_t)) == cudaSuccess) {
+            k_smem_base<<<1, 1, 64, s>>>(dv);
+            if (cudaMemcpyAsync(&hv, dv, sizeof(uint32_t), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+                cudaStreamSynchronize(s) != cudaSuccess)
+                hv = 0xFFFFFFFFu;
+            cudaFree(dv);
+        }
+        cached[d] = (int)hv;
+        have[d] = true;
+    }
+    return cached[d];
 }
 
 size_t eplan_smem_bytes(const EPlan* p, int form)
@@ -670,20 +716,25 @@ int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     }
     const size_t sh = eplan_smem_bytes(p, form);
     // persistent CTAs: EPLAN_MINB per SM, each runs every gridDim.x-th patch
+    // stiffness: when the S array (behind the row block and the chunk headers) starts at shared address 0x10000 its load
+    // addresses are composed from bit fields of the unit word
+    const int sbase = smem_base(ctx, s);
+    const bool al = EPLAN_VS == 512 && sbase >= 0 &&
+                    sbase + (int64_t)p->omax * 8 + EPLAN_HDRS * (int64_t)sizeof(uint2) == 0x10000 && !getenv("FEELGPU_EPLAN_NO_ALIGNED_S");
     const int grid = (int)std::min<int64_t>(p->ncta, (int64_t)ctx->sm_count * EPLAN_MINB), threads = EPLAN_WARPS * 32;
     if (grid == 0) return FEELGPU_OK;
-#define ELAUNCH1(O, F, C)                                                                                          \
+#define ELAUNCH1(O, F, C, A)                                                                                         \
     do {                                                                                                            \
-        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_eplan<O, F, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-        k_eplan<O, F, C><<<grid, threads, sh, s>>>(p->d_ctas, (int)p->ncta, p->d_sched, p->d_verts, p->d_visits,                              \
+        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_eplan<O, F, C, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+        k_eplan<O, F, C, A><<<grid, threads, sh, s>>>(p->d_ctas, (int)p->ncta, p->d_sched, p->d_verts, p->d_visits,                              \
                                                    reinterpret_cast<const uint2*>(p->d_chunks), p->d_blob,          \
                                                    reinterpret_cast<const uint4*>(p->d_rows), m->d_xyz, a, accumulate, \
                                                    EPLAN_VS, p->omax, hp.cval[0], rem);                                  \
     } while (0)
 #define ELAUNCH(O, F)                         \
     do {                                      \
-        if (p->ncomp == 1) ELAUNCH1(O, F, 1); \
-        else ELAUNCH1(O, F, 3);               \
+        if (p->ncomp == 1) { if (F == 1 && al) ELAUNCH1(O, F, 1, true); else ELAUNCH1(O, F, 1, false); } \
+        else { if (F == 1 && al) ELAUNCH1(O, F, 3, true); else ELAUNCH1(O, F, 3, false); } \
     } while (0)
     switch (p->order * 2 + form) {
     case 2: ELAUNCH(1, 0); break;

@@ -131,7 +131,7 @@ def interpret(P, mesh, order, nnz, form, coef, mass):
                 sums = np.zeros((nld, 32))
                 for t in range(niter):           # plan order
                     for k in range(nld):
-                        idx = (words[t] >> (10 + 4 * k)) & 15 if form == 1 else 0
+                        idx = (words[t] >> (12 + 4 * k)) & 15 if form == 1 else 0
                         sums[k] += rec[slot[t], idx]
                 for o in range(no):
                     v = mass[ty][o] * sums[0] if form == 0 else sum(coef[ty][o][k] * sums[k] for k in range(nld))
