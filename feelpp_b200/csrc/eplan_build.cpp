@@ -853,9 +853,19 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                         for (int it = 0; it < tk.niter; ++it) cw[(size_t)it * 32 + l] = iterw[tk.first + it];
                         L.niters += tk.niter;
                     }
-                    L.niters_padded += (int64_t)cj.niter * 32;
                     model_chunk(T, cw, cj.niter, L.wf, L.wf_ideal);
-                    L.blob.insert(L.blob.end(), cw.begin(), cw.end());
+                    // as the kernel reads them: the visit slot already times 8 (bits 3-11), and the words of two
+                    // consecutive iterations side by side per lane ([ceil(niter/2)][32] pairs: one 64-bit load brings both;
+                    // an odd chunk ends with a word of the all-zero record)
+                    const size_t npair = ((size_t)cj.niter + 1) / 2;
+                    L.niters_padded += (int64_t)npair * 64;
+                    const size_t wb = L.blob.size();
+                    L.blob.resize(wb + npair * 64, (uint32_t)(EPLAN_VS - 1) << 3);
+                    for (int it = 0; it < cj.niter; ++it)
+                        for (int l = 0; l < 32; ++l) {
+                            const uint32_t w = cw[(size_t)it * 32 + l];
+                            L.blob[wb + ((size_t)(it >> 1) * 32 + l) * 2 + (it & 1)] = ((w & 0x1FFu) << 3) | (w & 0xFFFFF000u);
+                        }
                 }
                 for (size_t j = 0; j < nsub; ++j) {
                     const ChunkTmp& cj = ctmp[c0 + j];

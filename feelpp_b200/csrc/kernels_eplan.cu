@@ -64,10 +64,11 @@ __device__ __forceinline__ void sts64(uint32_t addr, double v)
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
 }
 
-// one chunk: lane = task.  wp points at this lane's first unit word; words are [niter][32] (the first two and the
-// out-buffer positions were fetched while the previous chunk ran).
+// one chunk: lane = task.  wp points at this lane's first pair of unit words; words are [ceil(niter/2)][32] pairs (two
+// consecutive iterations side by side; the first pair and the out-buffer positions were fetched while the previous chunk
+// ran).  A unit word holds the visit slot times 8 in bits 3-11 and the 4-bit S indices from bit 12.
 template <int ORDER, int FORM, int TYPE, bool AL>
-__device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int niter, uint32_t w, uint32_t w1,
+__device__ __forceinline__ void run_chunk(const uint2* __restrict__ wp, int npair, uint2 cur,
                                           const uint32_t (&pos)[EPLAN_MAXOUT], uint32_t sS, uint32_t vsb, uint32_t sO)
 {
     constexpr int NLD = FORM == 1 ? e_nld(ORDER, TYPE) : 1;
@@ -75,15 +76,15 @@ __device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int n
     double sum[NLD];
 #pragma unroll
     for (int k = 0; k < NLD; ++k) sum[k] = 0.0;
-    for (int t = 0; t < niter; ++t) {
-        const uint32_t w2 = (t + 2 < niter) ? __ldg(wp + (t + 2) * 32) : 0u;
+    auto visit = [&](uint32_t w) {
         if (AL) {
-            // S starts on a 64 KB boundary of shared memory and holds 4 KB per index: the address is a bit-field composition
-            const uint32_t va = (w & 0x1FFu) << 3;   // (sS == 0x10000: checked by the caller)
+            // S starts at shared address 0x10000 (checked by the caller) and holds 4 KB per index: the address of load k is
+            // a bit-field composition, the constant rides in the instruction
+            const uint32_t va = w & 0xFF8u;
 #pragma unroll
             for (int k = 0; k < NLD; ++k) sum[k] += lds64_s((((k == 0 || FORM == 0) ? w : (w >> (4 * k))) & (FORM == 0 ? 0u : 0xF000u)) | va);
         } else {
-            const uint32_t va = sS + ((w & 0x1FFu) << 3);
+            const uint32_t va = sS + (w & 0xFF8u);
             if (FORM == 0) {
                 sum[0] += lds64(va);
             } else {
@@ -91,8 +92,13 @@ __device__ __forceinline__ void run_chunk(const uint32_t* __restrict__ wp, int n
                 for (int k = 0; k < NLD; ++k) sum[k] += lds64(va + ((w >> (EPLAN_IDX_SHIFT + 4 * k)) & 15u) * vsb);
             }
         }
-        w = w1;
-        w1 = w2;
+    };
+    for (int t = 0; t < npair; ++t) {
+        uint2 nxt = make_uint2(0u, 0u);
+        if (t + 1 < npair) nxt = __ldg(wp + (t + 1) * 32);
+        visit(cur.x);
+        visit(cur.y);      // (an odd chunk ends with a word of the all-zero record)
+        cur = nxt;
     }
 #pragma unroll
     for (int o = 0; o < NOUT; ++o) {
@@ -306,44 +312,43 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
             int c = warp;
             if (c < nchunk) {
                 uint2 ch = header(c);
-                const uint32_t* wp = blob + (size_t)ch.x * 4 + lane;
+                const uint2* wp = reinterpret_cast<const uint2*>(blob + (size_t)ch.x * 4) + lane;
                 uint32_t meta = ch.y;
-                uint32_t w = __ldg(wp), w1 = __ldg(wp + 32);
+                uint2 w = __ldg(wp);
                 uint32_t pos[EPLAN_MAXOUT];
                 {
-                    const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((meta >> 8) & 0xFF) * 32) + lane;
+                    const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((((meta >> 8) & 0xFF) + 1) >> 1) * 32) + lane;
 #pragma unroll
                     for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = __ldg(op + o * 32);
                 }
                 while (true) {
-                    const int type = meta & 0xFF, niter = (meta >> 8) & 0xFF;
-                    const uint32_t* wpc = wp;
+                    const int type = meta & 0xFF, npair = (((meta >> 8) & 0xFF) + 1) >> 1;
+                    const uint2* wpc = wp;
                     int cn;   // next chunk: one shared-memory atomic by lane 0 (written out: the compiler's warp-aggregated form costs 20 instructions)
                     asm volatile("{ .reg .pred p; setp.eq.u32 p, %1, 0; mov.u32 %0, 0; @p atom.shared.inc.u32 %0, [%2], 0x7fffffff; }"
                                  : "=r"(cn) : "r"(lane), "r"(sCa) : "memory");
                     cn = __shfl_sync(0xffffffffu, cn, 0);
                     const bool more = cn < nchunk;
                     ch = header(more ? cn : c);                  // past the end: re-read the current chunk (harmless)
-                    wp = blob + (size_t)ch.x * 4 + lane;
+                    wp = reinterpret_cast<const uint2*>(blob + (size_t)ch.x * 4) + lane;
                     meta = ch.y;
-                    const uint32_t nw = __ldg(wp), nw1 = __ldg(wp + 32);
+                    const uint2 nw = __ldg(wp);
                     uint32_t npos[EPLAN_MAXOUT];
                     {
-                        const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((meta >> 8) & 0xFF) * 32) + lane;
+                        const uint16_t* op = reinterpret_cast<const uint16_t*>(wp - lane + ((((meta >> 8) & 0xFF) + 1) >> 1) * 32) + lane;
 #pragma unroll
                         for (int o = 0; o < EPLAN_MAXOUT; ++o) npos[o] = __ldg(op + o * 32);
                     }
                     switch (type) {
-                    case 0: run_chunk<ORDER, FORM, 0, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    case 1: run_chunk<ORDER, FORM, 1, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;
-                    default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4, AL>(wpc, niter, w, w1, pos, sSa, vsb, sOa); break;   // type 5: phase A
+                    case 0: run_chunk<ORDER, FORM, 0, AL>(wpc, npair, w, pos, sSa, vsb, sOa); break;
+                    case 1: run_chunk<ORDER, FORM, 1, AL>(wpc, npair, w, pos, sSa, vsb, sOa); break;
+                    case 2: if (ORDER >= 2) run_chunk<ORDER, FORM, 2, AL>(wpc, npair, w, pos, sSa, vsb, sOa); break;
+                    case 3: if (ORDER >= 2) run_chunk<ORDER, FORM, 3, AL>(wpc, npair, w, pos, sSa, vsb, sOa); break;
+                    default: if (ORDER >= 2) run_chunk<ORDER, FORM, 4, AL>(wpc, npair, w, pos, sSa, vsb, sOa); break;   // type 5: phase A
                     }
                     if (!more) break;
                     c = cn;
                     w = nw;
-                    w1 = nw1;
 #pragma unroll
                     for (int o = 0; o < EPLAN_MAXOUT; ++o) pos[o] = npos[o];
                 }

@@ -122,12 +122,14 @@ def interpret(P, mesh, order, nnz, form, coef, mass):
             ty, niter, nsub = int(ch["type"]), int(ch["niter"]), int(ch["pad"])
             nld, no = (NLD[order][ty] if form == 1 else 1), NOUT[order][ty]
             w0 = int(ch["q0"]) * 4
-            allw = P["blob"][w0:w0 + nsub * niter * 32].reshape(nsub, niter, 32)
-            p0 = w0 + nsub * niter * 32
+            npair = (niter + 1) // 2            # words of two consecutive iterations side by side per lane
+            raw = P["blob"][w0:w0 + nsub * npair * 64].reshape(nsub, npair, 32, 2)
+            allw = raw.transpose(0, 1, 3, 2).reshape(nsub, 2 * npair, 32)
+            p0 = w0 + nsub * npair * 64
             allp = P["blob"][p0:p0 + nsub * no * 16].view(np.uint16).reshape(nsub, no, 32)
             for j in range(nsub):
                 words, opos = allw[j], allp[j]
-                slot = words & 0x3FF
+                slot = (words >> 3) & 0x1FF      # stored times 8
                 sums = np.zeros((nld, 32))
                 for t in range(niter):           # plan order
                     for k in range(nld):
