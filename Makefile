@@ -21,7 +21,7 @@ $(LIB)/eplan_build.o: $(CSRC)/eplan_build.cpp $(CSRC)/eplan.h
 	@mkdir -p $(LIB)
 	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread $(EPLAN_DEFS) -c $< -o $@
 
-$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o $(LIB)/kernels_on.o
+$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o $(LIB)/kernels_on.o $(LIB)/kernels_graph.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart
 
 HOSTSRC := $(wildcard feelpp_b200/host/*.cpp)

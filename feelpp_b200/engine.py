@@ -59,6 +59,17 @@ class Engine:
             self._spaces[key] = (h, Xh)
         return self._spaces[key][0]
 
+    def graph(self, Xh):
+        """(ia, ja) of the COUPLED graph of (Xh, Xh), built on the device (feelgpu_graph_create): the device-side
+        Stencil::computeGraph; bit-exact with Xh.graph()"""
+        g, nnz = C.c_void_p(), C.c_int64()
+        check(self.lib.feelgpu_graph_create(self.space(Xh), C.byref(g), C.byref(nnz)), self.ctx)
+        ia = np.empty(Xh.nDof() + 1, dtype=np.int64)
+        ja = np.empty(nnz.value, dtype=np.int64)
+        check(self.lib.feelgpu_graph_get(g, ptr(ia, c_i64p), ptr(ja, c_i64p)), self.ctx)
+        self.lib.feelgpu_graph_destroy(g)
+        return ia, ja
+
     def faces(self, rng):
         """device list of the (element, local face) pairs of a face range (feelgpu_faces_create)"""
         key = builtins_id(rng)

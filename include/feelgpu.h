@@ -62,6 +62,7 @@ typedef struct feelgpu_mesh_s* feelgpu_mesh_t;
 typedef struct feelgpu_space_s* feelgpu_space_t;
 typedef struct feelgpu_pattern_s* feelgpu_pattern_t;
 typedef struct feelgpu_faces_s* feelgpu_faces_t;
+typedef struct feelgpu_graph_s* feelgpu_graph_t;
 
 typedef struct {
     int kind;                     /* FEELGPU_COEFF_*                                                            */
@@ -163,6 +164,16 @@ int feelgpu_form1_assemble_host(feelgpu_space_t space, const feelgpu_form1_desc*
 enum { FEELGPU_ON_ELIMINATION = 1, FEELGPU_ON_SYMMETRIC = 2, FEELGPU_ON_KEEP_DIAGONAL = 4 };
 int feelgpu_form2_zero_rows(feelgpu_pattern_t pattern, int64_t n, const int32_t* rows, const double* values, int strategy,
                             double value_on_diagonal, double* a_values, double* b, void* stream);
+
+/* ---- sparsity graph on the device -------------------------------------------------------------------------------
+ * Replaces Stencil::computeGraph + GraphCSR::close for test space == trial space, pattern COUPLED
+ * (feeldiscr/stencil.hpp:1500-1798, feelalg/graphcsr.cpp:662-1022): rows = dofs of the space (sequential numbering),
+ * columns ascending as the reference's std::set keeps them, the diagonal always present (graphcsr.cpp:633-659).
+ * Bit-exact with the host graph.  feelgpu_graph_get copies ia[nDof+1] / ja[nnz] (int64) to HOST arrays: what the adapter
+ * hands to MatSeqAIJSetPreallocationCSR and back to feelgpu_pattern_create.  Either pointer may be NULL.            */
+int feelgpu_graph_create(feelgpu_space_t space, feelgpu_graph_t* graph, int64_t* nnz);
+int feelgpu_graph_get(feelgpu_graph_t graph, int64_t* ia, int64_t* ja);
+int feelgpu_graph_destroy(feelgpu_graph_t graph);
 
 /* ---- device hand-off: y = A x on the assembled CSR (MatrixPetsc::multVector -> MatMult, feelalg/matrixpetsc.cpp:998-1062;
  * with it MatrixPetsc::energy :2132-2170 is a dot product).  Sequential matrices (one space, identity cluster numbering);

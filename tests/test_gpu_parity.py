@@ -197,6 +197,18 @@ def test_matvec_and_energy(engine, meshes, order, ncomp):
         assert abs(a.energy(f, f) - (4.0 + 1.0 + 0.25)) < 1e-11
 
 
+@pytest.mark.parametrize("order,ncomp,mk", [(1, 1, "reg"), (2, 1, "jit"), (3, 1, "jit"), (2, 3, "jit")])
+def test_device_graph_bit_exact(engine, meshes, order, ncomp, mk):
+    """Stencil::computeGraph on the device (feelgpu_graph_create): ia/ja identical to the host graph, which the
+    not-gpu tests pin against the oracle's std::set restatement"""
+    mesh = meshes[mk]
+    Xh = fpp.FunctionSpace(mesh, order, ncomp)
+    ia, ja = Xh.graph()
+    dia, dja = engine.graph(Xh)
+    assert np.array_equal(dia, ia)
+    assert np.array_equal(dja, ja)
+
+
 def test_errors(engine, meshes):
     mesh = meshes["reg"]
     Xh = fpp.Pch(mesh, 1)
