@@ -209,6 +209,31 @@ def test_device_graph_bit_exact(engine, meshes, order, ncomp, mk):
     assert np.array_equal(dja, ja)
 
 
+def test_value_array_on_odd_double(engine, meshes):
+    """a value array that starts on an odd multiple of 8 bytes: no row segment shares the 16-byte phase of its row-block
+    slot any more, so phase C falls back from bulk copies to the warp copy loop for every segment ('=' and '+=')"""
+    import ctypes as C
+    from feelpp_b200 import engine as E
+    from feelpp_b200._capi import check
+    mesh = meshes["jit"]
+    Xh = fpp.Pch(mesh, 2)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine)
+    keep = E._Keep()
+    ds = a._desc(integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v))), keep)
+    dm = a._desc(integrate(_range=elements(mesh), _expr=idt(u) * id(v)), keep)
+    raw = engine.malloc(8 * (a.nnz + 2))
+    odd = C.c_void_p(raw.value + 8)
+    check(engine.lib.feelgpu_form2_assemble(a.pat, C.byref(dm), 0, odd, None), engine.ctx)
+    check(engine.lib.feelgpu_form2_assemble(a.pat, C.byref(ds), 1, odd, None), engine.ctx)
+    engine.sync()
+    got = engine.to_host(raw, a.nnz + 2)[1:a.nnz + 1]
+    (K, ia, ja), ks = oracle_form2(orc.STIFFNESS, Xh, 2)
+    (M, _, _), ms = oracle_form2(orc.MASS, Xh, 4)
+    check_values(got, (K + M, ia, ja), ks + ms, "odd-aligned value array")
+    engine.free(raw)
+
+
 def test_errors(engine, meshes):
     mesh = meshes["reg"]
     Xh = fpp.Pch(mesh, 1)
