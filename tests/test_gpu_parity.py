@@ -209,6 +209,36 @@ def test_device_graph_bit_exact(engine, meshes, order, ncomp, mk):
     assert np.array_equal(dja, ja)
 
 
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_tiny_and_empty_inputs(engine, order):
+    """one cell (6 tets): a single ragged patch / partial warp in every kernel; an empty face range and an empty
+    Dirichlet set are no-ops"""
+    import ctypes as C
+    from feelpp_b200 import hostmirror as hm
+    from feelpp_b200._capi import check, ptr, c_i32p, c_dblp
+    mesh = fpp.unitCube(1, 0.1, False)
+    Xh = fpp.Pch(mesh, order)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine)
+    a.assign(integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v))))
+    ref, scale = oracle_form2(orc.STIFFNESS, Xh, orc.quad_order_form2(orc.STIFFNESS, order))
+    check_values(a.values(), ref, scale, "one cell")
+    before = a.values().copy()
+    empty = C.c_void_p()
+    e0 = np.zeros(0, dtype=np.int32)
+    check(engine.lib.feelgpu_faces_create(engine.mesh(mesh), 0, ptr(e0, c_i32p), ptr(e0, c_i32p), C.byref(empty)), engine.ctx)
+    from feelpp_b200 import engine as E
+    keep = E._Keep()
+    d = a._desc(integrate(_range=hm.boundaryfaces(mesh), _expr=idt(u) * id(v)), keep)
+    check(engine.lib.feelgpu_form2_assemble_faces(a.pat, empty, C.byref(d), 1, a.d_values, None), engine.ctx)
+    x0 = np.zeros(0)
+    check(engine.lib.feelgpu_form2_zero_rows(a.pat, 0, ptr(e0, c_i32p), ptr(x0, c_dblp), 1, 1.0, a.d_values, None, None),
+          engine.ctx)
+    engine.sync()
+    assert np.array_equal(a.values(), before)
+    engine.lib.feelgpu_faces_destroy(empty)
+
+
 def test_value_array_on_odd_double(engine, meshes):
     """a value array that starts on an odd multiple of 8 bytes: no row segment shares the 16-byte phase of its row-block
     slot any more, so phase C falls back from bulk copies to the warp copy loop for every segment ('=' and '+=')"""
