@@ -1,4 +1,4 @@
 source tools/variants.sh true
-run w18
-run w20 -DEPLAN_WARPS=20
-run w17 -DEPLAN_WARPS=17
+timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -2
+run new
+runref old
