@@ -16,6 +16,23 @@ static std::string g_create_error;
         return FEELGPU_ERR_ARG;        \
     } while (0)
 
+// No exception crosses the ABI (include/feelgpu.h): the create calls build std::vector-based host plans, so they run
+// inside this guard.  `cleanup` releases what the body had allocated when the exception was thrown.
+template <class Body, class Cleanup>
+static int abi_guard(feelgpu_context_t ctx, const char* what, Body body, Cleanup cleanup)
+{
+    try {
+        return body();
+    } catch (const std::exception& e) {
+        cleanup();
+        ctx->last_error = std::string(what) + ": " + e.what();
+    } catch (...) {
+        cleanup();
+        ctx->last_error = std::string(what) + ": unknown host exception";
+    }
+    return FEELGPU_ERR_HOST;
+}
+
 extern "C" {
 
 int feelgpu_context_create(int device, feelgpu_context_t* out)
@@ -38,6 +55,7 @@ int feelgpu_context_create(int device, feelgpu_context_t* out)
     if ((err = cudaSetDevice(device)) != cudaSuccess || (err = cudaStreamCreate(&ctx->stream)) != cudaSuccess ||
         (err = cudaMalloc(&ctx->d_flag, sizeof(int))) != cudaSuccess) {
         g_create_error = cudaGetErrorString(err);
+        if (ctx->stream) cudaStreamDestroy(ctx->stream);
         delete ctx;
         return FEELGPU_ERR_CUDA;
     }
@@ -95,7 +113,9 @@ int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz, 
     for (int64_t k = 0; k < 4 * nElt; ++k)
         if (conn[k] < 0 || conn[k] >= nPts) ARG_FAIL(ctx, "mesh_create: connectivity entry outside [0,nPts)");
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));
-    feelgpu_mesh_t m = new feelgpu_mesh_s;
+    feelgpu_mesh_t m = nullptr;
+    return abi_guard(ctx, "mesh_create", [&]() -> int {
+    m = new feelgpu_mesh_s;
     m->ctx = ctx;
     m->nPts = nPts;
     m->nElt = nElt;
@@ -120,6 +140,7 @@ int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz, 
     }
     *out = m;
     return FEELGPU_OK;
+    }, [&] { if (m) feelgpu_mesh_destroy(m); });
 }
 
 int feelgpu_mesh_update_points(feelgpu_mesh_t m, const double* xyz, void* stream)
@@ -164,7 +185,9 @@ int feelgpu_space_create(feelgpu_context_t ctx, feelgpu_mesh_t mesh, int order, 
                 }
         }
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));
-    feelgpu_space_t sp = new feelgpu_space_s;
+    feelgpu_space_t sp = nullptr;
+    return abi_guard(ctx, "space_create", [&]() -> int {
+    sp = new feelgpu_space_s;
     sp->ctx = ctx;
     sp->mesh = mesh;
     sp->order = order;
@@ -187,6 +210,7 @@ int feelgpu_space_create(feelgpu_context_t ctx, feelgpu_mesh_t mesh, int order, 
     }
     *out = sp;
     return FEELGPU_OK;
+    }, [&] { if (sp) feelgpu_space_destroy(sp); });
 }
 
 int feelgpu_space_destroy(feelgpu_space_t sp)
@@ -215,7 +239,10 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
         if (ia[r + 1] < ia[r]) ARG_FAIL(ctx, "pattern_create: ia not monotone");
     if (flags == 0) flags = FEELGPU_PATTERN_SLOTMAP | (test->order <= 2 ? FEELGPU_PATTERN_EPLAN : FEELGPU_PATTERN_ROWPLAN);
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));
-    feelgpu_pattern_t pat = new feelgpu_pattern_s;
+    feelgpu_pattern_t pat = nullptr;
+    int64_t* d_ja = nullptr;
+    return abi_guard(ctx, "pattern_create", [&]() -> int {
+    pat = new feelgpu_pattern_s;
     pat->ctx = ctx;
     pat->test = test;
     pat->trial = trial;
@@ -224,7 +251,6 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     pat->h_ia_owned_end = ia[std::min<int64_t>(test->nDofOwned, nRows)];
     const int n = test->n;
     const int64_t nElt = test->mesh->nElt;
-    int64_t* d_ja = nullptr;
     cudaError_t err = cudaMalloc(&pat->d_ia, sizeof(int64_t) * (nRows + 1));
     if (err == cudaSuccess) err = cudaMemcpy(pat->d_ia, ia, sizeof(int64_t) * (nRows + 1), cudaMemcpyHostToDevice);
     if (err == cudaSuccess) err = cudaMalloc(&d_ja, sizeof(int64_t) * std::max<int64_t>(pat->nnz, 1));
@@ -238,6 +264,7 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     }
     int rc = feelgpu_launch_build_pos(pat, d_ja, ctx->stream);
     cudaFree(d_ja); // the 64-bit column array is only needed to build the maps
+    d_ja = nullptr;
     {   // 32-bit copy of the columns for feelgpu_form2_zero_rows
         bool fits = true;
         std::vector<int32_t> ja32((size_t)pat->nnz);
@@ -265,6 +292,10 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     }
     *out = pat;
     return FEELGPU_OK;
+    }, [&] {
+        if (d_ja) cudaFree(d_ja);
+        if (pat) feelgpu_pattern_destroy(pat);
+    });
 }
 
 int feelgpu_pattern_nnz(feelgpu_pattern_t pat, int64_t* nnz)
@@ -522,15 +553,19 @@ int feelgpu_faces_create(feelgpu_mesh_t mesh, int64_t nFaces, const int32_t* ele
         if (element[k] < 0 || element[k] >= mesh->nElt || local_face[k] < 0 || local_face[k] > 3)
             ARG_FAIL(ctx, "faces_create: (element, local face) out of range");
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));
-    feelgpu_faces_t fc = new feelgpu_faces_s;
+    feelgpu_faces_t fc = new (std::nothrow) feelgpu_faces_s;
+    if (!fc) { ctx->last_error = "faces_create: out of host memory"; return FEELGPU_ERR_HOST; }
     fc->mesh = mesh;
     fc->n = nFaces;
     const size_t bytes = sizeof(int32_t) * (size_t)std::max<int64_t>(nFaces, 1);
-    CTX_CUDA(ctx, cudaMalloc(&fc->d_elt, bytes));
-    CTX_CUDA(ctx, cudaMalloc(&fc->d_lface, bytes));
-    if (nFaces > 0) {
-        CTX_CUDA(ctx, cudaMemcpy(fc->d_elt, element, sizeof(int32_t) * nFaces, cudaMemcpyHostToDevice));
-        CTX_CUDA(ctx, cudaMemcpy(fc->d_lface, local_face, sizeof(int32_t) * nFaces, cudaMemcpyHostToDevice));
+    cudaError_t err = cudaMalloc(&fc->d_elt, bytes);
+    if (err == cudaSuccess) err = cudaMalloc(&fc->d_lface, bytes);
+    if (err == cudaSuccess && nFaces > 0) err = cudaMemcpy(fc->d_elt, element, sizeof(int32_t) * nFaces, cudaMemcpyHostToDevice);
+    if (err == cudaSuccess && nFaces > 0) err = cudaMemcpy(fc->d_lface, local_face, sizeof(int32_t) * nFaces, cudaMemcpyHostToDevice);
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("faces_create: ") + cudaGetErrorString(err);
+        feelgpu_faces_destroy(fc);
+        return FEELGPU_ERR_CUDA;
     }
     *out = fc;
     return FEELGPU_OK;

@@ -17,6 +17,7 @@
 #include <cub/device/device_select.cuh>
 
 #include <algorithm>
+#include <new>
 
 struct feelgpu_graph_s {
     feelgpu_space_t space = nullptr;
@@ -131,7 +132,12 @@ extern "C" int feelgpu_graph_create(feelgpu_space_t sp, feelgpu_graph_t* out, in
     ctx->launches++;
     need = tmp_bytes;
     GRAPH_CUDA(cub::DeviceScan::ExclusiveSum(d_tmp, need, d_cnt, d_ian, nNode + 1, s));
-    g = new feelgpu_graph_s;
+    g = new (std::nothrow) feelgpu_graph_s;
+    if (!g) {
+        ctx->last_error = "graph_create: out of host memory";
+        rc = FEELGPU_ERR_HOST;
+        goto done;
+    }
     g->space = sp;
     g->nRows = nNode * ncomp;
     g->nnz = nUnique * ncomp * ncomp;

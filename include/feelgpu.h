@@ -32,7 +32,8 @@ enum {
     FEELGPU_ERR_NCCL = 3,         /* NCCL error                                                          */
     FEELGPU_ERR_NOT_IN_PATTERN = 4, /* a (row,col) of an element is absent from the CSR graph: the analogue of
                                      PETSc's MAT_NEW_NONZERO_ALLOCATION_ERR (feelalg/matrixpetsc.cpp:2688)  */
-    FEELGPU_ERR_UNSUPPORTED = 5   /* form / order / quadrature outside the supported set                 */
+    FEELGPU_ERR_UNSUPPORTED = 5,  /* form / order / quadrature outside the supported set                 */
+    FEELGPU_ERR_HOST = 6          /* host-side failure while building device data (out of host memory)   */
 };
 
 /* bilinear forms recognised on the path (feelvf/operators.hpp:134-153, operations.hpp:585-646, inner.hpp:374-420) */
