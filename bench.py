@@ -7,8 +7,8 @@ jittered vertices, generated (cell-major) element order.  Device-resident inputs
 element->CSR maps) are prepared untimed: they are Feel++'s setup (Pch, newMatrix).
 
   value  : elements/s, inputs resident in HBM, CUDA events on the launching stream
-  e2e    : the same through feelgpu_form2_assemble_host: per step H2D of the vertex coordinates (pinned) and D2H of the
-           CSR values into pinned host memory
+  e2e    : the same through feelgpu_form2_assemble_host: per step H2D of the vertex coordinates from pinned host memory
+           (padded to one sector per vertex on the device) and D2H of the CSR values into pinned host memory
   --impl reference : the CPU element loop (oracle restatement of the reference; Feel++ itself cannot be built here)
 """
 import argparse
@@ -270,12 +270,17 @@ def gpu_arm(args):
         check(lib.feelgpu_host_alloc_pinned(eng.ctx, 8 * max(nown, 1), C.byref(hp)), eng.ctx)
         hostvals = C.cast(hp, c_dblp)
         mh = eng.mesh(mesh)
+        # the step's input, the vertex coordinates, waits in pinned host memory ([nPts][3] doubles, the caller's layout)
+        hx = C.c_void_p()
+        check(lib.feelgpu_host_alloc_pinned(eng.ctx, mesh.xyz.nbytes, C.byref(hx)), eng.ctx)
+        C.memmove(hx, mesh.xyz.ctypes.data, mesh.xyz.nbytes)
+        hostxyz = C.cast(hx, c_dblp)
         ksteps = max(2, min(args.steps, 5))
         for it in range(1 + ksteps):
             if it == 1:
                 barrier()
                 te0 = time.perf_counter()
-            check(lib.feelgpu_mesh_update_points(mh, ptr(mesh.xyz, c_dblp), None if world == 1 else sptr), eng.ctx)
+            check(lib.feelgpu_mesh_update_points(mh, hostxyz, None if world == 1 else sptr), eng.ctx)
             if world == 1:
                 check(lib.feelgpu_form2_assemble_host(a.pat, C.byref(desc), 0, hostvals), eng.ctx)
             else:
@@ -285,7 +290,7 @@ def gpu_arm(args):
         barrier()
         te = (time.perf_counter() - te0) / ksteps
         tt = torch.tensor([te], device="cuda", dtype=torch.float64)
-        tb = torch.tensor([mesh.xyz.nbytes * 4 // 3, 8 * nown], device="cuda", dtype=torch.int64)
+        tb = torch.tensor([mesh.xyz.nbytes, 8 * nown], device="cuda", dtype=torch.int64)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dist.all_reduce(tb)
@@ -294,6 +299,7 @@ def gpu_arm(args):
                "d2h_bytes_per_step": int(tb[1].item()), "ms_per_step": 1e3 * te, "steps": ksteps,
                "timer": "host perf_counter around synchronous host-buffer calls, max over ranks"}
         lib.feelgpu_host_free_pinned(eng.ctx, hp)
+        lib.feelgpu_host_free_pinned(eng.ctx, hx)
 
     if rank == 0:
         peaks = {}

@@ -91,16 +91,36 @@ int feelgpu_sync(feelgpu_context_t ctx)
 }
 
 // ---- mesh ------------------------------------------------------------------------------------------------------
+// [nPts][3] (the caller's layout, elt.G() columns) -> [nPts][4], one 32-byte sector per vertex
+static __global__ void k_pad_points(int64_t nPts, const double* __restrict__ raw, double* __restrict__ xyz)
+{
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < nPts; p += (int64_t)gridDim.x * blockDim.x) {
+        const double x = raw[3 * p], y = raw[3 * p + 1], z = raw[3 * p + 2];
+        reinterpret_cast<double4*>(xyz)[p] = make_double4(x, y, z, 0.0);
+    }
+}
+
+// Coordinates travel in the caller's 24-byte layout and are padded on the device.  Page-locked caller memory is read
+// by the copy engine directly; pageable memory goes through the mesh's pinned staging buffer (one memcpy).
 static int upload_points(feelgpu_mesh_t m, const double* xyz, cudaStream_t s)
 {
     feelgpu_context_t ctx = m->ctx;
-    for (int64_t p = 0; p < m->nPts; ++p) {
-        m->h_stage[4 * p + 0] = xyz[3 * p + 0];
-        m->h_stage[4 * p + 1] = xyz[3 * p + 1];
-        m->h_stage[4 * p + 2] = xyz[3 * p + 2];
-        m->h_stage[4 * p + 3] = 0.0;
+    const size_t bytes = sizeof(double) * 3 * (size_t)m->nPts;
+    cudaPointerAttributes at;
+    const bool pinned = cudaPointerGetAttributes(&at, xyz) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();   // (older drivers report unregistered host memory as an error)
+    const double* src = xyz;
+    if (!pinned) {
+        // the staging buffer is reused: a previous upload on this stream must have left it
+        CTX_CUDA(ctx, cudaStreamSynchronize(s));
+        std::memcpy(m->h_stage, xyz, bytes);
+        src = m->h_stage;
     }
-    CTX_CUDA(ctx, cudaMemcpyAsync(m->d_xyz, m->h_stage, sizeof(double) * 4 * m->nPts, cudaMemcpyHostToDevice, s));
+    CTX_CUDA(ctx, cudaMemcpyAsync(m->d_raw, src, bytes, cudaMemcpyHostToDevice, s));
+    const int grid = (int)std::min<int64_t>((m->nPts + 255) / 256, (int64_t)std::max(ctx->sm_count, 1) * 8);
+    k_pad_points<<<grid, 256, 0, s>>>(m->nPts, m->d_raw, m->d_xyz);
+    ctx->launches++;
+    CTX_CUDA(ctx, cudaGetLastError());
     return FEELGPU_OK;
 }
 
@@ -122,7 +142,8 @@ int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz, 
     cudaError_t err;
     if ((err = cudaMalloc(&m->d_xyz, sizeof(double) * 4 * nPts)) != cudaSuccess ||
         (err = cudaMalloc(&m->d_conn, sizeof(int4) * std::max<int64_t>(nElt, 1))) != cudaSuccess ||
-        (err = cudaMallocHost(&m->h_stage, sizeof(double) * 4 * nPts)) != cudaSuccess) {
+        (err = cudaMalloc(&m->d_raw, sizeof(double) * 3 * nPts)) != cudaSuccess ||
+        (err = cudaMallocHost(&m->h_stage, sizeof(double) * 3 * nPts)) != cudaSuccess) {
         ctx->last_error = std::string("mesh_create: ") + cudaGetErrorString(err);
         feelgpu_mesh_destroy(m);
         return FEELGPU_ERR_CUDA;
@@ -148,8 +169,7 @@ int feelgpu_mesh_update_points(feelgpu_mesh_t m, const double* xyz, void* stream
     if (!m) return FEELGPU_ERR_ARG;
     if (!xyz) ARG_FAIL(m->ctx, "mesh_update_points: null xyz");
     cudaStream_t s = stream ? (cudaStream_t)stream : m->ctx->stream;
-    // the pinned staging buffer is reused: wait for a previous upload on this stream to finish first
-    CTX_CUDA(m->ctx, cudaStreamSynchronize(s));
+    CTX_CUDA(m->ctx, cudaSetDevice(m->ctx->device));
     return upload_points(m, xyz, s);
 }
 
@@ -157,6 +177,7 @@ int feelgpu_mesh_destroy(feelgpu_mesh_t m)
 {
     if (!m) return FEELGPU_ERR_ARG;
     if (m->d_xyz) cudaFree(m->d_xyz);
+    if (m->d_raw) cudaFree(m->d_raw);
     if (m->d_conn) cudaFree(m->d_conn);
     if (m->h_stage) cudaFreeHost(m->h_stage);
     delete m;

@@ -28,7 +28,8 @@ struct feelgpu_mesh_s {
     int64_t nPts = 0, nElt = 0;
     double* d_xyz = nullptr;     // [nPts][4]: x,y,z,0 -- one 32-byte sector per vertex
     int4* d_conn = nullptr;      // [nElt]
-    double* h_stage = nullptr;   // pinned staging for update_points
+    double* d_raw = nullptr;     // [nPts][3]: the caller's layout as it arrives; k_pad_points writes d_xyz from it
+    double* h_stage = nullptr;   // pinned staging for update_points from pageable caller memory
     std::vector<double> h_xyz;   // host copies: the plan builder orders rows along a space-filling curve
     std::vector<int32_t> h_conn;
 };

@@ -121,6 +121,9 @@ int feelgpu_sync(feelgpu_context_t ctx);
 /* ---- mesh: element connectivity + vertex coordinates (replaces elt.point(i).id(), elt.G(): feelmesh/geond.hpp:626) */
 int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz /*[nPts][3]*/, int64_t nElt,
                         const int32_t* conn /*[nElt][4]*/, feelgpu_mesh_t* mesh);
+/* new vertex coordinates (moving meshes, the per-step input of an end-to-end assembly): stream-ordered; page-locked
+ * caller memory is read by the copy engine directly and must stay valid until the stream reaches the copy, pageable
+ * memory is staged (the call then waits for the stream first) */
 int feelgpu_mesh_update_points(feelgpu_mesh_t mesh, const double* xyz /*host [nPts][3]*/, void* stream);
 int feelgpu_mesh_destroy(feelgpu_mesh_t mesh);
 

@@ -279,3 +279,40 @@ def test_errors(engine, meshes):
                                            C.byref(pat))
     assert rc == 4
     assert b"not in the CSR graph" in engine.lib.feelgpu_last_error(engine.ctx)
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_update_points(engine, pinned):
+    """moved vertices (the per-step input of an end-to-end assembly): feelgpu_mesh_update_points from pageable memory
+    (staged) and from page-locked memory (read by the copy engine), padded on the device; same pattern, new values"""
+    import ctypes as C
+    from feelpp_b200._capi import check, ptr, c_dblp
+    mesh = fpp.unitCube(4, 0.1, False)
+    Xh = fpp.Pch(mesh, 2)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine)
+    integ = integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v)))
+    a.assign(integ)
+    rng = np.random.default_rng(5)
+    old = mesh.xyz.copy()
+    new = old + 0.02 * rng.standard_normal(old.shape)
+    hx = C.c_void_p()
+    try:
+        if pinned:
+            check(engine.lib.feelgpu_host_alloc_pinned(engine.ctx, new.nbytes, C.byref(hx)), engine.ctx)
+            C.memmove(hx, new.ctypes.data, new.nbytes)
+            src = C.cast(hx, c_dblp)
+        else:
+            src = ptr(new, c_dblp)
+        check(engine.lib.feelgpu_mesh_update_points(engine.mesh(mesh), src, None), engine.ctx)
+        a.assign(integ)
+        vals = a.values()
+        mesh.xyz[:] = new
+        ref, scale = oracle_form2(orc.STIFFNESS, Xh, 2)
+        check_values(vals, ref, scale, "moved vertices")
+    finally:
+        mesh.xyz[:] = old
+        check(engine.lib.feelgpu_mesh_update_points(engine.mesh(mesh), ptr(old, c_dblp), None), engine.ctx)
+        engine.lib.feelgpu_sync(engine.ctx)
+        if hx:
+            engine.lib.feelgpu_host_free_pinned(engine.ctx, hx)
