@@ -734,6 +734,8 @@ double oracle_form2_threads(int kind, int order, int ncomp, int quad_order, int6
 {
     (void)nPts;
     (void)nElt;
+    const bool absmode = (kind & ORACLE_ABS_FLAG) != 0;   // as in oracle_form2: the cancellation scale sum_e |a^e_ij|
+    kind &= ~ORACLE_ABS_FLAG;
     Tables T = make_tables(order, quad_order);
     Tables Tf;
     if (coeff && coeff->kind == ORACLE_COEFF_FIELD) Tf = make_tables(coeff->field_order, quad_order);
@@ -766,6 +768,8 @@ double oracle_form2_threads(int kind, int order, int ncomp, int quad_order, int6
             Geo g;
             geo_update(Gp, g);
             local_matrix(kind, ncomp, T, &Tf, coeff, g, e, W.Ae.data(), W.grad.data(), W.prod.data(), W.kq.data());
+            if (absmode)
+                for (int k = 0; k < nd * nd; ++k) W.Ae[k] = std::fabs(W.Ae[k]);
             const int32_t* idx = l2g + e * nd;
             for (int i = 0; i < nd; ++i) {
                 const bool mine = owner[idx[i]] == p;

@@ -139,3 +139,21 @@ def test_threaded_baseline_matches_serial(mesh):
     ref = orc.form2(orc.STIFFNESS, 2, 1, 2, mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
     par, secs = orc.form2(orc.STIFFNESS, 2, 1, 2, mesh.xyz, mesh.conn, Xh.l2g, ia, ja, threads=3)
     assert secs >= 0 and np.abs(par - ref).max() < 1e-13 * np.abs(ref).max()
+
+
+def test_threaded_loop_matches_serial_loop():
+    """the threaded element loop (CPU baseline, full-size parity) gives the serial loop's matrix up to summation order,
+    and the same cancellation scale in ABS mode"""
+    import feelpp_b200 as fpp
+    m = fpp.unitCube(4, 0.15, False)
+    Xh = fpp.Pch(m, 2)
+    ia, ja = Xh.graph()
+    for kind in (orc.STIFFNESS, orc.MASS):
+        q = orc.quad_order_form2(kind, 2)
+        s = orc.form2(kind, 2, 1, q, m.xyz, m.conn, Xh.l2g, ia, ja)
+        t, _ = orc.form2(kind, 2, 1, q, m.xyz, m.conn, Xh.l2g, ia, ja, threads=3)
+        sa = orc.form2(kind | orc.ABS_FLAG, 2, 1, q, m.xyz, m.conn, Xh.l2g, ia, ja)
+        ta, _ = orc.form2(kind | orc.ABS_FLAG, 2, 1, q, m.xyz, m.conn, Xh.l2g, ia, ja, threads=3)
+        assert np.abs(s - t).max() <= 1e-15 * np.abs(sa).max()
+        np.testing.assert_allclose(ta, sa, rtol=1e-14)
+        assert (ta >= np.abs(t) - 1e-18).all()
