@@ -157,9 +157,12 @@ def interpret(P, mesh, order, nnz, form, coef, mass):
 
 
 @pytest.mark.parametrize("order", [1, 2])
-@pytest.mark.parametrize("mk", ["reg", "jit"])
+@pytest.mark.parametrize("mk", ["reg", "jit", "scr"])
 def test_plan_interpreted_on_host_matches_oracle(order, mk):
     mesh = fpp.unitCube(4) if mk == "reg" else fpp.unitCube(5, 0.15, True)
+    if mk == "scr":
+        from conftest import scrambled
+        mesh = scrambled(mesh)
     Xh = fpp.Pch(mesh, order)
     ia, ja = Xh.graph()
     P = build_plan(mesh, Xh, ia, ja)

@@ -48,12 +48,13 @@ def oracle_form2(kind, Xh, quad, coeff=None):
 
 @pytest.fixture(scope="module")
 def meshes():
-    return {"reg": fpp.unitCube(4), "jit": fpp.unitCube(5, 0.15, True)}
+    from conftest import scrambled
+    return {"reg": fpp.unitCube(4), "jit": fpp.unitCube(5, 0.15, True), "scr": scrambled(fpp.unitCube(5, 0.15, True))}
 
 
 @pytest.mark.parametrize("algo", ALGOS)
 @pytest.mark.parametrize("order", [1, 2, 3])
-@pytest.mark.parametrize("mk", ["reg", "jit"])
+@pytest.mark.parametrize("mk", ["reg", "jit", "scr"])
 def test_stiffness_and_mass(engine, meshes, order, mk, algo):
     mesh = meshes[mk]
     Xh = fpp.Pch(mesh, order)

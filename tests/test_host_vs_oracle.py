@@ -24,6 +24,19 @@ def test_doftable_and_graph_bit_exact(m, jit, shuf, order, ncomp):
         assert np.all(np.diff(row) > 0) and r in row
 
 
+@pytest.mark.parametrize("order,ncomp", [(1, 1), (2, 1), (3, 1), (2, 3)])
+def test_doftable_and_graph_bit_exact_scrambled_mesh(order, ncomp):
+    """random vertex ids and random local vertex order: edge / face orientation by point ids (feelmesh/mesh3d.hpp:755-782)"""
+    from conftest import scrambled
+    mesh = scrambled(fpp.unitCube(3, 0.1, True))
+    Xh = fpp.FunctionSpace(mesh, order, ncomp)
+    l2g, ndof = orc.doftable(mesh.numPoints(), mesh.conn, order, ncomp)
+    assert ndof == Xh.nDof() and np.array_equal(l2g, Xh.l2g)
+    ia, ja = Xh.graph()
+    oia, oja = orc.graph(l2g, ndof)
+    assert np.array_equal(ia, oia) and np.array_equal(ja, oja)
+
+
 def test_dof_counts_unit_cube():
     m = 4
     mesh = fpp.unitCube(m)
