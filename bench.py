@@ -138,17 +138,24 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
 
+    def wait_first(self, timeout=8.0):
+        """nvidia-smi needs a moment to come up: do not start the timed region before it prints"""
+        t0 = time.time()
+        while self.proc and not self.rows and time.time() - t0 < timeout:
+            time.sleep(0.02)
+
     def stop(self, t0, t1):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
-        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.2] or [r for _, r in self.rows[-3:]]
+        rows = [r for t, r in self.rows if t0 <= t <= t1] or [r for _, r in self.rows[-3:]]
         sm = sorted(float(r[0]) for r in rows if r[0].replace(".", "").isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k] == "Active" for r in rows)]
         smax = float(rows[0][1]) if rows and rows[0][1].replace(".", "").isdigit() else None
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": reasons, "samples": len(rows)}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": reasons, "samples": len(rows),
+                "window": "timed region and the same step repeated back to back for %.2f s after it" % (t1 - t0)}
 
 
 def gpu_arm(args):
@@ -222,12 +229,14 @@ def gpu_arm(args):
             dist.barrier()
             torch.cuda.synchronize()
 
+    sampler = ClockSampler(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
         step()
+    if sampler:
+        sampler.wait_first()
     barrier()
     check(lib.feelgpu_set_timing(eng.ctx, 1), eng.ctx)
     l0 = eng.launch_count()
-    sampler = ClockSampler(local) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kern_ms = []
     tw0 = time.time()
@@ -239,7 +248,6 @@ def gpu_arm(args):
     tw1 = time.time()
     ms = ev0.elapsed_time(ev1)
     launches = eng.launch_count() - l0
-    clocks = sampler.stop(tw0, tw1) if sampler else None
     # dominant-kernel duration, measured live with CUDA events on the launching stream (a few extra steps)
     tm = (C.c_double * 3)()
     for _ in range(min(args.steps, 10)):
@@ -259,6 +267,12 @@ def gpu_arm(args):
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms = float(tmax.item())
     value = nElt_total * args.steps / (ms * 1e-3)
+    # clocks under load: 20 steps last ~26 ms and nvidia-smi samples every 100 ms, so the same step keeps running for
+    # ~0.6 s more (the count is derived from the all-reduced time: every rank runs the same number of collectives)
+    for _ in range(int(min(2000, max(50, 0.6 / (ms / args.steps * 1e-3))))):
+        step()
+    barrier()
+    clocks = sampler.stop(tw0, time.time()) if sampler else None
 
     # ---- end to end: host buffers, H2D of the coordinates + D2H of the CSR values inside the timed region ----
     e2e = None
