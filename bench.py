@@ -94,6 +94,8 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # the same global mesh as the GPU arm at this N (weak scaling: m grows with N^(1/3)); a step is a bounded sample of it
+    args.m = int(round(args.m * max(args.gpus, 1) ** (1.0 / 3.0)))
     mesh, Xh, ia, ja, info = workload(args)
     cores = physical_cores()
     sample = min(mesh.numElements(), 400_000 * cores)
