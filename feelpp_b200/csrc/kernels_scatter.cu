@@ -304,6 +304,43 @@ k_form1(const FormParams* __restrict__ P, DevTables T, int64_t nElt, const doubl
     }
 }
 
+// form1 with a point-dependent coefficient (expr("...") at xReal, idv(field)): the coefficient is evaluated once per
+// (element, quadrature point) -- thread = (element, q) -- and left in shared memory together with prod[q] = w_q J; then
+// thread = (element, node) forms the same sum, in the same order, as k_form1.  A block works on tiles of `tile` elements.
+__global__ void __launch_bounds__(256)
+k_form1_coeff(const FormParams* __restrict__ P, DevTables T, int64_t nElt, int tile, const double* __restrict__ xyz,
+              const int4* __restrict__ conn, const int32_t* __restrict__ l2g, int nd, const int32_t* __restrict__ l2gf,
+              const double* __restrict__ fvals, double* __restrict__ b)
+{
+    extern __shared__ double smem[];
+    const int n = P->n, nq = P->nq, nf = P->nf;
+    double* s_phi = smem;
+    double* s_phif = s_phi + n * nq;
+    double* s_prod = s_phif + nf * nq;       // [tile][nq]
+    double* s_f = s_prod + tile * nq;        // [tile][nq]
+    for (int k = threadIdx.x; k < n * nq; k += blockDim.x) s_phi[k] = T.phi[k];
+    for (int k = threadIdx.x; k < nf * nq; k += blockDim.x) s_phif[k] = T.phif[k];
+    __syncthreads();
+    for (int64_t e0 = (int64_t)blockIdx.x * tile; e0 < nElt; e0 += (int64_t)gridDim.x * tile) {
+        const int ne = (int)min((int64_t)tile, nElt - e0);
+        for (int t = threadIdx.x; t < ne * nq; t += blockDim.x) {
+            const int el = t / nq, q = t - el * nq;
+            Geo g;
+            geo_update(xyz, __ldg(&conn[e0 + el]), g);
+            s_prod[t] = P->w[q] * g.J;
+            s_f[t] = coeff_at(P, s_phif, g, e0 + el, q, l2gf, fvals);
+        }
+        __syncthreads();
+        for (int t = threadIdx.x; t < ne * n; t += blockDim.x) {
+            const int el = t / n, i = t - el * n;
+            double s = 0;
+            for (int q = 0; q < nq; ++q) s += s_prod[el * nq + q] * (s_f[el * nq + q] * s_phi[i * nq + q]);
+            atomicAdd(&b[l2g[(e0 + el) * nd + i]], s);
+        }
+        __syncthreads();
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // boundary faces (feelvf/integrator.hpp:3242-3704): the points q of block f = local face of the tables lie on that face of
 // the reference tet; prod[q] = w[q] * J * |B n_f| (feelpoly/pointsetquadrature.hpp:481-490), n_f the reference normal:
@@ -625,6 +662,18 @@ int feelgpu_launch_form1(feelgpu_space_t sp, const FormParams& hp, const feelgpu
         fvals = desc->coeff.field_values;
     }
     size_t sh = sizeof(double) * (hp.n * hp.nq + hp.nf * hp.nq);
+    if (hp.coeff_kind != FEELGPU_COEFF_CONST && hp.ncomp == 1) {
+        // tiles sized to the default 48 KB of dynamic shared memory (tables <= 20 KB at nq = 64)
+        const int tile = (int)std::min<size_t>(64, (48 * 1024 - sh) / (sizeof(double) * 2 * hp.nq));
+        if (tile >= 1) {
+            const size_t sht = sh + sizeof(double) * 2 * tile * hp.nq;
+            const int g2 = (int)std::max<int64_t>(1, std::min<int64_t>((m->nElt + tile - 1) / tile, (int64_t)ctx->sm_count * 16));
+            k_form1_coeff<<<g2, 256, sht, s>>>(dP, T, m->nElt, tile, m->d_xyz, m->d_conn, sp->d_l2g, sp->nd, l2gf, fvals, b);
+            ctx->launches++;
+            FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+            return FEELGPU_OK;
+        }
+    }
     int64_t total = m->nElt * hp.n;
     int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 64);
     if (grid < 1) grid = 1;

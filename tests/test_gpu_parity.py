@@ -317,3 +317,22 @@ def test_update_points(engine, pinned):
         engine.lib.feelgpu_sync(engine.ctx)
         if hx:
             engine.lib.feelgpu_host_free_pinned(engine.ctx, hx)
+
+
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_form1_field_coefficient(engine, meshes, order):
+    """l = integrate(elements(mesh), idv(k)*id(v)) with k a P1 field on the device (the right-hand side / residual of a
+    nonlinear re-assembly): quadrature order = order + 1"""
+    mesh = meshes["scr"]
+    Xh, Kh = fpp.Pch(mesh, order), fpp.Pch(mesh, 1)
+    kv = Kh.interpolate(lambda x, y, z: 1 + 0.5 * np.sin(2 * np.pi * x) + y * z)
+    k = fpp.Element(Kh, kv)
+    v = fpp.Element(Xh)
+    l = fpp.form1(_test=Xh, engine=engine)
+    l.assign(integrate(_range=elements(mesh), _expr=idv(k) * id(v)))
+    co = orc.Coeff(kind=orc.COEFF_FIELD, field_order=1, field_l2g=Kh.l2g, field_values=kv)
+    ref = orc.form1(order, 1, orc.quad_order_form1(order, 1), mesh.xyz, mesh.conn, Xh.l2g, Xh.nDof(), co)
+    np.testing.assert_allclose(l.values(), ref, rtol=1e-12, atol=1e-12 * np.abs(ref).max())
+    # int k = sum_i b_i (partition of unity); k is piecewise linear, the vertex rule on every tet is exact
+    vol = np.abs(np.linalg.det(mesh.xyz[mesh.conn[:, 1:]] - mesh.xyz[mesh.conn[:, :1]])) / 6
+    assert abs(l.values().sum() - float((vol * kv[Kh.l2g].mean(1)).sum())) <= 1e-12
