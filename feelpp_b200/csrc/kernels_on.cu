@@ -11,6 +11,7 @@
 #include "feelgpu_internal.h"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace {
 
@@ -68,6 +69,7 @@ __global__ void k_on_rows(int n, const int32_t* __restrict__ rows, const double*
 
 // y = A x on the device CSR (MatrixPetsc::multVector -> MatMult, feelalg/matrixpetsc.cpp:998-1062): one warp per row,
 // 32-bit column ids, x through the read-only path (it stays in L2: 8 B per dof against 12 B per nonzero streamed)
+// Row-per-warp variant: used for rows longer than MATVEC_CAP and under FEELGPU_MATVEC_ROW_PER_WARP=1 (A/B timing).
 __global__ void __launch_bounds__(256)
 k_matvec(int64_t nRows, const int64_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
          const double* __restrict__ x, double* __restrict__ y)
@@ -81,6 +83,56 @@ k_matvec(int64_t nRows, const int64_t* __restrict__ ia, const int32_t* __restric
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         if (lane == 0) y[r] = s;
+    }
+}
+
+// Streaming variant (FE rows are short: 15 / 29 / 48 nonzeros for P1 / P2 / P3): a warp takes up to 32 consecutive rows
+// whose nonzeros fit MATVEC_CAP values, streams that contiguous piece of (a, ja) with all lanes -- coalesced, many loads in
+// flight -- leaves the products in shared memory, and lane l sums row l's piece.
+constexpr int MATVEC_CAP = 768, MATVEC_WARPS = 4;
+
+__global__ void __launch_bounds__(32 * MATVEC_WARPS, 8)
+k_matvec_stream(int64_t nRows, const int64_t* __restrict__ ia, const int32_t* __restrict__ ja,
+                const double* __restrict__ a, const double* __restrict__ x, double* __restrict__ y)
+{
+    __shared__ double s_prod[MATVEC_WARPS][MATVEC_CAP];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    double* sp = s_prod[w];
+    const int64_t nw = (int64_t)gridDim.x * MATVEC_WARPS;
+    for (int64_t r0 = ((int64_t)blockIdx.x * MATVEC_WARPS + w) * 32; r0 < nRows; r0 += nw * 32) {
+        const int64_t rend = min(r0 + 32, nRows);
+        int64_t rbeg = r0;
+        while (rbeg < rend) {
+            const int64_t myr = rbeg + lane;
+            const int64_t plo = ia[rbeg];
+            const int64_t myend = myr < rend ? ia[myr + 1] : -1;
+            const bool fits = myr < rend && myend - plo <= MATVEC_CAP;     // monotone in the lane: a prefix of the warp
+            const int R = __popc(__ballot_sync(full, fits));
+            if (R == 0) {   // one row longer than the staging buffer
+                const int64_t p1 = __shfl_sync(full, myend, 0);
+                double s = 0.0;
+                for (int64_t p = plo + lane; p < p1; p += 32) s += a[p] * __ldg(&x[ja[p]]);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(full, s, o);
+                if (lane == 0) y[rbeg] = s;
+                rbeg += 1;
+                continue;
+            }
+            const int cnt = (int)(__shfl_sync(full, myend, R - 1) - plo);
+            int64_t mybeg = __shfl_up_sync(full, myend, 1);
+            if (lane == 0) mybeg = plo;
+#pragma unroll 4
+            for (int k = lane; k < cnt; k += 32) sp[k] = a[plo + k] * __ldg(&x[ja[plo + k]]);
+            __syncwarp();
+            if (lane < R) {
+                double s = 0.0;
+                for (int k = (int)(mybeg - plo); k < (int)(myend - plo); ++k) s += sp[k];
+                y[myr] = s;
+            }
+            __syncwarp();
+            rbeg += R;
+        }
     }
 }
 
@@ -98,9 +150,19 @@ int feelgpu_launch_matvec(feelgpu_pattern_t pat, const double* a, const double* 
         return FEELGPU_ERR_UNSUPPORTED;
     }
     if (pat->nRows == 0) return FEELGPU_OK;
-    const int threads = 256;
-    const int grid = (int)std::min<int64_t>((pat->nRows * 32 + threads - 1) / threads, (int64_t)ctx->sm_count * 32);
-    k_matvec<<<grid, threads, 0, s>>>(pat->nRows, pat->d_ia, pat->d_ja32, a, x, y);
+    static const bool row_per_warp = [] {
+        const char* e = std::getenv("FEELGPU_MATVEC_ROW_PER_WARP");
+        return e && e[0] == '1';
+    }();
+    if (row_per_warp) {
+        const int threads = 256;
+        const int grid = (int)std::min<int64_t>((pat->nRows * 32 + threads - 1) / threads, (int64_t)ctx->sm_count * 32);
+        k_matvec<<<grid, threads, 0, s>>>(pat->nRows, pat->d_ia, pat->d_ja32, a, x, y);
+    } else {
+        const int64_t groups = (pat->nRows + 31) / 32;
+        const int grid = (int)std::min<int64_t>((groups + MATVEC_WARPS - 1) / MATVEC_WARPS, (int64_t)ctx->sm_count * 28);
+        k_matvec_stream<<<grid, 32 * MATVEC_WARPS, 0, s>>>(pat->nRows, pat->d_ia, pat->d_ja32, a, x, y);
+    }
     ctx->launches++;
     FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
     return FEELGPU_OK;

@@ -50,3 +50,18 @@ for name, ex in (("l = 1*id(v) (Q=4)", cst(1.0) * id(v)), ("l = sin(pi x)cos(pi 
         l.assign(integ)
     eng.sync()
     print(name, "ms per assembly (host clock, 10 back to back)", round(1e2 * (time.perf_counter() - t0), 4))
+
+# y = A x on the assembled matrix (device hand-off)
+import numpy as np
+n = Xh.nDof()
+dx = eng.to_device(np.ones(n))
+dy = eng.malloc(8 * n)
+check(lib.feelgpu_matvec(a.pat, a.d_values, dx, dy, None), eng.ctx)
+eng.sync()
+t0 = time.perf_counter()
+for _ in range(20):
+    check(lib.feelgpu_matvec(a.pat, a.d_values, dx, dy, None), eng.ctx)
+eng.sync()
+ms = 1e3 * (time.perf_counter() - t0) / 20
+nnz = int(a.nnz)
+print("y = A x  ms", round(ms, 4), " GB/s (12 B per nonzero + 24 B per row)", round((12.0 * nnz + 24.0 * n) / ms / 1e6, 1))
