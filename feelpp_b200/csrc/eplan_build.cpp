@@ -2,6 +2,8 @@
 #include "eplan.h"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <thread>
@@ -384,6 +386,15 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                       const double* xyz, const int32_t* conn, int64_t nRows, const int64_t* ia, const uint16_t* pos,
                       int nthreads, EPlanHost& plan)
 {
+    // FEELGPU_EPLAN_TIMING=1: phase times of the builder on stderr
+    const bool timing = std::getenv("FEELGPU_EPLAN_TIMING") != nullptr;
+    auto tprev = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[eplan build] %-28s %8.3f s\n", what, std::chrono::duration<double>(now - tprev).count());
+        tprev = now;
+    };
     Builder B;
     B.spec = eplan_spec(order);
     if (!B.spec) { plan.error = "entity plan: order not covered"; return false; }
@@ -407,9 +418,12 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             for (int b = a + 1; b < 4; ++b)
                 if (conn[4 * e + a] == conn[4 * e + b]) { plan.error = "entity plan: degenerate element"; return false; }
     }
+    lap("input checks");
     B.node_units();
+    lap("node -> element units");
     if (const char* cv = std::getenv("FEELGPU_EPLAN_CURVE")) B.use_hilbert = std::strcmp(cv, "morton") != 0;
     B.curve_order();
+    lap("space-filling curve order");
     if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
     nthreads = std::min(nthreads, 64);
 
@@ -485,6 +499,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         }
     }
 
+    lap("CTA packing (serial)");
     // ---- tasks and chunks, in parallel over CTAs ----
     const int64_t nCta = (int64_t)segs.size();
     const EPlanSpec& S = *B.spec;
@@ -507,7 +522,16 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         struct ChunkTmp { uint8_t type, niter; uint32_t first, count; int cost; };
         std::vector<ChunkTmp> ctmp;
         std::vector<uint32_t> noff, segoff, pads;
+        double sect[6] = {0, 0, 0, 0, 0, 0};
+        auto sprev = std::chrono::steady_clock::now();
+        auto mark = [&](int k) {
+            if (!timing || t != 0) return;
+            auto now = std::chrono::steady_clock::now();
+            sect[k] += std::chrono::duration<double>(now - sprev).count();
+            sprev = now;
+        };
         for (int64_t c = nCta * t / nthreads; c < nCta * (t + 1) / nthreads; ++c) {
+            mark(4);
             CtaSeg& sg = segs[c];
             for (int ty = 0; ty < S.ntypes; ++ty) tasks[ty].clear();
             iterw.clear();
@@ -614,6 +638,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                 }
             }
             pc.nrows = (uint32_t)L.rows.size() - pc.row0;
+            mark(0);
             // ---- renumber the visit slots: every half-warp wants 16 distinct bank pairs (slot mod 16) per iteration, which
             // needs the load-weighted use of the 16 residues to be level: deal the slots, most used first, in snake order
             {
@@ -647,12 +672,14 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                     }
                 }
             }
+            mark(1);
             if (!getenv("FEELGPU_EPLAN_NO_VERTEX_BANKS")) {
                 double before = 0;
                 L.a1 += level_vertex_banks(sg.nvisit, sg.nverts, plan.visits.data() + sg.visit_off, vstride,
                                            plan.verts.data() + sg.vert_off, sg.nverts, before);
                 L.a1_before += before;
             }
+            mark(2);
             // ---- chunks: 32 tasks of one type, longest first ----
             // All S loads of one iteration hit the bank pair (visit slot mod 16); a half-warp is served in one pass only
             // if its 16 lanes hit distinct bank pairs.  Which tasks share a half-warp and the order in which a task walks
@@ -661,6 +688,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             ctmp.clear();
             lanes.clear();
             for (int ty = 0; ty < S.ntypes; ++ty) {
+                mark(5);
                 std::vector<Task>& tv = tasks[ty];
                 L.ntasks += (int64_t)tv.size();
                 if (S.type[ty].phaseA) continue;
@@ -712,7 +740,9 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                                 }
                                 std::swap(res[it], res[bj]);
                                 cost += bc * S.type[ty].nld;
+                                if (cost >= bestcost) break;   // costs only grow: this candidate cannot win any more
                             }
+                            if (cost >= bestcost) continue;
                             for (int o = 0; o < nto; ++o) cost += outcnt[o * 16 + (tk.out[o] & 15)];   // stores into the row block
                             if (cost < bestcost) { bestcost = cost; best = c; if (!cost) break; }
                         }
@@ -738,18 +768,23 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                     }
                     ctmp.push_back(ch);
                 }
+                mark(3);
                 // ---- tasks with two elements, then with one: buckets by bank pair.  A lane takes a task whose bank pairs
                 // are still free in both iterations of its half-warp (the order of the two elements is chosen to fit).
                 {
                     for (auto& cvec : cell) cvec.clear();
                     for (auto& cvec : cell1) cvec.clear();
                     size_t rem2 = 0, rem1 = 0;
+                    uint16_t ne[16];      // ne[a] bit b: the cell of bank pairs {a, b} holds tasks (the scan below skips the rest)
+                    for (int z = 0; z < 16; ++z) ne[z] = 0;
                     for (size_t k = nlong; k < tv.size(); ++k) {
                         const uint32_t* src = &iterw[tv[k].first];
                         const int r0 = src[0] & 15;
                         if (tv[k].niter == 2) {
                             const int r1 = src[1] & 15;
                             cell[std::min(r0, r1) * 16 + std::max(r0, r1)].push_back((uint32_t)k);
+                            ne[r0] |= (uint16_t)(1u << r1);
+                            ne[r1] |= (uint16_t)(1u << r0);
                             ++rem2;
                         } else {
                             cell1[r0].push_back((uint32_t)k);
@@ -776,10 +811,10 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             std::vector<uint32_t>* bcv = nullptr;
                             if (nt == 2) {
                                 for (int a2 = 0; a2 < 16; ++a2)      // a2: bank pair of iteration 0, b2: of iteration 1
-                                    for (int b2 = 0; b2 < 16; ++b2) {
+                                    for (uint32_t mb = ne[a2]; mb; mb &= mb - 1) {
+                                        const int b2 = __builtin_ctz(mb);
                                         std::vector<uint32_t>& cv2 = cell[std::min(a2, b2) * 16 + std::max(a2, b2)];
                                         const size_t sz = cv2.size();
-                                        if (!sz) continue;
                                         const int cost = cnt2[a2] + cnt2[16 + b2];
                                         if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bcv = &cv2; ba = a2; bb = b2; }
                                     }
@@ -803,6 +838,10 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             const uint32_t ti = cv[bk];
                             cv[bk] = cv.back();
                             cv.pop_back();
+                            if (nt == 2 && cv.empty()) {
+                                ne[ba] &= (uint16_t)~(1u << bb);
+                                ne[bb] &= (uint16_t)~(1u << ba);
+                            }
                             if (nt == 2) --rem2; else --rem1;
                             const Task& tk = tv[ti];
                             uint32_t* src = &iterw[tk.first];
@@ -817,6 +856,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                     }
                 }
             }
+            mark(5);
             std::stable_sort(ctmp.begin(), ctmp.end(), [](const ChunkTmp& a, const ChunkTmp& b) { return a.cost > b.cost; });
             // does every slot of the row block receive a value?  (always, unless the graph holds entries no element produces)
             covered.assign(sg.nout, 0);
@@ -881,7 +921,11 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
             pc.nq = (uint32_t)(L.blob.size() / 4) - pc.q0;
             if (pc.nchunk > 65535 || pc.nq > 65535) { L.error = "entity plan: too many chunks in one CTA"; return; }
             L.per.push_back(pc);
+            mark(4);
         }
+        if (timing && t == 0)
+            std::fprintf(stderr, "[eplan build] thread 0: rows/tasks %.3f  slots %.3f  vertex banks %.3f  window search %.3f  buckets %.3f  emission %.3f s\n",
+                         sect[0], sect[1], sect[2], sect[3], sect[5], sect[4]);
     };
     {
         std::vector<std::thread> th;
@@ -891,6 +935,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     }
     for (auto& L : locals)
         if (!L.error.empty()) { plan.error = L.error; return false; }
+    lap("tasks and chunks (threads)");
 
     // ---- concatenate ----
     plan.order = order;
@@ -941,5 +986,6 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     }
     plan.blob.resize(plan.blob.size() + 64, 0u);
     plan.nvisits = (int64_t)plan.visits.size() / vstride;
+    lap("concatenate");
     return true;
 }
