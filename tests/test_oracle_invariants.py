@@ -157,3 +157,53 @@ def test_threaded_loop_matches_serial_loop():
         assert np.abs(s - t).max() <= 1e-15 * np.abs(sa).max()
         np.testing.assert_allclose(ta, sa, rtol=1e-14)
         assert (ta >= np.abs(t) - 1e-18).all()
+
+
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_local_matrices_match_exact_barycentric_integration(order):
+    """Known-answer check that shares nothing with the oracle's evaluation path but the nodal points: the nodal basis is
+    expanded in barycentric monomials (Vandermonde solve) and mass / stiffness are integrated exactly with
+    int_T lambda^alpha = 6|T| alpha! / (|alpha|+3)!  -- no quadrature table, no Dubiner basis, no geomap."""
+    from itertools import product
+    from math import factorial
+    pts = orc.lagrange_points(order)
+    n = len(pts)
+    lam = np.empty((n, 4))
+    lam[:, 1:] = (pts + 1) / 2
+    lam[:, 0] = 1 - lam[:, 1:].sum(1)
+    alphas = [a for a in product(range(order + 1), repeat=4) if sum(a) == order]
+    assert len(alphas) == n
+    V = np.array([[np.prod(lam[i] ** np.array(a)) for a in alphas] for i in range(n)])
+    Cf = np.linalg.inv(V)                         # phi_i = sum_a Cf[a, i] lambda^a
+    rng = np.random.default_rng(5)
+    G = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1.0]]) + 0.2 * rng.standard_normal((4, 3))
+    T = np.hstack([np.ones((4, 1)), G])
+    vol = abs(np.linalg.det(T)) / 6
+    dlam = np.linalg.inv(T)[1:, :].T              # dlam[m] = grad lambda_m
+
+    def integral(a):
+        if min(a) < 0:
+            return 0.0
+        return 6 * vol * np.prod([factorial(x) for x in a]) / factorial(sum(a) + 3)
+
+    na = len(alphas)
+    Ma = np.array([[integral(tuple(np.add(a, b))) for b in alphas] for a in alphas])
+    Ka = np.zeros((na, na))
+    gg = dlam @ dlam.T
+    for ia_, a in enumerate(alphas):
+        for ib, b in enumerate(alphas):
+            s = 0.0
+            for m in range(4):
+                if not a[m]:
+                    continue
+                for l in range(4):
+                    if not b[l]:
+                        continue
+                    e = list(np.add(a, b)); e[m] -= 1; e[l] -= 1
+                    s += a[m] * b[l] * gg[m, l] * integral(tuple(e))
+            Ka[ia_, ib] = s
+    M_exact, K_exact = Cf.T @ Ma @ Cf, Cf.T @ Ka @ Cf
+    M = orc.local_matrix(orc.MASS, order, 1, orc.quad_order_form2(orc.MASS, order), G).reshape(n, n)
+    K = orc.local_matrix(orc.STIFFNESS, order, 1, orc.quad_order_form2(orc.STIFFNESS, order), G).reshape(n, n)
+    assert np.abs(M - M_exact).max() < 1e-12 * np.abs(M_exact).max()
+    assert np.abs(K - K_exact).max() < 1e-12 * np.abs(K_exact).max()
