@@ -5,7 +5,8 @@
 // header include/feelgpu_quadrature_tables.h (tools/gen_quadrature_tables.py).
 //
 // Parity status: "parity unpinned" (no golden matrices exist in the reference test-suite and the reference cannot
-// be built here).  Pinned by invariants in tests/test_oracle_invariants.py.
+// be built here).  Pinned by invariants and by exactly integrated known answers (barycentric monomials) in
+// tests/test_oracle_invariants.py.
 #include "feel_oracle.h"
 #include "../include/feelgpu_quadrature_tables.h"
 

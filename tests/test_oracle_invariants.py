@@ -207,3 +207,92 @@ def test_local_matrices_match_exact_barycentric_integration(order):
     K = orc.local_matrix(orc.STIFFNESS, order, 1, orc.quad_order_form2(orc.STIFFNESS, order), G).reshape(n, n)
     assert np.abs(M - M_exact).max() < 1e-12 * np.abs(M_exact).max()
     assert np.abs(K - K_exact).max() < 1e-12 * np.abs(K_exact).max()
+
+
+def test_local_elasticity_matches_exact_barycentric_integration():
+    """P2 vector elasticity, local index I = n*c + i (doftable.hpp:1289-1292):
+    E[(i,c),(j,d)] = lam D[c,d,i,j] + mu (delta_cd tr D[.,.,i,j] + D[d,c,i,j]), D[c,d,i,j] = int d_c phi_i d_d phi_j, integrated
+    exactly in barycentric monomials."""
+    from itertools import product
+    from math import factorial
+    order, n = 2, 10
+    pts = orc.lagrange_points(order)
+    lam4 = np.empty((n, 4))
+    lam4[:, 1:] = (pts + 1) / 2
+    lam4[:, 0] = 1 - lam4[:, 1:].sum(1)
+    alphas = [a for a in product(range(order + 1), repeat=4) if sum(a) == order]
+    Cf = np.linalg.inv(np.array([[np.prod(lam4[i] ** np.array(a)) for a in alphas] for i in range(n)]))
+    rng = np.random.default_rng(11)
+    G = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1.0]]) + 0.2 * rng.standard_normal((4, 3))
+    T = np.hstack([np.ones((4, 1)), G])
+    vol = abs(np.linalg.det(T)) / 6
+    dlam = np.linalg.inv(T)[1:, :].T              # [m][c]
+
+    def integral(a):
+        return 0.0 if min(a) < 0 else 6 * vol * np.prod([factorial(x) for x in a]) / factorial(sum(a) + 3)
+
+    Da = np.zeros((3, 3, n, n))                  # in the monomial basis
+    for ia_, a in enumerate(alphas):
+        for ib, b in enumerate(alphas):
+            for m in range(4):
+                for l in range(4):
+                    if a[m] and b[l]:
+                        e = list(np.add(a, b)); e[m] -= 1; e[l] -= 1
+                        Da[:, :, ia_, ib] += a[m] * b[l] * integral(tuple(e)) * np.outer(dlam[m], dlam[l])
+    D = np.einsum("ai,cdab,bj->cdij", Cf, Da, Cf)
+    lam, mu = 4e7, 3e7
+    E_exact = np.zeros((3 * n, 3 * n))
+    for c in range(3):
+        for d in range(3):
+            blk = lam * D[c, d] + mu * D[d, c]
+            if c == d:
+                blk = blk + mu * (D[0, 0] + D[1, 1] + D[2, 2])
+            E_exact[n * c:n * c + n, n * d:n * d + n] = blk
+    E = orc.local_matrix(orc.ELASTICITY, 2, 3, 2, G, orc.Coeff(lam=lam, mu=mu)).reshape(3 * n, 3 * n)
+    assert np.abs(E - E_exact).max() < 1e-12 * np.abs(E_exact).max()
+
+
+@pytest.mark.parametrize("order", [1, 2, 3])
+def test_load_vector_and_field_weighted_stiffness_match_exact_integration(order):
+    """form1 f*id(v) with f = 1 (b_i = int phi_i) and form2 idv(k)*inner(gradt,grad) with k a P1 field
+    (K_ij = sum_p k_p int lambda_p grad phi_i . grad phi_j), both exactly in barycentric monomials; the oracle uses the
+    quadrature orders the reference selects (expr.hpp:1075-1076)."""
+    from itertools import product
+    from math import factorial
+    pts = orc.lagrange_points(order)
+    n = len(pts)
+    lam4 = np.empty((n, 4))
+    lam4[:, 1:] = (pts + 1) / 2
+    lam4[:, 0] = 1 - lam4[:, 1:].sum(1)
+    alphas = [a for a in product(range(order + 1), repeat=4) if sum(a) == order]
+    Cf = np.linalg.inv(np.array([[np.prod(lam4[i] ** np.array(a)) for a in alphas] for i in range(n)]))
+    rng = np.random.default_rng(order)
+    G = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1.0]]) + 0.2 * rng.standard_normal((4, 3))
+    T = np.hstack([np.ones((4, 1)), G])
+    vol = abs(np.linalg.det(T)) / 6
+    gg = np.linalg.inv(T)[1:, :].T
+    gg = gg @ gg.T
+
+    def integral(a):
+        return 0.0 if min(a) < 0 else 6 * vol * np.prod([factorial(x) for x in a]) / factorial(sum(a) + 3)
+
+    b_exact = Cf.T @ np.array([integral(a) for a in alphas])
+    conn = np.array([[0, 1, 2, 3]], dtype=np.int32)
+    l2g = np.arange(n, dtype=np.int32).reshape(1, n)
+    b = orc.form1(order, 1, orc.quad_order_form1(order, 0), G, conn, l2g, n)
+    assert np.abs(b - b_exact).max() < 1e-12 * np.abs(b_exact).max()
+
+    kv = 1 + rng.random(4)
+    Ka = np.zeros((n, n))
+    for ia_, a in enumerate(alphas):
+        for ib, bb in enumerate(alphas):
+            for m in range(4):
+                for l in range(4):
+                    if a[m] and bb[l]:
+                        for p in range(4):
+                            e = list(np.add(a, bb)); e[m] -= 1; e[l] -= 1; e[p] += 1
+                            Ka[ia_, ib] += kv[p] * a[m] * bb[l] * gg[m, l] * integral(tuple(e))
+    K_exact = Cf.T @ Ka @ Cf
+    co = orc.Coeff(kind=orc.COEFF_FIELD, field_order=1, field_l2g=conn, field_values=kv)
+    K = orc.local_matrix(orc.STIFFNESS, order, 1, orc.quad_order_form2(orc.STIFFNESS, order, 1), G, co).reshape(n, n)
+    assert np.abs(K - K_exact).max() < 1e-12 * np.abs(K_exact).max()
