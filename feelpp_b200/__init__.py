@@ -3,7 +3,7 @@
 The product is the CUDA library behind include/feelgpu.h (feelpp_b200/csrc -> feelpp_b200/lib/libfeelgpu.so) and the
 C++ host mirror (feelpp_b200/host).  This Python package is the test/bench harness around them (ctypes only).
 """
-from .hostmirror import (Mesh, unitCube, elements, boundaryfaces, FunctionSpace, Pch, Pchv, im, tabulate, lagrangePoints,
+from .hostmirror import (Mesh, unitCube, loadMesh, elements, boundaryfaces, markedfaces, FunctionSpace, Pch, Pchv, im, tabulate, lagrangePoints,
                          nLocalDof, GinacProgram)
 from .vf import (Element, cst, vec, idv, expr, id, idt, grad, gradt, trans, sym, trace, Id, inner, integrate, on,
                  classify_form1, classify_form2)

@@ -8,6 +8,7 @@
 
 #include "doftable.hpp"
 #include "ginac.hpp"
+#include "gmsh.hpp"
 #include "lagrange.hpp"
 #include "mesh.hpp"
 #include "stencil.hpp"
@@ -38,6 +39,40 @@ int feelhost_unit_cube(int m, double jitter, int shuffle, double* xyz, int32_t* 
         std::memcpy(conn, mesh->conn.data(), sizeof(int32_t) * mesh->conn.size());
     })
 }
+
+// ---- Gmsh .msh reader (feelfilters/importergmsh.hpp:983-1420) ----
+struct feelhost_gmsh_s { GmshMesh m; };
+int feelhost_gmsh_open(const char* path, int elementaryAsPhysical, feelhost_gmsh_s** out, int64_t* nPts, int64_t* nElt,
+                       int64_t* nTri, int64_t* namesLen, double* version, int* binary)
+{
+    GUARD({
+        auto* h = new feelhost_gmsh_s;
+        try { h->m = readGmsh(path, elementaryAsPhysical != 0); }
+        catch (...) { delete h; throw; }
+        *out = h;
+        *nPts = (int64_t)h->m.pointId.size();
+        *nElt = (int64_t)h->m.eltMarker.size();
+        *nTri = (int64_t)h->m.triMarker.size();
+        *namesLen = (int64_t)h->m.physicalNames.size();
+        *version = h->m.version;
+        *binary = h->m.binary ? 1 : 0;
+    })
+}
+int feelhost_gmsh_get(feelhost_gmsh_s* h, double* xyz, int64_t* pointId, int32_t* conn, int32_t* eltMarker, int32_t* tri,
+                      int32_t* triMarker, char* names)
+{
+    GUARD({
+        GmshMesh const& m = h->m;
+        std::memcpy(xyz, m.xyz.data(), sizeof(double) * m.xyz.size());
+        std::memcpy(pointId, m.pointId.data(), sizeof(int64_t) * m.pointId.size());
+        std::memcpy(conn, m.conn.data(), sizeof(int32_t) * m.conn.size());
+        std::memcpy(eltMarker, m.eltMarker.data(), sizeof(int32_t) * m.eltMarker.size());
+        if (!m.tri.empty()) std::memcpy(tri, m.tri.data(), sizeof(int32_t) * m.tri.size());
+        if (!m.triMarker.empty()) std::memcpy(triMarker, m.triMarker.data(), sizeof(int32_t) * m.triMarker.size());
+        if (!m.physicalNames.empty()) std::memcpy(names, m.physicalNames.data(), m.physicalNames.size());
+    })
+}
+int feelhost_gmsh_free(feelhost_gmsh_s* h) { delete h; return 0; }
 
 // ---- DofTable ----
 int feelhost_doftable(int64_t nPts, const double* xyz, int64_t nElt, const int32_t* conn, int order, int ncomp,

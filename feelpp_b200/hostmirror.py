@@ -25,6 +25,16 @@ class Mesh:
 
     numGlobalElements = numElements
 
+    tri = None
+
+    def markerId(self, m):
+        """marker name ($PhysicalNames) or number -> number (MeshBase::markerId)"""
+        if isinstance(m, str):
+            if m not in getattr(self, "markerNames", {}):
+                raise KeyError("unknown marker %r" % m)
+            return self.markerNames[m][1]
+        return int(m)
+
 
 def unitCube(m, jitter=0.0, shuffle=False):
     """Synthetic unit-cube tet mesh, m^3 cells x 6 tets (stands in for gmsh's unitCube(), feelfilters/unitcube.cpp:38-52)."""
@@ -60,6 +70,68 @@ class BoundaryFaceRange:
 
 def boundaryfaces(mesh):
     return BoundaryFaceRange(mesh)
+
+
+class MarkedFaceRange(BoundaryFaceRange):
+    """markedfaces(mesh, marker) (feelmesh/filters.hpp): the boundary faces that carry one of the given markers, as
+    (element, local face) pairs in element order.  Markers come from the triangles of a .msh file (loadMesh)."""
+
+    def __init__(self, mesh, markers):
+        super().__init__(mesh)
+        self.markers = markers
+
+    def faces(self):
+        if self._faces is None:
+            mesh = self.mesh
+            if getattr(mesh, "tri", None) is None:
+                raise ValueError("markedfaces(): the mesh carries no marked faces (use loadMesh on a .msh with triangles)")
+            ids = [mesh.markerId(m) for m in (self.markers if isinstance(self.markers, (list, tuple)) else [self.markers])]
+            e, f = BoundaryFaceRange(mesh).faces()
+            npts = mesh.numPoints()
+            F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])
+            fv = np.sort(mesh.conn.astype(np.int64)[e[:, None], F2P[f]], axis=1)
+            key = (fv[:, 0] * npts + fv[:, 1]) * npts + fv[:, 2]
+            tv = np.sort(mesh.tri[np.isin(mesh.triMarker, ids)].astype(np.int64), axis=1)
+            tkey = (tv[:, 0] * npts + tv[:, 1]) * npts + tv[:, 2]
+            sel = np.isin(key, tkey)
+            self._faces = (np.ascontiguousarray(e[sel]), np.ascontiguousarray(f[sel]))
+        return self._faces
+
+
+def markedfaces(mesh, markers):
+    return MarkedFaceRange(mesh, markers)
+
+
+def loadMesh(path, elementaryAsPhysical=False):
+    """loadMesh(_mesh=new Mesh<Simplex<3>>, _filename="x.msh") (feelfilters/loadmesh.hpp -> ImporterGmsh::readFromFile,
+    feelfilters/importergmsh.hpp:983-1420): MSH 2.x ASCII / binary and MSH 4.1 ASCII, tetrahedra + marked triangles.
+    Point indices follow the ascending node numbers of the file (mesh.pointId holds them)."""
+    h = capi.host()
+    hd = C.c_void_p()
+    npts, nelt, ntri, nlen = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+    version, binary = C.c_double(), C.c_int()
+    hcheck(h.feelhost_gmsh_open(str(path).encode(), int(bool(elementaryAsPhysical)), C.byref(hd), C.byref(npts),
+                                C.byref(nelt), C.byref(ntri), C.byref(nlen), C.byref(version), C.byref(binary)))
+    try:
+        xyz = np.empty((npts.value, 3), dtype=np.float64)
+        pid = np.empty(npts.value, dtype=np.int64)
+        conn = np.empty((nelt.value, 4), dtype=np.int32)
+        em = np.empty(nelt.value, dtype=np.int32)
+        tri = np.empty((ntri.value, 3), dtype=np.int32)
+        tm = np.empty(ntri.value, dtype=np.int32)
+        names = C.create_string_buffer(max(nlen.value, 1))
+        hcheck(h.feelhost_gmsh_get(hd, ptr(xyz, c_dblp), ptr(pid, c_i64p), ptr(conn, c_i32p), ptr(em, c_i32p),
+                                   ptr(tri, c_i32p), ptr(tm, c_i32p), names))
+    finally:
+        h.feelhost_gmsh_free(hd)
+    mesh = Mesh(xyz, conn)
+    mesh.pointId, mesh.eltMarker, mesh.tri, mesh.triMarker = pid, em, tri, tm
+    mesh.version, mesh.binary = version.value, bool(binary.value)
+    mesh.markerNames = {}
+    for line in names.raw[:nlen.value].decode().splitlines():
+        dim, tag, name = line.split(" ", 2)
+        mesh.markerNames[name] = (int(dim), int(tag))
+    return mesh
 
 
 class ElementRange:
@@ -130,17 +202,22 @@ class FunctionSpace:
         p = self.dofPoints()
         return np.asarray(f(p[:, 0], p[:, 1], p[:, 2]), dtype=np.float64)
 
-    def boundaryDofs(self):
+    def boundaryDofs(self, faces=None):
         """scalar node ids carried by the boundary faces (faces of exactly one element): what
-        on(_range=boundaryfaces(mesh), ...) visits through the face dof table (feelvf/on.hpp:395-449)."""
+        on(_range=boundaryfaces(mesh), ...) visits through the face dof table (feelvf/on.hpp:395-449).  With
+        faces = (element, local face) arrays -- markedfaces(mesh, marker).faces() -- only those faces are visited."""
         conn = self.mesh.conn.astype(np.int64)
         npts = self.mesh.numPoints()
         F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])        # feelmesh/simplexordering.hpp:341-347
         E2P = np.array([[1, 2], [2, 0], [0, 1], [0, 3], [1, 3], [2, 3]])    # :283-291
-        fv = np.sort(conn[:, F2P], axis=2)                                    # [nElt][4][3]
-        key = (fv[..., 0] * npts + fv[..., 1]) * npts + fv[..., 2]
-        _, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
-        onb = (cnt[inv] == 1).reshape(key.shape)                             # [nElt][4] boundary faces
+        if faces is None:
+            fv = np.sort(conn[:, F2P], axis=2)                                    # [nElt][4][3]
+            key = (fv[..., 0] * npts + fv[..., 1]) * npts + fv[..., 2]
+            _, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
+            onb = (cnt[inv] == 1).reshape(key.shape)                             # [nElt][4] boundary faces
+        else:
+            onb = np.zeros((conn.shape[0], 4), dtype=bool)
+            onb[faces[0], faces[1]] = True
         nodes = self.l2g[:, :self.n] // self.ncomp
         out = []
         npe = self.order - 1

@@ -248,7 +248,7 @@ class Integrator:
 
 
 def integrate(_range, _expr, _quad=None):
-    """integrate(_range=elements(mesh) | boundaryfaces(mesh), _expr=..., [_quad=order]) (feelvf/integrate.hpp:64-98)."""
+    """integrate(_range=elements(mesh) | boundaryfaces(mesh) | markedfaces(mesh, m), _expr=..., [_quad=order]) (feelvf/integrate.hpp:64-98)."""
     if not isinstance(_range, (hm.ElementRange, hm.BoundaryFaceRange)):
         raise NotImplementedError("only elements(mesh) and boundaryfaces(mesh) ranges are accelerated")
     return Integrator(_range, _expr, _quad)
@@ -260,7 +260,7 @@ _ON_TYPES = {"elimination": ON_ELIMINATION, "elimination_keep_diagonal": ON_ELIM
 
 
 class On:
-    """on(_range=boundaryfaces(mesh), _rhs=l, _element=u, _expr=g, _type="elimination", _value_on_diagonal=1.0)
+    """on(_range=boundaryfaces(mesh) | markedfaces(mesh, m), _rhs=l, _element=u, _expr=g, _type="elimination", _value_on_diagonal=1.0)
     (feelvf/on.hpp:1126-1190): the Dirichlet dofs and their values are collected on the host by nodal interpolation of
     g (on.hpp:395-449: fe->interpolate(expr)); the elimination itself runs on the device CSR (feelgpu_form2_zero_rows)."""
 
@@ -274,7 +274,7 @@ class On:
 
     def dofs_and_values(self):
         Xh = self.element.space
-        nodes = Xh.boundaryDofs()
+        nodes = Xh.boundaryDofs(self.range.faces() if isinstance(self.range, hm.MarkedFaceRange) else None)
         p = Xh.dofPoints()[nodes]
         g = self.expr
         if callable(g):
