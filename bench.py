@@ -39,6 +39,8 @@ def parse():
     ap.add_argument("--order", type=int, default=2)
     ap.add_argument("--algo", default="auto", choices=["auto", "scatter", "rowplan", "eplan"])
     ap.add_argument("--shuffle", action="store_true", help="Fisher-Yates shuffled element order")
+    ap.add_argument("--mesh", default=None, help="a Gmsh .msh file (tetrahedra) used instead of the synthetic cube; "
+                    "one GPU only, reported as its own workload (never the configs[1] line)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -62,7 +64,7 @@ def workload(args, want_graph=True):
     """builds the host-side objects (untimed setup)"""
     import feelpp_b200 as fpp
     t0 = time.time()
-    mesh = fpp.unitCube(args.m, 0.15, args.shuffle)
+    mesh = fpp.loadMesh(args.mesh) if args.mesh else fpp.unitCube(args.m, 0.15, args.shuffle)
     Xh = fpp.Pch(mesh, args.order)
     t1 = time.time()
     ia, ja = Xh.graph() if want_graph else (None, None)
@@ -72,6 +74,13 @@ def workload(args, want_graph=True):
 
 
 def config_dict(args, mesh, Xh, nnz):
+    if args.mesh:
+        return {"workload": "P%d scalar Laplacian form2 gradt(u)*trans(grad(v)) on the mesh file %s (not a BASELINE config)"
+                            % (args.order, os.path.basename(args.mesh)),
+                "elements": int(mesh.numElements()), "points": int(mesh.numPoints()), "dofs": int(Xh.nDof()),
+                "nnz": int(nnz), "quadrature": "IMTetrahedra<%d>" % max(1, 2 * (args.order - 1)),
+                "vertices": "file", "element_order": "file",
+                "l2_policy": "inputs larger than L2 only if the mesh is (CSR values %.0f MB)" % (8e-6 * nnz)}
     return {"workload": "configs[1]: P%d scalar Laplacian form2 gradt(u)*trans(grad(v)), unit cube m=%d" % (args.order, args.m),
             "elements": int(mesh.numElements()), "points": int(mesh.numPoints()), "dofs": int(Xh.nDof()),
             "nnz": int(nnz), "quadrature": "IMTetrahedra<%d>" % max(1, 2 * (args.order - 1)),
@@ -95,6 +104,8 @@ def reference_arm(args):
     if rank != 0:
         return
     # the same global mesh as the GPU arm at this N (weak scaling: m grows with N^(1/3)); a step is a bounded sample of it
+    if args.mesh and args.gpus > 1:
+        raise SystemExit("--mesh runs on one GPU (the multi-GPU line is the weak-scaling cube)")
     args.m = int(round(args.m * max(args.gpus, 1) ** (1.0 / 3.0)))
     mesh, Xh, ia, ja, info = workload(args)
     cores = physical_cores()
@@ -110,7 +121,7 @@ def reference_arm(args):
     value = n / t
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "mesh file" if args.mesh else "synthetic",
             "config": config_dict(args, mesh, Xh, ia[-1]),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": "first %d elements of the mesh per step, %d threads, contiguous element blocks "
@@ -172,6 +183,8 @@ def gpu_arm(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    if world > 1 and args.mesh:
+        raise SystemExit("--mesh runs on one GPU (the multi-GPU line is the weak-scaling cube)")
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -333,7 +346,7 @@ def gpu_arm(args):
         traffic = None     # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same config only)
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "r1_eplan_traffic.json")))
-            if world == 1 and args.m == 110 and args.order == 2 and args.algo in ("auto", "eplan") and not args.shuffle:
+            if world == 1 and args.m == 110 and args.order == 2 and args.algo in ("auto", "eplan") and not args.shuffle and not args.mesh:
                 traffic = tr["dram_bytes_per_launch"]
         except Exception:
             pass
@@ -360,7 +373,7 @@ def gpu_arm(args):
         cfg["setup"] = info
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "mesh file" if args.mesh else "synthetic", "config": cfg,
                 "nnz_per_s": nnz_total * args.steps / (ms * 1e-3), "roofline": roof, "cpu_baseline": cpu,
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
         print(json.dumps(line))

@@ -37,3 +37,17 @@ def test_reference_arm_under_torchrun_env_prints_on_rank_0_only():
     d = json.loads(lines[0])
     # the global mesh of the GPU arm at N=2: m grows with N^(1/3)
     assert d["n_gpus"] == 2 and d["config"]["elements"] == 6 * round(6 * 2 ** (1 / 3)) ** 3
+
+
+def test_reference_arm_on_a_mesh_file(tmp_path):
+    """--mesh x.msh: the bench takes a Gmsh file instead of the synthetic cube and reports it as its own workload"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_gmsh as G
+    mesh, tri, marker, ids, perm = G.cube_with_sides(4)
+    path = str(tmp_path / "cube4.msh")
+    G.write_v2(path, mesh, tri, marker, ids, perm, True)
+    lines = run("--mesh", path)
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["data"] == "mesh file" and d["config"]["elements"] == 6 * 4 ** 3 and "cube4.msh" in d["config"]["workload"]
+    assert "configs[1]" not in d["config"]["workload"] and d["value"] > 0
