@@ -43,7 +43,7 @@ int feelhost_unit_cube(int m, double jitter, int shuffle, double* xyz, int32_t* 
 // ---- Gmsh .msh reader (feelfilters/importergmsh.hpp:983-1420) ----
 struct feelhost_gmsh_s { GmshMesh m; };
 int feelhost_gmsh_open(const char* path, int elementaryAsPhysical, feelhost_gmsh_s** out, int64_t* nPts, int64_t* nElt,
-                       int64_t* nTri, int64_t* namesLen, double* version, int* binary)
+                       int64_t* nTri, int64_t* namesLen, double* version, int* binary, int* numPartitions)
 {
     GUARD({
         auto* h = new feelhost_gmsh_s;
@@ -56,10 +56,11 @@ int feelhost_gmsh_open(const char* path, int elementaryAsPhysical, feelhost_gmsh
         *namesLen = (int64_t)h->m.physicalNames.size();
         *version = h->m.version;
         *binary = h->m.binary ? 1 : 0;
+        *numPartitions = h->m.numPartitions;
     })
 }
 int feelhost_gmsh_get(feelhost_gmsh_s* h, double* xyz, int64_t* pointId, int32_t* conn, int32_t* eltMarker, int32_t* tri,
-                      int32_t* triMarker, char* names)
+                      int32_t* triMarker, char* names, int32_t* eltPartition)
 {
     GUARD({
         GmshMesh const& m = h->m;
@@ -67,6 +68,7 @@ int feelhost_gmsh_get(feelhost_gmsh_s* h, double* xyz, int64_t* pointId, int32_t
         std::memcpy(pointId, m.pointId.data(), sizeof(int64_t) * m.pointId.size());
         std::memcpy(conn, m.conn.data(), sizeof(int32_t) * m.conn.size());
         std::memcpy(eltMarker, m.eltMarker.data(), sizeof(int32_t) * m.eltMarker.size());
+        std::memcpy(eltPartition, m.eltPartition.data(), sizeof(int32_t) * m.eltPartition.size());
         if (!m.tri.empty()) std::memcpy(tri, m.tri.data(), sizeof(int32_t) * m.tri.size());
         if (!m.triMarker.empty()) std::memcpy(triMarker, m.triMarker.data(), sizeof(int32_t) * m.triMarker.size());
         if (!m.physicalNames.empty()) std::memcpy(names, m.physicalNames.data(), m.physicalNames.size());

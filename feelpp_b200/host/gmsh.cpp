@@ -95,14 +95,14 @@ template <class T> T rd(Cursor& is, bool swap)
 
 struct Raw {
     std::vector<std::pair<int64_t, std::array<double, 3>>> nodes;
-    struct Elt { int type; int physical; int elementary; int64_t v[4]; };
+    struct Elt { int type; int physical; int elementary; int partition; int64_t v[4]; };
     std::vector<Elt> elts;
 };
 
-void keep(Raw& R, int type, int physical, int elementary, const int64_t* idx)
+void keep(Raw& R, int type, int physical, int elementary, int partition, const int64_t* idx)
 {
     if (type == 4 || type == 2) {
-        Raw::Elt e{type, physical, elementary, {0, 0, 0, 0}};
+        Raw::Elt e{type, physical, elementary, partition, {0, 0, 0, 0}};
         for (int j = 0; j < nodesOfType(type); ++j) e.v[j] = idx[j];
         R.elts.push_back(e);
     } else if (type == 1 || type == 15) {
@@ -140,19 +140,20 @@ void readV2(Cursor& is, bool binary, bool swap, Raw& R)
             int64_t num;
             int type, ntags;
             if (!(is >> num >> type >> ntags)) fail("bad element line");
-            int physical = 0, elementary = 0;
+            int physical = 0, elementary = 0, partition = 0;
             for (int j = 0; j < ntags; ++j) {
                 int tag;
                 is >> tag;
                 if (j == 0) physical = tag;
                 else if (j == 1) elementary = tag;
+                else if (j == 3 && ntags > 3) partition = tag - 1;     // tag 2 = number of partitions, then the owner, then -ghosts
             }
             const int nv = nodesOfType(type);
             if (!nv) fail("unknown number of vertices for element type " + std::to_string(type));
             int64_t idx[27];
             for (int j = 0; j < nv; ++j) is >> idx[j];
             if (!is) fail("bad element line");
-            keep(R, type, physical, elementary, idx);
+            keep(R, type, physical, elementary, partition, idx);
         }
     } else {
         int64_t done = 0;
@@ -162,15 +163,16 @@ void readV2(Cursor& is, bool binary, bool swap, Raw& R)
             if (!nv) fail("unknown number of vertices for element type " + std::to_string(type));
             for (int i = 0; i < cnt; ++i) {
                 rd<int32_t>(is, swap);   // element number
-                int physical = 0, elementary = 0;
+                int physical = 0, elementary = 0, partition = 0;
                 for (int j = 0; j < ntags; ++j) {
                     const int tag = rd<int32_t>(is, swap);
                     if (j == 0) physical = tag;
                     else if (j == 1) elementary = tag;
+                    else if (j == 3 && ntags > 3) partition = tag - 1;
                 }
                 int64_t idx[27];
                 for (int j = 0; j < nv; ++j) idx[j] = rd<int32_t>(is, swap);
-                keep(R, type, physical, elementary, idx);
+                keep(R, type, physical, elementary, partition, idx);
             }
             done += cnt;
         }
@@ -245,7 +247,7 @@ void readV4(Cursor& is, Raw& R)
                     is >> num;
                     for (int j = 0; j < nv; ++j) is >> idx[j];
                     if (!is) fail("bad element line");
-                    keep(R, type, physical, tag, idx);
+                    keep(R, type, physical, tag, 0, idx);
                 }
             }
             expect(is, "$EndElements");
@@ -356,6 +358,9 @@ GmshMesh readGmsh(std::string const& path, bool elementaryAsPhysical)
         if (e.type == 4) {
             M.conn.insert(M.conn.end(), v, v + 4);
             M.eltMarker.push_back(marker);
+            if (e.partition < 0) fail("negative partition tag");
+            M.eltPartition.push_back(e.partition);
+            M.numPartitions = std::max(M.numPartitions, e.partition + 1);
         } else {
             M.tri.insert(M.tri.end(), v, v + 3);
             M.triMarker.push_back(marker);

@@ -20,6 +20,9 @@ struct GmshMesh {
     std::vector<int64_t> pointId;      // [nPts] node numbers of the file, ascending
     std::vector<int32_t> conn;         // [nElt][4] compact point indices, file order
     std::vector<int32_t> eltMarker;    // [nElt]
+    std::vector<int32_t> eltPartition; // [nElt] 0-based partition tag of the file (MSH 2.x: tags numPartitions, partition, -ghosts;
+                                       // importergmsh.hpp:1239-1242, 1337-1340), 0 when the file is not partitioned
+    int32_t numPartitions = 1;         // 1 + the largest partition tag met
     std::vector<int32_t> tri;          // [nTri][3] compact point indices (marked faces), file order
     std::vector<int32_t> triMarker;    // [nTri]
     std::string physicalNames;         // "dim tag name\n" per entry

@@ -105,28 +105,33 @@ def markedfaces(mesh, markers):
 def loadMesh(path, elementaryAsPhysical=False):
     """loadMesh(_mesh=new Mesh<Simplex<3>>, _filename="x.msh") (feelfilters/loadmesh.hpp -> ImporterGmsh::readFromFile,
     feelfilters/importergmsh.hpp:983-1420): MSH 2.x ASCII / binary and MSH 4.1 ASCII, tetrahedra + marked triangles.
-    Point indices follow the ascending node numbers of the file (mesh.pointId holds them)."""
+    Point indices follow the ascending node numbers of the file (mesh.pointId holds them).  A partitioned MSH 2.2 file
+    (tags numPartitions, partition, -ghosts) gives mesh.eltPartition, the `part` input of parallel.LocalProblem: the
+    reference keeps the elements of its own partition the same way (importergmsh.hpp:1272-1281)."""
     h = capi.host()
     hd = C.c_void_p()
     npts, nelt, ntri, nlen = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
-    version, binary = C.c_double(), C.c_int()
+    version, binary, nparts = C.c_double(), C.c_int(), C.c_int()
     hcheck(h.feelhost_gmsh_open(str(path).encode(), int(bool(elementaryAsPhysical)), C.byref(hd), C.byref(npts),
-                                C.byref(nelt), C.byref(ntri), C.byref(nlen), C.byref(version), C.byref(binary)))
+                                C.byref(nelt), C.byref(ntri), C.byref(nlen), C.byref(version), C.byref(binary),
+                                C.byref(nparts)))
     try:
         xyz = np.empty((npts.value, 3), dtype=np.float64)
         pid = np.empty(npts.value, dtype=np.int64)
         conn = np.empty((nelt.value, 4), dtype=np.int32)
         em = np.empty(nelt.value, dtype=np.int32)
+        ep = np.empty(nelt.value, dtype=np.int32)
         tri = np.empty((ntri.value, 3), dtype=np.int32)
         tm = np.empty(ntri.value, dtype=np.int32)
         names = C.create_string_buffer(max(nlen.value, 1))
         hcheck(h.feelhost_gmsh_get(hd, ptr(xyz, c_dblp), ptr(pid, c_i64p), ptr(conn, c_i32p), ptr(em, c_i32p),
-                                   ptr(tri, c_i32p), ptr(tm, c_i32p), names))
+                                   ptr(tri, c_i32p), ptr(tm, c_i32p), names, ptr(ep, c_i32p)))
     finally:
         h.feelhost_gmsh_free(hd)
     mesh = Mesh(xyz, conn)
     mesh.pointId, mesh.eltMarker, mesh.tri, mesh.triMarker = pid, em, tri, tm
     mesh.version, mesh.binary = version.value, bool(binary.value)
+    mesh.eltPartition, mesh.numPartitions = ep, nparts.value     # partition tags of the file (0-based), input of LocalProblem
     mesh.markerNames = {}
     for line in names.raw[:nlen.value].decode().splitlines():
         dim, tag, name = line.split(" ", 2)

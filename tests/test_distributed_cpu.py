@@ -12,7 +12,7 @@ import torch.multiprocessing as mp
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, order, ncomp, kind, out):
+def _worker(rank, world, port, order, ncomp, kind, out, msh=None):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
     import scipy.sparse as sps
@@ -20,9 +20,15 @@ def _worker(rank, world, port, order, ncomp, kind, out):
     from feelpp_b200 import parallel as par
     from oracle import oracle as orc
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
-    mesh = fpp.unitCube(4, 0.15, True)
-    part = par.partition_rcb(mesh, world)
+    if msh is None:
+        mesh = fpp.unitCube(4, 0.15, True)
+        part = par.partition_rcb(mesh, world)
+    else:       # a partitioned .msh file: every rank reads it and keeps the elements tagged with its own partition
+        mesh = fpp.loadMesh(msh)
+        part = mesh.eltPartition
+        assert mesh.numPartitions == world
     lp = par.LocalProblem(mesh, part, order, ncomp, par.Comm(rank, world, dist))
+    assert lp.mesh.numElements() == int((part == rank).sum())
     quad = orc.quad_order_form2(kind, order)
     co = orc.Coeff(lam=2.0, mu=1.5)
     # local assembly with process-local rows and cluster columns: columns of local elements are local dofs, so assemble
@@ -50,14 +56,14 @@ def _worker(rank, world, port, order, ncomp, kind, out):
 
 
 @pytest.mark.parametrize("world,order,ncomp,kind", [(2, 1, 1, 1), (2, 2, 1, 1), (3, 2, 1, 0), (2, 2, 3, 2)])
-def test_distributed_assembly_matches_sequential(world, order, ncomp, kind):
+def test_distributed_assembly_matches_sequential(world, order, ncomp, kind, msh=None):
     import scipy.sparse as sps
     import feelpp_b200 as fpp
     from oracle import oracle as orc
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = 29500 + (os.getpid() + 7 * world + order) % 2000
-    procs = [ctx.Process(target=_worker, args=(r, world, port, order, ncomp, kind, out)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, order, ncomp, kind, out, msh)) for r in range(world)]
     for p in procs:
         p.start()
     gathered = out.get(timeout=240)
@@ -86,3 +92,18 @@ def test_distributed_assembly_matches_sequential(world, order, ncomp, kind):
     assert abs(sps.linalg.norm(D) - sps.linalg.norm(R)) < 1e-12 * sps.linalg.norm(R)
     x = np.ones(N)
     assert abs(x @ D @ x - x @ R @ x) < 1e-10 * max(1.0, abs(R).sum())
+
+
+def test_distributed_assembly_from_a_partitioned_msh_file(tmp_path):
+    """the partition is an input (Feel++ reads it from the tags of the .msh file, importergmsh.hpp:1239-1242,1272-1281):
+    two unequal parts written into the file, both ranks load it, the gathered matrix is the sequential one"""
+    import feelpp_b200 as fpp
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_gmsh as G
+    mesh = fpp.unitCube(4, 0.15, True)
+    part = (mesh.xyz[mesh.conn].mean(1)[:, 0] > 0.4).astype(np.int32)
+    ids = np.arange(mesh.numPoints()) * 2 + 1
+    path = str(tmp_path / "cube_part.msh")
+    G.write_v2(path, mesh, np.zeros((0, 3), dtype=np.int32), np.zeros(0, dtype=np.int32), ids,
+               np.random.default_rng(1).permutation(mesh.numPoints()), True, part)
+    test_distributed_assembly_matches_sequential(2, 2, 1, 1, msh=path)

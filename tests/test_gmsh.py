@@ -30,7 +30,7 @@ def cube_with_sides(m=3):
     return mesh, tri, marker, ids, rng.permutation(mesh.numPoints())
 
 
-def write_v2(path, mesh, tri, marker, ids, perm, binary):
+def write_v2(path, mesh, tri, marker, ids, perm, binary, part=None):
     with open(path, "wb") as fh:
         fh.write(b"$MeshFormat\n2.2 %d 8\n" % (1 if binary else 0))
         if binary:
@@ -55,9 +55,10 @@ def write_v2(path, mesh, tri, marker, ids, perm, binary):
             for t, mk in zip(tri, marker):
                 fh.write(struct.pack("6i", num, int(mk), int(mk) + 100, *[int(ids[v]) for v in t]))
                 num += 1
-            fh.write(struct.pack("3i", 4, mesh.numElements(), 2))
-            for t in mesh.conn:
-                fh.write(struct.pack("7i", num, 7, 1, *[int(ids[v]) for v in t]))
+            fh.write(struct.pack("3i", 4, mesh.numElements(), 2 if part is None else 4))
+            for k, t in enumerate(mesh.conn):
+                tags = [7, 1] if part is None else [7, 1, 1, int(part[k]) + 1]
+                fh.write(struct.pack("%di" % (5 + len(tags)), num, *tags, *[int(ids[v]) for v in t]))
                 num += 1
             fh.write(b"\n")
         else:
@@ -66,8 +67,11 @@ def write_v2(path, mesh, tri, marker, ids, perm, binary):
             for t, mk in zip(tri, marker):
                 fh.write(b"%d 2 2 %d %d %d %d %d\n" % (num, mk, mk + 100, *ids[t]))
                 num += 1
-            for t in mesh.conn:
-                fh.write(b"%d 4 2 7 1 %d %d %d %d\n" % (num, *ids[t]))
+            for k, t in enumerate(mesh.conn):
+                if part is None:
+                    fh.write(b"%d 4 2 7 1 %d %d %d %d\n" % (num, *ids[t]))
+                else:      # physical, elementary, number of partitions, owner (1-based), one ghost partition (negative)
+                    fh.write(b"%d 4 5 7 1 2 %d %d %d %d %d %d\n" % (num, part[k] + 1, -(2 - part[k]), *ids[t]))
                 num += 1
         fh.write(b"$EndElements\n")
 
@@ -160,6 +164,19 @@ def test_reader_returns_the_mesh_dofs_and_sides(tmp_path, cube, enc):
     assert np.abs(b[~on_side]).max() == 0
     # on(markedfaces): the Dirichlet dofs are the nodes of that side only
     assert np.array_equal(np.sort(Xh.boundaryDofs((e, f))), np.nonzero(on_side)[0])
+
+
+@pytest.mark.parametrize("binary", [False, True])
+def test_partition_tags_of_the_file(tmp_path, cube, binary):
+    mesh, tri, marker, ids, perm = cube
+    part = (mesh.xyz[mesh.conn].mean(1)[:, 0] > 0.4).astype(np.int32)     # two unequal parts, not the bisection
+    path = str(tmp_path / "cube.msh")
+    write_v2(path, mesh, tri, marker, ids, perm, binary, part)
+    got = fpp.loadMesh(path)
+    assert got.numPartitions == 2 and np.array_equal(got.eltPartition, part) and np.array_equal(got.conn, mesh.conn)
+    write_v2(path, mesh, tri, marker, ids, perm, binary)
+    got = fpp.loadMesh(path)
+    assert got.numPartitions == 1 and not got.eltPartition.any()
 
 
 def test_elementary_tag_as_marker(tmp_path, cube):
