@@ -296,3 +296,48 @@ def test_load_vector_and_field_weighted_stiffness_match_exact_integration(order)
     co = orc.Coeff(kind=orc.COEFF_FIELD, field_order=1, field_l2g=conn, field_values=kv)
     K = orc.local_matrix(orc.STIFFNESS, order, 1, orc.quad_order_form2(orc.STIFFNESS, order, 1), G, co).reshape(n, n)
     assert np.abs(K - K_exact).max() < 1e-12 * np.abs(K_exact).max()
+
+
+@pytest.mark.parametrize("order", [2, 3])
+def test_polynomial_coefficient_stiffness_matches_exact_integration(order):
+    """config 3's form: k*inner(gradt(u),grad(v)) with k = 1+x*y+z^2 given as expr("...") (degree 2 -> quadrature order
+    2(k-1)+2, Q = 24 for P3).  k is rewritten in barycentric coordinates (x = sum_m lambda_m X_m) and the integral taken
+    exactly."""
+    from itertools import product
+    from math import factorial
+    pts = orc.lagrange_points(order)
+    n = len(pts)
+    lam4 = np.empty((n, 4))
+    lam4[:, 1:] = (pts + 1) / 2
+    lam4[:, 0] = 1 - lam4[:, 1:].sum(1)
+    alphas = [a for a in product(range(order + 1), repeat=4) if sum(a) == order]
+    Cf = np.linalg.inv(np.array([[np.prod(lam4[i] ** np.array(a)) for a in alphas] for i in range(n)]))
+    rng = np.random.default_rng(40 + order)
+    G = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1.0]]) + 0.2 * rng.standard_normal((4, 3))
+    T = np.hstack([np.ones((4, 1)), G])
+    vol = abs(np.linalg.det(T)) / 6
+    gg = np.linalg.inv(T)[1:, :].T
+    gg = gg @ gg.T
+
+    def integral(a):
+        return 0.0 if min(a) < 0 else 6 * vol * np.prod([factorial(x) for x in a]) / factorial(sum(a) + 3)
+
+    kterms = [((0, 0, 0, 0), 1.0)]                                  # k = 1 + x*y + z^2 as a polynomial in lambda
+    for m in range(4):
+        for l in range(4):
+            e = [0, 0, 0, 0]; e[m] += 1; e[l] += 1
+            kterms.append((tuple(e), G[m, 0] * G[l, 1] + G[m, 2] * G[l, 2]))
+    Ka = np.zeros((n, n))
+    for ia_, a in enumerate(alphas):
+        for ib, b in enumerate(alphas):
+            for m in range(4):
+                for l in range(4):
+                    if a[m] and b[l]:
+                        e = np.add(a, b); e[m] -= 1; e[l] -= 1
+                        Ka[ia_, ib] += a[m] * b[l] * gg[m, l] * sum(c * integral(tuple(e + np.array(kb))) for kb, c in kterms)
+    K_exact = Cf.T @ Ka @ Cf
+    g = fpp.expr("1+x*y+z^2")
+    assert orc.quad_order_form2(orc.STIFFNESS, order, 2) == 2 * (order - 1) + 2
+    co = orc.Coeff(kind=orc.COEFF_EXPR, ops=g.prog.ops, consts=g.prog.consts)
+    K = orc.local_matrix(orc.STIFFNESS, order, 1, orc.quad_order_form2(orc.STIFFNESS, order, 2), G, co).reshape(n, n)
+    assert np.abs(K - K_exact).max() < 1e-12 * np.abs(K_exact).max()
