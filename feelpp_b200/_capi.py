@@ -138,6 +138,7 @@ def host():
         lib.feelhost_last_error.restype = C.c_char_p
         lib.feelhost_unit_cube_sizes.argtypes = [C.c_int, c_i64p, c_i64p]
         lib.feelhost_unit_cube.argtypes = [C.c_int, C.c_double, C.c_int, c_dblp, c_i32p]
+        lib.feelhost_boundary_faces.argtypes = [C.c_int64, C.c_int64, c_i32p, c_i32p, c_i32p, c_i64p]
         lib.feelhost_gmsh_open.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_void_p), c_i64p, c_i64p, c_i64p, c_i64p,
                                            c_dblp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         lib.feelhost_gmsh_get.argtypes = [C.c_void_p, c_dblp, c_i64p, c_i32p, c_i32p, c_i32p, c_i32p, C.c_char_p,

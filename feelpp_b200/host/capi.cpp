@@ -40,6 +40,21 @@ int feelhost_unit_cube(int m, double jitter, int shuffle, double* xyz, int32_t* 
     })
 }
 
+// boundaryfaces(mesh): elt/face have room for 4*nElt entries, *n receives the count
+int feelhost_boundary_faces(int64_t nPts, int64_t nElt, const int32_t* conn, int32_t* elt, int32_t* face, int64_t* n)
+{
+    GUARD({
+        std::vector<int32_t> e;
+        std::vector<int32_t> f;
+        boundaryFaces(nPts, nElt, conn, e, f);
+        *n = (int64_t)e.size();
+        if (!e.empty()) {
+            std::memcpy(elt, e.data(), sizeof(int32_t) * e.size());
+            std::memcpy(face, f.data(), sizeof(int32_t) * f.size());
+        }
+    })
+}
+
 // ---- Gmsh .msh reader (feelfilters/importergmsh.hpp:983-1420) ----
 struct feelhost_gmsh_s { GmshMesh m; };
 int feelhost_gmsh_open(const char* path, int elementaryAsPhysical, feelhost_gmsh_s** out, int64_t* nPts, int64_t* nElt,

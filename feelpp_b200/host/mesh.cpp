@@ -69,4 +69,40 @@ mesh_ptrtype unitCube(int m, double jitter, bool shuffle)
     return mesh;
 }
 
+void boundaryFaces(int64_t nPts, int64_t nElt, const int32_t* conn, std::vector<int32_t>& elt, std::vector<int32_t>& face)
+{
+    static const int F2P[4][3] = {{1, 2, 3}, {0, 2, 3}, {0, 1, 3}, {0, 1, 2}};
+    struct Key { int32_t a, b, c; int64_t ef; };
+    std::vector<Key> keys((size_t)nElt * 4);
+    for (int64_t e = 0; e < nElt; ++e)
+        for (int f = 0; f < 4; ++f) {
+            int32_t v[3] = {conn[4 * e + F2P[f][0]], conn[4 * e + F2P[f][1]], conn[4 * e + F2P[f][2]]};
+            for (int k = 0; k < 3; ++k)
+                if (v[k] < 0 || v[k] >= nPts) throw std::invalid_argument("boundaryFaces: point id out of range");
+            if (v[0] > v[1]) std::swap(v[0], v[1]);
+            if (v[1] > v[2]) std::swap(v[1], v[2]);
+            if (v[0] > v[1]) std::swap(v[0], v[1]);
+            keys[(size_t)e * 4 + f] = Key{v[0], v[1], v[2], e * 4 + f};
+        }
+    std::sort(keys.begin(), keys.end(), [](Key const& x, Key const& y) {
+        if (x.a != y.a) return x.a < y.a;
+        if (x.b != y.b) return x.b < y.b;
+        return x.c < y.c;
+    });
+    std::vector<uint8_t> single((size_t)nElt * 4, 0);
+    for (size_t i = 0; i < keys.size();) {
+        size_t j = i + 1;
+        while (j < keys.size() && keys[j].a == keys[i].a && keys[j].b == keys[i].b && keys[j].c == keys[i].c) ++j;
+        if (j == i + 1) single[(size_t)keys[i].ef] = 1;
+        i = j;
+    }
+    elt.clear();
+    face.clear();
+    for (size_t k = 0; k < single.size(); ++k)
+        if (single[k]) {
+            elt.push_back((int32_t)(k / 4));
+            face.push_back((int32_t)(k % 4));
+        }
+}
+
 } // namespace feelpp_b200

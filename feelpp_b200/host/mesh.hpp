@@ -26,6 +26,10 @@ using mesh_ptrtype = std::shared_ptr<Mesh>;
 // Point ids are the lexicographic grid index; all elements are positively oriented.
 mesh_ptrtype unitCube(int m, double jitter = 0.0, bool shuffle = false);
 
+// boundaryfaces(mesh) (feelmesh/filters.hpp): the faces that belong to exactly one element, as (element, local face) pairs
+// in element order; local face f is opposite to local vertex f (feelmesh/simplexordering.hpp:341-347).
+void boundaryFaces(int64_t nPts, int64_t nElt, const int32_t* conn, std::vector<int32_t>& elt, std::vector<int32_t>& face);
+
 // element range: elements(mesh) (feelmesh/filters.hpp:201) -- the only range kind on this path
 struct ElementRange {
     mesh_ptrtype mesh;

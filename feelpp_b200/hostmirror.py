@@ -57,14 +57,13 @@ class BoundaryFaceRange:
 
     def faces(self):
         if self._faces is None:
-            conn = self.mesh.conn.astype(np.int64)
-            npts = self.mesh.numPoints()
-            F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])    # feelmesh/simplexordering.hpp:341-347
-            fv = np.sort(conn[:, F2P], axis=2)
-            key = (fv[..., 0] * npts + fv[..., 1]) * npts + fv[..., 2]
-            _, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
-            e, f = np.nonzero((cnt[inv] == 1).reshape(key.shape))
-            self._faces = (np.ascontiguousarray(e, dtype=np.int32), np.ascontiguousarray(f, dtype=np.int32))
+            mesh = self.mesh
+            e = np.empty(4 * mesh.numElements(), dtype=np.int32)
+            f = np.empty(4 * mesh.numElements(), dtype=np.int32)
+            n = C.c_int64()
+            hcheck(capi.host().feelhost_boundary_faces(mesh.numPoints(), mesh.numElements(), ptr(mesh.conn, c_i32p),
+                                                       ptr(e, c_i32p), ptr(f, c_i32p), C.byref(n)))
+            self._faces = (e[:n.value].copy(), f[:n.value].copy())
         return self._faces
 
 
@@ -211,18 +210,12 @@ class FunctionSpace:
         """scalar node ids carried by the boundary faces (faces of exactly one element): what
         on(_range=boundaryfaces(mesh), ...) visits through the face dof table (feelvf/on.hpp:395-449).  With
         faces = (element, local face) arrays -- markedfaces(mesh, marker).faces() -- only those faces are visited."""
-        conn = self.mesh.conn.astype(np.int64)
-        npts = self.mesh.numPoints()
         F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])        # feelmesh/simplexordering.hpp:341-347
         E2P = np.array([[1, 2], [2, 0], [0, 1], [0, 3], [1, 3], [2, 3]])    # :283-291
         if faces is None:
-            fv = np.sort(conn[:, F2P], axis=2)                                    # [nElt][4][3]
-            key = (fv[..., 0] * npts + fv[..., 1]) * npts + fv[..., 2]
-            _, inv, cnt = np.unique(key.ravel(), return_inverse=True, return_counts=True)
-            onb = (cnt[inv] == 1).reshape(key.shape)                             # [nElt][4] boundary faces
-        else:
-            onb = np.zeros((conn.shape[0], 4), dtype=bool)
-            onb[faces[0], faces[1]] = True
+            faces = BoundaryFaceRange(self.mesh).faces()
+        onb = np.zeros((self.mesh.numElements(), 4), dtype=bool)             # [nElt][4] the faces visited
+        onb[faces[0], faces[1]] = True
         nodes = self.l2g[:, :self.n] // self.ncomp
         out = []
         npe = self.order - 1
