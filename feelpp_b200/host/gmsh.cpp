@@ -181,6 +181,86 @@ void readV2(Cursor& is, bool binary, bool swap, Raw& R)
     expect(is, "$EndElements");
 }
 
+// MSH 4.1 binary: the same sections, counts as size_t (8 bytes), tags as int, node / element tags as size_t
+void readV4Binary(Cursor& is, bool swap, Raw& R)
+{
+    std::map<std::pair<int, int>, int> phys;
+    std::string buf;
+    auto sz = [&]() { return (int64_t)rd<uint64_t>(is, swap); };
+    while (!is.atEnd() && is.word(buf)) {
+        if (buf == "$Entities") {
+            is.get();
+            int64_t cnt[4];
+            for (int d = 0; d < 4; ++d) cnt[d] = sz();
+            for (int dim = 0; dim < 4; ++dim)
+                for (int64_t k = 0; k < cnt[dim]; ++k) {
+                    const int tag = rd<int32_t>(is, swap);
+                    for (int c = 0; c < (dim == 0 ? 3 : 6); ++c) rd<double>(is, swap);
+                    const int64_t np = sz();
+                    for (int64_t j = 0; j < np; ++j) {
+                        const int p = rd<int32_t>(is, swap);
+                        if (j == 0) phys[{dim, tag}] = p;
+                    }
+                    if (dim > 0) {
+                        const int64_t nb = sz();
+                        for (int64_t j = 0; j < nb; ++j) rd<int32_t>(is, swap);
+                    }
+                }
+            expect(is, "$EndEntities");
+        } else if (buf == "$Nodes") {
+            is.get();
+            const int64_t nblk = sz(), n = sz();
+            sz();
+            sz();
+            R.nodes.reserve((size_t)n);
+            for (int64_t b = 0; b < nblk; ++b) {
+                const int dim = rd<int32_t>(is, swap);
+                rd<int32_t>(is, swap);
+                const int parametric = rd<int32_t>(is, swap);
+                const int64_t nb = sz();
+                const size_t first = R.nodes.size();
+                R.nodes.resize(first + (size_t)nb);
+                for (int64_t i = 0; i < nb; ++i) R.nodes[first + (size_t)i].first = sz();
+                for (int64_t i = 0; i < nb; ++i) {
+                    auto& x = R.nodes[first + (size_t)i].second;
+                    for (int c = 0; c < 3; ++c) x[c] = rd<double>(is, swap);
+                    for (int c = 0; parametric && c < dim; ++c) rd<double>(is, swap);
+                }
+            }
+            if ((int64_t)R.nodes.size() != n) fail("bad $Nodes section");
+            expect(is, "$EndNodes");
+        } else if (buf == "$Elements") {
+            is.get();
+            const int64_t nblk = sz();
+            sz();
+            sz();
+            sz();
+            for (int64_t b = 0; b < nblk; ++b) {
+                const int dim = rd<int32_t>(is, swap), tag = rd<int32_t>(is, swap), type = rd<int32_t>(is, swap);
+                const int64_t nb = sz();
+                const int nv = nodesOfType(type);
+                if (!nv) fail("unknown number of vertices for element type " + std::to_string(type));
+                auto it = phys.find({dim, tag});
+                const int physical = it == phys.end() ? 0 : it->second;
+                for (int64_t i = 0; i < nb; ++i) {
+                    int64_t idx[27];
+                    sz();
+                    for (int j = 0; j < nv; ++j) idx[j] = sz();
+                    keep(R, type, physical, tag, 0, idx);
+                }
+            }
+            expect(is, "$EndElements");
+            return;
+        } else if (buf[0] == '$') {   // a section the path does not use: find its end marker in the bytes
+            const std::string end = "\n$End" + buf.substr(1);
+            const auto at = std::search(is.buf.begin() + (long)is.pos, is.buf.end(), end.begin(), end.end());
+            if (at == is.buf.end()) fail("section " + buf + " has no end");
+            is.pos = (size_t)(at - is.buf.begin()) + end.size();
+        }
+    }
+    fail("no $Elements section");
+}
+
 void readV4(Cursor& is, Raw& R)
 {
     // entity (dim, tag) -> first physical tag
@@ -285,7 +365,6 @@ GmshMesh readGmsh(std::string const& path, bool elementaryAsPhysical)
     M.binary = format != 0;
     bool swap = false;
     if (M.binary) {
-        if (M.version >= 4) fail("binary MSH 4 is not supported (ASCII 4.1, ASCII / binary 2.x are)");
         is.get();
         int one = 0;
         is.read(reinterpret_cast<char*>(&one), sizeof(int));
@@ -332,7 +411,7 @@ GmshMesh readGmsh(std::string const& path, bool elementaryAsPhysical)
             expect(is, "$EndPhysicalNames");
         } else
             is.pos = at;
-        readV4(is, R);
+        if (M.binary) readV4Binary(is, swap, R); else readV4(is, R);
     }
     // compact the node numbers in ascending order (order-preserving: id comparisons are unchanged)
     std::sort(R.nodes.begin(), R.nodes.end(), [](auto const& a, auto const& b) { return a.first < b.first; });

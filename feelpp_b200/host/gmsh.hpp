@@ -1,7 +1,7 @@
 // gmsh.hpp -- reader of Gmsh .msh files (tetrahedra + marked boundary triangles), the data format on the caller side
 // of the assembly path.  Stands where ImporterGmsh<MeshType>::readFromFile stands (feelfilters/importergmsh.hpp:983-1103:
-// $MeshFormat / $PhysicalNames, then readFromFileVersion2 :1106-1420 or readFromFileVersion4): MSH 2.x ASCII and binary,
-// MSH 4.1 ASCII.  As in the reference the node numbers of the file are the point ids ("we do not renumber anymore",
+// $MeshFormat / $PhysicalNames, then readFromFileVersion2 :1106-1420 or readFromFileVersion4): MSH 2.x and MSH 4.1, ASCII and
+// binary.  As in the reference the node numbers of the file are the point ids ("we do not renumber anymore",
 // :1262-1266); here they are compacted to 0..nPts-1 in ascending id order, which keeps every id comparison the DofTable
 // makes (edge orientation, feelmesh/mesh3d.hpp:755-782).  The physical tag is the marker (elementary tag on request,
 // M_use_elementary_region_as_physical_region :1268-1271).  Lines, points and higher-order elements are refused or

@@ -103,7 +103,7 @@ def markedfaces(mesh, markers):
 
 def loadMesh(path, elementaryAsPhysical=False):
     """loadMesh(_mesh=new Mesh<Simplex<3>>, _filename="x.msh") (feelfilters/loadmesh.hpp -> ImporterGmsh::readFromFile,
-    feelfilters/importergmsh.hpp:983-1420): MSH 2.x ASCII / binary and MSH 4.1 ASCII, tetrahedra + marked triangles.
+    feelfilters/importergmsh.hpp:983-1420): MSH 2.x and MSH 4.1, ASCII or binary, tetrahedra + marked triangles.
     Point indices follow the ascending node numbers of the file (mesh.pointId holds them).  A partitioned MSH 2.2 file
     (tags numPartitions, partition, -ghosts) gives mesh.eltPartition, the `part` input of parallel.LocalProblem: the
     reference keeps the elements of its own partition the same way (importergmsh.hpp:1272-1281)."""

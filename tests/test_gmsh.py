@@ -1,5 +1,5 @@
 """loadMesh / markedfaces: the .msh reader on the caller side of the path (feelfilters/importergmsh.hpp:983-1420).
-The files are written here in the three encodings the reader takes (MSH 2.2 ASCII, MSH 2.2 binary, MSH 4.1 ASCII) from
+The files are written here in the four encodings the reader takes (MSH 2.2 and MSH 4.1, ASCII and binary) from
 the synthetic cube, with non-contiguous node numbers listed out of order; what comes back must be the same mesh, the
 same DofTable / graph (bit-exact against the oracle) and the marked sides of the cube."""
 import os
@@ -110,21 +110,58 @@ def write_v4(path, mesh, tri, marker, ids, perm):
         fh.write("$EndElements\n")
 
 
+def write_v4_binary(path, mesh, tri, marker, ids, perm):
+    Q, I = "=Q", "=i"
+    with open(path, "wb") as fh:
+        fh.write(b"$MeshFormat\n4.1 1 8\n" + struct.pack(I, 1) + b"\n$EndMeshFormat\n$PhysicalNames\n%d\n" % (len(SIDES) + 1))
+        for name, tag in SIDES.items():
+            fh.write(b'2 %d "%s"\n' % (tag, name.encode()))
+        fh.write(b'3 7 "Omega"\n$EndPhysicalNames\n$Entities\n')
+        fh.write(struct.pack("=4Q", 1, 0, 6, 1))
+        fh.write(struct.pack("=i3dQ", 900, 0.0, 0.0, 0.0, 0))                       # a point without physical tags
+        for sd in range(6):
+            fh.write(struct.pack("=i6dQiQ", 101 + sd, 0, 0, 0, 1, 1, 1, 1, 1 + sd, 0))
+        fh.write(struct.pack("=i6dQiQ6i", 1, 0, 0, 0, 1, 1, 1, 1, 7, 6, 101, 102, 103, 104, 105, 106))
+        fh.write(b"\n$EndEntities\n$Unused\n" + struct.pack("=3d", 1.0, 2.0, 3.0) + b"\n$EndUnused\n$Nodes\n")
+        half = len(perm) // 2
+        fh.write(struct.pack("=4Q", 2, len(perm), int(ids.min()), int(ids.max())))
+        for blk, (dim, tag) in zip((perm[:half], perm[half:]), ((2, 101), (3, 1))):
+            fh.write(struct.pack("=3iQ", dim, tag, 0, len(blk)))
+            fh.write(np.asarray(ids[blk], dtype="<u8").tobytes())
+            fh.write(np.ascontiguousarray(mesh.xyz[blk], dtype="<f8").tobytes())
+        ntot = len(tri) + mesh.numElements()
+        fh.write(b"\n$EndNodes\n$Elements\n" + struct.pack("=4Q", 7, ntot, 1, ntot))
+        num = 1
+        for sd in range(6):
+            sel = np.nonzero(marker == 1 + sd)[0]
+            fh.write(struct.pack("=3iQ", 2, 101 + sd, 2, len(sel)))
+            for k in sel:
+                fh.write(struct.pack("=4Q", num, *[int(x) for x in ids[tri[k]]]))
+                num += 1
+        fh.write(struct.pack("=3iQ", 3, 1, 4, mesh.numElements()))
+        for t in mesh.conn:
+            fh.write(struct.pack("=5Q", num, *[int(x) for x in ids[t]]))
+            num += 1
+        fh.write(b"\n$EndElements\n")
+
+
 @pytest.fixture(scope="module")
 def cube():
     return cube_with_sides(3)
 
 
-@pytest.mark.parametrize("enc", ["v2-ascii", "v2-binary", "v4-ascii"])
+@pytest.mark.parametrize("enc", ["v2-ascii", "v2-binary", "v4-ascii", "v4-binary"])
 def test_reader_returns_the_mesh_dofs_and_sides(tmp_path, cube, enc):
     mesh, tri, marker, ids, perm = cube
     path = str(tmp_path / "cube.msh")
     if enc == "v4-ascii":
         write_v4(path, mesh, tri, marker, ids, perm)
+    elif enc == "v4-binary":
+        write_v4_binary(path, mesh, tri, marker, ids, perm)
     else:
         write_v2(path, mesh, tri, marker, ids, perm, enc == "v2-binary")
     got = fpp.loadMesh(path)
-    assert got.binary == (enc == "v2-binary") and got.version == (4.1 if enc == "v4-ascii" else 2.2)
+    assert got.binary == enc.endswith("binary") and got.version == (4.1 if enc.startswith("v4") else 2.2)
     assert np.array_equal(got.pointId, ids)                     # ascending node numbers -> compact indices
     assert np.array_equal(got.xyz, mesh.xyz)                    # %.17g round-trips doubles
     assert np.array_equal(got.conn, mesh.conn) and (got.eltMarker == 7).all()
@@ -212,3 +249,17 @@ def test_reader_refuses_what_the_path_cannot_take(tmp_path):
     assert one.numElements() == 1 and one.numPoints() == 4 and len(one.tri) == 0
     with pytest.raises(KeyError):
         fpp.markedfaces(one, "nope").faces()
+
+
+@pytest.mark.parametrize("v4", [False, True])
+def test_truncated_binary_file_is_refused(tmp_path, cube, v4):
+    mesh, tri, marker, ids, perm = cube
+    path = str(tmp_path / "cube.msh")
+    if v4:
+        write_v4_binary(path, mesh, tri, marker, ids, perm)
+    else:
+        write_v2(path, mesh, tri, marker, ids, perm, True)
+    data = open(path, "rb").read()
+    open(path, "wb").write(data[:len(data) // 2])
+    with pytest.raises(RuntimeError, match="truncated|expected|bad"):
+        fpp.loadMesh(path)
