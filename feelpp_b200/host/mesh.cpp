@@ -72,29 +72,46 @@ mesh_ptrtype unitCube(int m, double jitter, bool shuffle)
 void boundaryFaces(int64_t nPts, int64_t nElt, const int32_t* conn, std::vector<int32_t>& elt, std::vector<int32_t>& face)
 {
     static const int F2P[4][3] = {{1, 2, 3}, {0, 2, 3}, {0, 1, 3}, {0, 1, 2}};
-    struct Key { int32_t a, b, c; int64_t ef; };
-    std::vector<Key> keys((size_t)nElt * 4);
+    // faces bucketed by their smallest point id (counting sort: one pass to count, one to place), then each small bucket
+    // (about a dozen faces) is sorted by the two other ids: linear in the number of elements
+    struct Rest { int32_t b, c; int64_t ef; };
+    std::vector<int64_t> first((size_t)nPts + 1, 0);
+    auto sorted3 = [&](int64_t e, int f, int32_t* v) {
+        for (int k = 0; k < 3; ++k) {
+            v[k] = conn[4 * e + F2P[f][k]];
+            if (v[k] < 0 || v[k] >= nPts) throw std::invalid_argument("boundaryFaces: point id out of range");
+        }
+        if (v[0] > v[1]) std::swap(v[0], v[1]);
+        if (v[1] > v[2]) std::swap(v[1], v[2]);
+        if (v[0] > v[1]) std::swap(v[0], v[1]);
+    };
+    int32_t v[3];
     for (int64_t e = 0; e < nElt; ++e)
         for (int f = 0; f < 4; ++f) {
-            int32_t v[3] = {conn[4 * e + F2P[f][0]], conn[4 * e + F2P[f][1]], conn[4 * e + F2P[f][2]]};
-            for (int k = 0; k < 3; ++k)
-                if (v[k] < 0 || v[k] >= nPts) throw std::invalid_argument("boundaryFaces: point id out of range");
-            if (v[0] > v[1]) std::swap(v[0], v[1]);
-            if (v[1] > v[2]) std::swap(v[1], v[2]);
-            if (v[0] > v[1]) std::swap(v[0], v[1]);
-            keys[(size_t)e * 4 + f] = Key{v[0], v[1], v[2], e * 4 + f};
+            sorted3(e, f, v);
+            ++first[(size_t)v[0] + 1];
         }
-    std::sort(keys.begin(), keys.end(), [](Key const& x, Key const& y) {
-        if (x.a != y.a) return x.a < y.a;
-        if (x.b != y.b) return x.b < y.b;
-        return x.c < y.c;
-    });
+    for (int64_t p = 0; p < nPts; ++p) first[(size_t)p + 1] += first[(size_t)p];
+    std::vector<Rest> rest((size_t)nElt * 4);
+    {
+        std::vector<int64_t> at(first.begin(), first.end() - 1);
+        for (int64_t e = 0; e < nElt; ++e)
+            for (int f = 0; f < 4; ++f) {
+                sorted3(e, f, v);
+                rest[(size_t)at[(size_t)v[0]]++] = Rest{v[1], v[2], e * 4 + f};
+            }
+    }
     std::vector<uint8_t> single((size_t)nElt * 4, 0);
-    for (size_t i = 0; i < keys.size();) {
-        size_t j = i + 1;
-        while (j < keys.size() && keys[j].a == keys[i].a && keys[j].b == keys[i].b && keys[j].c == keys[i].c) ++j;
-        if (j == i + 1) single[(size_t)keys[i].ef] = 1;
-        i = j;
+    for (int64_t p = 0; p < nPts; ++p) {
+        Rest* b = rest.data() + first[(size_t)p];
+        Rest* e = rest.data() + first[(size_t)p + 1];
+        std::sort(b, e, [](Rest const& x, Rest const& y) { return x.b != y.b ? x.b < y.b : x.c < y.c; });
+        for (Rest* i = b; i < e;) {
+            Rest* k = i + 1;
+            while (k < e && k->b == i->b && k->c == i->c) ++k;
+            if (k == i + 1) single[(size_t)i->ef] = 1;
+            i = k;
+        }
     }
     elt.clear();
     face.clear();
