@@ -1,15 +1,26 @@
 #!/usr/bin/env python3
-"""bench.py -- P2 tet Laplacian form2 assembly on B200 (BASELINE.json metric), one JSON line on stdout.
+"""bench.py -- form2 assembly on B200 for BASELINE.json's configs, one JSON line on stdout.
 
-A "step" is one `a = integrate(elements(mesh), gradt(u)*trans(grad(v)))` over the whole mesh (zero + assemble).
-Workload at N=1: BASELINE.json configs[1] -- P2 on the ~8M-element unit-cube tet mesh (m=110, 7 986 000 tets),
-jittered vertices, generated (cell-major) element order.  Device-resident inputs (mesh, DofTable, CSR graph and the
-element->CSR maps) are prepared untimed: they are Feel++'s setup (Pch, newMatrix).
+A "step" is one `a = integrate(elements(mesh), <form>)` over the whole mesh (zero + assemble [+ ghost-row exchange]).
+Default workload (N=1): BASELINE.json configs[1] -- P2 scalar Laplacian on the ~8M-element unit-cube tet mesh (m=110,
+7 986 000 tets), jittered vertices, generated (cell-major) element order: the configuration the metric is quoted on.
+`--config` selects the other configurations of BASELINE.json:
+
+  1  P1 scalar  gradt(u)*trans(grad(v))                                   m=55   (configs[0], with the single-core CPU time)
+  2  P2 scalar  gradt(u)*trans(grad(v))                                   m=110  (configs[1], the headline line)
+  3  P3 scalar  k*inner(gradt(u),grad(v)), k = expr("1+x*y+z^2") (Q=24)   m=87   (configs[2]; --coeff idv: k = idv(P1 field), Q=14)
+  4  P2 vector  inner(lambda*trace(sym(gradt u))*Id + 2 mu sym(gradt u), grad v), E=1e8, nu=0.25
+                                                                          m=139 on 8 GPUs (configs[3]); at N GPUs its
+                                                                          per-GPU share m = 139 (N/8)^(1/3): 70 / 88 / 110 / 139
+
+Device-resident inputs (mesh, DofTable, CSR graph and the element->CSR maps / plans) are prepared untimed: they are
+Feel++'s setup (Pch, newMatrix); their cost is reported in run_info.setup together with the break-even count.
 
   value  : elements/s, inputs resident in HBM, CUDA events on the launching stream
   e2e    : the same through feelgpu_form2_assemble_host: per step H2D of the vertex coordinates from pinned host memory
            (padded to one sector per vertex on the device) and D2H of the CSR values into pinned host memory
   --impl reference : the CPU element loop (oracle restatement of the reference; Feel++ itself cannot be built here)
+  --scaling strong : the global mesh is fixed (--m) and split over the GPUs; weak (default): m grows with N^(1/3)
 """
 import argparse
 import ctypes as C
@@ -28,6 +39,18 @@ sys.path.insert(0, ROOT)
 METRIC = "P2 tet Laplacian form2 assembly throughput"
 UNIT = "elements/s"
 
+# per config: Lagrange order, components, form, cells per edge at ONE GPU (weak scaling multiplies by N^(1/3))
+CONFIGS = {
+    1: {"order": 1, "ncomp": 1, "form": "stiffness", "m1": 55.0, "name": "configs[0]"},
+    2: {"order": 2, "ncomp": 1, "form": "stiffness", "m1": 110.0, "name": "configs[1]"},
+    3: {"order": 3, "ncomp": 1, "form": "kstiffness", "m1": 87.0, "name": "configs[2]"},
+    4: {"order": 2, "ncomp": 3, "form": "elasticity", "m1": 69.5, "name": "configs[3]"},
+}
+E_MOD, NU = 1e8, 0.25          # benchmarks/ATTIC/perf/assembly.cpp:86-89
+LAME_LAMBDA = E_MOD * NU / ((1 + NU) * (1 - 2 * NU))
+LAME_MU = E_MOD / (2 * (1 + NU))
+K_EXPR = "1+x*y+z^2"
+
 
 def parse():
     ap = argparse.ArgumentParser()
@@ -35,15 +58,30 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--m", type=int, default=110, help="cells per edge of the unit cube (110 -> 7 986 000 tets)")
-    ap.add_argument("--order", type=int, default=2)
+    ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
+    ap.add_argument("--coeff", default="expr", choices=["expr", "idv"], help="config 3: closed-form k or a P1 field idv(k)")
+    ap.add_argument("--m", type=int, default=None, help="cells per edge of the unit cube (overrides the config's size)")
+    ap.add_argument("--order", type=int, default=None, help="Lagrange order (overrides the config's)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--partition", default="auto", choices=["auto", "metis", "rcb"],
+                    help="element partition at N>1: METIS on the face-adjacency graph as the reference does, or coordinate bisection")
     ap.add_argument("--algo", default="auto", choices=["auto", "scatter", "rowplan", "eplan"])
     ap.add_argument("--shuffle", action="store_true", help="Fisher-Yates shuffled element order")
     ap.add_argument("--mesh", default=None, help="a Gmsh .msh file (tetrahedra) used instead of the synthetic cube; "
-                    "one GPU only, reported as its own workload (never the configs[1] line)")
+                    "one GPU only, reported as its own workload (never a BASELINE config line)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity block (N>1)")
+    args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    if args.order is None:
+        args.order = cfg["order"]
+    args.ncomp, args.form = cfg["ncomp"], cfg["form"]
+    # cells per edge of the GLOBAL mesh: weak scaling grows the one-GPU size with N^(1/3), strong scaling keeps it
+    m1 = float(args.m) if args.m is not None else cfg["m1"]
+    world = max(args.gpus, 1)
+    args.m_global = int(round(m1 * world ** (1.0 / 3.0))) if args.scaling == "weak" else int(round(m1))
+    return args
 
 
 def physical_cores():
@@ -60,12 +98,83 @@ def physical_cores():
     return max(1, n)
 
 
+# ---- the workload: space, expression, oracle arguments, algorithmic bytes -----------------------------------------------
+def quad_order(args):
+    k = args.order
+    if args.form == "kstiffness":
+        return 2 * (k - 1) + (2 if args.coeff == "expr" else 1)     # degree-2 polynomial / P1 field (expr.hpp:1075)
+    return max(1, 2 * (k - 1))
+
+
+def make_space(args, mesh):
+    import feelpp_b200 as fpp
+    return fpp.Pchv(mesh, args.order) if args.ncomp == 3 else fpp.Pch(mesh, args.order)
+
+
+def field_values(mesh_xyz):
+    """nodal values of the P1 conductivity field of config 3: 1 + 0.5 sin(2 pi x)"""
+    return 1.0 + 0.5 * np.sin(2 * np.pi * mesh_xyz[:, 0])
+
+
+def make_expr(args, Xh, mesh):
+    """the expression of the step in the harness' Feel++ language (feelpp_b200/vf.py)"""
+    import feelpp_b200 as fpp
+    from feelpp_b200 import Id, expr, grad, gradt, idv, inner, sym, trace, trans
+    u = v = fpp.Element(Xh)
+    if args.form == "stiffness":
+        return gradt(u) * trans(grad(v))
+    if args.form == "kstiffness":
+        if args.coeff == "expr":
+            return expr(K_EXPR) * inner(gradt(u), grad(v))
+        Kh = fpp.Pch(mesh, 1)
+        kf = fpp.Element(Kh, Kh.interpolate(lambda x, y, z: 1.0 + 0.5 * np.sin(2 * np.pi * x)))
+        return idv(kf) * inner(gradt(u), grad(v))
+    return inner(LAME_LAMBDA * trace(sym(gradt(u))) * Id() + 2 * LAME_MU * sym(gradt(u)), grad(v))
+
+
+def oracle_args(args, mesh):
+    """(kind, coefficient) of the same form for the oracle element loop"""
+    import feelpp_b200 as fpp
+    from oracle import oracle as orc
+    if args.form == "stiffness":
+        return orc.STIFFNESS, orc.Coeff()
+    if args.form == "kstiffness":
+        if args.coeff == "expr":
+            prog = fpp.GinacProgram(K_EXPR)
+            return orc.STIFFNESS, orc.Coeff(kind=orc.COEFF_EXPR, ops=prog.ops, consts=prog.consts)
+        Kh = fpp.Pch(mesh, 1)
+        return orc.STIFFNESS, orc.Coeff(kind=orc.COEFF_FIELD, field_order=1, field_l2g=Kh.l2g,
+                                        field_values=Kh.interpolate(lambda x, y, z: 1.0 + 0.5 * np.sin(2 * np.pi * x)))
+    return orc.ELASTICITY, orc.Coeff(lam=LAME_LAMBDA, mu=LAME_MU)
+
+
+def form_text(args):
+    if args.form == "stiffness":
+        return "gradt(u)*trans(grad(v))"
+    if args.form == "kstiffness":
+        return ("expr(\"%s\")" % K_EXPR if args.coeff == "expr" else "idv(k), k in P1 = 1+0.5 sin(2 pi x)") + "*inner(gradt(u),grad(v))"
+    return "inner(lambda*trace(sym(gradt(u)))*Id + 2 mu sym(gradt(u)), grad(v)), E=1e8, nu=0.25"
+
+
+def bytes_per_element(args, npts, nelt, nnz):
+    """algorithmic bytes per element: connectivity + coordinates (each point once) + int32
+    element->slot map (node level: the 3x3 blocks of a product space are contiguous) + every CSR value written once
+    [+ coefficient: the field's l2g and nodal values]"""
+    n = (args.order + 1) * (args.order + 2) * (args.order + 3) // 6
+    nd = n * args.ncomp
+    slotmap = 4 * n * n if args.ncomp == 3 else 4 * nd * nd
+    be = 16 + 24.0 * npts / nelt + slotmap + 8.0 * nnz / nelt
+    if args.form == "kstiffness" and args.coeff == "idv":
+        be += 16 + 8.0 * npts / nelt
+    return be
+
+
 def workload(args, want_graph=True):
     """builds the host-side objects (untimed setup)"""
     import feelpp_b200 as fpp
     t0 = time.time()
-    mesh = fpp.loadMesh(args.mesh) if args.mesh else fpp.unitCube(args.m, 0.15, args.shuffle)
-    Xh = fpp.Pch(mesh, args.order)
+    mesh = fpp.loadMesh(args.mesh) if args.mesh else fpp.unitCube(args.m_global, 0.15, args.shuffle)
+    Xh = make_space(args, mesh)
     t1 = time.time()
     ia, ja = Xh.graph() if want_graph else (None, None)
     t2 = time.time()
@@ -73,43 +182,56 @@ def workload(args, want_graph=True):
     return mesh, Xh, ia, ja, info
 
 
-def config_dict(args, mesh, Xh, nnz):
+def config_dict(args, npts, nelt, ndof, nnz):
+    """identical in both arms (the driver compares the dicts): what is computed, not how"""
+    sp = "P%d %s" % (args.order, "vector (3 components)" if args.ncomp == 3 else "scalar")
     if args.mesh:
-        return {"workload": "P%d scalar Laplacian form2 gradt(u)*trans(grad(v)) on the mesh file %s (not a BASELINE config)"
-                            % (args.order, os.path.basename(args.mesh)),
-                "elements": int(mesh.numElements()), "points": int(mesh.numPoints()), "dofs": int(Xh.nDof()),
-                "nnz": int(nnz), "quadrature": "IMTetrahedra<%d>" % max(1, 2 * (args.order - 1)),
-                "vertices": "file", "element_order": "file",
+        return {"workload": "%s form2 %s on the mesh file %s (not a BASELINE config)" % (sp, form_text(args), os.path.basename(args.mesh)),
+                "elements": int(nelt), "points": int(npts), "dofs": int(ndof), "nnz": int(nnz),
+                "quadrature": "IMTetrahedra<%d>" % quad_order(args), "vertices": "file", "element_order": "file",
                 "l2_policy": "inputs larger than L2 only if the mesh is (CSR values %.0f MB)" % (8e-6 * nnz)}
-    return {"workload": "configs[1]: P%d scalar Laplacian form2 gradt(u)*trans(grad(v)), unit cube m=%d" % (args.order, args.m),
-            "elements": int(mesh.numElements()), "points": int(mesh.numPoints()), "dofs": int(Xh.nDof()),
-            "nnz": int(nnz), "quadrature": "IMTetrahedra<%d>" % max(1, 2 * (args.order - 1)),
+    return {"workload": "%s: %s form2 %s, unit cube m=%d" % (CONFIGS[args.config]["name"], sp, form_text(args), args.m_global),
+            "elements": int(nelt), "points": int(npts), "dofs": int(ndof), "nnz": int(nnz),
+            "quadrature": "IMTetrahedra<%d>" % quad_order(args),
             "vertices": "jittered 0.15h", "element_order": "shuffled" if args.shuffle else "generated",
             "l2_policy": "inputs larger than L2 (CSR values + element maps >> 126 MB)"}
+
+
+def metric_name(args):
+    if args.config == 2 and args.order == 2:
+        return METRIC
+    return "P%d%s tet form2 assembly throughput (%s)" % (args.order, "v" if args.ncomp == 3 else "", args.form)
 
 
 def cpu_run(args, mesh, Xh, ia, ja, threads, sample_elts):
     """times the oracle element loop (restatement of integrator.hpp:1093-1207 + MatSetValues) on `threads` host threads"""
     from oracle import oracle as orc
     n = min(sample_elts, mesh.numElements())
-    quad = max(1, 2 * (args.order - 1))
+    kind, co = oracle_args(args, mesh)
     a = np.zeros(int(ia[-1]))
-    _, secs = orc.form2(orc.STIFFNESS, args.order, 1, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja, a=a,
+    _, secs = orc.form2(kind, args.order, args.ncomp, quad_order(args), mesh.xyz, mesh.conn, Xh.l2g, ia, ja, co, a=a,
                         elt_range=(0, n), threads=threads)
     return n / secs, n, secs
+
+
+def cpu_sample_size(args, cores, nelt):
+    """elements per timed CPU step: about 10-30 s of host work in total, scaled by the cost of an element of the form"""
+    per_core = {"stiffness": 400_000 if args.order <= 2 else 60_000, "kstiffness": 50_000, "elasticity": 50_000}[args.form]
+    if args.order == 1:
+        per_core = 1_000_000
+    return int(min(nelt, per_core * cores))
 
 
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    # the same global mesh as the GPU arm at this N (weak scaling: m grows with N^(1/3)); a step is a bounded sample of it
+    # the same global mesh as the GPU arm at this N; a step is a bounded sample of it
     if args.mesh and args.gpus > 1:
-        raise SystemExit("--mesh runs on one GPU (the multi-GPU line is the weak-scaling cube)")
-    args.m = int(round(args.m * max(args.gpus, 1) ** (1.0 / 3.0)))
+        raise SystemExit("--mesh runs on one GPU (the multi-GPU line is the cube)")
     mesh, Xh, ia, ja, info = workload(args)
     cores = physical_cores()
-    sample = min(mesh.numElements(), 400_000 * cores)
+    sample = cpu_sample_size(args, cores, mesh.numElements())
     for _ in range(args.warmup):
         cpu_run(args, mesh, Xh, ia, ja, cores, max(1, sample // 8))
     t = 0.0
@@ -119,10 +241,11 @@ def reference_arm(args):
         t += si
         n += ni
     value = n / t
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "mesh file" if args.mesh else "synthetic",
-            "config": config_dict(args, mesh, Xh, ia[-1]),
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
+            "data": "mesh file" if args.mesh else "synthetic",
+            "config": config_dict(args, mesh.numPoints(), mesh.numElements(), Xh.nDof(), ia[-1]),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": "first %d elements of the mesh per step, %d threads, contiguous element blocks "
                                        "with owner/stash merge (oracle_form2_threads)" % (sample, cores)},
@@ -175,8 +298,8 @@ def gpu_arm(args):
     import torch
     import torch.distributed as dist
     import feelpp_b200 as fpp
-    from feelpp_b200 import elements, grad, gradt, integrate, trans
-    from feelpp_b200._capi import Form2Desc, check, c_dblp, ptr
+    from feelpp_b200 import elements, integrate
+    from feelpp_b200._capi import check, c_dblp
     from feelpp_b200 import engine as E
 
     rank = int(os.environ.get("RANK", "0"))
@@ -184,12 +307,13 @@ def gpu_arm(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1 and args.mesh:
-        raise SystemExit("--mesh runs on one GPU (the multi-GPU line is the weak-scaling cube)")
+        raise SystemExit("--mesh runs on one GPU (the multi-GPU line is the cube)")
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     algo = {"auto": fpp.ALGO_AUTO, "scatter": fpp.ALGO_SCATTER, "rowplan": fpp.ALGO_ROWPLAN, "eplan": fpp.ALGO_EPLAN}[args.algo]
     eng = fpp.Engine(local)
+    lp = None
     if world == 1:
         mesh, Xh, ia, ja, info = workload(args)
         nElt, nnz = mesh.numElements(), int(ia[-1])
@@ -197,17 +321,16 @@ def gpu_arm(args):
         a = fpp.form2(_test=Xh, _trial=Xh, engine=eng, algorithm=algo,
                       pattern_flags={"rowplan": 3, "scatter": 1}.get(args.algo, 0))
         info["pattern_create_s"] = round(time.time() - t0, 2)
-        nElt_total, nnz_total, gmesh = nElt, nnz, mesh
+        nElt_total, nnz_total, gmesh, ndof_total = nElt, nnz, mesh, Xh.nDof()
+        part_name = "1 GPU"
     else:
-        # weak scaling: the global mesh grows with the number of GPUs (m = 110 * N^(1/3): 16.1M / 32.2M / 63.9M tets),
-        # recursive-bisection partition, one partition + owned row block per GPU, NCCL ghost-row exchange per step
+        # one partition + owned row block per GPU (the reference's MPI layout), ghost rows handed to their owners per step
         from feelpp_b200 import parallel as par, distributed as dd
-        args.m = int(round(args.m * world ** (1.0 / 3.0)))
         t0 = time.time()
-        gmesh = fpp.unitCube(args.m, 0.15, args.shuffle)
-        part = par.partition_rcb(gmesh, world)
+        gmesh = fpp.unitCube(args.m_global, 0.15, args.shuffle)
+        part, part_name = par.partition(gmesh, world, args.partition)
         t1 = time.time()
-        lp = par.LocalProblem(gmesh, part, args.order, 1, par.Comm(rank, world, dist))
+        lp = par.LocalProblem(gmesh, part, args.order, args.ncomp, par.Comm(rank, world, dist))
         t2 = time.time()
         Xh = dd.LocalSpace(lp)
         mesh = lp.mesh
@@ -215,16 +338,16 @@ def gpu_arm(args):
         info = {"mesh_partition_s": round(t1 - t0, 2), "local_problem_s": round(t2 - t1, 2),
                 "pattern_create_s": round(time.time() - t2, 2), "local_elements": int(mesh.numElements()),
                 "owned_dofs": int(lp.nDofOwned), "ghost_dofs": int(lp.nDofWithGhost - lp.nDofOwned),
-                "send_values": int(sum(c for _, _, c in lp.send))}
+                "send_values": int(lp.send_values()), "neighbours": int(lp.num_neighbours())}
         ia = lp.ia
         nElt, nnz = mesh.numElements(), int(ia[-1])
         nElt_total = gmesh.numElements()
         tn = torch.tensor([lp.nnz_owned()], device="cuda", dtype=torch.int64)
         dist.all_reduce(tn)
         nnz_total = int(tn.item())
+        ndof_total = int(lp.nGlobalDof)
     info["plan"] = a.plan_stats()
-    u = v = fpp.Element(Xh)
-    integ = integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v)))
+    integ = integrate(_range=elements(mesh), _expr=make_expr(args, Xh, mesh))
     keep = E._Keep()
     desc = a._desc(integ, keep)
     stream = torch.cuda.current_stream()
@@ -233,8 +356,8 @@ def gpu_arm(args):
 
     def step():
         if world > 1:
-            a.assemble_desc(desc, 0, sptr)   # ghost rows land in their owners' memory while the kernel runs
-            a.close()                        # NCCL barrier + owner-side add
+            a.assemble_desc(desc, 0, sptr)   # ghost rows land in their owners' memory while the kernel runs (entity plan)
+            a.close()                        # completion barrier / NCCL exchange + owner-side add
         else:
             check(lib.feelgpu_form2_assemble(a.pat, C.byref(desc), 0, a.d_values, sptr), eng.ctx)
 
@@ -273,27 +396,39 @@ def gpu_arm(args):
     tmax = torch.tensor([ms], device="cuda", dtype=torch.float64)
     if world > 1:
         # per rank: elements, ghost-row values sent, step and kernel milliseconds (the step time reported is the maximum)
-        mine = torch.tensor([float(nElt), float(sum(c for _, _, c in lp.send)), ms / args.steps,
-                             sorted(k[1] for k in kern_ms)[len(kern_ms) // 2]], device="cuda", dtype=torch.float64)
+        mine = torch.tensor([float(nElt), float(lp.send_values()), ms / args.steps,
+                             sorted(k[1] for k in kern_ms)[len(kern_ms) // 2], float(lp.num_neighbours())],
+                            device="cuda", dtype=torch.float64)
         every = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(every, mine)
         info["per_rank"] = [{"elements": int(t[0].item()), "send_values": int(t[1].item()),
-                             "step_ms": round(t[2].item(), 4), "kernel_ms": round(t[3].item(), 4)} for t in every]
+                             "step_ms": round(t[2].item(), 4), "kernel_ms": round(t[3].item(), 4),
+                             "neighbours": int(t[4].item())} for t in every]
+        ne = [p["elements"] for p in info["per_rank"]]
+        info["imbalance"] = round(max(ne) * world / float(sum(ne)), 4)
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms = float(tmax.item())
     value = nElt_total * args.steps / (ms * 1e-3)
-    # clocks under load: 20 steps last ~26 ms and nvidia-smi samples every 100 ms, so the same step keeps running for
-    # ~0.6 s more (the count is derived from the all-reduced time: every rank runs the same number of collectives)
-    for _ in range(int(min(2000, max(50, 0.6 / (ms / args.steps * 1e-3))))):
+    # clocks under load: the timed region may last only ~26 ms and nvidia-smi samples every 100 ms, so the same step keeps
+    # running for ~0.6 s more (the count is derived from the all-reduced time: every rank runs the same number of collectives)
+    for _ in range(int(min(2000, max(10, 0.6 / (ms / args.steps * 1e-3))))):
         step()
     barrier()
     clocks = sampler.stop(tw0, time.time()) if sampler else None
+
+    # ---- multi-GPU parity: every owned row after close(), against the invariant and the oracle ----
+    parity = None
+    if world > 1 and not args.no_parity:
+        from feelpp_b200 import parity_mp
+        step()
+        barrier()
+        parity = parity_mp.check(args, lp, gmesh, a, dist, oracle_args(args, gmesh), quad_order(args))
 
     # ---- end to end: host buffers, H2D of the coordinates + D2H of the CSR values inside the timed region ----
     e2e = None
     if not args.no_e2e:
         # host buffers in, host buffers out: per step H2D of the (local) vertex coordinates from host memory, assembly
-        # [+ NCCL ghost-row exchange], D2H of the (owned) CSR values into pinned host memory
+        # [+ ghost-row exchange], D2H of the (owned) CSR values into pinned host memory
         nown = nnz if world == 1 else lp.nnz_owned()
         hp = C.c_void_p()
         check(lib.feelgpu_host_alloc_pinned(eng.ctx, 8 * max(nown, 1), C.byref(hp)), eng.ctx)
@@ -337,48 +472,54 @@ def gpu_arm(args):
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        nd = Xh.nd
-        # algorithmic bytes per element: conn + coords + int32 element->slot map + CSR values once
-        Be = 16 + 24.0 * gmesh.numPoints() / nElt_total + 4 * nd * nd + 8.0 * nnz_total / nElt_total
+        Be = bytes_per_element(args, gmesh.numPoints(), nElt_total, nnz_total)
         kms = sorted(k[1] for k in kern_ms)[len(kern_ms) // 2]
         zms = sorted(k[0] for k in kern_ms)[len(kern_ms) // 2]
         achieved = Be * nElt / (kms * 1e-3) / 1e9
-        traffic = None     # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same config only)
-        try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_eplan_traffic.json")))
-            if world == 1 and args.m == 110 and args.order == 2 and args.algo in ("auto", "eplan") and not args.shuffle and not args.mesh:
-                traffic = tr["dram_bytes_per_launch"]
-        except Exception:
-            pass
         roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel_ms": kms, "zero_fill_ms": zms, "algorithmic_bytes_per_element": Be,
+                "traffic": None, "traffic_source": "not measured in this run (ncu captures: profiles/)",
+                "kernel_ms": kms, "zero_fill_ms": zms, "algorithmic_bytes_per_element": Be,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                 "step_frac_vs_peak": Be * nElt_total / world / (ms / args.steps * 1e-3) / 1e9 / peak}
         cpu = None
+        setup_s = sum(v for k, v in info.items() if k.endswith("_s"))
         if not args.no_cpu_baseline and world == 1:
             cores = physical_cores()
-            sample = min(nElt, 400_000 * cores)
+            sample = cpu_sample_size(args, cores, nElt)
             cpu_run(args, mesh, Xh, ia, ja, cores, max(1, sample // 8))
             v, n, s = cpu_run(args, mesh, Xh, ia, ja, cores, sample)
             cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": "first %d elements, %d threads, %.1f s (oracle_form2_threads)" % (n, cores, s)}
-        cfg = config_dict(args, gmesh, Xh, nnz_total)
-        cfg["dofs"] = int(Xh.nDof()) if world == 1 else int(lp.nGlobalDof)
-        cfg["algorithm"] = args.algo
-        cfg["parallelism"] = "1 GPU" if world == 1 else ("%d GPUs: recursive-bisection element partition, owned row "
-                                                         "blocks; every step hands the ghost rows to their owners (%s)"
-                                                         % (world, "stored over NVLink peer memory by the assembly "
-                                                            "kernel, NCCL barrier, owner-side add" if a.peer else
-                                                            "NCCL send/recv of the ghost-row tail, owner-side add"))
-        cfg["setup"] = info
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            if args.config == 1:
+                # BASELINE.json configs[0]: "single process on CPU" -- the whole mesh on one core
+                v1, n1, s1 = cpu_run(args, mesh, Xh, ia, ja, 1, nElt)
+                cpu["single_core"] = {"value": v1, "unit": UNIT, "cores": 1, "elements": n1, "seconds": round(s1, 3)}
+            # break-even: assemblies on one mesh+space after which engine setup + k GPU steps beat k CPU assemblies
+            t_cpu = nElt / v
+            t_gpu = (e2e["ms_per_step"] if e2e else ms / args.steps) * 1e-3
+            info["engine_setup_s"] = round(info.get("pattern_create_s", 0.0), 2)
+            info["breakeven_assemblies"] = (round(info["engine_setup_s"] / (t_cpu - t_gpu), 1) if t_cpu > t_gpu else None)
+        info["setup_s"] = round(setup_s, 2)
+        run_info = {"algorithm": args.algo,
+                    "parallelism": part_name if world == 1 else (
+                        "%d GPUs: %s, owned row blocks; every step hands the ghost rows to their owners (%s)"
+                        % (world, part_name, "stored over NVLink peer memory by the assembly kernel, NCCL barrier, "
+                           "owner-side add" if a.peer else "NCCL send/recv of the ghost rows, owner-side add")),
+                    "setup": info}
+        line = {"metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "mesh file" if args.mesh else "synthetic", "config": cfg,
+                "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
+                "data": "mesh file" if args.mesh else "synthetic",
+                "config": config_dict(args, gmesh.numPoints(), nElt_total, ndof_total, nnz_total),
                 "nnz_per_s": nnz_total * args.steps / (ms * 1e-3), "roofline": roof, "cpu_baseline": cpu,
-                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "run_info": run_info}
+        if parity is not None:
+            line["parity"] = parity
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and not parity.get("ok", False):
+        sys.exit(3)
 
 
 if __name__ == "__main__":

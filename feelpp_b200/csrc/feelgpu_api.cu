@@ -111,16 +111,20 @@ static int upload_points(feelgpu_mesh_t m, const double* xyz, cudaStream_t s)
     cudaGetLastError();   // (older drivers report unregistered host memory as an error)
     const double* src = xyz;
     if (!pinned) {
-        // the staging buffer is reused: a previous upload on this stream must have left it
-        CTX_CUDA(ctx, cudaStreamSynchronize(s));
+        // the staging buffer is reused: the previous upload through it (on whatever stream) must have left it
+        if (m->stage_busy) CTX_CUDA(ctx, cudaEventSynchronize(m->stage_event));
         std::memcpy(m->h_stage, xyz, bytes);
         src = m->h_stage;
     }
+    // d_raw is shared as well: order this upload after the previous one's padding kernel when the stream differs
+    if (m->stage_busy) CTX_CUDA(ctx, cudaStreamWaitEvent(s, m->stage_event, 0));
     CTX_CUDA(ctx, cudaMemcpyAsync(m->d_raw, src, bytes, cudaMemcpyHostToDevice, s));
     const int grid = (int)std::min<int64_t>((m->nPts + 255) / 256, (int64_t)std::max(ctx->sm_count, 1) * 8);
     k_pad_points<<<grid, 256, 0, s>>>(m->nPts, m->d_raw, m->d_xyz);
     ctx->launches++;
     CTX_CUDA(ctx, cudaGetLastError());
+    CTX_CUDA(ctx, cudaEventRecord(m->stage_event, s));
+    m->stage_busy = true;
     return FEELGPU_OK;
 }
 
@@ -143,7 +147,8 @@ int feelgpu_mesh_create(feelgpu_context_t ctx, int64_t nPts, const double* xyz, 
     if ((err = cudaMalloc(&m->d_xyz, sizeof(double) * 4 * nPts)) != cudaSuccess ||
         (err = cudaMalloc(&m->d_conn, sizeof(int4) * std::max<int64_t>(nElt, 1))) != cudaSuccess ||
         (err = cudaMalloc(&m->d_raw, sizeof(double) * 3 * nPts)) != cudaSuccess ||
-        (err = cudaMallocHost(&m->h_stage, sizeof(double) * 3 * nPts)) != cudaSuccess) {
+        (err = cudaMallocHost(&m->h_stage, sizeof(double) * 3 * nPts)) != cudaSuccess ||
+        (err = cudaEventCreateWithFlags(&m->stage_event, cudaEventDisableTiming)) != cudaSuccess) {
         ctx->last_error = std::string("mesh_create: ") + cudaGetErrorString(err);
         feelgpu_mesh_destroy(m);
         return FEELGPU_ERR_CUDA;
@@ -180,6 +185,7 @@ int feelgpu_mesh_destroy(feelgpu_mesh_t m)
     if (m->d_raw) cudaFree(m->d_raw);
     if (m->d_conn) cudaFree(m->d_conn);
     if (m->h_stage) cudaFreeHost(m->h_stage);
+    if (m->stage_event) cudaEventDestroy(m->stage_event);
     delete m;
     return FEELGPU_OK;
 }
@@ -545,8 +551,8 @@ int feelgpu_form2_zero_rows(feelgpu_pattern_t pat, int64_t n, const int32_t* row
     if (!pat) return FEELGPU_ERR_ARG;
     feelgpu_context_t ctx = pat->ctx;
     if (n < 0 || n > pat->nRows || (n && (!rows || !values)) || !a_values) ARG_FAIL(ctx, "zero_rows: bad argument");
-    if (!(strategy & (FEELGPU_ON_ELIMINATION | FEELGPU_ON_SYMMETRIC))) {
-        ctx->last_error = "zero_rows: the strategy must contain ELIMINATION or SYMMETRIC (penalisation stays on the host)";
+    if (!(strategy & FEELGPU_ON_ELIMINATION) || (strategy & ~(FEELGPU_ON_ELIMINATION | FEELGPU_ON_KEEP_DIAGONAL | FEELGPU_ON_SYMMETRIC))) {
+        ctx->last_error = "zero_rows: the strategy must contain ContextOn::ELIMINATION (penalisation stays on the host)";
         return FEELGPU_ERR_UNSUPPORTED;
     }
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));

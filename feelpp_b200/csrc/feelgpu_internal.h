@@ -30,6 +30,8 @@ struct feelgpu_mesh_s {
     int4* d_conn = nullptr;      // [nElt]
     double* d_raw = nullptr;     // [nPts][3]: the caller's layout as it arrives; k_pad_points writes d_xyz from it
     double* h_stage = nullptr;   // pinned staging for update_points from pageable caller memory
+    cudaEvent_t stage_event = nullptr;   // recorded after every coordinate upload (h_stage / d_raw are reused across streams)
+    bool stage_busy = false;
     std::vector<double> h_xyz;   // host copies: the plan builder orders rows along a space-filling curve
     std::vector<int32_t> h_conn;
 };

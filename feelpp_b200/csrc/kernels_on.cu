@@ -12,6 +12,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <vector>
 
 namespace {
 
@@ -182,33 +183,61 @@ int feelgpu_launch_zero_rows(feelgpu_pattern_t pat, int n, const int32_t* h_rows
         ctx->last_error = "zero_rows: the pattern holds column ids beyond 32 bits";
         return FEELGPU_ERR_UNSUPPORTED;
     }
-    for (int k = 0; k < n; ++k)
-        if (h_rows[k] < 0 || h_rows[k] >= pat->nRows) {
-            ctx->last_error = "zero_rows: row id outside [0,nRows)";
-            return FEELGPU_ERR_ARG;
+    // The reference de-duplicates the dofs while it collects them (feelvf/on.hpp: std::find(dofs...) -> continue), so a row
+    // listed twice keeps its first value.  The same is done here, on private copies: two warps of k_on_columns working on
+    // one row would otherwise both subtract a_cr x_r from b_c.  The copies are pageable, so the asynchronous uploads
+    // below have staged them when cudaMemcpyAsync returns, whatever kind of memory the caller passed.
+    std::vector<int32_t> rows;
+    std::vector<double> xs;
+    rows.reserve(n);
+    xs.reserve(n);
+    {
+        std::vector<uint8_t> seen((size_t)pat->nRows, 0);
+        for (int k = 0; k < n; ++k) {
+            const int32_t r = h_rows[k];
+            if (r < 0 || r >= pat->nRows) {
+                ctx->last_error = "zero_rows: row id outside [0,nRows)";
+                return FEELGPU_ERR_ARG;
+            }
+            if (seen[r]) continue;
+            seen[r] = 1;
+            rows.push_back(r);
+            xs.push_back(h_x[k]);
         }
+    }
+    n = (int)rows.size();
     int32_t* d_rows = nullptr;
     double* d_x = nullptr;
-    FEELGPU_CHECK_CUDA(ctx, cudaMallocAsync(&d_rows, sizeof(int32_t) * n, s));
-    FEELGPU_CHECK_CUDA(ctx, cudaMallocAsync(&d_x, sizeof(double) * n, s));
-    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(d_rows, h_rows, sizeof(int32_t) * n, cudaMemcpyHostToDevice, s));
-    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(d_x, h_x, sizeof(double) * n, cudaMemcpyHostToDevice, s));
+    int32_t* d_mark = nullptr;
+    // every exit path releases the stream-ordered temporaries
+    auto fail = [&](cudaError_t err, const char* what) {
+        ctx->last_error = std::string("zero_rows: ") + what + ": " + cudaGetErrorString(err);
+        if (d_rows) cudaFreeAsync(d_rows, s);
+        if (d_x) cudaFreeAsync(d_x, s);
+        if (d_mark) cudaFreeAsync(d_mark, s);
+        return FEELGPU_ERR_CUDA;
+    };
+    cudaError_t err;
+    if ((err = cudaMallocAsync(&d_rows, sizeof(int32_t) * n, s)) != cudaSuccess) return fail(err, "cudaMallocAsync");
+    if ((err = cudaMallocAsync(&d_x, sizeof(double) * n, s)) != cudaSuccess) return fail(err, "cudaMallocAsync");
+    if ((err = cudaMemcpyAsync(d_rows, rows.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
+        (err = cudaMemcpyAsync(d_x, xs.data(), sizeof(double) * n, cudaMemcpyHostToDevice, s)) != cudaSuccess)
+        return fail(err, "cudaMemcpyAsync");
     const int threads = 256, wblocks = (int)(((int64_t)n * 32 + threads - 1) / threads);
     if (symmetric) {
-        int32_t* d_mark = nullptr;
-        FEELGPU_CHECK_CUDA(ctx, cudaMallocAsync(&d_mark, sizeof(int32_t) * std::max<int64_t>(pat->nRows, 1), s));
-        FEELGPU_CHECK_CUDA(ctx, cudaMemsetAsync(d_mark, 0, sizeof(int32_t) * pat->nRows, s));
+        if ((err = cudaMallocAsync(&d_mark, sizeof(int32_t) * std::max<int64_t>(pat->nRows, 1), s)) != cudaSuccess ||
+            (err = cudaMemsetAsync(d_mark, 0, sizeof(int32_t) * pat->nRows, s)) != cudaSuccess)
+            return fail(err, "mark array");
         k_on_mark<<<(n + threads - 1) / threads, threads, 0, s>>>(n, d_rows, d_mark);
         k_on_columns<<<wblocks, threads, 0, s>>>(n, d_rows, d_x, d_mark, pat->d_ia, pat->d_ja32, a, b);
         ctx->launches += 2;
-        FEELGPU_CHECK_CUDA(ctx, cudaFreeAsync(d_mark, s));
     }
     k_on_rows<<<wblocks, threads, 0, s>>>(n, d_rows, d_x, pat->d_ia, pat->d_ja32, pat->test->d_p2c, a, b,
                                           (strategy & FEELGPU_ON_KEEP_DIAGONAL) ? 1 : 0, value_on_diagonal);
     ctx->launches++;
-    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
-    FEELGPU_CHECK_CUDA(ctx, cudaFreeAsync(d_rows, s));
-    FEELGPU_CHECK_CUDA(ctx, cudaFreeAsync(d_x, s));
-    // the host arrays were read by asynchronous copies from pageable memory: those are staged before the call returns
+    if ((err = cudaGetLastError()) != cudaSuccess) return fail(err, "kernel launch");
+    cudaFreeAsync(d_rows, s);
+    cudaFreeAsync(d_x, s);
+    if (d_mark) cudaFreeAsync(d_mark, s);
     return FEELGPU_OK;
 }

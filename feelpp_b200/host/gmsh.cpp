@@ -362,6 +362,8 @@ GmshMesh readGmsh(std::string const& path, bool elementaryAsPhysical)
     is >> M.version >> format >> size;
     if (!is) fail("bad $MeshFormat line");
     if (M.version < 2) fail("only Gmsh version >= 2 is supported");    // importergmsh.hpp:1014-1015
+    // MSH 4.0 lays out $Entities / $Nodes / $Elements differently from 4.1 (importergmsh.hpp:1932-2143): not read here
+    if (M.version >= 4 && M.version < 4.1) fail("MSH 4.0 files are not supported (re-save as 4.1 or 2.2)");
     M.binary = format != 0;
     bool swap = false;
     if (M.binary) {

@@ -86,13 +86,13 @@ class MarkedFaceRange(BoundaryFaceRange):
                 raise ValueError("markedfaces(): the mesh carries no marked faces (use loadMesh on a .msh with triangles)")
             ids = [mesh.markerId(m) for m in (self.markers if isinstance(self.markers, (list, tuple)) else [self.markers])]
             e, f = BoundaryFaceRange(mesh).faces()
-            npts = mesh.numPoints()
             F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])
-            fv = np.sort(mesh.conn.astype(np.int64)[e[:, None], F2P[f]], axis=1)
-            key = (fv[:, 0] * npts + fv[:, 1]) * npts + fv[:, 2]
-            tv = np.sort(mesh.tri[np.isin(mesh.triMarker, ids)].astype(np.int64), axis=1)
-            tkey = (tv[:, 0] * npts + tv[:, 1]) * npts + tv[:, 2]
-            sel = np.isin(key, tkey)
+            # match on the three sorted point ids as one 24-byte record (no packing into one integer: npts^3 overflows
+            # int64 beyond ~2 M points)
+            rec = np.dtype([("a", np.int64), ("b", np.int64), ("c", np.int64)])
+            fv = np.ascontiguousarray(np.sort(mesh.conn.astype(np.int64)[e[:, None], F2P[f]], axis=1)).view(rec).ravel()
+            tv = np.ascontiguousarray(np.sort(mesh.tri[np.isin(mesh.triMarker, ids)].astype(np.int64), axis=1)).view(rec).ravel()
+            sel = np.isin(fv, tv)
             self._faces = (np.ascontiguousarray(e[sel]), np.ascontiguousarray(f[sel]))
         return self._faces
 

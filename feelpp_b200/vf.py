@@ -254,9 +254,11 @@ def integrate(_range, _expr, _quad=None):
     return Integrator(_range, _expr, _quad)
 
 
-ON_ELIMINATION, ON_SYMMETRIC, ON_KEEP_DIAGONAL = 1, 2, 4
+# ContextOn (feelalg/enums.hpp:56-66) and ContextOnMap (feelalg/enums.cpp:28-35), numerically as in the reference
+ON_PENALISATION, ON_ELIMINATION, ON_KEEP_DIAGONAL, ON_SYMMETRIC = 0, 1, 2, 4
 _ON_TYPES = {"elimination": ON_ELIMINATION, "elimination_keep_diagonal": ON_ELIMINATION | ON_KEEP_DIAGONAL,
-             "elimination_symmetric": ON_SYMMETRIC, "elimination_symmetric_keep_diagonal": ON_SYMMETRIC | ON_KEEP_DIAGONAL}
+             "elimination_symmetric": ON_ELIMINATION | ON_SYMMETRIC,
+             "elimination_symmetric_keep_diagonal": ON_ELIMINATION | ON_SYMMETRIC | ON_KEEP_DIAGONAL}
 
 
 class On:

@@ -161,11 +161,15 @@ int feelgpu_form1_assemble_host(feelgpu_space_t space, const feelgpu_form1_desc*
  * form2 += on(_range=boundaryfaces(mesh), _rhs=l, _element=u, _expr=g) collects the boundary dofs and their values on the
  * host (feelvf/on.hpp:395-449) and calls MatrixPetsc::zeroRows (feelalg/matrixpetsc.cpp:1762-1860), i.e. PETSc's
  * MatZeroRows / MatZeroRowsColumns.  rows: process-local dof ids (host), values: the Dirichlet value of every row (host);
- * a_values and b are DEVICE arrays (b may be NULL).  Strategies (feelvf/on.hpp:1159-1175):
- *   ELIMINATION      rows zeroed, a_rr = d, b_r = d*x_r                      (unsymmetric, the reference's default)
- *   SYMMETRIC        also the columns: b_i -= a_ir*x_r, a_ir = 0             (one space, identity cluster numbering)
- *   KEEP_DIAGONAL    d = the assembled a_rr instead of value_on_diagonal                                          */
-enum { FEELGPU_ON_ELIMINATION = 1, FEELGPU_ON_SYMMETRIC = 2, FEELGPU_ON_KEEP_DIAGONAL = 4 };
+ * a_values and b are DEVICE arrays (b may be NULL).  `strategy` is the reference's ContextOn bit set, passed through
+ * unchanged (feelalg/enums.hpp:56-66, string names feelalg/enums.cpp:28-35):
+ *   ELIMINATION   0x1  rows zeroed, a_rr = d, b_r = d*x_r; REQUIRED, as MatrixPetsc::zeroRows does nothing without it
+ *                      (matrixpetsc.cpp:1784); PENALISATION (0x0) stays on the host and is FEELGPU_ERR_UNSUPPORTED here
+ *   KEEP_DIAGONAL 0x2  d = the assembled a_rr instead of value_on_diagonal
+ *   SYMMETRIC     0x4  also the columns: b_i -= a_ir*x_r, a_ir = 0             (one space, identity cluster numbering)
+ * rows/values are read during the call (any host memory, may be freed afterwards).  A row listed more than once keeps
+ * its first value, as the reference's collection loop does (feelvf/on.hpp: std::find(dofs...) -> continue).         */
+enum { FEELGPU_ON_PENALISATION = 0, FEELGPU_ON_ELIMINATION = 1, FEELGPU_ON_KEEP_DIAGONAL = 2, FEELGPU_ON_SYMMETRIC = 4 };
 int feelgpu_form2_zero_rows(feelgpu_pattern_t pattern, int64_t n, const int32_t* rows, const double* values, int strategy,
                             double value_on_diagonal, double* a_values, double* b, void* stream);
 

@@ -806,11 +806,13 @@ double oracle_form2_threads(int kind, int order, int ncomp, int quad_order, int6
 // diagonal, b_r = diag*x_r -- or, with ContextOn::SYMMETRIC, MatZeroRowsColumns -- additionally b_i -= a_ir*x_r and
 // a_ir = 0 for the other rows.  ContextOn::KEEP_DIAGONAL restores the assembled diagonal afterwards
 // (MatDiagonalSet(diag, INSERT_VALUES)) and sets b_r = x_r * a_rr (matrixpetsc.cpp:1817-1829).
-// strategy bits: 1 elimination, 2 symmetric, 4 keep diagonal.  Sequential restatement, test infrastructure only.
+// strategy = ContextOn bits (feelalg/enums.hpp:56-66): 0x1 ELIMINATION (nothing happens without it, matrixpetsc.cpp:1784),
+// 0x2 KEEP_DIAGONAL, 0x4 SYMMETRIC.  Sequential restatement, test infrastructure only.
 // ---------------------------------------------------------------------------------------------------------------
 extern "C" int oracle_zero_rows(int64_t nRows, const int64_t* ia, const int64_t* ja, int64_t n, const int32_t* rows,
                                 const double* x, int strategy, double value_on_diagonal, double* a, double* b)
 {
+    if (!(strategy & 1)) return 0;                       // matrixpetsc.cpp:1784: only ContextOn::ELIMINATION acts
     std::vector<int64_t> mark((size_t)nRows, -1);
     for (int64_t k = 0; k < n; ++k) {
         if (rows[k] < 0 || rows[k] >= nRows) return 1;
@@ -820,7 +822,7 @@ extern "C" int oracle_zero_rows(int64_t nRows, const int64_t* ia, const int64_t*
     for (int64_t k = 0; k < n; ++k)
         for (int64_t p = ia[rows[k]]; p < ia[rows[k] + 1]; ++p)
             if (ja[p] == rows[k]) olddiag[k] = a[p];
-    if (strategy & 2)
+    if (strategy & 4)
         for (int64_t i = 0; i < nRows; ++i) {          // columns first: every other row loses its coupling to the rows
             for (int64_t p = ia[i]; p < ia[i + 1]; ++p) {
                 const int64_t k = mark[ja[p]];
@@ -831,7 +833,7 @@ extern "C" int oracle_zero_rows(int64_t nRows, const int64_t* ia, const int64_t*
         }
     for (int64_t k = 0; k < n; ++k) {
         const int64_t r = rows[k];
-        const double d = (strategy & 4) ? olddiag[k] : value_on_diagonal;
+        const double d = (strategy & 2) ? olddiag[k] : value_on_diagonal;
         for (int64_t p = ia[r]; p < ia[r + 1]; ++p) a[p] = (ja[p] == r) ? d : 0.0;
         if (b) b[r] = x[k] * d;
     }

@@ -63,7 +63,7 @@ int oracle_form1(int kind, int order, int ncomp, int quad_order,
                  int64_t nPts, const double* xyz, int64_t nElt, const int32_t* conn,
                  const int32_t* l2g, const oracle_coeff* coeff, int64_t elt_begin, int64_t elt_end, double* b);
 /* local matrix of ONE element (row-major nd x nd, bilinearform.hpp:462-464), for unit tests */
-/* on(): MatrixPetsc::zeroRows (feelalg/matrixpetsc.cpp:1762-1860); strategy bits 1 elimination, 2 symmetric, 4 keep diagonal */
+/* on(): MatrixPetsc::zeroRows (feelalg/matrixpetsc.cpp:1762-1860); strategy = ContextOn bits (feelalg/enums.hpp:56-66): 1 elimination (required), 2 keep diagonal, 4 symmetric */
 int oracle_zero_rows(int64_t nRows, const int64_t* ia, const int64_t* ja, int64_t n, const int32_t* rows, const double* x,
                      int strategy, double value_on_diagonal, double* a, double* b);
 int oracle_local_matrix(int kind, int order, int ncomp, int quad_order, const double* G /*[4][3]*/,

@@ -231,7 +231,7 @@ def local_matrix(kind, order, ncomp, quad_order, G, coeff=None):
     return Ae
 
 
-ON_ELIMINATION, ON_SYMMETRIC, ON_KEEP_DIAGONAL = 1, 2, 4
+ON_ELIMINATION, ON_KEEP_DIAGONAL, ON_SYMMETRIC = 1, 2, 4   # ContextOn, feelalg/enums.hpp:56-66
 
 
 def zero_rows(ia, ja, a, b, rows, x, strategy=ON_ELIMINATION, value_on_diagonal=1.0):

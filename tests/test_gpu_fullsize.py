@@ -116,3 +116,79 @@ def test_full_size_against_oracle_and_invariants(engine, order, m):
     co = orc.Coeff(kind=orc.COEFF_EXPR, ops=f.prog.ops, consts=f.prog.consts)
     ref = orc.form1(order, 1, orc.quad_order_form1(order, -1), mesh.xyz, mesh.conn, Xh.l2g, n, co)
     np.testing.assert_allclose(l.values(), ref, rtol=1e-12, atol=1e-12 * float(np.abs(ref).max()))
+
+
+# ---- configs[2] and configs[3] at full size (one GPU's share of config 4: m = 139 / 2) -------------------------------
+def _fullsize_form(engine, order, ncomp, m, make_expr, kind, coeff, quad, what, invariant):
+    """assemble `make_expr(Xh, mesh)` over the whole mesh with the default algorithm and compare every nonzero with the
+    oracle's threaded element loop; then the form's size-independent property"""
+    mesh = fpp.unitCube(m, 0.15, False)
+    Xh = fpp.Pchv(mesh, order) if ncomp == 3 else fpp.Pch(mesh, order)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine)
+    ia, ja = a.ia, a.ja
+    co = coeff(mesh)
+    a.assign(integrate(_range=elements(mesh), _expr=make_expr(Xh, mesh)))
+    vals = a.values()
+    ref, _ = orc.form2(kind, order, ncomp, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja, co, threads=THREADS)
+    scale, _ = orc.form2(kind | orc.ABS_FLAG, order, ncomp, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja, co, threads=THREADS)
+    worst = check_chunked(vals, ref, scale, ia, ja, what)
+    del ref, scale
+    invariant(a, Xh, vals, ia)
+    return worst
+
+
+K_EXPR = "1+x*y+z^2"
+
+
+def _k_field(mesh):
+    Kh = fpp.Pch(mesh, 1)
+    return Kh, Kh.interpolate(lambda x, y, z: 1.0 + 0.5 * np.sin(2 * np.pi * x))
+
+
+def _rows_sum_to_zero(a, Xh, vals, ia):
+    y = a.multVector(np.ones(Xh.nDof()))
+    assert (np.abs(y) <= 1e-12 * row_abs_sums(vals, ia)).all(), "K 1 != 0"
+
+
+@pytest.mark.parametrize("coeff", ["expr", "idv"])
+def test_full_size_config3_p3_variable_conductivity(engine, coeff):
+    """configs[2]: P3, k(x) inner(gradt(u), grad(v)) on m=87 (3 951 018 tets): k = expr("1+x*y+z^2") (order 6, 24 points)
+    and k = idv(P1 field) (order 5, 14 points) -- heat-toolbox style (toolboxes/feel/feelmodels/heat/heatassembly.hpp:69-86)"""
+    from feelpp_b200 import idv, inner
+    if coeff == "expr":
+        prog = fpp.GinacProgram(K_EXPR)
+        mk = lambda Xh, mesh: expr(K_EXPR) * inner(gradt(fpp.Element(Xh)), grad(fpp.Element(Xh)))
+        co = lambda mesh: orc.Coeff(kind=orc.COEFF_EXPR, ops=prog.ops, consts=prog.consts)
+        quad = orc.quad_order_form2(orc.STIFFNESS, 3, 2)
+    else:
+        def mk(Xh, mesh):
+            Kh, kv = _k_field(mesh)
+            return idv(fpp.Element(Kh, kv)) * inner(gradt(fpp.Element(Xh)), grad(fpp.Element(Xh)))
+
+        def co(mesh):
+            Kh, kv = _k_field(mesh)
+            return orc.Coeff(kind=orc.COEFF_FIELD, field_order=1, field_l2g=Kh.l2g, field_values=kv)
+        quad = orc.quad_order_form2(orc.STIFFNESS, 3, 1)
+    _fullsize_form(engine, 3, 1, 87, mk, orc.STIFFNESS, co, quad, "P3 k*stiffness (%s) m=87" % coeff, _rows_sum_to_zero)
+
+
+def test_full_size_config4_p2_vector_elasticity(engine):
+    """configs[3] per-GPU share: P2 vector elasticity, E=1e8, nu=0.25 (benchmarks/ATTIC/perf/assembly.cpp:86-89), m=70
+    (2 058 000 tets, 8 x that on 8 GPUs = m=139); rigid translations are in the kernel of the operator"""
+    from feelpp_b200 import Id, inner, sym, trace
+    E, nu = 1e8, 0.25
+    lam, mu = E * nu / ((1 + nu) * (1 - 2 * nu)), E / (2 * (1 + nu))
+
+    def mk(Xh, mesh):
+        u = v = fpp.Element(Xh)
+        return inner(lam * trace(sym(gradt(u))) * Id() + 2 * mu * sym(gradt(u)), grad(v))
+
+    def inv(a, Xh, vals, ia):
+        rabs = row_abs_sums(vals, ia)
+        for c in range(3):
+            t = np.zeros(Xh.nDof())
+            t[c::3] = 1.0
+            assert (np.abs(a.multVector(t)) <= 1e-12 * rabs).all(), "a rigid translation is not in the kernel"
+
+    _fullsize_form(engine, 2, 3, 70, mk, orc.ELASTICITY, lambda mesh: orc.Coeff(lam=lam, mu=mu),
+                   orc.quad_order_form2(orc.ELASTICITY, 2), "P2v elasticity m=70", inv)
