@@ -24,11 +24,36 @@ $(LIB)/eplan_build.o: $(CSRC)/eplan_build.cpp $(CSRC)/eplan.h
 $(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o $(LIB)/kernels_on.o $(LIB)/kernels_graph.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart
 
+# METIS 5.1.0 as vendored by the reference (feelpp/contrib/metis: the partitioner Feel++ itself uses,
+# feelpartition/partitionermetis_impl.hpp).  Its C sources are compiled where they lie under /root/reference into a static
+# archive (a built artefact like the .so files: git-ignored, it travels to the GPU box; no source is copied).  Where the
+# reference tree is absent (the GPU box) the archive built here is used as it is; without either, the host mirror is
+# built without METIS and the harness partitions by coordinate bisection.
+REF_METIS ?= /root/reference/feelpp/contrib/metis
+METIS_A := $(LIB)/libfeelmetis.a
+ifneq ($(wildcard $(REF_METIS)/libmetis/pmetis.c),)
+METIS_SRC := $(wildcard $(REF_METIS)/GKlib/*.c) $(wildcard $(REF_METIS)/libmetis/*.c)
+$(METIS_A): $(METIS_SRC)
+	@mkdir -p $(LIB)/metis_obj
+	@for f in $(METIS_SRC); do echo "gcc -O2 -fPIC -DLINUX -D_FILE_OFFSET_BITS=64 -std=c99 -fno-strict-aliasing -DNDEBUG -DNDEBUG2 -DHAVE_EXECINFO_H -DHAVE_GETLINE -w -I$(REF_METIS)/GKlib -I$(REF_METIS)/include -I$(REF_METIS)/libmetis -c $$f -o $(LIB)/metis_obj/`basename $$(dirname $$f)`_`basename $$f .c`.o"; done | xargs -P 8 -I CMD sh -c CMD
+	rm -f $@ && ar rcs $@ $(LIB)/metis_obj/*.o
+HAVE_METIS := 1
+else ifneq ($(wildcard $(METIS_A)),)
+HAVE_METIS := 1
+endif
+ifeq ($(HAVE_METIS),1)
+METIS_LINK := $(METIS_A)
+METIS_DEF :=
+else
+METIS_LINK :=
+METIS_DEF := -DFEELHOST_NO_METIS
+endif
+
 HOSTSRC := $(wildcard feelpp_b200/host/*.cpp)
 HOSTHDR := $(wildcard feelpp_b200/host/*.hpp) include/feelgpu.h include/feelgpu_quadrature_tables.h
-$(LIB)/libfeelhost.so: $(HOSTSRC) $(HOSTHDR)
+$(LIB)/libfeelhost.so: $(HOSTSRC) $(HOSTHDR) $(METIS_LINK)
 	@mkdir -p $(LIB)
-	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread -shared -Iinclude -o $@ $(HOSTSRC)
+	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread -shared -Iinclude $(METIS_DEF) -o $@ $(HOSTSRC) $(METIS_LINK) -lm
 
 oracle:
 	$(MAKE) -C oracle

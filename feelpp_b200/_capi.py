@@ -136,6 +136,7 @@ def host():
             raise ImportError("feelpp_b200: %s is missing -- run `make`" % path)
         lib = C.CDLL(path)
         lib.feelhost_last_error.restype = C.c_char_p
+        lib.feelhost_partition_last_error.restype = C.c_char_p
         lib.feelhost_unit_cube_sizes.argtypes = [C.c_int, c_i64p, c_i64p]
         lib.feelhost_unit_cube.argtypes = [C.c_int, C.c_double, C.c_int, c_dblp, c_i32p]
         lib.feelhost_boundary_faces.argtypes = [C.c_int64, C.c_int64, c_i32p, c_i32p, c_i32p, c_i64p]
@@ -158,6 +159,9 @@ def host():
                                             C.POINTER(C.c_int)]
         lib.feelhost_csr_select_remap_sort.argtypes = [C.c_int64, C.c_int64, c_i64p, c_i64p, c_i64p, c_i64p, c_i64p,
                                                        c_i64p, c_i64p, c_i64p]
+        lib.feelhost_dual_graph.argtypes = [C.c_int64, C.c_int64, c_i32p, c_i32p, c_i32p]
+        if hasattr(lib, "feelhost_partition_metis"):      # absent when the host mirror was built without METIS
+            lib.feelhost_partition_metis.argtypes = [C.c_int64, C.c_int64, c_i32p, C.c_int, C.c_int, c_i32p]
         _host = lib
     return _host
 
@@ -170,7 +174,8 @@ def check(rc, ctx=None):
 
 def hcheck(rc):
     if rc != 0:
-        raise RuntimeError("feelhost: " + host().feelhost_last_error().decode())
+        msg = host().feelhost_last_error().decode() or host().feelhost_partition_last_error().decode()
+        raise RuntimeError("feelhost: " + msg)
 
 
 def ptr(a, typ):

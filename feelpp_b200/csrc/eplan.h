@@ -41,7 +41,8 @@
 #define EPLAN_IDX_SHIFT 12          // unit word: bits 0-8 visit slot, 4-bit S indices from bit 12 (index k at 12 + 4k): with the S
                                    // array on a 64 KB boundary of shared memory, (w >> 4k) & 0xF000 | base is the address of load k
 #define EPLAN_PADRES 16            // row-block slots the packing pass holds back for phase pads (see eplan_build.cpp)
-#define EPLAN_MAXREMOTE 8          // peers a rank's ghost rows can belong to
+#define EPLAN_MAXREMOTE 16         // owners a rank's ghost rows can belong to (one node: up to 7; room for more)
+#define EPLAN_REMOTE_FLAG (int64_t(1) << 62)   // row-table base of a ghost row that lands in an owner's buffer
 #ifndef EPLAN_NSUB
 #define EPLAN_NSUB 1               // short chunks run under one header: measured slower on B200 (coarser hand-out, deeper word stream); kept at 1
 #endif
@@ -124,11 +125,14 @@ struct EPlan {                   // device mirror
     EPlanChunk* d_chunks = nullptr;
     uint32_t* d_blob = nullptr;
     EPlanRow* d_rows = nullptr;
-    // ghost rows written straight into their owners' memory (feelgpu_pattern_set_remote)
+    // ghost rows written straight into their owners' memory (feelgpu_eplan_set_remote): the row-table entries of the ghost
+    // rows carry (neighbour, offset) instead of a CSR offset: base = EPLAN_REMOTE_FLAG | neighbour << 56 | offset
     int nremote = 0;
     bool remote_fresh = true;    // no assembly has written the current landing buffers yet: the first one stores, later ones may add
-    int64_t remote_lo[EPLAN_MAXREMOTE], remote_hi[EPLAN_MAXREMOTE];
-    double* remote_ptr[EPLAN_MAXREMOTE];
+    int remote_epoch = 0;
+    double* remote_ptr[2][EPLAN_MAXREMOTE];
+    int64_t nrowent = 0;         // entries of d_rows
+    EPlanRow* d_rows_local = nullptr;   // the row table as built (local CSR offsets), kept to patch from
     int* d_sched = nullptr;      // [2] patch counter and exit counter of the persistent kernel (zero between launches)
     int64_t bytes = 0;
     int64_t ntasks = 0, niters = 0, niters_padded = 0, nvisits = 0, nouts = 0;

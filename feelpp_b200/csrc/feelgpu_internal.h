@@ -21,6 +21,10 @@ struct feelgpu_context_s {
     int* d_flag = nullptr;       // device error flag (slot-map build)
     struct TableEntry { std::vector<char> host; void* dev; };
     std::vector<TableEntry> table_cache;   // parameter blocks + reference tables already on the device
+    // multi-GPU (exchange.cu): the NCCL communicator of feelgpu_comm_init (ncclComm_t kept opaque here)
+    void* comm = nullptr;
+    int rank = 0, nranks = 1;
+    int* d_barrier = nullptr;    // the word all-reduced by close() as a completion barrier
 };
 
 struct feelgpu_mesh_s {
@@ -44,6 +48,7 @@ struct feelgpu_space_s {
     int32_t* d_l2g = nullptr;    // [nElt][nd]
     int64_t* d_p2c = nullptr;    // process -> cluster ids, or null (identity)
     std::vector<int32_t> h_l2g;  // host copy for the plan builder
+    std::vector<int64_t> h_p2c;  // host copy (ghost rows name their owner-side row by cluster id)
 };
 
 struct RowPlan;  // kernels_rowplan.cu
@@ -65,6 +70,10 @@ struct feelgpu_pattern_s {
     std::string plan_note;       // why no owner-computes plan exists (if none)
     EPlan* eplan = nullptr;
     std::string eplan_note;
+    // multi-GPU: host copies of what the graph exchange ships (interface-sized) and the exchange itself
+    std::vector<int64_t> h_ia;        // [nRows+1]
+    std::vector<int64_t> h_ja_tail;   // columns of the ghost rows: ja[ia[nDofOwned] .. nnz)
+    struct feelgpu_exchange_s* exchange = nullptr;
 };
 
 // parameter block copied to the device per assemble call
@@ -121,3 +130,13 @@ int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, cons
                                int accumulate, double* a, cudaStream_t s);
 bool feelgpu_eplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
 int feelgpu_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10]);
+// ghost rows of the plan go to landing buffers in their owners' memory: per ghost dof row (local row nDofOwned + g) the
+// neighbour index and the offset (in doubles) inside that neighbour's landing buffer; ptr[epoch][neighbour] = the buffers.
+// n = 0 restores local stores.
+int feelgpu_eplan_set_remote(feelgpu_pattern_t pat, int n, const int32_t* h_ghost_nb, const int64_t* h_ghost_off,
+                             double* const* ptr_epoch0, double* const* ptr_epoch1);
+void feelgpu_eplan_remote_epoch(feelgpu_pattern_t pat, int epoch);   // which set the next launches write; the set counts as empty
+void feelgpu_eplan_remote_fresh(feelgpu_pattern_t pat);              // the current set counts as empty again ('=' on the form)
+// ---- exchange.cu ----
+void feelgpu_exchange_note_assembly(feelgpu_pattern_t pat, bool through_eplan, int accumulate, double* a, cudaStream_t s);
+void feelgpu_exchange_detach(feelgpu_pattern_t pat);

@@ -1,18 +1,23 @@
 """Domain decomposition of the assembly: one process per GPU, element partition + owned row block + ghost rows.
 
-Mirrors what the reference does in MPI mode:
+Host-side mirror of what the reference's DofTable / DataMap / GraphCSR hold in MPI mode -- the
+inputs a Feel++ adapter flattens into the C ABI:
   * every rank assembles its active elements only (feelmesh/filters.hpp:201);
-  * a dof is owned by the lowest rank that shares it (feeldiscr/doftablempi.hpp:138-200); local numbering = owned dofs
-    first, ghosts after (feeldiscr/doftable.hpp:1975-2030); global-cluster numbering = rank-contiguous blocks
-    (feelalg/datamap.hpp:305-347);
+  * the local DofTable is built by first touch over the ACTIVE elements in local element order (feeldiscr/doftable.hpp
+    :1802-1940); a dof is a ghost when a lower rank shares its entity (feeldiscr/doftablempi.hpp:138-200, :548); the
+    local numbering is then reordered "active dofs before, ghost dofs after", each group keeping its first-touch order
+    (feeldiscr/doftable.hpp:1975-1992) -- so the ghosts of one owner are NOT contiguous;
+  * global-cluster numbering = rank-contiguous blocks, active dofs numbered in their local order
+    (feeldiscr/doftablempi.hpp:593-636, feelalg/datamap.hpp:305-347);
   * the graph of the owned rows is complete (ghost rows are shipped to their owner in GraphCSR::close,
     feelalg/graphcsr.cpp:800-951); the values assembled into ghost rows travel once per assembly
-    (MatAssemblyBegin/End, feelalg/matrixpetsc.cpp:750-752) -- here: values only, NCCL send/recv, then a scatter-add
-    through slot lists precomputed from the graph exchange.
+    (MatAssemblyBegin/End, feelalg/matrixpetsc.cpp:750-752).
 
-The partition itself is an input (Feel++ gets it from METIS, feelpartition/partitionermetis_impl.hpp:42-316); the
-harness uses recursive coordinate bisection of the element centroids.  Setup communication goes through
-torch.distributed object collectives (any backend); the per-assembly exchange is P2P on tensors (NCCL on GPUs).
+The partition itself is an input: METIS on the face-adjacency graph as Feel++ does it
+(feelpartition/partitionermetis_impl.hpp:118-253; vendored sources compiled into libfeelhost.so), or, for tests and
+comparison, coordinate bisection / seeds grown breadth-first.  Setup communication of this harness goes through
+torch.distributed object collectives (any backend); the engine's own exchange (feelgpu_exchange_create, NCCL) takes the
+ghost owners and cluster ids computed here, exactly what DataMap gives an adapter.
 """
 import ctypes as C
 
@@ -22,9 +27,11 @@ from . import _capi as capi
 from . import hostmirror as hm
 from ._capi import c_i32p, c_i64p, hcheck, ptr
 
-E2P = np.array([[1, 2], [2, 0], [0, 1], [0, 3], [1, 3], [2, 3]])
+E2P = np.array([[1, 2], [2, 0], [0, 1], [0, 3], [1, 3], [2, 3]])      # feelmesh/simplexordering.hpp:283-291
+F2P = np.array([[1, 2, 3], [0, 2, 3], [0, 1, 3], [0, 1, 2]])          # :341-347
 
 
+# ---- partitioners ----------------------------------------------------------------------------------------------------
 def partition_rcb(mesh, nparts):
     """recursive coordinate bisection of the element centroids into nparts (power of two or not) balanced parts"""
     cent = [sum(mesh.xyz[mesh.conn[:, v], c].astype(np.float32) for v in range(4)) for c in range(3)]
@@ -46,15 +53,98 @@ def partition_rcb(mesh, nparts):
     return part
 
 
+def face_adjacency(mesh):
+    """dual graph of the mesh by faces (the graph Feel++ hands to METIS, partitionermetis_impl.hpp:118-186):
+    (xadj[nElt+1], adjncy) int32"""
+    h = capi.host()
+    ne = mesh.numElements()
+    xadj = np.empty(ne + 1, dtype=np.int32)
+    adj = np.empty(4 * ne, dtype=np.int32)
+    hcheck(h.feelhost_dual_graph(mesh.numPoints(), ne, ptr(mesh.conn, c_i32p), ptr(xadj, c_i32p), ptr(adj, c_i32p)))
+    return xadj, adj[:xadj[-1]]
+
+
+def partition_metis(mesh, nparts, seed=None):
+    """Feel++'s partitioner (feelpartition/partitionermetis_impl.hpp:118-253): METIS 5.1.0 on the face-adjacency graph,
+    vertex weight = points per element (:133), recursive bisection for nparts <= 8, k-way above (:227-239)"""
+    h = capi.host()
+    ne = mesh.numElements()
+    part = np.zeros(ne, dtype=np.int32)
+    if nparts > 1:
+        hcheck(h.feelhost_partition_metis(mesh.numPoints(), ne, ptr(mesh.conn, c_i32p), int(nparts),
+                                          -1 if seed is None else int(seed), ptr(part, c_i32p)))
+    return part
+
+
+def partition_bfs(mesh, nparts, seed=0):
+    """irregular partition for tests: nparts random seed elements grown breadth-first over the face-adjacency graph,
+    unequal sizes, ranks with three and more neighbours"""
+    xadj, adj = face_adjacency(mesh)
+    ne = mesh.numElements()
+    rng = np.random.default_rng(seed)
+    part = np.full(ne, -1, dtype=np.int32)
+    fronts = [[int(s)] for s in rng.choice(ne, nparts, replace=False)]
+    for q, f in enumerate(fronts):
+        part[f[0]] = q
+    speed = 1 + rng.integers(0, 3, nparts)          # unequal growth -> unequal sizes
+    left = ne - nparts
+    while left > 0:
+        moved = False
+        for q in range(nparts):
+            for _ in range(int(speed[q])):
+                nxt = []
+                for e in fronts[q]:
+                    for nb in adj[xadj[e]:xadj[e + 1]]:
+                        if part[nb] < 0:
+                            part[nb] = q
+                            nxt.append(int(nb))
+                            left -= 1
+                if nxt:
+                    moved = True
+                    fronts[q] = nxt
+        if not moved:                               # disconnected leftovers
+            part[part < 0] = 0
+            break
+    return part
+
+
+def partition(mesh, nparts, method="auto"):
+    """(part, description): METIS when libfeelhost.so carries it (the reference's choice), else coordinate bisection"""
+    if method in ("auto", "metis"):
+        if hasattr(capi.host(), "feelhost_partition_metis"):
+            return partition_metis(mesh, nparts), ("METIS %s element partition of the face-adjacency graph "
+                                                   "(partitionermetis_impl.hpp:118-253)"
+                                                   % ("recursive-bisection" if nparts <= 8 else "k-way"))
+        if method == "metis":
+            raise RuntimeError("libfeelhost.so was built without METIS")
+    return partition_rcb(mesh, nparts), "recursive coordinate bisection element partition"
+
+
+# ---- geometric identity of the nodes ---------------------------------------------------------------------------------
 def node_keys(conn, order, npts):
-    """global identity of every local node of every element: vertices by point id, edge nodes by their end points"""
-    if order > 2:
-        raise NotImplementedError("the distributed harness covers Lagrange orders 1 and 2")
-    conn = conn.astype(np.int64)
+    """global identity of every local node of every element, [nElt][n] int64: vertices by point id, edge nodes by their end
+    points and their rank along the edge counted from the lower point id, face nodes by the sorted point triple.  Equal
+    keys <=> the same Lagrange node, whatever the rank, the element or the local numbering."""
+    conn = np.asarray(conn).astype(np.int64)
     keys = [conn]
-    if order == 2:
+    npe = order - 1
+    if order >= 2:
         a, b = conn[:, E2P[:, 0]], conn[:, E2P[:, 1]]
-        keys.append(npts + np.minimum(a, b) * npts + np.maximum(a, b))
+        base = npts + (np.minimum(a, b) * npts + np.maximum(a, b)) * npe
+        if npe == 1:
+            keys.append(base)
+        else:
+            # local dof 4 + npe*e + s is the s-th node from the edge's first local vertex (simplexordering.hpp:306-314)
+            fwd = (a < b)[:, :, None]
+            s = np.arange(npe)[None, None, :]
+            keys.append((base[:, :, None] + np.where(fwd, s, npe - 1 - s)).reshape(conn.shape[0], 6 * npe))
+    if order >= 3:
+        if order > 3:
+            raise NotImplementedError("node keys: Lagrange orders 1 to 3")
+        if npts >= (1 << 20):
+            raise NotImplementedError("node keys of face dofs: more than 2^20 points")
+        f = np.sort(conn[:, F2P], axis=2)
+        keys.append(npts + 2 * npts * npts * npe + (f[:, :, 0] * npts + f[:, :, 1]) * npts + f[:, :, 2])
     return np.concatenate(keys, axis=1)
 
 
@@ -84,7 +174,7 @@ class LocalProblem:
         conn = mesh.conn
         part = np.asarray(part, dtype=np.int32)
         mine = np.flatnonzero(part == rank)
-        # ---- extended element set: my elements + every element sharing a vertex with them ----
+        # ---- extended element set: my elements + every element sharing a vertex with them (the ghost layer) ----
         vmask = np.zeros(npts, dtype=bool)
         vmask[conn[mine]] = True
         ext = np.flatnonzero(vmask[conn].any(axis=1))
@@ -101,27 +191,39 @@ class LocalProblem:
         owner = np.full(nnode, P, dtype=np.int32)
         for q in range(P - 1, -1, -1):                       # descending: the lowest rank sharing a node wins
             owner[L[part_ext == q]] = q
-        local = np.zeros(nnode, dtype=bool)
-        local[L[is_mine]] = True
-        owned = local & (owner == rank)
-        ghost = local & (owner != rank)
-        owned_ids = np.flatnonzero(owned)
-        ghost_ids = np.flatnonzero(ghost)
-        ghost_ids = ghost_ids[np.lexsort((keys[ghost_ids], owner[ghost_ids]))]   # grouped by owner: contiguous sends
-        self.nOwnedNodes, self.nGhostNodes = len(owned_ids), len(ghost_ids)
+        # ---- the local DofTable: first touch over MY elements in local element order (doftable.hpp:1802-1940) ----
+        self.elements = mine
+        self.mesh = hm.Mesh(mesh.xyz[pts_ext], conn_ext[is_mine])
+        self.point_ids = pts_ext                             # global point id of every local point
+        Xl = hm.FunctionSpace(self.mesh, order, 1)
+        Ll = Xl.l2g.astype(np.int64)                         # [nMine][n] first-touch ids
+        nloc = Xl.nDof()
+        ext_of_ft = np.empty(nloc, dtype=np.int64)
+        ext_of_ft[Ll] = L[is_mine]
+        ghost_ft = owner[ext_of_ft] != rank                  # a lower rank shares the entity (doftablempi.hpp:548)
+        # active dofs before, ghost dofs after, each group in first-touch order (doftable.hpp:1975-1992)
+        order_ft = np.concatenate([np.flatnonzero(~ghost_ft), np.flatnonzero(ghost_ft)])
+        loc_nodes = ext_of_ft[order_ft]                      # ext node id of every local node, new local order
+        self.nOwnedNodes = int((~ghost_ft).sum())
+        self.nGhostNodes = nloc - self.nOwnedNodes
+        owned_ids, ghost_ids = loc_nodes[:self.nOwnedNodes], loc_nodes[self.nOwnedNodes:]
+        owned = np.zeros(nnode, dtype=bool)
+        owned[owned_ids] = True
         counts = comm.allgather(self.nOwnedNodes)
         first = np.concatenate([[0], np.cumsum(counts)])
         self.firstNode, self.nGlobalNodes = int(first[rank]), int(first[-1])
-        # ---- cluster ids: mine are known, the others come from their owners ----
+        self.first_nodes = first.astype(np.int64)            # firstDofGlobalClusterWorld / ncomp
+        # ---- cluster ids: the active dofs in their local order (doftablempi.hpp:623-635), ghosts from their owners ----
         cluster = np.full(nnode, -1, dtype=np.int64)
         cluster[owned_ids] = first[rank] + np.arange(len(owned_ids))
         # owners publish the nodes of their interface elements (elements with a vertex shared with another rank)
-        vbits = np.zeros(npts, dtype=np.uint64)
+        touched = np.zeros(npts, dtype=bool)
+        shared_v = np.zeros(npts, dtype=bool)
         for q in range(P):
             seen = np.zeros(npts, dtype=bool)
             seen[conn[part == q]] = True
-            vbits[seen] |= np.uint64(1) << np.uint64(q % 64)
-        shared_v = (vbits & (vbits - np.uint64(1))) != 0      # touched by elements of more than one rank
+            shared_v |= seen & touched                       # touched by elements of more than one rank
+            touched |= seen
         iface = is_mine & shared_v[conn[ext]].any(axis=1)
         pub = np.unique(L[iface])
         pub = pub[owned[pub]]
@@ -136,22 +238,21 @@ class LocalProblem:
         pos[pos >= len(allk)] = 0
         hit = allk[pos] == keys[need] if len(allk) else np.zeros(len(need), dtype=bool)
         cluster[need[hit]] = allc[pos[hit]]
-        self.cluster_of_ext = cluster
-        # ---- local numbering: owned first, ghosts after ----
-        loc_nodes = np.concatenate([owned_ids, ghost_ids])
+        self.cluster_of_ext, self.key_of_ext = cluster, keys
+        self.ext_elements, self.ext_l2g_nodes, self.ext_mesh = ext, L, mesh_ext
+        # ---- local numbering ----
         newidx = np.full(nnode, -1, dtype=np.int64)
-        newidx[loc_nodes] = np.arange(len(loc_nodes))
-        nloc = len(loc_nodes)
+        newidx[loc_nodes] = np.arange(nloc)
         if (cluster[loc_nodes] < 0).any():
             raise RuntimeError("distributed setup: a local node has no global-cluster id")
         Lm = newidx[L[is_mine]]                              # [nMine][n] local node ids
         self.l2g = (Lm[:, None, :] * ncomp + np.arange(ncomp)[None, :, None]).reshape(len(mine), ncomp * n).astype(np.int32)
         self.nDofOwned, self.nDofWithGhost = len(owned_ids) * ncomp, nloc * ncomp
         self.p2c = (cluster[loc_nodes][:, None] * ncomp + np.arange(ncomp)[None, :]).reshape(-1).astype(np.int64)
+        self.node_keys_local = keys[loc_nodes]               # geometric identity of every local node (tests, parity)
         self.firstDof, self.nGlobalDof = self.firstNode * ncomp, self.nGlobalNodes * ncomp
-        self.elements = mine
-        self.mesh = hm.Mesh(mesh.xyz[pts_ext], conn_ext[is_mine])
-        self.ghost_owner = owner[ghost_ids]
+        self.ghost_owner = owner[ghost_ids].astype(np.int32)  # per ghost node, local (first-touch) order
+        self.ghost_owner_dof = np.repeat(self.ghost_owner, ncomp).astype(np.int32)
         # ---- local CSR rows: complete pattern for owned rows, local-elements pattern for ghost rows ----
         ia, ja = self._local_graph(h, L, is_mine, nnode, loc_nodes, cluster, n)
         self.ia, self.ja = ia, ja
@@ -190,23 +291,25 @@ class LocalProblem:
 
     # ------------------------------------------------------------------------------------------------------------
     def _exchange_plan(self):
-        """graph exchange (GraphCSR::close analogue): tell every owner which (row, columns) my ghost rows carry, so
-        that it can precompute the CSR slots of the values it will receive at every assembly"""
-        comm, ncomp = self.comm, self.ncomp
+        """graph exchange (GraphCSR::close analogue, feelalg/graphcsr.cpp:800-951): tell every owner which (row, columns)
+        my ghost rows carry, so that it can precompute the CSR slots of the values it will receive at every assembly.
+        Host-side restatement used by the CPU (gloo) tests and the parity check; on GPUs the engine does the same
+        exchange itself over NCCL (feelgpu_exchange_create)."""
+        comm = self.comm
         rank = comm.rank
         nO = self.nDofOwned
         ia, ja = self.ia, self.ja
-        gowner = np.repeat(self.ghost_owner, ncomp)          # owner of every ghost dof row, grouped by owner
-        self.send = []                                        # (dest, value offset, count)
+        gowner = self.ghost_owner_dof                         # owner of every ghost dof row, local order (interleaved)
+        self.send = []                                        # (dest, ghost rows (local ids), value indices)
         msg = {}
         for q in np.unique(gowner):
             rows = nO + np.flatnonzero(gowner == q)
-            r0, r1 = rows[0], rows[-1] + 1                    # contiguous by construction
-            off, cnt = int(ia[r0]), int(ia[r1] - ia[r0])
-            self.send.append((int(q), off, cnt))
-            msg[int(q)] = (self.p2c[r0:r1].copy(), np.diff(ia[r0:r1 + 1]), ja[ia[r0]:ia[r1]].copy())
+            lens = ia[rows + 1] - ia[rows]
+            idx = np.repeat(ia[rows] - np.concatenate([[0], np.cumsum(lens)[:-1]]), lens) + np.arange(int(lens.sum()))
+            self.send.append((int(q), rows, idx))
+            msg[int(q)] = (self.p2c[rows].copy(), lens, ja[idx].copy())
         allmsg = comm.allgather(msg)
-        self.recv = []                                        # (source, slots int64[count])
+        self.recv = []                                        # (source, owned rows (local ids), slots int64[count])
         for p, m in enumerate(allmsg):
             if p == rank or rank not in m:
                 continue
@@ -223,7 +326,7 @@ class LocalProblem:
                     raise RuntimeError("distributed setup: a ghost-row entry is not in the owner's graph")
                 slots[k:k + ln] = ia[r] + pos
                 k += ln
-            self.recv.append((p, slots))
+            self.recv.append((p, lrow.astype(np.int64), slots))
 
     def nnz_local(self):
         return int(self.ia[-1])
@@ -231,15 +334,21 @@ class LocalProblem:
     def nnz_owned(self):
         return int(self.ia[self.nDofOwned])
 
+    def send_values(self):
+        return int(self.ia[-1] - self.ia[self.nDofOwned])
+
+    def num_neighbours(self):
+        return len({q for q, _, _ in self.send} | {p for p, _, _ in self.recv})
+
 
 def exchange_numpy(lp, a, dist):
-    """CPU/gloo form of close(): used by the world_size-2 tests; a is the rank's full local value array (numpy)"""
+    """CPU/gloo form of MatAssemblyBegin/End: a is the rank's full local value array (numpy)"""
     import torch
     ops, bufs = [], []
-    for q, off, cnt in lp.send:
-        t = torch.from_numpy(a[off:off + cnt].copy())
+    for q, _rows, idx in lp.send:
+        t = torch.from_numpy(a[idx].copy())
         ops.append(dist.P2POp(dist.isend, t, q))
-    for p, slots in lp.recv:
+    for p, _rows, slots in lp.recv:
         t = torch.empty(len(slots), dtype=torch.float64)
         bufs.append((t, slots))
         ops.append(dist.P2POp(dist.irecv, t, p))
@@ -249,3 +358,50 @@ def exchange_numpy(lp, a, dist):
     for t, slots in bufs:
         np.add.at(a, slots, t.numpy())
     return a
+
+
+def exchange_vector_numpy(lp, b, dist, ghost_update=True):
+    """CPU/gloo form of VectorPetscMPI::close (feelalg/vectorpetsc.cpp:1683-1693): VecAssemblyBegin/End adds the ghost
+    entries to their owners, then VecGhostUpdate (:1667-1676) refreshes the ghost copies from the owners; b is the rank's
+    local vector [nDofWithGhost]"""
+    import torch
+    ops, bufs = [], []
+    for q, rows, _ in lp.send:
+        ops.append(dist.P2POp(dist.isend, torch.from_numpy(b[rows].copy()), q))
+    for p, lrow, _ in lp.recv:
+        t = torch.empty(len(lrow), dtype=torch.float64)
+        bufs.append((t, lrow))
+        ops.append(dist.P2POp(dist.irecv, t, p))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    for t, lrow in bufs:
+        np.add.at(b, lrow, t.numpy())
+    if ghost_update:
+        ops, bufs = [], []
+        for p, lrow, _ in lp.recv:
+            ops.append(dist.P2POp(dist.isend, torch.from_numpy(b[lrow].copy()), p))
+        for q, rows, _ in lp.send:
+            t = torch.empty(len(rows), dtype=torch.float64)
+            bufs.append((t, rows))
+            ops.append(dist.P2POp(dist.irecv, t, q))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        for t, rows in bufs:
+            b[rows] = t.numpy()
+    return b
+
+
+# ---- gathering a distributed matrix in the sequential numbering (tests, bench parity) ----------------------------------
+def sequential_numbering_of_keys(mesh, order, Xh_seq):
+    """sorted (keys, sequential node id) of the sequential space on the global mesh: the permutation cluster -> sequential
+    goes through the geometric identity of the nodes"""
+    k = node_keys(mesh.conn, order, mesh.numPoints())
+    nodes = Xh_seq.l2g[:, :Xh_seq.n].astype(np.int64) // Xh_seq.ncomp
+    seq = np.empty(Xh_seq.nDof() // Xh_seq.ncomp, dtype=np.int64)
+    kk = np.empty_like(seq)
+    kk[nodes] = k
+    seq[:] = np.arange(len(seq))
+    srt = np.argsort(kk)
+    return kk[srt], seq[srt]
