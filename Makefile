@@ -21,8 +21,9 @@ $(LIB)/eplan_build.o: $(CSRC)/eplan_build.cpp $(CSRC)/eplan.h
 	@mkdir -p $(LIB)
 	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread $(EPLAN_DEFS) -c $< -o $@
 
-$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o $(LIB)/kernels_on.o $(LIB)/kernels_graph.o
-	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart
+# NCCL (exchange.cu) is bound with dlopen at feelgpu_comm_init, not linked: see the note at the top of exchange.cu
+$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o $(LIB)/kernels_on.o $(LIB)/kernels_graph.o $(LIB)/exchange.o
+	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart -ldl
 
 # METIS 5.1.0 as vendored by the reference (feelpp/contrib/metis: the partitioner Feel++ itself uses,
 # feelpartition/partitionermetis_impl.hpp).  Its C sources are compiled where they lie under /root/reference into a static

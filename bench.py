@@ -328,7 +328,17 @@ def gpu_arm(args):
         from feelpp_b200 import parallel as par, distributed as dd
         t0 = time.time()
         gmesh = fpp.unitCube(args.m_global, 0.15, args.shuffle)
-        part, part_name = par.partition(gmesh, world, args.partition)
+        # the partitioner runs on the master rank only and the result is broadcast, as in the reference
+        # (partitionermetis_impl.hpp:114-116 "Invoke METIS, but only on processor 0. Then broadcast")
+        tp = torch.zeros(gmesh.numElements(), dtype=torch.int32, device="cuda")
+        name_box = [None]
+        if rank == 0:
+            part, name_box[0] = par.partition(gmesh, world, args.partition)
+            tp.copy_(torch.from_numpy(part))
+        dist.broadcast(tp, src=0)
+        dist.broadcast_object_list(name_box, src=0)
+        part, part_name = tp.cpu().numpy(), name_box[0]
+        del tp
         t1 = time.time()
         lp = par.LocalProblem(gmesh, part, args.order, args.ncomp, par.Comm(rank, world, dist))
         t2 = time.time()
@@ -419,10 +429,10 @@ def gpu_arm(args):
     # ---- multi-GPU parity: every owned row after close(), against the invariant and the oracle ----
     parity = None
     if world > 1 and not args.no_parity:
-        from feelpp_b200 import parity_mp
+        import bench_parity
         step()
         barrier()
-        parity = parity_mp.check(args, lp, gmesh, a, dist, oracle_args(args, gmesh), quad_order(args))
+        parity = bench_parity.check(args, lp, gmesh, a, dist, oracle_args(args, gmesh), quad_order(args))
 
     # ---- end to end: host buffers, H2D of the coordinates + D2H of the CSR values inside the timed region ----
     e2e = None

@@ -85,11 +85,14 @@ GPU_SYMBOLS = {
     "feelgpu_faces_destroy": [C.c_void_p],
     "feelgpu_form1_assemble_faces": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form2_assemble_faces": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p],
-    "feelgpu_ipc_export": [C.c_void_p, C.c_void_p, C.c_char_p],
-    "feelgpu_ipc_open": [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)],
-    "feelgpu_ipc_close": [C.c_void_p, C.c_void_p],
-    "feelgpu_pattern_set_remote": [C.c_void_p, C.c_int, c_i64p, c_i64p, C.POINTER(C.c_void_p)],
-    "feelgpu_form2_uses_remote": [C.c_void_p, C.c_void_p, C.POINTER(C.c_int)],
+    "feelgpu_comm_unique_id": [C.c_char_p],
+    "feelgpu_comm_init": [C.c_void_p, C.c_char_p, C.c_int, C.c_int],
+    "feelgpu_comm_destroy": [C.c_void_p],
+    "feelgpu_exchange_create": [C.c_void_p, c_i32p, C.c_int64, C.c_int, C.POINTER(C.c_void_p)],
+    "feelgpu_exchange_destroy": [C.c_void_p],
+    "feelgpu_exchange_info": [C.c_void_p, c_i64p],
+    "feelgpu_form2_close": [C.c_void_p, C.c_void_p, C.c_void_p],
+    "feelgpu_form1_close": [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p],
     "feelgpu_launch_count": [C.c_void_p, c_i64p],
     "feelgpu_last_timing": [C.c_void_p, c_dblp],
     "feelgpu_set_timing": [C.c_void_p, C.c_int],

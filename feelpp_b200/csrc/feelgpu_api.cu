@@ -71,6 +71,7 @@ int feelgpu_context_destroy(feelgpu_context_t ctx)
     if (!ctx) return FEELGPU_ERR_ARG;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
+    feelgpu_comm_destroy(ctx);
     for (auto& e : ctx->table_cache) cudaFree(e.dev);
     for (int k = 0; k < 4; ++k)
         if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
@@ -224,6 +225,7 @@ int feelgpu_space_create(feelgpu_context_t ctx, feelgpu_mesh_t mesh, int order, 
     sp->nDofWithGhost = nWithGhost;
     sp->nDofOwned = nOwned;
     sp->h_l2g.assign(l2g, l2g + mesh->nElt * nd);
+    if (p2c) sp->h_p2c.assign(p2c, p2c + nWithGhost);
     cudaError_t err = cudaMalloc(&sp->d_l2g, sizeof(int32_t) * std::max<int64_t>(mesh->nElt * nd, 1));
     if (err == cudaSuccess) err = cudaMemcpy(sp->d_l2g, l2g, sizeof(int32_t) * mesh->nElt * nd, cudaMemcpyHostToDevice);
     if (err == cudaSuccess && p2c) {
@@ -276,6 +278,8 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     pat->nRows = nRows;
     pat->nnz = ia[nRows];
     pat->h_ia_owned_end = ia[std::min<int64_t>(test->nDofOwned, nRows)];
+    pat->h_ia.assign(ia, ia + nRows + 1);
+    if (test->nDofOwned < nRows) pat->h_ja_tail.assign(ja + pat->h_ia_owned_end, ja + ia[nRows]);
     const int n = test->n;
     const int64_t nElt = test->mesh->nElt;
     cudaError_t err = cudaMalloc(&pat->d_ia, sizeof(int64_t) * (nRows + 1));
@@ -360,6 +364,7 @@ int feelgpu_pattern_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
 int feelgpu_pattern_destroy(feelgpu_pattern_t pat)
 {
     if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_exchange_detach(pat);
     feelgpu_rowplan_destroy(pat);
     feelgpu_eplan_destroy(pat);
     if (pat->d_ia) cudaFree(pat->d_ia);
@@ -455,6 +460,7 @@ int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc
         ctx->last_error = "form2_assemble: the owner-computes plan does not cover this form/pattern";
         return FEELGPU_ERR_UNSUPPORTED;
     }
+    feelgpu_exchange_note_assembly(pat, algo == FEELGPU_ALGO_EPLAN, accumulate, a, s);   // multi-GPU: where the ghost rows go
     if (ctx->timing) cudaEventRecord(ctx->ev[0], s);
     if (algo == FEELGPU_ALGO_EPLAN) {
         if (ctx->timing) cudaEventRecord(ctx->ev[1], s);
@@ -469,16 +475,6 @@ int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc
     }
     if (ctx->timing) cudaEventRecord(ctx->ev[2], s);
     return rc;
-}
-
-int feelgpu_form2_uses_remote(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc, int* yes)
-{
-    if (!pat) return FEELGPU_ERR_ARG;
-    if (!desc || !yes) ARG_FAIL(pat->ctx, "form2_uses_remote: null argument");
-    const bool eplan = (desc->algorithm == FEELGPU_ALGO_AUTO || desc->algorithm == FEELGPU_ALGO_EPLAN) &&
-                       feelgpu_eplan_supports(pat, desc);
-    *yes = eplan && pat->eplan ? 1 : 0;   // (also on a rank without ghost rows: the answer must agree across ranks)
-    return FEELGPU_OK;
 }
 
 int feelgpu_form1_assemble(feelgpu_space_t sp, const feelgpu_form1_desc* desc, int accumulate, double* b, void* stream)
@@ -661,58 +657,6 @@ int feelgpu_form2_assemble_faces(feelgpu_pattern_t pat, feelgpu_faces_t fc, cons
     if ((rc = check_face_tables(ctx, desc->coeff, desc->tables))) return rc;
     if (!accumulate) CTX_CUDA(ctx, cudaMemsetAsync(a, 0, sizeof(double) * pat->nnz, s));
     return fc->n ? feelgpu_launch_form2_faces(pat, fc, hp, desc, a, s) : FEELGPU_OK;
-}
-
-int feelgpu_ipc_export(feelgpu_context_t ctx, void* device_ptr, unsigned char handle[64])
-{
-    if (!ctx) return FEELGPU_ERR_ARG;
-    if (!device_ptr || !handle) ARG_FAIL(ctx, "ipc_export: bad argument");
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
-    cudaIpcMemHandle_t h;
-    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
-    CTX_CUDA(ctx, cudaIpcGetMemHandle(&h, device_ptr));
-    std::memcpy(handle, &h, sizeof(h));
-    return FEELGPU_OK;
-}
-int feelgpu_ipc_open(feelgpu_context_t ctx, const unsigned char handle[64], void** device_ptr)
-{
-    if (!ctx) return FEELGPU_ERR_ARG;
-    if (!device_ptr || !handle) ARG_FAIL(ctx, "ipc_open: bad argument");
-    cudaIpcMemHandle_t h;
-    std::memcpy(&h, handle, sizeof(h));
-    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
-    CTX_CUDA(ctx, cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess));
-    return FEELGPU_OK;
-}
-int feelgpu_ipc_close(feelgpu_context_t ctx, void* device_ptr)
-{
-    if (!ctx) return FEELGPU_ERR_ARG;
-    CTX_CUDA(ctx, cudaIpcCloseMemHandle(device_ptr));
-    return FEELGPU_OK;
-}
-
-int feelgpu_pattern_set_remote(feelgpu_pattern_t pat, int n, const int64_t* lo, const int64_t* hi, void* const* target)
-{
-    if (!pat) return FEELGPU_ERR_ARG;
-    feelgpu_context_t ctx = pat->ctx;
-    if (n < 0 || n > EPLAN_MAXREMOTE || (n > 0 && (!lo || !hi || !target))) ARG_FAIL(ctx, "set_remote: bad argument");
-    if (n > 0 && !pat->eplan) {
-        ctx->last_error = "set_remote: the pattern has no entity plan (only that kernel writes to peer memory)";
-        return FEELGPU_ERR_UNSUPPORTED;
-    }
-    const int64_t tail = pat->test->nDofOwned < pat->nRows ? pat->h_ia_owned_end : pat->nnz;
-    for (int k = 0; k < n; ++k)
-        if (lo[k] < tail || hi[k] > pat->nnz || lo[k] > hi[k] || (k > 0 && lo[k] < hi[k - 1]) || !target[k])
-            ARG_FAIL(ctx, "set_remote: ranges must be ascending, disjoint and inside the ghost-row tail");
-    if (!pat->eplan) return FEELGPU_OK;
-    pat->eplan->nremote = n;
-    pat->eplan->remote_fresh = true;
-    for (int k = 0; k < n; ++k) {
-        pat->eplan->remote_lo[k] = lo[k];
-        pat->eplan->remote_hi[k] = hi[k];
-        pat->eplan->remote_ptr[k] = static_cast<double*>(target[k]);
-    }
-    return FEELGPU_OK;
 }
 
 int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr)

@@ -17,10 +17,10 @@ namespace {
 
 // out_o = sum_k coef[type][o][k] * (sum over the task's elements of the k-th loaded S entry)   (stiffness)
 // out_o = mass[type][o] * (sum over the task's elements of c J)                                  (mass)
-// value slots [lo, hi) of the CSR array live in another GPU's memory (ghost rows land directly in their owner's buffer)
+// ghost rows land directly in their owners' memory: the row-table base of such a row is EPLAN_REMOTE_FLAG | neighbour << 56 |
+// offset (in doubles) inside that neighbour's landing buffer ptr[neighbour]
 struct ERemote {
     int n, accumulate;
-    int64_t lo[EPLAN_MAXREMOTE], hi[EPLAN_MAXREMOTE];
     double* ptr[EPLAN_MAXREMOTE];
 };
 
@@ -365,17 +365,12 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
         // ---- phase C: the patch's row block goes to the CSR value array, every value once ----
         // a ghost row goes over NVLink into the buffer its owner exported (ranges are ordered: the first is the lowest)
         auto resolve = [&](int64_t base, int& acc) {
-            double* p = a + base;
             acc = accumulate;
-            if (rem.n > 0 && base >= rem.lo[0]) {
-#pragma unroll 1
-                for (int k = 0; k < rem.n; ++k)
-                    if (base >= rem.lo[k] && base < rem.hi[k]) {
-                        p = rem.ptr[k] + (base - rem.lo[k]);
-                        acc = rem.accumulate;
-                    }
+            if (base & EPLAN_REMOTE_FLAG) {
+                acc = rem.accumulate;
+                return rem.ptr[(base >> 56) & (EPLAN_MAXREMOTE - 1)] + (base & ((int64_t(1) << 56) - 1));
             }
-            return p;
+            return a + base;
         };
         if (NCOMP == 1) {
             // Scalar spaces: thread = row segment.  A segment that starts on the same 16-byte phase in the row block as in
@@ -592,6 +587,7 @@ int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     if (err == cudaSuccess) err = upload(&p->d_chunks, hp.chunks, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_blob, hp.blob, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_rows, hp.rows, p->bytes);
+    p->nrowent = (int64_t)hp.rows.size();
     if (err == cudaSuccess) err = cudaMalloc(&p->d_sched, 2 * sizeof(int));
     if (err == cudaSuccess) err = cudaMemset(p->d_sched, 0, 2 * sizeof(int));
     pat->eplan = p;
@@ -631,6 +627,7 @@ void feelgpu_eplan_destroy(feelgpu_pattern_t pat)
     cudaFree(p->d_chunks);
     cudaFree(p->d_blob);
     cudaFree(p->d_rows);
+    cudaFree(p->d_rows_local);
     cudaFree(p->d_sched);
     delete p;
     pat->eplan = nullptr;
@@ -714,11 +711,7 @@ int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     rem.n = p->nremote;
     rem.accumulate = accumulate && !p->remote_fresh;   // a landing buffer starts every epoch empty, whatever it holds
     p->remote_fresh = false;
-    for (int k = 0; k < EPLAN_MAXREMOTE; ++k) {
-        rem.lo[k] = k < p->nremote ? p->remote_lo[k] : 0;
-        rem.hi[k] = k < p->nremote ? p->remote_hi[k] : 0;
-        rem.ptr[k] = k < p->nremote ? p->remote_ptr[k] : nullptr;
-    }
+    for (int k = 0; k < EPLAN_MAXREMOTE; ++k) rem.ptr[k] = k < p->nremote ? p->remote_ptr[p->remote_epoch & 1][k] : nullptr;
     const size_t sh = eplan_smem_bytes(p, form);
     // persistent CTAs: EPLAN_MINB per SM, each runs every gridDim.x-th patch
     // stiffness: when the S array (behind the row block and the chunk headers) starts at shared address 0x10000 its load
@@ -753,6 +746,92 @@ int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     ctx->launches++;
     FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
     return FEELGPU_OK;
+}
+
+// ---- ghost rows into the owners' landing buffers --------------------------------------------------------------------------
+namespace {
+// every row-table entry of a ghost row (base at or behind tail0: one entry per node row, never merged) gets
+// EPLAN_REMOTE_FLAG | neighbour << 56 | offset; the dof row is found by its CSR offset
+__global__ void k_eplan_patch_rows(int64_t n, const EPlanRow* __restrict__ local, EPlanRow* __restrict__ rows, int64_t tail0,
+                                   const int64_t* __restrict__ ia, int64_t nOwned, int64_t nRows,
+                                   const int32_t* __restrict__ ghost_nb, const int64_t* __restrict__ ghost_off, int* __restrict__ flag)
+{
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
+        EPlanRow r = local[k];
+        if (ghost_nb && r.base >= tail0) {
+            int64_t lo = nOwned, hi = nRows;             // first row with ia[row] >= base (ghost rows are never empty)
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (ia[mid] < r.base) lo = mid + 1;
+                else hi = mid;
+            }
+            if (lo >= nRows || ia[lo] != r.base) atomicExch(flag, 1);
+            else r.base = EPLAN_REMOTE_FLAG | ((int64_t)ghost_nb[lo - nOwned] << 56) | ghost_off[lo - nOwned];
+        }
+        rows[k] = r;
+    }
+}
+} // namespace
+
+int feelgpu_eplan_set_remote(feelgpu_pattern_t pat, int n, const int32_t* h_ghost_nb, const int64_t* h_ghost_off,
+                             double* const* ptr0, double* const* ptr1)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    EPlan* p = pat->eplan;
+    if (!p) {
+        if (n == 0) return FEELGPU_OK;
+        ctx->last_error = "set_remote: the pattern has no entity plan (only that kernel writes to peer memory)";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    if (n < 0 || n > EPLAN_MAXREMOTE) { ctx->last_error = "set_remote: too many owners"; return FEELGPU_ERR_ARG; }
+    cudaStream_t s = ctx->stream;
+    const int64_t nO = pat->test->nDofOwned, nG = pat->nRows - nO;
+    if (!p->d_rows_local) {     // keep the table as built
+        FEELGPU_CHECK_CUDA(ctx, cudaMalloc(&p->d_rows_local, std::max<int64_t>(p->nrowent, 1) * sizeof(EPlanRow)));
+        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(p->d_rows_local, p->d_rows, p->nrowent * sizeof(EPlanRow), cudaMemcpyDeviceToDevice, s));
+    }
+    int32_t* d_nb = nullptr;
+    int64_t* d_off = nullptr;
+    if (n > 0 && nG > 0) {
+        FEELGPU_CHECK_CUDA(ctx, cudaMalloc(&d_nb, nG * sizeof(int32_t)));
+        FEELGPU_CHECK_CUDA(ctx, cudaMalloc(&d_off, nG * sizeof(int64_t)));
+        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(d_nb, h_ghost_nb, nG * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(d_off, h_ghost_off, nG * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+    }
+    int flag = 0;
+    if (p->nrowent > 0) {
+        FEELGPU_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), s));
+        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((p->nrowent + 255) / 256, (int64_t)ctx->sm_count * 8));
+        k_eplan_patch_rows<<<grid, 256, 0, s>>>(p->nrowent, p->d_rows_local, p->d_rows, pat->h_ia[nO], pat->d_ia, nO, pat->nRows,
+                                                d_nb, d_off, ctx->d_flag);
+        ctx->launches++;
+        FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(&flag, ctx->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    }
+    FEELGPU_CHECK_CUDA(ctx, cudaStreamSynchronize(s));
+    cudaFree(d_nb);
+    cudaFree(d_off);
+    if (flag) { ctx->last_error = "set_remote: a ghost row of the plan does not start at a CSR row"; return FEELGPU_ERR_ARG; }
+    p->nremote = (nG > 0) ? n : 0;
+    p->remote_fresh = true;
+    p->remote_epoch = 0;
+    for (int k = 0; k < EPLAN_MAXREMOTE; ++k) {
+        p->remote_ptr[0][k] = k < n && ptr0 ? ptr0[k] : nullptr;
+        p->remote_ptr[1][k] = k < n && ptr1 ? ptr1[k] : nullptr;
+    }
+    return FEELGPU_OK;
+}
+
+void feelgpu_eplan_remote_epoch(feelgpu_pattern_t pat, int epoch)
+{
+    if (!pat->eplan) return;
+    pat->eplan->remote_epoch = epoch;
+    pat->eplan->remote_fresh = true;
+}
+
+void feelgpu_eplan_remote_fresh(feelgpu_pattern_t pat)
+{
+    if (pat->eplan) pat->eplan->remote_fresh = true;
 }
 
 // ---- host-side view of the plan (include/feelgpu.h) ----------------------------------------------------------------

@@ -1,16 +1,33 @@
-"""Multi-GPU forms: one process per GPU, partition-local assembly + NCCL exchange of the ghost-row values.
+"""Multi-GPU forms: one process per GPU, partition-local assembly, close() through the engine's C ABI.
 
-torch is used for what it is here for: device memory (the value array is a torch tensor so that torch.distributed can
-send slices of it), streams and the NCCL communicator.  All kernels (assembly, owner-side scatter-add) are the engine's.
+Everything that happens per assembly -- where the ghost rows go, the NCCL exchange, the owner-side add -- lives in
+libfeelgpu.so (feelpp_b200/csrc/exchange.cu: feelgpu_comm_init, feelgpu_exchange_create, feelgpu_form2_close,
+feelgpu_form1_close); this module only flattens the host-side DofTable / DataMap mirror (parallel.LocalProblem) into those
+calls, as a Feel++ adapter would.  torch.distributed is used for what it is here for: shipping the 128-byte NCCL id at
+start-up (Feel++ would use its WorldComm) and the harness' own bookkeeping collectives.
 """
 import ctypes as C
 
 import numpy as np
 
 from . import hostmirror as hm
-from . import parallel as par
-from ._capi import check
-from .engine import ALGO_AUTO, BilinearForm
+from ._capi import c_i32p, c_i64p, check, ptr
+from .engine import ALGO_AUTO, BilinearForm, LinearForm
+
+
+def comm_init(engine, dist):
+    """feelgpu_comm_init on this rank's context (idempotent): rank 0 creates the NCCL id, everybody receives it"""
+    if getattr(engine, "_comm", False):
+        return
+    rank, world = dist.get_rank(), dist.get_world_size()
+    box = [None]
+    if rank == 0:
+        uid = C.create_string_buffer(128)
+        check(engine.lib.feelgpu_comm_unique_id(uid), None)
+        box[0] = uid.raw
+    dist.broadcast_object_list(box, src=0)
+    check(engine.lib.feelgpu_comm_init(engine.ctx, box[0], rank, world), engine.ctx)
+    engine._comm = True
 
 
 class LocalSpace:
@@ -38,98 +55,37 @@ class LocalSpace:
 
 
 class DistributedBilinearForm(BilinearForm):
-    """form2 on a LocalSpace; close() hands the ghost rows to their owners (MatAssemblyBegin/End analogue).
+    """form2 on a LocalSpace; close() hands the ghost rows to their owners (MatrixPetsc::close -> MatAssemblyBegin/End,
+    feelalg/matrixpetsc.cpp:726-760).  peer_memory=False keeps the ghost rows in the local tail and ships them with NCCL
+    send/recv (what forms outside the entity plan do anyway)."""
 
-    Two transports.  peer memory (default when every rank's pattern carries the entity plan): the owners export one
-    landing buffer per neighbour (CUDA IPC over NVLink/NVSwitch), the assembly kernel stores the ghost rows straight into
-    them while it runs, and close() is an NCCL barrier + the owner-side scatter-add; the buffers alternate between two
-    sets so that one barrier per close orders everything.  Otherwise, and for forms the entity plan does not cover, the
-    ghost rows are the tail of the local value array and close() ships it with NCCL send/recv."""
-
-    def __init__(self, Xh, engine, dist, algorithm=ALGO_AUTO, peer_memory=None):
+    def __init__(self, Xh, engine, dist, algorithm=ALGO_AUTO, peer_memory=None, pattern_flags=0):
         import os
         import torch
         self.torch, self.dist = torch, dist
-        super().__init__(Xh, Xh, engine, 0, algorithm)
+        comm_init(engine, dist)
+        super().__init__(Xh, Xh, engine, pattern_flags, algorithm)
         lp = Xh.lp
-        dev = self.t_values.device
-        self.recv = [(p, torch.from_numpy(slots).to(dev), torch.empty(len(slots), dtype=torch.float64, device=dev))
-                     for p, slots in lp.recv]
-        self.send = list(lp.send)
-        self.tail0 = int(self.ia[lp.nDofOwned])
-        self._tail_used = self._direct_used = False
-        self.peer = False
         if peer_memory is None:
             peer_memory = os.environ.get("FEELGPU_PEER_MEMORY", "1") != "0"
-        if peer_memory and dev.type == "cuda" and dist.get_world_size() > 1:
-            self._setup_peer()
+        self.ex = C.c_void_p()
+        go = np.ascontiguousarray(lp.ghost_owner_dof, dtype=np.int32)
+        check(engine.lib.feelgpu_exchange_create(self.pat, ptr(go, c_i32p) if len(go) else None, lp.firstDof,
+                                                 0 if peer_memory else 1, C.byref(self.ex)), engine.ctx)
+        self.peer = bool(self.exchange_info()["peer_memory"])
+
+    def exchange_info(self):
+        st = np.zeros(8, dtype=np.int64)
+        check(self.eng.lib.feelgpu_exchange_info(self.ex, ptr(st, c_i64p)), self.eng.ctx)
+        keys = ["owners", "ghost_rows", "send_values", "holders", "recv_rows", "recv_values", "peer_memory", "epoch"]
+        return dict(zip(keys, (int(x) for x in st)))
 
     def _alloc_values(self):
         self.t_values = self.torch.zeros(max(self.nnz, 1), dtype=self.torch.float64, device="cuda")
         return C.c_void_p(self.t_values.data_ptr())
 
-    # ---- peer-memory transport ----
-    def _setup_peer(self):
-        torch, dist, eng = self.torch, self.dist, self.eng
-        rank, world = dist.get_rank(), dist.get_world_size()
-        ok = int(self.plan_stats()["eplan"]["has_plan"] == 1 and len(self.send) <= 8)
-        t = torch.tensor([ok], device="cuda", dtype=torch.int32)
-        dist.all_reduce(t, op=dist.ReduceOp.MIN)
-        if int(t.item()) == 0:
-            return
-        # landing buffers for the rows my neighbours hold as ghosts: two sets (epoch parity), exported to the neighbours
-        self.land = []
-        mine = {}
-        for p, slots, _ in self.recv:
-            bufs, hs = [], []
-            for _e in range(2):
-                d = eng.malloc(8 * max(len(slots), 1))
-                h = C.create_string_buffer(64)
-                check(eng.lib.feelgpu_ipc_export(eng.ctx, d, h), eng.ctx)
-                bufs.append(d)
-                hs.append(h.raw)
-            self.land.append((p, slots, bufs))
-            mine[p] = hs
-        allh = [None] * world
-        dist.all_gather_object(allh, mine)
-        # the buffers of the owners of my ghost rows, in slot order
-        self.remote = []
-        for q, off, cnt in sorted(self.send, key=lambda x: x[1]):
-            ptrs = []
-            for e in range(2):
-                p = C.c_void_p()
-                check(eng.lib.feelgpu_ipc_open(eng.ctx, allh[q][rank][e], C.byref(p)), eng.ctx)
-                ptrs.append(p)
-            self.remote.append((off, off + cnt, ptrs))
-        self.flag = torch.zeros(1, device="cuda", dtype=torch.int32)
-        self.epoch = 0
-        self.peer = True
-        self._set_remote()
-
-    def _set_remote(self):
-        n = len(self.remote)
-        lo = np.array([r[0] for r in self.remote], dtype=np.int64)
-        hi = np.array([r[1] for r in self.remote], dtype=np.int64)
-        tg = (C.c_void_p * max(n, 1))(*[r[2][self.epoch & 1] for r in self.remote])
-        check(self.eng.lib.feelgpu_pattern_set_remote(self.pat, n, lo.ctypes.data_as(C.POINTER(C.c_int64)),
-                                                      hi.ctypes.data_as(C.POINTER(C.c_int64)), tg), self.eng.ctx)
-
     def assemble_desc(self, desc, accumulate, stream=None):
-        """feelgpu_form2_assemble with the bookkeeping of where the ghost rows went (asynchronous on `stream`)"""
-        direct = C.c_int(0)
-        if self.peer:
-            check(self.eng.lib.feelgpu_form2_uses_remote(self.pat, C.byref(desc), C.byref(direct)), self.eng.ctx)
-        if direct.value:
-            if not accumulate:
-                self._tail_used = False          # '=' voids what the local tail held
-            self._direct_used = True
-        else:
-            if self.peer and not accumulate:
-                self._direct_used = False        # '=' voids the landing buffers: they count as empty again
-                self._set_remote()
-            if accumulate and not self._tail_used and self.nnz > self.tail0:
-                self.t_values[self.tail0:].zero_()
-            self._tail_used = True
+        """feelgpu_form2_assemble (asynchronous on `stream`); the library notes where the ghost rows went"""
         check(self.eng.lib.feelgpu_form2_assemble(self.pat, C.byref(desc), accumulate, self.d_values, stream), self.eng.ctx)
 
     def _assemble(self, integ, accumulate):
@@ -146,28 +102,27 @@ class DistributedBilinearForm(BilinearForm):
 
     def close(self, stream=None):
         """stream-ordered on torch's current stream: owners add the ghost-row contributions of their neighbours"""
-        torch, dist = self.torch, self.dist
-        sptr = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        if self.peer and self._direct_used:
-            dist.all_reduce(self.flag)     # every rank's kernel is complete: its stores into my landing buffers are visible
-            for p, slots, bufs in self.land:
-                check(self.eng.lib.feelgpu_scatter_add(self.eng.ctx, len(slots), C.c_void_p(slots.data_ptr()),
-                                                       bufs[self.epoch & 1], self.d_values, sptr), self.eng.ctx)
-            self.epoch += 1
-            self._set_remote()
-            self._direct_used = False
-        if self._tail_used or not self.peer:
-            ops = [dist.P2POp(dist.isend, self.t_values[off:off + cnt], q) for q, off, cnt in self.send]
-            ops += [dist.P2POp(dist.irecv, buf, p) for p, _, buf in self.recv]
-            if ops:
-                for w in dist.batch_isend_irecv(ops):
-                    w.wait()
-            for p, slots, buf in self.recv:
-                check(self.eng.lib.feelgpu_scatter_add(self.eng.ctx, len(buf), C.c_void_p(slots.data_ptr()),
-                                                       C.c_void_p(buf.data_ptr()), self.d_values, sptr), self.eng.ctx)
-            self._tail_used = False
+        sptr = C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+        check(self.eng.lib.feelgpu_form2_close(self.pat, self.d_values, sptr), self.eng.ctx)
         return self
 
     def owned_values(self):
         nO = self.Xh.lp.nDofOwned
         return self.t_values[:int(self.ia[nO])].cpu().numpy()
+
+
+class DistributedLinearForm(LinearForm):
+    """form1 on a LocalSpace; close() = VectorPetscMPI::close (VecAssemblyBegin/End + VecGhostUpdate,
+    feelalg/vectorpetsc.cpp:1667-1693) through the exchange of a bilinear form on the same space"""
+
+    def __init__(self, Xh, engine, form2):
+        super().__init__(Xh, engine)
+        self.ex = form2.ex
+
+    def close(self, ghost_update=True):
+        check(self.eng.lib.feelgpu_form1_close(self.ex, self.d_values, 1 if ghost_update else 0, None), self.eng.ctx)
+        self.eng.sync()
+        return self
+
+    def owned_values(self):
+        return self.values()[:self.Xh.lp.nDofOwned]

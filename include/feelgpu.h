@@ -205,34 +205,45 @@ int feelgpu_form1_assemble_faces(feelgpu_space_t space, feelgpu_faces_t faces, c
 int feelgpu_form2_assemble_faces(feelgpu_pattern_t pattern, feelgpu_faces_t faces, const feelgpu_form2_desc* desc /*MASS*/,
                                  int accumulate, double* a_values /*DEVICE*/, void* stream);
 
-/* ---- close(): owner-side accumulation of ghost-row contributions -------------------------------------------------
- * The reference ships stashed off-rank rows inside MatAssemblyBegin/End (feelalg/matrixpetsc.cpp:750-752).  Here the
- * values of a rank's ghost rows are the tail of its value array (rows nDofOwned..nDofLocalWithGhost-1), sent as they
- * are (values only, NCCL send/recv on the caller's communicator); the owner adds what it received with
- *     a[slots[k]] += vals[k],  k < n        (slots: DEVICE int64, built once from the graph exchange)              */
+/* ---- multi-GPU: one context (one MPI rank of the reference) per GPU of a node ------------------------------------------
+ * The reference ships stashed off-process rows inside MatAssemblyBegin/End (feelalg/matrixpetsc.cpp:726-760; MatSetValues
+ * on ghost rows :2875-2880) after GraphCSR::close has told every owner which (row, columns) its neighbours hold
+ * (feelalg/graphcsr.cpp:800-951).  Here:
+ *   feelgpu_comm_unique_id / feelgpu_comm_init   an NCCL communicator over the ranks (rank 0 creates the id, the caller
+ *       ships the 128 bytes by its own means -- Feel++'s WorldComm / MPI_Bcast -- every rank calls comm_init: collective)
+ *   feelgpu_exchange_create (collective, once per pattern)   the graph exchange.  Rows of the pattern are the process-local
+ *       dofs in the reference's order: active dofs first, ghost dofs after, each group in first-touch order
+ *       (feeldiscr/doftable.hpp:1975-1992) -- the ghost rows of one owner need NOT be contiguous.
+ *       ghost_owner[k] = rank owning local row nDofOwned + k (DataMap::procOnGlobalCluster), first_dof_cluster =
+ *       firstDofGlobalCluster() of this rank (feelalg/datamap.hpp:305); the cluster id of a ghost row comes from the
+ *       space's proc2cluster map.  Builds the owner-side slot lists and, unless FEELGPU_EXCHANGE_NO_PEER_MEMORY, the
+ *       peer-memory transport: every owner exports a landing buffer (CUDA IPC over NVLink/NVSwitch) and the assembly kernel
+ *       of the entity plan stores a rank's ghost rows straight into their owners' memory while it runs.
+ *   feelgpu_form2_close   MatrixPetsc::close (feelvf/bilinearformbase.hpp:353-357): stream-ordered; afterwards the owned
+ *       rows hold the contributions of every rank.  Peer transport: one NCCL all-reduce of a word (completion barrier)
+ *       + one owner-side add kernel; otherwise pack, ncclSend/ncclRecv (one group), add.  The library tracks which
+ *       assemblies since the last close wrote where ('=' and '+=' keep their meaning across ranks).
+ *   feelgpu_form1_close   VectorPetscMPI::close: VecAssemblyBegin/End (ghost entries added to their owners) and, with
+ *       ghost_update != 0, VecGhostUpdate (ghost copies refreshed from the owners) (feelalg/vectorpetsc.cpp:1667-1693).
+ * Work calls of all ranks must be issued in the same order (they contain collectives).                                 */
+#define FEELGPU_UNIQUE_ID_BYTES 128
+enum { FEELGPU_EXCHANGE_NO_PEER_MEMORY = 1 };
+typedef struct feelgpu_exchange_s* feelgpu_exchange_t;
+int feelgpu_comm_unique_id(unsigned char id[FEELGPU_UNIQUE_ID_BYTES]);
+int feelgpu_comm_init(feelgpu_context_t ctx, const unsigned char id[FEELGPU_UNIQUE_ID_BYTES], int rank, int nranks);
+int feelgpu_comm_destroy(feelgpu_context_t ctx);
+int feelgpu_exchange_create(feelgpu_pattern_t pattern, const int32_t* ghost_owner /*[nRows - nDofOwned]*/,
+                            int64_t first_dof_cluster, int flags, feelgpu_exchange_t* exchange);
+int feelgpu_exchange_destroy(feelgpu_exchange_t exchange);
+/* info: [0] owners of my ghost rows, [1] ghost rows, [2] ghost-row values sent per close, [3] ranks holding ghosts of my
+ * rows, [4] rows received, [5] values received, [6] 1 = peer-memory transport, [7] closes so far (epoch)              */
+int feelgpu_exchange_info(feelgpu_exchange_t exchange, int64_t info[8]);
+int feelgpu_form2_close(feelgpu_pattern_t pattern, double* a_values /*DEVICE [nnz]*/, void* stream);
+int feelgpu_form1_close(feelgpu_exchange_t exchange, double* b /*DEVICE [nDofLocalWithGhost]*/, int ghost_update, void* stream);
+
+/* owner-side helper kept for callers that run their own transport: a[slots[k]] += vals[k], k < n (DEVICE arrays)      */
 int feelgpu_scatter_add(feelgpu_context_t ctx, int64_t n, const int64_t* slots, const double* vals, double* a,
                         void* stream);
-
-/* ---- ghost rows over peer memory (one node, NVLink / NVSwitch) ------------------------------------------------------
- * Instead of stashing off-rank rows and shipping them in MatAssemblyBegin (feelalg/matrixpetsc.cpp:726-760, stash
- * exchange :750-752), the assembly kernel can store a rank's ghost rows straight into a landing buffer in the owner's
- * memory while it runs: the owner allocates one buffer per neighbour (feelgpu_malloc), exports it
- * (feelgpu_ipc_export, a 64-byte cudaIpcMemHandle_t that the caller ships by any means), the neighbour opens it
- * (feelgpu_ipc_open) and registers it for the slot range of the rows that neighbour owns:
- *     value slots [lo[k], hi[k]) of this pattern are written to target[k][slot - lo[k]] instead of a_values[slot]
- * (ranges ascending, disjoint, inside the ghost-row tail; n = 0 restores local stores; at most 8 ranges).  A landing
- * buffer counts as empty after every set_remote call: the first assembly after it stores into the buffer, later
- * accumulating assemblies add to it.  Forms that the entity plan does not cover keep writing the local tail:
- * feelgpu_form2_uses_remote tells the caller which of the two happens for a description (same answer on every rank).
- * After a device-wide barrier across the ranks (any NCCL collective on the stream), the owner adds the landing
- * buffers with feelgpu_scatter_add; callers alternate between two sets of buffers so that one barrier per close
- * is enough (feelpp_b200/distributed.py).                                                                          */
-int feelgpu_ipc_export(feelgpu_context_t ctx, void* device_ptr /* from feelgpu_malloc */, unsigned char handle[64]);
-int feelgpu_ipc_open(feelgpu_context_t ctx, const unsigned char handle[64], void** device_ptr);
-int feelgpu_ipc_close(feelgpu_context_t ctx, void* device_ptr);
-int feelgpu_pattern_set_remote(feelgpu_pattern_t pattern, int n, const int64_t* lo, const int64_t* hi,
-                               void* const* target);
-int feelgpu_form2_uses_remote(feelgpu_pattern_t pattern, const feelgpu_form2_desc* desc, int* yes);
 
 /* ---- device memory helpers for callers without a CUDA runtime of their own ---------------------------------- */
 int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr);

@@ -1,5 +1,8 @@
-"""Multi-GPU parity (needs >= 2 GPUs; skipped otherwise): each rank assembles its partition with the CUDA engine,
-ghost rows are exchanged with NCCL, and the gathered matrix is compared with the sequential oracle matrix."""
+"""Multi-GPU parity (needs >= 2 GPUs; skipped otherwise): each rank assembles its partition with the CUDA engine, close()
+runs through the C ABI (feelgpu_exchange_create / feelgpu_form2_close / feelgpu_form1_close: NCCL + peer memory), and the
+gathered matrix is compared with the sequential oracle matrix entry by entry after the cluster -> sequential permutation
+(tests/mp_util.py): identical pattern, every value within the parity bound.  Ghost rows come in the reference's order
+(first touch, not grouped by owner) and the partitions are irregular (METIS / breadth-first seeds)."""
 import os
 import sys
 
@@ -10,101 +13,128 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, order, ncomp, out):
+def _init(rank, world, port):
     sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch
     import torch.distributed as dist
-    import feelpp_b200 as fpp
-    from feelpp_b200 import parallel as par, distributed as dd
-    from feelpp_b200 import elements, grad, gradt, integrate, inner, trans, sym, trace, Id
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world,
                             device_id=torch.device("cuda", rank))
-    mesh = fpp.unitCube(6, 0.15, True)
-    part = par.partition_rcb(mesh, world)
+    return torch, dist
+
+
+def _forms(order, ncomp, Xh, mesh):
+    import feelpp_b200 as fpp
+    from feelpp_b200 import elements, grad, gradt, integrate, inner, trans, sym, trace, Id
+    u = v = fpp.Element(Xh)
+    if ncomp == 1:
+        return integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v)))
+    return integrate(_range=elements(mesh), _expr=inner(2.0 * trace(sym(gradt(u))) * Id() + 2 * 1.5 * sym(gradt(u)), grad(v)))
+
+
+def _worker(rank, world, port, m, order, ncomp, how, out):
+    torch, dist = _init(rank, world, port)
+    import feelpp_b200 as fpp
+    from feelpp_b200 import parallel as par, distributed as dd
+    from feelpp_b200 import cst, elements, id, integrate, vec, inner
+    import mp_util
+    mesh = fpp.unitCube(m, 0.15, True)
+    part = mp_util.make_partition(mesh, world, how)
     lp = par.LocalProblem(mesh, part, order, ncomp, par.Comm(rank, world, dist))
     eng = fpp.Engine(rank)
     Xh = dd.LocalSpace(lp)
-    u = v = fpp.Element(Xh)
     res = {}
-    for algo in (fpp.ALGO_SCATTER, fpp.ALGO_AUTO):
-        a = dd.DistributedBilinearForm(Xh, eng, dist, algorithm=algo)
-        if ncomp == 1:
-            a.assign(integrate(_range=elements(lp.mesh), _expr=gradt(u) * trans(grad(v))))
-        else:
-            a.assign(integrate(_range=elements(lp.mesh),
-                               _expr=inner(2.0 * trace(sym(gradt(u))) * Id() + 2 * 1.5 * sym(gradt(u)), grad(v))))
+    for name, algo, peer in (("scatter", fpp.ALGO_SCATTER, True), ("auto", fpp.ALGO_AUTO, True), ("auto-nopeer", fpp.ALGO_AUTO, False)):
+        a = dd.DistributedBilinearForm(Xh, eng, dist, algorithm=algo, peer_memory=peer)
+        a.assign(_forms(order, ncomp, Xh, lp.mesh))
         torch.cuda.synchronize()
         a.close()
         torch.cuda.synchronize()
-        nO = lp.nDofOwned
-        rows = np.repeat(lp.p2c[:nO], np.diff(lp.ia[:nO + 1]))
-        res[algo] = (rows, lp.ja[:lp.ia[nO]], a.owned_values())
+        b = None
+        if name == "auto":
+            v = fpp.Element(Xh)
+            l = dd.DistributedLinearForm(Xh, eng, a)
+            f = cst(3.0) * id(v) if ncomp == 1 else inner(vec(3.0, -6.0, 1.5), id(v))
+            l.assign(integrate(_range=elements(lp.mesh), _expr=f))
+            l.close()
+            b = l.values()
+            res["info"] = a.exchange_info()
+        res[name] = mp_util.rank_payload(lp, a.owned_values(), b)
+        if b is not None:
+            res[name]["ghost_check"] = (lp.p2c[lp.nDofOwned:], b[lp.nDofOwned:])
     gathered = [None] * world
-    dist.all_gather_object(gathered, (res, lp.firstDof, lp.nDofOwned))
+    dist.all_gather_object(gathered, res)
     if rank == 0:
         out.put(gathered)
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("order,ncomp", [(2, 1), (1, 1), (2, 3)])
-def test_two_gpus_match_sequential(order, ncomp):
+def _run(worker, world, args, timeout=900):
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    import scipy.sparse as sps
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
     import torch.multiprocessing as mp
-    import feelpp_b200 as fpp
-    from oracle import oracle as orc
-    world = 2
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
-    port = 29600 + (os.getpid() + order + ncomp) % 2000
-    procs = [ctx.Process(target=_worker, args=(r, world, port, order, ncomp, out)) for r in range(world)]
+    port = 29600 + (os.getpid() * 3 + 17 * world + sum(hash(str(a)) % 97 for a in args)) % 2000
+    procs = [ctx.Process(target=worker, args=(r, world, port) + tuple(args) + (out,)) for r in range(world)]
     for p in procs:
         p.start()
-    gathered = out.get(timeout=600)
+    gathered = out.get(timeout=timeout)
     for p in procs:
-        p.join(timeout=120)
+        p.join(timeout=180)
         assert p.exitcode == 0
-    N = sum(g[2] for g in gathered)
-    mesh = fpp.unitCube(6, 0.15, True)
-    Xh = fpp.FunctionSpace(mesh, order, ncomp)
-    ia, ja = Xh.graph()
+    return gathered
+
+
+@pytest.mark.parametrize("world,m,order,ncomp,how", [(2, 8, 2, 1, "metis"), (2, 6, 1, 1, "bfs1"), (2, 6, 2, 3, "bfs2"),
+                                                     (4, 12, 2, 1, "bfs3"), (4, 8, 2, 3, "metis"), (8, 12, 2, 1, "metis"),
+                                                     (8, 8, 2, 3, "bfs5"), (8, 12, 1, 1, "bfs4")])
+def test_gpus_match_sequential_entry_by_entry(world, m, order, ncomp, how):
+    gathered = _run(_worker, world, (m, order, ncomp, how))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import feelpp_b200 as fpp
+    from oracle import oracle as orc
+    import mp_util
+    mesh = fpp.unitCube(m, 0.15, True)
     kind = orc.STIFFNESS if ncomp == 1 else orc.ELASTICITY
-    ref = orc.form2(kind, order, ncomp, orc.quad_order_form2(kind, order), mesh.xyz, mesh.conn, Xh.l2g, ia, ja,
-                    orc.Coeff(lam=2.0, mu=1.5))
-    R = sps.csr_matrix((ref, ja, ia), shape=(N, N))
-    for algo in gathered[0][0]:
-        D = sum(sps.coo_matrix((g[0][algo][2], (g[0][algo][0], g[0][algo][1])), shape=(N, N)).tocsr() for g in gathered)
-        sc = np.abs(ref).max()
-        assert np.allclose(np.sort(D.diagonal()), np.sort(R.diagonal()), rtol=1e-12, atol=1e-14 * sc)
-        assert np.allclose(np.sort(np.asarray(abs(D).sum(1)).ravel()), np.sort(np.asarray(abs(R).sum(1)).ravel()), rtol=1e-11)
-        assert abs(sps.linalg.norm(D) - sps.linalg.norm(R)) < 1e-12 * sps.linalg.norm(R)
+    co = orc.Coeff(lam=2.0, mu=1.5)
+    for name in ("scatter", "auto", "auto-nopeer"):
+        mp_util.check_against_sequential([g[name] for g in gathered], mesh, order, ncomp, kind, co,
+                                         "world %d P%d x%d %s %s" % (world, order, ncomp, how, name))
+    # the entity plan covers scalar and vector mass/stiffness: those ghost rows travelled through peer memory
+    if ncomp == 1:
+        assert all(g["info"]["peer_memory"] == 1 for g in gathered)
+    vecf = [3.0, -6.0, 1.5] if ncomp == 3 else None
+    ref_of = lambda Xh: orc.form1(order, ncomp, orc.quad_order_form1(order, 0), mesh.xyz, mesh.conn, Xh.l2g, Xh.nDof(),
+                                  orc.Coeff(value=3.0, vector=vecf))
+    mp_util.check_vector_against_sequential([g["auto"] for g in gathered], mesh, order, ncomp, ref_of, "form1 close")
+    Xh = fpp.FunctionSpace(mesh, order, ncomp)
+    perm = mp_util.cluster_to_sequential([g["auto"] for g in gathered], mesh, order, ncomp, Xh)
+    ref = ref_of(Xh)
+    for g in gathered:
+        gc, gb = g["auto"]["ghost_check"]
+        np.testing.assert_allclose(gb, ref[perm[gc]], rtol=1e-12, atol=1e-13 * np.abs(ref).max())
 
 
 def _worker_sequences(rank, world, port, out):
-    """peer-memory transport: '=' / '+=' sequences, two epochs, and a term that goes through the local tail"""
-    sys.path.insert(0, ROOT)
-    import torch
-    import torch.distributed as dist
+    """'=' / '+=' sequences over several closes, peer-memory and send/recv transports, and a term that goes through the
+    local tail between two terms that go to the peers"""
+    torch, dist = _init(rank, world, port)
     import feelpp_b200 as fpp
     from feelpp_b200 import parallel as par, distributed as dd
     from feelpp_b200 import elements, grad, gradt, id, idt, integrate, trans
-    torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world,
-                            device_id=torch.device("cuda", rank))
+    import mp_util
     mesh = fpp.unitCube(6, 0.15, True)
-    part = par.partition_rcb(mesh, world)
+    part = mp_util.make_partition(mesh, world, "bfs7")
     lp = par.LocalProblem(mesh, part, 2, 1, par.Comm(rank, world, dist))
     eng = fpp.Engine(rank)
     Xh = dd.LocalSpace(lp)
     u = v = fpp.Element(Xh)
     mass = integrate(_range=elements(lp.mesh), _expr=idt(u) * id(v))
     stiff = integrate(_range=elements(lp.mesh), _expr=gradt(u) * trans(grad(v)))
-    nO = lp.nDofOwned
-    rows = np.repeat(lp.p2c[:nO], np.diff(lp.ia[:nO + 1]))
     res = {}
     for peer in (True, False):
         a = dd.DistributedBilinearForm(Xh, eng, dist, peer_memory=peer)
@@ -113,11 +143,11 @@ def _worker_sequences(rank, world, port, out):
         a += stiff
         a.close()
         torch.cuda.synchronize()
-        res[("mass+stiff", peer)] = a.owned_values()
+        res[("mass+stiff", peer)] = mp_util.rank_payload(lp, a.owned_values())
         a.assign(stiff)                      # second epoch: the other set of landing buffers, '=' starts from scratch
         a.close()
         torch.cuda.synchronize()
-        res[("stiff", peer)] = a.owned_values()
+        res[("stiff", peer)] = mp_util.rank_payload(lp, a.owned_values())
         a.assign(mass)                       # third epoch: one term through the kernel that writes to the peers ...
         a.algorithm = fpp.ALGO_SCATTER       # ... and one through the local tail + NCCL send/recv
         a += stiff
@@ -125,50 +155,40 @@ def _worker_sequences(rank, world, port, out):
         a += stiff
         a.close()
         torch.cuda.synchronize()
-        res[("mass+2stiff", peer)] = a.owned_values()
+        res[("mass+2stiff", peer)] = mp_util.rank_payload(lp, a.owned_values())
+        a += stiff                           # '+=' after a close: only the new contribution travels
+        a.close()
+        torch.cuda.synchronize()
+        res[("mass+3stiff", peer)] = mp_util.rank_payload(lp, a.owned_values())
     gathered = [None] * world
-    dist.all_gather_object(gathered, (res, rows, lp.ja[:lp.ia[nO]], lp.nDofOwned))
+    dist.all_gather_object(gathered, res)
     if rank == 0:
         out.put(gathered)
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_two_gpus_peer_memory_sequences():
-    import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    import scipy.sparse as sps
-    import torch.multiprocessing as mp
+@pytest.mark.parametrize("world", [2, 4])
+def test_gpus_assignment_sequences(world):
+    gathered = _run(_worker_sequences, world, ())
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
     import feelpp_b200 as fpp
     from oracle import oracle as orc
-    world = 2
-    ctx = mp.get_context("spawn")
-    out = ctx.Queue()
-    port = 29600 + (os.getpid() + 77) % 2000
-    procs = [ctx.Process(target=_worker_sequences, args=(r, world, port, out)) for r in range(world)]
-    for p in procs:
-        p.start()
-    gathered = out.get(timeout=600)
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
-    N = sum(g[3] for g in gathered)
+    from oracle import parity
+    import mp_util
     mesh = fpp.unitCube(6, 0.15, True)
     Xh = fpp.FunctionSpace(mesh, 2, 1)
     ia, ja = Xh.graph()
-    M = orc.form2(orc.MASS, 2, 1, orc.quad_order_form2(orc.MASS, 2), mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
-    K = orc.form2(orc.STIFFNESS, 2, 1, orc.quad_order_form2(orc.STIFFNESS, 2), mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
-    want = {"mass+stiff": M + K, "stiff": K, "mass+2stiff": M + 2 * K}
-    for (name, peer) in gathered[0][0]:
-        ref = want[name]
-        R = sps.csr_matrix((ref, ja, ia), shape=(N, N))
-        D = sum(sps.coo_matrix((g[0][(name, peer)], (g[1], g[2])), shape=(N, N)).tocsr() for g in gathered)
-        sc = np.abs(ref).max()
-        assert np.allclose(np.sort(D.diagonal()), np.sort(R.diagonal()), rtol=1e-12, atol=1e-14 * sc), (name, peer)
-        assert np.allclose(np.sort(np.asarray(abs(D).sum(1)).ravel()), np.sort(np.asarray(abs(R).sum(1)).ravel()),
-                           rtol=1e-11), (name, peer)
-        assert abs(sps.linalg.norm(D) - sps.linalg.norm(R)) < 1e-12 * sps.linalg.norm(R), (name, peer)
-    # both transports give the same owned values bit for bit where the summation order is the same
-    for g in gathered:
-        assert np.array_equal(g[0][("stiff", True)], g[0][("stiff", False)])
+    N = Xh.nDof()
+    f = lambda kind: orc.form2(kind, 2, 1, orc.quad_order_form2(kind, 2), mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+    M, K = f(orc.MASS), f(orc.STIFFNESS)
+    Ma, Ka = f(orc.MASS | orc.ABS_FLAG), f(orc.STIFFNESS | orc.ABS_FLAG)
+    want = {"mass+stiff": (M + K, Ma + Ka), "stiff": (K, Ka), "mass+2stiff": (M + 2 * K, Ma + 2 * Ka),
+            "mass+3stiff": (M + 3 * K, Ma + 3 * Ka)}
+    for key in gathered[0]:
+        name, peer = key
+        g = [r[key] for r in gathered]
+        perm = mp_util.cluster_to_sequential(g, mesh, 2, 1, Xh)
+        D = mp_util.gathered_matrix(g, perm, N)
+        assert np.array_equal(D.indptr, ia) and np.array_equal(D.indices, ja)
+        parity.check(D.data, want[name][0], want[name][1], ia, ja, "%s peer=%s world %d" % (name, peer, world))
