@@ -9,11 +9,15 @@ LIB := feelpp_b200/lib
 
 all: $(LIB)/libfeelgpu.so $(LIB)/libfeelhost.so oracle
 
-$(LIB)/%.o: $(CSRC)/%.cu $(CSRC)/feelgpu_internal.h $(CSRC)/rowplan.h $(CSRC)/eplan.h include/feelgpu.h
+$(LIB)/%.o: $(CSRC)/%.cu $(CSRC)/feelgpu_internal.h $(CSRC)/rowplan.h $(CSRC)/eplan.h $(CSRC)/rplan.h $(CSRC)/device_common.cuh include/feelgpu.h
 	@mkdir -p $(LIB)
 	$(NVCC) $(NVCCFLAGS) -c $< -o $@ 2> $(LIB)/$*.ptxas.log || (cat $(LIB)/$*.ptxas.log; false)
 
 $(LIB)/rowplan_build.o: $(CSRC)/rowplan_build.cpp $(CSRC)/rowplan.h
+	@mkdir -p $(LIB)
+	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread -c $< -o $@
+
+$(LIB)/rplan_build.o: $(CSRC)/rplan_build.cpp $(CSRC)/rplan.h
 	@mkdir -p $(LIB)
 	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread -c $< -o $@
 
@@ -22,7 +26,7 @@ $(LIB)/eplan_build.o: $(CSRC)/eplan_build.cpp $(CSRC)/eplan.h
 	$(CXX) -O3 -march=x86-64-v3 -std=c++17 -fPIC -Wall -pthread $(EPLAN_DEFS) -c $< -o $@
 
 # NCCL (exchange.cu) is bound with dlopen at feelgpu_comm_init, not linked: see the note at the top of exchange.cu
-$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o $(LIB)/kernels_on.o $(LIB)/kernels_graph.o $(LIB)/exchange.o
+$(LIB)/libfeelgpu.so: $(LIB)/feelgpu_api.o $(LIB)/kernels_scatter.o $(LIB)/kernels_rowplan.o $(LIB)/rowplan_build.o $(LIB)/kernels_eplan.o $(LIB)/eplan_build.o $(LIB)/kernels_on.o $(LIB)/kernels_graph.o $(LIB)/exchange.o $(LIB)/kernels_rplan.o $(LIB)/rplan_build.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart -ldl
 
 # METIS 5.1.0 as vendored by the reference (feelpp/contrib/metis: the partitioner Feel++ itself uses,

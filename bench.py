@@ -65,7 +65,7 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--partition", default="auto", choices=["auto", "metis", "rcb"],
                     help="element partition at N>1: METIS on the face-adjacency graph as the reference does, or coordinate bisection")
-    ap.add_argument("--algo", default="auto", choices=["auto", "scatter", "rowplan", "eplan"])
+    ap.add_argument("--algo", default="auto", choices=["auto", "scatter", "rowplan", "eplan", "rplan"])
     ap.add_argument("--shuffle", action="store_true", help="Fisher-Yates shuffled element order")
     ap.add_argument("--mesh", default=None, help="a Gmsh .msh file (tetrahedra) used instead of the synthetic cube; "
                     "one GPU only, reported as its own workload (never a BASELINE config line)")
@@ -311,7 +311,8 @@ def gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    algo = {"auto": fpp.ALGO_AUTO, "scatter": fpp.ALGO_SCATTER, "rowplan": fpp.ALGO_ROWPLAN, "eplan": fpp.ALGO_EPLAN}[args.algo]
+    algo = {"auto": fpp.ALGO_AUTO, "scatter": fpp.ALGO_SCATTER, "rowplan": fpp.ALGO_ROWPLAN, "eplan": fpp.ALGO_EPLAN,
+            "rplan": fpp.ALGO_RPLAN}[args.algo]
     eng = fpp.Engine(local)
     lp = None
     if world == 1:
@@ -319,7 +320,7 @@ def gpu_arm(args):
         nElt, nnz = mesh.numElements(), int(ia[-1])
         t0 = time.time()
         a = fpp.form2(_test=Xh, _trial=Xh, engine=eng, algorithm=algo,
-                      pattern_flags={"rowplan": 3, "scatter": 1}.get(args.algo, 0))
+                      pattern_flags={"rowplan": 3, "scatter": 1, "rplan": 9}.get(args.algo, 0))
         info["pattern_create_s"] = round(time.time() - t0, 2)
         nElt_total, nnz_total, gmesh, ndof_total = nElt, nnz, mesh, Xh.nDof()
         part_name = "1 GPU"

@@ -7,6 +7,6 @@ from .hostmirror import (Mesh, unitCube, loadMesh, elements, boundaryfaces, mark
                          nLocalDof, GinacProgram)
 from .vf import (Element, cst, vec, idv, expr, id, idt, grad, gradt, trans, sym, trace, Id, inner, integrate, on,
                  classify_form1, classify_form2)
-from .engine import (Engine, form1, form2, ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN,
-                     PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN)
+from .engine import (Engine, form1, form2, ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN, ALGO_RPLAN,
+                     PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN, PATTERN_RPLAN)
 from ._capi import FeelGpuError

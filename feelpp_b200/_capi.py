@@ -59,11 +59,16 @@ GPU_SYMBOLS = {
     "feelgpu_pattern_destroy": [C.c_void_p],
     "feelgpu_pattern_plan_stats": [C.c_void_p, c_i64p],
     "feelgpu_pattern_eplan_stats": [C.c_void_p, c_i64p],
+    "feelgpu_pattern_rplan_stats": [C.c_void_p, c_i64p],
     "feelgpu_eplan_host_build": [C.c_int, C.c_int, C.c_int64, c_i32p, C.c_int64, c_dblp, c_i32p, C.c_int64, c_i64p,
                                  C.c_void_p, C.POINTER(C.c_void_p), c_i64p],
     "feelgpu_eplan_host_copy": [C.c_void_p, C.c_void_p, c_i32p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, c_dblp],
     "feelgpu_eplan_host_free": [C.c_void_p],
     "feelgpu_eplan_host_coefficients": [C.c_int, C.POINTER(Tables), C.c_int, c_dblp, c_dblp],
+    "feelgpu_rplan_host_build": [C.c_int, C.c_int, C.c_int64, c_i32p, C.c_int64, c_dblp, c_i32p, C.c_int64, c_i64p, C.c_int,
+                                 C.c_int, C.c_int, C.POINTER(C.c_void_p), c_i64p],
+    "feelgpu_rplan_host_copy": [C.c_void_p, C.c_void_p, c_i32p, C.c_void_p, C.c_void_p],
+    "feelgpu_rplan_host_free": [C.c_void_p],
     "feelgpu_form2_assemble": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form1_assemble": [C.c_void_p, C.POINTER(Form1Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form2_assemble_host": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, c_dblp],
@@ -127,6 +132,8 @@ def gpu():
         lib.feelgpu_last_error.restype = C.c_char_p
         lib.feelgpu_eplan_host_error.argtypes = [C.c_void_p]
         lib.feelgpu_eplan_host_error.restype = C.c_char_p
+        lib.feelgpu_rplan_host_error.argtypes = [C.c_void_p]
+        lib.feelgpu_rplan_host_error.restype = C.c_char_p
         _gpu = lib
     return _gpu
 

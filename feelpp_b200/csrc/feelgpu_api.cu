@@ -266,7 +266,7 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     if (ia[0] != 0) ARG_FAIL(ctx, "pattern_create: ia[0] != 0");
     for (int64_t r = 0; r < nRows; ++r)
         if (ia[r + 1] < ia[r]) ARG_FAIL(ctx, "pattern_create: ia not monotone");
-    if (flags == 0) flags = FEELGPU_PATTERN_SLOTMAP | (test->order <= 2 ? FEELGPU_PATTERN_EPLAN : FEELGPU_PATTERN_ROWPLAN);
+    if (flags == 0) flags = FEELGPU_PATTERN_SLOTMAP | FEELGPU_PATTERN_RPLAN | (test->order <= 2 ? FEELGPU_PATTERN_EPLAN : 0);
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));
     feelgpu_pattern_t pat = nullptr;
     int64_t* d_ja = nullptr;
@@ -314,8 +314,9 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
         }
     }
     if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_EPLAN)) rc = feelgpu_eplan_build(pat, ia);
+    if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_RPLAN)) rc = feelgpu_rplan_build(pat, ia);
     // the row plan is also the fallback of a mesh the entity plan could not take
-    if (rc == FEELGPU_OK && ((flags & FEELGPU_PATTERN_ROWPLAN) || ((flags & FEELGPU_PATTERN_EPLAN) && !pat->eplan)))
+    if (rc == FEELGPU_OK && ((flags & FEELGPU_PATTERN_ROWPLAN) || ((flags & FEELGPU_PATTERN_EPLAN) && !pat->eplan && !pat->rplan)))
         rc = feelgpu_rowplan_build(pat, ia, ja);
     if (rc != FEELGPU_OK) {
         feelgpu_pattern_destroy(pat);
@@ -361,12 +362,19 @@ int feelgpu_pattern_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
     return feelgpu_eplan_stats(pat, stats);
 }
 
+int feelgpu_pattern_rplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
+{
+    if (!pat || !stats) return FEELGPU_ERR_ARG;
+    return feelgpu_rplan_stats(pat, stats);
+}
+
 int feelgpu_pattern_destroy(feelgpu_pattern_t pat)
 {
     if (!pat) return FEELGPU_ERR_ARG;
     feelgpu_exchange_detach(pat);
     feelgpu_rowplan_destroy(pat);
     feelgpu_eplan_destroy(pat);
+    feelgpu_rplan_destroy(pat);
     if (pat->d_ia) cudaFree(pat->d_ia);
     if (pat->d_pos) cudaFree(pat->d_pos);
     if (pat->d_stage) cudaFree(pat->d_stage);
@@ -453,9 +461,13 @@ int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc
     if (rc) return rc;
     int algo = desc->algorithm;
     if (algo == FEELGPU_ALGO_AUTO)
-        algo = feelgpu_eplan_supports(pat, desc) ? FEELGPU_ALGO_EPLAN
-                                                 : (feelgpu_rowplan_supports(pat, desc) ? FEELGPU_ALGO_ROWPLAN : FEELGPU_ALGO_SCATTER);
+        algo = feelgpu_eplan_supports(pat, desc)     ? FEELGPU_ALGO_EPLAN
+               : feelgpu_rplan_supports(pat, desc)   ? FEELGPU_ALGO_RPLAN
+               : feelgpu_rowplan_supports(pat, desc) ? FEELGPU_ALGO_ROWPLAN
+                                                     : FEELGPU_ALGO_SCATTER;
+    if (algo < FEELGPU_ALGO_SCATTER || algo > FEELGPU_ALGO_RPLAN) ARG_FAIL(ctx, "form2_assemble: unknown algorithm");
     if ((algo == FEELGPU_ALGO_ROWPLAN && !feelgpu_rowplan_supports(pat, desc)) ||
+        (algo == FEELGPU_ALGO_RPLAN && !feelgpu_rplan_supports(pat, desc)) ||
         (algo == FEELGPU_ALGO_EPLAN && !feelgpu_eplan_supports(pat, desc))) {
         ctx->last_error = "form2_assemble: the owner-computes plan does not cover this form/pattern";
         return FEELGPU_ERR_UNSUPPORTED;
@@ -465,6 +477,9 @@ int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc
     if (algo == FEELGPU_ALGO_EPLAN) {
         if (ctx->timing) cudaEventRecord(ctx->ev[1], s);
         rc = feelgpu_launch_form2_eplan(pat, hp, desc, accumulate, a, s);
+    } else if (algo == FEELGPU_ALGO_RPLAN) {
+        if (ctx->timing) cudaEventRecord(ctx->ev[1], s);
+        rc = feelgpu_launch_form2_rplan(pat, hp, desc, accumulate, a, s);
     } else if (algo == FEELGPU_ALGO_ROWPLAN) {
         if (ctx->timing) cudaEventRecord(ctx->ev[1], s);
         rc = feelgpu_launch_form2_rowplan(pat, hp, desc, accumulate, a, s);

@@ -53,6 +53,7 @@ struct feelgpu_space_s {
 
 struct RowPlan;  // kernels_rowplan.cu
 struct EPlan;    // kernels_eplan.cu
+struct RPlan;    // kernels_rplan.cu
 
 struct feelgpu_pattern_s {
     feelgpu_context_t ctx;
@@ -70,6 +71,8 @@ struct feelgpu_pattern_s {
     std::string plan_note;       // why no owner-computes plan exists (if none)
     EPlan* eplan = nullptr;
     std::string eplan_note;
+    RPlan* rplan = nullptr;      // row-thread plan: owner-computes path of the forms the entity plan does not cover
+    std::string rplan_note;
     // multi-GPU: host copies of what the graph exchange ships (interface-sized) and the exchange itself
     std::vector<int64_t> h_ia;        // [nRows+1]
     std::vector<int64_t> h_ja_tail;   // columns of the ghost rows: ja[ia[nDofOwned] .. nnz)
@@ -123,6 +126,13 @@ void feelgpu_rowplan_destroy(feelgpu_pattern_t pat);
 int feelgpu_launch_form2_rowplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
                                  int accumulate, double* a, cudaStream_t s);
 bool feelgpu_rowplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
+// ---- kernels_rplan.cu ----
+int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia);
+void feelgpu_rplan_destroy(feelgpu_pattern_t pat);
+int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
+                               int accumulate, double* a, cudaStream_t s);
+bool feelgpu_rplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
+int feelgpu_rplan_stats(feelgpu_pattern_t pat, int64_t stats[10]);
 // ---- kernels_eplan.cu ----
 int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia);
 void feelgpu_eplan_destroy(feelgpu_pattern_t pat);

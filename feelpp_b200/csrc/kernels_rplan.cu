@@ -1,0 +1,434 @@
+// kernels_rplan.cu -- row-thread assembly kernel (see rplan.h for the design) and the plan's device mirror.
+//
+// Replaces, for coefficient-weighted mass / stiffness forms (cst, idv(k), expr("...")) of every order and for the
+// vector-elasticity form, the reference's per-element update/integrate/assemble + MatSetValues(ADD_VALUES)
+// (feelvf/integrator.hpp:1093-1207, feelvf/bilinearformcontext.hpp:585-589, feelalg/matrixpetsc.cpp:917-936): the thread
+// that owns a CSR row forms the rows of the local matrices of the elements around its node by the quadrature sum
+// (feelpoly/pointsetquadrature.hpp:403-416) and adds them into its own segment of the CTA's shared-memory row block; the
+// block leaves the SM once, with coalesced stores.  No atomics, no zero fill, fixed summation order.
+#include <string>
+#include "feelgpu_internal.h"
+#include "device_common.cuh"
+#include "rplan.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+
+int feelgpu_upload_tables_public(feelgpu_context_t ctx, const FormParams& hp, const feelgpu_tables& t, cudaStream_t s,
+                                 const FormParams** dP, const double** phi, const double** dphi, const double** phif,
+                                 const double** M9, const double** Mm);
+
+namespace {
+
+struct RArgs {
+    const RPlanPatch* patches;
+    const int32_t* visits;
+    const uint4* rows;
+    const uint32_t* units;
+    const double* xyz;
+    const int4* conn;
+    const uint16_t* pos;
+    const FormParams* P;
+    DevTables T;
+    const int32_t* l2gf;
+    const double* fvals;
+    double* a;
+    int accumulate, maxslots, maxvis;
+};
+
+// FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)) (thread = node row), 2: elasticity (thread = (node row, column j))
+template <int ORDER, int FORM>
+__global__ void __launch_bounds__(512, 1)
+k_rplan(const RArgs A)
+{
+    constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
+    extern __shared__ double sm[];
+    const FormParams* __restrict__ P = A.P;
+    const int nq = P->nq, nf = P->nf, maxvis = A.maxvis;
+    const int nrec = FORM == 0 ? nq : FORM == 1 ? 6 + nq : 10;
+    double* blk = sm;                                        // [maxslots] the patch's row block
+    double* rec = blk + A.maxslots;                          // [nrec][maxvis] per-visit records
+    double* tab = rec + (size_t)nrec * maxvis;               // reference tables (layout per form, below)
+    const int ntab = FORM == 0 ? N * nq : FORM == 1 ? N * nq * 3 : N * N * 9;
+    double* tphif = tab + ntab;                              // [nf][nq] basis of the coefficient field
+    int32_t* sE = reinterpret_cast<int32_t*>(tphif + nf * nq);   // [maxvis] element of every visit
+    const int tid = threadIdx.x;
+
+    const uint4* pq = reinterpret_cast<const uint4*>(A.patches + blockIdx.x);
+    const uint4 p0 = __ldg(pq), p1 = __ldg(pq + 1);
+    const uint32_t visit_off = p0.x, nvisit = p0.y, row_off = p0.z, nrows = p0.w, unit_off = p1.x, nslots = p1.z;
+
+    // ---- tables: [q][j](x3) so that a warp walking (q, j) reads one address (broadcast) ----
+    if (FORM == 0) {
+        for (int k = tid; k < N * nq; k += blockDim.x) { const int j = k / nq, q = k - j * nq; tab[q * N + j] = A.T.phi[k]; }
+    } else if (FORM == 1) {
+        for (int k = tid; k < N * nq; k += blockDim.x) {
+            const int j = k / nq, q = k - j * nq;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) tab[(q * N + j) * 3 + c] = A.T.dphi[3 * k + c];
+        }
+    } else {
+        for (int k = tid; k < N * N * 9; k += blockDim.x) tab[k] = A.T.M9[k];
+    }
+    for (int k = tid; k < nf * nq; k += blockDim.x) tphif[k] = A.T.phif[k];
+    for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;
+    __syncthreads();    // (phase A reads tphif)
+
+    // ---- phase A: geometry and coefficient of every element touching the patch's rows, once (thread = visit) ----
+    for (uint32_t v = tid; v < nvisit; v += blockDim.x) {
+        const int32_t e = __ldg(&A.visits[visit_off + v]);
+        sE[v] = e;
+        Geo g;
+        geo_update(A.xyz, __ldg(&A.conn[e]), g);
+        if (FORM == 2) {
+#pragma unroll
+            for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+                for (int b = 0; b < 3; ++b) rec[(a1 * 3 + b) * maxvis + v] = g.B[a1][b];
+            rec[9 * maxvis + v] = g.J;
+        } else {
+            int r0 = 0;
+            if (FORM == 1) {
+                // G = B^T B (the factor J goes with the weights): G_bd = sum_a B_ab B_ad, order 00 01 02 11 12 22
+                int k = 0;
+#pragma unroll
+                for (int b = 0; b < 3; ++b)
+#pragma unroll
+                    for (int d = b; d < 3; ++d)
+                        rec[(k++) * maxvis + v] = g.B[0][b] * g.B[0][d] + g.B[1][b] * g.B[1][d] + g.B[2][b] * g.B[2][d];
+                r0 = 6;
+            }
+            // prod[q] * k(x_q) = w_q J k(x_q)   (feelpoly/pointsetquadrature.hpp:481-490)
+            for (int q = 0; q < nq; ++q)
+                rec[(r0 + q) * maxvis + v] = (P->w[q] * g.J) * coeff_at(P, tphif, g, e, q, A.l2gf, A.fvals);
+        }
+    }
+    __syncthreads();
+
+    // ---- phase B: every row is summed by its own thread(s) ----
+    const uint4* rows = A.rows + 2 * (size_t)row_off;
+    const uint32_t* units = A.units + unit_off;
+    if (FORM != 2) {
+        for (uint32_t r = tid; r < nrows; r += blockDim.x) {
+            const uint4 q1 = __ldg(rows + 2 * r + 1);
+            const uint32_t roff = __ldg(rows + 2 * r).z, unit0 = q1.x, nun = q1.y;
+            double* rb = blk + roff;
+            for (uint32_t u = 0; u < nun; ++u) {
+                const uint32_t w = __ldg(&units[unit0 + u]);
+                const int v = w & 0xFFFF, i = (w >> 16) & 0xFF;
+                const uint16_t* pp = A.pos + ((int64_t)sE[v] * N + i) * N;
+                uint16_t ps[N];
+#pragma unroll
+                for (int j = 0; j < N; ++j) ps[j] = __ldg(pp + j);
+                double acc[N];
+#pragma unroll
+                for (int j = 0; j < N; ++j) acc[j] = 0.0;
+                if (FORM == 0) {
+                    for (int q = 0; q < nq; ++q) {
+                        const double s = rec[q * maxvis + v] * tab[q * N + i];
+                        const double* tq = tab + q * N;
+#pragma unroll
+                        for (int j = 0; j < N; ++j) acc[j] = fma(s, tq[j], acc[j]);
+                    }
+                } else {
+                    const double G00 = rec[0 * maxvis + v], G01 = rec[1 * maxvis + v], G02 = rec[2 * maxvis + v],
+                                 G11 = rec[3 * maxvis + v], G12 = rec[4 * maxvis + v], G22 = rec[5 * maxvis + v];
+                    for (int q = 0; q < nq; ++q) {
+                        const double wk = rec[(6 + q) * maxvis + v];
+                        const double* gi = tab + (q * N + i) * 3;
+                        const double a0 = gi[0], a1 = gi[1], a2 = gi[2];
+                        // s = w_q J k_q G grad^(phi_i)(q)
+                        const double s0 = wk * (G00 * a0 + G01 * a1 + G02 * a2);
+                        const double s1 = wk * (G01 * a0 + G11 * a1 + G12 * a2);
+                        const double s2 = wk * (G02 * a0 + G12 * a1 + G22 * a2);
+                        const double* tq = tab + q * N * 3;
+#pragma unroll
+                        for (int j = 0; j < N; ++j)
+                            acc[j] = fma(s2, tq[3 * j + 2], fma(s1, tq[3 * j + 1], fma(s0, tq[3 * j], acc[j])));
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < N; ++j) rb[ps[j]] += acc[j];
+            }
+        }
+    } else {
+        const double lambda = P->lambda, mu = P->mu;
+        for (uint32_t t = tid; t < nrows * N; t += blockDim.x) {
+            const uint32_t r = t / N;
+            const int j = (int)(t - r * N);
+            const uint4 q0 = __ldg(rows + 2 * r), q1 = __ldg(rows + 2 * r + 1);
+            const uint32_t roff = q0.z, len = q0.w, unit0 = q1.x, nun = q1.y;
+            for (uint32_t u = 0; u < nun; ++u) {
+                const uint32_t w = __ldg(&units[unit0 + u]);
+                const int v = w & 0xFFFF, i = (w >> 16) & 0xFF;
+                const uint32_t p0c = __ldg(A.pos + ((int64_t)sE[v] * N + i) * N + j);
+                double B[3][3];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) B[k / 3][k % 3] = rec[k * maxvis + v];
+                const double J = rec[9 * maxvis + v];
+                // Pm[c][d] = sum_q w_q (grad phi_i)_c (grad phi_j)_d = (B M B^T)[c][d], M = sum_q w_q grad^phi_i grad^phi_j^T
+                const double* M = tab + (i * N + j) * 9;
+                double BD[3][3], Pm[3][3];
+#pragma unroll
+                for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) BD[a1][d] = B[a1][0] * M[0 * 3 + d] + B[a1][1] * M[1 * 3 + d] + B[a1][2] * M[2 * 3 + d];
+#pragma unroll
+                for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+                    for (int c2 = 0; c2 < 3; ++c2) Pm[a1][c2] = BD[a1][0] * B[c2][0] + BD[a1][1] * B[c2][1] + BD[a1][2] * B[c2][2];
+                const double tr = Pm[0][0] + Pm[1][1] + Pm[2][2];
+                // block (c1,c2) = J [lambda Pm_c1c2 + mu Pm_c2c1 + mu delta tr Pm]   (feelvf/inner.hpp:374-420)
+#pragma unroll
+                for (int c1 = 0; c1 < 3; ++c1) {
+                    double* rb = blk + roff + c1 * len + p0c;
+#pragma unroll
+                    for (int c2 = 0; c2 < 3; ++c2) {
+                        double val = lambda * Pm[c1][c2] + mu * Pm[c2][c1];
+                        if (c1 == c2) val += mu * tr;
+                        rb[c2] += J * val;
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- phase C: the row block goes to the CSR value array: one contiguous piece per node row, a warp per row ----
+    {
+        const int lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+        constexpr int NC = FORM == 2 ? 3 : 1;
+        for (uint32_t r = warp; r < nrows; r += nwarp) {
+            const uint4 q0 = __ldg(rows + 2 * r);
+            double* dst = A.a + (int64_t)(((uint64_t)q0.y << 32) | q0.x);
+            const double* src = blk + q0.z;
+            const uint32_t cnt = q0.w * NC;
+            if (A.accumulate) {
+                for (uint32_t k = lane; k < cnt; k += 32) dst[k] += src[k];
+            } else {
+                for (uint32_t k = lane; k < cnt; k += 32) dst[k] = src[k];
+            }
+        }
+    }
+}
+
+template <typename T>
+cudaError_t upload(T** d, const std::vector<T>& h, int64_t& bytes)
+{
+    cudaError_t err = cudaMalloc(d, std::max<size_t>(h.size(), 1) * sizeof(T));
+    if (err != cudaSuccess) return err;
+    bytes += (int64_t)(h.size() * sizeof(T));
+    return cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+size_t rplan_smem_bytes(const RPlan* p, int form, int nq, int nf)
+{
+    const int n = p->n;
+    const size_t nrec = form == 0 ? nq : form == 1 ? 6 + nq : 10;
+    const size_t ntab = form == 0 ? (size_t)n * nq : form == 1 ? (size_t)n * nq * 3 : (size_t)n * n * 9;
+    return sizeof(double) * ((size_t)p->maxslots + nrec * p->maxvisits + ntab + (size_t)nf * nq) + sizeof(int32_t) * (size_t)p->maxvisits + 16;
+}
+
+int env_int(const char* name, int dflt)
+{
+    const char* e = std::getenv(name);
+    return e && *e ? std::atoi(e) : dflt;
+}
+
+} // namespace
+
+int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    feelgpu_space_t sp = pat->test;
+    feelgpu_mesh_t m = sp->mesh;
+    if (pat->test != pat->trial) return FEELGPU_OK;   // the plan needs test == trial
+    // patch limits: the row block and the visit records share the SM's 227 KB with the reference tables
+    int maxslots, maxvis;
+    if (sp->ncomp == 3) { maxslots = 20480; maxvis = 256; }
+    else if (sp->order == 1) { maxslots = 8192; maxvis = 512; }
+    else if (sp->order == 2) { maxslots = 12288; maxvis = 384; }
+    else { maxslots = 16384; maxvis = 256; }
+    maxslots = env_int("FEELGPU_RPLAN_SLOTS", maxslots);
+    maxvis = env_int("FEELGPU_RPLAN_VISITS", maxvis);
+    const int maxrows = env_int("FEELGPU_RPLAN_ROWS", 1 << 20);
+    RPlanHost hp;
+    const auto t0 = std::chrono::steady_clock::now();
+    if (!rplan_build_host(sp->order, sp->ncomp, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(), m->h_conn.data(),
+                          pat->nRows, h_ia, maxslots, maxvis, maxrows, 0, hp)) {
+        pat->rplan_note = hp.error;   // not an error: another path stays available
+        return FEELGPU_OK;
+    }
+    RPlan* p = new RPlan;
+    p->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    p->order = hp.order;
+    p->n = hp.n;
+    p->ncomp = hp.ncomp;
+    p->maxslots = hp.maxpatch_slots;         // what the kernel has to provide: the largest patch, not the limit
+    p->maxvisits = std::max(hp.maxpatch_visits, 1);
+    p->maxrows = hp.maxpatch_rows;
+    p->npatch = (int64_t)hp.patches.size();
+    p->nunits = hp.nunits;
+    p->nvisits = hp.nvisits;
+    p->maxpatch_visits = hp.maxpatch_visits;
+    p->maxpatch_rows = hp.maxpatch_rows;
+    p->maxpatch_slots = hp.maxpatch_slots;
+    cudaError_t err = upload(&p->d_patches, hp.patches, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_visits, hp.visits, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_rows, hp.rows, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_units, hp.units, p->bytes);
+    pat->rplan = p;
+    if (err != cudaSuccess) {
+        ctx->last_error = std::string("row-thread plan upload: ") + cudaGetErrorString(err);
+        feelgpu_rplan_destroy(pat);
+        return FEELGPU_ERR_CUDA;
+    }
+    return FEELGPU_OK;
+}
+
+void feelgpu_rplan_destroy(feelgpu_pattern_t pat)
+{
+    RPlan* p = pat->rplan;
+    if (!p) return;
+    cudaFree(p->d_patches);
+    cudaFree(p->d_visits);
+    cudaFree(p->d_rows);
+    cudaFree(p->d_units);
+    delete p;
+    pat->rplan = nullptr;
+}
+
+int feelgpu_rplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
+{
+    for (int k = 0; k < 10; ++k) stats[k] = 0;
+    const RPlan* p = pat->rplan;
+    if (!p) return FEELGPU_OK;
+    stats[0] = 1;
+    stats[1] = p->npatch;
+    stats[2] = p->nunits;
+    stats[3] = p->nvisits;
+    stats[4] = p->bytes;
+    stats[5] = p->maxpatch_slots;
+    stats[6] = p->maxpatch_visits;
+    stats[7] = p->maxpatch_rows;
+    stats[8] = (int64_t)(p->build_seconds * 1e3);
+    return FEELGPU_OK;
+}
+
+static int rplan_form(const feelgpu_form2_desc* desc)
+{
+    return desc->kind == FEELGPU_FORM2_MASS ? 0 : desc->kind == FEELGPU_FORM2_STIFFNESS ? 1 : 2;
+}
+
+bool feelgpu_rplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc)
+{
+    const RPlan* p = pat->rplan;
+    if (!p || !pat->d_pos) return false;
+    const int form = rplan_form(desc);
+    if (desc->tables.n != p->n || desc->tables.nq < 1 || desc->tables.nq > FEELGPU_MAX_NQ) return false;
+    if (form == 2 ? p->ncomp != 3 : p->ncomp != 1) return false;    // product spaces: elasticity; mass/stiffness blocks go through the entity plan
+    if (form != 0 && !desc->tables.dphi) return false;
+    const int nf = desc->coeff.kind == FEELGPU_COEFF_FIELD ? desc->tables.nf : 0;
+    return rplan_smem_bytes(p, form, desc->tables.nq, nf) <= 227 * 1024;
+}
+
+int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc, int accumulate,
+                               double* a, cudaStream_t s)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    RPlan* p = pat->rplan;
+    feelgpu_space_t sp = pat->test;
+    feelgpu_mesh_t m = sp->mesh;
+    const int form = rplan_form(desc);
+    RArgs A;
+    int rc = feelgpu_upload_tables_public(ctx, hp, desc->tables, s, &A.P, &A.T.phi, &A.T.dphi, &A.T.phif, &A.T.M9, &A.T.Mm);
+    if (rc) return rc;
+    A.patches = p->d_patches;
+    A.visits = p->d_visits;
+    A.rows = reinterpret_cast<const uint4*>(p->d_rows);
+    A.units = p->d_units;
+    A.xyz = m->d_xyz;
+    A.conn = m->d_conn;
+    A.pos = pat->d_pos;
+    A.l2gf = nullptr;
+    A.fvals = nullptr;
+    if (hp.coeff_kind == FEELGPU_COEFF_FIELD && form != 2) {
+        A.l2gf = desc->coeff.field_space->d_l2g;
+        A.fvals = desc->coeff.field_values;
+    }
+    A.a = a;
+    A.accumulate = accumulate;
+    A.maxslots = p->maxslots;
+    A.maxvis = p->maxvisits;
+    const size_t sh = rplan_smem_bytes(p, form, hp.nq, hp.nf);
+    const int grid = (int)p->npatch;
+    if (grid == 0) return FEELGPU_OK;
+    const int threads = std::min(512, std::max(64, env_int("FEELGPU_RPLAN_THREADS", 512)));
+#define PLAUNCH(O, F)                                                                                                      \
+    do {                                                                                                                   \
+        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rplan<O, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+        k_rplan<O, F><<<grid, threads, sh, s>>>(A);                                                                        \
+    } while (0)
+    switch (p->order * 3 + form) {
+    case 3: PLAUNCH(1, 0); break;
+    case 4: PLAUNCH(1, 1); break;
+    case 5: PLAUNCH(1, 2); break;
+    case 6: PLAUNCH(2, 0); break;
+    case 7: PLAUNCH(2, 1); break;
+    case 8: PLAUNCH(2, 2); break;
+    case 9: PLAUNCH(3, 0); break;
+    case 10: PLAUNCH(3, 1); break;
+    case 11: PLAUNCH(3, 2); break;
+    default: ctx->last_error = "row-thread plan: unsupported order"; return FEELGPU_ERR_UNSUPPORTED;
+    }
+#undef PLAUNCH
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    return FEELGPU_OK;
+}
+
+// ---- host-side view of the plan (include/feelgpu.h): no device needed, used by the CPU tests ----------------------------
+extern "C" {
+
+int feelgpu_rplan_host_build(int order, int ncomp, int64_t nElt, const int32_t* l2g, int64_t nPts, const double* xyz,
+                             const int32_t* conn, int64_t nRows, const int64_t* ia, int maxslots, int maxvisits, int maxrows,
+                             void** plan, int64_t sizes[8])
+{
+    if (!l2g || !xyz || !conn || !ia || !plan || !sizes || order < 1 || order > 3) return FEELGPU_ERR_ARG;
+    RPlanHost* hp = new RPlanHost;
+    *plan = hp;
+    const int n = (order + 1) * (order + 2) * (order + 3) / 6;
+    const bool ok = rplan_build_host(order, ncomp, nElt, l2g, n * ncomp, nPts, xyz, conn, nRows, ia, maxslots, maxvisits, maxrows, 0, *hp);
+    sizes[0] = (int64_t)hp->patches.size();
+    sizes[1] = (int64_t)hp->visits.size();
+    sizes[2] = (int64_t)hp->rows.size();
+    sizes[3] = (int64_t)hp->units.size();
+    sizes[4] = hp->maxpatch_slots;
+    sizes[5] = hp->maxpatch_visits;
+    sizes[6] = hp->maxpatch_rows;
+    sizes[7] = 0;
+    return ok ? FEELGPU_OK : FEELGPU_ERR_UNSUPPORTED;
+}
+
+int feelgpu_rplan_host_copy(void* plan, void* patches /*32 B each*/, int32_t* visits, void* rows /*32 B each*/, uint32_t* units)
+{
+    if (!plan) return FEELGPU_ERR_ARG;
+    const RPlanHost* hp = static_cast<const RPlanHost*>(plan);
+    if (patches) std::memcpy(patches, hp->patches.data(), hp->patches.size() * sizeof(RPlanPatch));
+    if (visits) std::memcpy(visits, hp->visits.data(), hp->visits.size() * sizeof(int32_t));
+    if (rows) std::memcpy(rows, hp->rows.data(), hp->rows.size() * sizeof(RPlanRow));
+    if (units) std::memcpy(units, hp->units.data(), hp->units.size() * sizeof(uint32_t));
+    return FEELGPU_OK;
+}
+
+const char* feelgpu_rplan_host_error(void* plan) { return plan ? static_cast<const RPlanHost*>(plan)->error.c_str() : ""; }
+
+int feelgpu_rplan_host_free(void* plan)
+{
+    delete static_cast<RPlanHost*>(plan);
+    return FEELGPU_OK;
+}
+
+} // extern "C"

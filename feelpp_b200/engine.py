@@ -11,8 +11,8 @@ from . import hostmirror as hm
 from . import vf
 from ._capi import Coeff, Form1Desc, Form2Desc, Tables, c_dblp, c_i32p, c_i64p, check, ptr
 
-ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN = 0, 1, 2, 3
-PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN = 1, 2, 4
+ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN, ALGO_RPLAN = 0, 1, 2, 3, 4
+PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN, PATTERN_RPLAN = 1, 2, 4, 8
 
 
 class Engine:
@@ -262,6 +262,9 @@ class BilinearForm:
         ekeys = ["has_plan", "ctas", "tasks", "iterations", "iterations_padded", "visits", "outputs", "bytes",
                  "lds_wavefronts", "lds_wavefronts_ideal"]
         out["eplan"] = dict(zip(ekeys, (int(x) for x in st)))
+        check(self.eng.lib.feelgpu_pattern_rplan_stats(self.pat, ptr(st, c_i64p)), self.eng.ctx)
+        rkeys = ["has_plan", "patches", "units", "visits", "bytes", "max_slots", "max_visits", "max_rows", "build_ms"]
+        out["rplan"] = dict(zip(rkeys, (int(x) for x in st)))
         return out
 
     def scipy(self):

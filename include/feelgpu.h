@@ -104,13 +104,16 @@ typedef struct {
 
 /* assembly algorithms for form2 */
 enum {
-    FEELGPU_ALGO_AUTO = 0,        /* entity plan, else row plan, when the pattern has one and the form is covered; else scatter */
+    FEELGPU_ALGO_AUTO = 0,        /* the first plan of the pattern that covers the form: entity plan, row-thread plan, row plan; else scatter */
     FEELGPU_ALGO_SCATTER = 1,     /* element loop + red.global.add.f64 through the element->CSR-slot map         */
     FEELGPU_ALGO_ROWPLAN = 2,     /* owner-computes by (row, element) units: warp tile + planned gather          */
-    FEELGPU_ALGO_EPLAN = 3        /* owner-computes by (row, simplex) tasks: register accumulation over star(sigma) */
+    FEELGPU_ALGO_EPLAN = 3,       /* owner-computes by (row, simplex) tasks: register accumulation over star(sigma)
+                                     (constant-coefficient P1/P2 mass and stiffness, scalar and vector)               */
+    FEELGPU_ALGO_RPLAN = 4        /* owner-computes by row threads: the thread that owns a CSR row sums the quadrature rows
+                                     of the elements around it (cst / idv / expr coefficients, P1-P3, elasticity)      */
 };
-/* flags of feelgpu_pattern_create (0 = SLOTMAP + the best plan available for the space: EPLAN for P1/P2, ROWPLAN for P3) */
-enum { FEELGPU_PATTERN_SLOTMAP = 1, FEELGPU_PATTERN_ROWPLAN = 2, FEELGPU_PATTERN_EPLAN = 4 };
+/* flags of feelgpu_pattern_create (0 = SLOTMAP + RPLAN + EPLAN for P1/P2 spaces) */
+enum { FEELGPU_PATTERN_SLOTMAP = 1, FEELGPU_PATTERN_ROWPLAN = 2, FEELGPU_PATTERN_EPLAN = 4, FEELGPU_PATTERN_RPLAN = 8 };
 
 /* ---- context ------------------------------------------------------------------------------------------------ */
 int feelgpu_context_create(int device, feelgpu_context_t* ctx);
@@ -268,6 +271,10 @@ int feelgpu_pattern_plan_stats(feelgpu_pattern_t pattern, int64_t stats[10]);
  * word), [4] iterations incl. padding, [5] element visits, [6] output values, [7] plan bytes on the device,
  * [8] modelled shared-memory wavefronts of the S loads, [9] the same without bank conflicts                          */
 int feelgpu_pattern_eplan_stats(feelgpu_pattern_t pattern, int64_t stats[10]);
+/* statistics of the row-thread plan: stats[0] = 1 if it exists, [1] patches (CTAs), [2] units (row, element), [3] element
+ * visits, [4] plan bytes on the device, [5] largest row block (doubles), [6] most visits in a patch, [7] most rows in a
+ * patch, [8] host build time in milliseconds                                                                          */
+int feelgpu_pattern_rplan_stats(feelgpu_pattern_t pattern, int64_t stats[10]);
 
 
 /* ---- host-side view of the entity plan (no device needed): what feelgpu_pattern_create builds for P1/P2 spaces ------
@@ -285,6 +292,18 @@ int feelgpu_eplan_host_free(void* plan);
 /* coefficients the kernel applies to the per-task sums, from the caller's reference tables:
  * coef[type][out][load] (6 x 3 x 5), mass[type][out] (6 x 3); form: 0 mass, 1 stiffness                              */
 int feelgpu_eplan_host_coefficients(int order, const feelgpu_tables* tables, int form, double* coef, double* mass);
+
+/* ---- host-side view of the row-thread plan (no device needed): what feelgpu_pattern_create builds with
+ * FEELGPU_PATTERN_RPLAN; used by the CPU tests to interpret the plan on the host.  sizes: [0] patches, [1] visits,
+ * [2] node rows, [3] units, [4] largest row block, [5] most visits in a patch, [6] most rows in a patch.
+ * patches: {u32 visit_off, nvisit, row_off, nrows, unit_off, nunits, nslots, pad}; rows: {i64 base, u32 off, len, unit0,
+ * nunits, pad, pad}; unit word: visit index in the patch | local dof << 16                                               */
+int feelgpu_rplan_host_build(int order, int ncomp, int64_t nElt, const int32_t* l2g, int64_t nPts, const double* xyz,
+                             const int32_t* conn, int64_t nRows, const int64_t* ia, int maxslots, int maxvisits, int maxrows,
+                             void** plan, int64_t sizes[8]);
+int feelgpu_rplan_host_copy(void* plan, void* patches, int32_t* visits, void* rows, uint32_t* units);
+const char* feelgpu_rplan_host_error(void* plan);
+int feelgpu_rplan_host_free(void* plan);
 
 #ifdef __cplusplus
 }

@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     # and the Python binding table covers the header
-    assert set(capi.GPU_SYMBOLS) | {"feelgpu_last_error", "feelgpu_eplan_host_error"} == set(names)
+    assert set(capi.GPU_SYMBOLS) | {"feelgpu_last_error", "feelgpu_eplan_host_error", "feelgpu_rplan_host_error"} == set(names)
 
 
 def test_no_device_fails_loudly():

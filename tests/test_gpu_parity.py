@@ -15,8 +15,8 @@ from oracle import parity
 
 pytestmark = pytest.mark.gpu
 
-PFLAGS = {fpp.ALGO_SCATTER: 1, fpp.ALGO_ROWPLAN: 3, fpp.ALGO_EPLAN: 5}
-ALGOS = [fpp.ALGO_SCATTER, fpp.ALGO_ROWPLAN, fpp.ALGO_EPLAN]
+PFLAGS = {fpp.ALGO_SCATTER: 1, fpp.ALGO_ROWPLAN: 3, fpp.ALGO_EPLAN: 5, fpp.ALGO_RPLAN: 9}
+ALGOS = [fpp.ALGO_SCATTER, fpp.ALGO_ROWPLAN, fpp.ALGO_EPLAN, fpp.ALGO_RPLAN]
 
 
 import contextlib
@@ -28,7 +28,7 @@ def guard(algo):
     try:
         yield
     except fpp.FeelGpuError as e:
-        if algo in (fpp.ALGO_ROWPLAN, fpp.ALGO_EPLAN) and e.code == 5:
+        if algo in (fpp.ALGO_ROWPLAN, fpp.ALGO_EPLAN, fpp.ALGO_RPLAN) and e.code == 5:
             pytest.skip("the plan does not cover this form: " + str(e))
         raise
 
@@ -132,6 +132,37 @@ def test_elasticity(engine, meshes, order, algo):
         a.assign(integrate(_range=elements(mesh), _expr=inner(idt(u), id(v))))
     ref, scale = oracle_form2(orc.MASS, Xh, orc.quad_order_form2(orc.MASS, order))
     check_values(a.values(), ref, scale, "vector mass P%dv" % order)
+
+
+@pytest.mark.parametrize("order,ncomp", [(1, 1), (2, 1), (3, 1), (2, 3)])
+def test_row_thread_plan_with_many_small_patches(engine, meshes, order, ncomp, monkeypatch):
+    """the row-thread plan cut into many patches (tight row-block / visit limits): variable-coefficient stiffness and mass,
+    elasticity, '=' then '+=' """
+    monkeypatch.setenv("FEELGPU_RPLAN_SLOTS", "2600" if ncomp == 3 else "900")
+    monkeypatch.setenv("FEELGPU_RPLAN_VISITS", "72")
+    mesh = meshes["scr"]
+    Xh = fpp.Pchv(mesh, order) if ncomp == 3 else fpp.Pch(mesh, order)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, algorithm=fpp.ALGO_RPLAN, pattern_flags=9)
+    st = a.plan_stats()["rplan"]
+    assert st["has_plan"] == 1 and st["patches"] > 4 and st["units"] == mesh.numElements() * Xh.n
+    if ncomp == 3:
+        lam, mu = 3.0, 1.25
+        form = integrate(_range=elements(mesh), _expr=inner(lam * trace(sym(gradt(u))) * Id() + 2 * mu * sym(gradt(u)), grad(v)))
+        a.assign(form)
+        ref, scale = oracle_form2(orc.ELASTICITY, Xh, orc.quad_order_form2(orc.ELASTICITY, order), orc.Coeff(lam=lam, mu=mu))
+        check_values(a.values(), ref, scale, "elasticity, small patches")
+        a += form
+        check_values(a.values(), (2 * ref[0], ref[1], ref[2]), 2 * scale, "elasticity twice, small patches")
+        return
+    k = expr("2+sin(x)*y-z^2")
+    co = orc.Coeff(kind=orc.COEFF_EXPR, ops=k.prog.ops, consts=k.prog.consts)
+    a.assign(integrate(_range=elements(mesh), _expr=k * inner(gradt(u), grad(v))))
+    ref, scale = oracle_form2(orc.STIFFNESS, Xh, orc.quad_order_form2(orc.STIFFNESS, order, -1), co)
+    check_values(a.values(), ref, scale, "k(x)*stiffness, small patches")
+    a += integrate(_range=elements(mesh), _expr=k * idt(u) * id(v))
+    refm, scalem = oracle_form2(orc.MASS, Xh, orc.quad_order_form2(orc.MASS, order, -1), co)
+    check_values(a.values(), (ref[0] + refm[0], ref[1], ref[2]), scale + scalem, "k(x)*(stiffness+mass), small patches")
 
 
 @pytest.mark.parametrize("order", [1, 2, 3])

@@ -1,0 +1,111 @@
+"""The row-thread plan (feelpp_b200/csrc/rplan.h) interpreted on the CPU: every (row, element) unit of the mesh occurs
+exactly once, in the row of its node; patches respect their limits; and walking the plan exactly as the kernel does --
+thread = row, its units in plan order, each unit's row of the oracle's local matrix added through the element->CSR position
+map into the row's segment of the patch's row block, the block copied to the CSR array -- reproduces the oracle matrix.
+The GPU parity tests then only have to show that the kernel is a faithful interpreter with its own quadrature rows."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import feelpp_b200 as fpp
+from feelpp_b200 import _capi as capi
+from feelpp_b200._capi import c_dblp, c_i32p, c_i64p, ptr
+from oracle import oracle as orc
+
+PATCH = np.dtype([("visit_off", "u4"), ("nvisit", "u4"), ("row_off", "u4"), ("nrows", "u4"), ("unit_off", "u4"),
+                  ("nunits", "u4"), ("nslots", "u4"), ("pad", "u4")])
+ROW = np.dtype([("base", "i8"), ("off", "u4"), ("len", "u4"), ("unit0", "u4"), ("nunits", "u4"), ("pad", "u4", 2)])
+
+
+def build(Xh, ia, maxslots, maxvisits, maxrows=1 << 20):
+    lib = capi.gpu()
+    mesh = Xh.mesh
+    plan, sizes = C.c_void_p(), np.zeros(8, dtype=np.int64)
+    rc = lib.feelgpu_rplan_host_build(Xh.order, Xh.ncomp, mesh.numElements(), ptr(Xh.l2g, c_i32p), mesh.numPoints(),
+                                      ptr(mesh.xyz, c_dblp), ptr(mesh.conn, c_i32p), Xh.nDof(), ptr(ia, c_i64p), maxslots,
+                                      maxvisits, maxrows, C.byref(plan), ptr(sizes, c_i64p))
+    if rc:
+        msg = lib.feelgpu_rplan_host_error(plan).decode()
+        lib.feelgpu_rplan_host_free(plan)
+        raise RuntimeError(msg)
+    patches, rows = np.zeros(sizes[0], dtype=PATCH), np.zeros(sizes[2], dtype=ROW)
+    visits, units = np.zeros(sizes[1], dtype=np.int32), np.zeros(sizes[3], dtype=np.uint32)
+    lib.feelgpu_rplan_host_copy(plan, patches.ctypes.data_as(C.c_void_p), ptr(visits, c_i32p), rows.ctypes.data_as(C.c_void_p),
+                                units.ctypes.data_as(C.c_void_p))
+    lib.feelgpu_rplan_host_free(plan)
+    return patches, visits, rows, units, sizes
+
+
+def position_map(Xh, ia, ja):
+    """pos[e][i][j]: position of the (component-0) column of local node j inside the (component-0) row of local node i"""
+    n, nc = Xh.n, Xh.ncomp
+    pos = np.zeros((Xh.mesh.numElements(), n, n), dtype=np.int64)
+    for e in range(Xh.mesh.numElements()):
+        for i in range(n):
+            r = Xh.l2g[e, i]
+            seg = ja[ia[r]:ia[r + 1]]
+            pos[e, i] = np.searchsorted(seg, Xh.l2g[e, :n])
+    return pos
+
+
+@pytest.mark.parametrize("order,ncomp,kind,m,maxslots,maxvisits", [(1, 1, 1, 4, 200, 60), (2, 1, 1, 3, 700, 50), (2, 1, 0, 3, 4000, 400),
+                                                                   (3, 1, 1, 3, 1500, 40), (2, 3, 2, 3, 3000, 64)])
+def test_plan_interpreted_on_the_host_gives_the_oracle_matrix(order, ncomp, kind, m, maxslots, maxvisits):
+    mesh = fpp.unitCube(m, 0.15, True)
+    Xh = fpp.FunctionSpace(mesh, order, ncomp)
+    ia, ja = Xh.graph()
+    n, nd = Xh.n, Xh.nd
+    patches, visits, rows, units, sizes = build(Xh, ia, maxslots, maxvisits)
+    assert len(patches) > 1, "the limits should cut the mesh into several patches"
+    assert sizes[4] <= maxslots and sizes[5] <= maxvisits
+    pos = position_map(Xh, ia, ja)
+    q = orc.quad_order_form2(kind, order)
+    co = orc.Coeff(lam=2.0, mu=1.5)
+    a = np.full(len(ja), np.nan)
+    seen_units = set()
+    seen_nodes = set()
+    for P in patches:
+        vis = visits[P["visit_off"]:P["visit_off"] + P["nvisit"]]
+        assert len(np.unique(vis)) == len(vis)
+        blk = np.zeros(P["nslots"])
+        used = np.zeros(P["nslots"], dtype=bool)
+        prow = rows[P["row_off"]:P["row_off"] + P["nrows"]]
+        assert (np.diff(prow["nunits"].astype(np.int64)) <= 0).all(), "rows are sorted by descending unit count"
+        local = {}
+        for R in prow:
+            node = int(np.searchsorted(ia, R["base"])) // ncomp
+            assert ia[node * ncomp] == R["base"] and node not in seen_nodes
+            seen_nodes.add(node)
+            assert R["len"] == ia[node * ncomp + 1] - ia[node * ncomp]
+            seg = slice(int(R["off"]), int(R["off"]) + int(R["len"]) * ncomp)
+            assert not used[seg].any(), "row segments of a patch overlap"
+            used[seg] = True
+            for w in units[P["unit_off"] + R["unit0"]:P["unit_off"] + R["unit0"] + R["nunits"]]:
+                v, i = int(w & 0xFFFF), int(w >> 16) & 0xFF
+                e = int(vis[v])
+                assert Xh.l2g[e, i] // ncomp == node and (e, i) not in seen_units
+                seen_units.add((e, i))
+                if e not in local:
+                    local[e] = orc.local_matrix(kind, order, ncomp, q, mesh.xyz[mesh.conn[e]], co)
+                Ae = local[e]
+                for c1 in range(ncomp):
+                    for j in range(n):
+                        for c2 in range(ncomp):
+                            blk[int(R["off"]) + c1 * int(R["len"]) + pos[e, i, j] + c2] += Ae[n * c1 + i, n * c2 + j]
+        for R in prow:
+            cnt = int(R["len"]) * ncomp
+            a[R["base"]:R["base"] + cnt] = blk[R["off"]:R["off"] + cnt]
+    assert len(seen_units) == mesh.numElements() * n and len(seen_nodes) == Xh.nDof() // ncomp
+    assert not np.isnan(a).any(), "a CSR value was never written"
+    ref = orc.form2(kind, order, ncomp, q, mesh.xyz, mesh.conn, Xh.l2g, ia, ja, co)
+    scale = np.abs(ref).max()
+    np.testing.assert_allclose(a, ref, rtol=1e-13, atol=1e-14 * scale)
+
+
+def test_a_row_that_does_not_fit_is_refused():
+    mesh = fpp.unitCube(3, 0.0, False)
+    Xh = fpp.FunctionSpace(mesh, 2, 1)
+    ia, ja = Xh.graph()
+    with pytest.raises(RuntimeError):
+        build(Xh, ia, 8, 400)
