@@ -38,7 +38,10 @@ struct RArgs {
     int accumulate, maxslots, maxvis;
 };
 
-// FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)) (thread = node row), 2: elasticity (thread = (node row, column j))
+// shared-memory add of one double (ATOMS.CAST.SPIN loop in SASS: the hardware has no native fp64 shared atomic)
+__device__ __forceinline__ void sadd(double* p, double v) { atomicAdd(p, v); }
+
+// FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)) (thread = unit), 2: elasticity (thread = (unit, column j))
 template <int ORDER, int FORM>
 __global__ void __launch_bounds__(512, 1)
 k_rplan(const RArgs A)
@@ -54,29 +57,36 @@ k_rplan(const RArgs A)
     const int ntab = FORM == 0 ? N * nq : FORM == 1 ? N * nq * 3 : N * N * 9;
     double* tphif = tab + ntab;                              // [nf][nq] basis of the coefficient field
     int32_t* sE = reinterpret_cast<int32_t*>(tphif + nf * nq);   // [maxvis] element of every visit
+    uint32_t* sRoff = reinterpret_cast<uint32_t*>(sE + maxvis);  // [maxrows][2] row-block offset and length of every row
     const int tid = threadIdx.x;
 
     const uint4* pq = reinterpret_cast<const uint4*>(A.patches + blockIdx.x);
     const uint4 p0 = __ldg(pq), p1 = __ldg(pq + 1);
-    const uint32_t visit_off = p0.x, nvisit = p0.y, row_off = p0.z, nrows = p0.w, unit_off = p1.x, nslots = p1.z;
+    const uint32_t visit_off = p0.x, nvisit = p0.y, row_off = p0.z, nrows = p0.w, unit_off = p1.x, nunits = p1.y, nslots = p1.z;
+    const uint4* rows = A.rows + 2 * (size_t)row_off;
 
-    // ---- tables: [q][j](x3) so that a warp walking (q, j) reads one address (broadcast) ----
+    // ---- tables.  Stiffness: [q][c][j], so that a warp walking (q, j) reads one address (broadcast) and two columns come
+    //      with one 16-byte load; mass: [q][j]; elasticity: the pre-contracted M[i][j][9] ----
     if (FORM == 0) {
         for (int k = tid; k < N * nq; k += blockDim.x) { const int j = k / nq, q = k - j * nq; tab[q * N + j] = A.T.phi[k]; }
     } else if (FORM == 1) {
         for (int k = tid; k < N * nq; k += blockDim.x) {
             const int j = k / nq, q = k - j * nq;
 #pragma unroll
-            for (int c = 0; c < 3; ++c) tab[(q * N + j) * 3 + c] = A.T.dphi[3 * k + c];
+            for (int c = 0; c < 3; ++c) tab[(q * 3 + c) * N + j] = A.T.dphi[3 * k + c];
         }
     } else {
         for (int k = tid; k < N * N * 9; k += blockDim.x) tab[k] = A.T.M9[k];
     }
     for (int k = tid; k < nf * nq; k += blockDim.x) tphif[k] = A.T.phif[k];
     for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;
-    __syncthreads();    // (phase A reads tphif)
+    for (uint32_t r = tid; r < nrows; r += blockDim.x) {
+        const uint4 q0 = __ldg(rows + 2 * r);
+        sRoff[2 * r] = q0.z;
+        sRoff[2 * r + 1] = q0.w;
+    }
 
-    // ---- phase A: geometry and coefficient of every element touching the patch's rows, once (thread = visit) ----
+    // ---- phase A: geometry of every element touching the patch's rows, once (thread = visit) ----
     for (uint32_t v = tid; v < nvisit; v += blockDim.x) {
         const int32_t e = __ldg(&A.visits[visit_off + v]);
         sE[v] = e;
@@ -89,7 +99,6 @@ k_rplan(const RArgs A)
                 for (int b = 0; b < 3; ++b) rec[(a1 * 3 + b) * maxvis + v] = g.B[a1][b];
             rec[9 * maxvis + v] = g.J;
         } else {
-            int r0 = 0;
             if (FORM == 1) {
                 // G = B^T B (the factor J goes with the weights): G_bd = sum_a B_ab B_ad, order 00 01 02 11 12 22
                 int k = 0;
@@ -98,98 +107,111 @@ k_rplan(const RArgs A)
 #pragma unroll
                     for (int d = b; d < 3; ++d)
                         rec[(k++) * maxvis + v] = g.B[0][b] * g.B[0][d] + g.B[1][b] * g.B[1][d] + g.B[2][b] * g.B[2][d];
-                r0 = 6;
             }
-            // prod[q] * k(x_q) = w_q J k(x_q)   (feelpoly/pointsetquadrature.hpp:481-490)
-            for (int q = 0; q < nq; ++q)
-                rec[(r0 + q) * maxvis + v] = (P->w[q] * g.J) * coeff_at(P, tphif, g, e, q, A.l2gf, A.fvals);
+            if (P->coeff_kind == FEELGPU_COEFF_CONST) {
+                const double cj = P->cval[0] * g.J;
+                for (int q = 0; q < nq; ++q) rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = P->w[q] * cj;
+            }
         }
     }
     __syncthreads();
+    // the coefficient at every quadrature point of every visit (thread = (visit, q)): prod[q] * k(x_q) = w_q J k(x_q)
+    // (feelpoly/pointsetquadrature.hpp:481-490); the geometry is formed again from the cached vertices, which is cheaper than
+    // keeping the four vertices of every visit in shared memory
+    if (FORM != 2 && P->coeff_kind != FEELGPU_COEFF_CONST) {
+        for (uint32_t t = tid; t < nvisit * (uint32_t)nq; t += blockDim.x) {
+            const uint32_t v = t / (uint32_t)nq;
+            const int q = (int)(t - v * (uint32_t)nq);
+            const int32_t e = sE[v];
+            Geo g;
+            geo_update(A.xyz, __ldg(&A.conn[e]), g);
+            rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = (P->w[q] * g.J) * coeff_at(P, tphif, g, e, q, A.l2gf, A.fvals);
+        }
+        __syncthreads();
+    }
 
-    // ---- phase B: every row is summed by its own thread(s) ----
-    const uint4* rows = A.rows + 2 * (size_t)row_off;
+    // ---- phase B: one thread per unit (per (unit, column) for the 3x3 blocks) ----
     const uint32_t* units = A.units + unit_off;
     if (FORM != 2) {
-        for (uint32_t r = tid; r < nrows; r += blockDim.x) {
-            const uint4 q1 = __ldg(rows + 2 * r + 1);
-            const uint32_t roff = __ldg(rows + 2 * r).z, unit0 = q1.x, nun = q1.y;
-            double* rb = blk + roff;
-            for (uint32_t u = 0; u < nun; ++u) {
-                const uint32_t w = __ldg(&units[unit0 + u]);
-                const int v = w & 0xFFFF, i = (w >> 16) & 0xFF;
-                const uint16_t* pp = A.pos + ((int64_t)sE[v] * N + i) * N;
-                uint16_t ps[N];
+        for (uint32_t u = tid; u < nunits; u += blockDim.x) {
+            const uint32_t w = __ldg(&units[u]);
+            const int v = w & 0xFFF, i = (w >> 12) & 31;
+            double* rb = blk + sRoff[2 * (w >> 17)];
+            const uint16_t* pp = A.pos + ((int64_t)sE[v] * N + i) * N;
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(pp));     // the positions are needed after the quadrature loop
+            double acc[N];
 #pragma unroll
-                for (int j = 0; j < N; ++j) ps[j] = __ldg(pp + j);
-                double acc[N];
+            for (int j = 0; j < N; ++j) acc[j] = 0.0;
+            if (FORM == 0) {
+                for (int q = 0; q < nq; ++q) {
+                    const double s = rec[q * maxvis + v] * tab[q * N + i];
+                    const double2* tq = reinterpret_cast<const double2*>(tab + q * N);
 #pragma unroll
-                for (int j = 0; j < N; ++j) acc[j] = 0.0;
-                if (FORM == 0) {
-                    for (int q = 0; q < nq; ++q) {
-                        const double s = rec[q * maxvis + v] * tab[q * N + i];
-                        const double* tq = tab + q * N;
-#pragma unroll
-                        for (int j = 0; j < N; ++j) acc[j] = fma(s, tq[j], acc[j]);
-                    }
-                } else {
-                    const double G00 = rec[0 * maxvis + v], G01 = rec[1 * maxvis + v], G02 = rec[2 * maxvis + v],
-                                 G11 = rec[3 * maxvis + v], G12 = rec[4 * maxvis + v], G22 = rec[5 * maxvis + v];
-                    for (int q = 0; q < nq; ++q) {
-                        const double wk = rec[(6 + q) * maxvis + v];
-                        const double* gi = tab + (q * N + i) * 3;
-                        const double a0 = gi[0], a1 = gi[1], a2 = gi[2];
-                        // s = w_q J k_q G grad^(phi_i)(q)
-                        const double s0 = wk * (G00 * a0 + G01 * a1 + G02 * a2);
-                        const double s1 = wk * (G01 * a0 + G11 * a1 + G12 * a2);
-                        const double s2 = wk * (G02 * a0 + G12 * a1 + G22 * a2);
-                        const double* tq = tab + q * N * 3;
-#pragma unroll
-                        for (int j = 0; j < N; ++j)
-                            acc[j] = fma(s2, tq[3 * j + 2], fma(s1, tq[3 * j + 1], fma(s0, tq[3 * j], acc[j])));
+                    for (int j = 0; j < N / 2; ++j) {
+                        const double2 t = tq[j];
+                        acc[2 * j] = fma(s, t.x, acc[2 * j]);
+                        acc[2 * j + 1] = fma(s, t.y, acc[2 * j + 1]);
                     }
                 }
+            } else {
+                const double G00 = rec[0 * maxvis + v], G01 = rec[1 * maxvis + v], G02 = rec[2 * maxvis + v],
+                             G11 = rec[3 * maxvis + v], G12 = rec[4 * maxvis + v], G22 = rec[5 * maxvis + v];
+                for (int q = 0; q < nq; ++q) {
+                    const double wk = rec[(6 + q) * maxvis + v];
+                    const double* tq = tab + q * 3 * N;
+                    const double a0 = tq[i], a1 = tq[N + i], a2 = tq[2 * N + i];
+                    // s = w_q J k_q G grad^(phi_i)(q)
+                    const double s0 = wk * (G00 * a0 + G01 * a1 + G02 * a2);
+                    const double s1 = wk * (G01 * a0 + G11 * a1 + G12 * a2);
+                    const double s2 = wk * (G02 * a0 + G12 * a1 + G22 * a2);
+                    const double2* t0 = reinterpret_cast<const double2*>(tq);
+                    const double2* t1 = reinterpret_cast<const double2*>(tq + N);
+                    const double2* t2 = reinterpret_cast<const double2*>(tq + 2 * N);
 #pragma unroll
-                for (int j = 0; j < N; ++j) rb[ps[j]] += acc[j];
+                    for (int j = 0; j < N / 2; ++j) {
+                        const double2 x = t0[j], y = t1[j], z = t2[j];
+                        acc[2 * j] = fma(s2, z.x, fma(s1, y.x, fma(s0, x.x, acc[2 * j])));
+                        acc[2 * j + 1] = fma(s2, z.y, fma(s1, y.y, fma(s0, x.y, acc[2 * j + 1])));
+                    }
+                }
             }
+#pragma unroll
+            for (int j = 0; j < N; ++j) sadd(rb + __ldg(pp + j), acc[j]);
         }
     } else {
         const double lambda = P->lambda, mu = P->mu;
-        for (uint32_t t = tid; t < nrows * N; t += blockDim.x) {
-            const uint32_t r = t / N;
-            const int j = (int)(t - r * N);
-            const uint4 q0 = __ldg(rows + 2 * r), q1 = __ldg(rows + 2 * r + 1);
-            const uint32_t roff = q0.z, len = q0.w, unit0 = q1.x, nun = q1.y;
-            for (uint32_t u = 0; u < nun; ++u) {
-                const uint32_t w = __ldg(&units[unit0 + u]);
-                const int v = w & 0xFFFF, i = (w >> 16) & 0xFF;
-                const uint32_t p0c = __ldg(A.pos + ((int64_t)sE[v] * N + i) * N + j);
-                double B[3][3];
+        for (uint32_t t = tid; t < nunits * N; t += blockDim.x) {
+            const uint32_t u = t / N;
+            const int j = (int)(t - u * N);
+            const uint32_t w = __ldg(&units[u]);
+            const int v = w & 0xFFF, i = (w >> 12) & 31;
+            const uint32_t roff = sRoff[2 * (w >> 17)], len = sRoff[2 * (w >> 17) + 1];
+            const uint32_t p0c = __ldg(A.pos + ((int64_t)sE[v] * N + i) * N + j);
+            double B[3][3];
 #pragma unroll
-                for (int k = 0; k < 9; ++k) B[k / 3][k % 3] = rec[k * maxvis + v];
-                const double J = rec[9 * maxvis + v];
-                // Pm[c][d] = sum_q w_q (grad phi_i)_c (grad phi_j)_d = (B M B^T)[c][d], M = sum_q w_q grad^phi_i grad^phi_j^T
-                const double* M = tab + (i * N + j) * 9;
-                double BD[3][3], Pm[3][3];
+            for (int k = 0; k < 9; ++k) B[k / 3][k % 3] = rec[k * maxvis + v];
+            const double J = rec[9 * maxvis + v];
+            // Pm[c][d] = sum_q w_q (grad phi_i)_c (grad phi_j)_d = (B M B^T)[c][d], M = sum_q w_q grad^phi_i grad^phi_j^T
+            const double* M = tab + (i * N + j) * 9;
+            double BD[3][3], Pm[3][3];
 #pragma unroll
-                for (int a1 = 0; a1 < 3; ++a1)
+            for (int a1 = 0; a1 < 3; ++a1)
 #pragma unroll
-                    for (int d = 0; d < 3; ++d) BD[a1][d] = B[a1][0] * M[0 * 3 + d] + B[a1][1] * M[1 * 3 + d] + B[a1][2] * M[2 * 3 + d];
+                for (int d = 0; d < 3; ++d) BD[a1][d] = B[a1][0] * M[0 * 3 + d] + B[a1][1] * M[1 * 3 + d] + B[a1][2] * M[2 * 3 + d];
 #pragma unroll
-                for (int a1 = 0; a1 < 3; ++a1)
+            for (int a1 = 0; a1 < 3; ++a1)
 #pragma unroll
-                    for (int c2 = 0; c2 < 3; ++c2) Pm[a1][c2] = BD[a1][0] * B[c2][0] + BD[a1][1] * B[c2][1] + BD[a1][2] * B[c2][2];
-                const double tr = Pm[0][0] + Pm[1][1] + Pm[2][2];
-                // block (c1,c2) = J [lambda Pm_c1c2 + mu Pm_c2c1 + mu delta tr Pm]   (feelvf/inner.hpp:374-420)
+                for (int c2 = 0; c2 < 3; ++c2) Pm[a1][c2] = BD[a1][0] * B[c2][0] + BD[a1][1] * B[c2][1] + BD[a1][2] * B[c2][2];
+            const double tr = Pm[0][0] + Pm[1][1] + Pm[2][2];
+            // block (c1,c2) = J [lambda Pm_c1c2 + mu Pm_c2c1 + mu delta tr Pm]   (feelvf/inner.hpp:374-420)
 #pragma unroll
-                for (int c1 = 0; c1 < 3; ++c1) {
-                    double* rb = blk + roff + c1 * len + p0c;
+            for (int c1 = 0; c1 < 3; ++c1) {
+                double* rb = blk + roff + c1 * len + p0c;
 #pragma unroll
-                    for (int c2 = 0; c2 < 3; ++c2) {
-                        double val = lambda * Pm[c1][c2] + mu * Pm[c2][c1];
-                        if (c1 == c2) val += mu * tr;
-                        rb[c2] += J * val;
-                    }
+                for (int c2 = 0; c2 < 3; ++c2) {
+                    double val = lambda * Pm[c1][c2] + mu * Pm[c2][c1];
+                    if (c1 == c2) val += mu * tr;
+                    sadd(rb + c2, J * val);
                 }
             }
         }
@@ -228,7 +250,8 @@ size_t rplan_smem_bytes(const RPlan* p, int form, int nq, int nf)
     const int n = p->n;
     const size_t nrec = form == 0 ? nq : form == 1 ? 6 + nq : 10;
     const size_t ntab = form == 0 ? (size_t)n * nq : form == 1 ? (size_t)n * nq * 3 : (size_t)n * n * 9;
-    return sizeof(double) * ((size_t)p->maxslots + nrec * p->maxvisits + ntab + (size_t)nf * nq) + sizeof(int32_t) * (size_t)p->maxvisits + 16;
+    return sizeof(double) * ((size_t)p->maxslots + nrec * p->maxvisits + ntab + (size_t)nf * nq) +
+           sizeof(int32_t) * ((size_t)p->maxvisits + 2 * (size_t)p->maxrows) + 16;
 }
 
 int env_int(const char* name, int dflt)

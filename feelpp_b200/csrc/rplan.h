@@ -12,13 +12,16 @@
 //           (feelpoly/geomap.hpp:2320-2355,1971-1991), the coefficient at every quadrature point (cst / idv / expr at
 //           xReal), i.e. prod[q]*k(x_q) = w_q J k(x_q) (feelpoly/pointsetquadrature.hpp:481-490) -> shared memory.
 //   unit  = (row r, element e containing r's node): the row of e's local matrix that belongs to r
-//           (feelvf/bilinearformcontext.hpp:585-589).  Phase B: ONE thread owns row r (or (r, column j) for product
-//           spaces, whose rows are 9 times as long): it walks the units of r, forms the unit's row by the quadrature sum
-//           (feelpoly/pointsetquadrature.hpp:403-416) and adds it into its own segment of the row block through the
-//           element->CSR position map.  Rows are disjoint segments, so the adds are plain shared-memory read-modify-writes:
-//           no atomics, a fixed summation order (bit-reproducible), and every CSR value leaves the SM exactly once.
+//           (feelvf/bilinearformcontext.hpp:585-589).  Phase B: one thread per unit (per (unit, column j) for the 3x3 blocks
+//           of product spaces) forms the unit's row by the quadrature sum (feelpoly/pointsetquadrature.hpp:403-416) and adds
+//           it into row r's segment of the row block through the element->CSR position map.  Units are dealt in round
+//           order (the k-th unit of every row), so the lanes of a warp work on different rows and all lanes are busy
+//           whatever the row lengths (a vertex row has ~24 units, a face row 2); units of one row that run at the same time
+//           in different warps meet on the columns they share, hence the adds are shared-memory atomics -- inside the SM,
+//           never in L2.  Every CSR value leaves the SM exactly once.
 //   Phase C: the row block is streamed to the CSR value array (coalesced, one contiguous piece per node row).
 //
+// The row-thread name stays from the first version (thread = row), which left the SM waiting for its longest row.
 // The plan is small (one 32-bit word per unit, one element id per visit, 32 bytes per node row) and is built in one pass
 // over the node -> element adjacency, so its setup cost is a fraction of the entity plan's.
 #pragma once
@@ -41,7 +44,8 @@ struct RPlanRow {                // 32 bytes
     uint32_t pad[2];
 };
 static_assert(sizeof(RPlanPatch) == 32 && sizeof(RPlanRow) == 32, "read as two uint4");
-// unit word: visit index inside the patch (bits 0-15) | local dof i of the row's node in that element (bits 16-23)
+// unit word: visit index inside the patch (bits 0-11) | local dof i of the row's node in that element (bits 12-16) | row
+// index inside the patch (bits 17-31).  Units are stored in round order: the k-th unit of every row that has one, k = 0, 1, ...
 
 struct RPlanHost {
     int order = 0, n = 0, ncomp = 1;

@@ -57,7 +57,8 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
     plan.maxvisits = maxvisits;
     plan.maxrows = maxrows;
     if (nd != n * ncomp) { plan.error = "row-thread plan: nd != n * ncomp"; return false; }
-    if (maxvisits > 65536 || n > 255) { plan.error = "row-thread plan: unit word overflow"; return false; }
+    if (maxvisits > 4096 || n > 32) { plan.error = "row-thread plan: unit word overflow"; return false; }
+    maxrows = std::min(maxrows, 32767);
     const int64_t nNode = nRows / ncomp;
     // ---- node -> (element, local dof) adjacency ----
     std::vector<int64_t> nptr((size_t)nNode + 1, 0);
@@ -212,6 +213,7 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
                 R.nunits = byn[r].first;
                 R.pad[0] = R.pad[1] = 0;
                 off += R.len * (uint32_t)ncomp;
+                un += R.nunits;
                 for (int64_t q = nptr[(size_t)node]; q < nptr[(size_t)node + 1]; ++q) {
                     const int32_t e = uelt[(size_t)q];
                     if (stp[(size_t)e] != (int32_t)p) {
@@ -220,9 +222,17 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
                         plan.visits[(size_t)P.visit_off + nv] = e;
                         ++nv;
                     }
-                    plan.units[(size_t)P.unit_off + un++] = (uint32_t)slot[(size_t)e] | ((uint32_t)uloc[(size_t)q] << 16);
                 }
             }
+            // unit words in "round" order: the k-th unit of every row that has one, k = 0, 1, ...: the lanes of a warp work
+            // on different rows (their adds into the row block do not meet) and every lane has work whatever the row lengths
+            uint32_t w = 0;
+            for (uint32_t k = 0; !byn.empty() && k < byn[0].first; ++k)
+                for (size_t r = 0; r < byn.size() && byn[r].first > k; ++r) {
+                    const int64_t q = nptr[(size_t)byn[r].second] + k;
+                    plan.units[(size_t)P.unit_off + w++] =
+                        (uint32_t)slot[(size_t)uelt[(size_t)q]] | ((uint32_t)uloc[(size_t)q] << 12) | ((uint32_t)r << 17);
+                }
         }
     });
     return true;

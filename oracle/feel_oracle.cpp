@@ -462,6 +462,160 @@ int64_t oracle_doftable(int64_t nPts, int64_t nElt, const int32_t* conn, int ord
     return next_free;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// DofTable / DataMap / GraphCSR in MPI mode, restated for one rank of a partitioned mesh (test infrastructure: pins the
+// partitioned numbering and pattern of feelpp_b200/parallel.py).
+//   * every rank builds its table by first touch over its ACTIVE elements in local element order (same loop as above,
+//     feeldiscr/doftable.hpp:1802-1940);
+//   * a dof is a ghost on rank p when a lower rank has an element containing its entity: procMin over the ranks sharing
+//     the point / edge / face (feeldiscr/doftablempi.hpp:138-200 updateDofOnVertices/Edges, :548 "IdProcessOfGhost<myRank");
+//   * M_first_df_globalcluster = prefix sums of the active counts (doftablempi.hpp:593-621); active dofs get
+//     firstGlobIndex + running index in local order (:623-635); ghosts receive their owner's cluster id;
+//   * the local ids are then reordered: active dofs before, ghost dofs after, each group keeping its order
+//     (feeldiscr/doftable.hpp:1975-1992).
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+typedef std::tuple<int, int64_t, int64_t, int64_t, int> ekey_t;   // (entity dim, sorted vertex ids..., l)
+
+void element_keys(const int32_t* v, int64_t e, int order, std::vector<ekey_t>& out)
+{
+    const int nPerEdge = order - 1, nPerFace = (order - 1) * (order - 2) / 2, nPerVol = (order - 1) * (order - 2) * (order - 3) / 6;
+    out.clear();
+    for (int i = 0; i < 4; ++i) out.emplace_back(0, v[i], -1, -1, 0);
+    for (int ed = 0; ed < 6 && nPerEdge > 0; ++ed) {
+        const int64_t i1 = v[E2P[ed][0]], i2 = v[E2P[ed][1]];
+        for (int l = 0; l < nPerEdge; ++l) out.emplace_back(1, std::min(i1, i2), std::max(i1, i2), -1, i1 > i2 ? nPerEdge - 1 - l : l);
+    }
+    for (int f = 0; f < 4 && nPerFace > 0; ++f) {
+        std::array<int64_t, 3> fv = {v[F2P[f][0]], v[F2P[f][1]], v[F2P[f][2]]};
+        std::sort(fv.begin(), fv.end());
+        for (int l = 0; l < nPerFace; ++l) out.emplace_back(2, fv[0], fv[1], fv[2], l);
+    }
+    for (int l = 0; l < nPerVol; ++l) out.emplace_back(3, e, -1, -1, l);
+}
+
+struct MpiTables {
+    std::map<ekey_t, int> owner;                         // procMin
+    std::vector<std::vector<ekey_t>> touch;              // per rank: entities in first-touch order
+    std::vector<std::map<ekey_t, int64_t>> active_idx;   // per rank: running index among its active entities
+    std::vector<int64_t> first;                          // per rank: first cluster NODE id
+};
+
+void mpi_tables(int64_t nElt, const int32_t* conn, const int32_t* part, int nparts, int order, MpiTables& M)
+{
+    std::vector<ekey_t> keys;
+    M.touch.assign(nparts, {});
+    M.active_idx.assign(nparts, {});
+    std::vector<std::set<ekey_t>> seen(nparts);
+    for (int64_t e = 0; e < nElt; ++e) {
+        const int p = part[e];
+        element_keys(conn + 4 * e, e, order, keys);
+        for (const ekey_t& k : keys) {
+            auto it = M.owner.find(k);
+            if (it == M.owner.end()) M.owner.emplace(k, p);
+            else if (p < it->second) it->second = p;
+            if (seen[p].insert(k).second) M.touch[p].push_back(k);
+        }
+    }
+    M.first.assign(nparts + 1, 0);
+    for (int p = 0; p < nparts; ++p) {
+        int64_t run = 0;
+        for (const ekey_t& k : M.touch[p])
+            if (M.owner[k] == p) M.active_idx[p].emplace(k, run++);
+        M.first[p + 1] = M.first[p] + run;
+    }
+}
+} // namespace
+
+extern "C" {
+
+// local table of `rank`: l2g[nMine][nd] (elements of the rank in global element order; local ids: active first, ghosts
+// after), p2c[nWithGhost] global-cluster ids, ghost_owner[nWithGhost - nOwned] (dof level), first_dof[nparts+1].
+// Arrays sized by the caller (nMine*nd bounds the dofs).  Returns nWithGhost.
+int64_t oracle_doftable_mpi(int64_t nElt, const int32_t* conn, const int32_t* part, int nparts, int rank, int order, int ncomp,
+                            int32_t* l2g, int64_t* nOwned, int64_t* p2c, int32_t* ghost_owner, int64_t* first_dof)
+{
+    MpiTables M;
+    mpi_tables(nElt, conn, part, nparts, order, M);
+    const int n = nloc(order), nd = n * ncomp;
+    for (int p = 0; p <= nparts; ++p) first_dof[p] = M.first[p] * ncomp;
+    std::map<ekey_t, int64_t> local;                     // entity -> local node id
+    int64_t nact = 0, ngh = 0;
+    for (const ekey_t& k : M.touch[rank])
+        if (M.owner[k] == rank) local[k] = nact++;
+    for (const ekey_t& k : M.touch[rank])
+        if (M.owner[k] != rank) {
+            const int64_t id = nact + ngh++;
+            local[k] = id;
+            const int q = M.owner[k];
+            for (int c = 0; c < ncomp; ++c) {
+                p2c[id * ncomp + c] = (M.first[q] + M.active_idx[q][k]) * ncomp + c;
+                ghost_owner[(id - nact) * ncomp + c] = q;
+            }
+        }
+    for (const auto& kv : M.active_idx[rank])
+        for (int c = 0; c < ncomp; ++c) p2c[kv.second * ncomp + c] = (M.first[rank] + kv.second) * ncomp + c;
+    std::vector<ekey_t> keys;
+    int64_t m = 0;
+    for (int64_t e = 0; e < nElt; ++e) {
+        if (part[e] != rank) continue;
+        element_keys(conn + 4 * e, e, order, keys);
+        for (int i = 0; i < n; ++i)
+            for (int c = 0; c < ncomp; ++c) l2g[m * nd + n * c + i] = (int32_t)(local[keys[i]] * ncomp + c);
+        ++m;
+    }
+    *nOwned = nact * ncomp;
+    return (nact + ngh) * ncomp;
+}
+
+// local graph of `rank` (Stencil::computeGraph + GraphCSR::close in MPI mode, feelalg/graphcsr.cpp:800-951): rows = local
+// dofs; an OWNED row holds the columns of every element of the mesh containing its entity (the neighbours' ghost rows were
+// shipped to it), a GHOST row those of the rank's own elements; columns = global-cluster ids, ascending.
+int64_t oracle_graph_mpi(int64_t nElt, const int32_t* conn, const int32_t* part, int nparts, int rank, int order, int ncomp,
+                         int64_t nWithGhost, const int32_t* l2g, int64_t* ia, int64_t** ja_out)
+{
+    MpiTables M;
+    mpi_tables(nElt, conn, part, nparts, order, M);
+    const int n = nloc(order), nd = n * ncomp;
+    std::map<ekey_t, int64_t> local;                     // as above, rebuilt from the rank's l2g
+    std::vector<ekey_t> keys;
+    {
+        int64_t m = 0;
+        for (int64_t e = 0; e < nElt; ++e) {
+            if (part[e] != rank) continue;
+            element_keys(conn + 4 * e, e, order, keys);
+            for (int i = 0; i < n; ++i) local[keys[i]] = l2g[m * nd + i] / ncomp;
+            ++m;
+        }
+    }
+    std::vector<std::set<int64_t>> rows((size_t)nWithGhost);
+    std::vector<int64_t> cols(nd);
+    for (int64_t e = 0; e < nElt; ++e) {
+        element_keys(conn + 4 * e, e, order, keys);
+        for (int j = 0; j < n; ++j) {
+            const int q = M.owner[keys[j]];
+            for (int c = 0; c < ncomp; ++c) cols[n * c + j] = (M.first[q] + M.active_idx[q][keys[j]]) * ncomp + c;
+        }
+        for (int i = 0; i < n; ++i) {
+            auto it = local.find(keys[i]);
+            if (it == local.end()) continue;
+            const bool owned = M.owner[keys[i]] == rank;
+            if (!owned && part[e] != rank) continue;     // ghost rows only carry the rank's own contributions
+            for (int c = 0; c < ncomp; ++c) rows[(size_t)(it->second * ncomp + c)].insert(cols.begin(), cols.end());
+        }
+    }
+    ia[0] = 0;
+    for (int64_t r = 0; r < nWithGhost; ++r) ia[r + 1] = ia[r] + (int64_t)rows[(size_t)r].size();
+    int64_t* ja = (int64_t*)std::malloc(sizeof(int64_t) * (size_t)std::max<int64_t>(ia[nWithGhost], 1));
+    int64_t k = 0;
+    for (int64_t r = 0; r < nWithGhost; ++r)
+        for (int64_t c : rows[(size_t)r]) ja[k++] = c;
+    *ja_out = ja;
+    return ia[nWithGhost];
+}
+
+} // extern "C"
+
 // Stencil::computeGraph, Pattern::COUPLED (feeldiscr/stencil.hpp:1560-1634): for every element, every test dof row
 // receives the sorted set of all trial dofs of the element (std::set per row, feelalg/graphcsr.hpp:77);
 // addMissingZeroEntriesDiagonal (feelalg/graphcsr.cpp:633-659); close() lays rows out with ascending columns

@@ -53,6 +53,12 @@ int64_t oracle_doftable(int64_t nPts, int64_t nElt, const int32_t* conn, int ord
 /* Stencil::computeGraph (COUPLED) + GraphCSR::close, one process: ia[ndof+1], ja[nnz] ascending. ja malloc'd */
 int64_t oracle_graph(int64_t nElt, int nd, const int32_t* l2g, int64_t ndof, int64_t* ia, int64_t** ja);
 void oracle_free(void* p);
+/* the same in MPI mode for one rank of an element partition (feeldiscr/doftablempi.hpp:138-200,548,593-636,
+ * feeldiscr/doftable.hpp:1975-1992, feelalg/graphcsr.cpp:800-951): see feel_oracle.cpp */
+int64_t oracle_doftable_mpi(int64_t nElt, const int32_t* conn, const int32_t* part, int nparts, int rank, int order, int ncomp,
+                            int32_t* l2g, int64_t* nOwned, int64_t* p2c, int32_t* ghost_owner, int64_t* first_dof);
+int64_t oracle_graph_mpi(int64_t nElt, const int32_t* conn, const int32_t* part, int nparts, int rank, int order, int ncomp,
+                         int64_t nWithGhost, const int32_t* l2g, int64_t* ia, int64_t** ja);
 
 /* element loop: a[nnz] += local matrices (MatSetValues ADD_VALUES semantics; binary search per row)           */
 int oracle_form2(int kind, int order, int ncomp, int quad_order,

@@ -109,6 +109,43 @@ def graph(l2g, ndof):
     return ia, ja
 
 
+def doftable_mpi(conn, part, nparts, rank, order, ncomp=1):
+    """DofTable + DataMap of one rank in MPI mode: (l2g[nMine][nd], nOwned, p2c[nWithGhost], ghost_owner, first_dof[nparts+1])"""
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    part = np.ascontiguousarray(part, dtype=np.int32)
+    L = lib()
+    L.oracle_doftable_mpi.argtypes = [C.c_int64, c_i32p, c_i32p, C.c_int, C.c_int, C.c_int, C.c_int, c_i32p, c_i64p, c_i64p,
+                                      c_i32p, c_i64p]
+    L.oracle_doftable_mpi.restype = C.c_int64
+    nd = nloc(order) * ncomp
+    nmine = int((part == rank).sum())
+    l2g = np.empty((nmine, nd), dtype=np.int32)
+    p2c = np.empty(max(nmine * nd, 1), dtype=np.int64)
+    gho = np.empty(max(nmine * nd, 1), dtype=np.int32)
+    first = np.empty(nparts + 1, dtype=np.int64)
+    nown = C.c_int64()
+    nwg = L.oracle_doftable_mpi(conn.shape[0], _p(conn, c_i32p), _p(part, c_i32p), nparts, rank, order, ncomp, _p(l2g, c_i32p),
+                                C.byref(nown), _p(p2c, c_i64p), _p(gho, c_i32p), _p(first, c_i64p))
+    return l2g, int(nown.value), p2c[:nwg].copy(), gho[:nwg - nown.value].copy(), first
+
+
+def graph_mpi(conn, part, nparts, rank, order, ncomp, l2g, nwithghost):
+    conn = np.ascontiguousarray(conn, dtype=np.int32)
+    part = np.ascontiguousarray(part, dtype=np.int32)
+    l2g = np.ascontiguousarray(l2g, dtype=np.int32)
+    L = lib()
+    L.oracle_graph_mpi.argtypes = [C.c_int64, c_i32p, c_i32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, c_i32p, c_i64p,
+                                   C.POINTER(c_i64p)]
+    L.oracle_graph_mpi.restype = C.c_int64
+    ia = np.empty(nwithghost + 1, dtype=np.int64)
+    jap = c_i64p()
+    nnz = L.oracle_graph_mpi(conn.shape[0], _p(conn, c_i32p), _p(part, c_i32p), nparts, rank, order, ncomp, nwithghost,
+                             _p(l2g, c_i32p), _p(ia, c_i64p), C.byref(jap))
+    ja = np.ctypeslib.as_array(jap, shape=(max(nnz, 1),))[:nnz].copy()
+    L.oracle_free(jap)
+    return ia, ja
+
+
 class Coeff:
     """keeps the numpy buffers of an oracle_coeff alive"""
 

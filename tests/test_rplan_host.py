@@ -1,6 +1,6 @@
 """The row-thread plan (feelpp_b200/csrc/rplan.h) interpreted on the CPU: every (row, element) unit of the mesh occurs
 exactly once, in the row of its node; patches respect their limits; and walking the plan exactly as the kernel does --
-thread = row, its units in plan order, each unit's row of the oracle's local matrix added through the element->CSR position
+one thread per unit in the plan's round order, each unit's row of the oracle's local matrix added through the element->CSR position
 map into the row's segment of the patch's row block, the block copied to the CSR array -- reproduces the oracle matrix.
 The GPU parity tests then only have to show that the kernel is a faithful interpreter with its own quadrature rows."""
 import ctypes as C
@@ -73,16 +73,28 @@ def test_plan_interpreted_on_the_host_gives_the_oracle_matrix(order, ncomp, kind
         prow = rows[P["row_off"]:P["row_off"] + P["nrows"]]
         assert (np.diff(prow["nunits"].astype(np.int64)) <= 0).all(), "rows are sorted by descending unit count"
         local = {}
+        rownode = []
         for R in prow:
             node = int(np.searchsorted(ia, R["base"])) // ncomp
             assert ia[node * ncomp] == R["base"] and node not in seen_nodes
             seen_nodes.add(node)
+            rownode.append(node)
             assert R["len"] == ia[node * ncomp + 1] - ia[node * ncomp]
             seg = slice(int(R["off"]), int(R["off"]) + int(R["len"]) * ncomp)
             assert not used[seg].any(), "row segments of a patch overlap"
             used[seg] = True
-            for w in units[P["unit_off"] + R["unit0"]:P["unit_off"] + R["unit0"] + R["nunits"]]:
-                v, i = int(w & 0xFFFF), int(w >> 16) & 0xFF
+        assert int(prow["nunits"].sum()) == P["nunits"]
+        per_row = np.zeros(len(prow), dtype=np.int64)
+        pu = units[P["unit_off"]:P["unit_off"] + P["nunits"]]
+        # round order: the lanes of a warp (32 consecutive units) work on different rows while enough rows have a k-th unit
+        for k0 in range(0, len(pu), 32):
+            rr = (pu[k0:k0 + 32] >> 17).astype(np.int64)
+            if int((prow["nunits"] > per_row.max()).sum()) >= 64:
+                assert len(np.unique(rr)) == len(rr)
+            for w in pu[k0:k0 + 32]:
+                v, i, r = int(w & 0xFFF), int(w >> 12) & 31, int(w >> 17)
+                R, node = prow[r], rownode[r]
+                per_row[r] += 1
                 e = int(vis[v])
                 assert Xh.l2g[e, i] // ncomp == node and (e, i) not in seen_units
                 seen_units.add((e, i))
@@ -93,6 +105,7 @@ def test_plan_interpreted_on_the_host_gives_the_oracle_matrix(order, ncomp, kind
                     for j in range(n):
                         for c2 in range(ncomp):
                             blk[int(R["off"]) + c1 * int(R["len"]) + pos[e, i, j] + c2] += Ae[n * c1 + i, n * c2 + j]
+        assert np.array_equal(per_row, prow["nunits"])
         for R in prow:
             cnt = int(R["len"]) * ncomp
             a[R["base"]:R["base"] + cnt] = blk[R["off"]:R["off"] + cnt]
