@@ -254,6 +254,30 @@ def reference_arm(args):
     print(json.dumps(line))
 
 
+def pin_to_gpu_numa(local):
+    """bind this rank's threads to the CPUs of its GPU's NUMA node BEFORE any pinned host buffer is allocated: page-locked
+    memory is then placed on that node (first touch) and the D2H/H2D copies of the end-to-end step do not cross sockets.
+    Returns a short description for run_info."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        if node < 0:
+            return "gpu %s: no NUMA node reported" % bus
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if not allowed:
+            return "gpu %s on NUMA node %d: none of its CPUs is in this process' affinity mask" % (bus, node)
+        os.sched_setaffinity(0, allowed)
+        return "gpu %s on NUMA node %d: bound to %d of its CPUs" % (bus, node, len(allowed))
+    except Exception as ex:      # best effort: containers may hide sysfs
+        return "not pinned (%s)" % type(ex).__name__
+
+
 class ClockSampler:
     """samples nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)"""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -306,6 +330,7 @@ def gpu_arm(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    numa = pin_to_gpu_numa(local)
     if world > 1 and args.mesh:
         raise SystemExit("--mesh runs on one GPU (the multi-GPU line is the cube)")
     if world > 1:
@@ -516,7 +541,7 @@ def gpu_arm(args):
                         "%d GPUs: %s, owned row blocks; every step hands the ghost rows to their owners (%s)"
                         % (world, part_name, "stored over NVLink peer memory by the assembly kernel, NCCL barrier, "
                            "owner-side add" if a.peer else "NCCL send/recv of the ghost rows, owner-side add")),
-                    "setup": info}
+                    "host_affinity": numa, "setup": info}
         line = {"metric": metric_name(args), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",

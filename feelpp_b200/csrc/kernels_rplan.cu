@@ -27,6 +27,7 @@ struct RArgs {
     const int32_t* visits;
     const uint4* rows;
     const uint32_t* units;
+    const uint32_t* rounds;
     const double* xyz;
     const int4* conn;
     const uint16_t* pos;
@@ -35,48 +36,75 @@ struct RArgs {
     const int32_t* l2gf;
     const double* fvals;
     double* a;
-    int accumulate, maxslots, maxvis;
+    int accumulate, maxslots, maxvis, maxrows;
 };
 
-// shared-memory add of one double (ATOMS.CAST.SPIN loop in SASS: the hardware has no native fp64 shared atomic)
-__device__ __forceinline__ void sadd(double* p, double v) { atomicAdd(p, v); }
+// Reference tables in constant memory: every lane of a warp reads the same entry, so they ride as constant-bank operands
+// of the DFMAs instead of occupying the shared-memory pipe (one shared-memory double per DFMA caps the kernel at a quarter
+// of the FP64 rate).  Layout: stiffness / elasticity [q][c][j] (c = reference direction), mass [q][j]; then the weights.
+#define RTAB_MAX (3 * FEELGPU_MAX_NQ * FEELGPU_MAX_NLOC)
+__constant__ double c_rtab[RTAB_MAX];
+__constant__ double c_rw[FEELGPU_MAX_NQ];
 
-// FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)) (thread = unit), 2: elasticity (thread = (unit, column j))
-template <int ORDER, int FORM>
+// adds of a batch of units into the row block, round by round: units of one round belong to different rows, so the adds of
+// a round are plain read-modify-writes; `add` performs this thread's adds.  rnd = shared copy of the patch's round offsets.
+template <class F>
+__device__ __forceinline__ void add_in_rounds(const uint32_t* rnd, int nrounds, uint32_t u, bool active, uint32_t b0, uint32_t b1, F add)
+{
+    // rounds present in the batch [b0, b1): binary searches in the (short) offset table, the same for every thread
+    auto round_of = [&](uint32_t x) {
+        int lo = 0, hi = nrounds;                 // last k with rnd[k] <= x
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (rnd[mid] <= x) lo = mid;
+            else hi = mid;
+        }
+        return lo;
+    };
+    const int kmin = round_of(b0), kmax = round_of(b1 - 1);
+    const int myk = active ? round_of(u) : -1;
+    for (int k = kmin; k <= kmax; ++k) {
+        if (k == myk) add();
+        __syncthreads();
+    }
+}
+
+// FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)), 2: elasticity.  Thread = unit.  NQ > 0: quadrature points known at
+// compile time, tables in constant memory, loops unrolled; NQ = 0: any nq, tables in shared memory (mass / stiffness only).
+template <int ORDER, int FORM, int NQ>
 __global__ void __launch_bounds__(512, 1)
 k_rplan(const RArgs A)
 {
     constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
     extern __shared__ double sm[];
     const FormParams* __restrict__ P = A.P;
-    const int nq = P->nq, nf = P->nf, maxvis = A.maxvis;
+    const int nq = NQ > 0 ? NQ : P->nq, nf = P->nf, maxvis = A.maxvis;
     const int nrec = FORM == 0 ? nq : FORM == 1 ? 6 + nq : 10;
     double* blk = sm;                                        // [maxslots] the patch's row block
     double* rec = blk + A.maxslots;                          // [nrec][maxvis] per-visit records
-    double* tab = rec + (size_t)nrec * maxvis;               // reference tables (layout per form, below)
-    const int ntab = FORM == 0 ? N * nq : FORM == 1 ? N * nq * 3 : N * N * 9;
+    double* tab = rec + (size_t)nrec * maxvis;               // reference tables, [q][c][j] / [q][j] (read with a per-lane row dof)
+    const int ntab = FORM == 0 ? N * nq : N * nq * 3;
     double* tphif = tab + ntab;                              // [nf][nq] basis of the coefficient field
     int32_t* sE = reinterpret_cast<int32_t*>(tphif + nf * nq);   // [maxvis] element of every visit
     uint32_t* sRoff = reinterpret_cast<uint32_t*>(sE + maxvis);  // [maxrows][2] row-block offset and length of every row
+    uint32_t* sRnd = sRoff + 2 * A.maxrows;                  // [maxrounds + 1] first unit of every round
     const int tid = threadIdx.x;
 
     const uint4* pq = reinterpret_cast<const uint4*>(A.patches + blockIdx.x);
     const uint4 p0 = __ldg(pq), p1 = __ldg(pq + 1);
-    const uint32_t visit_off = p0.x, nvisit = p0.y, row_off = p0.z, nrows = p0.w, unit_off = p1.x, nunits = p1.y, nslots = p1.z;
+    const uint32_t visit_off = p0.x, nvisit = p0.y, row_off = p0.z, nrows = p0.w, unit_off = p1.x, nunits = p1.y, nslots = p1.z,
+                   round_off = p1.w;
     const uint4* rows = A.rows + 2 * (size_t)row_off;
+    const int nrounds = nrows ? (int)__ldg(rows + 1).y : 0;  // rows are sorted by descending unit count
 
-    // ---- tables.  Stiffness: [q][c][j], so that a warp walking (q, j) reads one address (broadcast) and two columns come
-    //      with one 16-byte load; mass: [q][j]; elasticity: the pre-contracted M[i][j][9] ----
     if (FORM == 0) {
         for (int k = tid; k < N * nq; k += blockDim.x) { const int j = k / nq, q = k - j * nq; tab[q * N + j] = A.T.phi[k]; }
-    } else if (FORM == 1) {
+    } else {
         for (int k = tid; k < N * nq; k += blockDim.x) {
             const int j = k / nq, q = k - j * nq;
 #pragma unroll
             for (int c = 0; c < 3; ++c) tab[(q * 3 + c) * N + j] = A.T.dphi[3 * k + c];
         }
-    } else {
-        for (int k = tid; k < N * N * 9; k += blockDim.x) tab[k] = A.T.M9[k];
     }
     for (int k = tid; k < nf * nq; k += blockDim.x) tphif[k] = A.T.phif[k];
     for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;
@@ -85,6 +113,7 @@ k_rplan(const RArgs A)
         sRoff[2 * r] = q0.z;
         sRoff[2 * r + 1] = q0.w;
     }
+    for (int k = tid; k <= nrounds; k += blockDim.x) sRnd[k] = __ldg(&A.rounds[round_off + k]);
 
     // ---- phase A: geometry of every element touching the patch's rows, once (thread = visit) ----
     for (uint32_t v = tid; v < nvisit; v += blockDim.x) {
@@ -130,89 +159,152 @@ k_rplan(const RArgs A)
         __syncthreads();
     }
 
-    // ---- phase B: one thread per unit (per (unit, column) for the 3x3 blocks) ----
+    // ---- phase B: one thread per unit, batches of blockDim.x units in round order ----
     const uint32_t* units = A.units + unit_off;
-    if (FORM != 2) {
-        for (uint32_t u = tid; u < nunits; u += blockDim.x) {
-            const uint32_t w = __ldg(&units[u]);
-            const int v = w & 0xFFF, i = (w >> 12) & 31;
-            double* rb = blk + sRoff[2 * (w >> 17)];
-            const uint16_t* pp = A.pos + ((int64_t)sE[v] * N + i) * N;
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(pp));     // the positions are needed after the quadrature loop
+    for (uint32_t b0 = 0; b0 < nunits; b0 += blockDim.x) {
+        const uint32_t b1 = min(b0 + blockDim.x, nunits), u = b0 + tid;
+        const bool active = u < b1;
+        const uint32_t w = active ? __ldg(&units[u]) : 0u;
+        const int v = w & 0xFFF, i = (w >> 12) & 31;
+        const uint32_t roff = sRoff[2 * (w >> 17)], rlen = sRoff[2 * (w >> 17) + 1];
+        const uint16_t* pp = A.pos + ((int64_t)sE[v] * N + i) * N;
+        if (FORM != 2) {
             double acc[N];
 #pragma unroll
             for (int j = 0; j < N; ++j) acc[j] = 0.0;
-            if (FORM == 0) {
-                for (int q = 0; q < nq; ++q) {
-                    const double s = rec[q * maxvis + v] * tab[q * N + i];
-                    const double2* tq = reinterpret_cast<const double2*>(tab + q * N);
+            if (active) {
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(pp));     // the positions are needed after the quadrature loop
+                if (FORM == 0) {
+                    if (NQ > 0) {
 #pragma unroll
-                    for (int j = 0; j < N / 2; ++j) {
-                        const double2 t = tq[j];
-                        acc[2 * j] = fma(s, t.x, acc[2 * j]);
-                        acc[2 * j + 1] = fma(s, t.y, acc[2 * j + 1]);
+                        for (int q = 0; q < NQ; ++q) {
+                            const double s = rec[q * maxvis + v] * tab[q * N + i];
+#pragma unroll
+                            for (int j = 0; j < N; ++j) acc[j] = fma(s, c_rtab[q * N + j], acc[j]);
+                        }
+                    } else {
+                        for (int q = 0; q < nq; ++q) {
+                            const double s = rec[q * maxvis + v] * tab[q * N + i];
+                            const double2* tq = reinterpret_cast<const double2*>(tab + q * N);
+#pragma unroll
+                            for (int j = 0; j < N / 2; ++j) {
+                                const double2 t = tq[j];
+                                acc[2 * j] = fma(s, t.x, acc[2 * j]);
+                                acc[2 * j + 1] = fma(s, t.y, acc[2 * j + 1]);
+                            }
+                        }
                     }
-                }
-            } else {
-                const double G00 = rec[0 * maxvis + v], G01 = rec[1 * maxvis + v], G02 = rec[2 * maxvis + v],
-                             G11 = rec[3 * maxvis + v], G12 = rec[4 * maxvis + v], G22 = rec[5 * maxvis + v];
-                for (int q = 0; q < nq; ++q) {
-                    const double wk = rec[(6 + q) * maxvis + v];
-                    const double* tq = tab + q * 3 * N;
-                    const double a0 = tq[i], a1 = tq[N + i], a2 = tq[2 * N + i];
-                    // s = w_q J k_q G grad^(phi_i)(q)
-                    const double s0 = wk * (G00 * a0 + G01 * a1 + G02 * a2);
-                    const double s1 = wk * (G01 * a0 + G11 * a1 + G12 * a2);
-                    const double s2 = wk * (G02 * a0 + G12 * a1 + G22 * a2);
-                    const double2* t0 = reinterpret_cast<const double2*>(tq);
-                    const double2* t1 = reinterpret_cast<const double2*>(tq + N);
-                    const double2* t2 = reinterpret_cast<const double2*>(tq + 2 * N);
+                } else {
+                    const double G00 = rec[0 * maxvis + v], G01 = rec[1 * maxvis + v], G02 = rec[2 * maxvis + v],
+                                 G11 = rec[3 * maxvis + v], G12 = rec[4 * maxvis + v], G22 = rec[5 * maxvis + v];
+                    auto point = [&](int q, double& s0, double& s1, double& s2) {
+                        const double wk = rec[(6 + q) * maxvis + v];
+                        const double* tq = tab + q * 3 * N;
+                        const double a0 = tq[i], a1 = tq[N + i], a2 = tq[2 * N + i];
+                        // s = w_q J k_q G grad^(phi_i)(q)
+                        s0 = wk * (G00 * a0 + G01 * a1 + G02 * a2);
+                        s1 = wk * (G01 * a0 + G11 * a1 + G12 * a2);
+                        s2 = wk * (G02 * a0 + G12 * a1 + G22 * a2);
+                    };
+                    if (NQ > 0) {
 #pragma unroll
-                    for (int j = 0; j < N / 2; ++j) {
-                        const double2 x = t0[j], y = t1[j], z = t2[j];
-                        acc[2 * j] = fma(s2, z.x, fma(s1, y.x, fma(s0, x.x, acc[2 * j])));
-                        acc[2 * j + 1] = fma(s2, z.y, fma(s1, y.y, fma(s0, x.y, acc[2 * j + 1])));
+                        for (int q = 0; q < NQ; ++q) {
+                            double s0, s1, s2;
+                            point(q, s0, s1, s2);
+#pragma unroll
+                            for (int j = 0; j < N; ++j)
+                                acc[j] = fma(s2, c_rtab[(q * 3 + 2) * N + j], fma(s1, c_rtab[(q * 3 + 1) * N + j], fma(s0, c_rtab[q * 3 * N + j], acc[j])));
+                        }
+                    } else {
+                        for (int q = 0; q < nq; ++q) {
+                            double s0, s1, s2;
+                            point(q, s0, s1, s2);
+                            const double* tq = tab + q * 3 * N;
+                            const double2* t0 = reinterpret_cast<const double2*>(tq);
+                            const double2* t1 = reinterpret_cast<const double2*>(tq + N);
+                            const double2* t2 = reinterpret_cast<const double2*>(tq + 2 * N);
+#pragma unroll
+                            for (int j = 0; j < N / 2; ++j) {
+                                const double2 x = t0[j], y = t1[j], z = t2[j];
+                                acc[2 * j] = fma(s2, z.x, fma(s1, y.x, fma(s0, x.x, acc[2 * j])));
+                                acc[2 * j + 1] = fma(s2, z.y, fma(s1, y.y, fma(s0, x.y, acc[2 * j + 1])));
+                            }
+                        }
                     }
                 }
             }
+            add_in_rounds(sRnd, nrounds, u, active, b0, b1, [&] {
+                double* rb = blk + roff;
 #pragma unroll
-            for (int j = 0; j < N; ++j) sadd(rb + __ldg(pp + j), acc[j]);
-        }
-    } else {
-        const double lambda = P->lambda, mu = P->mu;
-        for (uint32_t t = tid; t < nunits * N; t += blockDim.x) {
-            const uint32_t u = t / N;
-            const int j = (int)(t - u * N);
-            const uint32_t w = __ldg(&units[u]);
-            const int v = w & 0xFFF, i = (w >> 12) & 31;
-            const uint32_t roff = sRoff[2 * (w >> 17)], len = sRoff[2 * (w >> 17) + 1];
-            const uint32_t p0c = __ldg(A.pos + ((int64_t)sE[v] * N + i) * N + j);
-            double B[3][3];
+                for (int j = 0; j < N; ++j) rb[__ldg(pp + j)] += acc[j];
+            });
+        } else if (NQ > 0) {
+            // elasticity: physical gradients of the row function at the quadrature points, then column by column the 3x3 block
+            // a_cd = sum_q w_q J (grad phi_i)_c (grad phi_j)_d ; block(c1,c2) = lambda a_c1c2 + mu a_c2c1 + mu delta tr a
+            // (feelvf/inner.hpp:374-420).  The blocks of a unit (N x 9 values) are added round by round as they are formed:
+            // one round loop per column.
+            double B[3][3], pi[NQ > 0 ? NQ : 1][3];
+            double J = 0.0;
+            if (active) {
 #pragma unroll
-            for (int k = 0; k < 9; ++k) B[k / 3][k % 3] = rec[k * maxvis + v];
-            const double J = rec[9 * maxvis + v];
-            // Pm[c][d] = sum_q w_q (grad phi_i)_c (grad phi_j)_d = (B M B^T)[c][d], M = sum_q w_q grad^phi_i grad^phi_j^T
-            const double* M = tab + (i * N + j) * 9;
-            double BD[3][3], Pm[3][3];
+                for (int k = 0; k < 9; ++k) B[k / 3][k % 3] = rec[k * maxvis + v];
+                J = rec[9 * maxvis + v];
 #pragma unroll
-            for (int a1 = 0; a1 < 3; ++a1)
+                for (int q = 0; q < NQ; ++q) {
+                    const double* tq = tab + q * 3 * N;
+                    const double a0 = tq[i], a1 = tq[N + i], a2 = tq[2 * N + i];
+                    const double wj = c_rw[q] * J;
 #pragma unroll
-                for (int d = 0; d < 3; ++d) BD[a1][d] = B[a1][0] * M[0 * 3 + d] + B[a1][1] * M[1 * 3 + d] + B[a1][2] * M[2 * 3 + d];
-#pragma unroll
-            for (int a1 = 0; a1 < 3; ++a1)
-#pragma unroll
-                for (int c2 = 0; c2 < 3; ++c2) Pm[a1][c2] = BD[a1][0] * B[c2][0] + BD[a1][1] * B[c2][1] + BD[a1][2] * B[c2][2];
-            const double tr = Pm[0][0] + Pm[1][1] + Pm[2][2];
-            // block (c1,c2) = J [lambda Pm_c1c2 + mu Pm_c2c1 + mu delta tr Pm]   (feelvf/inner.hpp:374-420)
-#pragma unroll
-            for (int c1 = 0; c1 < 3; ++c1) {
-                double* rb = blk + roff + c1 * len + p0c;
-#pragma unroll
-                for (int c2 = 0; c2 < 3; ++c2) {
-                    double val = lambda * Pm[c1][c2] + mu * Pm[c2][c1];
-                    if (c1 == c2) val += mu * tr;
-                    sadd(rb + c2, J * val);
+                    for (int c = 0; c < 3; ++c) pi[q][c] = wj * (B[c][0] * a0 + B[c][1] * a1 + B[c][2] * a2);
                 }
+            }
+            const double lambda = P->lambda, mu = P->mu;
+            // columns in chunks of JC: the 9 x JC values of a chunk wait in registers for the thread's round
+            constexpr int JC = 3;
+#pragma unroll
+            for (int j0 = 0; j0 < N; j0 += JC) {
+                double blkv[JC][9];
+                if (active) {
+#pragma unroll
+                    for (int jj = 0; jj < JC; ++jj) {
+                        const int j = j0 + jj;
+                        if (j >= N) break;
+                        double a[3][3];
+#pragma unroll
+                        for (int c = 0; c < 9; ++c) a[c / 3][c % 3] = 0.0;
+#pragma unroll
+                        for (int q = 0; q < NQ; ++q) {
+                            double pj[3];
+#pragma unroll
+                            for (int d = 0; d < 3; ++d)
+                                pj[d] = B[d][0] * c_rtab[q * 3 * N + j] + B[d][1] * c_rtab[(q * 3 + 1) * N + j] + B[d][2] * c_rtab[(q * 3 + 2) * N + j];
+#pragma unroll
+                            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                                for (int d = 0; d < 3; ++d) a[c][d] = fma(pi[q][c], pj[d], a[c][d]);
+                        }
+                        const double tr = a[0][0] + a[1][1] + a[2][2];
+#pragma unroll
+                        for (int c1 = 0; c1 < 3; ++c1)
+#pragma unroll
+                            for (int c2 = 0; c2 < 3; ++c2)
+                                blkv[jj][c1 * 3 + c2] = lambda * a[c1][c2] + mu * a[c2][c1] + (c1 == c2 ? mu * tr : 0.0);
+                    }
+                }
+                add_in_rounds(sRnd, nrounds, u, active, b0, b1, [&] {
+#pragma unroll
+                    for (int jj = 0; jj < JC; ++jj) {
+                        const int j = j0 + jj;
+                        if (j >= N) break;
+                        const uint32_t p0c = __ldg(pp + j);
+#pragma unroll
+                        for (int c1 = 0; c1 < 3; ++c1) {
+                            double* rb = blk + roff + c1 * rlen + p0c;
+#pragma unroll
+                            for (int c2 = 0; c2 < 3; ++c2) rb[c2] += blkv[jj][c1 * 3 + c2];
+                        }
+                    }
+                });
             }
         }
     }
@@ -249,9 +341,9 @@ size_t rplan_smem_bytes(const RPlan* p, int form, int nq, int nf)
 {
     const int n = p->n;
     const size_t nrec = form == 0 ? nq : form == 1 ? 6 + nq : 10;
-    const size_t ntab = form == 0 ? (size_t)n * nq : form == 1 ? (size_t)n * nq * 3 : (size_t)n * n * 9;
+    const size_t ntab = form == 0 ? (size_t)n * nq : (size_t)n * nq * 3;
     return sizeof(double) * ((size_t)p->maxslots + nrec * p->maxvisits + ntab + (size_t)nf * nq) +
-           sizeof(int32_t) * ((size_t)p->maxvisits + 2 * (size_t)p->maxrows) + 16;
+           sizeof(int32_t) * ((size_t)p->maxvisits + 2 * (size_t)p->maxrows + (size_t)p->maxrounds + 2) + 16;
 }
 
 int env_int(const char* name, int dflt)
@@ -289,9 +381,10 @@ int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     p->order = hp.order;
     p->n = hp.n;
     p->ncomp = hp.ncomp;
-    p->maxslots = hp.maxpatch_slots;         // what the kernel has to provide: the largest patch, not the limit
-    p->maxvisits = std::max(hp.maxpatch_visits, 1);
+    p->maxslots = (hp.maxpatch_slots + 1) & ~1;      // what the kernel has to provide: the largest patch, not the limit;
+    p->maxvisits = (std::max(hp.maxpatch_visits, 1) + 1) & ~1;   // even counts keep the shared arrays behind them 16-byte aligned
     p->maxrows = hp.maxpatch_rows;
+    p->maxrounds = hp.maxpatch_rounds;
     p->npatch = (int64_t)hp.patches.size();
     p->nunits = hp.nunits;
     p->nvisits = hp.nvisits;
@@ -302,6 +395,7 @@ int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     if (err == cudaSuccess) err = upload(&p->d_visits, hp.visits, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_rows, hp.rows, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_units, hp.units, p->bytes);
+    if (err == cudaSuccess) err = upload(&p->d_rounds, hp.rounds, p->bytes);
     pat->rplan = p;
     if (err != cudaSuccess) {
         ctx->last_error = std::string("row-thread plan upload: ") + cudaGetErrorString(err);
@@ -319,6 +413,7 @@ void feelgpu_rplan_destroy(feelgpu_pattern_t pat)
     cudaFree(p->d_visits);
     cudaFree(p->d_rows);
     cudaFree(p->d_units);
+    cudaFree(p->d_rounds);
     delete p;
     pat->rplan = nullptr;
 }
@@ -351,8 +446,9 @@ bool feelgpu_rplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* des
     if (!p || !pat->d_pos) return false;
     const int form = rplan_form(desc);
     if (desc->tables.n != p->n || desc->tables.nq < 1 || desc->tables.nq > FEELGPU_MAX_NQ) return false;
-    if (form == 2 ? p->ncomp != 3 : p->ncomp != 1) return false;    // product spaces: elasticity; mass/stiffness blocks go through the entity plan
+    if (form == 2 ? (p->ncomp != 3 || p->order > 2) : p->ncomp != 1) return false;    // product spaces: elasticity; mass/stiffness blocks go through the entity plan
     if (form != 0 && !desc->tables.dphi) return false;
+    if (form == 2 && desc->tables.nq != 1 && desc->tables.nq != 4) return false;   // elasticity: compile-time rules only (P1: 1 point, P2: 4)
     const int nf = desc->coeff.kind == FEELGPU_COEFF_FIELD ? desc->tables.nf : 0;
     return rplan_smem_bytes(p, form, desc->tables.nq, nf) <= 227 * 1024;
 }
@@ -372,6 +468,7 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     A.visits = p->d_visits;
     A.rows = reinterpret_cast<const uint4*>(p->d_rows);
     A.units = p->d_units;
+    A.rounds = p->d_rounds;
     A.xyz = m->d_xyz;
     A.conn = m->d_conn;
     A.pos = pat->d_pos;
@@ -385,27 +482,54 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     A.accumulate = accumulate;
     A.maxslots = p->maxslots;
     A.maxvis = p->maxvisits;
+    A.maxrows = p->maxrows;
     const size_t sh = rplan_smem_bytes(p, form, hp.nq, hp.nf);
     const int grid = (int)p->npatch;
     if (grid == 0) return FEELGPU_OK;
     const int threads = std::min(512, std::max(64, env_int("FEELGPU_RPLAN_THREADS", 512)));
-#define PLAUNCH(O, F)                                                                                                      \
-    do {                                                                                                                   \
-        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rplan<O, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-        k_rplan<O, F><<<grid, threads, sh, s>>>(A);                                                                        \
+    // constant-memory copy of the tables in the kernel's layout (stream-ordered; one context drives one stream at a time)
+    const int n = p->n, nq = hp.nq;
+    const bool fixed = !env_int("FEELGPU_RPLAN_NO_CONST", 0) && (nq == 1 || nq == 4 || nq == 5 || nq == 11 || nq == 14 || nq == 24);
+    if (fixed || form == 2) {
+        std::vector<double> ct((size_t)(form == 0 ? n * nq : 3 * n * nq));
+        for (int j = 0; j < n; ++j)
+            for (int q = 0; q < nq; ++q) {
+                if (form == 0) ct[(size_t)q * n + j] = desc->tables.phi[j * nq + q];
+                else
+                    for (int c = 0; c < 3; ++c) ct[((size_t)q * 3 + c) * n + j] = desc->tables.dphi[(j * nq + q) * 3 + c];
+            }
+        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rtab, ct.data(), ct.size() * sizeof(double), 0, cudaMemcpyHostToDevice, s));
+        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rw, desc->tables.w, nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
+    }
+#define PLAUNCH(O, F, Q)                                                                                                       \
+    do {                                                                                                                       \
+        FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rplan<O, F, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));  \
+        k_rplan<O, F, Q><<<grid, threads, sh, s>>>(A);                                                                         \
+    } while (0)
+#define PQ(O, F)                                                  \
+    do {                                                          \
+        if (!fixed) PLAUNCH(O, F, 0);                             \
+        else switch (nq) {                                        \
+            case 1: PLAUNCH(O, F, 1); break;                      \
+            case 4: PLAUNCH(O, F, 4); break;                      \
+            case 5: PLAUNCH(O, F, 5); break;                      \
+            case 11: PLAUNCH(O, F, 11); break;                    \
+            case 14: PLAUNCH(O, F, 14); break;                    \
+            default: PLAUNCH(O, F, 24); break;                    \
+        }                                                         \
     } while (0)
     switch (p->order * 3 + form) {
-    case 3: PLAUNCH(1, 0); break;
-    case 4: PLAUNCH(1, 1); break;
-    case 5: PLAUNCH(1, 2); break;
-    case 6: PLAUNCH(2, 0); break;
-    case 7: PLAUNCH(2, 1); break;
-    case 8: PLAUNCH(2, 2); break;
-    case 9: PLAUNCH(3, 0); break;
-    case 10: PLAUNCH(3, 1); break;
-    case 11: PLAUNCH(3, 2); break;
-    default: ctx->last_error = "row-thread plan: unsupported order"; return FEELGPU_ERR_UNSUPPORTED;
+    case 3: PQ(1, 0); break;
+    case 4: PQ(1, 1); break;
+    case 5: PLAUNCH(1, 2, 1); break;
+    case 6: PQ(2, 0); break;
+    case 7: PQ(2, 1); break;
+    case 8: if (nq == 4) PLAUNCH(2, 2, 4); else PLAUNCH(2, 2, 1); break;
+    case 9: PQ(3, 0); break;
+    case 10: PQ(3, 1); break;
+    default: ctx->last_error = "row-thread plan: unsupported order / form"; return FEELGPU_ERR_UNSUPPORTED;
     }
+#undef PQ
 #undef PLAUNCH
     ctx->launches++;
     FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
@@ -431,11 +555,12 @@ int feelgpu_rplan_host_build(int order, int ncomp, int64_t nElt, const int32_t* 
     sizes[4] = hp->maxpatch_slots;
     sizes[5] = hp->maxpatch_visits;
     sizes[6] = hp->maxpatch_rows;
-    sizes[7] = 0;
+    sizes[7] = (int64_t)hp->rounds.size();
     return ok ? FEELGPU_OK : FEELGPU_ERR_UNSUPPORTED;
 }
 
-int feelgpu_rplan_host_copy(void* plan, void* patches /*32 B each*/, int32_t* visits, void* rows /*32 B each*/, uint32_t* units)
+int feelgpu_rplan_host_copy(void* plan, void* patches /*32 B each*/, int32_t* visits, void* rows /*32 B each*/, uint32_t* units,
+                            uint32_t* rounds)
 {
     if (!plan) return FEELGPU_ERR_ARG;
     const RPlanHost* hp = static_cast<const RPlanHost*>(plan);
@@ -443,6 +568,7 @@ int feelgpu_rplan_host_copy(void* plan, void* patches /*32 B each*/, int32_t* vi
     if (visits) std::memcpy(visits, hp->visits.data(), hp->visits.size() * sizeof(int32_t));
     if (rows) std::memcpy(rows, hp->rows.data(), hp->rows.size() * sizeof(RPlanRow));
     if (units) std::memcpy(units, hp->units.data(), hp->units.size() * sizeof(uint32_t));
+    if (rounds) std::memcpy(rounds, hp->rounds.data(), hp->rounds.size() * sizeof(uint32_t));
     return FEELGPU_OK;
 }
 
