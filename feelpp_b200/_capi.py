@@ -67,7 +67,7 @@ GPU_SYMBOLS = {
     "feelgpu_eplan_host_coefficients": [C.c_int, C.POINTER(Tables), C.c_int, c_dblp, c_dblp],
     "feelgpu_rplan_host_build": [C.c_int, C.c_int, C.c_int64, c_i32p, C.c_int64, c_dblp, c_i32p, C.c_int64, c_i64p, C.c_int,
                                  C.c_int, C.c_int, C.POINTER(C.c_void_p), c_i64p],
-    "feelgpu_rplan_host_copy": [C.c_void_p, C.c_void_p, c_i32p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "feelgpu_rplan_host_copy": [C.c_void_p, C.c_void_p, c_i32p, C.c_void_p, C.c_void_p],
     "feelgpu_rplan_host_free": [C.c_void_p],
     "feelgpu_form2_assemble": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form1_assemble": [C.c_void_p, C.POINTER(Form1Desc), C.c_int, C.c_void_p, C.c_void_p],

@@ -27,7 +27,6 @@ struct RArgs {
     const int32_t* visits;
     const uint4* rows;
     const uint32_t* units;
-    const uint32_t* rounds;
     const double* xyz;
     const int4* conn;
     const uint16_t* pos;
@@ -46,27 +45,45 @@ struct RArgs {
 __constant__ double c_rtab[RTAB_MAX];
 __constant__ double c_rw[FEELGPU_MAX_NQ];
 
-// adds of a batch of units into the row block, round by round: units of one round belong to different rows, so the adds of
-// a round are plain read-modify-writes; `add` performs this thread's adds.  rnd = shared copy of the patch's round offsets.
-template <class F>
-__device__ __forceinline__ void add_in_rounds(const uint32_t* rnd, int nrounds, uint32_t u, bool active, uint32_t b0, uint32_t b1, F add)
+// shared-memory add of one double (a compare-and-swap loop in SASS, ATOMS.CAST.SPIN: no native fp64 shared atomic)
+__device__ __forceinline__ void sadd(double* p, double v) { atomicAdd(p, v); }
+
+// the closed-form coefficient with its program in shared memory (the interpreter of device_common.cuh reads the program
+// from global memory: one dependent load per operation)
+__device__ double eval_expr_sm(int len, const int* ops, const double* consts, double x, double y, double z)
 {
-    // rounds present in the batch [b0, b1): binary searches in the (short) offset table, the same for every thread
-    auto round_of = [&](uint32_t x) {
-        int lo = 0, hi = nrounds;                 // last k with rnd[k] <= x
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (rnd[mid] <= x) lo = mid;
-            else hi = mid;
+    double st[16];
+    int sp = 0;
+    for (int k = 0; k < len; ++k) {
+        switch (ops[k]) {
+        case FEELGPU_OP_X: st[sp++] = x; break;
+        case FEELGPU_OP_Y: st[sp++] = y; break;
+        case FEELGPU_OP_Z: st[sp++] = z; break;
+        case FEELGPU_OP_CONST: st[sp++] = consts[k]; break;
+        case FEELGPU_OP_ADD: --sp; st[sp - 1] += st[sp]; break;
+        case FEELGPU_OP_SUB: --sp; st[sp - 1] -= st[sp]; break;
+        case FEELGPU_OP_MUL: --sp; st[sp - 1] *= st[sp]; break;
+        case FEELGPU_OP_DIV: --sp; st[sp - 1] /= st[sp]; break;
+        case FEELGPU_OP_NEG: st[sp - 1] = -st[sp - 1]; break;
+        case FEELGPU_OP_SIN: st[sp - 1] = sin(st[sp - 1]); break;
+        case FEELGPU_OP_COS: st[sp - 1] = cos(st[sp - 1]); break;
+        case FEELGPU_OP_EXP: st[sp - 1] = exp(st[sp - 1]); break;
+        case FEELGPU_OP_LOG: st[sp - 1] = log(st[sp - 1]); break;
+        case FEELGPU_OP_SQRT: st[sp - 1] = sqrt(st[sp - 1]); break;
+        case FEELGPU_OP_POW: {
+            --sp;
+            const double ex = st[sp], b = st[sp - 1];
+            // small integer exponents by multiplication (x^2 is what pow returns, correctly rounded; 3 and 4 differ by an ulp)
+            if (ex == 2.0) st[sp - 1] = b * b;
+            else if (ex == 3.0) st[sp - 1] = b * b * b;
+            else if (ex == 4.0) { const double b2 = b * b; st[sp - 1] = b2 * b2; }
+            else st[sp - 1] = pow(b, ex);
+            break;
         }
-        return lo;
-    };
-    const int kmin = round_of(b0), kmax = round_of(b1 - 1);
-    const int myk = active ? round_of(u) : -1;
-    for (int k = kmin; k <= kmax; ++k) {
-        if (k == myk) add();
-        __syncthreads();
+        default: break;
+        }
     }
+    return st[0];
 }
 
 // FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)), 2: elasticity.  Thread = unit.  NQ > 0: quadrature points known at
@@ -87,15 +104,14 @@ k_rplan(const RArgs A)
     double* tphif = tab + ntab;                              // [nf][nq] basis of the coefficient field
     int32_t* sE = reinterpret_cast<int32_t*>(tphif + nf * nq);   // [maxvis] element of every visit
     uint32_t* sRoff = reinterpret_cast<uint32_t*>(sE + maxvis);  // [maxrows][2] row-block offset and length of every row
-    uint32_t* sRnd = sRoff + 2 * A.maxrows;                  // [maxrounds + 1] first unit of every round
+    int* sOps = reinterpret_cast<int*>(sRoff + 2 * A.maxrows);    // [2 * FEELGPU_EXPR_MAX_LEN] the coefficient program ...
+    double* sCst = reinterpret_cast<double*>(sOps + 2 * FEELGPU_EXPR_MAX_LEN);   // ... and its constants (8-byte aligned: the counts before are even)
     const int tid = threadIdx.x;
 
     const uint4* pq = reinterpret_cast<const uint4*>(A.patches + blockIdx.x);
     const uint4 p0 = __ldg(pq), p1 = __ldg(pq + 1);
-    const uint32_t visit_off = p0.x, nvisit = p0.y, row_off = p0.z, nrows = p0.w, unit_off = p1.x, nunits = p1.y, nslots = p1.z,
-                   round_off = p1.w;
+    const uint32_t visit_off = p0.x, nvisit = p0.y, row_off = p0.z, nrows = p0.w, unit_off = p1.x, nunits = p1.y, nslots = p1.z;
     const uint4* rows = A.rows + 2 * (size_t)row_off;
-    const int nrounds = nrows ? (int)__ldg(rows + 1).y : 0;  // rows are sorted by descending unit count
 
     if (FORM == 0) {
         for (int k = tid; k < N * nq; k += blockDim.x) { const int j = k / nq, q = k - j * nq; tab[q * N + j] = A.T.phi[k]; }
@@ -113,7 +129,7 @@ k_rplan(const RArgs A)
         sRoff[2 * r] = q0.z;
         sRoff[2 * r + 1] = q0.w;
     }
-    for (int k = tid; k <= nrounds; k += blockDim.x) sRnd[k] = __ldg(&A.rounds[round_off + k]);
+    for (int k = tid; k < P->expr_len; k += blockDim.x) { sOps[k] = P->expr_ops[k]; sCst[k] = P->expr_consts[k]; }
 
     // ---- phase A: geometry of every element touching the patch's rows, once (thread = visit) ----
     for (uint32_t v = tid; v < nvisit; v += blockDim.x) {
@@ -154,7 +170,14 @@ k_rplan(const RArgs A)
             const int32_t e = sE[v];
             Geo g;
             geo_update(A.xyz, __ldg(&A.conn[e]), g);
-            rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = (P->w[q] * g.J) * coeff_at(P, tphif, g, e, q, A.l2gf, A.fvals);
+            double kq;
+            if (P->coeff_kind == FEELGPU_COEFF_EXPR) {
+                double x[3];
+                xreal(g, &P->xi[3 * q], x);
+                kq = eval_expr_sm(P->expr_len, sOps, sCst, x[0], x[1], x[2]);
+            } else
+                kq = coeff_at(P, tphif, g, e, q, A.l2gf, A.fvals);
+            rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = (P->w[q] * g.J) * kq;
         }
         __syncthreads();
     }
@@ -233,11 +256,11 @@ k_rplan(const RArgs A)
                     }
                 }
             }
-            add_in_rounds(sRnd, nrounds, u, active, b0, b1, [&] {
+            if (active) {
                 double* rb = blk + roff;
 #pragma unroll
-                for (int j = 0; j < N; ++j) rb[__ldg(pp + j)] += acc[j];
-            });
+                for (int j = 0; j < N; ++j) sadd(rb + __ldg(pp + j), acc[j]);
+            }
         } else if (NQ > 0) {
             // elasticity: physical gradients of the row function at the quadrature points, then column by column the 3x3 block
             // a_cd = sum_q w_q J (grad phi_i)_c (grad phi_j)_d ; block(c1,c2) = lambda a_c1c2 + mu a_c2c1 + mu delta tr a
@@ -259,7 +282,7 @@ k_rplan(const RArgs A)
                 }
             }
             const double lambda = P->lambda, mu = P->mu;
-            // columns in chunks of JC: the 9 x JC values of a chunk wait in registers for the thread's round
+            // columns in chunks of JC (register budget)
             constexpr int JC = 3;
 #pragma unroll
             for (int j0 = 0; j0 < N; j0 += JC) {
@@ -291,7 +314,7 @@ k_rplan(const RArgs A)
                                 blkv[jj][c1 * 3 + c2] = lambda * a[c1][c2] + mu * a[c2][c1] + (c1 == c2 ? mu * tr : 0.0);
                     }
                 }
-                add_in_rounds(sRnd, nrounds, u, active, b0, b1, [&] {
+                if (active) {
 #pragma unroll
                     for (int jj = 0; jj < JC; ++jj) {
                         const int j = j0 + jj;
@@ -301,10 +324,10 @@ k_rplan(const RArgs A)
                         for (int c1 = 0; c1 < 3; ++c1) {
                             double* rb = blk + roff + c1 * rlen + p0c;
 #pragma unroll
-                            for (int c2 = 0; c2 < 3; ++c2) rb[c2] += blkv[jj][c1 * 3 + c2];
+                            for (int c2 = 0; c2 < 3; ++c2) sadd(rb + c2, blkv[jj][c1 * 3 + c2]);
                         }
                     }
-                });
+                }
             }
         }
     }
@@ -343,7 +366,7 @@ size_t rplan_smem_bytes(const RPlan* p, int form, int nq, int nf)
     const size_t nrec = form == 0 ? nq : form == 1 ? 6 + nq : 10;
     const size_t ntab = form == 0 ? (size_t)n * nq : (size_t)n * nq * 3;
     return sizeof(double) * ((size_t)p->maxslots + nrec * p->maxvisits + ntab + (size_t)nf * nq) +
-           sizeof(int32_t) * ((size_t)p->maxvisits + 2 * (size_t)p->maxrows + (size_t)p->maxrounds + 2) + 16;
+           sizeof(int32_t) * ((size_t)p->maxvisits + 2 * (size_t)p->maxrows + 2 * FEELGPU_EXPR_MAX_LEN) + sizeof(double) * FEELGPU_EXPR_MAX_LEN + 16;
 }
 
 int env_int(const char* name, int dflt)
@@ -384,7 +407,6 @@ int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     p->maxslots = (hp.maxpatch_slots + 1) & ~1;      // what the kernel has to provide: the largest patch, not the limit;
     p->maxvisits = (std::max(hp.maxpatch_visits, 1) + 1) & ~1;   // even counts keep the shared arrays behind them 16-byte aligned
     p->maxrows = hp.maxpatch_rows;
-    p->maxrounds = hp.maxpatch_rounds;
     p->npatch = (int64_t)hp.patches.size();
     p->nunits = hp.nunits;
     p->nvisits = hp.nvisits;
@@ -395,7 +417,6 @@ int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     if (err == cudaSuccess) err = upload(&p->d_visits, hp.visits, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_rows, hp.rows, p->bytes);
     if (err == cudaSuccess) err = upload(&p->d_units, hp.units, p->bytes);
-    if (err == cudaSuccess) err = upload(&p->d_rounds, hp.rounds, p->bytes);
     pat->rplan = p;
     if (err != cudaSuccess) {
         ctx->last_error = std::string("row-thread plan upload: ") + cudaGetErrorString(err);
@@ -413,7 +434,6 @@ void feelgpu_rplan_destroy(feelgpu_pattern_t pat)
     cudaFree(p->d_visits);
     cudaFree(p->d_rows);
     cudaFree(p->d_units);
-    cudaFree(p->d_rounds);
     delete p;
     pat->rplan = nullptr;
 }
@@ -468,7 +488,6 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     A.visits = p->d_visits;
     A.rows = reinterpret_cast<const uint4*>(p->d_rows);
     A.units = p->d_units;
-    A.rounds = p->d_rounds;
     A.xyz = m->d_xyz;
     A.conn = m->d_conn;
     A.pos = pat->d_pos;
@@ -555,12 +574,11 @@ int feelgpu_rplan_host_build(int order, int ncomp, int64_t nElt, const int32_t* 
     sizes[4] = hp->maxpatch_slots;
     sizes[5] = hp->maxpatch_visits;
     sizes[6] = hp->maxpatch_rows;
-    sizes[7] = (int64_t)hp->rounds.size();
+    sizes[7] = 0;
     return ok ? FEELGPU_OK : FEELGPU_ERR_UNSUPPORTED;
 }
 
-int feelgpu_rplan_host_copy(void* plan, void* patches /*32 B each*/, int32_t* visits, void* rows /*32 B each*/, uint32_t* units,
-                            uint32_t* rounds)
+int feelgpu_rplan_host_copy(void* plan, void* patches /*32 B each*/, int32_t* visits, void* rows /*32 B each*/, uint32_t* units)
 {
     if (!plan) return FEELGPU_ERR_ARG;
     const RPlanHost* hp = static_cast<const RPlanHost*>(plan);
@@ -568,7 +586,6 @@ int feelgpu_rplan_host_copy(void* plan, void* patches /*32 B each*/, int32_t* vi
     if (visits) std::memcpy(visits, hp->visits.data(), hp->visits.size() * sizeof(int32_t));
     if (rows) std::memcpy(rows, hp->rows.data(), hp->rows.size() * sizeof(RPlanRow));
     if (units) std::memcpy(units, hp->units.data(), hp->units.size() * sizeof(uint32_t));
-    if (rounds) std::memcpy(rounds, hp->rounds.data(), hp->rounds.size() * sizeof(uint32_t));
     return FEELGPU_OK;
 }
 

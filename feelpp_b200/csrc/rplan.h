@@ -17,10 +17,11 @@
 //           it into row r's segment of the row block through the element->CSR position map.  Units are dealt in round
 //           order (the k-th unit of every row), so all lanes are busy whatever the row lengths (a vertex row has ~24 units, a
 //           face row 2) and the units of a round belong to different rows; units
-//           of one row meet on the columns they share, so the adds are done round by round (a barrier in between; a batch
-//           of 512 consecutive units spans one or two rounds): inside a round every row occurs once, the adds are plain
-//           shared-memory read-modify-writes, and the summation order of every CSR value is fixed by the plan
-//           (bit-reproducible run to run).  Every CSR value leaves the SM exactly once.
+//           of one row that run at the same time meet on the columns they share, hence the adds are shared-memory atomics
+//           (a compare-and-swap loop: the hardware has no fp64 shared atomic) -- inside the SM, never in L2.  Adding round
+//           by round with a barrier in between (plain read-modify-writes, fixed order) was measured: 39 % of the kernel went
+//           into the barriers.  Every CSR value leaves the SM exactly once; the order of the <= ~30 additions into a value
+//           is not fixed, as with the reference's own MPI runs (values within 1e-12, not bit-identical run to run).
 //   Phase C: the row block is streamed to the CSR value array (coalesced, one contiguous piece per node row).
 //
 // The row-thread name stays from the first version (thread = row), which left the SM waiting for its longest row.
@@ -36,7 +37,7 @@ struct RPlanPatch {              // 32 bytes
     uint32_t row_off, nrows;     // node rows: RPlanRow rows[row_off + r], sorted by descending unit count
     uint32_t unit_off, nunits;   // unit words: uint32 units[unit_off + k]
     uint32_t nslots;             // row-block slots used
-    uint32_t round_off;          // rounds[round_off + k] = first unit of round k (k-th unit of every row), k <= max units of a row
+    uint32_t pad;
 };
 struct RPlanRow {                // 32 bytes
     int64_t base;                // CSR offset of the node's component-0 row
@@ -56,9 +57,7 @@ struct RPlanHost {
     std::vector<int32_t> visits;
     std::vector<RPlanRow> rows;
     std::vector<uint32_t> units;
-    std::vector<uint32_t> rounds;
     int64_t nunits = 0, nvisits = 0;
-    int maxpatch_rounds = 0;
     int maxpatch_visits = 0, maxpatch_rows = 0, maxpatch_slots = 0;
     std::string error;
 };
@@ -71,8 +70,6 @@ struct RPlan {                   // device mirror
     int32_t* d_visits = nullptr;
     RPlanRow* d_rows = nullptr;
     uint32_t* d_units = nullptr;
-    uint32_t* d_rounds = nullptr;
-    int maxrounds = 0;
     int64_t bytes = 0, nunits = 0, nvisits = 0;
     int maxpatch_visits = 0, maxpatch_rows = 0, maxpatch_slots = 0;
     double build_seconds = 0;

@@ -176,8 +176,7 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
     plan.units.resize((size_t)uoff[(size_t)nP]);
     plan.nunits = uoff[(size_t)nP];
     plan.nvisits = voff[(size_t)nP];
-    // rounds: offsets of the k-th units inside every patch (nrounds + 1 entries per patch), filled after the parallel pass
-    std::vector<std::vector<uint32_t>> prounds((size_t)nP);
+
     std::vector<std::vector<int32_t>> slot_of(nthreads);       // per thread: element -> visit slot of the current patch
     std::vector<std::vector<int32_t>> slot_stamp(nthreads);
     parallel_for(nP, nthreads, [&](int64_t p0, int64_t p1, int t) {
@@ -196,7 +195,7 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
             P.unit_off = (uint32_t)uoff[(size_t)p];
             P.nunits = c.nunits;
             P.nslots = c.nslots;
-            P.round_off = 0;
+            P.pad = 0;
             // rows sorted by descending unit count: the lanes of a warp walk lists of similar length
             byn.clear();
             for (int64_t k = c.k0; k < c.k1; ++k) {
@@ -229,22 +228,14 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
             // unit words in "round" order: the k-th unit of every row that has one, k = 0, 1, ...: the lanes of a warp work
             // on different rows (their adds into the row block do not meet) and every lane has work whatever the row lengths
             uint32_t w = 0;
-            auto& rd = prounds[(size_t)p];
             for (uint32_t k = 0; !byn.empty() && k < byn[0].first; ++k) {
-                rd.push_back(w);
                 for (size_t r = 0; r < byn.size() && byn[r].first > k; ++r) {
                     const int64_t q = nptr[(size_t)byn[r].second] + k;
                     plan.units[(size_t)P.unit_off + w++] =
                         (uint32_t)slot[(size_t)uelt[(size_t)q]] | ((uint32_t)uloc[(size_t)q] << 12) | ((uint32_t)r << 17);
                 }
             }
-            rd.push_back(w);
         }
     });
-    for (int64_t p = 0; p < nP; ++p) {
-        plan.patches[(size_t)p].round_off = (uint32_t)plan.rounds.size();
-        plan.rounds.insert(plan.rounds.end(), prounds[(size_t)p].begin(), prounds[(size_t)p].end());
-        plan.maxpatch_rounds = std::max(plan.maxpatch_rounds, (int)prounds[(size_t)p].size() - 1);
-    }
     return true;
 }

@@ -296,13 +296,13 @@ int feelgpu_eplan_host_coefficients(int order, const feelgpu_tables* tables, int
 /* ---- host-side view of the row-thread plan (no device needed): what feelgpu_pattern_create builds with
  * FEELGPU_PATTERN_RPLAN; used by the CPU tests to interpret the plan on the host.  sizes: [0] patches, [1] visits,
  * [2] node rows, [3] units, [4] largest row block, [5] most visits in a patch, [6] most rows in a patch.
- * [7] round offsets.  patches: {u32 visit_off, nvisit, row_off, nrows, unit_off, nunits, nslots, round_off}; rows: {i64 base,
- * u32 off, len, unit0, nunits, pad, pad}; unit word: visit index in the patch | local dof << 12 | row in the patch << 17;
- * rounds[round_off + k] = first unit of round k (the k-th unit of every row that has one)                                */
+ * patches: {u32 visit_off, nvisit, row_off, nrows, unit_off, nunits, nslots, pad}; rows: {i64 base, u32 off, len, unit0,
+ * nunits, pad, pad}; unit word: visit index in the patch | local dof << 12 | row in the patch << 17, stored in round order
+ * (the k-th unit of every row that has one, k = 0, 1, ...)                                                              */
 int feelgpu_rplan_host_build(int order, int ncomp, int64_t nElt, const int32_t* l2g, int64_t nPts, const double* xyz,
                              const int32_t* conn, int64_t nRows, const int64_t* ia, int maxslots, int maxvisits, int maxrows,
                              void** plan, int64_t sizes[8]);
-int feelgpu_rplan_host_copy(void* plan, void* patches, int32_t* visits, void* rows, uint32_t* units, uint32_t* rounds);
+int feelgpu_rplan_host_copy(void* plan, void* patches, int32_t* visits, void* rows, uint32_t* units);
 const char* feelgpu_rplan_host_error(void* plan);
 int feelgpu_rplan_host_free(void* plan);
 

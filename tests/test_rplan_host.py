@@ -14,7 +14,7 @@ from feelpp_b200._capi import c_dblp, c_i32p, c_i64p, ptr
 from oracle import oracle as orc
 
 PATCH = np.dtype([("visit_off", "u4"), ("nvisit", "u4"), ("row_off", "u4"), ("nrows", "u4"), ("unit_off", "u4"),
-                  ("nunits", "u4"), ("nslots", "u4"), ("round_off", "u4")])
+                  ("nunits", "u4"), ("nslots", "u4"), ("pad", "u4")])
 ROW = np.dtype([("base", "i8"), ("off", "u4"), ("len", "u4"), ("unit0", "u4"), ("nunits", "u4"), ("pad", "u4", 2)])
 
 
@@ -31,11 +31,10 @@ def build(Xh, ia, maxslots, maxvisits, maxrows=1 << 20):
         raise RuntimeError(msg)
     patches, rows = np.zeros(sizes[0], dtype=PATCH), np.zeros(sizes[2], dtype=ROW)
     visits, units = np.zeros(sizes[1], dtype=np.int32), np.zeros(sizes[3], dtype=np.uint32)
-    rounds = np.zeros(sizes[7], dtype=np.uint32)
     lib.feelgpu_rplan_host_copy(plan, patches.ctypes.data_as(C.c_void_p), ptr(visits, c_i32p), rows.ctypes.data_as(C.c_void_p),
-                                units.ctypes.data_as(C.c_void_p), rounds.ctypes.data_as(C.c_void_p))
+                                units.ctypes.data_as(C.c_void_p))
     lib.feelgpu_rplan_host_free(plan)
-    return patches, visits, rows, units, sizes, rounds
+    return patches, visits, rows, units, sizes
 
 
 def position_map(Xh, ia, ja):
@@ -57,7 +56,7 @@ def test_plan_interpreted_on_the_host_gives_the_oracle_matrix(order, ncomp, kind
     Xh = fpp.FunctionSpace(mesh, order, ncomp)
     ia, ja = Xh.graph()
     n, nd = Xh.n, Xh.nd
-    patches, visits, rows, units, sizes, rounds = build(Xh, ia, maxslots, maxvisits)
+    patches, visits, rows, units, sizes = build(Xh, ia, maxslots, maxvisits)
     assert len(patches) > 1, "the limits should cut the mesh into several patches"
     assert sizes[4] <= maxslots and sizes[5] <= maxvisits
     pos = position_map(Xh, ia, ja)
@@ -107,13 +106,6 @@ def test_plan_interpreted_on_the_host_gives_the_oracle_matrix(order, ncomp, kind
                         for c2 in range(ncomp):
                             blk[int(R["off"]) + c1 * int(R["len"]) + pos[e, i, j] + c2] += Ae[n * c1 + i, n * c2 + j]
         assert np.array_equal(per_row, prow["nunits"])
-        # rounds: round k = the k-th unit of every row that has one, so inside a round every row occurs at most once
-        nr = int(prow["nunits"][0])
-        rd = rounds[P["round_off"]:P["round_off"] + nr + 1].astype(np.int64)
-        assert rd[0] == 0 and rd[-1] == P["nunits"] and (np.diff(rd) > 0).all()
-        for k in range(nr):
-            rr = pu[rd[k]:rd[k + 1]] >> 17
-            assert len(np.unique(rr)) == len(rr) == int((prow["nunits"] > k).sum())
         for R in prow:
             cnt = int(R["len"]) * ncomp
             a[R["base"]:R["base"] + cnt] = blk[R["off"]:R["off"] + cnt]
