@@ -44,6 +44,7 @@ struct RArgs {
 #define RTAB_MAX (3 * FEELGPU_MAX_NQ * FEELGPU_MAX_NLOC)
 __constant__ double c_rtab[RTAB_MAX];
 __constant__ double c_rw[FEELGPU_MAX_NQ];
+__constant__ double c_rxi[3 * FEELGPU_MAX_NQ];
 
 // shared-memory add of one double (a compare-and-swap loop in SASS, ATOMS.CAST.SPIN: no native fp64 shared atomic)
 __device__ __forceinline__ void sadd(double* p, double v) { atomicAdd(p, v); }
@@ -123,7 +124,9 @@ k_rplan(const RArgs A)
         }
     }
     for (int k = tid; k < nf * nq; k += blockDim.x) tphif[k] = A.T.phif[k];
-    for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;
+    const bool varcoef = FORM != 2 && P->coeff_kind != FEELGPU_COEFF_CONST;
+    if (!varcoef)      // (otherwise the block first serves as scratch of phase A and is zeroed after it)
+        for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;
     for (uint32_t r = tid; r < nrows; r += blockDim.x) {
         const uint4 q0 = __ldg(rows + 2 * r);
         sRoff[2 * r] = q0.z;
@@ -131,7 +134,9 @@ k_rplan(const RArgs A)
     }
     for (int k = tid; k < P->expr_len; k += blockDim.x) { sOps[k] = P->expr_ops[k]; sCst[k] = P->expr_consts[k]; }
 
-    // ---- phase A: geometry of every element touching the patch's rows, once (thread = visit) ----
+    // ---- phase A: geometry of every element touching the patch's rows, once (thread = visit).  For a point-dependent
+    //      coefficient the four vertices and J wait in the (still unused) row block for the second pass ----
+    double* scr = blk;                                       // [13][maxvis] scratch: x0..x3 (12), J
     for (uint32_t v = tid; v < nvisit; v += blockDim.x) {
         const int32_t e = __ldg(&A.visits[visit_off + v]);
         sE[v] = e;
@@ -153,32 +158,46 @@ k_rplan(const RArgs A)
                     for (int d = b; d < 3; ++d)
                         rec[(k++) * maxvis + v] = g.B[0][b] * g.B[0][d] + g.B[1][b] * g.B[1][d] + g.B[2][b] * g.B[2][d];
             }
-            if (P->coeff_kind == FEELGPU_COEFF_CONST) {
+            if (!varcoef) {
                 const double cj = P->cval[0] * g.J;
-                for (int q = 0; q < nq; ++q) rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = P->w[q] * cj;
+                for (int q = 0; q < nq; ++q) rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = c_rw[q] * cj;
+            } else {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    scr[(0 + c) * maxvis + v] = g.x0[c];
+                    scr[(3 + c) * maxvis + v] = g.x1[c];
+                    scr[(6 + c) * maxvis + v] = g.x2[c];
+                    scr[(9 + c) * maxvis + v] = g.x3[c];
+                }
+                scr[12 * maxvis + v] = g.J;
             }
         }
     }
     __syncthreads();
     // the coefficient at every quadrature point of every visit (thread = (visit, q)): prod[q] * k(x_q) = w_q J k(x_q)
-    // (feelpoly/pointsetquadrature.hpp:481-490); the geometry is formed again from the cached vertices, which is cheaper than
-    // keeping the four vertices of every visit in shared memory
-    if (FORM != 2 && P->coeff_kind != FEELGPU_COEFF_CONST) {
+    // (feelpoly/pointsetquadrature.hpp:481-490), x_q = G N(xi_q) (feelpoly/geomap.hpp:1964-1969)
+    if (varcoef) {
         for (uint32_t t = tid; t < nvisit * (uint32_t)nq; t += blockDim.x) {
             const uint32_t v = t / (uint32_t)nq;
             const int q = (int)(t - v * (uint32_t)nq);
-            const int32_t e = sE[v];
-            Geo g;
-            geo_update(A.xyz, __ldg(&A.conn[e]), g);
             double kq;
             if (P->coeff_kind == FEELGPU_COEFF_EXPR) {
+                const double xi0 = c_rxi[3 * q], xi1 = c_rxi[3 * q + 1], xi2 = c_rxi[3 * q + 2];
+                const double N0 = -0.5 * (1.0 + xi0 + xi1 + xi2), N1 = 0.5 * (1.0 + xi0), N2 = 0.5 * (1.0 + xi1), N3 = 0.5 * (1.0 + xi2);
                 double x[3];
-                xreal(g, &P->xi[3 * q], x);
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                    x[c] = scr[c * maxvis + v] * N0 + scr[(3 + c) * maxvis + v] * N1 + scr[(6 + c) * maxvis + v] * N2 + scr[(9 + c) * maxvis + v] * N3;
                 kq = eval_expr_sm(P->expr_len, sOps, sCst, x[0], x[1], x[2]);
-            } else
-                kq = coeff_at(P, tphif, g, e, q, A.l2gf, A.fvals);
-            rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = (P->w[q] * g.J) * kq;
+            } else {
+                const int32_t* lf = A.l2gf + (int64_t)sE[v] * nf;
+                kq = 0.0;
+                for (int i = 0; i < nf; ++i) kq += __ldg(&A.fvals[__ldg(lf + i)]) * tphif[i * nq + q];
+            }
+            rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = (c_rw[q] * scr[12 * maxvis + v]) * kq;
         }
+        __syncthreads();
+        for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;   // the scratch becomes the row block
         __syncthreads();
     }
 
@@ -191,12 +210,18 @@ k_rplan(const RArgs A)
         const int v = w & 0xFFF, i = (w >> 12) & 31;
         const uint32_t roff = sRoff[2 * (w >> 17)], rlen = sRoff[2 * (w >> 17) + 1];
         const uint16_t* pp = A.pos + ((int64_t)sE[v] * N + i) * N;
+        // the unit's positions in its row (N 16-bit values, 4-byte aligned: N is even) are requested before the quadrature loop
+        uint32_t pw[N / 2];
+        if (active) {
+#pragma unroll
+            for (int j = 0; j < N / 2; ++j) pw[j] = __ldg(reinterpret_cast<const uint32_t*>(pp) + j);
+        }
+        auto posj = [&](int j) { return (pw[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu; };
         if (FORM != 2) {
             double acc[N];
 #pragma unroll
             for (int j = 0; j < N; ++j) acc[j] = 0.0;
             if (active) {
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(pp));     // the positions are needed after the quadrature loop
                 if (FORM == 0) {
                     if (NQ > 0) {
 #pragma unroll
@@ -259,7 +284,7 @@ k_rplan(const RArgs A)
             if (active) {
                 double* rb = blk + roff;
 #pragma unroll
-                for (int j = 0; j < N; ++j) sadd(rb + __ldg(pp + j), acc[j]);
+                for (int j = 0; j < N; ++j) sadd(rb + posj(j), acc[j]);
             }
         } else if (NQ > 0) {
             // elasticity: physical gradients of the row function at the quadrature points, then column by column the 3x3 block
@@ -319,7 +344,7 @@ k_rplan(const RArgs A)
                     for (int jj = 0; jj < JC; ++jj) {
                         const int j = j0 + jj;
                         if (j >= N) break;
-                        const uint32_t p0c = __ldg(pp + j);
+                        const uint32_t p0c = posj(j);
 #pragma unroll
                         for (int c1 = 0; c1 < 3; ++c1) {
                             double* rb = blk + roff + c1 * rlen + p0c;
@@ -404,7 +429,7 @@ int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     p->order = hp.order;
     p->n = hp.n;
     p->ncomp = hp.ncomp;
-    p->maxslots = (hp.maxpatch_slots + 1) & ~1;      // what the kernel has to provide: the largest patch, not the limit;
+    p->maxslots = (std::max(hp.maxpatch_slots, 13 * std::max(hp.maxpatch_visits, 1) + 13) + 1) & ~1;   // the largest patch (not the limit), and room for phase A's scratch;
     p->maxvisits = (std::max(hp.maxpatch_visits, 1) + 1) & ~1;   // even counts keep the shared arrays behind them 16-byte aligned
     p->maxrows = hp.maxpatch_rows;
     p->npatch = (int64_t)hp.patches.size();
@@ -518,8 +543,9 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
                     for (int c = 0; c < 3; ++c) ct[((size_t)q * 3 + c) * n + j] = desc->tables.dphi[(j * nq + q) * 3 + c];
             }
         FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rtab, ct.data(), ct.size() * sizeof(double), 0, cudaMemcpyHostToDevice, s));
-        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rw, desc->tables.w, nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
     }
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rw, desc->tables.w, nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rxi, desc->tables.xi, 3 * nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
 #define PLAUNCH(O, F, Q)                                                                                                       \
     do {                                                                                                                       \
         FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rplan<O, F, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));  \
