@@ -8,5 +8,5 @@ from .hostmirror import (Mesh, unitCube, loadMesh, elements, boundaryfaces, mark
 from .vf import (Element, cst, vec, idv, expr, id, idt, grad, gradt, trans, sym, trace, Id, inner, integrate, on,
                  classify_form1, classify_form2)
 from .engine import (Engine, form1, form2, ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN, ALGO_RPLAN,
-                     PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN, PATTERN_RPLAN)
+                     PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN, PATTERN_RPLAN, PATTERN_ASYNC)
 from ._capi import FeelGpuError

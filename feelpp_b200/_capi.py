@@ -56,6 +56,7 @@ GPU_SYMBOLS = {
     "feelgpu_pattern_create": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, c_i64p, c_i64p, C.c_int,
                                C.POINTER(C.c_void_p)],
     "feelgpu_pattern_nnz": [C.c_void_p, c_i64p],
+    "feelgpu_pattern_plans_ready": [C.c_void_p, C.c_int, C.POINTER(C.c_int), c_dblp],
     "feelgpu_pattern_destroy": [C.c_void_p],
     "feelgpu_pattern_plan_stats": [C.c_void_p, c_i64p],
     "feelgpu_pattern_eplan_stats": [C.c_void_p, c_i64p],

@@ -299,6 +299,7 @@ int feelgpu_exchange_create(feelgpu_pattern_t pat, const int32_t* ghost_owner, i
     *out = nullptr;
     if (!ctx->comm) { ctx->last_error = "exchange_create: no communicator (feelgpu_comm_init)"; return FEELGPU_ERR_ARG; }
     if (pat->exchange) { ctx->last_error = "exchange_create: the pattern already has an exchange"; return FEELGPU_ERR_ARG; }
+    if (int prc = feelgpu_eplan_poll(pat, true)) return prc;     // the peer-memory transport patches the entity plan
     feelgpu_space_t sp = pat->test;
     const int P = ctx->nranks, me = ctx->rank;
     const int64_t nO = sp->nDofOwned, nG = pat->nRows - nO;

@@ -266,6 +266,8 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     if (ia[0] != 0) ARG_FAIL(ctx, "pattern_create: ia[0] != 0");
     for (int64_t r = 0; r < nRows; ++r)
         if (ia[r + 1] < ia[r]) ARG_FAIL(ctx, "pattern_create: ia not monotone");
+    const bool async = (flags & FEELGPU_PATTERN_ASYNC) != 0;
+    flags &= ~FEELGPU_PATTERN_ASYNC;
     if (flags == 0) flags = FEELGPU_PATTERN_SLOTMAP | FEELGPU_PATTERN_RPLAN | (test->order <= 2 ? FEELGPU_PATTERN_EPLAN : 0);
     CTX_CUDA(ctx, cudaSetDevice(ctx->device));
     feelgpu_pattern_t pat = nullptr;
@@ -313,10 +315,12 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
             }
         }
     }
-    if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_EPLAN)) rc = feelgpu_eplan_build(pat, ia);
+    // (the background build of the entity plan starts first: it overlaps the row-thread plan's build)
+    if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_EPLAN)) rc = feelgpu_eplan_build(pat, ia, async && (flags & FEELGPU_PATTERN_RPLAN));
     if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_RPLAN)) rc = feelgpu_rplan_build(pat, ia);
     // the row plan is also the fallback of a mesh the entity plan could not take
-    if (rc == FEELGPU_OK && ((flags & FEELGPU_PATTERN_ROWPLAN) || ((flags & FEELGPU_PATTERN_EPLAN) && !pat->eplan && !pat->rplan)))
+    if (rc == FEELGPU_OK && ((flags & FEELGPU_PATTERN_ROWPLAN) ||
+                             ((flags & FEELGPU_PATTERN_EPLAN) && !pat->eplan && !pat->eplan_async && !pat->rplan)))
         rc = feelgpu_rowplan_build(pat, ia, ja);
     if (rc != FEELGPU_OK) {
         feelgpu_pattern_destroy(pat);
@@ -359,7 +363,18 @@ int feelgpu_pattern_plan_stats(feelgpu_pattern_t pat, int64_t stats[10])
 int feelgpu_pattern_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
 {
     if (!pat || !stats) return FEELGPU_ERR_ARG;
+    int rc = feelgpu_eplan_poll(pat, false);
+    if (rc) return rc;
     return feelgpu_eplan_stats(pat, stats);
+}
+
+int feelgpu_pattern_plans_ready(feelgpu_pattern_t pat, int wait, int* ready, double* build_seconds)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    int rc = feelgpu_eplan_poll(pat, wait != 0);
+    if (ready) *ready = pat->eplan_async ? 0 : 1;
+    if (build_seconds) *build_seconds = pat->eplan_build_seconds;
+    return rc;
 }
 
 int feelgpu_pattern_rplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
@@ -459,6 +474,8 @@ int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc
     FormParams hp;
     int rc = fill_params(ctx, desc->kind, desc->coeff, desc->tables, pat->test, true, &hp);
     if (rc) return rc;
+    // a plan built in the background is installed as soon as it is ready; asking for it by name waits for it
+    if (pat->eplan_async && (rc = feelgpu_eplan_poll(pat, desc->algorithm == FEELGPU_ALGO_EPLAN))) return rc;
     int algo = desc->algorithm;
     if (algo == FEELGPU_ALGO_AUTO)
         algo = feelgpu_eplan_supports(pat, desc)     ? FEELGPU_ALGO_EPLAN

@@ -71,6 +71,8 @@ struct feelgpu_pattern_s {
     std::string plan_note;       // why no owner-computes plan exists (if none)
     EPlan* eplan = nullptr;
     std::string eplan_note;
+    struct EPlanAsync* eplan_async = nullptr;   // a build in flight (FEELGPU_PATTERN_ASYNC) or waiting to be installed
+    double eplan_build_seconds = 0;
     RPlan* rplan = nullptr;      // row-thread plan: owner-computes path of the forms the entity plan does not cover
     std::string rplan_note;
     // multi-GPU: host copies of what the graph exchange ships (interface-sized) and the exchange itself
@@ -134,7 +136,8 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
 bool feelgpu_rplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
 int feelgpu_rplan_stats(feelgpu_pattern_t pat, int64_t stats[10]);
 // ---- kernels_eplan.cu ----
-int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia);
+int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, bool async);
+int feelgpu_eplan_poll(feelgpu_pattern_t pat, bool wait);
 void feelgpu_eplan_destroy(feelgpu_pattern_t pat);
 int feelgpu_launch_form2_eplan(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
                                int accumulate, double* a, cudaStream_t s);

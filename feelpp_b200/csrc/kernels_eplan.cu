@@ -9,9 +9,12 @@
 #include "eplan.h"
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 
 namespace {
 
@@ -551,23 +554,18 @@ void s_in_b0(int k, int l, double* v)
 
 } // namespace
 
-int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
+// ---- building the plan: on the calling thread, or by a background thread (FEELGPU_PATTERN_ASYNC) -------------------------
+struct EPlanAsync {
+    std::thread th;
+    std::atomic<int> state{0};       // 0 building, 1 built, 2 the mesh does not fit the plan (hp.error)
+    EPlanHost hp;
+    std::vector<uint16_t> pos;
+    double seconds = 0;
+};
+
+static int eplan_install(feelgpu_pattern_t pat, EPlanHost& hp)
 {
     feelgpu_context_t ctx = pat->ctx;
-    feelgpu_space_t sp = pat->test;
-    feelgpu_mesh_t m = sp->mesh;
-    if (pat->test != pat->trial) return FEELGPU_OK;   // the plan needs test == trial
-    if (!eplan_spec(sp->order)) { pat->eplan_note = "entity plan: order not covered"; return FEELGPU_OK; }
-    const int n = sp->n;
-    std::vector<uint16_t> pos((size_t)m->nElt * n * n);
-    FEELGPU_CHECK_CUDA(ctx, cudaMemcpy(pos.data(), pat->d_pos, pos.size() * sizeof(uint16_t), cudaMemcpyDeviceToHost));
-    EPlanHost hp;
-    if (sp->nDofOwned < pat->nRows) hp.nomerge_from = h_ia[sp->nDofOwned];
-    if (!eplan_build_host(sp->order, sp->ncomp, EPLAN_OMAX, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(),
-                          m->h_conn.data(), pat->nRows, h_ia, pos.data(), 0, hp)) {
-        pat->eplan_note = hp.error;   // not an error: another path stays available
-        return FEELGPU_OK;
-    }
     EPlan* p = new EPlan;
     p->order = hp.order;
     p->n = hp.n;
@@ -599,6 +597,65 @@ int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     return FEELGPU_OK;
 }
 
+int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, bool async)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    feelgpu_space_t sp = pat->test;
+    feelgpu_mesh_t m = sp->mesh;
+    if (pat->test != pat->trial) return FEELGPU_OK;   // the plan needs test == trial
+    if (!eplan_spec(sp->order)) { pat->eplan_note = "entity plan: order not covered"; return FEELGPU_OK; }
+    const int n = sp->n;
+    (void)h_ia;                                       // (the pattern keeps its own copy: pat->h_ia)
+    EPlanAsync* job = new EPlanAsync;
+    job->pos.resize((size_t)m->nElt * n * n);
+    cudaError_t err = cudaMemcpy(job->pos.data(), pat->d_pos, job->pos.size() * sizeof(uint16_t), cudaMemcpyDeviceToHost);
+    if (err != cudaSuccess) {
+        delete job;
+        ctx->last_error = std::string("entity plan: ") + cudaGetErrorString(err);
+        return FEELGPU_ERR_CUDA;
+    }
+    if (sp->nDofOwned < pat->nRows) job->hp.nomerge_from = pat->h_ia[sp->nDofOwned];
+    auto work = [pat, sp, m, job] {
+        const auto t0 = std::chrono::steady_clock::now();
+        bool ok = false;
+        try {
+            ok = eplan_build_host(sp->order, sp->ncomp, EPLAN_OMAX, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(),
+                                  m->h_conn.data(), pat->nRows, pat->h_ia.data(), job->pos.data(), 0, job->hp);
+        } catch (const std::exception& e) {
+            job->hp.error = std::string("entity plan: ") + e.what();
+        }
+        std::vector<uint16_t>().swap(job->pos);
+        job->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        job->state.store(ok ? 1 : 2, std::memory_order_release);
+    };
+    pat->eplan_async = job;
+    if (async) {
+        job->th = std::thread(work);
+        return FEELGPU_OK;
+    }
+    work();
+    return feelgpu_eplan_poll(pat, true);
+}
+
+// installs the plan of a finished background build (wait: block until it is finished)
+int feelgpu_eplan_poll(feelgpu_pattern_t pat, bool wait)
+{
+    EPlanAsync* job = pat->eplan_async;
+    if (!job) return FEELGPU_OK;
+    if (!wait && job->state.load(std::memory_order_acquire) == 0) return FEELGPU_OK;
+    if (job->th.joinable()) job->th.join();
+    pat->eplan_async = nullptr;
+    int rc = FEELGPU_OK;
+    pat->eplan_build_seconds = job->seconds;
+    if (job->state.load() == 1) {
+        cudaSetDevice(pat->ctx->device);
+        rc = eplan_install(pat, job->hp);
+    } else
+        pat->eplan_note = job->hp.error;   // not an error: another path stays available
+    delete job;
+    return rc;
+}
+
 int feelgpu_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
 {
     for (int k = 0; k < 10; ++k) stats[k] = 0;
@@ -619,6 +676,11 @@ int feelgpu_eplan_stats(feelgpu_pattern_t pat, int64_t stats[10])
 
 void feelgpu_eplan_destroy(feelgpu_pattern_t pat)
 {
+    if (EPlanAsync* job = pat->eplan_async) {      // a build still running: let it finish, drop the result
+        if (job->th.joinable()) job->th.join();
+        delete job;
+        pat->eplan_async = nullptr;
+    }
     EPlan* p = pat->eplan;
     if (!p) return;
     cudaFree(p->d_ctas);

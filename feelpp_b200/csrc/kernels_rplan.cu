@@ -34,6 +34,7 @@ struct RArgs {
     DevTables T;
     const int32_t* l2gf;
     const double* fvals;
+    const double* kq;            // [nElt][nq] coefficient at the quadrature points (variable coefficients)
     double* a;
     int accumulate, maxslots, maxvis, maxrows;
 };
@@ -87,6 +88,46 @@ __device__ double eval_expr_sm(int len, const int* ops, const double* consts, do
     return st[0];
 }
 
+// Coefficient pass: k(x_q) at every quadrature point of every element, once (thread = (element, q), full occupancy: the
+// interpreter is a chain of dependent loads that the 16 warps of the assembly kernel cannot hide, and a visit-based
+// evaluation would repeat it for every patch an element touches).  kq[e][q], read back by phase A of the assembly kernel.
+__global__ void __launch_bounds__(256)
+k_rplan_coeff(const FormParams* __restrict__ P, int64_t nElt, int nq, const double* __restrict__ xyz, const int4* __restrict__ conn,
+              const double* __restrict__ phif, const int32_t* __restrict__ l2gf, const double* __restrict__ fvals,
+              double* __restrict__ kq)
+{
+    __shared__ int sOps[FEELGPU_EXPR_MAX_LEN];
+    __shared__ double sCst[FEELGPU_EXPR_MAX_LEN];
+    const int len = P->expr_len, kind = P->coeff_kind, nf = P->nf;
+    for (int k = threadIdx.x; k < len; k += blockDim.x) { sOps[k] = P->expr_ops[k]; sCst[k] = P->expr_consts[k]; }
+    __syncthreads();
+    const int64_t total = nElt * nq;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t e = t / nq;
+        const int q = (int)(t - e * nq);
+        double v;
+        if (kind == FEELGPU_COEFF_EXPR) {
+            const int4 c = __ldg(&conn[e]);
+            double x0[3], x1[3], x2[3], x3[3];
+            load_vertex(xyz, c.x, x0);
+            load_vertex(xyz, c.y, x1);
+            load_vertex(xyz, c.z, x2);
+            load_vertex(xyz, c.w, x3);
+            const double xi0 = c_rxi[3 * q], xi1 = c_rxi[3 * q + 1], xi2 = c_rxi[3 * q + 2];
+            const double N0 = -0.5 * (1.0 + xi0 + xi1 + xi2), N1 = 0.5 * (1.0 + xi0), N2 = 0.5 * (1.0 + xi1), N3 = 0.5 * (1.0 + xi2);
+            double x[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) x[a] = x0[a] * N0 + x1[a] * N1 + x2[a] * N2 + x3[a] * N3;
+            v = eval_expr_sm(len, sOps, sCst, x[0], x[1], x[2]);
+        } else {
+            const int32_t* lf = l2gf + e * nf;
+            v = 0.0;
+            for (int i = 0; i < nf; ++i) v += __ldg(&fvals[__ldg(lf + i)]) * __ldg(&phif[i * nq + q]);
+        }
+        kq[t] = v;
+    }
+}
+
 // FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)), 2: elasticity.  Thread = unit.  NQ > 0: quadrature points known at
 // compile time, tables in constant memory, loops unrolled; NQ = 0: any nq, tables in shared memory (mass / stiffness only).
 template <int ORDER, int FORM, int NQ>
@@ -105,8 +146,6 @@ k_rplan(const RArgs A)
     double* tphif = tab + ntab;                              // [nf][nq] basis of the coefficient field
     int32_t* sE = reinterpret_cast<int32_t*>(tphif + nf * nq);   // [maxvis] element of every visit
     uint32_t* sRoff = reinterpret_cast<uint32_t*>(sE + maxvis);  // [maxrows][2] row-block offset and length of every row
-    int* sOps = reinterpret_cast<int*>(sRoff + 2 * A.maxrows);    // [2 * FEELGPU_EXPR_MAX_LEN] the coefficient program ...
-    double* sCst = reinterpret_cast<double*>(sOps + 2 * FEELGPU_EXPR_MAX_LEN);   // ... and its constants (8-byte aligned: the counts before are even)
     const int tid = threadIdx.x;
 
     const uint4* pq = reinterpret_cast<const uint4*>(A.patches + blockIdx.x);
@@ -125,18 +164,14 @@ k_rplan(const RArgs A)
     }
     for (int k = tid; k < nf * nq; k += blockDim.x) tphif[k] = A.T.phif[k];
     const bool varcoef = FORM != 2 && P->coeff_kind != FEELGPU_COEFF_CONST;
-    if (!varcoef)      // (otherwise the block first serves as scratch of phase A and is zeroed after it)
-        for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;
+    for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;
     for (uint32_t r = tid; r < nrows; r += blockDim.x) {
         const uint4 q0 = __ldg(rows + 2 * r);
         sRoff[2 * r] = q0.z;
         sRoff[2 * r + 1] = q0.w;
     }
-    for (int k = tid; k < P->expr_len; k += blockDim.x) { sOps[k] = P->expr_ops[k]; sCst[k] = P->expr_consts[k]; }
 
-    // ---- phase A: geometry of every element touching the patch's rows, once (thread = visit).  For a point-dependent
-    //      coefficient the four vertices and J wait in the (still unused) row block for the second pass ----
-    double* scr = blk;                                       // [13][maxvis] scratch: x0..x3 (12), J
+    // ---- phase A: geometry of every element touching the patch's rows, once (thread = visit) ----
     for (uint32_t v = tid; v < nvisit; v += blockDim.x) {
         const int32_t e = __ldg(&A.visits[visit_off + v]);
         sE[v] = e;
@@ -158,48 +193,17 @@ k_rplan(const RArgs A)
                     for (int d = b; d < 3; ++d)
                         rec[(k++) * maxvis + v] = g.B[0][b] * g.B[0][d] + g.B[1][b] * g.B[1][d] + g.B[2][b] * g.B[2][d];
             }
+            // prod[q] * k(x_q) = w_q J k(x_q)   (feelpoly/pointsetquadrature.hpp:481-490)
             if (!varcoef) {
                 const double cj = P->cval[0] * g.J;
                 for (int q = 0; q < nq; ++q) rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = c_rw[q] * cj;
             } else {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    scr[(0 + c) * maxvis + v] = g.x0[c];
-                    scr[(3 + c) * maxvis + v] = g.x1[c];
-                    scr[(6 + c) * maxvis + v] = g.x2[c];
-                    scr[(9 + c) * maxvis + v] = g.x3[c];
-                }
-                scr[12 * maxvis + v] = g.J;
+                const double* kp = A.kq + (int64_t)e * nq;
+                for (int q = 0; q < nq; ++q) rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = (c_rw[q] * g.J) * __ldg(kp + q);
             }
         }
     }
     __syncthreads();
-    // the coefficient at every quadrature point of every visit (thread = (visit, q)): prod[q] * k(x_q) = w_q J k(x_q)
-    // (feelpoly/pointsetquadrature.hpp:481-490), x_q = G N(xi_q) (feelpoly/geomap.hpp:1964-1969)
-    if (varcoef) {
-        for (uint32_t t = tid; t < nvisit * (uint32_t)nq; t += blockDim.x) {
-            const uint32_t v = t / (uint32_t)nq;
-            const int q = (int)(t - v * (uint32_t)nq);
-            double kq;
-            if (P->coeff_kind == FEELGPU_COEFF_EXPR) {
-                const double xi0 = c_rxi[3 * q], xi1 = c_rxi[3 * q + 1], xi2 = c_rxi[3 * q + 2];
-                const double N0 = -0.5 * (1.0 + xi0 + xi1 + xi2), N1 = 0.5 * (1.0 + xi0), N2 = 0.5 * (1.0 + xi1), N3 = 0.5 * (1.0 + xi2);
-                double x[3];
-#pragma unroll
-                for (int c = 0; c < 3; ++c)
-                    x[c] = scr[c * maxvis + v] * N0 + scr[(3 + c) * maxvis + v] * N1 + scr[(6 + c) * maxvis + v] * N2 + scr[(9 + c) * maxvis + v] * N3;
-                kq = eval_expr_sm(P->expr_len, sOps, sCst, x[0], x[1], x[2]);
-            } else {
-                const int32_t* lf = A.l2gf + (int64_t)sE[v] * nf;
-                kq = 0.0;
-                for (int i = 0; i < nf; ++i) kq += __ldg(&A.fvals[__ldg(lf + i)]) * tphif[i * nq + q];
-            }
-            rec[((FORM == 1 ? 6 : 0) + q) * maxvis + v] = (c_rw[q] * scr[12 * maxvis + v]) * kq;
-        }
-        __syncthreads();
-        for (uint32_t k = tid; k < nslots; k += blockDim.x) blk[k] = 0.0;   // the scratch becomes the row block
-        __syncthreads();
-    }
 
     // ---- phase B: one thread per unit, batches of blockDim.x units in round order ----
     const uint32_t* units = A.units + unit_off;
@@ -391,7 +395,7 @@ size_t rplan_smem_bytes(const RPlan* p, int form, int nq, int nf)
     const size_t nrec = form == 0 ? nq : form == 1 ? 6 + nq : 10;
     const size_t ntab = form == 0 ? (size_t)n * nq : (size_t)n * nq * 3;
     return sizeof(double) * ((size_t)p->maxslots + nrec * p->maxvisits + ntab + (size_t)nf * nq) +
-           sizeof(int32_t) * ((size_t)p->maxvisits + 2 * (size_t)p->maxrows + 2 * FEELGPU_EXPR_MAX_LEN) + sizeof(double) * FEELGPU_EXPR_MAX_LEN + 16;
+           sizeof(int32_t) * ((size_t)p->maxvisits + 2 * (size_t)p->maxrows) + 16;
 }
 
 int env_int(const char* name, int dflt)
@@ -429,7 +433,7 @@ int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     p->order = hp.order;
     p->n = hp.n;
     p->ncomp = hp.ncomp;
-    p->maxslots = (std::max(hp.maxpatch_slots, 13 * std::max(hp.maxpatch_visits, 1) + 13) + 1) & ~1;   // the largest patch (not the limit), and room for phase A's scratch;
+    p->maxslots = (hp.maxpatch_slots + 1) & ~1;      // what the kernel has to provide: the largest patch, not the limit;
     p->maxvisits = (std::max(hp.maxpatch_visits, 1) + 1) & ~1;   // even counts keep the shared arrays behind them 16-byte aligned
     p->maxrows = hp.maxpatch_rows;
     p->npatch = (int64_t)hp.patches.size();
@@ -459,6 +463,7 @@ void feelgpu_rplan_destroy(feelgpu_pattern_t pat)
     cudaFree(p->d_visits);
     cudaFree(p->d_rows);
     cudaFree(p->d_units);
+    cudaFree(p->d_kq);
     delete p;
     pat->rplan = nullptr;
 }
@@ -546,6 +551,23 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     }
     FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rw, desc->tables.w, nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
     FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rxi, desc->tables.xi, 3 * nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
+    A.kq = nullptr;
+    if (form != 2 && hp.coeff_kind != FEELGPU_COEFF_CONST) {
+        const size_t need = sizeof(double) * (size_t)m->nElt * nq;
+        if (p->kq_bytes < need) {
+            if (p->d_kq) FEELGPU_CHECK_CUDA(ctx, cudaFree(p->d_kq));
+            p->d_kq = nullptr;
+            p->kq_bytes = 0;
+            FEELGPU_CHECK_CUDA(ctx, cudaMalloc(&p->d_kq, std::max<size_t>(need, 8)));
+            p->kq_bytes = need;
+        }
+        const int64_t total = m->nElt * nq;
+        const int cgrid = (int)std::max<int64_t>(1, std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 32));
+        k_rplan_coeff<<<cgrid, 256, 0, s>>>(A.P, m->nElt, nq, m->d_xyz, m->d_conn, A.T.phif, A.l2gf, A.fvals, p->d_kq);
+        ctx->launches++;
+        FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+        A.kq = p->d_kq;
+    }
 #define PLAUNCH(O, F, Q)                                                                                                       \
     do {                                                                                                                       \
         FEELGPU_CHECK_CUDA(ctx, cudaFuncSetAttribute(k_rplan<O, F, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));  \

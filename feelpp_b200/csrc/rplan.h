@@ -9,8 +9,9 @@
 //   patch = spatially compact set of node rows (consecutive along a Hilbert curve) whose CSR values fit the CTA's
 //           shared-memory row block.
 //   visit = an element touching a row of the patch.  Phase A (thread = visit): vertex coordinates -> K, J, B
-//           (feelpoly/geomap.hpp:2320-2355,1971-1991), the coefficient at every quadrature point (cst / idv / expr at
-//           xReal), i.e. prod[q]*k(x_q) = w_q J k(x_q) (feelpoly/pointsetquadrature.hpp:481-490) -> shared memory.
+//           (feelpoly/geomap.hpp:2320-2355,1971-1991) and prod[q]*k(x_q) = w_q J k(x_q) at every quadrature point
+//           (feelpoly/pointsetquadrature.hpp:481-490) -> shared memory.  A point-dependent coefficient (idv / expr at xReal)
+//           is evaluated once per (element, point) by a small kernel in front of the assembly kernel.
 //   unit  = (row r, element e containing r's node): the row of e's local matrix that belongs to r
 //           (feelvf/bilinearformcontext.hpp:585-589).  Phase B: one thread per unit (per (unit, column j) for the 3x3 blocks
 //           of product spaces) forms the unit's row by the quadrature sum (feelpoly/pointsetquadrature.hpp:403-416) and adds
@@ -70,6 +71,8 @@ struct RPlan {                   // device mirror
     int32_t* d_visits = nullptr;
     RPlanRow* d_rows = nullptr;
     uint32_t* d_units = nullptr;
+    double* d_kq = nullptr;      // [nElt][nq] coefficient at the quadrature points, filled by the coefficient pass of an assembly
+    size_t kq_bytes = 0;
     int64_t bytes = 0, nunits = 0, nvisits = 0;
     int maxpatch_visits = 0, maxpatch_rows = 0, maxpatch_slots = 0;
     double build_seconds = 0;

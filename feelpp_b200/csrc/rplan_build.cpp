@@ -4,6 +4,8 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -48,6 +50,14 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
                       int nthreads, RPlanHost& plan)
 {
     (void)nPts;
+    const bool timing = std::getenv("FEELGPU_RPLAN_TIMING") != nullptr;
+    auto tprev = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "rplan build: %-12s %.3f s\n", what, std::chrono::duration<double>(now - tprev).count());
+        tprev = now;
+    };
     if (nthreads <= 0) nthreads = (int)std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
     const int n = (order + 1) * (order + 2) * (order + 3) / 6;
     plan.order = order;
@@ -81,6 +91,7 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
                 uloc[(size_t)q] = (uint8_t)i;
             }
     }
+    lap("adjacency");
     // ---- curve order of the nodes (position = centroid of the node's entity in its first element) ----
     static const int E2P[6][2] = {{1, 2}, {2, 0}, {0, 1}, {0, 3}, {1, 3}, {2, 3}};
     static const int F2P[4][3] = {{1, 2, 3}, {0, 2, 3}, {0, 1, 3}, {0, 1, 2}};
@@ -115,7 +126,25 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
         }
     });
     if (nNode >= ((int64_t)1 << 32)) { plan.error = "row-thread plan: more than 2^32 nodes"; return false; }
-    std::sort(key.begin(), key.end());
+    lap("keys");
+    {   // parallel sort: chunks sorted by the threads, then merged pairwise
+        int nch = 1;
+        while (nch * 2 <= nthreads && (int64_t)key.size() / (nch * 2) > 65536) nch *= 2;
+        std::vector<size_t> cut(nch + 1);
+        for (int c = 0; c <= nch; ++c) cut[c] = key.size() * (size_t)c / nch;
+        {
+            std::vector<std::thread> th;
+            for (int c = 0; c < nch; ++c) th.emplace_back([&, c] { std::sort(key.begin() + cut[c], key.begin() + cut[c + 1]); });
+            for (auto& x : th) x.join();
+        }
+        for (int w = 1; w < nch; w *= 2) {
+            std::vector<std::thread> th;
+            for (int c = 0; c + w < nch; c += 2 * w)
+                th.emplace_back([&, c, w] { std::inplace_merge(key.begin() + cut[c], key.begin() + cut[c + w], key.begin() + cut[std::min(c + 2 * w, nch)]); });
+            for (auto& x : th) x.join();
+        }
+    }
+    lap("sort");
     // ---- greedy cut into patches ----
     struct Cut { int64_t k0, k1; uint32_t nvisit, nslots, nunits; };
     std::vector<Cut> cuts;
@@ -155,6 +184,7 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
         }
         if (nNode > k0) cuts.push_back(Cut{k0, nNode, nvis, nslots, nun});
     }
+    lap("cut");
     // ---- emit ----
     const int64_t nP = (int64_t)cuts.size();
     plan.patches.resize((size_t)nP);
@@ -237,5 +267,6 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
             }
         }
     });
+    lap("emit");
     return true;
 }

@@ -12,7 +12,7 @@ from . import vf
 from ._capi import Coeff, Form1Desc, Form2Desc, Tables, c_dblp, c_i32p, c_i64p, check, ptr
 
 ALGO_AUTO, ALGO_SCATTER, ALGO_ROWPLAN, ALGO_EPLAN, ALGO_RPLAN = 0, 1, 2, 3, 4
-PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN, PATTERN_RPLAN = 1, 2, 4, 8
+PATTERN_SLOTMAP, PATTERN_ROWPLAN, PATTERN_EPLAN, PATTERN_RPLAN, PATTERN_ASYNC = 1, 2, 4, 8, 16
 
 
 class Engine:
@@ -251,6 +251,18 @@ class BilinearForm:
     def energy(self, v, u):
         """v^T A u (MatrixPetsc::energy, feelalg/matrixpetsc.cpp:2132-2170)"""
         return float(np.dot(v, self.multVector(u)))
+
+    def close(self):
+        """release the device mirrors of this form (feelgpu_pattern_destroy joins a background plan build first)"""
+        if self.pat:
+            self.eng.lib.feelgpu_pattern_destroy(self.pat)
+            self.pat = C.c_void_p()
+
+    def plans_ready(self, wait=False):
+        """(ready, seconds the entity plan took to build): background plan builds of FEELGPU_PATTERN_ASYNC"""
+        ready, secs = C.c_int(), C.c_double()
+        check(self.eng.lib.feelgpu_pattern_plans_ready(self.pat, 1 if wait else 0, C.byref(ready), C.byref(secs)), self.eng.ctx)
+        return bool(ready.value), secs.value
 
     def plan_stats(self):
         st = np.zeros(10, dtype=np.int64)

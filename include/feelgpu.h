@@ -112,8 +112,13 @@ enum {
     FEELGPU_ALGO_RPLAN = 4        /* owner-computes by row threads: the thread that owns a CSR row sums the quadrature rows
                                      of the elements around it (cst / idv / expr coefficients, P1-P3, elasticity)      */
 };
-/* flags of feelgpu_pattern_create (0 = SLOTMAP + RPLAN + EPLAN for P1/P2 spaces) */
-enum { FEELGPU_PATTERN_SLOTMAP = 1, FEELGPU_PATTERN_ROWPLAN = 2, FEELGPU_PATTERN_EPLAN = 4, FEELGPU_PATTERN_RPLAN = 8 };
+/* flags of feelgpu_pattern_create (0 = SLOTMAP + RPLAN + EPLAN for P1/P2 spaces).  FEELGPU_PATTERN_ASYNC: the entity plan,
+ * whose construction takes seconds on meshes of millions of elements, is built by a background host thread; pattern_create
+ * returns when the row-thread plan is ready, FEELGPU_ALGO_AUTO assembles through it until the entity plan is installed
+ * (feelgpu_pattern_plans_ready tells / waits), FEELGPU_ALGO_EPLAN waits for it.  The mesh and the spaces must outlive the
+ * pattern (as always).                                                                                                 */
+enum { FEELGPU_PATTERN_SLOTMAP = 1, FEELGPU_PATTERN_ROWPLAN = 2, FEELGPU_PATTERN_EPLAN = 4, FEELGPU_PATTERN_RPLAN = 8,
+       FEELGPU_PATTERN_ASYNC = 16 };
 
 /* ---- context ------------------------------------------------------------------------------------------------ */
 int feelgpu_context_create(int device, feelgpu_context_t* ctx);
@@ -145,6 +150,9 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
                            const int64_t* ia /*[nRows+1]*/, const int64_t* ja /*[nnz], ascending per row*/,
                            int flags, feelgpu_pattern_t* pattern);
 int feelgpu_pattern_nnz(feelgpu_pattern_t pattern, int64_t* nnz);
+/* background plan builds: *ready = 1 when none is in flight (wait != 0: block until then); *build_seconds = host time the
+ * entity plan took.  Either output may be NULL.                                                                          */
+int feelgpu_pattern_plans_ready(feelgpu_pattern_t pattern, int wait, int* ready, double* build_seconds);
 int feelgpu_pattern_destroy(feelgpu_pattern_t pattern);
 
 /* ---- work calls (replace the loop integrator.hpp:1093-1207 + MatSetValues/VecSetValues ADD_VALUES) ----------- */

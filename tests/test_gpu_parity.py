@@ -165,6 +165,29 @@ def test_row_thread_plan_with_many_small_patches(engine, meshes, order, ncomp, m
     check_values(a.values(), (ref[0] + refm[0], ref[1], ref[2]), scale + scalem, "k(x)*(stiffness+mass), small patches")
 
 
+def test_background_plan_build(engine):
+    """FEELGPU_PATTERN_ASYNC: the pattern is usable as soon as pattern_create returns (row-thread plan) while the entity plan
+    is built by a background thread; both give the oracle matrix, and asking for the entity plan by name waits for it"""
+    mesh = fpp.unitCube(12, 0.15, True)
+    Xh = fpp.Pch(mesh, 2)
+    u = v = fpp.Element(Xh)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, pattern_flags=fpp.PATTERN_ASYNC)
+    form = integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v)))
+    ref, scale = oracle_form2(orc.STIFFNESS, Xh, orc.quad_order_form2(orc.STIFFNESS, 2))
+    a.assign(form)                              # whichever plan is ready
+    check_values(a.values(), ref, scale, "async: first assembly")
+    ready, secs = a.plans_ready(wait=True)
+    assert ready and secs > 0 and a.plan_stats()["eplan"]["has_plan"] == 1
+    a.algorithm = fpp.ALGO_EPLAN
+    a.assign(form)
+    check_values(a.values(), ref, scale, "async: entity plan")
+    b = fpp.form2(_test=Xh, _trial=Xh, engine=engine, pattern_flags=fpp.PATTERN_ASYNC, algorithm=fpp.ALGO_EPLAN)
+    b.assign(form)                              # by name: waits for the build
+    check_values(b.values(), ref, scale, "async: entity plan by name")
+    c = fpp.form2(_test=Xh, _trial=Xh, engine=engine, pattern_flags=fpp.PATTERN_ASYNC)
+    c.close()                                   # destroyed while the build may still run
+
+
 @pytest.mark.parametrize("order", [1, 2, 3])
 def test_form1(engine, meshes, order):
     mesh = meshes["jit"]
