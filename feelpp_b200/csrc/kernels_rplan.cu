@@ -130,8 +130,10 @@ k_rplan_coeff(const FormParams* __restrict__ P, int64_t nElt, int nq, const doub
 
 // FORM 0: k*idt(u)*id(v), 1: k*gradt(u)*trans(grad(v)), 2: elasticity.  Thread = unit.  NQ > 0: quadrature points known at
 // compile time, tables in constant memory, loops unrolled; NQ = 0: any nq, tables in shared memory (mass / stiffness only).
+constexpr int rplan_threads(int form) { return form == 2 ? 512 : 640; }   // elasticity holds 3x3 blocks in registers
+
 template <int ORDER, int FORM, int NQ>
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(rplan_threads(FORM), 1)
 k_rplan(const RArgs A)
 {
     constexpr int N = (ORDER + 1) * (ORDER + 2) * (ORDER + 3) / 6;
@@ -535,7 +537,7 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     const size_t sh = rplan_smem_bytes(p, form, hp.nq, hp.nf);
     const int grid = (int)p->npatch;
     if (grid == 0) return FEELGPU_OK;
-    const int threads = std::min(512, std::max(64, env_int("FEELGPU_RPLAN_THREADS", 512)));
+    const int threads = std::min(rplan_threads(form), std::max(64, env_int("FEELGPU_RPLAN_THREADS", rplan_threads(form))));
     // constant-memory copy of the tables in the kernel's layout (stream-ordered; one context drives one stream at a time)
     const int n = p->n, nq = hp.nq;
     const bool fixed = !env_int("FEELGPU_RPLAN_NO_CONST", 0) && (nq == 1 || nq == 4 || nq == 5 || nq == 11 || nq == 14 || nq == 24);
