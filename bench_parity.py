@@ -40,6 +40,20 @@ def check(args, lp, gmesh, a, dist, oracle_kind_coeff, quad, sample_rows=SAMPLE_
     ratio = (s.abs() / rabs.clamp_min(1e-300))
     worst_inv = float(ratio.max().item()) if nO else 0.0
     inv_ok = worst_inv <= 1e-12
+    n_inv_bad = int((ratio > 1e-12).sum().item()) if nO else 0
+    if n_inv_bad:
+        # where: row, its sum and absolute sum, its largest entry -- on stderr, for the record
+        import sys
+        badk = torch.nonzero(ratio > 1e-12).flatten()[:8].cpu().numpy()
+        recv_rows_all = np.unique(np.concatenate([r for _, r, _ in lp.recv])) if lp.recv else np.zeros(0, dtype=np.int64)
+        for kk in badk:
+            r = int(kk) // ncomp
+            lo, hi = int(ia[r]), int(ia[r + 1])
+            rv = a.t_values[lo:hi].cpu().numpy()
+            print("[parity] rank %d: row %d (of %d owned) comp %d: sum %.3e abs-sum %.3e, %d entries, max |a| %.3e at col %d (diag col %d), "
+                  "receives ghost rows: %s" % (lp.comm.rank, r, nO, int(kk) % ncomp, float(s[kk]), float(rabs[kk]), hi - lo,
+                                              float(np.abs(rv).max()), int(lp.ja[lo + int(np.abs(rv).argmax())]), int(lp.p2c[r]),
+                                              bool(r in set(recv_rows_all.tolist()))), file=sys.stderr)
     del rows, cols, key, s, sabs, rabs, ratio
     # ---- (2) a sample of owned interface rows against the oracle ----
     recv_rows = np.unique(np.concatenate([r for _, r, _ in lp.recv])) if lp.recv else np.zeros(0, dtype=np.int64)
@@ -98,7 +112,7 @@ def check(args, lp, gmesh, a, dist, oracle_kind_coeff, quad, sample_rows=SAMPLE_
                 worst = max(worst, float((err / np.maximum(tol, 1e-300)).max()))
                 bad += int((err > tol).any())
                 rows_checked += 1
-    t = torch.tensor([worst_inv, worst, float(bad), float(rows_checked), float(nO), 0.0 if inv_ok else 1.0],
+    t = torch.tensor([worst_inv, worst, float(bad), float(rows_checked), float(nO), float(n_inv_bad)],
                      device=dev, dtype=torch.float64)
     every = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
     dist.all_gather(every, t)
@@ -106,7 +120,7 @@ def check(args, lp, gmesh, a, dist, oracle_kind_coeff, quad, sample_rows=SAMPLE_
     ok = bool((E[:, 2] == 0).all() and (E[:, 5] == 0).all() and (E[:, 1] <= 1.0).all())
     return {"ok": ok,
             "invariant": "per owned row and column component |sum_j a_ij| <= 1e-12 sum_j |a_ij| (constants / rigid translations in the kernel)",
-            "invariant_rows": int(E[:, 4].sum()), "invariant_worst": float(E[:, 0].max()),
+            "invariant_rows": int(E[:, 4].sum()), "invariant_rows_failed": int(E[:, 5].sum()), "invariant_worst": float(E[:, 0].max()),
             "oracle_rows_checked": int(E[:, 3].sum()), "oracle_rows_failed": int(E[:, 2].sum()),
             "worst_err_over_tol": float(E[:, 1].max()),
             "oracle_rows": "owned interface rows (rows that received ghost contributions), <= %d per rank, entry by entry "
