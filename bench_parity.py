@@ -41,6 +41,7 @@ def check(args, lp, gmesh, a, dist, oracle_kind_coeff, quad, sample_rows=SAMPLE_
     worst_inv = float(ratio.max().item()) if nO else 0.0
     inv_ok = worst_inv <= 1e-12
     n_inv_bad = int((ratio > 1e-12).sum().item()) if nO else 0
+    n_zero_rows = int((rabs == 0).sum().item()) if nO else 0        # an assembled row always has a positive diagonal
     if n_inv_bad:
         # where: row, its sum and absolute sum, its largest entry -- on stderr, for the record
         import sys
@@ -112,15 +113,15 @@ def check(args, lp, gmesh, a, dist, oracle_kind_coeff, quad, sample_rows=SAMPLE_
                 worst = max(worst, float((err / np.maximum(tol, 1e-300)).max()))
                 bad += int((err > tol).any())
                 rows_checked += 1
-    t = torch.tensor([worst_inv, worst, float(bad), float(rows_checked), float(nO), float(n_inv_bad)],
+    t = torch.tensor([worst_inv, worst, float(bad), float(rows_checked), float(nO), float(n_inv_bad), float(n_zero_rows)],
                      device=dev, dtype=torch.float64)
     every = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
     dist.all_gather(every, t)
     E = np.array([e.cpu().numpy() for e in every])
-    ok = bool((E[:, 2] == 0).all() and (E[:, 5] == 0).all() and (E[:, 1] <= 1.0).all())
+    ok = bool((E[:, 2] == 0).all() and (E[:, 5] == 0).all() and (E[:, 6] == 0).all() and (E[:, 1] <= 1.0).all())
     return {"ok": ok,
             "invariant": "per owned row and column component |sum_j a_ij| <= 1e-12 sum_j |a_ij| (constants / rigid translations in the kernel)",
-            "invariant_rows": int(E[:, 4].sum()), "invariant_rows_failed": int(E[:, 5].sum()), "invariant_worst": float(E[:, 0].max()),
+            "invariant_rows": int(E[:, 4].sum()), "invariant_rows_failed": int(E[:, 5].sum()), "all_zero_rows": int(E[:, 6].sum()), "invariant_worst": float(E[:, 0].max()),
             "oracle_rows_checked": int(E[:, 3].sum()), "oracle_rows_failed": int(E[:, 2].sum()),
             "worst_err_over_tol": float(E[:, 1].max()),
             "oracle_rows": "owned interface rows (rows that received ghost contributions), <= %d per rank, entry by entry "

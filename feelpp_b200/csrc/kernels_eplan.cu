@@ -193,8 +193,12 @@ k_eplan(const EPlanCta* __restrict__ ctas, int ncta, int* __restrict__ sched, co
             sX[2 * EPLAN_VERTS + tid] = sZ[tid];
         }
         if (tid == 0) *sCnt = EPLAN_WARPS;     // chunks 0..W-1 are the warps' first ones, the rest is handed out on demand
-        if (needzero)   // only when the graph holds entries that no element produces
+        if (needzero) {   // only when the graph holds entries that no element produces (owned rows of a partition's interface)
+            // every thread has waited for ITS OWN bulk copies of the previous patch only: the row block may be overwritten once
+            // all of them have (found by the multi-GPU parity block: 2-3 rows of 43 M came out zero, different ones every run)
+            __syncthreads();
             for (uint32_t i = tid; i < (nout + 1) / 2; i += blockDim.x) reinterpret_cast<double2*>(sO)[i] = make_double2(0.0, 0.0);
+        }
         __syncthreads();
         // ---- phase A1: geometry of every element touched by this patch's rows, once (thread = visit) ----
         if (tid < nvisit) {
