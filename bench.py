@@ -523,7 +523,9 @@ def gpu_arm(args):
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                 "step_frac_vs_peak": Be * nElt_total / world / (ms / args.steps * 1e-3) / 1e9 / peak}
         cpu = None
-        setup_s = sum(v for k, v in info.items() if k.endswith("_s"))
+        # host setup until the steady-state plans stand: mesh + DofTable, graph [partition, local problem], pattern + plans
+        setup_s = sum(info.get(k, 0.0) for k in ("mesh_doftable_s", "graph_s", "mesh_partition_s", "local_problem_s")) + \
+            info.get("plans_ready_s", info.get("pattern_create_s", 0.0))
         if not args.no_cpu_baseline and world == 1:
             cores = physical_cores()
             sample = cpu_sample_size(args, cores, nElt)

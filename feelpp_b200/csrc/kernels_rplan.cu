@@ -50,27 +50,8 @@ __constant__ double c_rxi[3 * FEELGPU_MAX_NQ];
 // shared-memory add of one double (a compare-and-swap loop in SASS, ATOMS.CAST.SPIN: no native fp64 shared atomic)
 __device__ __forceinline__ void sadd(double* p, double v) { atomicAdd(p, v); }
 
-// K adds to K distinct shared addresses with the K compare-and-swap chains in flight together: loads, sums and first
-// attempts are issued back to back (atomicAdd's own loop serialises load -> add -> CAS -> test per value); an attempt that
-// lost against another warp is repeated on its own
-template <int K>
-__device__ __forceinline__ void sadd_batch(double* const (&p)[K], const double (&v)[K])
-{
-    unsigned long long old[K], got[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) old[k] = *reinterpret_cast<volatile unsigned long long*>(p[k]);
-#pragma unroll
-    for (int k = 0; k < K; ++k)
-        got[k] = atomicCAS(reinterpret_cast<unsigned long long*>(p[k]), old[k],
-                           (unsigned long long)__double_as_longlong(__longlong_as_double((long long)old[k]) + v[k]));
-#pragma unroll
-    for (int k = 0; k < K; ++k)
-        while (got[k] != old[k]) {
-            old[k] = got[k];
-            got[k] = atomicCAS(reinterpret_cast<unsigned long long*>(p[k]), old[k],
-                               (unsigned long long)__double_as_longlong(__longlong_as_double((long long)old[k]) + v[k]));
-        }
-}
+// (issuing the compare-and-swap chains of several values together -- loads, sums, first attempts back to back -- was measured:
+// slower, 7.6 -> 12.6 ms on the elasticity form, 22.1 -> 22.9 ms on P3: more registers, no gain in the pipe)
 
 // the closed-form coefficient with its program in shared memory (the interpreter of device_common.cuh reads the program
 // from global memory: one dependent load per operation)
@@ -311,15 +292,8 @@ k_rplan(const RArgs A)
             }
             if (active) {
                 double* rb = blk + roff;
-                constexpr int KB = N % 5 == 0 ? 5 : 4;      // N = 4, 10, 20
 #pragma unroll
-                for (int j0 = 0; j0 < N; j0 += KB) {
-                    double* pa[KB];
-                    double va[KB];
-#pragma unroll
-                    for (int k = 0; k < KB; ++k) { pa[k] = rb + posj(j0 + k); va[k] = acc[j0 + k]; }
-                    sadd_batch<KB>(pa, va);
-                }
+                for (int j = 0; j < N; ++j) sadd(rb + posj(j), acc[j]);
             }
         } else if (NQ > 0) {
             // elasticity: physical gradients of the row function at the quadrature points, then column by column the 3x3 block
@@ -383,9 +357,8 @@ k_rplan(const RArgs A)
 #pragma unroll
                         for (int c1 = 0; c1 < 3; ++c1) {
                             double* rb = blk + roff + c1 * rlen + p0c;
-                            double* pa[3] = {rb, rb + 1, rb + 2};
-                            const double va[3] = {blkv[jj][c1 * 3], blkv[jj][c1 * 3 + 1], blkv[jj][c1 * 3 + 2]};
-                            sadd_batch<3>(pa, va);
+#pragma unroll
+                            for (int c2 = 0; c2 < 3; ++c2) sadd(rb + c2, blkv[jj][c1 * 3 + c2]);
                         }
                     }
                 }
