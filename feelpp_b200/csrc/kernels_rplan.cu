@@ -2,10 +2,12 @@
 //
 // Replaces, for coefficient-weighted mass / stiffness forms (cst, idv(k), expr("...")) of every order and for the
 // vector-elasticity form, the reference's per-element update/integrate/assemble + MatSetValues(ADD_VALUES)
-// (feelvf/integrator.hpp:1093-1207, feelvf/bilinearformcontext.hpp:585-589, feelalg/matrixpetsc.cpp:917-936): the thread
-// that owns a CSR row forms the rows of the local matrices of the elements around its node by the quadrature sum
-// (feelpoly/pointsetquadrature.hpp:403-416) and adds them into its own segment of the CTA's shared-memory row block; the
-// block leaves the SM once, with coalesced stores.  No atomics, no zero fill, fixed summation order.
+// (feelvf/integrator.hpp:1093-1207, feelvf/bilinearformcontext.hpp:585-589, feelalg/matrixpetsc.cpp:917-936): the CTA
+// that owns a patch of CSR rows forms, one thread per (row, element) unit, the rows of the local matrices of the elements
+// around the patch's nodes by the quadrature sum (feelpoly/pointsetquadrature.hpp:403-416) and adds them into the row's
+// segment of its shared-memory row block; the
+// block leaves the SM once, with coalesced stores.  No L2 atomics and no zero fill of the CSR array; the adds into the row
+// block are shared-memory atomics (rplan.h), so the summation order inside a value is not fixed (values within 1e-12).
 #include <string>
 #include "feelgpu_internal.h"
 #include "device_common.cuh"
