@@ -73,6 +73,7 @@ GPU_SYMBOLS = {
     "feelgpu_form2_assemble": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form1_assemble": [C.c_void_p, C.POINTER(Form1Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form2_assemble_host": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, c_dblp],
+    "feelgpu_form2_assemble_noalloc": [C.c_void_p, C.POINTER(Form2Desc), C.c_int, C.c_void_p, C.c_void_p],
     "feelgpu_form1_assemble_host": [C.c_void_p, C.POINTER(Form1Desc), C.c_int, c_dblp],
     "feelgpu_form2_zero_rows": [C.c_void_p, C.c_int64, c_i32p, c_dblp, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
                                 C.c_void_p],

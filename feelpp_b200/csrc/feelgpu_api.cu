@@ -509,6 +509,31 @@ int feelgpu_form2_assemble(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc
     return rc;
 }
 
+// Allocation-free variant (include/feelgpu.h): no cudaMalloc / cudaFree / allocating library call between entry and return;
+// the table cache, the background plan installer and the exchange bookkeeping of feelgpu_form2_assemble are not touched.
+int feelgpu_form2_assemble_noalloc(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc, int accumulate, double* a,
+                                   void* stream)
+{
+    if (!pat) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = pat->ctx;
+    if (!desc || !a) ARG_FAIL(ctx, "form2_assemble_noalloc: null argument");
+    if (pat->exchange) {
+        ctx->last_error = "form2_assemble_noalloc: patterns with an exchange attached are not supported";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    FormParams hp;
+    int rc = fill_params(ctx, desc->kind, desc->coeff, desc->tables, pat->test, true, &hp);
+    if (rc) return rc;
+    if (!feelgpu_rplan_noalloc_supports(pat, desc)) {
+        ctx->last_error = "form2_assemble_noalloc: needs a MASS / STIFFNESS form with a FIELD or EXPR coefficient on a scalar "
+                          "space whose pattern carries the row-thread plan";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    return feelgpu_launch_form2_rplan_noalloc(pat, hp, desc, accumulate, a, s);
+}
+
 int feelgpu_form1_assemble(feelgpu_space_t sp, const feelgpu_form1_desc* desc, int accumulate, double* b, void* stream)
 {
     if (!sp) return FEELGPU_ERR_ARG;

@@ -135,6 +135,10 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
                                int accumulate, double* a, cudaStream_t s);
 bool feelgpu_rplan_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
 int feelgpu_rplan_stats(feelgpu_pattern_t pat, int64_t stats[10]);
+// allocation-free variant (feelgpu_form2_assemble_noalloc): scratch in a static device array of kernels_rplan.cu
+bool feelgpu_rplan_noalloc_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc);
+int feelgpu_launch_form2_rplan_noalloc(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
+                                       int accumulate, double* a, cudaStream_t s);
 // ---- kernels_eplan.cu ----
 int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, bool async);
 int feelgpu_eplan_poll(feelgpu_pattern_t pat, bool wait);

@@ -610,6 +610,182 @@ int feelgpu_launch_form2_rplan(feelgpu_pattern_t pat, const FormParams& hp, cons
     return FEELGPU_OK;
 }
 
+// ---- allocation-free variant (feelgpu_form2_assemble_noalloc, include/feelgpu.h) ---------------------------------------
+// The coefficient pass writes k(x_q) of every (element, point) into scratch memory that the assembly kernel reads back; the
+// regular path keeps that scratch (and the parameter block + reference tables) in cudaMalloc'ed buffers.  This variant keeps
+// both in ONE file-scope device array of fixed size, so that the call allocates nothing: [0, NA_PAR_DOUBLES) the FormParams
+// block followed by phi | dphi | phif, then FEELGPU_NOALLOC_MAX_KQ doubles of kq.  Every GPU that loads the library holds
+// the array (16.05 MiB) until exit.  All calls share it: it keeps the previous call's contents (nothing in it has to start at
+// zero -- the copy and the coefficient pass overwrite every entry the assembly kernel reads) and calls that overlap on the
+// GPU (different streams, no ordering between them) race on it.
+namespace {
+
+constexpr size_t NA_TAB_DOUBLES = (size_t)5 * FEELGPU_MAX_NQ * FEELGPU_MAX_NLOC;           // phi (1) + dphi (3) + phif (1)
+constexpr size_t NA_PAR_DOUBLES = ((sizeof(FormParams) / 8 + NA_TAB_DOUBLES + 31) / 32) * 32;   // kq starts 256-byte aligned
+static_assert(sizeof(FormParams) % 8 == 0, "the tables follow the parameter block as doubles");
+
+static __device__ __align__(256) double g_noalloc_scratch[NA_PAR_DOUBLES + FEELGPU_NOALLOC_MAX_KQ];
+
+// In host code g_noalloc_scratch is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+constexpr int NA_MAX_DEVICES = 64;
+double* g_noalloc_ptr[NA_MAX_DEVICES] = {};
+
+int noalloc_scratch(feelgpu_context_t ctx, double** ptr)
+{
+    int dev = -1;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NA_MAX_DEVICES) {
+        ctx->last_error = "form2_assemble_noalloc: device ordinal outside [0,64)";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    double* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        FEELGPU_CHECK_CUDA(ctx, cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) {
+            ctx->last_error = "form2_assemble_noalloc: cudaGetSymbolAddress returned a null address";
+            return FEELGPU_ERR_CUDA;
+        }
+        __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);   // the same value whichever thread gets here first
+    }
+    *ptr = p;
+    return FEELGPU_OK;
+}
+
+template <int O, int F, int Q>
+cudaError_t na_launch(const RArgs& A, int grid, int threads, size_t sh, cudaStream_t s)
+{
+    cudaError_t err = cudaFuncSetAttribute(k_rplan<O, F, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+    if (err != cudaSuccess) return err;
+    k_rplan<O, F, Q><<<grid, threads, sh, s>>>(A);
+    return cudaGetLastError();
+}
+
+template <int O, int F>
+cudaError_t na_launch_q(bool fixed, int nq, const RArgs& A, int grid, int threads, size_t sh, cudaStream_t s)
+{
+    if (!fixed) return na_launch<O, F, 0>(A, grid, threads, sh, s);
+    switch (nq) {
+    case 1: return na_launch<O, F, 1>(A, grid, threads, sh, s);
+    case 4: return na_launch<O, F, 4>(A, grid, threads, sh, s);
+    case 5: return na_launch<O, F, 5>(A, grid, threads, sh, s);
+    case 11: return na_launch<O, F, 11>(A, grid, threads, sh, s);
+    case 14: return na_launch<O, F, 14>(A, grid, threads, sh, s);
+    default: return na_launch<O, F, 24>(A, grid, threads, sh, s);
+    }
+}
+
+} // namespace
+
+bool feelgpu_rplan_noalloc_supports(feelgpu_pattern_t pat, const feelgpu_form2_desc* desc)
+{
+    // the forms that use the scratch: mass / stiffness of a scalar space with a point-dependent coefficient
+    if (desc->kind != FEELGPU_FORM2_MASS && desc->kind != FEELGPU_FORM2_STIFFNESS) return false;
+    if (desc->coeff.kind != FEELGPU_COEFF_FIELD && desc->coeff.kind != FEELGPU_COEFF_EXPR) return false;
+    return feelgpu_rplan_supports(pat, desc);
+}
+
+int feelgpu_launch_form2_rplan_noalloc(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
+                                       int accumulate, double* a, cudaStream_t s)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    const RPlan* p = pat->rplan;
+    feelgpu_space_t sp = pat->test;
+    feelgpu_mesh_t m = sp->mesh;
+    const int form = rplan_form(desc), n = p->n, nq = hp.nq, nf = hp.nf;
+    const int64_t total = m->nElt * nq;
+    if (total > (int64_t)FEELGPU_NOALLOC_MAX_KQ) {
+        ctx->last_error = "form2_assemble_noalloc: elements x quadrature points = " + std::to_string(total) +
+                          " exceeds the static scratch (FEELGPU_NOALLOC_MAX_KQ = " + std::to_string((int64_t)FEELGPU_NOALLOC_MAX_KQ) +
+                          " doubles); use feelgpu_form2_assemble";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    if (n > FEELGPU_MAX_NLOC || nq > FEELGPU_MAX_NQ || nf > FEELGPU_MAX_NLOC) {
+        ctx->last_error = "form2_assemble_noalloc: tables larger than the static parameter block";
+        return FEELGPU_ERR_UNSUPPORTED;
+    }
+    const int grid = (int)p->npatch;
+    if (grid == 0) return FEELGPU_OK;
+    double* scratch = nullptr;
+    int rc = noalloc_scratch(ctx, &scratch);
+    if (rc) return rc;
+    double* d_kq = scratch + NA_PAR_DOUBLES;
+
+    // parameter block + tables, staged on the stack (the copy from pageable memory has left the buffer when the call returns)
+    alignas(16) double hb[sizeof(FormParams) / 8 + NA_TAB_DOUBLES];
+    std::memcpy(hb, &hp, sizeof(FormParams));
+    double* hphi = hb + sizeof(FormParams) / 8;
+    double* hdphi = hphi + (size_t)n * nq;
+    double* hphif = hdphi + (size_t)3 * n * nq;
+    std::memcpy(hphi, desc->tables.phi, sizeof(double) * n * nq);
+    if (desc->tables.dphi) std::memcpy(hdphi, desc->tables.dphi, sizeof(double) * 3 * n * nq);
+    else std::memset(hdphi, 0, sizeof(double) * 3 * n * nq);
+    if (nf) std::memcpy(hphif, desc->tables.phif, sizeof(double) * nf * nq);
+    const size_t used = sizeof(FormParams) / 8 + (size_t)4 * n * nq + (size_t)nf * nq;
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(scratch, hb, used * sizeof(double), cudaMemcpyHostToDevice, s));
+
+    RArgs A;
+    A.P = reinterpret_cast<const FormParams*>(scratch);
+    A.T.phi = scratch + sizeof(FormParams) / 8;
+    A.T.dphi = A.T.phi + (size_t)n * nq;
+    A.T.phif = A.T.dphi + (size_t)3 * n * nq;
+    A.T.M9 = nullptr;                 // not read by the row-thread kernels
+    A.T.Mm = nullptr;
+    A.patches = p->d_patches;
+    A.visits = p->d_visits;
+    A.rows = reinterpret_cast<const uint4*>(p->d_rows);
+    A.units = p->d_units;
+    A.xyz = m->d_xyz;
+    A.conn = m->d_conn;
+    A.pos = pat->d_pos;
+    A.l2gf = nullptr;
+    A.fvals = nullptr;
+    if (hp.coeff_kind == FEELGPU_COEFF_FIELD) {
+        A.l2gf = desc->coeff.field_space->d_l2g;
+        A.fvals = desc->coeff.field_values;
+    }
+    A.kq = d_kq;
+    A.a = a;
+    A.accumulate = accumulate;
+    A.maxslots = p->maxslots;
+    A.maxvis = p->maxvisits;
+    A.maxrows = p->maxrows;
+    const size_t sh = rplan_smem_bytes(p, form, nq, nf);
+    const int threads = rplan_threads(form);
+    const bool fixed = nq == 1 || nq == 4 || nq == 5 || nq == 11 || nq == 14 || nq == 24;
+    if (fixed) {
+        double ct[RTAB_MAX];
+        for (int j = 0; j < n; ++j)
+            for (int q = 0; q < nq; ++q) {
+                if (form == 0) ct[(size_t)q * n + j] = desc->tables.phi[j * nq + q];
+                else
+                    for (int c = 0; c < 3; ++c) ct[((size_t)q * 3 + c) * n + j] = desc->tables.dphi[(j * nq + q) * 3 + c];
+            }
+        const size_t cnt = (size_t)(form == 0 ? n * nq : 3 * n * nq);
+        FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rtab, ct, cnt * sizeof(double), 0, cudaMemcpyHostToDevice, s));
+    }
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rw, desc->tables.w, nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyToSymbolAsync(c_rxi, desc->tables.xi, 3 * nq * sizeof(double), 0, cudaMemcpyHostToDevice, s));
+
+    const int cgrid = (int)std::max<int64_t>(1, std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 32));
+    k_rplan_coeff<<<cgrid, 256, 0, s>>>(A.P, m->nElt, nq, m->d_xyz, m->d_conn, A.T.phif, A.l2gf, A.fvals, d_kq);
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    cudaError_t err;
+    switch (p->order * 2 + form) {
+    case 2: err = na_launch_q<1, 0>(fixed, nq, A, grid, threads, sh, s); break;
+    case 3: err = na_launch_q<1, 1>(fixed, nq, A, grid, threads, sh, s); break;
+    case 4: err = na_launch_q<2, 0>(fixed, nq, A, grid, threads, sh, s); break;
+    case 5: err = na_launch_q<2, 1>(fixed, nq, A, grid, threads, sh, s); break;
+    case 6: err = na_launch_q<3, 0>(fixed, nq, A, grid, threads, sh, s); break;
+    case 7: err = na_launch_q<3, 1>(fixed, nq, A, grid, threads, sh, s); break;
+    default: ctx->last_error = "form2_assemble_noalloc: unsupported order / form"; return FEELGPU_ERR_UNSUPPORTED;
+    }
+    ctx->launches++;
+    FEELGPU_CHECK_CUDA(ctx, err);
+    return FEELGPU_OK;
+}
+
 // ---- host-side view of the plan (include/feelgpu.h): no device needed, used by the CPU tests ----------------------------
 extern "C" {
 

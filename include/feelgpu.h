@@ -167,6 +167,22 @@ int feelgpu_form2_assemble_host(feelgpu_pattern_t pattern, const feelgpu_form2_d
                                 double* a_host /*[nnz]*/);
 int feelgpu_form1_assemble_host(feelgpu_space_t space, const feelgpu_form1_desc* desc, int accumulate,
                                 double* b_host);
+/* Allocation-free variant of feelgpu_form2_assemble for the forms whose kernels use scratch memory: MASS / STIFFNESS of a
+ * scalar space with a point-dependent coefficient (FEELGPU_COEFF_FIELD, FEELGPU_COEFF_EXPR) through the row-thread plan
+ * (the pattern must carry it: FEELGPU_PATTERN_RPLAN, the default).  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The coefficient values k(x_q) [nElt][nq], the parameter block and the reference tables live in ONE static
+ * device array of the library (16.05 MiB, held by every GPU that loads the library until exit) instead of cudaMalloc'ed
+ * buffers; the call issues no cudaMalloc / cudaFree and calls no allocating library routine.  Limit: nElt * tables.nq <=
+ * FEELGPU_NOALLOC_MAX_KQ, otherwise FEELGPU_ERR_UNSUPPORTED with a message (use feelgpu_form2_assemble).  Patterns with an
+ * exchange attached (multi-GPU) are refused.  Inputs, outputs and semantics are those of feelgpu_form2_assemble
+ * (desc->algorithm is ignored); results agree with it within the tolerance of the row-thread plan (1e-12 relative to the
+ * row's absolute sum; the order of the shared-memory adds is not fixed).  All calls share the static array: calls that
+ * overlap on the GPU (different streams without ordering between them, or several host threads) race on it -- order them
+ * on one stream or with events.  Nothing in the array has to start at zero: each call overwrites what its kernels read.  */
+#define FEELGPU_NOALLOC_MAX_KQ 2097152   /* doubles of coefficient scratch: elements x quadrature points */
+int feelgpu_form2_assemble_noalloc(feelgpu_pattern_t pattern, const feelgpu_form2_desc* desc, int accumulate,
+                                   double* a_values /*DEVICE [nnz], slot order == ja order*/, void* stream);
 
 /* ---- on(): Dirichlet elimination on the assembled matrix and right-hand side -----------------------------------------
  * form2 += on(_range=boundaryfaces(mesh), _rhs=l, _element=u, _expr=g) collects the boundary dofs and their values on the
