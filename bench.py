@@ -169,16 +169,24 @@ def bytes_per_element(args, npts, nelt, nnz):
     return be
 
 
-def workload(args, want_graph=True):
-    """builds the host-side objects (untimed setup)"""
+def workload(args, want_graph=True, eng=None):
+    """builds the host-side objects (untimed setup); with an engine the COUPLED graph is built on the device
+    (feelgpu_graph_create, bit-exact with the host graph: tests/test_gpu_parity.py)"""
     import feelpp_b200 as fpp
     t0 = time.time()
     mesh = fpp.loadMesh(args.mesh) if args.mesh else fpp.unitCube(args.m_global, 0.15, args.shuffle)
     Xh = make_space(args, mesh)
     t1 = time.time()
-    ia, ja = Xh.graph() if want_graph else (None, None)
+    if not want_graph:
+        ia, ja = None, None
+    elif eng is not None:
+        ia, ja = eng.graph(Xh)
+        Xh._graph = (ia, ja)      # form2() asks the space for its graph: the device one stands in (same arrays, bit for bit)
+    else:
+        ia, ja = Xh.graph()
     t2 = time.time()
-    info = {"mesh_doftable_s": round(t1 - t0, 2), "graph_s": round(t2 - t1, 2)}
+    info = {"mesh_doftable_s": round(t1 - t0, 2), "graph_s": round(t2 - t1, 2),
+            "graph": "device (feelgpu_graph_create + copy to the host)" if eng is not None and want_graph else "host"}
     return mesh, Xh, ia, ja, info
 
 
@@ -341,7 +349,7 @@ def gpu_arm(args):
     eng = fpp.Engine(local)
     lp = None
     if world == 1:
-        mesh, Xh, ia, ja, info = workload(args)
+        mesh, Xh, ia, ja, info = workload(args, eng=eng)
         nElt, nnz = mesh.numElements(), int(ia[-1])
         t0 = time.time()
         # FEELGPU_PATTERN_ASYNC: pattern_create returns once the row-thread plan stands (assembly can start); the entity plan

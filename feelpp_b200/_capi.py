@@ -80,6 +80,7 @@ GPU_SYMBOLS = {
     "feelgpu_malloc": [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)],
     "feelgpu_free": [C.c_void_p, C.c_void_p],
     "feelgpu_memcpy_h2d": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64],
+    "feelgpu_memset_zero": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
     "feelgpu_memcpy_d2h": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64],
     "feelgpu_host_alloc_pinned": [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)],
     "feelgpu_host_free_pinned": [C.c_void_p, C.c_void_p],

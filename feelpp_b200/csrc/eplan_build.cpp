@@ -10,6 +10,18 @@
 
 namespace {
 
+// f(k0, k1, t) on contiguous pieces of [0, n), one per thread
+template <class F>
+void parallel_for(int64_t n, int nthreads, F f, int64_t serial_below = 65536)
+{
+    nthreads = (int)std::min<int64_t>(nthreads, n);
+    if (nthreads <= 1 || n < serial_below) { f((int64_t)0, n, 0); return; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < nthreads; ++t) th.emplace_back([=] { f(n * t / nthreads, n * (t + 1) / nthreads, t); });
+    f((int64_t)0, n / nthreads, 0);
+    for (auto& x : th) x.join();
+}
+
 // local entity numbering of the reference tetrahedron (feelmesh/simplexordering.hpp:283-291)
 const int E2P[6][2] = {{1, 2}, {2, 0}, {0, 1}, {0, 3}, {1, 3}, {2, 3}};
 
@@ -126,59 +138,110 @@ struct Builder {
     inline int64_t node_of(int64_t e, int i) const { return l2g[e * nd + i] / ncomp; }
     inline int row_len(int64_t node) const { return (int)((ia[node * ncomp + 1] - ia[node * ncomp]) / ncomp); }
 
-    void node_units()
+    // units of every node in ascending element order (every task sums its elements in mesh order).  Counting and filling run
+    // on all threads with atomic cursors; the few units of a node are then put back in element order (an element holds a
+    // node once, so the order is unique and the result does not depend on the thread count).
+    void node_units(int nthreads)
     {
         nptr.assign(nNode + 1, 0);
-        for (int64_t e = 0; e < nElt; ++e)
-            for (int i = 0; i < n; ++i) nptr[node_of(e, i) + 1]++;
+        int64_t* cnt = nptr.data() + 1;
+        parallel_for(nElt, nthreads, [&](int64_t e0, int64_t e1, int) {
+            for (int64_t e = e0; e < e1; ++e)
+                for (int i = 0; i < n; ++i) __atomic_fetch_add(&cnt[node_of(e, i)], (int64_t)1, __ATOMIC_RELAXED);
+        });
         for (int64_t k = 0; k < nNode; ++k) nptr[k + 1] += nptr[k];
         uelt.resize(nptr[nNode]);
         uloc.resize(nptr[nNode]);
         std::vector<int64_t> cur(nptr.begin(), nptr.end() - 1);
-        for (int64_t e = 0; e < nElt; ++e)          // ascending e: every task sums its elements in mesh order
-            for (int i = 0; i < n; ++i) {
-                int64_t q = cur[node_of(e, i)]++;
-                uelt[q] = (int32_t)e;
-                uloc[q] = (uint8_t)i;
-            }
+        parallel_for(nElt, nthreads, [&](int64_t e0, int64_t e1, int) {
+            for (int64_t e = e0; e < e1; ++e)
+                for (int i = 0; i < n; ++i) {
+                    const int64_t q = __atomic_fetch_add(&cur[node_of(e, i)], (int64_t)1, __ATOMIC_RELAXED);
+                    uelt[q] = (int32_t)e;
+                    uloc[q] = (uint8_t)i;
+                }
+        });
+        parallel_for(nNode, nthreads, [&](int64_t k0, int64_t k1, int) {
+            for (int64_t k = k0; k < k1; ++k)
+                for (int64_t a = nptr[k] + 1; a < nptr[k + 1]; ++a) {      // insertion sort by element
+                    const int32_t e = uelt[a];
+                    const uint8_t l = uloc[a];
+                    int64_t b = a;
+                    for (; b > nptr[k] && uelt[b - 1] > e; --b) { uelt[b] = uelt[b - 1]; uloc[b] = uloc[b - 1]; }
+                    uelt[b] = e;
+                    uloc[b] = l;
+                }
+        });
     }
 
-    void curve_order()
+    void curve_order(int nthreads)
     {
         double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
-        for (int64_t e = 0; e < nElt; ++e)
-            for (int a = 0; a < 4; ++a)
-                for (int c = 0; c < 3; ++c) {
-                    double x = xyz[3 * (int64_t)conn[4 * e + a] + c];
-                    lo[c] = std::min(lo[c], x);
-                    hi[c] = std::max(hi[c], x);
-                }
+        {
+            std::vector<double> plo((size_t)std::max(nthreads, 1) * 3, 1e300), phi((size_t)std::max(nthreads, 1) * 3, -1e300);
+            parallel_for(nElt, nthreads, [&](int64_t e0, int64_t e1, int t) {
+                double l[3] = {1e300, 1e300, 1e300}, h[3] = {-1e300, -1e300, -1e300};
+                for (int64_t e = e0; e < e1; ++e)
+                    for (int a = 0; a < 4; ++a)
+                        for (int c = 0; c < 3; ++c) {
+                            const double x = xyz[3 * (int64_t)conn[4 * e + a] + c];
+                            l[c] = std::min(l[c], x);
+                            h[c] = std::max(h[c], x);
+                        }
+                for (int c = 0; c < 3; ++c) { plo[(size_t)t * 3 + c] = l[c]; phi[(size_t)t * 3 + c] = h[c]; }
+            });
+            for (size_t t = 0; t < plo.size() / 3; ++t)
+                for (int c = 0; c < 3; ++c) { lo[c] = std::min(lo[c], plo[t * 3 + c]); hi[c] = std::max(hi[c], phi[t * 3 + c]); }
+        }
         // one scale for the three axes: the curve's cells stay cubes on a partition whose bounding box is not one
         double sc[3], ext = 0.0;
         for (int c = 0; c < 3; ++c) ext = std::max(ext, hi[c] - lo[c]);
         for (int c = 0; c < 3; ++c) sc[c] = ext > 0.0 ? 1023.999 / ext : 0.0;
         std::vector<uint64_t> key(nNode);
-        for (int64_t k = 0; k < nNode; ++k) {
-            if (nptr[k] == nptr[k + 1]) { key[k] = ((uint64_t)0x3FFFFFFF << 32) | (uint32_t)k; continue; }
-            const int64_t e = uelt[nptr[k]];
-            const int i = uloc[nptr[k]];
-            int v[2], nv = 1;
-            if (i < 4) v[0] = i;
-            else { v[0] = E2P[i - 4][0]; v[1] = E2P[i - 4][1]; nv = 2; }
-            double p[3] = {0, 0, 0};
-            for (int a = 0; a < nv; ++a)
-                for (int c = 0; c < 3; ++c) p[c] += xyz[3 * (int64_t)conn[4 * e + v[a]] + c];
-            uint32_t m = 0;
-            if (use_hilbert)
-                m = hilbert3((uint32_t)((p[0] / nv - lo[0]) * sc[0]), (uint32_t)((p[1] / nv - lo[1]) * sc[1]),
-                             (uint32_t)((p[2] / nv - lo[2]) * sc[2]));
-            else
-                for (int c = 0; c < 3; ++c) m |= spread3((uint32_t)((p[c] / nv - lo[c]) * sc[c])) << c;
-            key[k] = ((uint64_t)m << 32) | (uint32_t)k;
+        parallel_for(nNode, nthreads, [&](int64_t k0, int64_t k1, int) {
+            for (int64_t k = k0; k < k1; ++k) {
+                if (nptr[k] == nptr[k + 1]) { key[k] = ((uint64_t)0x3FFFFFFF << 32) | (uint32_t)k; continue; }
+                const int64_t e = uelt[nptr[k]];
+                const int i = uloc[nptr[k]];
+                int v[2], nv = 1;
+                if (i < 4) v[0] = i;
+                else { v[0] = E2P[i - 4][0]; v[1] = E2P[i - 4][1]; nv = 2; }
+                double p[3] = {0, 0, 0};
+                for (int a = 0; a < nv; ++a)
+                    for (int c = 0; c < 3; ++c) p[c] += xyz[3 * (int64_t)conn[4 * e + v[a]] + c];
+                uint32_t m = 0;
+                if (use_hilbert)
+                    m = hilbert3((uint32_t)((p[0] / nv - lo[0]) * sc[0]), (uint32_t)((p[1] / nv - lo[1]) * sc[1]),
+                                 (uint32_t)((p[2] / nv - lo[2]) * sc[2]));
+                else
+                    for (int c = 0; c < 3; ++c) m |= spread3((uint32_t)((p[c] / nv - lo[c]) * sc[c])) << c;
+                key[k] = ((uint64_t)m << 32) | (uint32_t)k;
+            }
+        });
+        {   // the keys are distinct (node id in the low word): chunks sorted by the threads, then merged pairwise
+            int nch = 1;
+            while (nch * 2 <= nthreads && (int64_t)key.size() / (nch * 2) > 65536) nch *= 2;
+            std::vector<size_t> cut((size_t)nch + 1);
+            for (int c = 0; c <= nch; ++c) cut[c] = key.size() * (size_t)c / nch;
+            {
+                std::vector<std::thread> th;
+                for (int c = 1; c < nch; ++c) th.emplace_back([&, c] { std::sort(key.begin() + cut[c], key.begin() + cut[c + 1]); });
+                std::sort(key.begin() + cut[0], key.begin() + cut[1]);
+                for (auto& x : th) x.join();
+            }
+            for (int w = 1; w < nch; w *= 2) {
+                std::vector<std::thread> th;
+                for (int c = 0; c + w < nch; c += 2 * w)
+                    th.emplace_back([&, c, w] {
+                        std::inplace_merge(key.begin() + cut[c], key.begin() + cut[c + w], key.begin() + cut[std::min(c + 2 * w, nch)]);
+                    });
+                for (auto& x : th) x.join();
+            }
         }
-        std::sort(key.begin(), key.end());
         order_.resize(nNode);
-        for (int64_t k = 0; k < nNode; ++k) order_[k] = (int32_t)(key[k] & 0xFFFFFFFFu);
+        parallel_for(nNode, nthreads, [&](int64_t k0, int64_t k1, int) {
+            for (int64_t k = k0; k < k1; ++k) order_[k] = (int32_t)(key[k] & 0xFFFFFFFFu);
+        });
     }
 
     // entries of one unit (row node, element e, local dof i)
@@ -411,95 +474,162 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     B.pos = pos;
     if (nRows % ncomp) { plan.error = "entity plan: rows not a multiple of ncomp"; return false; }
     if (omax < 512 || omax > 32767) { plan.error = "entity plan: bad out-buffer size"; return false; }
-    for (int64_t e = 0; e < nElt; ++e) {
-        for (int i = 0; i < B.n; ++i)
-            if (l2g[e * nd + i] >= nRows) { plan.error = "entity plan: a test dof has no CSR row"; return false; }
-        for (int a = 0; a < 4; ++a)
-            for (int b = a + 1; b < 4; ++b)
-                if (conn[4 * e + a] == conn[4 * e + b]) { plan.error = "entity plan: degenerate element"; return false; }
-    }
-    lap("input checks");
-    B.node_units();
-    lap("node -> element units");
-    if (const char* cv = std::getenv("FEELGPU_EPLAN_CURVE")) B.use_hilbert = std::strcmp(cv, "morton") != 0;
-    B.curve_order();
-    lap("space-filling curve order");
     if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
     nthreads = std::min(nthreads, 64);
+    {
+        std::vector<int> bad((size_t)nthreads, 0);
+        parallel_for(nElt, nthreads, [&](int64_t e0, int64_t e1, int t) {
+            int b = 0;
+            for (int64_t e = e0; e < e1 && !b; ++e) {
+                for (int i = 0; i < B.n; ++i)
+                    if (l2g[e * nd + i] < 0 || l2g[e * nd + i] >= nRows) b = 1;
+                for (int a = 0; a < 4; ++a)
+                    for (int c = a + 1; c < 4; ++c)
+                        if (conn[4 * e + a] == conn[4 * e + c]) b = std::max(b, 2);
+            }
+            bad[t] = b;
+        });
+        for (int b : bad) {
+            if (b == 1) { plan.error = "entity plan: a test dof has no CSR row"; return false; }
+            if (b == 2) { plan.error = "entity plan: degenerate element"; return false; }
+        }
+    }
+    lap("input checks");
+    B.node_units(nthreads);
+    lap("node -> element units");
+    if (const char* cv = std::getenv("FEELGPU_EPLAN_CURVE")) B.use_hilbert = std::strcmp(cv, "morton") != 0;
+    B.curve_order(nthreads);
+    lap("space-filling curve order");
 
     // ---- CTA packing along the curve: consecutive rows while visits, unique vertices and outputs fit ----
+    // The curve is cut into pieces of PACK_PIECE rows that are packed independently (a piece ends with a CTA that may be short:
+    // 1 in ~240 for P2); the pieces are a property of the mesh, not of the thread count, so the plan does not depend on it.
     std::vector<CtaSeg> segs;
     B.uvis.resize(B.uelt.size());
     plan.verts.clear();
     plan.visits.clear();
     const int vstride = order == 2 ? 4 : 1;   // words per visit: vertex bytes [+ 6 u16 row-block slots of the tet-type outputs]
     {
-        std::vector<int32_t> estamp(nElt, -1), eslot(nElt, 0), pstamp(nPts, -1), pslot(nPts, 0), newpts;
-        int64_t k = 0;
-        while (k < B.nNode) {
-            CtaSeg sg;
-            sg.nb = k;
-            sg.vert_off = (uint32_t)plan.verts.size();
-            sg.visit_off = (uint32_t)plan.visits.size();
-            const int32_t id = (int32_t)segs.size();
-            uint32_t nv = 0, np = 0, nout = 1;      // slot 0 of the out buffer is the trash cell
-            int64_t rows = 0;
-            for (; k < B.nNode; ++k) {
-                const int64_t node = B.order_[k];
-                uint32_t addv = 0, addp = 0;
-                newpts.clear();
-                for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) {
-                    const int32_t e = B.uelt[q];
-                    if (estamp[e] != id) {
-                        ++addv;
-                        for (int a = 0; a < 4; ++a) {
-                            const int32_t pt = conn[4 * e + a];
-                            if (pstamp[pt] != id && std::find(newpts.begin(), newpts.end(), pt) == newpts.end()) newpts.push_back(pt);
-                        }
-                    }
+        constexpr int64_t PACK_PIECE = 1 << 16;
+        struct Piece { std::vector<CtaSeg> segs; std::vector<int32_t> verts; std::vector<uint32_t> visits; std::string error; };
+        const int64_t npiece = std::max<int64_t>(1, (B.nNode + PACK_PIECE - 1) / PACK_PIECE);
+        std::vector<Piece> pieces((size_t)npiece);
+        int64_t next_piece = 0;
+        auto pack = [&]() {
+            std::vector<int32_t> estamp, eslot, pstamp, pslot, newpts;
+            int32_t id = 0;                       // stamp of the CTA being packed (unique inside this thread's arrays)
+            for (;;) {
+                const int64_t pi = __atomic_fetch_add(&next_piece, (int64_t)1, __ATOMIC_RELAXED);
+                if (pi >= npiece) break;
+                if (estamp.empty()) {
+                    estamp.assign((size_t)nElt, -1);
+                    eslot.assign((size_t)nElt, 0);
+                    pstamp.assign((size_t)nPts, -1);
+                    pslot.assign((size_t)nPts, 0);
                 }
-                addp = (uint32_t)newpts.size();
-                const uint32_t len = (uint32_t)B.row_len(node);
-                if (rows > 0 && (nv + addv > EPLAN_VS - 1 || np + addp > EPLAN_VERTS || nout + len > (uint32_t)omax - (B.ncomp == 1 ? EPLAN_PADRES : 0) ||
-                                 rows >= EPLAN_ROWS))
-                    break;
-                if (addv > EPLAN_VS - 1 || addp > EPLAN_VERTS || 1 + len > (uint32_t)omax) {
-                    plan.error = "entity plan: a single row exceeds the CTA limits (elements around a node / row length)";
-                    return false;
-                }
-                for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) {
-                    const int32_t e = B.uelt[q];
-                    if (estamp[e] != id) {
-                        estamp[e] = id;
-                        eslot[e] = (int32_t)nv++;
-                        uint32_t w = 0;
-                        for (int a = 0; a < 4; ++a) {
-                            const int32_t pt = conn[4 * e + a];
-                            if (pstamp[pt] != id) {
-                                pstamp[pt] = id;
-                                pslot[pt] = (int32_t)np++;
-                                plan.verts.push_back(pt);
+                Piece& P = pieces[(size_t)pi];
+                const int64_t kend = std::min(B.nNode, (pi + 1) * PACK_PIECE);
+                int64_t k = pi * PACK_PIECE;
+                while (k < kend) {
+                    CtaSeg sg;
+                    sg.nb = k;
+                    sg.vert_off = (uint32_t)P.verts.size();       // inside the piece; rebased below
+                    sg.visit_off = (uint32_t)P.visits.size();
+                    ++id;
+                    uint32_t nv = 0, np = 0, nout = 1;      // slot 0 of the out buffer is the trash cell
+                    int64_t rows = 0;
+                    for (; k < kend; ++k) {
+                        const int64_t node = B.order_[k];
+                        uint32_t addv = 0, addp = 0;
+                        newpts.clear();
+                        for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) {
+                            const int32_t e = B.uelt[q];
+                            if (estamp[e] != id) {
+                                ++addv;
+                                for (int a = 0; a < 4; ++a) {
+                                    const int32_t pt = conn[4 * e + a];
+                                    if (pstamp[pt] != id && std::find(newpts.begin(), newpts.end(), pt) == newpts.end()) newpts.push_back(pt);
+                                }
                             }
-                            w |= (uint32_t)pslot[pt] << (8 * a);
                         }
-                        plan.visits.push_back(w);
-                        for (int z = 1; z < vstride; ++z) plan.visits.push_back(0u);   // filled per CTA below
+                        addp = (uint32_t)newpts.size();
+                        const uint32_t len = (uint32_t)B.row_len(node);
+                        if (rows > 0 && (nv + addv > EPLAN_VS - 1 || np + addp > EPLAN_VERTS ||
+                                         nout + len > (uint32_t)omax - (B.ncomp == 1 ? EPLAN_PADRES : 0) || rows >= EPLAN_ROWS))
+                            break;
+                        if (addv > EPLAN_VS - 1 || addp > EPLAN_VERTS || 1 + len > (uint32_t)omax) {
+                            P.error = "entity plan: a single row exceeds the CTA limits (elements around a node / row length)";
+                            return;
+                        }
+                        for (int64_t q = B.nptr[node]; q < B.nptr[node + 1]; ++q) {
+                            const int32_t e = B.uelt[q];
+                            if (estamp[e] != id) {
+                                estamp[e] = id;
+                                eslot[e] = (int32_t)nv++;
+                                uint32_t w = 0;
+                                for (int a = 0; a < 4; ++a) {
+                                    const int32_t pt = conn[4 * e + a];
+                                    if (pstamp[pt] != id) {
+                                        pstamp[pt] = id;
+                                        pslot[pt] = (int32_t)np++;
+                                        P.verts.push_back(pt);
+                                    }
+                                    w |= (uint32_t)pslot[pt] << (8 * a);
+                                }
+                                P.visits.push_back(w);
+                                for (int z = 1; z < vstride; ++z) P.visits.push_back(0u);   // filled per CTA below
+                            }
+                            B.uvis[q] = (uint16_t)eslot[e];
+                        }
+                        nout += len;
+                        ++rows;
                     }
-                    B.uvis[q] = (uint16_t)eslot[e];
+                    sg.ne = k;
+                    sg.nverts = (uint16_t)np;
+                    P.verts.resize((size_t)sg.vert_off + EPLAN_VERTS, 0);   // fixed stride: the kernel loads ids before it has the CTA header
+                    sg.nvisit = (uint16_t)nv;
+                    sg.nout = nout;
+                    P.segs.push_back(sg);
                 }
-                nout += len;
-                ++rows;
             }
-            sg.ne = k;
-            sg.nverts = (uint16_t)np;
-            plan.verts.resize((size_t)sg.vert_off + EPLAN_VERTS, 0);   // fixed stride: the kernel loads ids before it has the CTA header
-            sg.nvisit = (uint16_t)nv;
-            sg.nout = nout;
-            segs.push_back(sg);
+        };
+        {
+            // every packing thread holds stamp arrays over the elements and points: a handful of threads is enough here
+            const int npack = (int)std::max<int64_t>(1, std::min<int64_t>(std::min(nthreads, 16), npiece));
+            std::vector<std::thread> th;
+            for (int t = 1; t < npack; ++t) th.emplace_back(pack);
+            pack();
+            for (auto& x : th) x.join();
         }
+        size_t nsg = 0, nvt = 0, nvs = 0;
+        std::vector<size_t> sgb((size_t)npiece), vtb((size_t)npiece), vsb((size_t)npiece);
+        for (int64_t pi = 0; pi < npiece; ++pi) {
+            const Piece& P = pieces[(size_t)pi];
+            if (!P.error.empty()) { plan.error = P.error; return false; }
+            sgb[(size_t)pi] = nsg; vtb[(size_t)pi] = nvt; vsb[(size_t)pi] = nvs;
+            nsg += P.segs.size(); nvt += P.verts.size(); nvs += P.visits.size();
+        }
+        if (nvt > 0xFFFFFFFFull || nvs > 0xFFFFFFFFull) { plan.error = "entity plan: visit offsets exceed 32 bits"; return false; }
+        segs.resize(nsg);
+        plan.verts.resize(nvt);
+        plan.visits.resize(nvs);
+        parallel_for(npiece, nthreads, [&](int64_t p0, int64_t p1, int) {
+            for (int64_t pi = p0; pi < p1; ++pi) {
+                Piece& P = pieces[(size_t)pi];
+                for (size_t c = 0; c < P.segs.size(); ++c) {
+                    CtaSeg sg = P.segs[c];
+                    sg.vert_off += (uint32_t)vtb[(size_t)pi];
+                    sg.visit_off += (uint32_t)vsb[(size_t)pi];
+                    segs[sgb[(size_t)pi] + c] = sg;
+                }
+                if (!P.verts.empty()) std::memcpy(plan.verts.data() + vtb[(size_t)pi], P.verts.data(), P.verts.size() * sizeof(int32_t));
+                if (!P.visits.empty()) std::memcpy(plan.visits.data() + vsb[(size_t)pi], P.visits.data(), P.visits.size() * sizeof(uint32_t));
+                P = Piece();
+            }
+        }, 4);
     }
 
-    lap("CTA packing (serial)");
+    lap("CTA packing");
     // ---- tasks and chunks, in parallel over CTAs ----
     const int64_t nCta = (int64_t)segs.size();
     const EPlanSpec& S = *B.spec;
@@ -810,14 +940,34 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             size_t bsize = 0;
                             std::vector<uint32_t>* bcv = nullptr;
                             if (nt == 2) {
-                                for (int a2 = 0; a2 < 16; ++a2)      // a2: bank pair of iteration 0, b2: of iteration 1
-                                    for (uint32_t mb = ne[a2]; mb; mb &= mb - 1) {
+                                // (for a given a2 only the b2 of least count can win: the others are skipped through the masks
+                                // of the bank pairs by their count in iteration 1 -- same choice as the full scan, a third of the work)
+                                uint32_t bycnt[18];
+                                for (int z = 0; z < 18; ++z) bycnt[z] = 0;
+                                for (int b2 = 0; b2 < 16; ++b2) bycnt[std::min(cnt2[16 + b2], 17)] |= 1u << b2;
+                                for (int a2 = 0; a2 < 16; ++a2) {    // a2: bank pair of iteration 0, b2: of iteration 1
+                                    const uint32_t na = ne[a2];
+                                    if (!na || cnt2[a2] > bcost) continue;
+                                    int c1 = 0;
+                                    while (c1 < 18 && !(na & bycnt[c1])) ++c1;
+                                    const int cost = cnt2[a2] + c1;
+                                    if (c1 >= 17) {                   // (never with 16 lanes per half-warp; kept exact all the same)
+                                        for (uint32_t mb = na; mb; mb &= mb - 1) {
+                                            const int b2 = __builtin_ctz(mb);
+                                            std::vector<uint32_t>& cv2 = cell[std::min(a2, b2) * 16 + std::max(a2, b2)];
+                                            const int co = cnt2[a2] + cnt2[16 + b2];
+                                            if (co < bcost || (co == bcost && cv2.size() > bsize)) { bcost = co; bsize = cv2.size(); bcv = &cv2; ba = a2; bb = b2; }
+                                        }
+                                        continue;
+                                    }
+                                    if (cost > bcost) continue;
+                                    for (uint32_t mb = na & bycnt[c1]; mb; mb &= mb - 1) {
                                         const int b2 = __builtin_ctz(mb);
                                         std::vector<uint32_t>& cv2 = cell[std::min(a2, b2) * 16 + std::max(a2, b2)];
                                         const size_t sz = cv2.size();
-                                        const int cost = cnt2[a2] + cnt2[16 + b2];
                                         if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bcv = &cv2; ba = a2; bb = b2; }
                                     }
+                                }
                             } else {
                                 for (int a2 = 0; a2 < 16; ++a2) {
                                     const size_t sz = cell1[a2].size();
@@ -946,45 +1096,60 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     for (auto& L : locals) { nq += L.blob.size() / 4; nch += L.chunks.size(); nrw += L.rows.size(); }
     if (nq + 64 > 0xFFFFFFFFull) { plan.error = "entity plan: blob offsets exceed 32 bits"; return false; }
     plan.ctas.resize(nCta);
-    plan.chunks.reserve(nch);
-    plan.rows.reserve(nrw);
-    plan.blob.reserve(nq * 4 + 64);
-    int64_t c = 0;
-    for (auto& L : locals) {
-        const uint32_t cb = (uint32_t)plan.chunks.size(), rb = (uint32_t)plan.rows.size(), qb = (uint32_t)(plan.blob.size() / 4);
-        for (auto h : L.chunks) {
-            h.q0 += qb;
-            plan.chunks.push_back(h);
+    plan.chunks.resize(nch);
+    plan.rows.resize(nrw);
+    plan.blob.resize(nq * 4 + 64);             // (the 64 trailing words stay zero)
+    {
+        // thread t built the CTAs [nCta t / nthreads, nCta (t+1) / nthreads): its pieces go behind those of the threads before it
+        std::vector<size_t> cb((size_t)nthreads), rb((size_t)nthreads), qb((size_t)nthreads);
+        size_t c0 = 0, r0 = 0, q0 = 0;
+        for (int t = 0; t < nthreads; ++t) {
+            cb[t] = c0; rb[t] = r0; qb[t] = q0;
+            c0 += locals[t].chunks.size(); r0 += locals[t].rows.size(); q0 += locals[t].blob.size() / 4;
         }
-        plan.rows.insert(plan.rows.end(), L.rows.begin(), L.rows.end());
-        plan.blob.insert(plan.blob.end(), L.blob.begin(), L.blob.end());
-        for (auto& pc : L.per) {
-            EPlanCta& ct = plan.ctas[c];
-            const CtaSeg& sg = segs[c];
-            ct.vert_off = sg.vert_off;
-            ct.visit_off = sg.visit_off;
-            ct.chunk_off = cb + pc.chunk0;
-            ct.row_off = rb + pc.row0;
-            ct.nverts = sg.nverts;
-            ct.nvisit = sg.nvisit;
-            ct.nchunk = (uint16_t)pc.nchunk;
-            ct.nrows = (uint16_t)pc.nrows;
-            ct.nout = (uint16_t)(sg.nout | (pc.needzero ? 0x8000u : 0u));
-            ct.blob_q0 = qb + pc.q0;
-            ct.blob_nq = (uint16_t)pc.nq;
-            plan.nouts += sg.nout - 1 - sg.npad;
-            ++c;
+        auto copy = [&](int t) {
+            Local& L = locals[t];
+            for (size_t k = 0; k < L.chunks.size(); ++k) {
+                EPlanChunk h = L.chunks[k];
+                h.q0 += (uint32_t)qb[t];
+                plan.chunks[cb[t] + k] = h;
+            }
+            if (!L.rows.empty()) std::memcpy(plan.rows.data() + rb[t], L.rows.data(), L.rows.size() * sizeof(EPlanRow));
+            if (!L.blob.empty()) std::memcpy(plan.blob.data() + qb[t] * 4, L.blob.data(), L.blob.size() * sizeof(uint32_t));
+            int64_t c = nCta * t / nthreads;
+            for (auto& pc : L.per) {
+                EPlanCta& ct = plan.ctas[c];
+                const CtaSeg& sg = segs[c];
+                ct.vert_off = sg.vert_off;
+                ct.visit_off = sg.visit_off;
+                ct.chunk_off = (uint32_t)cb[t] + pc.chunk0;
+                ct.row_off = (uint32_t)rb[t] + pc.row0;
+                ct.nverts = sg.nverts;
+                ct.nvisit = sg.nvisit;
+                ct.nchunk = (uint16_t)pc.nchunk;
+                ct.nrows = (uint16_t)pc.nrows;
+                ct.nout = (uint16_t)(sg.nout | (pc.needzero ? 0x8000u : 0u));
+                ct.blob_q0 = (uint32_t)qb[t] + pc.q0;
+                ct.blob_nq = (uint16_t)pc.nq;
+                ++c;
+            }
+        };
+        std::vector<std::thread> th;
+        for (int t = 1; t < nthreads; ++t) th.emplace_back(copy, t);
+        copy(0);
+        for (auto& x : th) x.join();
+        for (int64_t c = 0; c < nCta; ++c) plan.nouts += segs[c].nout - 1 - segs[c].npad;
+        for (auto& L : locals) {
+            plan.ntasks += L.ntasks;
+            plan.niters += L.niters;
+            plan.niters_padded += L.niters_padded;
+            plan.lds_wavefronts += L.wf;
+            plan.lds_ideal += L.wf_ideal;
+            plan.a1_passes += L.a1;
+            plan.a1_passes_before += L.a1_before;
+            L = Local();
         }
-        plan.ntasks += L.ntasks;
-        plan.niters += L.niters;
-        plan.niters_padded += L.niters_padded;
-        plan.lds_wavefronts += L.wf;
-        plan.lds_ideal += L.wf_ideal;
-        plan.a1_passes += L.a1;
-        plan.a1_passes_before += L.a1_before;
-        L = Local();
     }
-    plan.blob.resize(plan.blob.size() + 64, 0u);
     plan.nvisits = (int64_t)plan.visits.size() / vstride;
     lap("concatenate");
     return true;

@@ -296,24 +296,14 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
         return FEELGPU_ERR_CUDA;
     }
     int rc = feelgpu_launch_build_pos(pat, d_ja, ctx->stream);
+    // 32-bit copy of the columns for feelgpu_form2_zero_rows / matvec / the exchange, narrowed on the device
+    if (rc == FEELGPU_OK) rc = feelgpu_launch_narrow_columns(pat, d_ja, ctx->stream);
     cudaFree(d_ja); // the 64-bit column array is only needed to build the maps
     d_ja = nullptr;
-    {   // 32-bit copy of the columns for feelgpu_form2_zero_rows
-        bool fits = true;
-        std::vector<int32_t> ja32((size_t)pat->nnz);
-        for (int64_t k = 0; k < pat->nnz; ++k) {
-            if (ja[k] < 0 || ja[k] >= ((int64_t)1 << 31)) { fits = false; break; }
-            ja32[k] = (int32_t)ja[k];
-        }
-        if (fits && rc == FEELGPU_OK) {
-            err = cudaMalloc(&pat->d_ja32, sizeof(int32_t) * std::max<int64_t>(pat->nnz, 1));
-            if (err == cudaSuccess) err = cudaMemcpy(pat->d_ja32, ja32.data(), sizeof(int32_t) * pat->nnz, cudaMemcpyHostToDevice);
-            if (err != cudaSuccess) {
-                ctx->last_error = std::string("pattern_create: ") + cudaGetErrorString(err);
-                feelgpu_pattern_destroy(pat);
-                return FEELGPU_ERR_CUDA;
-            }
-        }
+    if (rc != FEELGPU_OK) {
+        feelgpu_pattern_destroy(pat);
+        pat = nullptr;
+        return rc;
     }
     // (the background build of the entity plan starts first: it overlaps the row-thread plan's build)
     if (rc == FEELGPU_OK && (flags & FEELGPU_PATTERN_EPLAN)) rc = feelgpu_eplan_build(pat, ia, async && (flags & FEELGPU_PATTERN_RPLAN));
@@ -735,6 +725,14 @@ int feelgpu_memcpy_h2d(feelgpu_context_t ctx, void* dst, const void* src, int64_
     if (!ctx) return FEELGPU_ERR_ARG;
     CTX_CUDA(ctx, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream));
     CTX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return FEELGPU_OK;
+}
+int feelgpu_memset_zero(feelgpu_context_t ctx, void* dptr, int64_t bytes, void* stream)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!dptr || bytes < 0) ARG_FAIL(ctx, "memset_zero: null pointer or negative size");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    CTX_CUDA(ctx, cudaMemsetAsync(dptr, 0, (size_t)bytes, stream ? (cudaStream_t)stream : ctx->stream));
     return FEELGPU_OK;
 }
 int feelgpu_memcpy_d2h(feelgpu_context_t ctx, void* dst, const void* src, int64_t bytes)

@@ -110,6 +110,7 @@ struct FormParams {
 
 // ---- kernel launchers (kernels_scatter.cu) ----
 int feelgpu_launch_build_pos(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s);
+int feelgpu_launch_narrow_columns(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s);
 int feelgpu_launch_form2_scatter(feelgpu_pattern_t pat, const FormParams& hp, const feelgpu_form2_desc* desc,
                                  double* a, cudaStream_t s);
 int feelgpu_launch_form1(feelgpu_space_t sp, const FormParams& hp, const feelgpu_form1_desc* desc, double* b,

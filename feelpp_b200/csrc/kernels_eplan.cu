@@ -12,6 +12,7 @@
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <memory>
 #include <cstdlib>
 #include <cstring>
 #include <thread>
@@ -563,7 +564,7 @@ struct EPlanAsync {
     std::thread th;
     std::atomic<int> state{0};       // 0 building, 1 built, 2 the mesh does not fit the plan (hp.error)
     EPlanHost hp;
-    std::vector<uint16_t> pos;
+    std::unique_ptr<uint16_t[]> pos;  // host copy of the position map, fetched by the builder's own thread
     double seconds = 0;
 };
 
@@ -611,24 +612,31 @@ int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, bool async)
     const int n = sp->n;
     (void)h_ia;                                       // (the pattern keeps its own copy: pat->h_ia)
     EPlanAsync* job = new EPlanAsync;
-    job->pos.resize((size_t)m->nElt * n * n);
-    cudaError_t err = cudaMemcpy(job->pos.data(), pat->d_pos, job->pos.size() * sizeof(uint16_t), cudaMemcpyDeviceToHost);
-    if (err != cudaSuccess) {
-        delete job;
-        ctx->last_error = std::string("entity plan: ") + cudaGetErrorString(err);
-        return FEELGPU_ERR_CUDA;
-    }
     if (sp->nDofOwned < pat->nRows) job->hp.nomerge_from = pat->h_ia[sp->nDofOwned];
-    auto work = [pat, sp, m, job] {
+    const int device = ctx->device;
+    auto work = [pat, sp, m, job, n, device] {
         const auto t0 = std::chrono::steady_clock::now();
         bool ok = false;
         try {
-            ok = eplan_build_host(sp->order, sp->ncomp, EPLAN_OMAX, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(),
-                                  m->h_conn.data(), pat->nRows, pat->h_ia.data(), job->pos.data(), 0, job->hp);
+            // the position map (2 bytes per local matrix entry, 1.6 GB on 8 M P2 elements) comes to the host on the builder's
+            // thread and its own stream: with FEELGPU_PATTERN_ASYNC neither the copy nor the page faults of the buffer hold
+            // up pattern_create
+            const size_t npos = (size_t)m->nElt * n * n;
+            job->pos.reset(new uint16_t[std::max<size_t>(npos, 1)]);
+            cudaStream_t cs = nullptr;
+            cudaError_t err = cudaSetDevice(device);
+            if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking);
+            if (err == cudaSuccess) err = cudaMemcpyAsync(job->pos.get(), pat->d_pos, npos * sizeof(uint16_t), cudaMemcpyDeviceToHost, cs);
+            if (err == cudaSuccess) err = cudaStreamSynchronize(cs);
+            if (cs) cudaStreamDestroy(cs);
+            if (err != cudaSuccess) job->hp.error = std::string("entity plan: position map to the host: ") + cudaGetErrorString(err);
+            else
+                ok = eplan_build_host(sp->order, sp->ncomp, EPLAN_OMAX, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(),
+                                      m->h_conn.data(), pat->nRows, pat->h_ia.data(), job->pos.get(), 0, job->hp);
         } catch (const std::exception& e) {
             job->hp.error = std::string("entity plan: ") + e.what();
         }
-        std::vector<uint16_t>().swap(job->pos);
+        job->pos.reset();
         job->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         job->state.store(ok ? 1 : 2, std::memory_order_release);
     };

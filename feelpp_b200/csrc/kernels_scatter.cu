@@ -349,6 +349,41 @@ extern "C" int feelgpu_scatter_add(feelgpu_context_t ctx, int64_t n, const int64
     return FEELGPU_OK;
 }
 
+// 32-bit copy of the column ids (matvec, zero_rows, the exchange's slot search), narrowed on the device from the 64-bit array
+// that is there anyway for the position map; flag = 1 when an id does not fit
+__global__ void k_narrow_columns(int64_t nnz, const int64_t* __restrict__ ja, int32_t* __restrict__ ja32, int* __restrict__ flag)
+{
+    bool bad = false;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < nnz; k += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t c = ja[k];
+        bad |= c < 0 || c >= ((int64_t)1 << 31);
+        ja32[k] = (int32_t)c;
+    }
+    if (bad) atomicOr(flag, 1);
+}
+
+// leaves pat->d_ja32 null (not an error) when the ids do not fit 32 bits
+int feelgpu_launch_narrow_columns(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s)
+{
+    feelgpu_context_t ctx = pat->ctx;
+    FEELGPU_CHECK_CUDA(ctx, cudaMalloc(&pat->d_ja32, sizeof(int32_t) * std::max<int64_t>(pat->nnz, 1)));
+    FEELGPU_CHECK_CUDA(ctx, cudaMemsetAsync(ctx->d_flag, 0, sizeof(int), s));
+    if (pat->nnz > 0) {
+        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((pat->nnz + 255) / 256, (int64_t)ctx->sm_count * 16));
+        k_narrow_columns<<<grid, 256, 0, s>>>(pat->nnz, d_ja, pat->d_ja32, ctx->d_flag);
+        ctx->launches++;
+        FEELGPU_CHECK_CUDA(ctx, cudaGetLastError());
+    }
+    int flag = 0;
+    FEELGPU_CHECK_CUDA(ctx, cudaMemcpyAsync(&flag, ctx->d_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    FEELGPU_CHECK_CUDA(ctx, cudaStreamSynchronize(s));
+    if (flag) {
+        cudaFree(pat->d_ja32);
+        pat->d_ja32 = nullptr;
+    }
+    return FEELGPU_OK;
+}
+
 int feelgpu_launch_build_pos(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s)
 {
     feelgpu_context_t ctx = pat->ctx;

@@ -71,25 +71,53 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
     maxrows = std::min(maxrows, 32767);
     const int64_t nNode = nRows / ncomp;
     // ---- node -> (element, local dof) adjacency ----
+    // (every thread owns a range of nodes and streams over the whole element -> dof table for it: no atomics, the units of a
+    // node stay in element order, and the sequential re-reads cost less than the scattered increments they spread out)
     std::vector<int64_t> nptr((size_t)nNode + 1, 0);
-    for (int64_t e = 0; e < nElt; ++e)
-        for (int i = 0; i < n; ++i) {
-            const int64_t node = l2g[e * nd + i] / ncomp;
-            if (node < nNode) ++nptr[(size_t)node + 1];
-        }
+    const int nadj = (nthreads > 1 && nElt >= 65536) ? nthreads : 1;
+    auto node_range = [&](int t, int64_t& lo, int64_t& hi) { lo = nNode * t / nadj; hi = nNode * (t + 1) / nadj; };
+    auto for_ranges = [&](auto body) {
+        if (nadj == 1) { body(0); return; }
+        std::vector<std::thread> th;
+        for (int t = 1; t < nadj; ++t) th.emplace_back(body, t);
+        body(0);
+        for (auto& x : th) x.join();
+    };
+    for_ranges([&](int t) {
+        int64_t lo, hi;
+        node_range(t, lo, hi);
+        int64_t* cnt = nptr.data() + 1;
+        // (the division by the component count is kept out of the loop: 1 and 3 are the cases that occur)
+        auto count = [&](auto nodeof) {
+            for (int64_t e = 0; e < nElt; ++e)
+                for (int i = 0; i < n; ++i) { const int64_t node = nodeof(l2g[e * nd + i]); if (node >= lo && node < hi) ++cnt[node]; }
+        };
+        if (ncomp == 1) count([](int32_t d) { return (int64_t)d; });
+        else if (ncomp == 3) count([](int32_t d) { return (int64_t)(d / 3); });
+        else count([ncomp](int32_t d) { return (int64_t)(d / ncomp); });
+    });
     for (int64_t k = 0; k < nNode; ++k) nptr[(size_t)k + 1] += nptr[(size_t)k];
     std::vector<int32_t> uelt((size_t)nptr[(size_t)nNode]);
     std::vector<uint8_t> uloc((size_t)nptr[(size_t)nNode]);
     {
         std::vector<int64_t> cur(nptr.begin(), nptr.end() - 1);
-        for (int64_t e = 0; e < nElt; ++e)
-            for (int i = 0; i < n; ++i) {
-                const int64_t node = l2g[e * nd + i] / ncomp;
-                if (node >= nNode) continue;
-                const int64_t q = cur[(size_t)node]++;
-                uelt[(size_t)q] = (int32_t)e;
-                uloc[(size_t)q] = (uint8_t)i;
-            }
+        for_ranges([&](int t) {
+            int64_t lo, hi;
+            node_range(t, lo, hi);
+            auto fill = [&](auto nodeof) {
+                for (int64_t e = 0; e < nElt; ++e)
+                    for (int i = 0; i < n; ++i) {
+                        const int64_t node = nodeof(l2g[e * nd + i]);
+                        if (node < lo || node >= hi) continue;
+                        const int64_t q = cur[(size_t)node]++;
+                        uelt[(size_t)q] = (int32_t)e;
+                        uloc[(size_t)q] = (uint8_t)i;
+                    }
+            };
+            if (ncomp == 1) fill([](int32_t d) { return (int64_t)d; });
+            else if (ncomp == 3) fill([](int32_t d) { return (int64_t)(d / 3); });
+            else fill([ncomp](int32_t d) { return (int64_t)(d / ncomp); });
+        });
     }
     lap("adjacency");
     // ---- curve order of the nodes (position = centroid of the node's entity in its first element) ----
@@ -146,43 +174,70 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
     }
     lap("sort");
     // ---- greedy cut into patches ----
+    // The curve is cut into pieces of CUT_PIECE rows that are handled independently (a piece ends with a patch that may be
+    // short, 1 in ~300); the pieces depend on the mesh only, so the plan does not depend on the thread count.
     struct Cut { int64_t k0, k1; uint32_t nvisit, nslots, nunits; };
     std::vector<Cut> cuts;
     {
-        std::vector<int32_t> stamp((size_t)nElt, -1);
-        int64_t k0 = 0;
-        uint32_t nvis = 0, nslots = 0, nun = 0;
-        int nrw = 0;
-        for (int64_t k = 0; k < nNode; ++k) {
-            const int64_t node = (int64_t)(key[(size_t)k] & 0xFFFFFFFFu);
-            const int64_t len = ia[node * ncomp + 1] - ia[node * ncomp];
-            const int64_t need = len * ncomp;
-            const int64_t u0 = nptr[(size_t)node], u1 = nptr[(size_t)node + 1];
-            if (need > maxslots || u1 - u0 > maxvisits) {
-                plan.error = "row-thread plan: one node row does not fit a patch";
-                return false;
-            }
-            for (int pass = 0; pass < 2; ++pass) {
-                const int32_t id = (int32_t)cuts.size();
-                uint32_t fresh = 0;
-                for (int64_t q = u0; q < u1; ++q)
-                    if (stamp[(size_t)uelt[(size_t)q]] != id) ++fresh;
-                if (pass == 0 && k > k0 && (nslots + need > (uint32_t)maxslots || nvis + fresh > (uint32_t)maxvisits || nrw + 1 > maxrows)) {
-                    cuts.push_back(Cut{k0, k, nvis, nslots, nun});
-                    k0 = k;
-                    nvis = nslots = nun = 0;
-                    nrw = 0;
-                    continue;        // recount against the new patch
+        constexpr int64_t CUT_PIECE = 1 << 16;
+        const int64_t npiece = std::max<int64_t>(1, (nNode + CUT_PIECE - 1) / CUT_PIECE);
+        std::vector<std::vector<Cut>> pcuts((size_t)npiece);
+        std::vector<int> perr((size_t)npiece, 0);
+        int64_t next_piece = 0;
+        auto cutter = [&]() {
+            std::vector<int32_t> stamp;
+            int32_t idnext = 0;                    // stamps are unique inside this thread's array
+            for (;;) {
+                const int64_t pi = __atomic_fetch_add(&next_piece, (int64_t)1, __ATOMIC_RELAXED);
+                if (pi >= npiece) break;
+                if (stamp.empty()) stamp.assign((size_t)nElt, -1);
+                std::vector<Cut>& lc = pcuts[(size_t)pi];
+                const int32_t idbase = idnext;
+                const int64_t kbeg = pi * CUT_PIECE, kend = std::min(nNode, (pi + 1) * CUT_PIECE);
+                int64_t k0 = kbeg;
+                uint32_t nvis = 0, nslots = 0, nun = 0;
+                int nrw = 0;
+                for (int64_t k = kbeg; k < kend; ++k) {
+                    const int64_t node = (int64_t)(key[(size_t)k] & 0xFFFFFFFFu);
+                    const int64_t len = ia[node * ncomp + 1] - ia[node * ncomp];
+                    const int64_t need = len * ncomp;
+                    const int64_t u0 = nptr[(size_t)node], u1 = nptr[(size_t)node + 1];
+                    if (need > maxslots || u1 - u0 > maxvisits) { perr[(size_t)pi] = 1; return; }
+                    for (int pass = 0; pass < 2; ++pass) {
+                        const int32_t id = idbase + (int32_t)lc.size();
+                        uint32_t fresh = 0;
+                        for (int64_t q = u0; q < u1; ++q)
+                            if (stamp[(size_t)uelt[(size_t)q]] != id) ++fresh;
+                        if (pass == 0 && k > k0 && (nslots + need > (uint32_t)maxslots || nvis + fresh > (uint32_t)maxvisits || nrw + 1 > maxrows)) {
+                            lc.push_back(Cut{k0, k, nvis, nslots, nun});
+                            k0 = k;
+                            nvis = nslots = nun = 0;
+                            nrw = 0;
+                            continue;        // recount against the new patch
+                        }
+                        for (int64_t q = u0; q < u1; ++q) stamp[(size_t)uelt[(size_t)q]] = id;
+                        nvis += fresh;
+                        nslots += (uint32_t)need;
+                        nun += (uint32_t)(u1 - u0);
+                        ++nrw;
+                        break;
+                    }
                 }
-                for (int64_t q = u0; q < u1; ++q) stamp[(size_t)uelt[(size_t)q]] = id;
-                nvis += fresh;
-                nslots += (uint32_t)need;
-                nun += (uint32_t)(u1 - u0);
-                ++nrw;
-                break;
+                if (kend > k0) lc.push_back(Cut{k0, kend, nvis, nslots, nun});
+                idnext = idbase + (int32_t)lc.size() + 1;
             }
+        };
+        {
+            const int ncut = (int)std::max<int64_t>(1, std::min<int64_t>(std::min(nthreads, 16), npiece));
+            std::vector<std::thread> th;
+            for (int t = 1; t < ncut; ++t) th.emplace_back(cutter);
+            cutter();
+            for (auto& x : th) x.join();
         }
-        if (nNode > k0) cuts.push_back(Cut{k0, nNode, nvis, nslots, nun});
+        for (int64_t pi = 0; pi < npiece; ++pi) {
+            if (perr[(size_t)pi]) { plan.error = "row-thread plan: one node row does not fit a patch"; return false; }
+            cuts.insert(cuts.end(), pcuts[(size_t)pi].begin(), pcuts[(size_t)pi].end());
+        }
     }
     lap("cut");
     // ---- emit ----

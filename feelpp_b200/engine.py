@@ -192,9 +192,8 @@ class BilinearForm:
     def assign(self, integ):
         """a = integrate(...): zero, then assemble (feelvf/bilinearform.hpp:1368-1371)."""
         if integ is None:
-            z = np.zeros(max(self.nnz, 1))
-            check(self.eng.lib.feelgpu_memcpy_h2d(self.eng.ctx, self.d_values, z.ctypes.data_as(C.c_void_p), z.nbytes),
-                  self.eng.ctx)
+            check(self.eng.lib.feelgpu_memset_zero(self.eng.ctx, self.d_values, 8 * max(self.nnz, 1), None), self.eng.ctx)
+            self.eng.sync()
             return self
         return self._assemble(integ, 0)
 

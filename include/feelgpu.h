@@ -276,6 +276,8 @@ int feelgpu_scatter_add(feelgpu_context_t ctx, int64_t n, const int64_t* slots, 
 int feelgpu_malloc(feelgpu_context_t ctx, int64_t bytes, void** dptr);
 int feelgpu_free(feelgpu_context_t ctx, void* dptr);
 int feelgpu_memcpy_h2d(feelgpu_context_t ctx, void* dst, const void* src, int64_t bytes);
+/* zero a device array, asynchronously on `stream` (MatrixPetsc::zero -> MatZeroEntries, feelalg/matrixpetsc.cpp:616-626) */
+int feelgpu_memset_zero(feelgpu_context_t ctx, void* dptr, int64_t bytes, void* stream);
 int feelgpu_memcpy_d2h(feelgpu_context_t ctx, void* dst, const void* src, int64_t bytes);
 int feelgpu_host_alloc_pinned(feelgpu_context_t ctx, int64_t bytes, void** hptr);
 int feelgpu_host_free_pinned(feelgpu_context_t ctx, void* hptr);

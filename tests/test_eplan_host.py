@@ -190,3 +190,21 @@ def test_plan_limits_split_ctas():
     assert (P["chunks"]["type"] != 5).all()
     assert (P["ctas"]["nvisit"] < P["vs"]).all() and (P["ctas"]["nverts"] <= 256).all()
     assert ((P["ctas"]["nout"] & 0x7FFF) <= P["omax"]).all() and (P["ctas"]["nrows"] <= 384).all()
+
+
+def test_plan_packed_in_pieces_matches_oracle():
+    """more than 65 536 nodes: the curve is cut into pieces that are packed into CTAs independently (by several threads);
+    the plan interpreted on the host still gives the oracle matrix and writes every CSR value once"""
+    mesh = fpp.unitCube(22, 0.15, True)
+    Xh = fpp.Pch(mesh, 2)
+    assert Xh.nDof() > 65536
+    ia, ja = Xh.graph()
+    P = build_plan(mesh, Xh, ia, ja)
+    nnz = int(ia[-1])
+    quad = orc.quad_order_form2(orc.STIFFNESS, 2)
+    coef, mass = coefficients(2, quad, 1)
+    a = interpret(P, mesh, 2, nnz, 1, coef, mass)
+    ref = orc.form2(orc.STIFFNESS, 2, 1, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+    scale = orc.form2(orc.STIFFNESS | orc.ABS_FLAG, 2, 1, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
+    parity.check(a, ref, scale, ia, ja, "eplan host, packed in pieces")
+    assert P["stats"]["outputs"] == nnz

@@ -122,3 +122,43 @@ def test_a_row_that_does_not_fit_is_refused():
     ia, ja = Xh.graph()
     with pytest.raises(RuntimeError):
         build(Xh, ia, 8, 400)
+
+
+def test_plan_cut_in_pieces_is_complete():
+    """more than 65 536 nodes: the curve is cut into pieces whose patches are formed independently (by several threads).
+    Structure of the whole plan, vectorised: every (element, local dof) unit once and in the row of its node, every node in
+    one patch, row segments tile the row block, visits of a patch distinct, limits respected."""
+    mesh = fpp.unitCube(22, 0.15, True)
+    Xh = fpp.FunctionSpace(mesh, 2, 1)
+    ia, ja = Xh.graph()
+    nNode, n, nElt = Xh.nDof(), Xh.n, mesh.numElements()
+    assert nNode > 65536
+    maxslots, maxvisits = 12288, 384
+    patches, visits, rows, units, sizes = build(Xh, ia, maxslots, maxvisits)
+    assert (patches["nslots"] <= maxslots).all() and (patches["nvisit"] <= maxvisits).all()
+    assert int(patches["nunits"].sum()) == len(units) == nElt * n and int(patches["nrows"].sum()) == len(rows) == nNode
+    assert int(patches["nvisit"].sum()) == len(visits)
+    # offsets are the running sums
+    for off, cnt in (("visit_off", "nvisit"), ("row_off", "nrows"), ("unit_off", "nunits")):
+        assert np.array_equal(patches[off].astype(np.int64), np.cumsum(patches[cnt].astype(np.int64)) - patches[cnt])
+    pid_u = np.repeat(np.arange(len(patches)), patches["nunits"].astype(np.int64))
+    pid_r = np.repeat(np.arange(len(patches)), patches["nrows"].astype(np.int64))
+    pid_v = np.repeat(np.arange(len(patches)), patches["nvisit"].astype(np.int64))
+    v, i, r = (units & 0xFFF).astype(np.int64), ((units >> 12) & 31).astype(np.int64), (units >> 17).astype(np.int64)
+    assert (v < patches["nvisit"][pid_u]).all() and (r < patches["nrows"][pid_u]).all() and (i < n).all()
+    e = visits[patches["visit_off"].astype(np.int64)[pid_u] + v].astype(np.int64)
+    assert len(np.unique(e * 32 + i)) == nElt * n, "a unit occurs twice"
+    row_node = np.searchsorted(ia, rows["base"])
+    assert np.array_equal(ia[row_node], rows["base"]) and len(np.unique(row_node)) == nNode
+    assert np.array_equal(rows["len"].astype(np.int64), ia[row_node + 1] - ia[row_node])
+    grow = patches["row_off"].astype(np.int64)[pid_u] + r
+    assert np.array_equal(Xh.l2g[e, i].astype(np.int64), row_node[grow]), "a unit sits in the row of another node"
+    assert np.array_equal(np.bincount(grow, minlength=len(rows)), rows["nunits"].astype(np.int64))
+    # row segments tile the row block of their patch in row order
+    ln = rows["len"].astype(np.int64)
+    excl = np.cumsum(ln) - ln
+    first = patches["row_off"].astype(np.int64)[pid_r]
+    assert np.array_equal(rows["off"].astype(np.int64), excl - excl[first])
+    last = patches["row_off"].astype(np.int64) + patches["nrows"].astype(np.int64) - 1
+    assert np.array_equal(patches["nslots"].astype(np.int64), rows["off"].astype(np.int64)[last] + ln[last])
+    assert len(np.unique(pid_v * nElt + visits.astype(np.int64))) == len(visits), "an element is visited twice by a patch"
