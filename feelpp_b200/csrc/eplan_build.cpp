@@ -646,6 +646,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
         std::vector<uint32_t> usage, sorted, perm, vtmp;
         std::vector<int32_t> cnodes;
         std::vector<uint32_t> cell[256];      // tasks with <= 2 elements by (bank pair of element 0, of element 1)
+        uint32_t csz[256];                    // their sizes, both orientations (csz[a * 16 + b] == csz[b * 16 + a])
         std::vector<uint32_t> cell1[16];
         int cnt2[32];
         std::vector<uint32_t> pool, lanes;    // remaining tasks of a type; tasks of every chunk lane
@@ -907,12 +908,15 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                     size_t rem2 = 0, rem1 = 0;
                     uint16_t ne[16];      // ne[a] bit b: the cell of bank pairs {a, b} holds tasks (the scan below skips the rest)
                     for (int z = 0; z < 16; ++z) ne[z] = 0;
+                    for (int z = 0; z < 256; ++z) csz[z] = 0;
                     for (size_t k = nlong; k < tv.size(); ++k) {
                         const uint32_t* src = &iterw[tv[k].first];
                         const int r0 = src[0] & 15;
                         if (tv[k].niter == 2) {
                             const int r1 = src[1] & 15;
                             cell[std::min(r0, r1) * 16 + std::max(r0, r1)].push_back((uint32_t)k);
+                            ++csz[r0 * 16 + r1];
+                            if (r0 != r1) ++csz[r1 * 16 + r0];
                             ne[r0] |= (uint16_t)(1u << r1);
                             ne[r1] |= (uint16_t)(1u << r0);
                             ++rem2;
@@ -940,6 +944,25 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             size_t bsize = 0;
                             std::vector<uint32_t>* bcv = nullptr;
                             if (nt == 2) {
+                                // cells whose bank pairs are unused in both iterations cost nothing: the fullest of them wins
+                                // (first in (a2, b2) order among equals, as in the full scan below)
+                                uint32_t FA = 0, FB = 0, bs = 0;
+                                for (int z = 0; z < 16; ++z) { FA |= (uint32_t)(cnt2[z] == 0) << z; FB |= (uint32_t)(cnt2[16 + z] == 0) << z; }
+                                for (uint32_t ma = FA; ma; ma &= ma - 1) {
+                                    const int a2 = __builtin_ctz(ma);
+                                    const uint32_t* row = csz + a2 * 16;
+                                    for (uint32_t mb = ne[a2] & FB; mb; mb &= mb - 1) {
+                                        const int b2 = __builtin_ctz(mb);
+                                        if (row[b2] > bs) { bs = row[b2]; ba = a2; bb = b2; }
+                                    }
+                                }
+                                if (bs) {
+                                    bcost = 0;
+                                    bsize = bs;
+                                    bcv = &cell[std::min(ba, bb) * 16 + std::max(ba, bb)];
+                                }
+                            }
+                            if (nt == 2 && !bcv) {
                                 // (for a given a2 only the b2 of least count can win: the others are skipped through the masks
                                 // of the bank pairs by their count in iteration 1 -- same choice as the full scan, a third of the work)
                                 uint32_t bycnt[18];
@@ -968,7 +991,7 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                                         if (cost < bcost || (cost == bcost && sz > bsize)) { bcost = cost; bsize = sz; bcv = &cv2; ba = a2; bb = b2; }
                                     }
                                 }
-                            } else {
+                            } else if (nt == 1) {
                                 for (int a2 = 0; a2 < 16; ++a2) {
                                     const size_t sz = cell1[a2].size();
                                     if (!sz) continue;
@@ -988,6 +1011,10 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
                             const uint32_t ti = cv[bk];
                             cv[bk] = cv.back();
                             cv.pop_back();
+                            if (nt == 2) {
+                                --csz[ba * 16 + bb];
+                                if (ba != bb) --csz[bb * 16 + ba];
+                            }
                             if (nt == 2 && cv.empty()) {
                                 ne[ba] &= (uint16_t)~(1u << bb);
                                 ne[bb] &= (uint16_t)~(1u << ba);

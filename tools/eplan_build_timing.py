@@ -28,3 +28,5 @@ for k in ("ctas", "verts", "visits", "chunks", "blob", "rows"):
     h.update(P[k].tobytes())
 print("elements", mesh.numElements(), "build_s", round(t3 - t2, 3), "(position map in numpy %.2f s)" % (t1 - t0),
       "ctas", len(P["ctas"]), "digest", h.hexdigest()[:16])
+st = P["stats"]
+print("iterations padded/real %.4f  modelled S-load wavefronts / ideal %.4f  (%.0f)" % (st["iters_padded"] / st["iters"], st["wavefronts"] / st["wavefronts_ideal"], st["wavefronts"]))
