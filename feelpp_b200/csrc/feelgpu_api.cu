@@ -4,7 +4,9 @@
 #include "eplan.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <new>
 
 static std::string g_create_error;
@@ -386,6 +388,20 @@ int feelgpu_pattern_destroy(feelgpu_pattern_t pat)
     if (pat->d_ja32) cudaFree(pat->d_ja32);
     delete pat;
     return FEELGPU_OK;
+}
+
+extern "C++" int feelgpu_builder_threads(feelgpu_context_t ctx)
+{
+    if (const char* e = std::getenv("FEELGPU_BUILD_THREADS"))
+        if (std::atoi(e) > 0) return std::atoi(e);
+    const int hw = (int)std::max(1u, std::thread::hardware_concurrency());
+    int share = 1;
+    if (ctx && ctx->nranks > 1) {
+        int ndev = 1;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) ndev = 1;
+        share = std::min(ctx->nranks, ndev);
+    }
+    return std::max(1, hw / share);
 }
 
 // ---- work calls ------------------------------------------------------------------------------------------------

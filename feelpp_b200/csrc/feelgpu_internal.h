@@ -108,6 +108,9 @@ struct FormParams {
         }                                                                                               \
     } while (0)
 
+// host threads a plan builder may use: FEELGPU_BUILD_THREADS, else the hardware threads shared among the ranks that build
+// at the same time on this node (after feelgpu_comm_init: min(ranks of the communicator, devices of the node))
+int feelgpu_builder_threads(feelgpu_context_t ctx);
 // ---- kernel launchers (kernels_scatter.cu) ----
 int feelgpu_launch_build_pos(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s);
 int feelgpu_launch_narrow_columns(feelgpu_pattern_t pat, const int64_t* d_ja, cudaStream_t s);

@@ -613,8 +613,8 @@ int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, bool async)
     (void)h_ia;                                       // (the pattern keeps its own copy: pat->h_ia)
     EPlanAsync* job = new EPlanAsync;
     if (sp->nDofOwned < pat->nRows) job->hp.nomerge_from = pat->h_ia[sp->nDofOwned];
-    const int device = ctx->device;
-    auto work = [pat, sp, m, job, n, device] {
+    const int device = ctx->device, nthreads = feelgpu_builder_threads(ctx);
+    auto work = [pat, sp, m, job, n, device, nthreads] {
         const auto t0 = std::chrono::steady_clock::now();
         bool ok = false;
         try {
@@ -632,7 +632,7 @@ int feelgpu_eplan_build(feelgpu_pattern_t pat, const int64_t* h_ia, bool async)
             if (err != cudaSuccess) job->hp.error = std::string("entity plan: position map to the host: ") + cudaGetErrorString(err);
             else
                 ok = eplan_build_host(sp->order, sp->ncomp, EPLAN_OMAX, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(),
-                                      m->h_conn.data(), pat->nRows, pat->h_ia.data(), job->pos.get(), 0, job->hp);
+                                      m->h_conn.data(), pat->nRows, pat->h_ia.data(), job->pos.get(), nthreads, job->hp);
         } catch (const std::exception& e) {
             job->hp.error = std::string("entity plan: ") + e.what();
         }

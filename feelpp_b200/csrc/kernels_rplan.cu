@@ -431,7 +431,7 @@ int feelgpu_rplan_build(feelgpu_pattern_t pat, const int64_t* h_ia)
     RPlanHost hp;
     const auto t0 = std::chrono::steady_clock::now();
     if (!rplan_build_host(sp->order, sp->ncomp, m->nElt, sp->h_l2g.data(), sp->nd, m->nPts, m->h_xyz.data(), m->h_conn.data(),
-                          pat->nRows, h_ia, maxslots, maxvis, maxrows, 0, hp)) {
+                          pat->nRows, h_ia, maxslots, maxvis, maxrows, feelgpu_builder_threads(ctx), hp)) {
         pat->rplan_note = hp.error;   // not an error: another path stays available
         return FEELGPU_OK;
     }
