@@ -169,6 +169,20 @@ def bytes_per_element(args, npts, nelt, nnz):
     return be
 
 
+def fp64_instr_per_element(args):
+    """DFMA-class instructions per element of the row-thread kernel for the forms it serves (a count of the kernel's own
+    arithmetic): these forms are bound by the FP64 pipe, not by HBM.  None for the entity-plan forms."""
+    n = (args.order + 1) * (args.order + 2) * (args.order + 3) // 6
+    nq = {1: 1, 2: 4, 3: 5, 4: 11, 5: 14, 6: 24}.get(quad_order(args))
+    if nq is None:
+        return None
+    if args.form == "kstiffness":
+        return n * (3 * n * nq + 12 * nq)          # per row: s = w J k G grad(phi_i) (12 per point), then 3 DFMA per (column, point)
+    if args.form == "elasticity" or args.ncomp == 3 and args.form not in ("stiffness",):
+        return n * (9 * nq + n * (18 * nq + 21))   # per row: gradients (9 per point); per column 18 per point + the 3x3 combination
+    return None
+
+
 def workload(args, want_graph=True, eng=None):
     """builds the host-side objects (untimed setup); with an engine the COUPLED graph is built on the device
     (feelgpu_graph_create, bit-exact with the host graph: tests/test_gpu_parity.py)"""
@@ -180,13 +194,15 @@ def workload(args, want_graph=True, eng=None):
     if not want_graph:
         ia, ja = None, None
     elif eng is not None:
-        ia, ja = eng.graph(Xh)
-        Xh._graph = (ia, ja)      # form2() asks the space for its graph: the device one stands in (same arrays, bit for bit)
+        dg = eng.device_graph(Xh)  # kept on the device: form2() builds its pattern from it (feelgpu_pattern_create_from_graph)
+        ia, ja = dg.ia, dg.ja
     else:
         ia, ja = Xh.graph()
     t2 = time.time()
     info = {"mesh_doftable_s": round(t1 - t0, 2), "graph_s": round(t2 - t1, 2),
             "graph": "device (feelgpu_graph_create + copy to the host)" if eng is not None and want_graph else "host"}
+    if eng is not None and want_graph:
+        info["_device_graph"] = dg
     return mesh, Xh, ia, ja, info
 
 
@@ -354,8 +370,10 @@ def gpu_arm(args):
         t0 = time.time()
         # FEELGPU_PATTERN_ASYNC: pattern_create returns once the row-thread plan stands (assembly can start); the entity plan
         # of P1/P2 spaces is built by a background thread and takes over when it is ready.  The timed steps wait for it.
-        a = fpp.form2(_test=Xh, _trial=Xh, engine=eng, algorithm=algo,
+        dg = info.pop("_device_graph")
+        a = fpp.form2(_test=Xh, _trial=Xh, engine=eng, algorithm=algo, device_graph=dg,
                       pattern_flags={"rowplan": 3, "scatter": 1, "rplan": 9}.get(args.algo, fpp.PATTERN_ASYNC))
+        dg.destroy()
         info["pattern_create_s"] = round(time.time() - t0, 2)
         _, eplan_s = a.plans_ready(wait=True)
         info["plans_ready_s"] = round(time.time() - t0, 2)
@@ -530,6 +548,16 @@ def gpu_arm(args):
                 "kernel_ms": kms, "zero_fill_ms": zms, "algorithmic_bytes_per_element": Be,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                 "step_frac_vs_peak": Be * nElt_total / world / (ms / args.steps * 1e-3) / 1e9 / peak}
+        fi = fp64_instr_per_element(args)
+        if fi and args.algo in ("auto", "rplan"):
+            # informational: the pipe that bounds this kernel (ncu: DRAM at 5 %, profiles/r2_rplan_summary.md)
+            mhz = (clocks or {}).get("sm_max_mhz") or 1965.0
+            sms = torch.cuda.get_device_properties(local).multi_processor_count
+            pk = sms * 64 * 2 * mhz * 1e6 / 1e12
+            ach = 2.0 * fi * nElt / (kms * 1e-3) / 1e12
+            roof["fp64"] = {"achieved": ach, "peak": pk, "unit": "TFLOP/s", "frac": ach / pk,
+                            "instructions_per_element": fi,
+                            "peak_source": "%d SMs x 64 DFMA/clk x 2 x %.0f MHz (nominal pipe rate, not measured)" % (sms, mhz)}
         cpu = None
         # host setup until the steady-state plans stand: mesh + DofTable, graph [partition, local problem], pattern + plans
         setup_s = sum(info.get(k, 0.0) for k in ("mesh_doftable_s", "graph_s", "mesh_partition_s", "local_problem_s")) + \

@@ -88,6 +88,7 @@ GPU_SYMBOLS = {
     "feelgpu_graph_create": [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)],
     "feelgpu_graph_get": [C.c_void_p, c_i64p, c_i64p],
     "feelgpu_graph_destroy": [C.c_void_p],
+    "feelgpu_pattern_create_from_graph": [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)],
     "feelgpu_matvec": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "feelgpu_faces_create": [C.c_void_p, C.c_int64, c_i32p, c_i32p, C.POINTER(C.c_void_p)],
     "feelgpu_faces_destroy": [C.c_void_p],

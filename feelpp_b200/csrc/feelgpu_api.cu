@@ -254,11 +254,12 @@ int feelgpu_space_destroy(feelgpu_space_t sp)
 }
 
 // ---- pattern ---------------------------------------------------------------------------------------------------
-int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_space_t trial, int64_t nRows,
-                           const int64_t* ia, const int64_t* ja, int flags, feelgpu_pattern_t* out)
+// ja: host columns, or null when the columns are already on the device (d_ja_graph, owned by a feelgpu_graph_t)
+static int pattern_create_impl(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_space_t trial, int64_t nRows,
+                               const int64_t* ia, const int64_t* ja, const int64_t* d_ja_graph, int flags, feelgpu_pattern_t* out)
 {
     if (!ctx) return FEELGPU_ERR_ARG;
-    if (!test || !trial || !ia || !ja || !out || nRows < 0) ARG_FAIL(ctx, "pattern_create: bad argument");
+    if (!test || !trial || !ia || (!ja && !d_ja_graph) || !out || nRows < 0) ARG_FAIL(ctx, "pattern_create: bad argument");
     if (test->mesh != trial->mesh) ARG_FAIL(ctx, "pattern_create: test and trial spaces live on different meshes");
     if (test->n != trial->n || test->ncomp != trial->ncomp) {
         ctx->last_error = "pattern_create: test and trial spaces must have the same order and components";
@@ -283,13 +284,28 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     pat->nnz = ia[nRows];
     pat->h_ia_owned_end = ia[std::min<int64_t>(test->nDofOwned, nRows)];
     pat->h_ia.assign(ia, ia + nRows + 1);
-    if (test->nDofOwned < nRows) pat->h_ja_tail.assign(ja + pat->h_ia_owned_end, ja + ia[nRows]);
+    if (test->nDofOwned < nRows) {
+        if (ja) pat->h_ja_tail.assign(ja + pat->h_ia_owned_end, ja + ia[nRows]);
+        else {
+            pat->h_ja_tail.resize((size_t)(ia[nRows] - pat->h_ia_owned_end));
+            if (cudaMemcpy(pat->h_ja_tail.data(), d_ja_graph + pat->h_ia_owned_end, sizeof(int64_t) * pat->h_ja_tail.size(),
+                           cudaMemcpyDeviceToHost) != cudaSuccess) {
+                ctx->last_error = "pattern_create: copy of the ghost rows' columns failed";
+                feelgpu_pattern_destroy(pat);
+                pat = nullptr;
+                return FEELGPU_ERR_CUDA;
+            }
+        }
+    }
     const int n = test->n;
     const int64_t nElt = test->mesh->nElt;
     cudaError_t err = cudaMalloc(&pat->d_ia, sizeof(int64_t) * (nRows + 1));
     if (err == cudaSuccess) err = cudaMemcpy(pat->d_ia, ia, sizeof(int64_t) * (nRows + 1), cudaMemcpyHostToDevice);
-    if (err == cudaSuccess) err = cudaMalloc(&d_ja, sizeof(int64_t) * std::max<int64_t>(pat->nnz, 1));
-    if (err == cudaSuccess) err = cudaMemcpy(d_ja, ja, sizeof(int64_t) * pat->nnz, cudaMemcpyHostToDevice);
+    if (!d_ja_graph) {
+        if (err == cudaSuccess) err = cudaMalloc(&d_ja, sizeof(int64_t) * std::max<int64_t>(pat->nnz, 1));
+        if (err == cudaSuccess) err = cudaMemcpy(d_ja, ja, sizeof(int64_t) * pat->nnz, cudaMemcpyHostToDevice);
+    }
+    const int64_t* d_cols = d_ja_graph ? d_ja_graph : d_ja;
     if (err == cudaSuccess) err = cudaMalloc(&pat->d_pos, sizeof(uint16_t) * std::max<int64_t>(nElt * n * n, 1));
     if (err != cudaSuccess) {
         ctx->last_error = std::string("pattern_create: ") + cudaGetErrorString(err);
@@ -297,10 +313,10 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
         feelgpu_pattern_destroy(pat);
         return FEELGPU_ERR_CUDA;
     }
-    int rc = feelgpu_launch_build_pos(pat, d_ja, ctx->stream);
+    int rc = feelgpu_launch_build_pos(pat, d_cols, ctx->stream);
     // 32-bit copy of the columns for feelgpu_form2_zero_rows / matvec / the exchange, narrowed on the device
-    if (rc == FEELGPU_OK) rc = feelgpu_launch_narrow_columns(pat, d_ja, ctx->stream);
-    cudaFree(d_ja); // the 64-bit column array is only needed to build the maps
+    if (rc == FEELGPU_OK) rc = feelgpu_launch_narrow_columns(pat, d_cols, ctx->stream);
+    if (d_ja) cudaFree(d_ja); // the 64-bit column array is only needed to build the maps
     d_ja = nullptr;
     if (rc != FEELGPU_OK) {
         feelgpu_pattern_destroy(pat);
@@ -313,9 +329,20 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
     // the row plan is also the fallback of a mesh the entity plan could not take
     if (rc == FEELGPU_OK && ((flags & FEELGPU_PATTERN_ROWPLAN) ||
                              ((flags & FEELGPU_PATTERN_EPLAN) && !pat->eplan && !pat->eplan_async && !pat->rplan)))
-        rc = feelgpu_rowplan_build(pat, ia, ja);
+    {
+        std::vector<int64_t> hja;                      // (the row plan's builder reads the columns on the host)
+        if (!ja) {
+            hja.resize((size_t)std::max<int64_t>(pat->nnz, 1));
+            if (cudaMemcpy(hja.data(), d_ja_graph, sizeof(int64_t) * pat->nnz, cudaMemcpyDeviceToHost) != cudaSuccess) {
+                ctx->last_error = "pattern_create: copy of the columns to the host failed";
+                rc = FEELGPU_ERR_CUDA;
+            }
+        }
+        if (rc == FEELGPU_OK) rc = feelgpu_rowplan_build(pat, ia, ja ? ja : hja.data());
+    }
     if (rc != FEELGPU_OK) {
         feelgpu_pattern_destroy(pat);
+        pat = nullptr;
         return rc;
     }
     *out = pat;
@@ -324,6 +351,32 @@ int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_
         if (d_ja) cudaFree(d_ja);
         if (pat) feelgpu_pattern_destroy(pat);
     });
+}
+
+int feelgpu_pattern_create(feelgpu_context_t ctx, feelgpu_space_t test, feelgpu_space_t trial, int64_t nRows,
+                           const int64_t* ia, const int64_t* ja, int flags, feelgpu_pattern_t* out)
+{
+    if (!ctx) return FEELGPU_ERR_ARG;
+    if (!ja) ARG_FAIL(ctx, "pattern_create: bad argument");
+    return pattern_create_impl(ctx, test, trial, nRows, ia, ja, nullptr, flags, out);
+}
+
+// The pattern of a graph that was built on the device (feelgpu_graph_create): the columns stay where they are, only the row
+// pointers come to the host (the plan builders read them).  The graph may be destroyed afterwards.
+int feelgpu_pattern_create_from_graph(feelgpu_graph_t graph, int flags, feelgpu_pattern_t* out)
+{
+    if (!graph || !graph->space) return FEELGPU_ERR_ARG;
+    feelgpu_context_t ctx = graph->space->ctx;
+    if (!out) ARG_FAIL(ctx, "pattern_create_from_graph: bad argument");
+    CTX_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::vector<int64_t> ia;
+    int rc = abi_guard(ctx, "pattern_create_from_graph", [&]() -> int {
+        ia.resize((size_t)graph->nRows + 1);
+        CTX_CUDA(ctx, cudaMemcpy(ia.data(), graph->d_ia, sizeof(int64_t) * ia.size(), cudaMemcpyDeviceToHost));
+        return FEELGPU_OK;
+    }, [] {});
+    if (rc) return rc;
+    return pattern_create_impl(ctx, graph->space, graph->space, graph->nRows, ia.data(), nullptr, graph->d_ja, flags, out);
 }
 
 int feelgpu_pattern_nnz(feelgpu_pattern_t pat, int64_t* nnz)

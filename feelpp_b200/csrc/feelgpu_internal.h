@@ -89,6 +89,13 @@ struct feelgpu_faces_s {
     int32_t* d_lface = nullptr;  // [n] local face id 0..3
 };
 
+struct feelgpu_graph_s {         // the COUPLED graph of (space, space) on the device (kernels_graph.cu)
+    feelgpu_space_t space = nullptr;
+    int64_t nRows = 0, nnz = 0;
+    int64_t* d_ia = nullptr;   // [nRows + 1]
+    int64_t* d_ja = nullptr;   // [nnz]
+};
+
 struct FormParams {
     int kind, coeff_kind, n, nq, nf, ncomp, expr_len, pad;
     double cval[3];

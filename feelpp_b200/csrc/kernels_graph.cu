@@ -19,12 +19,7 @@
 #include <algorithm>
 #include <new>
 
-struct feelgpu_graph_s {
-    feelgpu_space_t space = nullptr;
-    int64_t nRows = 0, nnz = 0;
-    int64_t* d_ia = nullptr;   // [nRows + 1]
-    int64_t* d_ja = nullptr;   // [nnz]
-};
+// (struct feelgpu_graph_s: feelgpu_internal.h)
 
 namespace {
 

@@ -70,6 +70,11 @@ class Engine:
         self.lib.feelgpu_graph_destroy(g)
         return ia, ja
 
+    def device_graph(self, Xh):
+        """the same graph kept on the device next to its host copies: form2(..., device_graph=g) builds the pattern from it
+        without sending the columns back (feelgpu_pattern_create_from_graph); g.destroy() when the forms are built"""
+        return DeviceGraph(self, Xh)
+
     def faces(self, rng):
         """device list of the (element, local face) pairs of a face range (feelgpu_faces_create)"""
         key = builtins_id(rng)
@@ -158,18 +163,39 @@ def _fill_coeff(eng, keep, cl, c):
         c.expr_consts = keep.arr(consts.astype(np.float64), c_dblp)
 
 
+class DeviceGraph:
+    def __init__(self, eng, Xh):
+        self.eng, self.Xh = eng, Xh
+        self.g, nnz = C.c_void_p(), C.c_int64()
+        check(eng.lib.feelgpu_graph_create(eng.space(Xh), C.byref(self.g), C.byref(nnz)), eng.ctx)
+        self.ia = np.empty(Xh.nDof() + 1, dtype=np.int64)
+        self.ja = np.empty(nnz.value, dtype=np.int64)
+        check(eng.lib.feelgpu_graph_get(self.g, ptr(self.ia, c_i64p), ptr(self.ja, c_i64p)), eng.ctx)
+
+    def destroy(self):
+        if self.g:
+            self.eng.lib.feelgpu_graph_destroy(self.g)
+            self.g = C.c_void_p()
+
+
 class BilinearForm:
     """form2(_test=Xh,_trial=Xh): owns the CSR graph (host) and the device value array."""
 
-    def __init__(self, test, trial, engine, pattern_flags=0, algorithm=ALGO_AUTO):
+    def __init__(self, test, trial, engine, pattern_flags=0, algorithm=ALGO_AUTO, device_graph=None):
         if test is not trial:
             raise NotImplementedError("test and trial spaces must be the same space on this path")
         self.Xh, self.eng, self.algorithm = test, engine, algorithm
-        self.ia, self.ja = test.graph()
         self.pat = C.c_void_p()
-        sp = engine.space(test)
-        check(engine.lib.feelgpu_pattern_create(engine.ctx, sp, sp, test.nDof(), ptr(self.ia, c_i64p),
-                                                ptr(self.ja, c_i64p), pattern_flags, C.byref(self.pat)), engine.ctx)
+        if device_graph is not None:
+            if device_graph.Xh is not test:
+                raise ValueError("the device graph belongs to another space")
+            self.ia, self.ja = device_graph.ia, device_graph.ja
+            check(engine.lib.feelgpu_pattern_create_from_graph(device_graph.g, pattern_flags, C.byref(self.pat)), engine.ctx)
+        else:
+            self.ia, self.ja = test.graph()
+            sp = engine.space(test)
+            check(engine.lib.feelgpu_pattern_create(engine.ctx, sp, sp, test.nDof(), ptr(self.ia, c_i64p),
+                                                    ptr(self.ja, c_i64p), pattern_flags, C.byref(self.pat)), engine.ctx)
         self.nnz = int(self.ia[-1])
         self.d_values = self._alloc_values()
         self._zeroed = False
@@ -325,9 +351,9 @@ class LinearForm:
         return self.eng.to_host(self.d_values, max(self.Xh.nDof(), 1))[:self.Xh.nDof()]
 
 
-def form2(_test, _trial, engine, pattern_flags=0, algorithm=ALGO_AUTO):
+def form2(_test, _trial, engine, pattern_flags=0, algorithm=ALGO_AUTO, device_graph=None):
     """form2(_test=Xh,_trial=Xh) (feelvf/form.hpp:130-147): pattern COUPLED, matrix zeroed."""
-    return BilinearForm(_test, _trial, engine, pattern_flags, algorithm)
+    return BilinearForm(_test, _trial, engine, pattern_flags, algorithm, device_graph)
 
 
 def form1(_test, engine):

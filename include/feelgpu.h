@@ -209,6 +209,10 @@ int feelgpu_form2_zero_rows(feelgpu_pattern_t pattern, int64_t n, const int32_t*
 int feelgpu_graph_create(feelgpu_space_t space, feelgpu_graph_t* graph, int64_t* nnz);
 int feelgpu_graph_get(feelgpu_graph_t graph, int64_t* ia, int64_t* ja);
 int feelgpu_graph_destroy(feelgpu_graph_t graph);
+/* The pattern of such a graph without the round trip of its columns through the host (feelgpu_pattern_create with the
+ * arrays of feelgpu_graph_get gives the same pattern): test == trial == the graph's space, nRows = its dofs.  Only ia comes to
+ * the host (the plan builders read it).  The graph may be destroyed once the call returns.                              */
+int feelgpu_pattern_create_from_graph(feelgpu_graph_t graph, int flags, feelgpu_pattern_t* pattern);
 
 /* ---- device hand-off: y = A x on the assembled CSR (MatrixPetsc::multVector -> MatMult, feelalg/matrixpetsc.cpp:998-1062;
  * with it MatrixPetsc::energy :2132-2170 is a dot product).  Sequential matrices (one space, identity cluster numbering);

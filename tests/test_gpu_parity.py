@@ -264,6 +264,41 @@ def test_device_graph_bit_exact(engine, meshes, order, ncomp, mk):
     assert np.array_equal(dja, ja)
 
 
+@pytest.mark.parametrize("order,ncomp", [(1, 1), (2, 1), (3, 1), (2, 3)])
+def test_pattern_from_device_graph(engine, meshes, order, ncomp):
+    """feelgpu_pattern_create_from_graph: the pattern built from the graph that stays on the device gives the same matrix
+    (bit for bit through the entity plan, within the tolerance otherwise), Dirichlet elimination and y = A x included --
+    they read the 32-bit columns narrowed on the device"""
+    mesh = meshes["scr"]
+    Xh = fpp.FunctionSpace(mesh, order, ncomp)
+    u = v = fpp.Element(Xh)
+    dg = engine.device_graph(Xh)
+    ia, ja = Xh.graph()
+    assert np.array_equal(dg.ia, ia) and np.array_equal(dg.ja, ja)
+    a = fpp.form2(_test=Xh, _trial=Xh, engine=engine, device_graph=dg)
+    dg.destroy()                                  # the pattern does not need the graph any more
+    b = fpp.form2(_test=Xh, _trial=Xh, engine=engine)
+    if ncomp == 3:
+        form = integrate(_range=elements(mesh), _expr=inner(gradt(u), grad(v)))
+        kind = orc.STIFFNESS
+    else:
+        form = integrate(_range=elements(mesh), _expr=gradt(u) * trans(grad(v)))
+        kind = orc.STIFFNESS
+    a.assign(form)
+    b.assign(form)
+    ref, scale = oracle_form2(kind, Xh, orc.quad_order_form2(kind, order))
+    check_values(a.values(), ref, scale, "pattern from the device graph P%d x%d" % (order, ncomp))
+    if order <= 2:
+        assert np.array_equal(a.values(), b.values())
+    x = np.linspace(-1.0, 2.0, Xh.nDof())
+    if order <= 2:
+        np.testing.assert_array_equal(a.multVector(x), b.multVector(x))
+    else:       # (row-thread plan: the order of the adds inside a value is not fixed)
+        np.testing.assert_allclose(a.multVector(x), b.multVector(x), rtol=1e-11, atol=1e-11 * np.abs(ref[0]).max())
+    a.close()
+    b.close()
+
+
 @pytest.mark.parametrize("order", [1, 2, 3])
 def test_tiny_and_empty_inputs(engine, order):
     """one cell (6 tets): a single ragged patch / partial warp in every kernel; an empty face range and an empty
