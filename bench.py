@@ -548,16 +548,19 @@ def gpu_arm(args):
                 "kernel_ms": kms, "zero_fill_ms": zms, "algorithmic_bytes_per_element": Be,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                 "step_frac_vs_peak": Be * nElt_total / world / (ms / args.steps * 1e-3) / 1e9 / peak}
-        fi = fp64_instr_per_element(args)
-        if fi and args.algo in ("auto", "rplan"):
-            # informational: the pipe that bounds this kernel (ncu: DRAM at 5 %, profiles/r2_rplan_summary.md)
-            mhz = (clocks or {}).get("sm_max_mhz") or 1965.0
-            sms = torch.cuda.get_device_properties(local).multi_processor_count
-            pk = sms * 64 * 2 * mhz * 1e6 / 1e12
-            ach = 2.0 * fi * nElt / (kms * 1e-3) / 1e12
-            roof["fp64"] = {"achieved": ach, "peak": pk, "unit": "TFLOP/s", "frac": ach / pk,
-                            "instructions_per_element": fi,
-                            "peak_source": "%d SMs x 64 DFMA/clk x 2 x %.0f MHz (nominal pipe rate, not measured)" % (sms, mhz)}
+        try:
+            fi = fp64_instr_per_element(args)
+            if fi and args.algo in ("auto", "rplan"):
+                # informational: the pipe that bounds this kernel (ncu: DRAM at 5 %, profiles/r2_rplan_summary.md)
+                mhz = float((clocks or {}).get("sm_max_mhz") or 1965.0)
+                sms = torch.cuda.get_device_properties(local).multi_processor_count
+                pk = sms * 64 * 2 * mhz * 1e6 / 1e12
+                ach = 2.0 * fi * nElt / (kms * 1e-3) / 1e12
+                roof["fp64"] = {"achieved": ach, "peak": pk, "unit": "TFLOP/s", "frac": ach / pk,
+                                "instructions_per_element": fi,
+                                "peak_source": "%d SMs x 64 DFMA/clk x 2 x %.0f MHz (nominal pipe rate, not measured)" % (sms, mhz)}
+        except Exception as ex:      # never lose the line over the informational block
+            roof["fp64"] = {"error": str(ex)}
         cpu = None
         # host setup until the steady-state plans stand: mesh + DofTable, graph [partition, local problem], pattern + plans
         setup_s = sum(info.get(k, 0.0) for k in ("mesh_doftable_s", "graph_s", "mesh_partition_s", "local_problem_s")) + \
