@@ -454,7 +454,8 @@ extern "C++" int feelgpu_builder_threads(feelgpu_context_t ctx)
         if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) ndev = 1;
         share = std::min(ctx->nranks, ndev);
     }
-    return std::max(1, hw / share);
+    // (at least 8 where the machine has them: mild oversubscription keeps the cores busy when the ranks finish at different times)
+    return std::max(hw / share, std::min(hw, 8));
 }
 
 // ---- work calls ------------------------------------------------------------------------------------------------
