@@ -20,7 +20,9 @@
 //           array with coalesced stores.  No atomics, no memset; the summation order is fixed by the plan.
 #pragma once
 #include <cstdint>
+#include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #ifndef EPLAN_VS
@@ -99,13 +101,24 @@ struct EPlanRow {                // 16 bytes
     uint32_t len;                // node-level row length
 };
 
+// allocator whose resize() leaves new elements uninitialised: the 2.6 GB blob of a large plan is filled by the builder's
+// threads (first touch in parallel) instead of being zeroed by one of them first
+template <class T>
+struct EPlanNoInit : std::allocator<T> {
+    template <class U> struct rebind { using other = EPlanNoInit<U>; };
+    EPlanNoInit() = default;
+    template <class U> EPlanNoInit(const EPlanNoInit<U>&) {}
+    template <class U> void construct(U* p) noexcept { ::new (static_cast<void*>(p)) U; }
+    template <class U, class... A> void construct(U* p, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A>(a)...); }
+};
+
 struct EPlanHost {
     int order = 0, n = 0, ncomp = 1, omax = 0;
     std::vector<EPlanCta> ctas;
     std::vector<int32_t> verts;
     std::vector<uint32_t> visits;
     std::vector<EPlanChunk> chunks;
-    std::vector<uint32_t> blob;
+    std::vector<uint32_t, EPlanNoInit<uint32_t>> blob;
     std::vector<EPlanRow> rows;
     // statistics
     int64_t ntasks = 0, niters = 0, niters_padded = 0, nvisits = 0, nouts = 0;

@@ -1125,7 +1125,8 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     plan.ctas.resize(nCta);
     plan.chunks.resize(nch);
     plan.rows.resize(nrw);
-    plan.blob.resize(nq * 4 + 64);             // (the 64 trailing words stay zero)
+    plan.blob.resize(nq * 4 + 64);             // (uninitialised: EPlanNoInit; the threads below touch their pieces first)
+    std::memset(plan.blob.data() + nq * 4, 0, 64 * sizeof(uint32_t));
     {
         // thread t built the CTAs [nCta t / nthreads, nCta (t+1) / nthreads): its pieces go behind those of the threads before it
         std::vector<size_t> cb((size_t)nthreads), rb((size_t)nthreads), qb((size_t)nthreads);

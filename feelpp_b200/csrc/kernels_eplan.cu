@@ -489,8 +489,8 @@ size_t eplan_smem_bytes(const EPlan* p, int form)
     return sizeof(double) * ((size_t)nsrec * EPLAN_VS + 3 * EPLAN_VERTS + (size_t)p->omax) + EPLAN_HDRS * sizeof(uint2) + 16 + 4 * sizeof(uint4) + EPLAN_VERTS * (sizeof(int32_t) + sizeof(double));
 }
 
-template <typename T>
-cudaError_t upload(T** d, const std::vector<T>& h, int64_t& bytes)
+template <typename T, typename A>
+cudaError_t upload(T** d, const std::vector<T, A>& h, int64_t& bytes)
 {
     cudaError_t err = cudaMalloc(d, std::max<size_t>(h.size(), 1) * sizeof(T));
     if (err != cudaSuccess) return err;
