@@ -275,7 +275,15 @@ class LocalProblem:
     def _local_graph(self, h, L, is_mine, nnode, loc_nodes, cluster, n):
         ncomp = self.ncomp
         iaA, jaA = self._graph(h, L, nnode)                  # all extended elements: complete rows of owned dofs
-        iaB, jaB = self._graph(h, L[is_mine], nnode)         # my elements only: what I contribute to ghost rows
+        # my elements only: what I contribute to ghost rows.  Only elements that hold a ghost node have a say in those rows,
+        # so the second graph is built over them alone (a rank without ghost nodes -- rank 0 always -- builds none)
+        ghost_node = np.zeros(nnode, dtype=bool)
+        ghost_node[loc_nodes[self.nOwnedNodes:]] = True
+        selB = is_mine & ghost_node[L].any(axis=1)
+        if selB.any():
+            iaB, jaB = self._graph(h, L[selB], nnode)
+        else:
+            iaB, jaB = np.zeros(nnode * ncomp + 1, dtype=np.int64), np.zeros(1, dtype=np.int64)
         rid = (loc_nodes[:, None] * ncomp + np.arange(ncomp)[None, :]).reshape(-1).astype(np.int64)
         colmap = (cluster[:, None] * ncomp + np.arange(ncomp)[None, :]).reshape(-1).astype(np.int64)
         nnew = len(rid)
