@@ -474,7 +474,10 @@ bool eplan_build_host(int order, int ncomp, int omax, int64_t nElt, const int32_
     B.pos = pos;
     if (nRows % ncomp) { plan.error = "entity plan: rows not a multiple of ncomp"; return false; }
     if (omax < 512 || omax > 32767) { plan.error = "entity plan: bad out-buffer size"; return false; }
-    if (nthreads <= 0) nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
+    if (nthreads <= 0) {
+        const char* bt = std::getenv("FEELGPU_BUILD_THREADS");
+        nthreads = bt && std::atoi(bt) > 0 ? std::atoi(bt) : (int)std::max(1u, std::thread::hardware_concurrency());
+    }
     nthreads = std::min(nthreads, 64);
     {
         std::vector<int> bad((size_t)nthreads, 0);

@@ -58,7 +58,11 @@ bool rplan_build_host(int order, int ncomp, int64_t nElt, const int32_t* l2g, in
         std::fprintf(stderr, "rplan build: %-12s %.3f s\n", what, std::chrono::duration<double>(now - tprev).count());
         tprev = now;
     };
-    if (nthreads <= 0) nthreads = (int)std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    if (nthreads <= 0) {
+        const char* bt = std::getenv("FEELGPU_BUILD_THREADS");
+        nthreads = bt && std::atoi(bt) > 0 ? std::atoi(bt) : (int)std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    }
+    nthreads = std::min(nthreads, 64);
     const int n = (order + 1) * (order + 2) * (order + 3) / 6;
     plan.order = order;
     plan.n = n;

@@ -208,3 +208,17 @@ def test_plan_packed_in_pieces_matches_oracle():
     scale = orc.form2(orc.STIFFNESS | orc.ABS_FLAG, 2, 1, quad, mesh.xyz, mesh.conn, Xh.l2g, ia, ja)
     parity.check(a, ref, scale, ia, ja, "eplan host, packed in pieces")
     assert P["stats"]["outputs"] == nnz
+
+
+def test_plan_does_not_depend_on_the_thread_count(monkeypatch):
+    """the builder's stages run on all threads, the pieces of the packing pass depend on the mesh only: the plan of a
+    mesh of several pieces is the same byte for byte with one builder thread and with seven"""
+    mesh = fpp.unitCube(22, 0.15, True)
+    Xh = fpp.Pch(mesh, 2)
+    ia, ja = Xh.graph()
+    plans = []
+    for nt in ("1", "7"):
+        monkeypatch.setenv("FEELGPU_BUILD_THREADS", nt)
+        plans.append(build_plan(mesh, Xh, ia, ja))
+    for k in ("ctas", "verts", "visits", "chunks", "blob", "rows"):
+        assert plans[0][k].tobytes() == plans[1][k].tobytes(), k

@@ -162,3 +162,15 @@ def test_plan_cut_in_pieces_is_complete():
     last = patches["row_off"].astype(np.int64) + patches["nrows"].astype(np.int64) - 1
     assert np.array_equal(patches["nslots"].astype(np.int64), rows["off"].astype(np.int64)[last] + ln[last])
     assert len(np.unique(pid_v * nElt + visits.astype(np.int64))) == len(visits), "an element is visited twice by a patch"
+
+
+def test_plan_does_not_depend_on_the_thread_count(monkeypatch):
+    mesh = fpp.unitCube(22, 0.15, True)
+    Xh = fpp.FunctionSpace(mesh, 2, 1)
+    ia, ja = Xh.graph()
+    plans = []
+    for nt in ("1", "7"):
+        monkeypatch.setenv("FEELGPU_BUILD_THREADS", nt)
+        plans.append(build(Xh, ia, 12288, 384))
+    for a, b in zip(plans[0][:4], plans[1][:4]):
+        assert a.tobytes() == b.tobytes()
